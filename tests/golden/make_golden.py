@@ -1,0 +1,22 @@
+"""Regenerates tests/golden/ from the reference checkout (run in the build container only;
+/root/reference does not exist on the GPU box).  Copies DATA fixtures, never sources:
+  * the committed energy traces Experiments/Results/<Name>/Ih0.txt (6 printed digits) that pin the oracle,
+  * the full-precision input mesh Experiments/Results/BaseCircle/CircleEx12{points,triangles,mask}.txt
+    and BaseCircle/CircleEx6*, BaseCircle3D/3DCircleEx6* used by the FromFile experiments.
+"""
+import json, os, shutil
+REF = "/root/reference/Experiments"
+HERE = os.path.dirname(os.path.abspath(__file__))
+traces = {}
+for name, k in [("Monitor210", 20), ("Monitor220", 34), ("Monitor310", 57), ("Monitor320", 40),
+                ("3DMonitor210", 30), ("3DMonitor220", 12), ("Monitor110", 20)]:
+    p = f"{REF}/Results/{name}/Ih0.txt"
+    if not os.path.exists(p):
+        continue
+    rows = [l.split(",") for l in open(p).read().strip().split("\n")][:k]
+    traces[name] = {"Ih": [float(r[1]) for r in rows], "input": json.load(open(f"{REF}/InputFiles/{name}.json"))}
+json.dump(traces, open(f"{HERE}/ih_traces.json", "w"), indent=1)
+for stem in ["BaseCircle/CircleEx12", "BaseCircle/CircleEx6", "BaseCircle3D/3DCircleEx6"]:
+    for suf in ["points", "triangles", "mask"]:
+        shutil.copy(f"{REF}/Results/{stem}{suf}.txt", f"{HERE}/{os.path.basename(stem)}{suf}.txt")
+print("wrote", sorted(os.listdir(HERE)))
