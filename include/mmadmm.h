@@ -1,0 +1,105 @@
+/* mmadmm.h -- C ABI of the B200-native MM-ADMM implicit-step library (libmmadmm_b200.so).
+ *
+ * This is the drop-in boundary for the hot path of connortannahill/MM-ADMM @ 895f4e3:
+ * the reference's Mesh<D> / MeshIntegrator<D> host classes (re-implemented in
+ * mm-admm_b200/host/) call these entry points instead of Eigen/OpenMP.  Plain pointers and
+ * sizes only; all arrays are caller-owned, row-major / interleaved, FP64 or int32, and are
+ * copied at the call.  Every function returns 0 on success or an MMADMM_E* code; no C++
+ * exception crosses this boundary.  A context is NOT thread-safe; one host thread drives it.
+ *
+ * Layouts:  Vp, Vc, x        P x D   row-major  (x[D*v + l])         reference: interleaved VectorXd x
+ *           F                E x (D+1) row-major                     reference: Eigen::MatrixXi F (values)
+ *           mask             P  ints, NodeType values 0/1/2          reference: src/NodeType.h:4-8
+ *           monVertex        P x D*D row-major flattened tensors     reference: MonitorFunction::evaluateAtVertices
+ *           z, u             E x n   (n = D*(D+1), vertex-major inside an element)
+ *           hessInv          E x n x n row-major
+ */
+#ifndef MMADMM_H
+#define MMADMM_H
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct mmadmm_ctx mmadmm_ctx;
+
+enum {
+    MMADMM_OK = 0,
+    MMADMM_EINVAL = 1,      /* bad argument */
+    MMADMM_ECUDA = 2,       /* CUDA runtime error (see mmadmm_last_error) */
+    MMADMM_EINVERTED = 3,   /* an element with det(E) <= 0 was evaluated; reference: assert(Edet > 0),
+                               src/AdaptationFunctional.cpp:174 */
+    MMADMM_ESINGULAR = 4,   /* singular finite-difference Hessian (reference: Eigen inverse() -> inf/nan) */
+    MMADMM_ENCCL = 5,       /* NCCL error */
+    MMADMM_ENODEVICE = 6    /* no CUDA device: there is no CPU fallback */
+};
+
+/* State selectors for mmadmm_get_state (inspection / parity tests). */
+enum { MMADMM_STATE_Z = 0, MMADMM_STATE_U = 1, MMADMM_STATE_HESSINV = 2, MMADMM_STATE_XBAR = 3,
+       MMADMM_STATE_XPREV = 4, MMADMM_STATE_MONGRID = 5 };
+
+/* Replaces Mesh<D>::Mesh / meshInit (src/Mesh.h:22-25, src/Mesh.cpp:384-472) + MeshIntegrator<D>::MeshIntegrator
+ * (src/MeshIntegrator.cpp:15-62): re-orients F (reOrientElements, src/Mesh.cpp:243-260), builds the monitor
+ * interpolation grid on the device (MeshInterpolator::updateMesh / nearestNeighGridMap / smoothMonitorGrid,
+ * src/MeshInterpolator.cpp:67-130,165-241,365-404), w = 0.5*sqrt(rho) (src/Mesh.cpp:451), hessInvs = I, x = xPrev =
+ * xBar = Vp, z = D x, u = 0, and the diagonal of t = M + dt^2 (WD)^T(WD).  Vc may be NULL (CompMesh false).
+ * `device` is the CUDA device ordinal. */
+int mmadmm_create(int D, int P, int E, const double *Vp, const double *Vc, const int *F, const int *mask,
+                  const double *monVertex, double rho, double tau, double dt, int gradUse, int device,
+                  mmadmm_ctx **out);
+
+/* Replaces MeshIntegrator<D>::step(nIters, tol) (src/MeshIntegrator.cpp:101-191), including Mesh::predictX,
+ * Mesh::prox -> bfgsOptSimplex, the x-update solves and the residual test.  Ih = energy returned by the
+ * reference (sum of the un-regularised element energies at entry to the first prox sweep). */
+int mmadmm_step(mmadmm_ctx *ctx, int nIters, double tol, double *Ih, int *itersTaken, double *primal, double *dual);
+
+/* Replaces MeshIntegrator<D>::getEnergy -> Mesh::computeEnergy (src/Mesh.cpp:496-530). */
+int mmadmm_energy(mmadmm_ctx *ctx, double *I);
+
+/* Replaces Mesh::updateAfterStep / copyX (src/Mesh.cpp:996-1004,1016-1036): current node positions, P x D. */
+int mmadmm_get_x(mmadmm_ctx *ctx, double *x);
+/* Same, but into a caller-provided *device* pointer (no host copy). */
+int mmadmm_get_x_device(mmadmm_ctx *ctx, double *x_dev);
+
+/* The re-oriented connectivity (the reference permutes the caller's F in place). */
+int mmadmm_get_F(mmadmm_ctx *ctx, int *F);
+
+/* Monitor grid geometry: dims = {nx, ny, nz} intervals; axes have nx+1 / ny+1 / nz+1 entries. */
+int mmadmm_grid_dims(mmadmm_ctx *ctx, int *dims);
+
+/* Copy a piece of integrator state to the host in the layouts above (parity tests / debugging). */
+int mmadmm_get_state(mmadmm_ctx *ctx, int which, double *out);
+
+/* evalMonitorOnGrid at npts host points (npts x D) -> npts x D*D   (src/MeshInterpolator.cpp:286-342). */
+int mmadmm_eval_monitor(mmadmm_ctx *ctx, const double *pts, int npts, double *out);
+
+/* Mesh::computeBlockGrad on the context's first `ne` elements with caller-supplied coordinates
+ * (src/Mesh.cpp:755-772 -> src/AdaptationFunctional.cpp:102-287).  zs, dxpu: ne x n. grad/igt may be NULL. */
+int mmadmm_block_grad(mmadmm_ctx *ctx, int ne, const double *zs, const double *dxpu, int computeGrad, int regularize,
+                      int applyMask, double *energy, double *grad, double *igt);
+
+/* Statistics since creation: hist52[k] = number of element-prox solves that ran k BFGS iterations
+ * (k = 51: hit the 50-iteration cap, the reference prints "MAX IN BFGS"); proxCalls = element-prox solves;
+ * admmIters = ADMM iterations executed; kernelLaunches = kernels launched by this library. */
+int mmadmm_get_stats(mmadmm_ctx *ctx, long long *hist52, long long *proxCalls, long long *admmIters,
+                     long long *kernelLaunches);
+
+/* Device time (ms, CUDA events on the library's stream) accumulated per phase since the last reset:
+ * ms[0]=predict, ms[1]=prox kernel, ms[2]=x-update, ms[3]=residual+reduce, ms[4]=hessian init.
+ * Enabled with mmadmm_set_option(ctx, "timing", 1); counts[i] = launches timed. */
+int mmadmm_get_timing(mmadmm_ctx *ctx, double *ms5, long long *counts5, int reset);
+
+/* Options: "timing" (0/1), "stats" (0/1, default 1). */
+int mmadmm_set_option(mmadmm_ctx *ctx, const char *name, int value);
+
+/* The CUDA stream every kernel of this context is launched on (cudaStream_t as void*). */
+void *mmadmm_stream(mmadmm_ctx *ctx);
+
+void mmadmm_destroy(mmadmm_ctx *ctx);
+const char *mmadmm_last_error(mmadmm_ctx *ctx);
+const char *mmadmm_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MMADMM_H */

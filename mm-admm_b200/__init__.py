@@ -1,0 +1,268 @@
+"""mm-admm_b200: B200-native implicit MMPDE step (ADMM) of connortannahill/MM-ADMM.
+
+This module is the Python-side mirror of the reference's host interface for the hot path
+(`Mesh<D>` src/Mesh.h:16-127, `MeshIntegrator<D>` src/MeshIntegrator.h:12-50): same constructor
+arguments, same method names, same return values.  It is a thin ctypes layer over the C ABI in
+include/mmadmm.h (libmmadmm_b200.so, hand-written sm_100a CUDA).  There is NO CPU fallback:
+if the CUDA library is missing or no GPU is present, constructing a MeshIntegrator raises.
+
+The directory name contains a hyphen, so import it with
+    import importlib; mm = importlib.import_module("mm-admm_b200")
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libmmadmm_b200.so")
+HOST_LIB_PATH = os.path.join(_HERE, "libmmadmm_host.so")
+
+BOUNDARY_FREE, BOUNDARY_FIXED, INTERIOR = 0, 1, 2  # src/NodeType.h:4-8
+
+_c_dp = C.POINTER(C.c_double)
+_c_ip = C.POINTER(C.c_int)
+_c_llp = C.POINTER(C.c_longlong)
+
+ERRORS = {1: "EINVAL", 2: "ECUDA", 3: "EINVERTED", 4: "ESINGULAR", 5: "ENCCL", 6: "ENODEVICE"}
+
+# every symbol include/mmadmm.h declares (checked by tests/test_abi.py)
+ABI_SYMBOLS = [
+    "mmadmm_create", "mmadmm_step", "mmadmm_energy", "mmadmm_get_x", "mmadmm_get_x_device", "mmadmm_get_F",
+    "mmadmm_grid_dims", "mmadmm_get_state", "mmadmm_eval_monitor", "mmadmm_block_grad", "mmadmm_get_stats",
+    "mmadmm_get_timing", "mmadmm_set_option", "mmadmm_stream", "mmadmm_destroy", "mmadmm_last_error",
+    "mmadmm_version",
+]
+
+
+class MMADMMError(RuntimeError):
+    pass
+
+
+def _dp(a):
+    return a.ctypes.data_as(_c_dp) if a is not None else None
+
+
+def _ip(a):
+    return a.ctypes.data_as(_c_ip) if a is not None else None
+
+
+_lib = None
+_host = None
+
+
+def lib():
+    """The CUDA library.  Raises (loudly) when it has not been built: there is no fallback path."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise MMADMMError(f"{LIB_PATH} is missing: run `python -c 'import __graft_entry__ as g; g.build()'` "
+                              "(nvcc, sm_100a). mm-admm_b200 has no CPU fallback.")
+        L = C.CDLL(LIB_PATH)
+        vp = C.c_void_p
+        L.mmadmm_create.restype = C.c_int
+        L.mmadmm_create.argtypes = [C.c_int, C.c_int, C.c_int, _c_dp, _c_dp, _c_ip, _c_ip, _c_dp, C.c_double, C.c_double,
+                                    C.c_double, C.c_int, C.c_int, C.POINTER(vp)]
+        L.mmadmm_step.argtypes = [vp, C.c_int, C.c_double, _c_dp, _c_ip, _c_dp, _c_dp]
+        L.mmadmm_energy.argtypes = [vp, _c_dp]
+        L.mmadmm_get_x.argtypes = [vp, _c_dp]
+        L.mmadmm_get_x_device.argtypes = [vp, vp]
+        L.mmadmm_get_F.argtypes = [vp, _c_ip]
+        L.mmadmm_grid_dims.argtypes = [vp, _c_ip]
+        L.mmadmm_get_state.argtypes = [vp, C.c_int, _c_dp]
+        L.mmadmm_eval_monitor.argtypes = [vp, _c_dp, C.c_int, _c_dp]
+        L.mmadmm_block_grad.argtypes = [vp, C.c_int, _c_dp, _c_dp, C.c_int, C.c_int, C.c_int, _c_dp, _c_dp, _c_dp]
+        L.mmadmm_get_stats.argtypes = [vp, _c_llp, _c_llp, _c_llp, _c_llp]
+        L.mmadmm_get_timing.argtypes = [vp, _c_dp, _c_llp, C.c_int]
+        L.mmadmm_set_option.argtypes = [vp, C.c_char_p, C.c_int]
+        L.mmadmm_stream.restype = vp
+        L.mmadmm_stream.argtypes = [vp]
+        L.mmadmm_destroy.restype = None
+        L.mmadmm_destroy.argtypes = [vp]
+        L.mmadmm_last_error.restype = C.c_char_p
+        L.mmadmm_last_error.argtypes = [vp]
+        L.mmadmm_version.restype = C.c_char_p
+        _lib = L
+    return _lib
+
+
+def host_lib():
+    global _host
+    if _host is None:
+        if not os.path.exists(HOST_LIB_PATH):
+            raise MMADMMError(f"{HOST_LIB_PATH} is missing: run __graft_entry__.build()")
+        H = C.CDLL(HOST_LIB_PATH)
+        H.mmadmm_host_monitor_eval.argtypes = [C.c_int, C.c_int, C.c_int, _c_dp, _c_dp]
+        H.mmadmm_host_uniform_rect_mesh.argtypes = [C.c_int] * 4 + [C.c_double] * 6 + [C.c_int, _c_dp, _c_ip, _c_ip]
+        _host = H
+    return _host
+
+
+# --------------------------------------------------------------------------------------------------
+# host helpers (mesh generators / monitors of the reference driver; init-time only)
+# --------------------------------------------------------------------------------------------------
+def generate_uniform_rect_mesh(D, nx, ny, nz=0, box=(0, 1, 0, 1, 0, 1), boundary_type=BOUNDARY_FIXED):
+    """utils::generateUniformRectMesh<D> (src/MeshUtils.h:82-335) -> (Vp[P,D], F[E,D+1] int32, mask[P] int32)."""
+    if D == 2:
+        P, E = (nx + 1) * (ny + 1) + nx * ny, 4 * nx * ny
+    else:
+        P, E = (nx + 1) * (ny + 1) * (nz + 1) + nx * ny * nz, 12 * nx * ny * nz
+    Vp = np.zeros((P, D))
+    F = np.zeros((E, D + 1), dtype=np.int32)
+    mask = np.zeros(P, dtype=np.int32)
+    rc = host_lib().mmadmm_host_uniform_rect_mesh(D, nx, ny, nz, *[float(b) for b in box], boundary_type,
+                                                  _dp(Vp), _ip(F), _ip(mask))
+    if rc:
+        raise MMADMMError("bad mesh parameters")
+    return Vp, F, mask
+
+
+class TestMonitor:
+    """One of the reference's analytic monitors (Experiments/TestMonitors/MEx*.h) by its main.cpp slot number."""
+
+    def __init__(self, D, kind):
+        self.D, self.kind = D, kind
+
+    def evaluate_at_vertices(self, X):
+        X = np.ascontiguousarray(X, dtype=np.float64)
+        out = np.zeros((X.shape[0], self.D * self.D))
+        rc = host_lib().mmadmm_host_monitor_eval(self.D, self.kind, X.shape[0], _dp(X), _dp(out))
+        if rc:
+            raise MMADMMError(f"no monitor {self.kind} in {self.D}D")
+        return out
+
+
+# --------------------------------------------------------------------------------------------------
+# Mesh / MeshIntegrator mirrors
+# --------------------------------------------------------------------------------------------------
+class Mesh:
+    """Mirror of `Mesh<D>` (src/Mesh.h:22-25).  Holds caller-visible `Vp` (updated by the integrator like the
+    reference's updateAfterStep does) and `F` (re-oriented in place at integrator construction, like
+    reOrientElements).  `monitor` is an object with evaluate_at_vertices(X)->(P,D*D), or the table itself."""
+
+    def __init__(self, Vp, F, boundary_mask, monitor, num_threads=1, rho=1.0, w=0.0, tau=1.0, integration_mode=0,
+                 grad_use=False, Vc=None):
+        self.Vp = np.ascontiguousarray(Vp, dtype=np.float64)
+        self.P, self.D = self.Vp.shape
+        if self.D not in (2, 3):
+            raise ValueError("D must be 2 or 3")
+        self.F = np.ascontiguousarray(F, dtype=np.int32)
+        self.E = self.F.shape[0]
+        self.boundary_mask = np.ascontiguousarray(boundary_mask, dtype=np.int32)[: self.P].copy()
+        self.Vc = None if Vc is None else np.ascontiguousarray(Vc, dtype=np.float64)
+        self.compMesh = Vc is not None
+        self.rho, self.tau, self.gradUse = float(rho), float(tau), bool(grad_use)
+        self.w_json = w  # ignored, as in the reference (src/Mesh.cpp:451 overrides it with 0.5*sqrt(rho))
+        self.integrationMode = integration_mode
+        if integration_mode != 0:
+            raise NotImplementedError("only Method 0 (ADMM) is built; Methods 1/2 are out of scope (SURVEY.md 8)")
+        mon = monitor.evaluate_at_vertices(self.Vp) if hasattr(monitor, "evaluate_at_vertices") else monitor
+        self.mon_vertex = np.ascontiguousarray(mon, dtype=np.float64).reshape(self.P, self.D * self.D)
+
+    def getNPnts(self):
+        return self.P
+
+
+class MeshIntegrator:
+    """Mirror of `MeshIntegrator<D>` (src/MeshIntegrator.h:15-27): step / getEnergy / done."""
+
+    def __init__(self, dt, mesh, device=0, sync_vp=True):
+        self.mesh, self.dt = mesh, float(dt)
+        self.sync_vp = sync_vp
+        self.L = lib()
+        self.h = C.c_void_p()
+        m = mesh
+        rc = self.L.mmadmm_create(m.D, m.P, m.E, _dp(m.Vp), _dp(m.Vc), _ip(m.F), _ip(m.boundary_mask), _dp(m.mon_vertex),
+                                  m.rho, m.tau, self.dt, int(m.gradUse), device, C.byref(self.h))
+        self._check(rc)
+        self._check(self.L.mmadmm_get_F(self.h, _ip(m.F)))  # the reference permutes the caller's F in place
+        self.n = m.D * (m.D + 1)
+        self.last = {}
+
+    def _check(self, rc):
+        if rc:
+            msg = self.L.mmadmm_last_error(self.h).decode() if self.h else ""
+            raise MMADMMError(f"mmadmm error {ERRORS.get(rc, rc)}: {msg}")
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.L.mmadmm_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def step(self, nIters, tol=1e-3):
+        Ih = C.c_double(); it = C.c_int(); pr = C.c_double(); du = C.c_double()
+        self._check(self.L.mmadmm_step(self.h, int(nIters), float(tol), C.byref(Ih), C.byref(it), C.byref(pr), C.byref(du)))
+        self.last = dict(Ih=Ih.value, iters=it.value, primal=pr.value, dual=du.value)
+        if self.sync_vp:  # Mesh::updateAfterStep writes the caller's Vp every step (src/Mesh.cpp:1030-1035)
+            self._check(self.L.mmadmm_get_x(self.h, _dp(self.mesh.Vp)))
+        return Ih.value
+
+    def getEnergy(self):
+        v = C.c_double()
+        self._check(self.L.mmadmm_energy(self.h, C.byref(v)))
+        return v.value
+
+    def done(self):
+        self._check(self.L.mmadmm_get_x(self.h, _dp(self.mesh.Vp)))
+
+    # ---- inspection (parity tests) ----
+    def x(self):
+        out = np.zeros((self.mesh.P, self.mesh.D))
+        self._check(self.L.mmadmm_get_x(self.h, _dp(out)))
+        return out
+
+    def state(self, which):
+        m = self.mesh
+        sizes = {0: (m.E, self.n), 1: (m.E, self.n), 2: (m.E, self.n, self.n), 3: (m.P, m.D), 4: (m.P, m.D)}
+        if which == 5:
+            nx, ny, nz = self.grid_dims()
+            shape = ((nx + 1) * (ny + 1) * ((nz + 1) if m.D == 3 else 1), m.D * m.D)
+        else:
+            shape = sizes[which]
+        out = np.zeros(shape)
+        self._check(self.L.mmadmm_get_state(self.h, which, _dp(out)))
+        return out
+
+    def grid_dims(self):
+        d = np.zeros(3, dtype=np.int32)
+        self._check(self.L.mmadmm_grid_dims(self.h, _ip(d)))
+        return tuple(int(v) for v in d)
+
+    def eval_monitor(self, pts):
+        pts = np.ascontiguousarray(pts, dtype=np.float64)
+        out = np.zeros((pts.shape[0], self.mesh.D ** 2))
+        self._check(self.L.mmadmm_eval_monitor(self.h, _dp(pts), pts.shape[0], _dp(out)))
+        return out
+
+    def block_grad(self, zs, dxpu=None, compute_grad=True, regularize=False, apply_mask=False):
+        zs = np.ascontiguousarray(zs, dtype=np.float64)
+        ne = zs.shape[0]
+        dx = None if dxpu is None else np.ascontiguousarray(dxpu, dtype=np.float64)
+        en = np.zeros(ne); g = np.zeros((ne, self.n)); igt = np.zeros(ne)
+        self._check(self.L.mmadmm_block_grad(self.h, ne, _dp(zs), _dp(dx), int(compute_grad), int(regularize),
+                                             int(apply_mask), _dp(en), _dp(g), _dp(igt)))
+        return en, g, igt
+
+    def stats(self):
+        hist = (C.c_longlong * 52)(); pc = C.c_longlong(); ai = C.c_longlong(); kl = C.c_longlong()
+        self._check(self.L.mmadmm_get_stats(self.h, hist, C.byref(pc), C.byref(ai), C.byref(kl)))
+        return dict(bfgs_hist=np.array(list(hist), dtype=np.int64), prox_calls=pc.value, admm_iters=ai.value,
+                    kernel_launches=kl.value)
+
+    def set_option(self, name, value):
+        self._check(self.L.mmadmm_set_option(self.h, name.encode(), int(value)))
+
+    def timing(self, reset=False):
+        ms = (C.c_double * 5)(); cnt = (C.c_longlong * 5)()
+        self._check(self.L.mmadmm_get_timing(self.h, ms, cnt, int(reset)))
+        names = ["predict", "prox", "xupdate", "residual", "hess_init"]
+        return {k: (ms[i], cnt[i]) for i, k in enumerate(names)}
+
+    def stream(self):
+        return self.L.mmadmm_stream(self.h)

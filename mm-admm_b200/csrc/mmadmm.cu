@@ -1,0 +1,1220 @@
+// libmmadmm_b200: hand-written FP64 sm_100a kernels + C ABI for the MM-ADMM implicit step.
+// See include/mmadmm.h for the boundary and DESIGN.md for the data layout and the roofline of each kernel.
+//
+// Hot path per ADMM iteration (reference src/MeshIntegrator.cpp:144-172):
+//   k_prox      K1+K2+K3a  DXpU = D x + u (gather), per-element BFGS prox (Mesh::bfgsOptSimplex,
+//                          src/Mesh.cpp:777-872), u = DXpU - z, ||z - zPrev||^2 and sum(Ih) partials
+//   k_xupdate   K3b+K4     vec = tau*xBar + dt^2 WD^T(w (z-u)) by vertex->element incidence gather (deterministic),
+//                          x = vec / diag(t)  (t is numerically diagonal)
+//   k_residual  K5         ||D x - z||^2 partials;  k_finalize reduces the three scalars in a fixed order
+// Element state is SoA over elements (component-major planes of length E) so every warp access is
+// one contiguous 256-byte line.
+#include <cuda_runtime.h>
+#include <cub/cub.cuh>
+
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <limits>
+#include <string>
+#include <vector>
+
+#include "../../include/mmadmm.h"
+#include "mmadmm_device.cuh"
+
+using namespace mmadmm;
+
+#define CK(call)                                                                                      \
+    do {                                                                                              \
+        cudaError_t _e = (call);                                                                      \
+        if (_e != cudaSuccess) {                                                                      \
+            char _b[512];                                                                             \
+            snprintf(_b, sizeof(_b), "%s:%d: %s -> %s", __FILE__, __LINE__, #call, cudaGetErrorString(_e)); \
+            ctx->err = _b;                                                                            \
+            return MMADMM_ECUDA;                                                                      \
+        }                                                                                             \
+    } while (0)
+
+namespace {
+
+constexpr int TPB = 128;       // element kernels: threads per block
+constexpr int TPB_V = 256;     // vertex kernels
+constexpr int MAXV = 4;        // D+1 <= 4
+
+template <int D> struct ElemArgs {
+    int E, P;
+    const int *F[MAXV];          // connectivity planes F[v][e]
+    const uint8_t *fixedBits;    // bit v: vertex v of the element is BOUNDARY_FIXED
+    const uint8_t *nonIntBits;   // bit v: vertex v is not INTERIOR
+    const double *x;             // P x D interleaved
+    const double *Vc;            // P x D or null
+    double *z, *u, *B;           // SoA planes of length E: z[n], u[n], B[n*n]
+    MonGrid mg;
+    FuncConsts<D> fc;
+    int compMesh;
+    double tol;
+    double *partIh, *partDual;   // per-block partial sums
+    unsigned long long *hist;    // 52 bins (may be null)
+    unsigned *status;
+};
+
+template <int D> __device__ __forceinline__ void gather_vertex(const double *x, int v, double *out) {
+    if (D == 2) {
+        double2 t = __ldg(reinterpret_cast<const double2 *>(x) + v);
+        out[0] = t.x; out[1] = t.y;
+    } else {
+        const double *p = x + (size_t)3 * v;
+        out[0] = __ldg(p); out[1] = __ldg(p + 1); out[2] = __ldg(p + 2);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// init kernels
+// ------------------------------------------------------------------------------------------------
+// reOrientElements (src/Mesh.cpp:243-260) + transpose of F to planes + per-element mask bits
+template <int D>
+__global__ void k_setup_F(int E, const int *Frow, int *F0, int *F1, int *F2, int *F3, const double *x,
+                          const uint8_t *mask, uint8_t *fixedBits, uint8_t *nonIntBits) {
+    int e = blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= E) return;
+    int f[D + 1];
+#pragma unroll
+    for (int v = 0; v < D + 1; v++) f[v] = Frow[(size_t)e * (D + 1) + v];
+    double p0[D];
+    gather_vertex<D>(x, f[0], p0);
+    SMat<D> Em;
+#pragma unroll
+    for (int j = 0; j < D; j++) {
+        double pj[D];
+        gather_vertex<D>(x, f[j + 1], pj);
+#pragma unroll
+        for (int l = 0; l < D; l++) Em(l, j) = pj[l] - p0[l];
+    }
+    if (sdet<D>(Em) < 0) { int t = f[2]; f[2] = f[1]; f[1] = t; }
+    F0[e] = f[0]; F1[e] = f[1]; F2[e] = f[2];
+    if (D == 3) F3[e] = f[D];
+    unsigned fb = 0, nb = 0;
+#pragma unroll
+    for (int v = 0; v < D + 1; v++) {
+        int m = mask[f[v]];
+        if (m == NT_BOUNDARY_FIXED) fb |= 1u << v;
+        if (m != NT_INTERIOR) nb |= 1u << v;
+    }
+    fixedBits[e] = (uint8_t)fb;
+    nonIntBits[e] = (uint8_t)nb;
+}
+
+// keys/vals for the vertex->(element,local vertex) incidence; slot id = e*4 + v
+template <int D> __global__ void k_inc_pairs(int E, const int *F0, const int *F1, const int *F2, const int *F3, int *keys, int *vals) {
+    int e = blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= E) return;
+    const int *F[4] = {F0, F1, F2, F3};
+#pragma unroll
+    for (int v = 0; v < D + 1; v++) {
+        keys[(size_t)e * (D + 1) + v] = F[v][e];
+        vals[(size_t)e * (D + 1) + v] = e * 4 + v;
+    }
+}
+__global__ void k_count_keys(size_t n, const int *keys, int *cnt) {
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) atomicAdd(&cnt[keys[i]], 1);
+}
+// diag(t) = tau + dt^2 * sum_{valence} (w*w)*1.0     (src/MeshIntegrator.cpp:45-51)
+__global__ void k_tdiag(int P, const int *incPtr, double m, double dtsq, double w, double *tdiag) {
+    int p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= P) return;
+    double s = 0.0;
+    int cnt = incPtr[p + 1] - incPtr[p];
+    for (int k = 0; k < cnt; k++) s += (w * w) * 1.0;
+    tdiag[p] = m + dtsq * s;
+}
+
+// ---- monitor grid: exact 1-NN of every grid point among the mesh vertices (uniform bins), then Jacobi smoothing
+struct BinGeom { int nb[3]; double lo[3], inv[3], minbw; int maxr; };
+
+template <int D> __global__ void k_bin_ids(int P, const double *x, BinGeom bg, int *bin, int *ids) {
+    int p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= P) return;
+    int c[3] = {0, 0, 0};
+#pragma unroll
+    for (int l = 0; l < D; l++) {
+        int k = (int)((x[(size_t)p * D + l] - bg.lo[l]) * bg.inv[l]);
+        c[l] = min(max(k, 0), bg.nb[l] - 1);
+    }
+    bin[p] = (c[2] * bg.nb[1] + c[1]) * bg.nb[0] + c[0];
+    ids[p] = p;
+}
+
+// one thread per grid point; rings of bins outwards until the best candidate is provably nearest.
+// Distances use explicit non-fused arithmetic so that exact ties are exact on every platform; ties -> lowest index.
+template <int D>
+__global__ void k_nn_grid(MonGrid mg, double *gridOut, const double *x, const double *monVertex, BinGeom bg,
+                          const int *binStart, const int *items) {
+    const int nx = mg.nx, ny = mg.ny, nz = (D == 3) ? mg.nz : 0;
+    size_t total = (size_t)(nx + 1) * (ny + 1) * (nz + 1);
+    size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= total) return;
+    int i = (int)(t % (nx + 1));
+    int j = (int)((t / (nx + 1)) % (ny + 1));
+    int k3 = (int)(t / ((size_t)(nx + 1) * (ny + 1)));
+    double q[3] = {mg.ax[i], mg.ay[j], (D == 3) ? mg.az[k3] : 0.0};
+    int c[3] = {0, 0, 0};
+#pragma unroll
+    for (int l = 0; l < D; l++) {
+        int k = (int)((q[l] - bg.lo[l]) * bg.inv[l]);
+        c[l] = min(max(k, 0), bg.nb[l] - 1);
+    }
+    int best = -1;
+    double bestd = INFINITY;
+    for (int r = 0; r <= bg.maxr; r++) {
+        int z0 = (D == 3) ? c[2] - r : 0, z1 = (D == 3) ? c[2] + r : 0;
+        for (int kz = z0; kz <= z1; kz++) {
+            if (kz < 0 || kz >= bg.nb[2]) continue;
+            for (int ky = c[1] - r; ky <= c[1] + r; ky++) {
+                if (ky < 0 || ky >= bg.nb[1]) continue;
+                bool edgeRow = (abs(ky - c[1]) == r) || (D == 3 && abs(kz - c[2]) == r);
+                int step = edgeRow ? 1 : max(2 * r, 1);  // interior rows of the shell: only the two end bins
+                for (int kx = c[0] - r; kx <= c[0] + r; kx += step) {
+                    if (kx < 0 || kx >= bg.nb[0]) continue;
+                    size_t b = ((size_t)kz * bg.nb[1] + ky) * bg.nb[0] + kx;
+                    for (int s = binStart[b]; s < binStart[b + 1]; s++) {
+                        int p = items[s];
+                        double d2 = 0.0;
+#pragma unroll
+                        for (int l = 0; l < D; l++) {
+                            double df = __dsub_rn(q[l], x[(size_t)p * D + l]);
+                            d2 = __dadd_rn(d2, __dmul_rn(df, df));
+                        }
+                        if (d2 < bestd || (d2 == bestd && p < best)) { bestd = d2; best = p; }
+                    }
+                }
+            }
+        }
+        if (best >= 0) {
+            double reach = r * bg.minbw;
+            if (bestd < reach * reach) break;
+        }
+    }
+    // 2D: row j*(nx+1)+i.  3D (sic, reference :198,234): row (nx+1)(ny+1)k + i*(nx+1) + j, i.e. transposed in x<->y
+    size_t row = (D == 2) ? ((size_t)j * (nx + 1) + i) : ((size_t)(nx + 1) * (ny + 1) * k3 + (size_t)i * (nx + 1) + j);
+    constexpr int DD = D * D;
+#pragma unroll
+    for (int k = 0; k < DD; k++) gridOut[row * DD + k] = monVertex[(size_t)best * DD + k];
+}
+
+// smoothMonitorGrid (src/MeshInterpolator.cpp:365-404): Jacobi sweep from `src` into `dst`, interior nodes only
+template <int D> __global__ void k_smooth(int nx, int ny, int nz, const double *src, double *dst) {
+    constexpr int DD = D * D;
+    size_t rows = (size_t)(nx + 1) * (ny + 1) * ((D == 3) ? (nz + 1) : 1);
+    size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= rows * DD) return;
+    size_t row = t / DD;
+    int k = (int)(t % DD);
+    int i = (int)(row % (nx + 1));
+    int j = (int)((row / (nx + 1)) % (ny + 1));
+    int k3 = (int)(row / ((size_t)(nx + 1) * (ny + 1)));
+    bool interior = (i >= 1 && i < nx && j >= 1 && j < ny) && (D == 2 || (k3 >= 1 && k3 < nz));
+    if (!interior) return;
+    size_t sx = DD, sy = (size_t)(nx + 1) * DD, sz = (size_t)(nx + 1) * (ny + 1) * DD;
+    const double *c = src + row * DD + k;
+    double v;
+    // explicit non-fused arithmetic: the grid is input data for everything downstream, keep it bit-reproducible
+    if (D == 2) {
+        v = __dmul_rn(0.6, c[0]);
+        v = __dadd_rn(v, __dmul_rn(0.1, c[sx]));
+        v = __dadd_rn(v, __dmul_rn(0.1, *(c - sx)));
+        v = __dadd_rn(v, __dmul_rn(0.1, c[sy]));
+        v = __dadd_rn(v, __dmul_rn(0.1, *(c - sy)));
+    } else {
+        const double h = 0.4 / 6.0;
+        v = __dmul_rn(0.6, c[0]);
+        v = __dadd_rn(v, __dmul_rn(h, c[sx]));
+        v = __dadd_rn(v, __dmul_rn(h, *(c - sx)));
+        v = __dadd_rn(v, __dmul_rn(h, c[sy]));
+        v = __dadd_rn(v, __dmul_rn(h, *(c - sy)));
+        v = __dadd_rn(v, __dmul_rn(h, c[sz]));
+        v = __dadd_rn(v, __dmul_rn(h, *(c - sz)));
+    }
+    dst[row * DD + k] = v;
+}
+
+// ------------------------------------------------------------------------------------------------
+// element kernels
+// ------------------------------------------------------------------------------------------------
+template <int D> __device__ __forceinline__ void load_elem_ids(const ElemArgs<D> &a, int e, int *vid) {
+#pragma unroll
+    for (int v = 0; v < D + 1; v++) vid[v] = __ldg(a.F[v] + e);
+}
+template <int D> __device__ __forceinline__ void load_xi(const ElemArgs<D> &a, const int *vid, double *xi) {
+    if (a.compMesh) {
+#pragma unroll
+        for (int v = 0; v < D + 1; v++) gather_vertex<D>(a.Vc, vid[v], xi + D * v);
+    }
+}
+
+// K8: Mesh::computeEnergy (src/Mesh.cpp:496-530); coordinates gathered from `x`
+template <int D> __global__ void __launch_bounds__(TPB) k_energy(ElemArgs<D> a, double *part) {
+    constexpr int n = D * (D + 1);
+    __shared__ double red[32];
+    int e = blockIdx.x * TPB + threadIdx.x;
+    double en = 0.0;
+    if (e < a.E) {
+        int vid[D + 1];
+        load_elem_ids<D>(a, e, vid);
+        double z[n], xi[n], g[n];
+#pragma unroll
+        for (int v = 0; v < D + 1; v++) gather_vertex<D>(a.x, vid[v], z + D * v);
+        load_xi<D>(a, vid, xi);
+        bool inv = false;
+        en = block_grad<D, false>(z, xi, a.compMesh, a.mg, a.fc, g, inv);
+        if (inv) atomicOr(a.status, ST_INVERTED);
+    }
+    double s = block_sum(en, red);
+    if (threadIdx.x == 0) part[blockIdx.x] = s;
+}
+
+// K6a: element part of Mesh::eulerGrad (src/Mesh.cpp:582-624): masked, un-regularised element gradients -> scratch planes
+template <int D> __global__ void __launch_bounds__(TPB) k_euler_elem(ElemArgs<D> a, double *gs) {
+    constexpr int n = D * (D + 1);
+    int e = blockIdx.x * TPB + threadIdx.x;
+    if (e >= a.E) return;
+    int vid[D + 1];
+    load_elem_ids<D>(a, e, vid);
+    double z[n], xi[n], g[n];
+#pragma unroll
+    for (int v = 0; v < D + 1; v++) gather_vertex<D>(a.x, vid[v], z + D * v);
+    load_xi<D>(a, vid, xi);
+    bool inv = false;
+    block_grad<D, true>(z, xi, a.compMesh, a.mg, a.fc, g, inv);
+    if (inv) atomicOr(a.status, ST_INVERTED);
+    unsigned fb = a.fixedBits[e];
+#pragma unroll
+    for (int v = 0; v < D + 1; v++)
+#pragma unroll
+        for (int l = 0; l < D; l++) gs[(size_t)(D * v + l) * a.E + e] = (fb & (1u << v)) ? 0.0 : g[D * v + l];
+}
+
+// first prox sweep only (hessComputed == false): finite-difference Hessian of the regularised, masked gradient,
+// unit diagonal on non-interior vertices, general inverse by partial-pivot LU (src/Mesh.cpp:793-817).
+template <int D> __global__ void __launch_bounds__(TPB) k_hess_init(ElemArgs<D> a) {
+    constexpr int n = D * (D + 1);
+    int e = blockIdx.x * TPB + threadIdx.x;
+    if (e >= a.E) return;
+    int vid[D + 1];
+    load_elem_ids<D>(a, e, vid);
+    unsigned fb = a.fixedBits[e], nb = a.nonIntBits[e];
+    double z[n], dx[n], xi[n], Gk[n], G1[n];
+#pragma unroll
+    for (int v = 0; v < D + 1; v++) gather_vertex<D>(a.x, vid[v], dx + D * v);
+#pragma unroll
+    for (int k = 0; k < n; k++) {
+        dx[k] += a.u[(size_t)k * a.E + e];
+        z[k] = a.z[(size_t)k * a.E + e];
+    }
+    load_xi<D>(a, vid, xi);
+    bool inv = false;
+    prox_grad<D>(z, dx, xi, a.compMesh, a.mg, a.fc, fb, Gk, inv);
+    const double h = 2.0 * 1.4901161193847656e-08;  // 2*sqrt(DBL_EPSILON)
+    double H[n * n];
+    for (int i = 0; i < n; i++) {
+        double zp[n];
+#pragma unroll
+        for (int k = 0; k < n; k++) zp[k] = (k == i) ? (z[k] + h) : z[k];
+        prox_grad<D>(zp, dx, xi, a.compMesh, a.mg, a.fc, fb, G1, inv);
+#pragma unroll
+        for (int r = 0; r < n; r++) H[r * n + i] = (G1[r] - Gk[r]) / h;
+    }
+    if (inv) atomicOr(a.status, ST_INVERTED);
+    for (int v = 0; v < D + 1; v++)
+        if (nb & (1u << v))
+            for (int l = 0; l < D; l++) H[(D * v + l) * n + (D * v + l)] = 1.0;
+    // partial-pivot LU in place
+    int perm[n];
+    for (int i = 0; i < n; i++) perm[i] = i;
+    bool singular = false;
+    for (int k = 0; k < n; k++) {
+        int piv = k;
+        double best = fabs(H[k * n + k]);
+        for (int i = k + 1; i < n; i++) {
+            double v = fabs(H[i * n + k]);
+            if (v > best) { best = v; piv = i; }
+        }
+        if (best == 0.0) { singular = true; break; }
+        if (piv != k) {
+            for (int j = 0; j < n; j++) { double t = H[k * n + j]; H[k * n + j] = H[piv * n + j]; H[piv * n + j] = t; }
+            int t = perm[k]; perm[k] = perm[piv]; perm[piv] = t;
+        }
+        for (int i = k + 1; i < n; i++) H[i * n + k] /= H[k * n + k];
+        for (int i = k + 1; i < n; i++) {
+            double l = H[i * n + k];
+            for (int j = k + 1; j < n; j++) H[i * n + j] -= l * H[k * n + j];
+        }
+    }
+    if (singular) { atomicOr(a.status, ST_SINGULAR_HESS); return; }
+    for (int c = 0; c < n; c++) {
+        double y[n];
+        for (int i = 0; i < n; i++) {
+            double s = (perm[i] == c) ? 1.0 : 0.0;
+            for (int j = 0; j < i; j++) s -= H[i * n + j] * y[j];
+            y[i] = s;
+        }
+        for (int i = n - 1; i >= 0; i--) {
+            double s = y[i];
+            for (int j = i + 1; j < n; j++) s -= H[i * n + j] * y[j];
+            y[i] = s / H[i * n + i];
+        }
+        for (int i = 0; i < n; i++) a.B[(size_t)(i * n + c) * a.E + e] = y[i];
+    }
+}
+
+// K1+K2+K3a: the per-element BFGS prox (thread per element; B held in registers for D=2)
+template <int D> __global__ void __launch_bounds__(TPB) k_prox(ElemArgs<D> a) {
+    constexpr int n = D * (D + 1);
+    __shared__ double red[32];
+    __shared__ int shist[52];
+    if (a.hist) {
+        if (threadIdx.x < 52) shist[threadIdx.x] = 0;
+        __syncthreads();
+    }
+    const int e = blockIdx.x * TPB + threadIdx.x;
+    double ih = 0.0, dual2 = 0.0;
+    if (e < a.E) {
+        const size_t E = a.E;
+        int vid[D + 1];
+        load_elem_ids<D>(a, e, vid);
+        const unsigned fb = a.fixedBits[e];
+        double z[n], dx[n], xi[n], Gk[n], G1[n], zold[n];
+#pragma unroll
+        for (int v = 0; v < D + 1; v++) gather_vertex<D>(a.x, vid[v], dx + D * v);
+#pragma unroll
+        for (int k = 0; k < n; k++) {
+            dx[k] += a.u[k * E + e];          // DXpU = D x + u
+            z[k] = a.z[k * E + e];
+            zold[k] = z[k];
+        }
+        load_xi<D>(a, vid, xi);
+        double B[n * n];
+#pragma unroll
+        for (int k = 0; k < n * n; k++) B[k] = a.B[k * E + e];
+        bool inv = false;
+        ih = prox_grad<D>(z, dx, xi, a.compMesh, a.mg, a.fc, fb, Gk, inv);   // Ihsave: energy at entry
+        int iter;
+        for (iter = 0; iter < 50; iter++) {
+            double pk[n];
+#pragma unroll
+            for (int r = 0; r < n; r++) {
+                double s = B[r * n] * Gk[0];
+#pragma unroll
+                for (int c = 1; c < n; c++) s += B[r * n + c] * Gk[c];
+                pk[r] = -s;
+                z[r] += pk[r];
+            }
+            prox_grad<D>(z, dx, xi, a.compMesh, a.mg, a.fc, fb, G1, inv);
+            double Ix = 0.0, yk[n];
+#pragma unroll
+            for (int k = 0; k < n; k++) { Ix += fabs(G1[k]); yk[k] = G1[k] - Gk[k]; }
+            double c2 = pk[0] * yk[0];
+#pragma unroll
+            for (int k = 1; k < n; k++) c2 += pk[k] * yk[k];
+            double By[n], yB[n];
+#pragma unroll
+            for (int r = 0; r < n; r++) {
+                double s = B[r * n] * yk[0];
+#pragma unroll
+                for (int c = 1; c < n; c++) s += B[r * n + c] * yk[c];
+                By[r] = s;
+            }
+#pragma unroll
+            for (int c = 0; c < n; c++) {
+                double s = yk[0] * B[c];
+#pragma unroll
+                for (int r = 1; r < n; r++) s += yk[r] * B[r * n + c];
+                yB[c] = s;
+            }
+            double yBy = yk[0] * By[0];
+#pragma unroll
+            for (int k = 1; k < n; k++) yBy += yk[k] * By[k];
+            const double ic2 = 1.0 / c2;
+            const double c1 = (c2 + yBy) * (ic2 * ic2);
+#pragma unroll
+            for (int r = 0; r < n; r++) {
+                const double a1 = c1 * pk[r], a3 = pk[r] * ic2, a2 = By[r] * ic2;
+#pragma unroll
+                for (int c = 0; c < n; c++) B[r * n + c] += (a1 * pk[c] - a2 * pk[c]) - a3 * yB[c];
+            }
+#pragma unroll
+            for (int k = 0; k < n; k++) Gk[k] = G1[k];
+            if (Ix < a.tol) break;
+        }
+        if (inv) atomicOr(a.status, ST_INVERTED);
+        if (iter == 50) atomicOr(a.status, ST_BFGS_MAX);
+        if (a.hist) atomicAdd(&shist[(iter == 50) ? 51 : iter + 1], 1);
+#pragma unroll
+        for (int k = 0; k < n; k++) {
+            a.z[k * E + e] = z[k];
+            a.u[k * E + e] = dx[k] - z[k];    // u = DXpU - z
+            double dz = z[k] - zold[k];
+            dual2 += dz * dz;
+        }
+#pragma unroll
+        for (int k = 0; k < n * n; k++) a.B[k * E + e] = B[k];
+    }
+    double s1 = block_sum(ih, red);
+    double s2 = block_sum(dual2, red);
+    if (threadIdx.x == 0) { a.partIh[blockIdx.x] = s1; a.partDual[blockIdx.x] = s2; }
+    if (a.hist) {
+        __syncthreads();
+        if (threadIdx.x < 52 && shist[threadIdx.x]) atomicAdd(&a.hist[threadIdx.x], (unsigned long long)shist[threadIdx.x]);
+    }
+}
+
+// z = D * src (gather), src is a P x D vertex vector
+template <int D> __global__ void __launch_bounds__(TPB) k_applyD(ElemArgs<D> a, const double *src) {
+    int e = blockIdx.x * TPB + threadIdx.x;
+    if (e >= a.E) return;
+    int vid[D + 1];
+    load_elem_ids<D>(a, e, vid);
+#pragma unroll
+    for (int v = 0; v < D + 1; v++) {
+        double p[D];
+        gather_vertex<D>(src, vid[v], p);
+#pragma unroll
+        for (int l = 0; l < D; l++) a.z[(size_t)(D * v + l) * a.E + e] = p[l];
+    }
+}
+
+// K5: ||D x - z||^2 partials
+template <int D> __global__ void __launch_bounds__(TPB) k_residual(ElemArgs<D> a, double *part) {
+    __shared__ double red[32];
+    int e = blockIdx.x * TPB + threadIdx.x;
+    double s = 0.0;
+    if (e < a.E) {
+        int vid[D + 1];
+        load_elem_ids<D>(a, e, vid);
+#pragma unroll
+        for (int v = 0; v < D + 1; v++) {
+            double p[D];
+            gather_vertex<D>(a.x, vid[v], p);
+#pragma unroll
+            for (int l = 0; l < D; l++) {
+                double df = p[l] - a.z[(size_t)(D * v + l) * a.E + e];
+                s += df * df;
+            }
+        }
+    }
+    double r = block_sum(s, red);
+    if (threadIdx.x == 0) part[blockIdx.x] = r;
+}
+
+// fixed-order final reduction of up to 3 partial arrays -> out[0..2]
+__global__ void __launch_bounds__(1024) k_finalize(int nblk, const double *p0, const double *p1, const double *p2, double *out) {
+    __shared__ double red[32];
+    const double *ps[3] = {p0, p1, p2};
+    for (int q = 0; q < 3; q++) {
+        if (!ps[q]) continue;
+        double s = 0.0;
+        for (int i = threadIdx.x; i < nblk; i += blockDim.x) s += ps[q][i];
+        double r = block_sum(s, red);
+        if (threadIdx.x == 0) out[q] = r;
+        __syncthreads();
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// vertex kernels
+// ------------------------------------------------------------------------------------------------
+// K3b+K4: x = (m*xBar + dt^2 * sum_{inc, ascending element} w*(w*(z-u))) / tdiag       (src/MeshIntegrator.cpp:137-138,159-160)
+template <int D>
+__global__ void __launch_bounds__(TPB_V) k_xupdate(int P, size_t E, const int *incPtr, const int *incIdx, const double *z,
+                                                   const double *u, const double *xBar, const double *tdiag, double m,
+                                                   double dtsq, double w, double *x) {
+    int p = blockIdx.x * TPB_V + threadIdx.x;
+    if (p >= P) return;
+    double s[D];
+#pragma unroll
+    for (int l = 0; l < D; l++) s[l] = 0.0;
+    int k0 = incPtr[p], k1 = incPtr[p + 1];
+    for (int k = k0; k < k1; k++) {
+        int slot = __ldg(incIdx + k);
+        size_t e = (size_t)(slot >> 2);
+        int v = slot & 3;
+#pragma unroll
+        for (int l = 0; l < D; l++) {
+            size_t idx = (size_t)(D * v + l) * E + e;
+            s[l] += w * (w * (__ldg(z + idx) - __ldg(u + idx)));
+        }
+    }
+    double td = tdiag[p];
+#pragma unroll
+    for (int l = 0; l < D; l++) x[(size_t)D * p + l] = ((m * xBar[(size_t)D * p + l]) + dtsq * s[l]) / td;
+}
+
+// K6b: grad = sum of element gradients (ascending element order, as the reference's serial loop accumulates);
+// xBar = x - (dt/tau)*grad ; xPrev = x     (src/Mesh.cpp:649-674, src/MeshIntegrator.cpp:119)
+template <int D>
+__global__ void __launch_bounds__(TPB_V) k_predict_grad(int P, size_t E, const int *incPtr, const int *incIdx, const double *gs,
+                                                        double dtOverTau, const double *x, double *xBar, double *xPrev) {
+    int p = blockIdx.x * TPB_V + threadIdx.x;
+    if (p >= P) return;
+    double s[D];
+#pragma unroll
+    for (int l = 0; l < D; l++) s[l] = 0.0;
+    int k0 = incPtr[p], k1 = incPtr[p + 1];
+    for (int k = k0; k < k1; k++) {
+        int slot = __ldg(incIdx + k);
+        size_t e = (size_t)(slot >> 2);
+        int v = slot & 3;
+#pragma unroll
+        for (int l = 0; l < D; l++) s[l] += __ldg(gs + (size_t)(D * v + l) * E + e);
+    }
+#pragma unroll
+    for (int l = 0; l < D; l++) {
+        double xv = x[(size_t)D * p + l];
+        xBar[(size_t)D * p + l] = xv - dtOverTau * s[l];
+        xPrev[(size_t)D * p + l] = xv;
+    }
+}
+// K7: xBar = 2x - xPrev ; xPrev = x
+__global__ void __launch_bounds__(TPB_V) k_predict_extrap(size_t N, const double *x, double *xBar, double *xPrev) {
+    size_t i = (size_t)blockIdx.x * TPB_V + threadIdx.x;
+    if (i >= N) return;
+    double xv = x[i];
+    xBar[i] = 2 * xv - xPrev[i];
+    xPrev[i] = xv;
+}
+
+// ---- unit-parity helpers ----
+template <int D> __global__ void k_eval_monitor(MonGrid mg, int npts, const double *pts, double *out) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= npts) return;
+    double p[D];
+#pragma unroll
+    for (int l = 0; l < D; l++) p[l] = pts[(size_t)i * D + l];
+    SMat<D> m;
+    eval_monitor<D>(mg, p, m);
+#pragma unroll
+    for (int k = 0; k < D * D; k++) out[(size_t)i * D * D + k] = m.a[k];
+}
+template <int D>
+__global__ void k_block_grad_dbg(ElemArgs<D> a, int ne, const double *zs, const double *dxpu, int computeGrad, int regularize,
+                                 int applyMask, double *energy, double *grad, double *igt) {
+    constexpr int n = D * (D + 1);
+    int e = blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= ne) return;
+    int vid[D + 1];
+    load_elem_ids<D>(a, e, vid);
+    double z[n], xi[n], g[n], dx[n];
+#pragma unroll
+    for (int k = 0; k < n; k++) { z[k] = zs[(size_t)e * n + k]; dx[k] = regularize ? dxpu[(size_t)e * n + k] : 0.0; g[k] = 0.0; }
+    load_xi<D>(a, vid, xi);
+    bool inv = false;
+    double en = computeGrad ? block_grad<D, true>(z, xi, a.compMesh, a.mg, a.fc, g, inv)
+                            : block_grad<D, false>(z, xi, a.compMesh, a.mg, a.fc, g, inv);
+    double I = en;
+    if (regularize) {
+        double sq = 0.0;
+#pragma unroll
+        for (int k = 0; k < n; k++) { double t = dx[k] - z[k]; sq += t * t; g[k] += a.fc.w2 * (-dx[k] + z[k]); }
+        en += 0.5 * a.fc.w2 * sq;
+    }
+    if (applyMask) {
+        unsigned fb = a.fixedBits[e];
+#pragma unroll
+        for (int v = 0; v < D + 1; v++)
+            if (fb & (1u << v))
+#pragma unroll
+                for (int l = 0; l < D; l++) g[D * v + l] = 0.0;
+    }
+    energy[e] = en;
+    if (igt) igt[e] = I;
+    if (grad && computeGrad)
+#pragma unroll
+        for (int k = 0; k < n; k++) grad[(size_t)e * n + k] = g[k];
+    if (inv) atomicOr(a.status, ST_INVERTED);
+}
+
+}  // namespace
+
+// =====================================================================================================
+// context
+// =====================================================================================================
+struct mmadmm_ctx {
+    int D = 0, n = 0, P = 0, E = 0, device = 0;
+    bool compMesh = false, gradUse = false;
+    cudaStream_t stream = nullptr;
+    int *F[4] = {nullptr, nullptr, nullptr, nullptr};
+    uint8_t *mask = nullptr, *fixedBits = nullptr, *nonIntBits = nullptr;
+    double *x = nullptr, *xPrev = nullptr, *xBar = nullptr, *Vc = nullptr, *tdiag = nullptr;
+    double *z = nullptr, *u = nullptr, *B = nullptr, *gs = nullptr;
+    int *incPtr = nullptr, *incIdx = nullptr;
+    double *grid = nullptr, *ax = nullptr, *ay = nullptr, *az = nullptr;
+    int nx = 0, ny = 0, nz = 0;
+    size_t gridRows = 0;
+    double rho = 0, w = 0, tau = 0, m = 0, dt = 0;
+    double Ehat[9] = {0}, dpow = 0;
+    bool stepTaken = false, hessComputed = false;
+    int stepsTaken = 0;
+    int nblkE = 0;
+    double *partIh = nullptr, *partDual = nullptr, *partPrimal = nullptr, *scal_d = nullptr, *scal_h = nullptr;
+    unsigned *status_d = nullptr, *status_h = nullptr;
+    unsigned long long *hist_d = nullptr;
+    bool statsOn = true, timingOn = false;
+    long long admmIters = 0, proxCalls = 0, launches = 0;
+    double phaseMs[5] = {0, 0, 0, 0, 0};
+    long long phaseCnt[5] = {0, 0, 0, 0, 0};
+    std::vector<cudaEvent_t> evPool;
+    std::vector<int> evPhase;
+    size_t evUsed = 0;
+    std::string err;
+
+    template <int D_> ElemArgs<D_> elemArgs(double tol) const {
+        ElemArgs<D_> a;
+        a.E = E; a.P = P;
+        for (int v = 0; v < MAXV; v++) a.F[v] = F[v];
+        a.fixedBits = fixedBits; a.nonIntBits = nonIntBits;
+        a.x = x; a.Vc = Vc; a.z = z; a.u = u; a.B = B;
+        a.mg.vals = grid; a.mg.ax = ax; a.mg.ay = ay; a.mg.az = az; a.mg.nx = nx; a.mg.ny = ny; a.mg.nz = nz;
+        for (int k = 0; k < D_ * D_; k++) a.fc.Ehat[k] = Ehat[k];
+        a.fc.dpow = dpow; a.fc.w2 = w * w;
+        a.compMesh = compMesh ? 1 : 0;
+        a.tol = tol;
+        a.partIh = partIh; a.partDual = partDual;
+        a.hist = statsOn ? hist_d : nullptr;
+        a.status = status_d;
+        return a;
+    }
+    void phaseBegin(int ph) {
+        if (!timingOn) return;
+        if (evUsed + 2 > evPool.size()) {
+            for (int i = 0; i < 64; i++) { cudaEvent_t e; cudaEventCreate(&e); evPool.push_back(e); evPhase.push_back(0); }
+        }
+        evPhase[evUsed] = ph;
+        cudaEventRecord(evPool[evUsed], stream);
+    }
+    void phaseEnd() {
+        if (!timingOn) return;
+        cudaEventRecord(evPool[evUsed + 1], stream);
+        evUsed += 2;
+    }
+    void phaseResolve() {
+        if (!timingOn) return;
+        for (size_t i = 0; i + 1 < evUsed; i += 2) {
+            float ms = 0;
+            cudaEventSynchronize(evPool[i + 1]);
+            cudaEventElapsedTime(&ms, evPool[i], evPool[i + 1]);
+            phaseMs[evPhase[i]] += ms;
+            phaseCnt[evPhase[i]]++;
+        }
+        evUsed = 0;
+    }
+};
+
+namespace {
+
+inline int cdiv(size_t a, size_t b) { return (int)((a + b - 1) / b); }
+
+// CSR by key: sorted vals (stable => ascending input order inside a key) and ptr[nkeys+1]
+int build_csr(mmadmm_ctx *ctx, size_t nItems, int nKeys, int *keys, int *vals, int **ptrOut, int **valsOut) {
+    cudaStream_t st = ctx->stream;
+    int *cnt = nullptr, *ptr = nullptr, *keysOut = nullptr, *valsSorted = nullptr;
+    CK(cudaMalloc(&cnt, sizeof(int) * ((size_t)nKeys + 1)));
+    CK(cudaMalloc(&ptr, sizeof(int) * ((size_t)nKeys + 1)));
+    CK(cudaMalloc(&keysOut, sizeof(int) * nItems));
+    CK(cudaMalloc(&valsSorted, sizeof(int) * nItems));
+    CK(cudaMemsetAsync(cnt, 0, sizeof(int) * ((size_t)nKeys + 1), st));
+    k_count_keys<<<cdiv(nItems, 256), 256, 0, st>>>(nItems, keys, cnt);
+    void *tmp = nullptr;
+    size_t tmpBytes = 0;
+    CK(cub::DeviceScan::ExclusiveSum(nullptr, tmpBytes, cnt, ptr, nKeys + 1, st));
+    CK(cudaMalloc(&tmp, tmpBytes));
+    CK(cub::DeviceScan::ExclusiveSum(tmp, tmpBytes, cnt, ptr, nKeys + 1, st));
+    CK(cudaFree(tmp));
+    int endBit = 1;
+    while ((1ll << endBit) < (long long)nKeys) endBit++;
+    tmp = nullptr; tmpBytes = 0;
+    CK(cub::DeviceRadixSort::SortPairs(nullptr, tmpBytes, keys, keysOut, vals, valsSorted, (int)nItems, 0, endBit, st));
+    CK(cudaMalloc(&tmp, tmpBytes));
+    CK(cub::DeviceRadixSort::SortPairs(tmp, tmpBytes, keys, keysOut, vals, valsSorted, (int)nItems, 0, endBit, st));
+    CK(cudaStreamSynchronize(st));
+    CK(cudaFree(tmp));
+    CK(cudaFree(cnt));
+    CK(cudaFree(keysOut));
+    *ptrOut = ptr;
+    *valsOut = valsSorted;
+    ctx->launches += 4;
+    return MMADMM_OK;
+}
+
+template <int D> int build_monitor_grid(mmadmm_ctx *ctx, const double *VpHost, const double *monVertexHost) {
+    cudaStream_t st = ctx->stream;
+    const int P = ctx->P;
+    constexpr int DD = D * D;
+    // MeshInterpolator::updateMesh (src/MeshInterpolator.cpp:67-130): grid size, bounding box, axes (host, init only)
+    ctx->nx = (int)std::pow((double)((size_t)P * D), 1.0 / D);
+    ctx->ny = ctx->nx;
+    ctx->nz = (D == 2) ? 1 : ctx->nx;
+    double mn[3] = {INFINITY, INFINITY, INFINITY}, mx[3] = {-INFINITY, -INFINITY, -INFINITY};
+    for (int p = 0; p < P; p++)
+        for (int l = 0; l < D; l++) {
+            double v = VpHost[(size_t)p * D + l];
+            mn[l] = (v < mn[l]) ? v : mn[l];
+            mx[l] = (v > mx[l]) ? v : mx[l];
+        }
+    auto linspace = [](double xa, double xb, int ns, std::vector<double> &x) {  // src/MeshUtils.h:24-29
+        x.resize(ns + 1);
+        for (int i = 0; i < ns + 1; i++) x[i] = xa + ((double)i) * (xb - xa) / ns;
+    };
+    std::vector<double> hx, hy, hz;
+    linspace(mn[0], mx[0], ctx->nx, hx);
+    linspace(mn[1], mx[1], ctx->ny, hy);
+    if (D == 3) linspace(mn[2], mx[2], ctx->nz, hz); else hz.assign(2, 0.0);
+    CK(cudaMalloc(&ctx->ax, sizeof(double) * hx.size()));
+    CK(cudaMalloc(&ctx->ay, sizeof(double) * hy.size()));
+    CK(cudaMalloc(&ctx->az, sizeof(double) * hz.size()));
+    CK(cudaMemcpyAsync(ctx->ax, hx.data(), sizeof(double) * hx.size(), cudaMemcpyHostToDevice, st));
+    CK(cudaMemcpyAsync(ctx->ay, hy.data(), sizeof(double) * hy.size(), cudaMemcpyHostToDevice, st));
+    CK(cudaMemcpyAsync(ctx->az, hz.data(), sizeof(double) * hz.size(), cudaMemcpyHostToDevice, st));
+    ctx->gridRows = (size_t)(ctx->nx + 1) * (ctx->ny + 1) * ((D == 3) ? (ctx->nz + 1) : 1);
+    double *gridTmp = nullptr, *monV = nullptr;
+    CK(cudaMalloc(&ctx->grid, sizeof(double) * ctx->gridRows * DD));
+    CK(cudaMalloc(&gridTmp, sizeof(double) * ctx->gridRows * DD));
+    CK(cudaMalloc(&monV, sizeof(double) * (size_t)P * DD));
+    CK(cudaMemcpyAsync(monV, monVertexHost, sizeof(double) * (size_t)P * DD, cudaMemcpyHostToDevice, st));
+
+    // uniform bins over the vertex bounding box (about 2 vertices per bin)
+    BinGeom bg;
+    int per = std::max(1, (int)std::floor(std::pow((double)P / 2.0, 1.0 / D)));
+    double minbw = INFINITY;
+    for (int l = 0; l < 3; l++) { bg.nb[l] = 1; bg.lo[l] = 0; bg.inv[l] = 0; }
+    for (int l = 0; l < D; l++) {
+        bg.nb[l] = per; bg.lo[l] = mn[l];
+        double ext = mx[l] - mn[l];
+        bg.inv[l] = ext > 0 ? per / ext : 0.0;
+        if (ext > 0) minbw = std::min(minbw, ext / per);
+    }
+    // the stop test uses a slightly shrunken bin width so that rounding in the bin assignment can never
+    // let a closer vertex hide in an unvisited ring
+    bg.minbw = std::isfinite(minbw) ? minbw * (1.0 - 1e-9) : 0.0;
+    bg.maxr = per;
+    size_t nbins = (size_t)bg.nb[0] * bg.nb[1] * bg.nb[2];
+    int *bin = nullptr, *ids = nullptr, *binStart = nullptr, *items = nullptr;
+    CK(cudaMalloc(&bin, sizeof(int) * (size_t)P));
+    CK(cudaMalloc(&ids, sizeof(int) * (size_t)P));
+    k_bin_ids<D><<<cdiv(P, 256), 256, 0, st>>>(P, ctx->x, bg, bin, ids);
+    int rc = build_csr(ctx, (size_t)P, (int)nbins, bin, ids, &binStart, &items);
+    if (rc) return rc;
+    MonGrid mg;
+    mg.vals = ctx->grid; mg.ax = ctx->ax; mg.ay = ctx->ay; mg.az = ctx->az; mg.nx = ctx->nx; mg.ny = ctx->ny; mg.nz = ctx->nz;
+    k_nn_grid<D><<<cdiv(ctx->gridRows, 128), 128, 0, st>>>(mg, ctx->grid, ctx->x, monV, bg, binStart, items);
+    int nSmooth = (D == 2) ? 5 : 2;  // src/MeshInterpolator.cpp:246-252
+    for (int it = 0; it < nSmooth; it++) {
+        CK(cudaMemcpyAsync(gridTmp, ctx->grid, sizeof(double) * ctx->gridRows * DD, cudaMemcpyDeviceToDevice, st));
+        k_smooth<D><<<cdiv(ctx->gridRows * DD, 256), 256, 0, st>>>(ctx->nx, ctx->ny, ctx->nz, gridTmp, ctx->grid);
+    }
+    ctx->launches += 2 + nSmooth;
+    CK(cudaStreamSynchronize(st));
+    CK(cudaGetLastError());
+    cudaFree(gridTmp); cudaFree(monV); cudaFree(bin); cudaFree(ids); cudaFree(binStart); cudaFree(items);
+    return MMADMM_OK;
+}
+
+template <int D>
+int create_impl(mmadmm_ctx *ctx, const double *Vp, const double *Vc, const int *F, const int *mask, const double *monVertex) {
+    constexpr int n = D * (D + 1);
+    const int P = ctx->P, E = ctx->E;
+    cudaStream_t st = ctx->stream;
+    const size_t NV = (size_t)P * D, NZ = (size_t)E * n;
+    CK(cudaMalloc(&ctx->x, sizeof(double) * NV));
+    CK(cudaMalloc(&ctx->xPrev, sizeof(double) * NV));
+    CK(cudaMalloc(&ctx->xBar, sizeof(double) * NV));
+    CK(cudaMalloc(&ctx->tdiag, sizeof(double) * (size_t)P));
+    CK(cudaMemcpyAsync(ctx->x, Vp, sizeof(double) * NV, cudaMemcpyHostToDevice, st));
+    CK(cudaMemcpyAsync(ctx->xPrev, ctx->x, sizeof(double) * NV, cudaMemcpyDeviceToDevice, st));
+    CK(cudaMemcpyAsync(ctx->xBar, ctx->x, sizeof(double) * NV, cudaMemcpyDeviceToDevice, st));
+    if (Vc) {
+        CK(cudaMalloc(&ctx->Vc, sizeof(double) * NV));
+        CK(cudaMemcpyAsync(ctx->Vc, Vc, sizeof(double) * NV, cudaMemcpyHostToDevice, st));
+    }
+    std::vector<uint8_t> m8(P);
+    for (int p = 0; p < P; p++) m8[p] = (uint8_t)mask[p];
+    CK(cudaMalloc(&ctx->mask, (size_t)P));
+    CK(cudaMemcpyAsync(ctx->mask, m8.data(), (size_t)P, cudaMemcpyHostToDevice, st));
+    int *Frow = nullptr;
+    CK(cudaMalloc(&Frow, sizeof(int) * (size_t)E * (D + 1)));
+    CK(cudaMemcpyAsync(Frow, F, sizeof(int) * (size_t)E * (D + 1), cudaMemcpyHostToDevice, st));
+    for (int v = 0; v < D + 1; v++) CK(cudaMalloc(&ctx->F[v], sizeof(int) * (size_t)E));
+    CK(cudaMalloc(&ctx->fixedBits, (size_t)E));
+    CK(cudaMalloc(&ctx->nonIntBits, (size_t)E));
+    k_setup_F<D><<<cdiv(E, 256), 256, 0, st>>>(E, Frow, ctx->F[0], ctx->F[1], ctx->F[2], ctx->F[3], ctx->x, ctx->mask,
+                                               ctx->fixedBits, ctx->nonIntBits);
+    // incidence
+    int *keys = nullptr, *vals = nullptr;
+    CK(cudaMalloc(&keys, sizeof(int) * (size_t)E * (D + 1)));
+    CK(cudaMalloc(&vals, sizeof(int) * (size_t)E * (D + 1)));
+    k_inc_pairs<D><<<cdiv(E, 256), 256, 0, st>>>(E, ctx->F[0], ctx->F[1], ctx->F[2], ctx->F[3], keys, vals);
+    int rc = build_csr(ctx, (size_t)E * (D + 1), P, keys, vals, &ctx->incPtr, &ctx->incIdx);
+    if (rc) return rc;
+    cudaFree(keys); cudaFree(vals); cudaFree(Frow);
+    ctx->launches += 2;
+
+    // functional constants, with the reference's own expressions (AdaptationFunctional.cpp:176-201, 219-220)
+    {
+        double Eh[3][3] = {{0}};
+        double dFact = (D == 2) ? 2.0 : 6.0;
+        if (D == 2) {
+            Eh[0][0] = 1.0; Eh[1][0] = 0.0; Eh[0][1] = 1.0 / 2.0; Eh[1][1] = std::sqrt(3) / 2.0;
+        } else {
+            Eh[0][0] = -2.0; Eh[1][0] = 0.0;  Eh[2][0] = -2.0;
+            Eh[0][1] = 0.0;  Eh[1][1] = -2.0; Eh[2][1] = -2.0;
+            Eh[0][2] = -2.0; Eh[1][2] = -2.0; Eh[2][2] = 0.0;
+        }
+        double det;
+        if (D == 2) det = Eh[0][0] * Eh[1][1] - Eh[1][0] * Eh[0][1];
+        else
+            det = Eh[0][0] * (Eh[1][1] * Eh[2][2] - Eh[1][2] * Eh[2][1]) - Eh[0][1] * (Eh[1][0] * Eh[2][2] - Eh[1][2] * Eh[2][0]) +
+                  Eh[0][2] * (Eh[1][0] * Eh[2][1] - Eh[1][1] * Eh[2][0]);
+        double s1 = std::pow((dFact / std::fabs(det)), 1.0 / ((double)D));
+        double s2 = (double)std::pow(E, 1.0 / D);
+        for (int a = 0; a < D; a++)
+            for (int b = 0; b < D; b++) { double v = Eh[a][b]; v *= s1; v /= s2; ctx->Ehat[a * D + b] = v; }
+        ctx->dpow = std::pow((double)D, (double)D * 1.5 / 2.0);
+    }
+    ctx->w = 0.5 * std::sqrt(ctx->rho);  // src/Mesh.cpp:451 (the JSON "w" is ignored by the reference)
+    ctx->m = ctx->tau;
+    k_tdiag<<<cdiv(P, 256), 256, 0, st>>>(P, ctx->incPtr, ctx->m, ctx->dt * ctx->dt, ctx->w, ctx->tdiag);
+    ctx->launches++;
+
+    rc = build_monitor_grid<D>(ctx, Vp, monVertex);
+    if (rc) return rc;
+
+    // element state: z = D x, u = 0, hessInvs = I
+    CK(cudaMalloc(&ctx->z, sizeof(double) * NZ));
+    CK(cudaMalloc(&ctx->u, sizeof(double) * NZ));
+    CK(cudaMalloc(&ctx->B, sizeof(double) * NZ * n));
+    CK(cudaMalloc(&ctx->gs, sizeof(double) * NZ));
+    CK(cudaMemsetAsync(ctx->u, 0, sizeof(double) * NZ, st));
+    CK(cudaMemsetAsync(ctx->B, 0, sizeof(double) * NZ * n, st));
+    {
+        std::vector<double> ones((size_t)E, 1.0);
+        for (int k = 0; k < n; k++)
+            CK(cudaMemcpyAsync(ctx->B + (size_t)(k * n + k) * E, ones.data(), sizeof(double) * (size_t)E, cudaMemcpyHostToDevice, st));
+        CK(cudaStreamSynchronize(st));
+    }
+    ctx->nblkE = cdiv(E, TPB);
+    CK(cudaMalloc(&ctx->partIh, sizeof(double) * ctx->nblkE));
+    CK(cudaMalloc(&ctx->partDual, sizeof(double) * ctx->nblkE));
+    CK(cudaMalloc(&ctx->partPrimal, sizeof(double) * ctx->nblkE));
+    CK(cudaMalloc(&ctx->scal_d, sizeof(double) * 4));
+    CK(cudaMallocHost(&ctx->scal_h, sizeof(double) * 4));
+    CK(cudaMalloc(&ctx->status_d, sizeof(unsigned)));
+    CK(cudaMallocHost(&ctx->status_h, sizeof(unsigned)));
+    CK(cudaMemsetAsync(ctx->status_d, 0, sizeof(unsigned), st));
+    CK(cudaMalloc(&ctx->hist_d, sizeof(unsigned long long) * 52));
+    CK(cudaMemsetAsync(ctx->hist_d, 0, sizeof(unsigned long long) * 52, st));
+    ElemArgs<D> a = ctx->elemArgs<D>(0.0);
+    k_applyD<D><<<ctx->nblkE, TPB, 0, st>>>(a, ctx->x);
+    ctx->launches++;
+    CK(cudaStreamSynchronize(st));
+    CK(cudaGetLastError());
+    return MMADMM_OK;
+}
+
+int check_status(mmadmm_ctx *ctx) {
+    unsigned s = *ctx->status_h;
+    if (s & ST_INVERTED) { ctx->err = "inverted element (det E <= 0): the reference asserts here (AdaptationFunctional.cpp:174)"; return MMADMM_EINVERTED; }
+    if (s & ST_SINGULAR_HESS) { ctx->err = "singular finite-difference Hessian"; return MMADMM_ESINGULAR; }
+    return MMADMM_OK;
+}
+
+template <int D> int step_impl(mmadmm_ctx *ctx, int nIters, double tol, double *IhOut, int *itersOut, double *primalOut, double *dualOut) {
+    constexpr int n = D * (D + 1);
+    cudaStream_t st = ctx->stream;
+    const int P = ctx->P;
+    const size_t E = ctx->E, NV = (size_t)P * D, NZ = E * n;
+    const double dtsq = ctx->dt * ctx->dt;
+    ElemArgs<D> a = ctx->elemArgs<D>(tol / 100);   // BFGS tolerance tol/100, 50 iterations (src/Mesh.cpp:968)
+    const int gE = ctx->nblkE, gV = cdiv(P, TPB_V);
+
+    // predictX (src/Mesh.cpp:649-674) fused with xPrev = x (src/MeshIntegrator.cpp:119)
+    ctx->phaseBegin(0);
+    if (ctx->gradUse || ctx->stepsTaken <= 2) {
+        k_euler_elem<D><<<gE, TPB, 0, st>>>(a, ctx->gs);
+        k_predict_grad<D><<<gV, TPB_V, 0, st>>>(P, E, ctx->incPtr, ctx->incIdx, ctx->gs, ctx->dt / ctx->tau, ctx->x, ctx->xBar, ctx->xPrev);
+        ctx->launches += 2;
+    } else {
+        k_predict_extrap<<<cdiv(NV, TPB_V), TPB_V, 0, st>>>(NV, ctx->x, ctx->xBar, ctx->xPrev);
+        ctx->launches += 1;
+    }
+    // x = xBar; z = D x  (z = D xPrev on the very first step); u = 0 until a step has been taken  (:120-127)
+    k_applyD<D><<<gE, TPB, 0, st>>>(a, (ctx->stepsTaken == 0) ? ctx->xPrev : ctx->xBar);
+    if (!ctx->stepTaken) CK(cudaMemsetAsync(ctx->u, 0, sizeof(double) * NZ, st));
+    ctx->phaseEnd();
+    // first x-solve (:137-138)
+    ctx->phaseBegin(2);
+    k_xupdate<D><<<gV, TPB_V, 0, st>>>(P, E, ctx->incPtr, ctx->incIdx, ctx->z, ctx->u, ctx->xBar, ctx->tdiag, ctx->m, dtsq, ctx->w, ctx->x);
+    ctx->phaseEnd();
+    ctx->launches += 2;
+
+    double Ihstart = 0, primal = 0, dual = 0;
+    int i;
+    for (i = 0; i < nIters; i++) {
+        if (!ctx->hessComputed) {
+            ctx->phaseBegin(4);
+            k_hess_init<D><<<gE, TPB, 0, st>>>(a);
+            ctx->phaseEnd();
+            ctx->launches++;
+        }
+        ctx->phaseBegin(1);
+        k_prox<D><<<gE, TPB, 0, st>>>(a);
+        ctx->phaseEnd();
+        ctx->hessComputed = true;
+        ctx->stepTaken = true;
+        ctx->phaseBegin(2);
+        k_xupdate<D><<<gV, TPB_V, 0, st>>>(P, E, ctx->incPtr, ctx->incIdx, ctx->z, ctx->u, ctx->xBar, ctx->tdiag, ctx->m, dtsq, ctx->w, ctx->x);
+        ctx->phaseEnd();
+        ctx->phaseBegin(3);
+        k_residual<D><<<gE, TPB, 0, st>>>(a, ctx->partPrimal);
+        k_finalize<<<1, 1024, 0, st>>>(gE, ctx->partIh, ctx->partPrimal, ctx->partDual, ctx->scal_d);
+        CK(cudaMemcpyAsync(ctx->scal_h, ctx->scal_d, sizeof(double) * 3, cudaMemcpyDeviceToHost, st));
+        CK(cudaMemcpyAsync(ctx->status_h, ctx->status_d, sizeof(unsigned), cudaMemcpyDeviceToHost, st));
+        ctx->phaseEnd();
+        ctx->launches += 4;
+        CK(cudaStreamSynchronize(st));
+        ctx->admmIters++;
+        ctx->proxCalls += (long long)E;
+        int rc = check_status(ctx);
+        if (rc) return rc;
+        if (i == 0) Ihstart = ctx->scal_h[0];
+        primal = std::sqrt(ctx->scal_h[1]);
+        dual = std::sqrt(ctx->scal_h[2]);
+        if (primal < tol && dual < tol) break;
+    }
+    ctx->phaseResolve();
+    CK(cudaGetLastError());
+    ctx->stepsTaken++;
+    if (IhOut) *IhOut = Ihstart;
+    if (itersOut) *itersOut = (i == nIters) ? nIters : i + 1;
+    if (primalOut) *primalOut = primal;
+    if (dualOut) *dualOut = dual;
+    return MMADMM_OK;
+}
+
+template <int D> int energy_impl(mmadmm_ctx *ctx, double *I) {
+    cudaStream_t st = ctx->stream;
+    ElemArgs<D> a = ctx->elemArgs<D>(0.0);
+    k_energy<D><<<ctx->nblkE, TPB, 0, st>>>(a, ctx->partPrimal);
+    k_finalize<<<1, 1024, 0, st>>>(ctx->nblkE, ctx->partPrimal, nullptr, nullptr, ctx->scal_d + 3);
+    ctx->launches += 2;
+    // k_finalize writes out[0] of its `out` argument => scal_d[3]
+    CK(cudaMemcpyAsync(ctx->scal_h + 3, ctx->scal_d + 3, sizeof(double), cudaMemcpyDeviceToHost, st));
+    CK(cudaMemcpyAsync(ctx->status_h, ctx->status_d, sizeof(unsigned), cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    CK(cudaGetLastError());
+    *I = ctx->scal_h[3];
+    return check_status(ctx);
+}
+
+}  // namespace
+
+// =====================================================================================================
+// C ABI
+// =====================================================================================================
+extern "C" {
+
+const char *mmadmm_version(void) { return "mmadmm_b200 0.1 (sm_100a, fp64)"; }
+
+int mmadmm_create(int D, int P, int E, const double *Vp, const double *Vc, const int *F, const int *mask,
+                  const double *monVertex, double rho, double tau, double dt, int gradUse, int device, mmadmm_ctx **out) {
+    if (!out) return MMADMM_EINVAL;
+    *out = nullptr;
+    if ((D != 2 && D != 3) || P <= 0 || E <= 0 || !Vp || !F || !mask || !monVertex) return MMADMM_EINVAL;
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) return MMADMM_ENODEVICE;
+    mmadmm_ctx *ctx = new mmadmm_ctx();
+    *out = ctx;  // returned even on failure so that mmadmm_last_error can be read; caller destroys it
+    ctx->D = D; ctx->n = D * (D + 1); ctx->P = P; ctx->E = E; ctx->device = device;
+    ctx->compMesh = (Vc != nullptr); ctx->gradUse = gradUse != 0;
+    ctx->rho = rho; ctx->tau = tau; ctx->dt = dt;
+    CK(cudaSetDevice(device));
+    CK(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
+    for (size_t p = 0; p < (size_t)E * (D + 1); p++)
+        if (F[p] < 0 || F[p] >= P) { ctx->err = "connectivity index out of range"; return MMADMM_EINVAL; }
+    int rc = (D == 2) ? create_impl<2>(ctx, Vp, Vc, F, mask, monVertex) : create_impl<3>(ctx, Vp, Vc, F, mask, monVertex);
+    return rc;
+}
+
+int mmadmm_step(mmadmm_ctx *ctx, int nIters, double tol, double *Ih, int *itersTaken, double *primal, double *dual) {
+    if (!ctx) return MMADMM_EINVAL;
+    CK(cudaSetDevice(ctx->device));
+    return (ctx->D == 2) ? step_impl<2>(ctx, nIters, tol, Ih, itersTaken, primal, dual)
+                         : step_impl<3>(ctx, nIters, tol, Ih, itersTaken, primal, dual);
+}
+
+int mmadmm_energy(mmadmm_ctx *ctx, double *I) {
+    if (!ctx || !I) return MMADMM_EINVAL;
+    CK(cudaSetDevice(ctx->device));
+    return (ctx->D == 2) ? energy_impl<2>(ctx, I) : energy_impl<3>(ctx, I);
+}
+
+int mmadmm_get_x(mmadmm_ctx *ctx, double *x) {
+    if (!ctx || !x) return MMADMM_EINVAL;
+    CK(cudaMemcpyAsync(x, ctx->x, sizeof(double) * (size_t)ctx->P * ctx->D, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    return MMADMM_OK;
+}
+int mmadmm_get_x_device(mmadmm_ctx *ctx, double *x_dev) {
+    if (!ctx || !x_dev) return MMADMM_EINVAL;
+    CK(cudaMemcpyAsync(x_dev, ctx->x, sizeof(double) * (size_t)ctx->P * ctx->D, cudaMemcpyDeviceToDevice, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    return MMADMM_OK;
+}
+
+int mmadmm_get_F(mmadmm_ctx *ctx, int *F) {
+    if (!ctx || !F) return MMADMM_EINVAL;
+    const int V = ctx->D + 1;
+    std::vector<int> plane(ctx->E);
+    for (int v = 0; v < V; v++) {
+        CK(cudaMemcpy(plane.data(), ctx->F[v], sizeof(int) * (size_t)ctx->E, cudaMemcpyDeviceToHost));
+        for (int e = 0; e < ctx->E; e++) F[(size_t)e * V + v] = plane[e];
+    }
+    return MMADMM_OK;
+}
+
+int mmadmm_grid_dims(mmadmm_ctx *ctx, int *dims) {
+    if (!ctx || !dims) return MMADMM_EINVAL;
+    dims[0] = ctx->nx; dims[1] = ctx->ny; dims[2] = ctx->nz;
+    return MMADMM_OK;
+}
+
+int mmadmm_get_state(mmadmm_ctx *ctx, int which, double *out) {
+    if (!ctx || !out) return MMADMM_EINVAL;
+    CK(cudaStreamSynchronize(ctx->stream));
+    const size_t E = ctx->E;
+    const int n = ctx->n;
+    if (which == MMADMM_STATE_Z || which == MMADMM_STATE_U || which == MMADMM_STATE_HESSINV) {
+        int planes = (which == MMADMM_STATE_HESSINV) ? n * n : n;
+        const double *src = (which == MMADMM_STATE_Z) ? ctx->z : (which == MMADMM_STATE_U) ? ctx->u : ctx->B;
+        std::vector<double> plane(E);
+        for (int k = 0; k < planes; k++) {
+            CK(cudaMemcpy(plane.data(), src + (size_t)k * E, sizeof(double) * E, cudaMemcpyDeviceToHost));
+            for (size_t e = 0; e < E; e++) out[e * planes + k] = plane[e];
+        }
+        return MMADMM_OK;
+    }
+    if (which == MMADMM_STATE_XBAR || which == MMADMM_STATE_XPREV) {
+        CK(cudaMemcpy(out, which == MMADMM_STATE_XBAR ? ctx->xBar : ctx->xPrev, sizeof(double) * (size_t)ctx->P * ctx->D, cudaMemcpyDeviceToHost));
+        return MMADMM_OK;
+    }
+    if (which == MMADMM_STATE_MONGRID) {
+        CK(cudaMemcpy(out, ctx->grid, sizeof(double) * ctx->gridRows * ctx->D * ctx->D, cudaMemcpyDeviceToHost));
+        return MMADMM_OK;
+    }
+    return MMADMM_EINVAL;
+}
+
+int mmadmm_eval_monitor(mmadmm_ctx *ctx, const double *pts, int npts, double *out) {
+    if (!ctx || !pts || !out || npts <= 0) return MMADMM_EINVAL;
+    const int D = ctx->D;
+    double *dp = nullptr, *dout = nullptr;
+    CK(cudaMalloc(&dp, sizeof(double) * (size_t)npts * D));
+    CK(cudaMalloc(&dout, sizeof(double) * (size_t)npts * D * D));
+    CK(cudaMemcpy(dp, pts, sizeof(double) * (size_t)npts * D, cudaMemcpyHostToDevice));
+    MonGrid mg;
+    mg.vals = ctx->grid; mg.ax = ctx->ax; mg.ay = ctx->ay; mg.az = ctx->az; mg.nx = ctx->nx; mg.ny = ctx->ny; mg.nz = ctx->nz;
+    if (D == 2) k_eval_monitor<2><<<cdiv(npts, 128), 128, 0, ctx->stream>>>(mg, npts, dp, dout);
+    else k_eval_monitor<3><<<cdiv(npts, 128), 128, 0, ctx->stream>>>(mg, npts, dp, dout);
+    ctx->launches++;
+    CK(cudaStreamSynchronize(ctx->stream));
+    CK(cudaGetLastError());
+    CK(cudaMemcpy(out, dout, sizeof(double) * (size_t)npts * D * D, cudaMemcpyDeviceToHost));
+    cudaFree(dp); cudaFree(dout);
+    return MMADMM_OK;
+}
+
+int mmadmm_block_grad(mmadmm_ctx *ctx, int ne, const double *zs, const double *dxpu, int computeGrad, int regularize,
+                      int applyMask, double *energy, double *grad, double *igt) {
+    if (!ctx || !zs || !energy || ne <= 0 || ne > ctx->E || (regularize && !dxpu)) return MMADMM_EINVAL;
+    const int n = ctx->n;
+    double *dz = nullptr, *dd = nullptr, *de = nullptr, *dg = nullptr, *di = nullptr;
+    CK(cudaMalloc(&dz, sizeof(double) * (size_t)ne * n));
+    CK(cudaMalloc(&dd, sizeof(double) * (size_t)ne * n));
+    CK(cudaMalloc(&de, sizeof(double) * (size_t)ne));
+    CK(cudaMalloc(&dg, sizeof(double) * (size_t)ne * n));
+    CK(cudaMalloc(&di, sizeof(double) * (size_t)ne));
+    CK(cudaMemcpy(dz, zs, sizeof(double) * (size_t)ne * n, cudaMemcpyHostToDevice));
+    if (regularize) CK(cudaMemcpy(dd, dxpu, sizeof(double) * (size_t)ne * n, cudaMemcpyHostToDevice));
+    CK(cudaMemsetAsync(ctx->status_d, 0, sizeof(unsigned), ctx->stream));
+    if (ctx->D == 2) {
+        ElemArgs<2> a = ctx->elemArgs<2>(0.0);
+        k_block_grad_dbg<2><<<cdiv(ne, 128), 128, 0, ctx->stream>>>(a, ne, dz, dd, computeGrad, regularize, applyMask, de, dg, di);
+    } else {
+        ElemArgs<3> a = ctx->elemArgs<3>(0.0);
+        k_block_grad_dbg<3><<<cdiv(ne, 128), 128, 0, ctx->stream>>>(a, ne, dz, dd, computeGrad, regularize, applyMask, de, dg, di);
+    }
+    ctx->launches++;
+    CK(cudaStreamSynchronize(ctx->stream));
+    CK(cudaGetLastError());
+    CK(cudaMemcpy(energy, de, sizeof(double) * (size_t)ne, cudaMemcpyDeviceToHost));
+    if (grad) CK(cudaMemcpy(grad, dg, sizeof(double) * (size_t)ne * n, cudaMemcpyDeviceToHost));
+    if (igt) CK(cudaMemcpy(igt, di, sizeof(double) * (size_t)ne, cudaMemcpyDeviceToHost));
+    CK(cudaMemsetAsync(ctx->status_d, 0, sizeof(unsigned), ctx->stream));  // probing inverted simplices is legal here
+    cudaFree(dz); cudaFree(dd); cudaFree(de); cudaFree(dg); cudaFree(di);
+    return MMADMM_OK;
+}
+
+int mmadmm_get_stats(mmadmm_ctx *ctx, long long *hist52, long long *proxCalls, long long *admmIters, long long *kernelLaunches) {
+    if (!ctx) return MMADMM_EINVAL;
+    if (hist52) {
+        unsigned long long h[52];
+        CK(cudaStreamSynchronize(ctx->stream));
+        CK(cudaMemcpy(h, ctx->hist_d, sizeof(h), cudaMemcpyDeviceToHost));
+        for (int k = 0; k < 52; k++) hist52[k] = (long long)h[k];
+    }
+    if (proxCalls) *proxCalls = ctx->proxCalls;
+    if (admmIters) *admmIters = ctx->admmIters;
+    if (kernelLaunches) *kernelLaunches = ctx->launches;
+    return MMADMM_OK;
+}
+
+int mmadmm_get_timing(mmadmm_ctx *ctx, double *ms5, long long *counts5, int reset) {
+    if (!ctx) return MMADMM_EINVAL;
+    for (int i = 0; i < 5; i++) {
+        if (ms5) ms5[i] = ctx->phaseMs[i];
+        if (counts5) counts5[i] = ctx->phaseCnt[i];
+        if (reset) { ctx->phaseMs[i] = 0; ctx->phaseCnt[i] = 0; }
+    }
+    return MMADMM_OK;
+}
+
+int mmadmm_set_option(mmadmm_ctx *ctx, const char *name, int value) {
+    if (!ctx || !name) return MMADMM_EINVAL;
+    if (!strcmp(name, "timing")) { ctx->timingOn = value != 0; return MMADMM_OK; }
+    if (!strcmp(name, "stats")) { ctx->statsOn = value != 0; return MMADMM_OK; }
+    return MMADMM_EINVAL;
+}
+
+void *mmadmm_stream(mmadmm_ctx *ctx) { return ctx ? (void *)ctx->stream : nullptr; }
+
+void mmadmm_destroy(mmadmm_ctx *ctx) {
+    if (!ctx) return;
+    cudaSetDevice(ctx->device);
+    if (ctx->stream) cudaStreamSynchronize(ctx->stream);
+    for (int v = 0; v < 4; v++) cudaFree(ctx->F[v]);
+    cudaFree(ctx->mask); cudaFree(ctx->fixedBits); cudaFree(ctx->nonIntBits);
+    cudaFree(ctx->x); cudaFree(ctx->xPrev); cudaFree(ctx->xBar); cudaFree(ctx->Vc); cudaFree(ctx->tdiag);
+    cudaFree(ctx->z); cudaFree(ctx->u); cudaFree(ctx->B); cudaFree(ctx->gs);
+    cudaFree(ctx->incPtr); cudaFree(ctx->incIdx);
+    cudaFree(ctx->grid); cudaFree(ctx->ax); cudaFree(ctx->ay); cudaFree(ctx->az);
+    cudaFree(ctx->partIh); cudaFree(ctx->partDual); cudaFree(ctx->partPrimal); cudaFree(ctx->scal_d);
+    if (ctx->scal_h) cudaFreeHost(ctx->scal_h);
+    cudaFree(ctx->status_d);
+    if (ctx->status_h) cudaFreeHost(ctx->status_h);
+    cudaFree(ctx->hist_d);
+    for (auto e : ctx->evPool) cudaEventDestroy(e);
+    if (ctx->stream) cudaStreamDestroy(ctx->stream);
+    delete ctx;
+}
+
+const char *mmadmm_last_error(mmadmm_ctx *ctx) { return ctx ? ctx->err.c_str() : "null context"; }
+
+}  // extern "C"

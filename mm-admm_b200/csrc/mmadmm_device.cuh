@@ -1,0 +1,347 @@
+// Device-side FP64 math of the MM-ADMM hot path for sm_100a.
+//
+//   block_grad<D>      AdaptationFunctional<D>::blockGrad      (reference src/AdaptationFunctional.cpp:102-287)
+//   eval_monitor<D>    MeshInterpolator<D>::evalMonitorOnGrid  (reference src/MeshInterpolator.cpp:286-342)
+//   find_cell          utils::findLimInfMeshPoint              (reference src/MeshUtils.h:45-54)
+//
+// Everything is fixed-size and fully unrolled so it lives in registers; the pow() calls of the reference
+// (exponents 1.5, 0.5, -0.5, 2.25, 1.25 only, because p = 3/2 and theta = 1/3 are hard-coded there,
+// AdaptationFunctional.cpp:210-211) are sqrt chains.  No tensor cores: the matrices are 2x2 / 3x3.
+#pragma once
+#include <cstdint>
+#include <cuda_runtime.h>
+
+namespace mmadmm {
+
+enum NodeTypeDev { NT_BOUNDARY_FREE = 0, NT_BOUNDARY_FIXED = 1, NT_INTERIOR = 2 };  // src/NodeType.h:4-8
+enum StatusBits { ST_INVERTED = 1, ST_SINGULAR_HESS = 2, ST_BFGS_MAX = 4, ST_NONFINITE = 8 };
+
+// Monitor grid (read-only after init).  Rows are grid points, D*D doubles each, row index
+// zInd*(nx+1)*(ny+1) + yInd*(nx+1) + xInd exactly as the reference's lookup reads it.
+struct MonGrid {
+    const double *vals;
+    const double *ax, *ay, *az;  // axis coordinates, nx+1 / ny+1 / nz+1 entries (utils::linspace values)
+    int nx, ny, nz;
+};
+
+template <int D> struct SMat {
+    double a[D * D];
+    __device__ __forceinline__ double &operator()(int i, int j) { return a[i * D + j]; }
+    __device__ __forceinline__ double operator()(int i, int j) const { return a[i * D + j]; }
+};
+
+template <int D> __device__ __forceinline__ double sdet(const SMat<D> &m);
+template <> __device__ __forceinline__ double sdet<2>(const SMat<2> &m) { return m(0, 0) * m(1, 1) - m(1, 0) * m(0, 1); }
+template <> __device__ __forceinline__ double sdet<3>(const SMat<3> &m) {
+    return m(0, 0) * (m(1, 1) * m(2, 2) - m(1, 2) * m(2, 1)) - m(0, 1) * (m(1, 0) * m(2, 2) - m(1, 2) * m(2, 0)) +
+           m(0, 2) * (m(1, 0) * m(2, 1) - m(1, 1) * m(2, 0));
+}
+template <int D> __device__ __forceinline__ SMat<D> sinv(const SMat<D> &m);
+template <> __device__ __forceinline__ SMat<2> sinv<2>(const SMat<2> &m) {
+    SMat<2> r;
+    double invdet = 1.0 / sdet<2>(m);
+    r(0, 0) = m(1, 1) * invdet;
+    r(1, 0) = -m(1, 0) * invdet;
+    r(0, 1) = -m(0, 1) * invdet;
+    r(1, 1) = m(0, 0) * invdet;
+    return r;
+}
+template <> __device__ __forceinline__ SMat<3> sinv<3>(const SMat<3> &m) {
+    SMat<3> r;
+    // cofactor form (what a fixed-size 3x3 inverse does): r(j,i) = cof(i,j)/det
+    double c00 = m(1, 1) * m(2, 2) - m(1, 2) * m(2, 1);
+    double c10 = m(2, 1) * m(0, 2) - m(2, 2) * m(0, 1);
+    double c20 = m(0, 1) * m(1, 2) - m(0, 2) * m(1, 1);
+    double invdet = 1.0 / (c00 * m(0, 0) + c10 * m(1, 0) + c20 * m(2, 0));
+    r(0, 0) = c00 * invdet; r(0, 1) = c10 * invdet; r(0, 2) = c20 * invdet;
+    r(1, 0) = (m(1, 2) * m(2, 0) - m(1, 0) * m(2, 2)) * invdet;
+    r(1, 1) = (m(2, 2) * m(0, 0) - m(2, 0) * m(0, 2)) * invdet;
+    r(1, 2) = (m(0, 2) * m(1, 0) - m(0, 0) * m(1, 2)) * invdet;
+    r(2, 0) = (m(1, 0) * m(2, 1) - m(1, 1) * m(2, 0)) * invdet;
+    r(2, 1) = (m(2, 0) * m(0, 1) - m(2, 1) * m(0, 0)) * invdet;
+    r(2, 2) = (m(0, 0) * m(1, 1) - m(0, 1) * m(1, 0)) * invdet;
+    return r;
+}
+template <int D> __device__ __forceinline__ SMat<D> smul(const SMat<D> &A, const SMat<D> &B) {
+    SMat<D> C;
+#pragma unroll
+    for (int i = 0; i < D; i++)
+#pragma unroll
+        for (int j = 0; j < D; j++) {
+            double s = A(i, 0) * B(0, j);
+#pragma unroll
+            for (int k = 1; k < D; k++) s += A(i, k) * B(k, j);
+            C(i, j) = s;
+        }
+    return C;
+}
+// A * B^T
+template <int D> __device__ __forceinline__ SMat<D> smul_nt(const SMat<D> &A, const SMat<D> &B) {
+    SMat<D> C;
+#pragma unroll
+    for (int i = 0; i < D; i++)
+#pragma unroll
+        for (int j = 0; j < D; j++) {
+            double s = A(i, 0) * B(j, 0);
+#pragma unroll
+            for (int k = 1; k < D; k++) s += A(i, k) * B(j, k);
+            C(i, j) = s;
+        }
+    return C;
+}
+// A^T * B
+template <int D> __device__ __forceinline__ SMat<D> smul_tn(const SMat<D> &A, const SMat<D> &B) {
+    SMat<D> C;
+#pragma unroll
+    for (int i = 0; i < D; i++)
+#pragma unroll
+        for (int j = 0; j < D; j++) {
+            double s = A(0, i) * B(0, j);
+#pragma unroll
+            for (int k = 1; k < D; k++) s += A(k, i) * B(k, j);
+            C(i, j) = s;
+        }
+    return C;
+}
+
+// t^(d*p/2) and t^(d*p/2 - 1) with p = 3/2:  D=2 -> t^1.5, t^0.5 ; D=3 -> t^2.25, t^1.25
+template <int D> __device__ __forceinline__ void pow_pair(double t, double &p_full, double &p_m1) {
+    if (D == 2) {
+        double s = sqrt(t);
+        p_m1 = s;
+        p_full = t * s;
+    } else {
+        double q = sqrt(sqrt(t));
+        p_m1 = t * q;
+        p_full = t * p_m1;
+    }
+}
+
+// utils::findLimInfMeshPoint: uint32 wrap for negatives => clamp to the last cell (size-2 = nIntervals-1)
+__device__ __forceinline__ int find_cell(double w, double a0, double a1, int nIntervals) {
+    uint32_t guess = (uint32_t)(int)((w - a0) / (a1 - a0));
+    if (guess > (uint32_t)(nIntervals - 1)) guess = (uint32_t)(nIntervals - 1);
+    return (int)guess;
+}
+
+template <int D> __device__ __forceinline__ void eval_monitor(const MonGrid &g, const double *pnt, SMat<D> &mVal);
+
+template <> __device__ __forceinline__ void eval_monitor<2>(const MonGrid &g, const double *pnt, SMat<2> &mVal) {
+    const double ax0 = __ldg(g.ax), ax1 = __ldg(g.ax + 1), ay0 = __ldg(g.ay), ay1 = __ldg(g.ay + 1);
+    int xInd = find_cell(pnt[0], ax0, ax1, g.nx);
+    int yInd = find_cell(pnt[1], ay0, ay1, g.ny);
+    double x0 = __ldg(g.ax + xInd), x1 = __ldg(g.ax + xInd + 1);
+    double y0 = __ldg(g.ay + yInd), y1 = __ldg(g.ay + yInd + 1);
+    double x = pnt[0], y = pnt[1];
+    double norm = (1 / ((x1 - x0) * (y1 - y0)));
+    double c0 = norm * (x1 - x) * (y1 - y);
+    double c1 = norm * (x - x0) * (y1 - y);
+    double c2 = norm * (x1 - x) * (y - y0);
+    double c3 = norm * (x - x0) * (y - y0);
+    // two adjacent grid points are 64 contiguous bytes (2 x 4 doubles): four 16-byte loads per grid row
+    const double2 *r0 = reinterpret_cast<const double2 *>(g.vals) + 2 * ((size_t)yInd * (g.nx + 1) + xInd);
+    const double2 *r1 = r0 + 2 * (size_t)(g.nx + 1);
+    double2 g00a = __ldg(r0), g00b = __ldg(r0 + 1), g10a = __ldg(r0 + 2), g10b = __ldg(r0 + 3);
+    double2 g01a = __ldg(r1), g01b = __ldg(r1 + 1), g11a = __ldg(r1 + 2), g11b = __ldg(r1 + 3);
+    mVal.a[0] = c0 * g00a.x + c1 * g10a.x + c2 * g01a.x + c3 * g11a.x;
+    mVal.a[1] = c0 * g00a.y + c1 * g10a.y + c2 * g01a.y + c3 * g11a.y;
+    mVal.a[2] = c0 * g00b.x + c1 * g10b.x + c2 * g01b.x + c3 * g11b.x;
+    mVal.a[3] = c0 * g00b.y + c1 * g10b.y + c2 * g01b.y + c3 * g11b.y;
+}
+
+template <> __device__ __forceinline__ void eval_monitor<3>(const MonGrid &g, const double *pnt, SMat<3> &mVal) {
+    const double ax0 = __ldg(g.ax), ax1 = __ldg(g.ax + 1), ay0 = __ldg(g.ay), ay1 = __ldg(g.ay + 1);
+    const double az0 = __ldg(g.az), az1 = __ldg(g.az + 1);
+    int xInd = find_cell(pnt[0], ax0, ax1, g.nx);
+    int yInd = find_cell(pnt[1], ay0, ay1, g.ny);
+    int zInd = find_cell(pnt[2], az0, az1, g.nz);
+    double x0 = __ldg(g.ax + xInd), x1 = __ldg(g.ax + xInd + 1);
+    double y0 = __ldg(g.ay + yInd), y1 = __ldg(g.ay + yInd + 1);
+    double z0 = __ldg(g.az + zInd), z1 = __ldg(g.az + zInd + 1);
+    // utils::triLinearInterpolation (src/MeshUtils.h:65-80)
+    double xd = (pnt[0] - x0) / (x1 - x0);
+    double yd = (pnt[1] - y0) / (y1 - y0);
+    double zd = (pnt[2] - z0) / (z1 - z0);
+    double c[8];
+    c[0] = (1 - xd) * (1 - yd) * (1 - zd);
+    c[1] = xd * (1 - yd) * (1 - zd);
+    c[2] = (1 - xd) * yd * (1 - zd);
+    c[3] = xd * yd * (1 - zd);
+    c[4] = (1 - xd) * (1 - yd) * zd;
+    c[5] = xd * (1 - yd) * zd;
+    c[6] = (1 - xd) * yd * zd;
+    c[7] = xd * yd * zd;
+    const size_t sl = (size_t)(g.nx + 1) * (g.ny + 1);
+    const size_t base = (size_t)zInd * sl + (size_t)yInd * (g.nx + 1) + xInd;
+#pragma unroll
+    for (int k = 0; k < 9; k++) mVal.a[k] = 0.0;
+#pragma unroll
+    for (int cc = 0; cc < 8; cc++) {
+        size_t row = base + ((cc & 1) ? 1 : 0) + ((cc & 2) ? (size_t)(g.nx + 1) : 0) + ((cc & 4) ? sl : 0);
+        const double *r = g.vals + row * 9;
+#pragma unroll
+        for (int k = 0; k < 9; k++) mVal.a[k] += c[cc] * __ldg(r + k);
+    }
+}
+
+// Constants of the functional that the reference recomputes per call (AdaptationFunctional.cpp:176-201,
+// 219-220): computed once on the host with the reference's own expressions (libm pow) and passed by value.
+template <int D> struct FuncConsts {
+    double Ehat[D * D];  // reference simplex scaled to volume 1/N (used when !compMesh)
+    double dpow;         // pow(d, d*p/2)
+    double w2;           // w*w (ADMM penalty)
+};
+
+// Energy G*|K| and (optionally) the unregularised element gradient.  z: n = D(D+1) doubles, vertex-major.
+// Returns absK*G.  `inverted` is set when det(E) <= 0 (the reference asserts there, :174).
+template <int D, bool GRAD>
+__device__ __forceinline__ double block_grad(const double *z, const double *xi, bool compMesh, const MonGrid &mg,
+                                             const FuncConsts<D> &fc, double *grad, bool &inverted) {
+    constexpr int n = D * (D + 1);
+    const double dFact = (D == 2) ? 2.0 : 6.0;
+    const double d = (double)D;
+    const double p = 1.5;
+    const double theta = 1.0 / 3.0;
+
+    SMat<D> mPre[D + 1];
+    SMat<D> M;
+#pragma unroll
+    for (int k = 0; k < D * D; k++) M.a[k] = 0.0;
+#pragma unroll
+    for (int i = 0; i < D + 1; i++) {
+        eval_monitor<D>(mg, z + i * D, mPre[i]);
+#pragma unroll
+        for (int k = 0; k < D * D; k++) M.a[k] += mPre[i].a[k];
+    }
+    SMat<D> Minv = sinv<D>(M);
+#pragma unroll
+    for (int k = 0; k < D * D; k++) Minv.a[k] /= ((double)D + 1);  // sic: M^{-1}/(D+1), :157
+
+    SMat<D> E, Ehat;
+#pragma unroll
+    for (int j = 0; j < D; j++)
+#pragma unroll
+        for (int l = 0; l < D; l++) {
+            E(l, j) = z[D * (j + 1) + l] - z[l];
+            Ehat(l, j) = compMesh ? (xi[D * (j + 1) + l] - xi[l]) : fc.Ehat[l * D + j];
+        }
+    double Edet = sdet<D>(E);
+    if (!(Edet > 0)) inverted = true;
+
+    SMat<D> Einv = sinv<D>(E);
+    SMat<D> FJ = smul<D>(Ehat, Einv);
+    double detFJ = sdet<D>(FJ);
+
+    SMat<D> MinvJt = smul_nt<D>(Minv, FJ);  // Minv * FJ^T
+    SMat<D> JMJt = smul<D>(FJ, MinvJt);
+    double trJMJt = JMJt(0, 0);
+#pragma unroll
+    for (int i = 1; i < D; i++) trJMJt += JMJt(i, i);
+    double detM = sqrt(1.0 / sdet<D>(Minv));
+
+    double trp, trpm1;
+    pow_pair<D>(trJMJt, trp, trpm1);
+    double q = detFJ / detM;
+    double G = theta * detM * trp + (1.0 - 2.0 * theta) * fc.dpow * detM * (q * sqrt(q));
+    double absK = fabs(Edet / dFact);
+    if (!GRAD) return absK * G;
+
+    double sJ = d * p * theta * detM * trpm1;
+    SMat<D> dGdJ;
+#pragma unroll
+    for (int k = 0; k < D * D; k++) dGdJ.a[k] = sJ * MinvJt.a[k];
+    double rsDetM = 1.0 / sqrt(detM);   // detM^(1-p)
+    double sDetFJ = sqrt(detFJ);        // detFJ^(p-1)
+    double dGddet = p * (1.0 - 2.0 * theta) * fc.dpow * rsDetM * sDetFJ;
+    SMat<D> dGdM;
+    {
+        double s1 = -0.5 * theta * d * p * detM * trpm1;
+        // Minv^T * FJ^T * FJ * Minv
+        SMat<D> A = smul_tn<D>(Minv, smul_tn<D>(FJ, smul<D>(FJ, Minv)));
+        // note: reference order ((Minv^T FJ^T) FJ) Minv; reassociated (rounding-level) to reuse FJ*Minv
+        double s2 = (0.5 * theta * detM * trp + ((0.5 - theta) * (1.0 - p) * fc.dpow) * rsDetM * (detFJ * sDetFJ));
+#pragma unroll
+        for (int k = 0; k < D * D; k++) dGdM.a[k] = s1 * A.a[k] + s2 * Minv.a[k];
+    }
+    double basisComb[D];
+#pragma unroll
+    for (int l = 0; l < D; l++) basisComb[l] = 0.0;
+#pragma unroll
+    for (int j = 0; j < D; j++) {
+        // trace(dGdM * (mPre[j+1] - mPre[0]))
+        double tr = 0.0;
+#pragma unroll
+        for (int a = 0; a < D; a++)
+#pragma unroll
+            for (int b = 0; b < D; b++) tr += dGdM(a, b) * (mPre[j + 1](b, a) - mPre[0](b, a));
+#pragma unroll
+        for (int l = 0; l < D; l++) basisComb[l] += Einv(j, l) * tr;
+    }
+    double c1 = (-G + dGddet * detFJ);
+    SMat<D> T = smul<D>(smul<D>(Einv, dGdJ), FJ);
+    SMat<D> vLoc;
+#pragma unroll
+    for (int r = 0; r < D; r++)
+#pragma unroll
+        for (int l = 0; l < D; l++) vLoc(r, l) = (c1 * Einv(r, l) + T(r, l)) - basisComb[l] / ((double)D + 1.0);
+    double g0[D];
+#pragma unroll
+    for (int l = 0; l < D; l++) {
+        double s = 0.0;
+#pragma unroll
+        for (int r = 0; r < D; r++) s += vLoc(r, l);
+        g0[l] = s + basisComb[l];
+    }
+#pragma unroll
+    for (int l = 0; l < D; l++) grad[l] = g0[l] * absK;
+#pragma unroll
+    for (int nn = 1; nn < D + 1; nn++)
+#pragma unroll
+        for (int l = 0; l < D; l++) grad[D * nn + l] = (-vLoc(nn - 1, l)) * absK;
+    (void)n;
+    return absK * G;
+}
+
+// Regularised + masked gradient as Mesh::computeBlockGrad(.., regularize=true) returns it
+// (src/Mesh.cpp:755-772 on top of AdaptationFunctional.cpp:279-282).  Returns the UNregularised energy (Igt).
+template <int D>
+__device__ __forceinline__ double prox_grad(const double *z, const double *dxpu, const double *xi, bool compMesh,
+                                            const MonGrid &mg, const FuncConsts<D> &fc, unsigned fixedBits, double *grad,
+                                            bool &inverted) {
+    constexpr int n = D * (D + 1);
+    double Igt = block_grad<D, true>(z, xi, compMesh, mg, fc, grad, inverted);
+#pragma unroll
+    for (int k = 0; k < n; k++) grad[k] += fc.w2 * (-dxpu[k] + z[k]);
+#pragma unroll
+    for (int v = 0; v < D + 1; v++)
+        if (fixedBits & (1u << v)) {
+#pragma unroll
+            for (int l = 0; l < D; l++) grad[D * v + l] = 0.0;
+        }
+    return Igt;
+}
+
+// ------------------------------------------------------------------------------------------------
+// reductions
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ double warp_sum(double v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+// Sum over the block; result valid in thread 0.  blockDim.x multiple of 32, <= 1024.
+__device__ __forceinline__ double block_sum(double v, double *smem /* >= 32 doubles */) {
+    v = warp_sum(v);
+    int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    __syncthreads();
+    if (lane == 0) smem[wid] = v;
+    __syncthreads();
+    double r = 0.0;
+    if (wid == 0) {
+        r = (lane < (int)(blockDim.x >> 5)) ? smem[lane] : 0.0;
+        r = warp_sum(r);
+    }
+    return r;
+}
+
+}  // namespace mmadmm
