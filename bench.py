@@ -159,6 +159,7 @@ def main():
     ap.add_argument("--nx", type=int, default=0, help="override the mesh resolution (debugging)")
     ap.add_argument("--cpu-nx", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--prox-variant", type=int, default=-1, help="prox kernel tile/occupancy variant (debugging; -1 = library default)")
     args = ap.parse_args()
     if args.impl == "reference":
         return reference_arm(args)
@@ -196,6 +197,8 @@ def main():
         t0 = time.perf_counter()
         solver = mm.MeshIntegrator(PARAMS["dt"], mesh, device=local, sync_vp=False)
         state["init_s"] = time.perf_counter() - t0
+        if args.prox_variant >= 0:
+            solver.set_option("prox_variant", args.prox_variant)
         state["e0"] = solver.getEnergy()
         warm = []
         for _ in range(W):

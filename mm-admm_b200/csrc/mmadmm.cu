@@ -6,12 +6,13 @@
 //                          src/Mesh.cpp:777-872), u = DXpU - z, ||z - zPrev||^2 and sum(Ih) partials
 //   k_xupdate   K3b+K4     vec = tau*xBar + dt^2 WD^T(w (z-u)) by vertex->element incidence gather (deterministic),
 //                          x = vec / diag(t)  (t is numerically diagonal)
-//   k_residual  K5         ||D x - z||^2 partials;  k_finalize reduces the three scalars in a fixed order
+//               K5         ||D x - z||^2 partials in the same pass;  k_finalize reduces the three scalars in a fixed order
 // Element state is SoA over elements (component-major planes of length E) so every warp access is
 // one contiguous 256-byte line.
 #include <cuda_runtime.h>
 #include <cub/cub.cuh>
 
+#include <algorithm>
 #include <cmath>
 #include <cstdio>
 #include <cstring>
@@ -40,9 +41,13 @@ namespace {
 constexpr int TPB = 128;       // element kernels: threads per block
 constexpr int TPB_V = 256;     // vertex kernels
 constexpr int MAXV = 4;        // D+1 <= 4
+constexpr int ES_ALIGN = 128;  // element planes are padded to full prox tiles (TMA bulk copies need whole, aligned tiles)
 
 template <int D> struct ElemArgs {
     int E, P;
+    size_t Es;                   // plane stride of the SoA element state (E rounded up to a multiple of ES_ALIGN)
+    const double *zsrc;          // non-null: z enters the sweep as D*zsrc (gathered), the z planes are not read
+    int uZero;                   // u == 0 on entry (before the first step is taken): the u planes are not read
     const int *F[MAXV];          // connectivity planes F[v][e]
     const uint8_t *fixedBits;    // bit v: vertex v of the element is BOUNDARY_FIXED
     const uint8_t *nonIntBits;   // bit v: vertex v is not INTERIOR
@@ -114,6 +119,10 @@ template <int D> __global__ void k_inc_pairs(int E, const int *F0, const int *F1
         keys[(size_t)e * (D + 1) + v] = F[v][e];
         vals[(size_t)e * (D + 1) + v] = e * 4 + v;
     }
+}
+__global__ void k_fill(size_t n, double *p, double v) {
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) p[i] = v;
 }
 __global__ void k_count_keys(size_t n, const int *keys, int *cnt) {
     size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -291,7 +300,26 @@ template <int D> __global__ void __launch_bounds__(TPB) k_euler_elem(ElemArgs<D>
 #pragma unroll
     for (int v = 0; v < D + 1; v++)
 #pragma unroll
-        for (int l = 0; l < D; l++) gs[(size_t)(D * v + l) * a.E + e] = (fb & (1u << v)) ? 0.0 : g[D * v + l];
+        for (int l = 0; l < D; l++) gs[(size_t)(D * v + l) * a.Es + e] = (fb & (1u << v)) ? 0.0 : g[D * v + l];
+}
+
+// DXpU = D x + u and the sweep's entry z for element e (src/MeshIntegrator.cpp:120-127,146)
+template <int D>
+__device__ __forceinline__ void load_z_dx(const ElemArgs<D> &a, int e, const int *vid, double *z, double *dx) {
+    constexpr int n = D * (D + 1);
+#pragma unroll
+    for (int v = 0; v < D + 1; v++) gather_vertex<D>(a.x, vid[v], dx + D * v);
+    if (!a.uZero) {
+#pragma unroll
+        for (int k = 0; k < n; k++) dx[k] += a.u[k * a.Es + e];
+    }
+    if (a.zsrc) {
+#pragma unroll
+        for (int v = 0; v < D + 1; v++) gather_vertex<D>(a.zsrc, vid[v], z + D * v);
+    } else {
+#pragma unroll
+        for (int k = 0; k < n; k++) z[k] = a.z[k * a.Es + e];
+    }
 }
 
 // first prox sweep only (hessComputed == false): finite-difference Hessian of the regularised, masked gradient,
@@ -304,13 +332,7 @@ template <int D> __global__ void __launch_bounds__(TPB) k_hess_init(ElemArgs<D> 
     load_elem_ids<D>(a, e, vid);
     unsigned fb = a.fixedBits[e], nb = a.nonIntBits[e];
     double z[n], dx[n], xi[n], Gk[n], G1[n];
-#pragma unroll
-    for (int v = 0; v < D + 1; v++) gather_vertex<D>(a.x, vid[v], dx + D * v);
-#pragma unroll
-    for (int k = 0; k < n; k++) {
-        dx[k] += a.u[(size_t)k * a.E + e];
-        z[k] = a.z[(size_t)k * a.E + e];
-    }
+    load_z_dx<D>(a, e, vid, z, dx);
     load_xi<D>(a, vid, xi);
     bool inv = false;
     prox_grad<D>(z, dx, xi, a.compMesh, a.mg, a.fc, fb, Gk, inv);
@@ -363,73 +385,95 @@ template <int D> __global__ void __launch_bounds__(TPB) k_hess_init(ElemArgs<D> 
             for (int j = i + 1; j < n; j++) s -= H[i * n + j] * y[j];
             y[i] = s / H[i * n + i];
         }
-        for (int i = 0; i < n; i++) a.B[(size_t)(i * n + c) * a.E + e] = y[i];
+        for (int i = 0; i < n; i++) a.B[(size_t)(i * n + c) * a.Es + e] = y[i];
     }
 }
 
-// K1+K2+K3a: the per-element BFGS prox (thread per element; B held in registers for D=2)
-template <int D> __global__ void __launch_bounds__(TPB) k_prox(ElemArgs<D> a) {
+// K1+K2+K3a: the per-element BFGS prox (Mesh::prox -> bfgsOptSimplex, src/Mesh.cpp:930-994, 777-872), one thread per
+// element.  The CTA's tile of inverse Hessians (n*n planes x TPB elements) is brought into shared memory by TMA
+// bulk copies while the threads gather their vertices and evaluate the entry gradient; the three passes over
+// Bkinv (pk = -B g; B y and y^T B; rank-2 update) run out of shared memory ([plane][thread]: conflict-free), and the
+// updated tile goes back with TMA bulk stores.  Also: DXpU = D x + u (K1), u = DXpU - z (K3a), sum(Ih) and
+// ||z - zPrev||^2 partials (K5).
+template <int D, int TPB_, int MINB, bool COMP>
+__global__ void __launch_bounds__(TPB_, MINB) k_prox(ElemArgs<D> a) {
     constexpr int n = D * (D + 1);
-    __shared__ double red[32];
-    __shared__ int shist[52];
-    if (a.hist) {
-        if (threadIdx.x < 52) shist[threadIdx.x] = 0;
-        __syncthreads();
+    constexpr int NN = n * n;
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    double *Bs = reinterpret_cast<double *>(smem_raw);                 // [NN][TPB_]
+    uint64_t *bar = reinterpret_cast<uint64_t *>(Bs + (size_t)NN * TPB_);
+    double *red = reinterpret_cast<double *>(bar + 2);                 // 32 doubles
+    int *shist = reinterpret_cast<int *>(red + 32);                    // 52 ints
+    const int tid = threadIdx.x;
+    const size_t e0 = (size_t)blockIdx.x * TPB_;
+    if (tid == 0) mbar_init(bar, 1);
+    if (a.hist && tid < 52) shist[tid] = 0;
+    __syncthreads();
+    if (tid == 0) mbar_expect_tx(bar, (unsigned)(NN * TPB_ * sizeof(double)));
+    if (tid < 32) {
+        for (int k = tid; k < NN; k += 32)
+            bulk_g2s(Bs + (size_t)k * TPB_, a.B + (size_t)k * a.Es + e0, (unsigned)(TPB_ * sizeof(double)), bar);
     }
-    const int e = blockIdx.x * TPB + threadIdx.x;
+    const int e = (int)e0 + tid;
     double ih = 0.0, dual2 = 0.0;
-    if (e < a.E) {
-        const size_t E = a.E;
+    const bool active = e < a.E;
+    double z[n], dx[n], xi[COMP ? n : 1], Gk[n];
+    unsigned fb = 0;
+    bool inv = false;
+    if (active) {
         int vid[D + 1];
         load_elem_ids<D>(a, e, vid);
-        const unsigned fb = a.fixedBits[e];
-        double z[n], dx[n], xi[n], Gk[n], G1[n], zold[n];
+        fb = a.fixedBits[e];
+        load_z_dx<D>(a, e, vid, z, dx);
+        if (COMP) {
 #pragma unroll
-        for (int v = 0; v < D + 1; v++) gather_vertex<D>(a.x, vid[v], dx + D * v);
-#pragma unroll
-        for (int k = 0; k < n; k++) {
-            dx[k] += a.u[k * E + e];          // DXpU = D x + u
-            z[k] = a.z[k * E + e];
-            zold[k] = z[k];
+            for (int v = 0; v < D + 1; v++) gather_vertex<D>(a.Vc, vid[v], xi + D * v);
         }
-        load_xi<D>(a, vid, xi);
-        double B[n * n];
+        ih = prox_grad<D>(z, dx, xi, COMP, a.mg, a.fc, fb, Gk, inv);   // Ihsave: energy at entry
+    }
+    mbar_wait(bar, 0);
+    if (active) {
+        double *Bt = Bs + tid;
+#define BS(k) Bt[(k) * TPB_]
+        double dz[n];
 #pragma unroll
-        for (int k = 0; k < n * n; k++) B[k] = a.B[k * E + e];
-        bool inv = false;
-        ih = prox_grad<D>(z, dx, xi, a.compMesh, a.mg, a.fc, fb, Gk, inv);   // Ihsave: energy at entry
+        for (int k = 0; k < n; k++) dz[k] = 0.0;
         int iter;
         for (iter = 0; iter < 50; iter++) {
-            double pk[n];
+            double pk[n], G1[n];
 #pragma unroll
             for (int r = 0; r < n; r++) {
-                double s = B[r * n] * Gk[0];
+                double s = BS(r * n) * Gk[0];
 #pragma unroll
-                for (int c = 1; c < n; c++) s += B[r * n + c] * Gk[c];
+                for (int c = 1; c < n; c++) s += BS(r * n + c) * Gk[c];
                 pk[r] = -s;
-                z[r] += pk[r];
             }
-            prox_grad<D>(z, dx, xi, a.compMesh, a.mg, a.fc, fb, G1, inv);
+            if (iter == 0) {
+#pragma unroll
+                for (int k = 0; k < n; k++) { dz[k] = z[k]; z[k] += pk[k]; }   // dz holds zPrev until the end
+            } else {
+#pragma unroll
+                for (int k = 0; k < n; k++) z[k] += pk[k];
+            }
+            prox_grad<D>(z, dx, xi, COMP, a.mg, a.fc, fb, G1, inv);
             double Ix = 0.0, yk[n];
 #pragma unroll
-            for (int k = 0; k < n; k++) { Ix += fabs(G1[k]); yk[k] = G1[k] - Gk[k]; }
+            for (int k = 0; k < n; k++) { Ix += fabs(G1[k]); yk[k] = G1[k] - Gk[k]; Gk[k] = G1[k]; }
             double c2 = pk[0] * yk[0];
 #pragma unroll
             for (int k = 1; k < n; k++) c2 += pk[k] * yk[k];
+            // one pass over B for both B*yk (rows) and yk^T*B (columns); accumulation order as in the two-pass form
             double By[n], yB[n];
 #pragma unroll
             for (int r = 0; r < n; r++) {
-                double s = B[r * n] * yk[0];
+                double s = 0.0;
 #pragma unroll
-                for (int c = 1; c < n; c++) s += B[r * n + c] * yk[c];
+                for (int c = 0; c < n; c++) {
+                    const double b = BS(r * n + c);
+                    s = (c == 0) ? b * yk[0] : s + b * yk[c];
+                    yB[c] = (r == 0) ? yk[0] * b : yB[c] + yk[r] * b;
+                }
                 By[r] = s;
-            }
-#pragma unroll
-            for (int c = 0; c < n; c++) {
-                double s = yk[0] * B[c];
-#pragma unroll
-                for (int r = 1; r < n; r++) s += yk[r] * B[r * n + c];
-                yB[c] = s;
             }
             double yBy = yk[0] * By[0];
 #pragma unroll
@@ -440,32 +484,203 @@ template <int D> __global__ void __launch_bounds__(TPB) k_prox(ElemArgs<D> a) {
             for (int r = 0; r < n; r++) {
                 const double a1 = c1 * pk[r], a3 = pk[r] * ic2, a2 = By[r] * ic2;
 #pragma unroll
-                for (int c = 0; c < n; c++) B[r * n + c] += (a1 * pk[c] - a2 * pk[c]) - a3 * yB[c];
+                for (int c = 0; c < n; c++) BS(r * n + c) += (a1 * pk[c] - a2 * pk[c]) - a3 * yB[c];
             }
-#pragma unroll
-            for (int k = 0; k < n; k++) Gk[k] = G1[k];
             if (Ix < a.tol) break;
         }
+#undef BS
         if (inv) atomicOr(a.status, ST_INVERTED);
         if (iter == 50) atomicOr(a.status, ST_BFGS_MAX);
         if (a.hist) atomicAdd(&shist[(iter == 50) ? 51 : iter + 1], 1);
 #pragma unroll
         for (int k = 0; k < n; k++) {
-            a.z[k * E + e] = z[k];
-            a.u[k * E + e] = dx[k] - z[k];    // u = DXpU - z
-            double dz = z[k] - zold[k];
-            dual2 += dz * dz;
+            a.z[k * a.Es + e] = z[k];
+            a.u[k * a.Es + e] = dx[k] - z[k];    // u = DXpU - z
+            const double d = z[k] - dz[k];
+            dual2 += d * d;
         }
-#pragma unroll
-        for (int k = 0; k < n * n; k++) a.B[k * E + e] = B[k];
+    }
+    // updated tile back to HBM: generic-proxy writes -> async proxy, then bulk stores
+    fence_async_smem();
+    __syncthreads();
+    if (tid < 32) {
+        for (int k = tid; k < NN; k += 32)
+            bulk_s2g(a.B + (size_t)k * a.Es + e0, Bs + (size_t)k * TPB_, (unsigned)(TPB_ * sizeof(double)));
+        bulk_commit();
     }
     double s1 = block_sum(ih, red);
     double s2 = block_sum(dual2, red);
-    if (threadIdx.x == 0) { a.partIh[blockIdx.x] = s1; a.partDual[blockIdx.x] = s2; }
+    if (tid == 0) { a.partIh[blockIdx.x] = s1; a.partDual[blockIdx.x] = s2; }
     if (a.hist) {
         __syncthreads();
-        if (threadIdx.x < 52 && shist[threadIdx.x]) atomicAdd(&a.hist[threadIdx.x], (unsigned long long)shist[threadIdx.x]);
+        if (tid < 52 && shist[tid]) atomicAdd(&a.hist[tid], (unsigned long long)shist[tid]);
     }
+    if (tid < 32) bulk_wait_read0();   // shared memory must stay allocated until the bulk stores have read it
+}
+
+// Warp-tile form of the prox kernel (thread per element, used for D = 2): every warp owns a tile of 32 elements with its
+// own mbarriers, its own TMA loads (B planes, u planes, z planes) and its own TMA stores, so there is no CTA barrier
+// anywhere: a warp that is waiting on HBM never holds up its neighbours.  u lands in the shared-memory slot that then
+// holds DXpU, z in the slot that holds zPrev, so the only per-thread state kept across a gradient evaluation is
+// z, Gk and pk.  Per-CTA sums / histogram are combined by the last warp to finish (fixed order -> deterministic).
+template <int D, int WPB, int MINB, bool COMP>
+__global__ void __launch_bounds__(WPB * 32, MINB) k_prox_w(ElemArgs<D> a) {
+    constexpr int n = D * (D + 1);
+    constexpr int NN = n * n;
+    constexpr int WARP_DOUBLES = (NN + 2 * n) * 32;
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    double *Bs = reinterpret_cast<double *>(smem_raw) + (size_t)warp * WARP_DOUBLES;   // [NN][32]
+    double *dxs = Bs + NN * 32;                                                        // [n][32]  u -> DXpU
+    double *zos = dxs + n * 32;                                                        // [n][32]  z at entry (zPrev)
+    uint64_t *bars = reinterpret_cast<uint64_t *>(reinterpret_cast<double *>(smem_raw) + (size_t)WPB * WARP_DOUBLES) + 2 * warp;
+    double *csum = reinterpret_cast<double *>(reinterpret_cast<uint64_t *>(reinterpret_cast<double *>(smem_raw) + (size_t)WPB * WARP_DOUBLES) + 2 * WPB);  // [2][WPB]
+    int *shist = reinterpret_cast<int *>(csum + 2 * WPB);                              // 52 bins
+    int *arrived = shist + 52;
+    if (threadIdx.x < 53) shist[threadIdx.x] = 0;   // 52 bins + arrival counter
+    const size_t e0 = ((size_t)blockIdx.x * WPB + warp) * 32;
+    const int e = (int)e0 + lane;
+    const bool tileLive = e0 < (size_t)a.E;
+    const bool active = e < a.E;
+    const bool haveU = !a.uZero, haveZ = (a.zsrc == nullptr);
+    if (lane == 0) { mbar_init(&bars[0], 1); mbar_init(&bars[1], 1); }
+    __syncthreads();   // the only CTA barrier: barrier init + histogram clear visible
+    if (tileLive) {
+        if (lane == 0) {
+            mbar_expect_tx(&bars[0], (unsigned)(((haveU ? n : 0) + (haveZ ? n : 0)) * 32 * sizeof(double)));
+            mbar_expect_tx(&bars[1], (unsigned)(NN * 32 * sizeof(double)));
+        }
+        __syncwarp();
+        if (lane < n) {
+            if (haveU) bulk_g2s(dxs + lane * 32, a.u + (size_t)lane * a.Es + e0, 256u, &bars[0]);
+            if (haveZ) bulk_g2s(zos + lane * 32, a.z + (size_t)lane * a.Es + e0, 256u, &bars[0]);
+        }
+        for (int k = lane; k < NN; k += 32) bulk_g2s(Bs + k * 32, a.B + (size_t)k * a.Es + e0, 256u, &bars[1]);
+    }
+    double ih = 0.0, dual2 = 0.0;
+    int bin = -1;
+    if (tileLive) {
+        double z[n], xi[COMP ? n : 1], Gk[n];
+        unsigned fb = 0;
+        bool inv = false;
+        int vid[D + 1];
+        if (active) {
+            load_elem_ids<D>(a, e, vid);
+            fb = a.fixedBits[e];
+        }
+        mbar_wait(&bars[0], 0);
+        if (active) {
+            {
+                double dx[n];
+#pragma unroll
+                for (int v = 0; v < D + 1; v++) gather_vertex<D>(a.x, vid[v], dx + D * v);
+#pragma unroll
+                for (int k = 0; k < n; k++) dxs[k * 32 + lane] = haveU ? dx[k] + dxs[k * 32 + lane] : dx[k];   // DXpU = D x + u
+            }
+            if (haveZ) {
+#pragma unroll
+                for (int k = 0; k < n; k++) z[k] = zos[k * 32 + lane];
+            } else {
+#pragma unroll
+                for (int v = 0; v < D + 1; v++) gather_vertex<D>(a.zsrc, vid[v], z + D * v);
+#pragma unroll
+                for (int k = 0; k < n; k++) zos[k * 32 + lane] = z[k];
+            }
+            if (COMP) {
+#pragma unroll
+                for (int v = 0; v < D + 1; v++) gather_vertex<D>(a.Vc, vid[v], xi + D * v);
+            }
+            ih = prox_grad_s<D>(z, dxs + lane, xi, COMP, a.mg, a.fc, fb, Gk, inv);   // Ihsave: energy at entry
+        }
+        mbar_wait(&bars[1], 0);
+        if (active) {
+            double *Bt = Bs + lane;
+#define BS(k) Bt[(k) * 32]
+            int iter;
+            for (iter = 0; iter < 50; iter++) {
+                double pk[n], G1[n];
+#pragma unroll
+                for (int r = 0; r < n; r++) {
+                    double s = BS(r * n) * Gk[0];
+#pragma unroll
+                    for (int c = 1; c < n; c++) s += BS(r * n + c) * Gk[c];
+                    pk[r] = -s;
+                    z[r] += pk[r];
+                }
+                prox_grad_s<D>(z, dxs + lane, xi, COMP, a.mg, a.fc, fb, G1, inv);
+                double Ix = 0.0, yk[n];
+#pragma unroll
+                for (int k = 0; k < n; k++) { Ix += fabs(G1[k]); yk[k] = G1[k] - Gk[k]; Gk[k] = G1[k]; }
+                double c2 = pk[0] * yk[0];
+#pragma unroll
+                for (int k = 1; k < n; k++) c2 += pk[k] * yk[k];
+                double By[n], yB[n];
+#pragma unroll
+                for (int r = 0; r < n; r++) {
+                    double s = 0.0;
+#pragma unroll
+                    for (int c = 0; c < n; c++) {
+                        const double b = BS(r * n + c);
+                        s = (c == 0) ? b * yk[0] : s + b * yk[c];
+                        yB[c] = (r == 0) ? yk[0] * b : yB[c] + yk[r] * b;
+                    }
+                    By[r] = s;
+                }
+                double yBy = yk[0] * By[0];
+#pragma unroll
+                for (int k = 1; k < n; k++) yBy += yk[k] * By[k];
+                const double ic2 = 1.0 / c2;
+                const double c1 = (c2 + yBy) * (ic2 * ic2);
+#pragma unroll
+                for (int r = 0; r < n; r++) {
+                    const double a1 = c1 * pk[r], a3 = pk[r] * ic2, a2 = By[r] * ic2;
+#pragma unroll
+                    for (int c = 0; c < n; c++) BS(r * n + c) += (a1 * pk[c] - a2 * pk[c]) - a3 * yB[c];
+                }
+                if (Ix < a.tol) break;
+            }
+#undef BS
+            if (inv) atomicOr(a.status, ST_INVERTED);
+            if (iter == 50) atomicOr(a.status, ST_BFGS_MAX);
+            bin = (iter == 50) ? 51 : iter + 1;
+#pragma unroll
+            for (int k = 0; k < n; k++) {
+                a.z[k * a.Es + e] = z[k];
+                a.u[k * a.Es + e] = dxs[k * 32 + lane] - z[k];    // u = DXpU - z
+                const double d = z[k] - zos[k * 32 + lane];
+                dual2 += d * d;
+            }
+        }
+        // updated tile back to HBM: generic-proxy writes -> async proxy, then bulk stores by this warp
+        fence_async_smem();
+        __syncwarp();
+        for (int k = lane; k < NN; k += 32) bulk_s2g(a.B + (size_t)k * a.Es + e0, Bs + k * 32, 256u);
+        bulk_commit();
+    }
+    ih = warp_sum(ih);
+    dual2 = warp_sum(dual2);
+    if (a.hist && bin >= 0) atomicAdd(&shist[bin], 1);
+    if (lane == 0) { csum[warp] = ih; csum[WPB + warp] = dual2; }
+    __threadfence_block();
+    int last = 0;
+    if (lane == 0) last = (atomicAdd(arrived, 1) == WPB - 1);
+    last = __shfl_sync(0xffffffffu, last, 0);
+    if (last) {
+        __threadfence_block();
+        if (lane == 0) {
+            double s1 = 0.0, s2 = 0.0;
+            for (int w = 0; w < WPB; w++) { s1 += csum[w]; s2 += csum[WPB + w]; }
+            a.partIh[blockIdx.x] = s1;
+            a.partDual[blockIdx.x] = s2;
+        }
+        if (a.hist) {
+            for (int k = lane; k < 52; k += 32) {
+                int c = ((volatile int *)shist)[k];
+                if (c) atomicAdd(&a.hist[k], (unsigned long long)c);
+            }
+        }
+    }
+    if (tileLive) bulk_wait_read0();   // shared memory must stay allocated until the bulk stores have read it
 }
 
 // z = D * src (gather), src is a P x D vertex vector
@@ -479,41 +694,20 @@ template <int D> __global__ void __launch_bounds__(TPB) k_applyD(ElemArgs<D> a, 
         double p[D];
         gather_vertex<D>(src, vid[v], p);
 #pragma unroll
-        for (int l = 0; l < D; l++) a.z[(size_t)(D * v + l) * a.E + e] = p[l];
+        for (int l = 0; l < D; l++) a.z[(size_t)(D * v + l) * a.Es + e] = p[l];
     }
 }
 
-// K5: ||D x - z||^2 partials
-template <int D> __global__ void __launch_bounds__(TPB) k_residual(ElemArgs<D> a, double *part) {
-    __shared__ double red[32];
-    int e = blockIdx.x * TPB + threadIdx.x;
-    double s = 0.0;
-    if (e < a.E) {
-        int vid[D + 1];
-        load_elem_ids<D>(a, e, vid);
-#pragma unroll
-        for (int v = 0; v < D + 1; v++) {
-            double p[D];
-            gather_vertex<D>(a.x, vid[v], p);
-#pragma unroll
-            for (int l = 0; l < D; l++) {
-                double df = p[l] - a.z[(size_t)(D * v + l) * a.E + e];
-                s += df * df;
-            }
-        }
-    }
-    double r = block_sum(s, red);
-    if (threadIdx.x == 0) part[blockIdx.x] = r;
-}
-
-// fixed-order final reduction of up to 3 partial arrays -> out[0..2]
-__global__ void __launch_bounds__(1024) k_finalize(int nblk, const double *p0, const double *p1, const double *p2, double *out) {
+// fixed-order final reduction of up to 3 partial arrays (lengths n0,n1,n2) -> out[0..2]
+__global__ void __launch_bounds__(1024) k_finalize(int n0, const double *p0, int n1, const double *p1, int n2, const double *p2,
+                                                   double *out) {
     __shared__ double red[32];
     const double *ps[3] = {p0, p1, p2};
+    const int ns[3] = {n0, n1, n2};
     for (int q = 0; q < 3; q++) {
         if (!ps[q]) continue;
         double s = 0.0;
-        for (int i = threadIdx.x; i < nblk; i += blockDim.x) s += ps[q][i];
+        for (int i = threadIdx.x; i < ns[q]; i += blockDim.x) s += ps[q][i];
         double r = block_sum(s, red);
         if (threadIdx.x == 0) out[q] = r;
         __syncthreads();
@@ -523,36 +717,66 @@ __global__ void __launch_bounds__(1024) k_finalize(int nblk, const double *p0, c
 // ------------------------------------------------------------------------------------------------
 // vertex kernels
 // ------------------------------------------------------------------------------------------------
-// K3b+K4: x = (m*xBar + dt^2 * sum_{inc, ascending element} w*(w*(z-u))) / tdiag       (src/MeshIntegrator.cpp:137-138,159-160)
-template <int D>
-__global__ void __launch_bounds__(TPB_V) k_xupdate(int P, size_t E, const int *incPtr, const int *incIdx, const double *z,
-                                                   const double *u, const double *xBar, const double *tdiag, double m,
-                                                   double dtsq, double w, double *x) {
+// K3b+K4(+K5): x = (m*xBar + dt^2 * sum_{inc, ascending element} w*(w*(z-u))) / tdiag   (src/MeshIntegrator.cpp:137-138,159-160)
+//   ZSRC : z == D*zsrc, so every incident slot of vertex p holds zsrc[p] (first solve of a step; z planes not read)
+//   UZERO: u == 0 (before the first step; u planes not read)
+//   PRIMAL: also accumulate ||D x - z||^2 = sum_p sum_{slots of p} |x_p - z_slot|^2 from the z values already in
+//           registers (src/MeshIntegrator.cpp:162) -> per-block partials
+template <int D, bool ZSRC, bool UZERO, bool PRIMAL>
+__global__ void __launch_bounds__(TPB_V) k_xupdate(int P, size_t Es, const int *incPtr, const int *incIdx, const double *z,
+                                                   const double *u, const double *zsrc, const double *xBar,
+                                                   const double *tdiag, double m, double dtsq, double w, double *x,
+                                                   double *partPrimal) {
+    __shared__ double red[32];
     int p = blockIdx.x * TPB_V + threadIdx.x;
-    if (p >= P) return;
-    double s[D];
+    double prim = 0.0;
+    if (p < P) {
+        double s[D], zs[D], xn[D];
 #pragma unroll
-    for (int l = 0; l < D; l++) s[l] = 0.0;
-    int k0 = incPtr[p], k1 = incPtr[p + 1];
-    for (int k = k0; k < k1; k++) {
-        int slot = __ldg(incIdx + k);
-        size_t e = (size_t)(slot >> 2);
-        int v = slot & 3;
+        for (int l = 0; l < D; l++) { s[l] = 0.0; zs[l] = ZSRC ? zsrc[(size_t)D * p + l] : 0.0; }
+        const int k0 = incPtr[p], k1 = incPtr[p + 1];
+        for (int k = k0; k < k1; k++) {
+            int slot = __ldg(incIdx + k);
+            size_t e = (size_t)(slot >> 2);
+            int v = slot & 3;
+#pragma unroll
+            for (int l = 0; l < D; l++) {
+                size_t idx = (size_t)(D * v + l) * Es + e;
+                double zv = ZSRC ? zs[l] : __ldg(z + idx);
+                double uv = UZERO ? 0.0 : __ldg(u + idx);
+                s[l] += w * (w * (zv - uv));
+            }
+        }
+        double td = tdiag[p];
 #pragma unroll
         for (int l = 0; l < D; l++) {
-            size_t idx = (size_t)(D * v + l) * E + e;
-            s[l] += w * (w * (__ldg(z + idx) - __ldg(u + idx)));
+            xn[l] = ((m * xBar[(size_t)D * p + l]) + dtsq * s[l]) / td;
+            x[(size_t)D * p + l] = xn[l];
+        }
+        if (PRIMAL) {   // second pass over the (L1-resident) slots: differences, not expanded squares
+            for (int k = k0; k < k1; k++) {
+                int slot = __ldg(incIdx + k);
+                size_t e = (size_t)(slot >> 2);
+                int v = slot & 3;
+#pragma unroll
+                for (int l = 0; l < D; l++) {
+                    double zv = ZSRC ? zs[l] : __ldg(z + (size_t)(D * v + l) * Es + e);
+                    double df = xn[l] - zv;
+                    prim += df * df;
+                }
+            }
         }
     }
-    double td = tdiag[p];
-#pragma unroll
-    for (int l = 0; l < D; l++) x[(size_t)D * p + l] = ((m * xBar[(size_t)D * p + l]) + dtsq * s[l]) / td;
+    if (PRIMAL) {
+        double r = block_sum(prim, red);
+        if (threadIdx.x == 0) partPrimal[blockIdx.x] = r;
+    }
 }
 
 // K6b: grad = sum of element gradients (ascending element order, as the reference's serial loop accumulates);
 // xBar = x - (dt/tau)*grad ; xPrev = x     (src/Mesh.cpp:649-674, src/MeshIntegrator.cpp:119)
 template <int D>
-__global__ void __launch_bounds__(TPB_V) k_predict_grad(int P, size_t E, const int *incPtr, const int *incIdx, const double *gs,
+__global__ void __launch_bounds__(TPB_V) k_predict_grad(int P, size_t Es, const int *incPtr, const int *incIdx, const double *gs,
                                                         double dtOverTau, const double *x, double *xBar, double *xPrev) {
     int p = blockIdx.x * TPB_V + threadIdx.x;
     if (p >= P) return;
@@ -565,7 +789,7 @@ __global__ void __launch_bounds__(TPB_V) k_predict_grad(int P, size_t E, const i
         size_t e = (size_t)(slot >> 2);
         int v = slot & 3;
 #pragma unroll
-        for (int l = 0; l < D; l++) s[l] += __ldg(gs + (size_t)(D * v + l) * E + e);
+        for (int l = 0; l < D; l++) s[l] += __ldg(gs + (size_t)(D * v + l) * Es + e);
     }
 #pragma unroll
     for (int l = 0; l < D; l++) {
@@ -640,6 +864,9 @@ __global__ void k_block_grad_dbg(ElemArgs<D> a, int ne, const double *zs, const 
 // =====================================================================================================
 struct mmadmm_ctx {
     int D = 0, n = 0, P = 0, E = 0, device = 0;
+    size_t Es = 0;               // element-plane stride
+    int proxVariant = 0;
+    bool smemAttrSet[8] = {false, false, false, false, false, false, false, false};
     bool compMesh = false, gradUse = false;
     cudaStream_t stream = nullptr;
     int *F[4] = {nullptr, nullptr, nullptr, nullptr};
@@ -654,7 +881,7 @@ struct mmadmm_ctx {
     double Ehat[9] = {0}, dpow = 0;
     bool stepTaken = false, hessComputed = false;
     int stepsTaken = 0;
-    int nblkE = 0;
+    int nblkE = 0, nblkV = 0, nblkProx = 0;
     double *partIh = nullptr, *partDual = nullptr, *partPrimal = nullptr, *scal_d = nullptr, *scal_h = nullptr;
     unsigned *status_d = nullptr, *status_h = nullptr;
     unsigned long long *hist_d = nullptr;
@@ -667,13 +894,20 @@ struct mmadmm_ctx {
     size_t evUsed = 0;
     std::string err;
 
+    double gridO[3] = {0, 0, 0}, gridRh[3] = {0, 0, 0};
+    MonGrid monGrid() const {
+        MonGrid mg;
+        mg.vals = grid; mg.ax = ax; mg.ay = ay; mg.az = az; mg.nx = nx; mg.ny = ny; mg.nz = nz;
+        for (int l = 0; l < 3; l++) { mg.o[l] = gridO[l]; mg.rh[l] = gridRh[l]; }
+        return mg;
+    }
     template <int D_> ElemArgs<D_> elemArgs(double tol) const {
         ElemArgs<D_> a;
-        a.E = E; a.P = P;
+        a.E = E; a.P = P; a.Es = Es; a.zsrc = nullptr; a.uZero = 0;
         for (int v = 0; v < MAXV; v++) a.F[v] = F[v];
         a.fixedBits = fixedBits; a.nonIntBits = nonIntBits;
         a.x = x; a.Vc = Vc; a.z = z; a.u = u; a.B = B;
-        a.mg.vals = grid; a.mg.ax = ax; a.mg.ay = ay; a.mg.az = az; a.mg.nx = nx; a.mg.ny = ny; a.mg.nz = nz;
+        a.mg = monGrid();
         for (int k = 0; k < D_ * D_; k++) a.fc.Ehat[k] = Ehat[k];
         a.fc.dpow = dpow; a.fc.w2 = w * w;
         a.compMesh = compMesh ? 1 : 0;
@@ -682,6 +916,10 @@ struct mmadmm_ctx {
         a.hist = statsOn ? hist_d : nullptr;
         a.status = status_d;
         return a;
+    }
+    int proxTile() const {
+        if (D == 2) return (proxVariant == 2) ? 64 : (proxVariant == 3) ? 256 : 128;
+        return (proxVariant == 1) ? 32 : 64;
     }
     void phaseBegin(int ph) {
         if (!timingOn) return;
@@ -803,8 +1041,10 @@ template <int D> int build_monitor_grid(mmadmm_ctx *ctx, const double *VpHost, c
     k_bin_ids<D><<<cdiv(P, 256), 256, 0, st>>>(P, ctx->x, bg, bin, ids);
     int rc = build_csr(ctx, (size_t)P, (int)nbins, bin, ids, &binStart, &items);
     if (rc) return rc;
-    MonGrid mg;
-    mg.vals = ctx->grid; mg.ax = ctx->ax; mg.ay = ctx->ay; mg.az = ctx->az; mg.nx = ctx->nx; mg.ny = ctx->ny; mg.nz = ctx->nz;
+    ctx->gridO[0] = hx[0]; ctx->gridO[1] = hy[0]; ctx->gridO[2] = hz[0];
+    ctx->gridRh[0] = 1.0 / (hx[1] - hx[0]); ctx->gridRh[1] = 1.0 / (hy[1] - hy[0]);
+    ctx->gridRh[2] = (D == 3) ? 1.0 / (hz[1] - hz[0]) : 0.0;
+    MonGrid mg = ctx->monGrid();
     k_nn_grid<D><<<cdiv(ctx->gridRows, 128), 128, 0, st>>>(mg, ctx->grid, ctx->x, monV, bg, binStart, items);
     int nSmooth = (D == 2) ? 5 : 2;  // src/MeshInterpolator.cpp:246-252
     for (int it = 0; it < nSmooth; it++) {
@@ -823,7 +1063,8 @@ int create_impl(mmadmm_ctx *ctx, const double *Vp, const double *Vc, const int *
     constexpr int n = D * (D + 1);
     const int P = ctx->P, E = ctx->E;
     cudaStream_t st = ctx->stream;
-    const size_t NV = (size_t)P * D, NZ = (size_t)E * n;
+    ctx->Es = ((size_t)E + ES_ALIGN - 1) / ES_ALIGN * ES_ALIGN;
+    const size_t NV = (size_t)P * D, NZ = ctx->Es * n;
     CK(cudaMalloc(&ctx->x, sizeof(double) * NV));
     CK(cudaMalloc(&ctx->xPrev, sizeof(double) * NV));
     CK(cudaMalloc(&ctx->xBar, sizeof(double) * NV));
@@ -892,18 +1133,19 @@ int create_impl(mmadmm_ctx *ctx, const double *Vp, const double *Vc, const int *
     CK(cudaMalloc(&ctx->u, sizeof(double) * NZ));
     CK(cudaMalloc(&ctx->B, sizeof(double) * NZ * n));
     CK(cudaMalloc(&ctx->gs, sizeof(double) * NZ));
+    CK(cudaMemsetAsync(ctx->z, 0, sizeof(double) * NZ, st));
     CK(cudaMemsetAsync(ctx->u, 0, sizeof(double) * NZ, st));
     CK(cudaMemsetAsync(ctx->B, 0, sizeof(double) * NZ * n, st));
-    {
-        std::vector<double> ones((size_t)E, 1.0);
-        for (int k = 0; k < n; k++)
-            CK(cudaMemcpyAsync(ctx->B + (size_t)(k * n + k) * E, ones.data(), sizeof(double) * (size_t)E, cudaMemcpyHostToDevice, st));
-        CK(cudaStreamSynchronize(st));
+    for (int k = 0; k < n; k++) {
+        k_fill<<<cdiv(ctx->Es, 256), 256, 0, st>>>(ctx->Es, ctx->B + (size_t)(k * n + k) * ctx->Es, 1.0);
+        ctx->launches++;
     }
     ctx->nblkE = cdiv(E, TPB);
-    CK(cudaMalloc(&ctx->partIh, sizeof(double) * ctx->nblkE));
-    CK(cudaMalloc(&ctx->partDual, sizeof(double) * ctx->nblkE));
-    CK(cudaMalloc(&ctx->partPrimal, sizeof(double) * ctx->nblkE));
+    ctx->nblkV = cdiv(P, TPB_V);
+    ctx->nblkProx = cdiv(E, 32);   // upper bound over the prox tile sizes
+    CK(cudaMalloc(&ctx->partIh, sizeof(double) * ctx->nblkProx));
+    CK(cudaMalloc(&ctx->partDual, sizeof(double) * ctx->nblkProx));
+    CK(cudaMalloc(&ctx->partPrimal, sizeof(double) * std::max(ctx->nblkE, ctx->nblkV)));
     CK(cudaMalloc(&ctx->scal_d, sizeof(double) * 4));
     CK(cudaMallocHost(&ctx->scal_h, sizeof(double) * 4));
     CK(cudaMalloc(&ctx->status_d, sizeof(unsigned)));
@@ -926,38 +1168,93 @@ int check_status(mmadmm_ctx *ctx) {
     return MMADMM_OK;
 }
 
-template <int D> int step_impl(mmadmm_ctx *ctx, int nIters, double tol, double *IhOut, int *itersOut, double *primalOut, double *dualOut) {
+template <int D, int TPB_> constexpr size_t prox_smem_bytes() {
+    return sizeof(double) * (size_t)(D * (D + 1)) * (D * (D + 1)) * TPB_ + 16 + sizeof(double) * 32 + sizeof(int) * 52;
+}
+
+template <int D, int TPB_, int MINB> int launch_prox_t(mmadmm_ctx *ctx, const ElemArgs<D> &a, int slot) {
+    constexpr size_t smem = prox_smem_bytes<D, TPB_>();
+    auto kern = ctx->compMesh ? k_prox<D, TPB_, MINB, true> : k_prox<D, TPB_, MINB, false>;
+    if (!ctx->smemAttrSet[slot]) {
+        CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        ctx->smemAttrSet[slot] = true;
+    }
+    kern<<<cdiv(ctx->E, TPB_), TPB_, smem, ctx->stream>>>(a);
+    ctx->launches++;
+    return MMADMM_OK;
+}
+
+// Tile shape / occupancy variants of the prox kernel ("prox_variant" option; 0 is the tuned default)
+template <int D> int launch_prox(mmadmm_ctx *ctx, const ElemArgs<D> &a);
+template <int D, int WPB, int MINB> int launch_prox_w(mmadmm_ctx *ctx, const ElemArgs<D> &a, int slot) {
     constexpr int n = D * (D + 1);
+    constexpr size_t smem = sizeof(double) * (size_t)WPB * (n * n + 2 * n) * 32 + 16 * WPB + sizeof(double) * 2 * WPB + sizeof(int) * 56;
+    auto kern = ctx->compMesh ? k_prox_w<D, WPB, MINB, true> : k_prox_w<D, WPB, MINB, false>;
+    if (!ctx->smemAttrSet[slot]) {
+        CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        ctx->smemAttrSet[slot] = true;
+    }
+    kern<<<cdiv(ctx->E, WPB * 32), WPB * 32, smem, ctx->stream>>>(a);
+    ctx->launches++;
+    return MMADMM_OK;
+}
+template <> int launch_prox<2>(mmadmm_ctx *ctx, const ElemArgs<2> &a) {
+    switch (ctx->proxVariant) {
+        case 1: return launch_prox_w<2, 4, 3>(ctx, a, 1);
+        case 2: return launch_prox_w<2, 2, 8>(ctx, a, 2);
+        case 3: return launch_prox_w<2, 8, 2>(ctx, a, 3);
+        case 4: return launch_prox_t<2, 128, 4>(ctx, a, 4);
+        default: return launch_prox_w<2, 4, 4>(ctx, a, 0);
+    }
+}
+template <> int launch_prox<3>(mmadmm_ctx *ctx, const ElemArgs<3> &a) {
+    switch (ctx->proxVariant) {
+        case 1: return launch_prox_t<3, 32, 6>(ctx, a, 1);
+        default: return launch_prox_t<3, 64, 3>(ctx, a, 0);
+    }
+}
+
+template <int D, bool ZSRC, bool UZERO, bool PRIMAL>
+void launch_xupdate_t(mmadmm_ctx *ctx, const double *zsrc) {
+    k_xupdate<D, ZSRC, UZERO, PRIMAL><<<ctx->nblkV, TPB_V, 0, ctx->stream>>>(
+        ctx->P, ctx->Es, ctx->incPtr, ctx->incIdx, ctx->z, ctx->u, zsrc, ctx->xBar, ctx->tdiag, ctx->m, ctx->dt * ctx->dt, ctx->w,
+        ctx->x, ctx->partPrimal);
+    ctx->launches++;
+}
+
+template <int D> int step_impl(mmadmm_ctx *ctx, int nIters, double tol, double *IhOut, int *itersOut, double *primalOut, double *dualOut) {
     cudaStream_t st = ctx->stream;
     const int P = ctx->P;
-    const size_t E = ctx->E, NV = (size_t)P * D, NZ = E * n;
-    const double dtsq = ctx->dt * ctx->dt;
+    const size_t NV = (size_t)P * D;
     ElemArgs<D> a = ctx->elemArgs<D>(tol / 100);   // BFGS tolerance tol/100, 50 iterations (src/Mesh.cpp:968)
-    const int gE = ctx->nblkE, gV = cdiv(P, TPB_V);
+    const int gE = ctx->nblkE, gV = ctx->nblkV;
 
     // predictX (src/Mesh.cpp:649-674) fused with xPrev = x (src/MeshIntegrator.cpp:119)
     ctx->phaseBegin(0);
     if (ctx->gradUse || ctx->stepsTaken <= 2) {
         k_euler_elem<D><<<gE, TPB, 0, st>>>(a, ctx->gs);
-        k_predict_grad<D><<<gV, TPB_V, 0, st>>>(P, E, ctx->incPtr, ctx->incIdx, ctx->gs, ctx->dt / ctx->tau, ctx->x, ctx->xBar, ctx->xPrev);
+        k_predict_grad<D><<<gV, TPB_V, 0, st>>>(P, ctx->Es, ctx->incPtr, ctx->incIdx, ctx->gs, ctx->dt / ctx->tau, ctx->x, ctx->xBar, ctx->xPrev);
         ctx->launches += 2;
     } else {
         k_predict_extrap<<<cdiv(NV, TPB_V), TPB_V, 0, st>>>(NV, ctx->x, ctx->xBar, ctx->xPrev);
         ctx->launches += 1;
     }
-    // x = xBar; z = D x  (z = D xPrev on the very first step); u = 0 until a step has been taken  (:120-127)
-    k_applyD<D><<<gE, TPB, 0, st>>>(a, (ctx->stepsTaken == 0) ? ctx->xPrev : ctx->xBar);
-    if (!ctx->stepTaken) CK(cudaMemsetAsync(ctx->u, 0, sizeof(double) * NZ, st));
     ctx->phaseEnd();
+    // x = xBar; z = D x (z = D xPrev on the very first step); u = 0 until a step has been taken (:120-127).
+    // z is not materialised: the first x-solve and the first prox sweep gather it from the vertex vector `zsrc`.
+    const double *zsrc = (ctx->stepsTaken == 0) ? ctx->xPrev : ctx->xBar;
+    const bool uZero = !ctx->stepTaken;
     // first x-solve (:137-138)
     ctx->phaseBegin(2);
-    k_xupdate<D><<<gV, TPB_V, 0, st>>>(P, E, ctx->incPtr, ctx->incIdx, ctx->z, ctx->u, ctx->xBar, ctx->tdiag, ctx->m, dtsq, ctx->w, ctx->x);
+    if (uZero) launch_xupdate_t<D, true, true, false>(ctx, zsrc);
+    else launch_xupdate_t<D, true, false, false>(ctx, zsrc);
     ctx->phaseEnd();
-    ctx->launches += 2;
 
     double Ihstart = 0, primal = 0, dual = 0;
     int i;
     for (i = 0; i < nIters; i++) {
+        a.zsrc = (i == 0) ? zsrc : nullptr;
+        a.uZero = (i == 0 && uZero) ? 1 : 0;
         if (!ctx->hessComputed) {
             ctx->phaseBegin(4);
             k_hess_init<D><<<gE, TPB, 0, st>>>(a);
@@ -965,23 +1262,24 @@ template <int D> int step_impl(mmadmm_ctx *ctx, int nIters, double tol, double *
             ctx->launches++;
         }
         ctx->phaseBegin(1);
-        k_prox<D><<<gE, TPB, 0, st>>>(a);
+        int rcl = launch_prox<D>(ctx, a);
+        if (rcl) return rcl;
         ctx->phaseEnd();
         ctx->hessComputed = true;
         ctx->stepTaken = true;
         ctx->phaseBegin(2);
-        k_xupdate<D><<<gV, TPB_V, 0, st>>>(P, E, ctx->incPtr, ctx->incIdx, ctx->z, ctx->u, ctx->xBar, ctx->tdiag, ctx->m, dtsq, ctx->w, ctx->x);
+        launch_xupdate_t<D, false, false, true>(ctx, nullptr);
         ctx->phaseEnd();
         ctx->phaseBegin(3);
-        k_residual<D><<<gE, TPB, 0, st>>>(a, ctx->partPrimal);
-        k_finalize<<<1, 1024, 0, st>>>(gE, ctx->partIh, ctx->partPrimal, ctx->partDual, ctx->scal_d);
+        const int nbp = cdiv(ctx->E, ctx->proxTile());
+        k_finalize<<<1, 1024, 0, st>>>(nbp, ctx->partIh, gV, ctx->partPrimal, nbp, ctx->partDual, ctx->scal_d);
         CK(cudaMemcpyAsync(ctx->scal_h, ctx->scal_d, sizeof(double) * 3, cudaMemcpyDeviceToHost, st));
         CK(cudaMemcpyAsync(ctx->status_h, ctx->status_d, sizeof(unsigned), cudaMemcpyDeviceToHost, st));
         ctx->phaseEnd();
-        ctx->launches += 4;
+        ctx->launches += 1;
         CK(cudaStreamSynchronize(st));
         ctx->admmIters++;
-        ctx->proxCalls += (long long)E;
+        ctx->proxCalls += (long long)ctx->E;
         int rc = check_status(ctx);
         if (rc) return rc;
         if (i == 0) Ihstart = ctx->scal_h[0];
@@ -1003,7 +1301,7 @@ template <int D> int energy_impl(mmadmm_ctx *ctx, double *I) {
     cudaStream_t st = ctx->stream;
     ElemArgs<D> a = ctx->elemArgs<D>(0.0);
     k_energy<D><<<ctx->nblkE, TPB, 0, st>>>(a, ctx->partPrimal);
-    k_finalize<<<1, 1024, 0, st>>>(ctx->nblkE, ctx->partPrimal, nullptr, nullptr, ctx->scal_d + 3);
+    k_finalize<<<1, 1024, 0, st>>>(ctx->nblkE, ctx->partPrimal, 0, nullptr, 0, nullptr, ctx->scal_d + 3);
     ctx->launches += 2;
     // k_finalize writes out[0] of its `out` argument => scal_d[3]
     CK(cudaMemcpyAsync(ctx->scal_h + 3, ctx->scal_d + 3, sizeof(double), cudaMemcpyDeviceToHost, st));
@@ -1096,7 +1394,7 @@ int mmadmm_get_state(mmadmm_ctx *ctx, int which, double *out) {
         const double *src = (which == MMADMM_STATE_Z) ? ctx->z : (which == MMADMM_STATE_U) ? ctx->u : ctx->B;
         std::vector<double> plane(E);
         for (int k = 0; k < planes; k++) {
-            CK(cudaMemcpy(plane.data(), src + (size_t)k * E, sizeof(double) * E, cudaMemcpyDeviceToHost));
+            CK(cudaMemcpy(plane.data(), src + (size_t)k * ctx->Es, sizeof(double) * E, cudaMemcpyDeviceToHost));
             for (size_t e = 0; e < E; e++) out[e * planes + k] = plane[e];
         }
         return MMADMM_OK;
@@ -1119,8 +1417,7 @@ int mmadmm_eval_monitor(mmadmm_ctx *ctx, const double *pts, int npts, double *ou
     CK(cudaMalloc(&dp, sizeof(double) * (size_t)npts * D));
     CK(cudaMalloc(&dout, sizeof(double) * (size_t)npts * D * D));
     CK(cudaMemcpy(dp, pts, sizeof(double) * (size_t)npts * D, cudaMemcpyHostToDevice));
-    MonGrid mg;
-    mg.vals = ctx->grid; mg.ax = ctx->ax; mg.ay = ctx->ay; mg.az = ctx->az; mg.nx = ctx->nx; mg.ny = ctx->ny; mg.nz = ctx->nz;
+    MonGrid mg = ctx->monGrid();
     if (D == 2) k_eval_monitor<2><<<cdiv(npts, 128), 128, 0, ctx->stream>>>(mg, npts, dp, dout);
     else k_eval_monitor<3><<<cdiv(npts, 128), 128, 0, ctx->stream>>>(mg, npts, dp, dout);
     ctx->launches++;
@@ -1190,6 +1487,7 @@ int mmadmm_set_option(mmadmm_ctx *ctx, const char *name, int value) {
     if (!ctx || !name) return MMADMM_EINVAL;
     if (!strcmp(name, "timing")) { ctx->timingOn = value != 0; return MMADMM_OK; }
     if (!strcmp(name, "stats")) { ctx->statsOn = value != 0; return MMADMM_OK; }
+    if (!strcmp(name, "prox_variant")) { ctx->proxVariant = value; return MMADMM_OK; }
     return MMADMM_EINVAL;
 }
 

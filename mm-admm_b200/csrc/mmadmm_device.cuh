@@ -22,6 +22,10 @@ struct MonGrid {
     const double *vals;
     const double *ax, *ay, *az;  // axis coordinates, nx+1 / ny+1 / nz+1 entries (utils::linspace values)
     int nx, ny, nz;
+    double o[3];                 // axis origin a[0]
+    double rh[3];                // 1 / (a[1] - a[0]): the cell guess multiplies instead of dividing (the bilinear
+                                 // interpolant is continuous across cells, so a one-ulp different guess on a grid line
+                                 // changes the result at rounding level only)
 };
 
 template <int D> struct SMat {
@@ -53,6 +57,32 @@ template <> __device__ __forceinline__ SMat<3> sinv<3>(const SMat<3> &m) {
     double c10 = m(2, 1) * m(0, 2) - m(2, 2) * m(0, 1);
     double c20 = m(0, 1) * m(1, 2) - m(0, 2) * m(1, 1);
     double invdet = 1.0 / (c00 * m(0, 0) + c10 * m(1, 0) + c20 * m(2, 0));
+    r(0, 0) = c00 * invdet; r(0, 1) = c10 * invdet; r(0, 2) = c20 * invdet;
+    r(1, 0) = (m(1, 2) * m(2, 0) - m(1, 0) * m(2, 2)) * invdet;
+    r(1, 1) = (m(2, 2) * m(0, 0) - m(2, 0) * m(0, 2)) * invdet;
+    r(1, 2) = (m(0, 2) * m(1, 0) - m(0, 0) * m(1, 2)) * invdet;
+    r(2, 0) = (m(1, 0) * m(2, 1) - m(1, 1) * m(2, 0)) * invdet;
+    r(2, 1) = (m(2, 0) * m(0, 1) - m(2, 1) * m(0, 0)) * invdet;
+    r(2, 2) = (m(0, 0) * m(1, 1) - m(0, 1) * m(1, 0)) * invdet;
+    return r;
+}
+// m^{-1} / s with a single division (adjugate times 1/(det*s))
+template <int D> __device__ __forceinline__ SMat<D> sinv_scaled(const SMat<D> &m, double s);
+template <> __device__ __forceinline__ SMat<2> sinv_scaled<2>(const SMat<2> &m, double s) {
+    SMat<2> r;
+    double invdet = 1.0 / (sdet<2>(m) * s);
+    r(0, 0) = m(1, 1) * invdet;
+    r(1, 0) = -m(1, 0) * invdet;
+    r(0, 1) = -m(0, 1) * invdet;
+    r(1, 1) = m(0, 0) * invdet;
+    return r;
+}
+template <> __device__ __forceinline__ SMat<3> sinv_scaled<3>(const SMat<3> &m, double s) {
+    SMat<3> r;
+    double c00 = m(1, 1) * m(2, 2) - m(1, 2) * m(2, 1);
+    double c10 = m(2, 1) * m(0, 2) - m(2, 2) * m(0, 1);
+    double c20 = m(0, 1) * m(1, 2) - m(0, 2) * m(1, 1);
+    double invdet = 1.0 / ((c00 * m(0, 0) + c10 * m(1, 0) + c20 * m(2, 0)) * s);
     r(0, 0) = c00 * invdet; r(0, 1) = c10 * invdet; r(0, 2) = c20 * invdet;
     r(1, 0) = (m(1, 2) * m(2, 0) - m(1, 0) * m(2, 2)) * invdet;
     r(1, 1) = (m(2, 2) * m(0, 0) - m(2, 0) * m(0, 2)) * invdet;
@@ -118,8 +148,8 @@ template <int D> __device__ __forceinline__ void pow_pair(double t, double &p_fu
 }
 
 // utils::findLimInfMeshPoint: uint32 wrap for negatives => clamp to the last cell (size-2 = nIntervals-1)
-__device__ __forceinline__ int find_cell(double w, double a0, double a1, int nIntervals) {
-    uint32_t guess = (uint32_t)(int)((w - a0) / (a1 - a0));
+__device__ __forceinline__ int find_cell(double w, double a0, double rh, int nIntervals) {
+    uint32_t guess = (uint32_t)(int)((w - a0) * rh);
     if (guess > (uint32_t)(nIntervals - 1)) guess = (uint32_t)(nIntervals - 1);
     return (int)guess;
 }
@@ -127,9 +157,8 @@ __device__ __forceinline__ int find_cell(double w, double a0, double a1, int nIn
 template <int D> __device__ __forceinline__ void eval_monitor(const MonGrid &g, const double *pnt, SMat<D> &mVal);
 
 template <> __device__ __forceinline__ void eval_monitor<2>(const MonGrid &g, const double *pnt, SMat<2> &mVal) {
-    const double ax0 = __ldg(g.ax), ax1 = __ldg(g.ax + 1), ay0 = __ldg(g.ay), ay1 = __ldg(g.ay + 1);
-    int xInd = find_cell(pnt[0], ax0, ax1, g.nx);
-    int yInd = find_cell(pnt[1], ay0, ay1, g.ny);
+    int xInd = find_cell(pnt[0], g.o[0], g.rh[0], g.nx);
+    int yInd = find_cell(pnt[1], g.o[1], g.rh[1], g.ny);
     double x0 = __ldg(g.ax + xInd), x1 = __ldg(g.ax + xInd + 1);
     double y0 = __ldg(g.ay + yInd), y1 = __ldg(g.ay + yInd + 1);
     double x = pnt[0], y = pnt[1];
@@ -150,11 +179,9 @@ template <> __device__ __forceinline__ void eval_monitor<2>(const MonGrid &g, co
 }
 
 template <> __device__ __forceinline__ void eval_monitor<3>(const MonGrid &g, const double *pnt, SMat<3> &mVal) {
-    const double ax0 = __ldg(g.ax), ax1 = __ldg(g.ax + 1), ay0 = __ldg(g.ay), ay1 = __ldg(g.ay + 1);
-    const double az0 = __ldg(g.az), az1 = __ldg(g.az + 1);
-    int xInd = find_cell(pnt[0], ax0, ax1, g.nx);
-    int yInd = find_cell(pnt[1], ay0, ay1, g.ny);
-    int zInd = find_cell(pnt[2], az0, az1, g.nz);
+    int xInd = find_cell(pnt[0], g.o[0], g.rh[0], g.nx);
+    int yInd = find_cell(pnt[1], g.o[1], g.rh[1], g.ny);
+    int zInd = find_cell(pnt[2], g.o[2], g.rh[2], g.nz);
     double x0 = __ldg(g.ax + xInd), x1 = __ldg(g.ax + xInd + 1);
     double y0 = __ldg(g.ay + yInd), y1 = __ldg(g.ay + yInd + 1);
     double z0 = __ldg(g.az + zInd), z1 = __ldg(g.az + zInd + 1);
@@ -213,9 +240,7 @@ __device__ __forceinline__ double block_grad(const double *z, const double *xi, 
 #pragma unroll
         for (int k = 0; k < D * D; k++) M.a[k] += mPre[i].a[k];
     }
-    SMat<D> Minv = sinv<D>(M);
-#pragma unroll
-    for (int k = 0; k < D * D; k++) Minv.a[k] /= ((double)D + 1);  // sic: M^{-1}/(D+1), :157
+    SMat<D> Minv = sinv_scaled<D>(M, (double)D + 1);  // sic: M^{-1}/(D+1), :157
 
     SMat<D> E, Ehat;
 #pragma unroll
@@ -237,7 +262,7 @@ __device__ __forceinline__ double block_grad(const double *z, const double *xi, 
     double trJMJt = JMJt(0, 0);
 #pragma unroll
     for (int i = 1; i < D; i++) trJMJt += JMJt(i, i);
-    double detM = sqrt(1.0 / sdet<D>(Minv));
+    double detM = rsqrt(sdet<D>(Minv));   // sqrt(1/det(Minv))
 
     double trp, trpm1;
     pow_pair<D>(trJMJt, trp, trpm1);
@@ -250,7 +275,7 @@ __device__ __forceinline__ double block_grad(const double *z, const double *xi, 
     SMat<D> dGdJ;
 #pragma unroll
     for (int k = 0; k < D * D; k++) dGdJ.a[k] = sJ * MinvJt.a[k];
-    double rsDetM = 1.0 / sqrt(detM);   // detM^(1-p)
+    double rsDetM = rsqrt(detM);        // detM^(1-p)
     double sDetFJ = sqrt(detFJ);        // detFJ^(p-1)
     double dGddet = p * (1.0 - 2.0 * theta) * fc.dpow * rsDetM * sDetFJ;
     SMat<D> dGdM;
@@ -283,7 +308,7 @@ __device__ __forceinline__ double block_grad(const double *z, const double *xi, 
 #pragma unroll
     for (int r = 0; r < D; r++)
 #pragma unroll
-        for (int l = 0; l < D; l++) vLoc(r, l) = (c1 * Einv(r, l) + T(r, l)) - basisComb[l] / ((double)D + 1.0);
+        for (int l = 0; l < D; l++) vLoc(r, l) = (c1 * Einv(r, l) + T(r, l)) - basisComb[l] * (1.0 / ((double)D + 1.0));
     double g0[D];
 #pragma unroll
     for (int l = 0; l < D; l++) {
@@ -320,6 +345,66 @@ __device__ __forceinline__ double prox_grad(const double *z, const double *dxpu,
         }
     return Igt;
 }
+
+// Same as prox_grad, with DXpU read from shared memory (dxs[k*32], one column per lane) after the gradient is formed,
+// so that it is not live in registers across block_grad.
+template <int D>
+__device__ __forceinline__ double prox_grad_s(const double *z, const double *dxs, const double *xi, bool compMesh,
+                                              const MonGrid &mg, const FuncConsts<D> &fc, unsigned fixedBits, double *grad,
+                                              bool &inverted) {
+    constexpr int n = D * (D + 1);
+    double Igt = block_grad<D, true>(z, xi, compMesh, mg, fc, grad, inverted);
+#pragma unroll
+    for (int k = 0; k < n; k++) grad[k] += fc.w2 * (-dxs[k * 32] + z[k]);
+#pragma unroll
+    for (int v = 0; v < D + 1; v++)
+        if (fixedBits & (1u << v)) {
+#pragma unroll
+            for (int l = 0; l < D; l++) grad[D * v + l] = 0.0;
+        }
+    return Igt;
+}
+
+// ------------------------------------------------------------------------------------------------
+// TMA (bulk async copy) + mbarrier helpers: the inverse-Hessian tile of a CTA is staged through shared memory
+// with cp.async.bulk (SASS UBLKCP) so that 79 % (2D) / 88 % (3D) of the bytes of the prox kernel never pass
+// through the register file or the LSU, and the load overlaps the first gradient evaluation.
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t *bar, unsigned count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, unsigned bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t *bar, unsigned parity) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "WAIT_%=:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra DONE_%=;\n"
+        "bra WAIT_%=;\n"
+        "DONE_%=:\n"
+        "}\n" ::"r"(smem_u32(bar)), "r"(parity)
+        : "memory");
+}
+// global -> shared, completion counted in bytes on `bar`; bytes % 16 == 0, both addresses 16-byte aligned
+__device__ __forceinline__ void bulk_g2s(void *dst_smem, const void *src_gmem, unsigned bytes, uint64_t *bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(dst_smem)),
+                 "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
+// shared -> global (bulk async group)
+__device__ __forceinline__ void bulk_s2g(void *dst_gmem, const void *src_smem, unsigned bytes) {
+    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst_gmem), "r"(smem_u32(src_smem)), "r"(bytes)
+                 : "memory");
+}
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait_read0() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+// make generic-proxy shared-memory writes visible to the async proxy (before a bulk store reads them)
+__device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 
 // ------------------------------------------------------------------------------------------------
 // reductions
