@@ -9,6 +9,7 @@
 //               K5         ||D x - z||^2 partials in the same pass;  k_finalize reduces the three scalars in a fixed order
 // Element state is SoA over elements (component-major planes of length E) so every warp access is
 // one contiguous 256-byte line.
+#include <cuda.h>
 #include <cuda_runtime.h>
 #include <cub/cub.cuh>
 
@@ -683,6 +684,212 @@ __global__ void __launch_bounds__(WPB * 32, MINB) k_prox_w(ElemArgs<D> a) {
     if (tileLive) bulk_wait_read0();   // shared memory must stay allocated until the bulk stores have read it
 }
 
+// Persistent, software-pipelined form of the warp-tile prox kernel (the default for D = 2).  One warp walks tiles
+// t = gw, gw + GW, ... of 32 elements.  While tile t is being solved, everything tile t+1 needs except its inverse
+// Hessians is already on its way into the other half of a double buffer: vertex gathers (x, zsrc, Vc) by per-thread
+// cp.async (LDGSTS, no registers held), the u / z planes by one tensor-map TMA each; the connectivity of tile t+2 is
+// loaded into three registers.  The inverse-Hessian tile itself is single-buffered: its TMA load is issued as soon as
+// the previous tile's TMA store has drained and is covered by the entry-gradient evaluation.
+struct ProxMaps { CUtensorMap B, u, z; };
+
+template <int D> __device__ __forceinline__ void gather_async(double *dst /* [D+1][32][D] */, const double *src, const int *vid, int lane) {
+#pragma unroll
+    for (int v = 0; v < D + 1; v++) {
+        double *d = dst + ((size_t)v * 32 + lane) * D;
+        const double *s = src + (size_t)D * vid[v];
+        if (D == 2) cp_async16(d, s);
+        else { cp_async8(d, s); cp_async8(d + 1, s + 1); cp_async8(d + 2, s + 2); }
+    }
+}
+
+template <int D, int WPB, int MINB, bool COMP>
+__global__ void __launch_bounds__(WPB * 32, MINB) k_prox_p(const __grid_constant__ ElemArgs<D> a, const __grid_constant__ ProxMaps maps) {
+    constexpr int n = D * (D + 1);
+    constexpr int NN = n * n;
+    constexpr int SLOTS = COMP ? 4 : 3;                 // per buffer: xg | u->DXpU | z (planes or gathered) | xi
+    constexpr int BUF_DOUBLES = SLOTS * n * 32;
+    constexpr int WARP_DOUBLES = NN * 32 + 2 * BUF_DOUBLES;
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    double *Bs = reinterpret_cast<double *>(smem_raw) + (size_t)warp * WARP_DOUBLES;   // [NN][32]
+    double *bufs = Bs + NN * 32;
+    uint64_t *bars = reinterpret_cast<uint64_t *>(reinterpret_cast<double *>(smem_raw) + (size_t)WPB * WARP_DOUBLES) + 4 * warp;
+    uint64_t *barB = &bars[2];
+    const int gw = blockIdx.x * WPB + warp, GW = gridDim.x * WPB;
+    const int nTiles = (a.E + 31) >> 5;
+    const bool haveU = !a.uZero, haveZ = (a.zsrc == nullptr);
+    const unsigned smallBytes = (unsigned)(((haveU ? n : 0) + (haveZ ? n : 0)) * 32 * sizeof(double));
+    if (lane == 0) { mbar_init(&bars[0], 1); mbar_init(&bars[1], 1); mbar_init(barB, 1); }
+    __syncwarp();
+
+    auto load_ids = [&](int tile, int *vid, unsigned &fb) {
+        const int e = tile * 32 + lane;
+        if (e < a.E) {
+            load_elem_ids<D>(a, e, vid);
+            fb = a.fixedBits[e];
+        } else {
+#pragma unroll
+            for (int v = 0; v < D + 1; v++) vid[v] = 0;
+            fb = 0;
+        }
+    };
+    auto issue_small = [&](int tile, int buf, const int *vid) {
+        double *b = bufs + (size_t)buf * BUF_DOUBLES;
+        gather_async<D>(b, a.x, vid, lane);
+        if (!haveZ) gather_async<D>(b + 2 * n * 32, a.zsrc, vid, lane);
+        if (COMP) gather_async<D>(b + 3 * n * 32, a.Vc, vid, lane);
+        cp_async_commit();
+        if (lane == 0 && smallBytes) {
+            mbar_expect_tx(&bars[buf], smallBytes);
+            if (haveU) tma_load_2d(b + n * 32, &maps.u, tile * 32, 0, &bars[buf]);
+            if (haveZ) tma_load_2d(b + 2 * n * 32, &maps.z, tile * 32, 0, &bars[buf]);
+        }
+    };
+
+    double ihAcc = 0.0, dualAcc = 0.0;
+    int t = gw, tn = gw + GW;
+    int nvid[D + 1];
+    unsigned fb = 0, nfb = 0, nfb2 = 0;
+    if (t < nTiles) {
+        load_ids(t, nvid, fb);
+        issue_small(t, 0, nvid);
+        if (tn < nTiles) load_ids(tn, nvid, nfb);
+    }
+    for (int it = 0; t < nTiles; t = tn, tn += GW, it++, fb = nfb, nfb = nfb2) {
+        const int buf = it & 1;
+        double *b = bufs + (size_t)buf * BUF_DOUBLES;
+        const int e = t * 32 + lane;
+        const bool active = e < a.E;
+        // inverse Hessians of this tile (the previous tile's store has drained: see the end of the loop body)
+        if (lane == 0) {
+            mbar_expect_tx(barB, (unsigned)(NN * 32 * sizeof(double)));
+            tma_load_2d(Bs, &maps.B, t * 32, 0, barB);
+        }
+        // everything but B for the next tile, connectivity for the one after
+        if (tn < nTiles) {
+            issue_small(tn, buf ^ 1, nvid);
+            if (tn + GW < nTiles) load_ids(tn + GW, nvid, nfb2);
+        } else {
+            cp_async_commit();   // keeps the group count uniform: exactly one younger group than this tile's
+        }
+        asm volatile("cp.async.wait_group 1;" ::: "memory");   // this tile's gathers have landed
+        if (smallBytes) mbar_wait(&bars[buf], (unsigned)((it >> 1) & 1));
+        double *xg = b + lane * D, *dxs = b + n * 32 + lane, *zs = b + 2 * n * 32, *xis = b + 3 * n * 32 + lane * D;
+        double z[n], xi[COMP ? n : 1], Gk[n];
+        bool inv = false;
+        double ih = 0.0;
+        // DXpU = D x + u  -> dxs[k*32];  z at entry -> z[] and (plane layout) zs[k*32 + lane]
+#pragma unroll
+        for (int v = 0; v < D + 1; v++)
+#pragma unroll
+            for (int l = 0; l < D; l++) {
+                const int k = D * v + l;
+                const double xv = xg[(size_t)v * 32 * D + l];
+                dxs[k * 32] = haveU ? xv + dxs[k * 32] : xv;
+            }
+        if (haveZ) {
+#pragma unroll
+            for (int k = 0; k < n; k++) z[k] = zs[k * 32 + lane];
+        } else {
+#pragma unroll
+            for (int v = 0; v < D + 1; v++)
+#pragma unroll
+                for (int l = 0; l < D; l++) z[D * v + l] = zs[((size_t)v * 32 + lane) * D + l];
+            __syncwarp();   // gathered layout is read by every lane before it is overwritten in plane layout
+#pragma unroll
+            for (int k = 0; k < n; k++) zs[k * 32 + lane] = z[k];
+        }
+        if (COMP) {
+#pragma unroll
+            for (int v = 0; v < D + 1; v++)
+#pragma unroll
+                for (int l = 0; l < D; l++) xi[D * v + l] = xis[(size_t)v * 32 * D + l];
+        }
+        if (active) ih = prox_grad_s<D>(z, dxs, xi, COMP, a.mg, a.fc, fb, Gk, inv);   // Ihsave: energy at entry
+        mbar_wait(barB, (unsigned)(it & 1));
+        int bin = -1;
+        if (active) {
+            double *Bt = Bs + lane;
+#define BS(k) Bt[(k) * 32]
+            int iter;
+            for (iter = 0; iter < 50; iter++) {
+                double pk[n], G1[n];
+#pragma unroll
+                for (int r = 0; r < n; r++) {
+                    double s = BS(r * n) * Gk[0];
+#pragma unroll
+                    for (int c = 1; c < n; c++) s += BS(r * n + c) * Gk[c];
+                    pk[r] = -s;
+                    z[r] += pk[r];
+                }
+                prox_grad_s<D>(z, dxs, xi, COMP, a.mg, a.fc, fb, G1, inv);
+                double Ix = 0.0, yk[n];
+#pragma unroll
+                for (int k = 0; k < n; k++) { Ix += fabs(G1[k]); yk[k] = G1[k] - Gk[k]; Gk[k] = G1[k]; }
+                double c2 = pk[0] * yk[0];
+#pragma unroll
+                for (int k = 1; k < n; k++) c2 += pk[k] * yk[k];
+                double By[n], yB[n];
+#pragma unroll
+                for (int r = 0; r < n; r++) {
+                    double s = 0.0;
+#pragma unroll
+                    for (int c = 0; c < n; c++) {
+                        const double bb = BS(r * n + c);
+                        s = (c == 0) ? bb * yk[0] : s + bb * yk[c];
+                        yB[c] = (r == 0) ? yk[0] * bb : yB[c] + yk[r] * bb;
+                    }
+                    By[r] = s;
+                }
+                double yBy = yk[0] * By[0];
+#pragma unroll
+                for (int k = 1; k < n; k++) yBy += yk[k] * By[k];
+                const double ic2 = 1.0 / c2;
+                const double c1 = (c2 + yBy) * (ic2 * ic2);
+#pragma unroll
+                for (int r = 0; r < n; r++) {
+                    const double a1 = c1 * pk[r], a3 = pk[r] * ic2, a2 = By[r] * ic2;
+#pragma unroll
+                    for (int c = 0; c < n; c++) BS(r * n + c) += (a1 * pk[c] - a2 * pk[c]) - a3 * yB[c];
+                }
+                if (Ix < a.tol) break;
+            }
+#undef BS
+            if (inv) atomicOr(a.status, ST_INVERTED);
+            if (iter == 50) atomicOr(a.status, ST_BFGS_MAX);
+            bin = (iter == 50) ? 51 : iter + 1;
+            double dual2 = 0.0;
+#pragma unroll
+            for (int k = 0; k < n; k++) {
+                a.z[k * a.Es + e] = z[k];
+                a.u[k * a.Es + e] = dxs[k * 32] - z[k];    // u = DXpU - z
+                const double d = z[k] - zs[k * 32 + lane];
+                dual2 += d * d;
+            }
+            ihAcc += ih;
+            dualAcc += dual2;
+        }
+        if (a.hist) {   // one atomic per distinct iteration count in the warp
+            const unsigned peers = __match_any_sync(0xffffffffu, bin);
+            if (bin >= 0 && lane == __ffs(peers) - 1) atomicAdd(&a.hist[bin], (unsigned long long)__popc(peers));
+        }
+        // updated tile back to HBM: generic-proxy writes -> async proxy, then one tensor-map store; the shared-memory
+        // tile may be overwritten (next tile's load) once the store has read it
+        fence_async_smem();
+        __syncwarp();
+        if (lane == 0) {
+            tma_store_2d(&maps.B, t * 32, 0, Bs);
+            bulk_commit();
+            bulk_wait_read0();
+        }
+        __syncwarp();
+    }
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+    ihAcc = warp_sum(ihAcc);
+    dualAcc = warp_sum(dualAcc);
+    if (lane == 0) { a.partIh[gw] = ihAcc; a.partDual[gw] = dualAcc; }
+}
+
 // z = D * src (gather), src is a P x D vertex vector
 template <int D> __global__ void __launch_bounds__(TPB) k_applyD(ElemArgs<D> a, const double *src) {
     int e = blockIdx.x * TPB + threadIdx.x;
@@ -866,6 +1073,10 @@ struct mmadmm_ctx {
     int D = 0, n = 0, P = 0, E = 0, device = 0;
     size_t Es = 0;               // element-plane stride
     int proxVariant = 0;
+    int nProxPart = 0;           // number of per-block (or per-warp) partial sums the last prox launch wrote
+    int numSMs = 148;
+    ProxMaps maps;
+    bool haveMaps = false;
     bool smemAttrSet[8] = {false, false, false, false, false, false, false, false};
     bool compMesh = false, gradUse = false;
     cudaStream_t stream = nullptr;
@@ -917,10 +1128,6 @@ struct mmadmm_ctx {
         a.status = status_d;
         return a;
     }
-    int proxTile() const {
-        if (D == 2) return (proxVariant == 2) ? 64 : (proxVariant == 3) ? 256 : 128;
-        return (proxVariant == 1) ? 32 : 64;
-    }
     void phaseBegin(int ph) {
         if (!timingOn) return;
         if (evUsed + 2 > evPool.size()) {
@@ -950,6 +1157,27 @@ struct mmadmm_ctx {
 namespace {
 
 inline int cdiv(size_t a, size_t b) { return (int)((a + b - 1) / b); }
+
+// Tensor map over `planes` planes of `Es` doubles (plane stride Es): box = [planes][boxElems] (whole tile in one TMA op).
+// cuTensorMapEncodeTiled is fetched through the runtime so that libcuda is not a link-time dependency.
+bool encode_plane_map(CUtensorMap *map, double *base, size_t Es, int planes, int boxElems) {
+    typedef CUresult (*EncodeFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *, const cuuint64_t *,
+                                 const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                 CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+    static EncodeFn fn = nullptr;
+    if (!fn) {
+        void *p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess || !p) return false;
+        fn = (EncodeFn)p;
+    }
+    cuuint64_t dims[2] = {(cuuint64_t)Es, (cuuint64_t)planes};
+    cuuint64_t strides[1] = {(cuuint64_t)Es * sizeof(double)};
+    cuuint32_t box[2] = {(cuuint32_t)boxElems, (cuuint32_t)planes};
+    cuuint32_t estr[2] = {1, 1};
+    return fn(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 2, base, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+              CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
 
 // CSR by key: sorted vals (stable => ascending input order inside a key) and ptr[nkeys+1]
 int build_csr(mmadmm_ctx *ctx, size_t nItems, int nKeys, int *keys, int *vals, int **ptrOut, int **valsOut) {
@@ -1140,9 +1368,13 @@ int create_impl(mmadmm_ctx *ctx, const double *Vp, const double *Vc, const int *
         k_fill<<<cdiv(ctx->Es, 256), 256, 0, st>>>(ctx->Es, ctx->B + (size_t)(k * n + k) * ctx->Es, 1.0);
         ctx->launches++;
     }
+    CK(cudaDeviceGetAttribute(&ctx->numSMs, cudaDevAttrMultiProcessorCount, ctx->device));
+    ctx->haveMaps = encode_plane_map(&ctx->maps.B, ctx->B, ctx->Es, n * n, 32) &&
+                    encode_plane_map(&ctx->maps.u, ctx->u, ctx->Es, n, 32) &&
+                    encode_plane_map(&ctx->maps.z, ctx->z, ctx->Es, n, 32);
     ctx->nblkE = cdiv(E, TPB);
     ctx->nblkV = cdiv(P, TPB_V);
-    ctx->nblkProx = cdiv(E, 32);   // upper bound over the prox tile sizes
+    ctx->nblkProx = std::max(cdiv(E, 32), 148 * 64);   // upper bound over the prox tile sizes / persistent warps
     CK(cudaMalloc(&ctx->partIh, sizeof(double) * ctx->nblkProx));
     CK(cudaMalloc(&ctx->partDual, sizeof(double) * ctx->nblkProx));
     CK(cudaMalloc(&ctx->partPrimal, sizeof(double) * std::max(ctx->nblkE, ctx->nblkV)));
@@ -1180,6 +1412,7 @@ template <int D, int TPB_, int MINB> int launch_prox_t(mmadmm_ctx *ctx, const El
         ctx->smemAttrSet[slot] = true;
     }
     kern<<<cdiv(ctx->E, TPB_), TPB_, smem, ctx->stream>>>(a);
+    ctx->nProxPart = cdiv(ctx->E, TPB_);
     ctx->launches++;
     return MMADMM_OK;
 }
@@ -1195,16 +1428,34 @@ template <int D, int WPB, int MINB> int launch_prox_w(mmadmm_ctx *ctx, const Ele
         ctx->smemAttrSet[slot] = true;
     }
     kern<<<cdiv(ctx->E, WPB * 32), WPB * 32, smem, ctx->stream>>>(a);
+    ctx->nProxPart = cdiv(ctx->E, WPB * 32);
+    ctx->launches++;
+    return MMADMM_OK;
+}
+template <int D, int WPB, int MINB> int launch_prox_p(mmadmm_ctx *ctx, const ElemArgs<D> &a, int slot) {
+    constexpr int n = D * (D + 1);
+    if (!ctx->haveMaps) { ctx->err = "tensor maps unavailable (cuTensorMapEncodeTiled)"; return MMADMM_ECUDA; }
+    const size_t slots = ctx->compMesh ? 4 : 3;
+    const size_t smem = sizeof(double) * (size_t)WPB * (n * n * 32 + 2 * slots * n * 32) + 32 * WPB;
+    auto kern = ctx->compMesh ? k_prox_p<D, WPB, MINB, true> : k_prox_p<D, WPB, MINB, false>;
+    if (!ctx->smemAttrSet[slot]) {
+        CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        ctx->smemAttrSet[slot] = true;
+    }
+    const int grid = std::min(ctx->numSMs * MINB, cdiv(ctx->E, WPB * 32));
+    kern<<<grid, WPB * 32, smem, ctx->stream>>>(a, ctx->maps);
+    ctx->nProxPart = grid * WPB;
     ctx->launches++;
     return MMADMM_OK;
 }
 template <> int launch_prox<2>(mmadmm_ctx *ctx, const ElemArgs<2> &a) {
     switch (ctx->proxVariant) {
-        case 1: return launch_prox_w<2, 4, 3>(ctx, a, 1);
-        case 2: return launch_prox_w<2, 2, 8>(ctx, a, 2);
+        case 1: return launch_prox_p<2, 6, 2>(ctx, a, 1);
+        case 2: return launch_prox_p<2, 2, 6>(ctx, a, 2);
         case 3: return launch_prox_w<2, 8, 2>(ctx, a, 3);
         case 4: return launch_prox_t<2, 128, 4>(ctx, a, 4);
-        default: return launch_prox_w<2, 4, 4>(ctx, a, 0);
+        case 5: return launch_prox_w<2, 4, 4>(ctx, a, 5);
+        default: return launch_prox_p<2, 4, 3>(ctx, a, 0);
     }
 }
 template <> int launch_prox<3>(mmadmm_ctx *ctx, const ElemArgs<3> &a) {
@@ -1271,7 +1522,7 @@ template <int D> int step_impl(mmadmm_ctx *ctx, int nIters, double tol, double *
         launch_xupdate_t<D, false, false, true>(ctx, nullptr);
         ctx->phaseEnd();
         ctx->phaseBegin(3);
-        const int nbp = cdiv(ctx->E, ctx->proxTile());
+        const int nbp = ctx->nProxPart;
         k_finalize<<<1, 1024, 0, st>>>(nbp, ctx->partIh, gV, ctx->partPrimal, nbp, ctx->partDual, ctx->scal_d);
         CK(cudaMemcpyAsync(ctx->scal_h, ctx->scal_d, sizeof(double) * 3, cudaMemcpyDeviceToHost, st));
         CK(cudaMemcpyAsync(ctx->status_h, ctx->status_d, sizeof(unsigned), cudaMemcpyDeviceToHost, st));
