@@ -722,23 +722,16 @@ __global__ void __launch_bounds__(WPB * 32, MINB) k_prox_p(const __grid_constant
     if (lane == 0) { mbar_init(&bars[0], 1); mbar_init(&bars[1], 1); mbar_init(barB, 1); }
     __syncwarp();
 
-    auto load_ids = [&](int tile, int *vid, unsigned &fb) {
-        const int e = tile * 32 + lane;
-        if (e < a.E) {
-            load_elem_ids<D>(a, e, vid);
-            fb = a.fixedBits[e];
-        } else {
+    // connectivity of a tile -> shared memory ([D+1][32] ints), asynchronously; the F planes are padded to Es
+    auto issue_ids = [&](int tile, int *dst) {
 #pragma unroll
-            for (int v = 0; v < D + 1; v++) vid[v] = 0;
-            fb = 0;
-        }
+        for (int v = 0; v < D + 1; v++) cp_async4(dst + v * 32 + lane, a.F[v] + (size_t)tile * 32 + lane);
     };
     auto issue_small = [&](int tile, int buf, const int *vid) {
         double *b = bufs + (size_t)buf * BUF_DOUBLES;
         gather_async<D>(b, a.x, vid, lane);
         if (!haveZ) gather_async<D>(b + 2 * n * 32, a.zsrc, vid, lane);
         if (COMP) gather_async<D>(b + 3 * n * 32, a.Vc, vid, lane);
-        cp_async_commit();
         if (lane == 0 && smallBytes) {
             mbar_expect_tx(&bars[buf], smallBytes);
             if (haveU) tma_load_2d(b + n * 32, &maps.u, tile * 32, 0, &bars[buf]);
@@ -748,31 +741,23 @@ __global__ void __launch_bounds__(WPB * 32, MINB) k_prox_p(const __grid_constant
 
     double ihAcc = 0.0, dualAcc = 0.0;
     int t = gw, tn = gw + GW;
-    int nvid[D + 1];
-    unsigned fb = 0, nfb = 0, nfb2 = 0;
     if (t < nTiles) {
-        load_ids(t, nvid, fb);
-        issue_small(t, 0, nvid);
-        if (tn < nTiles) load_ids(tn, nvid, nfb);
+        int vid[D + 1];
+        const int e = t * 32 + lane;
+#pragma unroll
+        for (int v = 0; v < D + 1; v++) vid[v] = __ldg(a.F[v] + e);     // padded planes: always in bounds
+        issue_small(t, 0, vid);
+        if (tn < nTiles) issue_ids(tn, reinterpret_cast<int *>(bufs + BUF_DOUBLES));   // -> xg slot of buffer 1
+        cp_async_commit();
     }
-    for (int it = 0; t < nTiles; t = tn, tn += GW, it++, fb = nfb, nfb = nfb2) {
+    for (int it = 0; t < nTiles; t = tn, tn += GW, it++) {
         const int buf = it & 1;
         double *b = bufs + (size_t)buf * BUF_DOUBLES;
+        double *bn = bufs + (size_t)(buf ^ 1) * BUF_DOUBLES;
         const int e = t * 32 + lane;
         const bool active = e < a.E;
-        // inverse Hessians of this tile (the previous tile's store has drained: see the end of the loop body)
-        if (lane == 0) {
-            mbar_expect_tx(barB, (unsigned)(NN * 32 * sizeof(double)));
-            tma_load_2d(Bs, &maps.B, t * 32, 0, barB);
-        }
-        // everything but B for the next tile, connectivity for the one after
-        if (tn < nTiles) {
-            issue_small(tn, buf ^ 1, nvid);
-            if (tn + GW < nTiles) load_ids(tn + GW, nvid, nfb2);
-        } else {
-            cp_async_commit();   // keeps the group count uniform: exactly one younger group than this tile's
-        }
-        asm volatile("cp.async.wait_group 1;" ::: "memory");   // this tile's gathers have landed
+        const unsigned fb = active ? (unsigned)a.fixedBits[e] : 0u;   // consumed after the first gradient evaluation
+        cp_async_wait_all();                                            // this tile's gathers and the next tile's connectivity
         if (smallBytes) mbar_wait(&bars[buf], (unsigned)((it >> 1) & 1));
         double *xg = b + lane * D, *dxs = b + n * 32 + lane, *zs = b + 2 * n * 32, *xis = b + 3 * n * 32 + lane * D;
         double z[n], xi[COMP ? n : 1], Gk[n];
@@ -804,6 +789,22 @@ __global__ void __launch_bounds__(WPB * 32, MINB) k_prox_p(const __grid_constant
             for (int v = 0; v < D + 1; v++)
 #pragma unroll
                 for (int l = 0; l < D; l++) xi[D * v + l] = xis[(size_t)v * 32 * D + l];
+        }
+        // everything but B for the next tile; connectivity for the one after (into this buffer's spent xg slot)
+        if (tn < nTiles) {
+            int vid[D + 1];
+#pragma unroll
+            for (int v = 0; v < D + 1; v++) vid[v] = reinterpret_cast<const int *>(bn)[v * 32 + lane];
+            __syncwarp();   // every lane has its ids (and has consumed xg) before the slots are overwritten
+            issue_small(tn, buf ^ 1, vid);
+            if (tn + GW < nTiles) issue_ids(tn + GW, reinterpret_cast<int *>(b));
+        }
+        cp_async_commit();
+        // inverse Hessians of this tile, once the previous tile's store has drained out of the shared-memory tile
+        if (lane == 0) {
+            bulk_wait_read0();
+            mbar_expect_tx(barB, (unsigned)(NN * 32 * sizeof(double)));
+            tma_load_2d(Bs, &maps.B, t * 32, 0, barB);
         }
         if (active) ih = prox_grad_s<D>(z, dxs, xi, COMP, a.mg, a.fc, fb, Gk, inv);   // Ihsave: energy at entry
         mbar_wait(barB, (unsigned)(it & 1));
@@ -880,11 +881,10 @@ __global__ void __launch_bounds__(WPB * 32, MINB) k_prox_p(const __grid_constant
         if (lane == 0) {
             tma_store_2d(&maps.B, t * 32, 0, Bs);
             bulk_commit();
-            bulk_wait_read0();
         }
-        __syncwarp();
     }
-    asm volatile("cp.async.wait_group 0;" ::: "memory");
+    cp_async_wait_all();
+    if (lane == 0) bulk_wait_read0();   // shared memory must stay allocated until the last store has read it
     ihAcc = warp_sum(ihAcc);
     dualAcc = warp_sum(dualAcc);
     if (lane == 0) { a.partIh[gw] = ihAcc; a.partDual[gw] = dualAcc; }
@@ -1311,7 +1311,10 @@ int create_impl(mmadmm_ctx *ctx, const double *Vp, const double *Vc, const int *
     int *Frow = nullptr;
     CK(cudaMalloc(&Frow, sizeof(int) * (size_t)E * (D + 1)));
     CK(cudaMemcpyAsync(Frow, F, sizeof(int) * (size_t)E * (D + 1), cudaMemcpyHostToDevice, st));
-    for (int v = 0; v < D + 1; v++) CK(cudaMalloc(&ctx->F[v], sizeof(int) * (size_t)E));
+    for (int v = 0; v < D + 1; v++) {   // padded to whole tiles (asynchronous tile loads read the padding)
+        CK(cudaMalloc(&ctx->F[v], sizeof(int) * ctx->Es));
+        CK(cudaMemsetAsync(ctx->F[v], 0, sizeof(int) * ctx->Es, st));
+    }
     CK(cudaMalloc(&ctx->fixedBits, (size_t)E));
     CK(cudaMalloc(&ctx->nonIntBits, (size_t)E));
     k_setup_F<D><<<cdiv(E, 256), 256, 0, st>>>(E, Frow, ctx->F[0], ctx->F[1], ctx->F[2], ctx->F[3], ctx->x, ctx->mask,
