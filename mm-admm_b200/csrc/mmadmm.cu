@@ -42,6 +42,7 @@ namespace {
 constexpr int TPB = 128;       // element kernels: threads per block
 constexpr int TPB_V = 256;     // vertex kernels
 constexpr int MAXV = 4;        // D+1 <= 4
+enum ProxFlags { PF_PREFETCH_GRID = 1 };   // template switches of the persistent prox kernel
 constexpr int ES_ALIGN = 128;  // element planes are padded to full prox tiles (TMA bulk copies need whole, aligned tiles)
 
 template <int D> struct ElemArgs {
@@ -207,14 +208,14 @@ __global__ void k_nn_grid(MonGrid mg, double *gridOut, const double *x, const do
     }
     // 2D: row j*(nx+1)+i.  3D (sic, reference :198,234): row (nx+1)(ny+1)k + i*(nx+1) + j, i.e. transposed in x<->y
     size_t row = (D == 2) ? ((size_t)j * (nx + 1) + i) : ((size_t)(nx + 1) * (ny + 1) * k3 + (size_t)i * (nx + 1) + j);
-    constexpr int DD = D * D;
+    constexpr int DD = D * D, RS = GridRow<D>::stride;
 #pragma unroll
-    for (int k = 0; k < DD; k++) gridOut[row * DD + k] = monVertex[(size_t)best * DD + k];
+    for (int k = 0; k < DD; k++) gridOut[row * RS + k] = monVertex[(size_t)best * DD + k];
 }
 
 // smoothMonitorGrid (src/MeshInterpolator.cpp:365-404): Jacobi sweep from `src` into `dst`, interior nodes only
 template <int D> __global__ void k_smooth(int nx, int ny, int nz, const double *src, double *dst) {
-    constexpr int DD = D * D;
+    constexpr int DD = D * D, RS = GridRow<D>::stride;
     size_t rows = (size_t)(nx + 1) * (ny + 1) * ((D == 3) ? (nz + 1) : 1);
     size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= rows * DD) return;
@@ -225,8 +226,8 @@ template <int D> __global__ void k_smooth(int nx, int ny, int nz, const double *
     int k3 = (int)(row / ((size_t)(nx + 1) * (ny + 1)));
     bool interior = (i >= 1 && i < nx && j >= 1 && j < ny) && (D == 2 || (k3 >= 1 && k3 < nz));
     if (!interior) return;
-    size_t sx = DD, sy = (size_t)(nx + 1) * DD, sz = (size_t)(nx + 1) * (ny + 1) * DD;
-    const double *c = src + row * DD + k;
+    size_t sx = RS, sy = (size_t)(nx + 1) * RS, sz = (size_t)(nx + 1) * (ny + 1) * RS;
+    const double *c = src + row * RS + k;
     double v;
     // explicit non-fused arithmetic: the grid is input data for everything downstream, keep it bit-reproducible
     if (D == 2) {
@@ -245,7 +246,7 @@ template <int D> __global__ void k_smooth(int nx, int ny, int nz, const double *
         v = __dadd_rn(v, __dmul_rn(h, c[sz]));
         v = __dadd_rn(v, __dmul_rn(h, *(c - sz)));
     }
-    dst[row * DD + k] = v;
+    dst[row * RS + k] = v;
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -519,171 +520,6 @@ __global__ void __launch_bounds__(TPB_, MINB) k_prox(ElemArgs<D> a) {
     if (tid < 32) bulk_wait_read0();   // shared memory must stay allocated until the bulk stores have read it
 }
 
-// Warp-tile form of the prox kernel (thread per element, used for D = 2): every warp owns a tile of 32 elements with its
-// own mbarriers, its own TMA loads (B planes, u planes, z planes) and its own TMA stores, so there is no CTA barrier
-// anywhere: a warp that is waiting on HBM never holds up its neighbours.  u lands in the shared-memory slot that then
-// holds DXpU, z in the slot that holds zPrev, so the only per-thread state kept across a gradient evaluation is
-// z, Gk and pk.  Per-CTA sums / histogram are combined by the last warp to finish (fixed order -> deterministic).
-template <int D, int WPB, int MINB, bool COMP>
-__global__ void __launch_bounds__(WPB * 32, MINB) k_prox_w(ElemArgs<D> a) {
-    constexpr int n = D * (D + 1);
-    constexpr int NN = n * n;
-    constexpr int WARP_DOUBLES = (NN + 2 * n) * 32;
-    extern __shared__ __align__(128) unsigned char smem_raw[];
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    double *Bs = reinterpret_cast<double *>(smem_raw) + (size_t)warp * WARP_DOUBLES;   // [NN][32]
-    double *dxs = Bs + NN * 32;                                                        // [n][32]  u -> DXpU
-    double *zos = dxs + n * 32;                                                        // [n][32]  z at entry (zPrev)
-    uint64_t *bars = reinterpret_cast<uint64_t *>(reinterpret_cast<double *>(smem_raw) + (size_t)WPB * WARP_DOUBLES) + 2 * warp;
-    double *csum = reinterpret_cast<double *>(reinterpret_cast<uint64_t *>(reinterpret_cast<double *>(smem_raw) + (size_t)WPB * WARP_DOUBLES) + 2 * WPB);  // [2][WPB]
-    int *shist = reinterpret_cast<int *>(csum + 2 * WPB);                              // 52 bins
-    int *arrived = shist + 52;
-    if (threadIdx.x < 53) shist[threadIdx.x] = 0;   // 52 bins + arrival counter
-    const size_t e0 = ((size_t)blockIdx.x * WPB + warp) * 32;
-    const int e = (int)e0 + lane;
-    const bool tileLive = e0 < (size_t)a.E;
-    const bool active = e < a.E;
-    const bool haveU = !a.uZero, haveZ = (a.zsrc == nullptr);
-    if (lane == 0) { mbar_init(&bars[0], 1); mbar_init(&bars[1], 1); }
-    __syncthreads();   // the only CTA barrier: barrier init + histogram clear visible
-    if (tileLive) {
-        if (lane == 0) {
-            mbar_expect_tx(&bars[0], (unsigned)(((haveU ? n : 0) + (haveZ ? n : 0)) * 32 * sizeof(double)));
-            mbar_expect_tx(&bars[1], (unsigned)(NN * 32 * sizeof(double)));
-        }
-        __syncwarp();
-        if (lane < n) {
-            if (haveU) bulk_g2s(dxs + lane * 32, a.u + (size_t)lane * a.Es + e0, 256u, &bars[0]);
-            if (haveZ) bulk_g2s(zos + lane * 32, a.z + (size_t)lane * a.Es + e0, 256u, &bars[0]);
-        }
-        for (int k = lane; k < NN; k += 32) bulk_g2s(Bs + k * 32, a.B + (size_t)k * a.Es + e0, 256u, &bars[1]);
-    }
-    double ih = 0.0, dual2 = 0.0;
-    int bin = -1;
-    if (tileLive) {
-        double z[n], xi[COMP ? n : 1], Gk[n];
-        unsigned fb = 0;
-        bool inv = false;
-        int vid[D + 1];
-        if (active) {
-            load_elem_ids<D>(a, e, vid);
-            fb = a.fixedBits[e];
-        }
-        mbar_wait(&bars[0], 0);
-        if (active) {
-            {
-                double dx[n];
-#pragma unroll
-                for (int v = 0; v < D + 1; v++) gather_vertex<D>(a.x, vid[v], dx + D * v);
-#pragma unroll
-                for (int k = 0; k < n; k++) dxs[k * 32 + lane] = haveU ? dx[k] + dxs[k * 32 + lane] : dx[k];   // DXpU = D x + u
-            }
-            if (haveZ) {
-#pragma unroll
-                for (int k = 0; k < n; k++) z[k] = zos[k * 32 + lane];
-            } else {
-#pragma unroll
-                for (int v = 0; v < D + 1; v++) gather_vertex<D>(a.zsrc, vid[v], z + D * v);
-#pragma unroll
-                for (int k = 0; k < n; k++) zos[k * 32 + lane] = z[k];
-            }
-            if (COMP) {
-#pragma unroll
-                for (int v = 0; v < D + 1; v++) gather_vertex<D>(a.Vc, vid[v], xi + D * v);
-            }
-            ih = prox_grad_s<D>(z, dxs + lane, xi, COMP, a.mg, a.fc, fb, Gk, inv);   // Ihsave: energy at entry
-        }
-        mbar_wait(&bars[1], 0);
-        if (active) {
-            double *Bt = Bs + lane;
-#define BS(k) Bt[(k) * 32]
-            int iter;
-            for (iter = 0; iter < 50; iter++) {
-                double pk[n], G1[n];
-#pragma unroll
-                for (int r = 0; r < n; r++) {
-                    double s = BS(r * n) * Gk[0];
-#pragma unroll
-                    for (int c = 1; c < n; c++) s += BS(r * n + c) * Gk[c];
-                    pk[r] = -s;
-                    z[r] += pk[r];
-                }
-                prox_grad_s<D>(z, dxs + lane, xi, COMP, a.mg, a.fc, fb, G1, inv);
-                double Ix = 0.0, yk[n];
-#pragma unroll
-                for (int k = 0; k < n; k++) { Ix += fabs(G1[k]); yk[k] = G1[k] - Gk[k]; Gk[k] = G1[k]; }
-                double c2 = pk[0] * yk[0];
-#pragma unroll
-                for (int k = 1; k < n; k++) c2 += pk[k] * yk[k];
-                double By[n], yB[n];
-#pragma unroll
-                for (int r = 0; r < n; r++) {
-                    double s = 0.0;
-#pragma unroll
-                    for (int c = 0; c < n; c++) {
-                        const double b = BS(r * n + c);
-                        s = (c == 0) ? b * yk[0] : s + b * yk[c];
-                        yB[c] = (r == 0) ? yk[0] * b : yB[c] + yk[r] * b;
-                    }
-                    By[r] = s;
-                }
-                double yBy = yk[0] * By[0];
-#pragma unroll
-                for (int k = 1; k < n; k++) yBy += yk[k] * By[k];
-                const double ic2 = 1.0 / c2;
-                const double c1 = (c2 + yBy) * (ic2 * ic2);
-#pragma unroll
-                for (int r = 0; r < n; r++) {
-                    const double a1 = c1 * pk[r], a3 = pk[r] * ic2, a2 = By[r] * ic2;
-#pragma unroll
-                    for (int c = 0; c < n; c++) BS(r * n + c) += (a1 * pk[c] - a2 * pk[c]) - a3 * yB[c];
-                }
-                if (Ix < a.tol) break;
-            }
-#undef BS
-            if (inv) atomicOr(a.status, ST_INVERTED);
-            if (iter == 50) atomicOr(a.status, ST_BFGS_MAX);
-            bin = (iter == 50) ? 51 : iter + 1;
-#pragma unroll
-            for (int k = 0; k < n; k++) {
-                a.z[k * a.Es + e] = z[k];
-                a.u[k * a.Es + e] = dxs[k * 32 + lane] - z[k];    // u = DXpU - z
-                const double d = z[k] - zos[k * 32 + lane];
-                dual2 += d * d;
-            }
-        }
-        // updated tile back to HBM: generic-proxy writes -> async proxy, then bulk stores by this warp
-        fence_async_smem();
-        __syncwarp();
-        for (int k = lane; k < NN; k += 32) bulk_s2g(a.B + (size_t)k * a.Es + e0, Bs + k * 32, 256u);
-        bulk_commit();
-    }
-    ih = warp_sum(ih);
-    dual2 = warp_sum(dual2);
-    if (a.hist && bin >= 0) atomicAdd(&shist[bin], 1);
-    if (lane == 0) { csum[warp] = ih; csum[WPB + warp] = dual2; }
-    __threadfence_block();
-    int last = 0;
-    if (lane == 0) last = (atomicAdd(arrived, 1) == WPB - 1);
-    last = __shfl_sync(0xffffffffu, last, 0);
-    if (last) {
-        __threadfence_block();
-        if (lane == 0) {
-            double s1 = 0.0, s2 = 0.0;
-            for (int w = 0; w < WPB; w++) { s1 += csum[w]; s2 += csum[WPB + w]; }
-            a.partIh[blockIdx.x] = s1;
-            a.partDual[blockIdx.x] = s2;
-        }
-        if (a.hist) {
-            for (int k = lane; k < 52; k += 32) {
-                int c = ((volatile int *)shist)[k];
-                if (c) atomicAdd(&a.hist[k], (unsigned long long)c);
-            }
-        }
-    }
-    if (tileLive) bulk_wait_read0();   // shared memory must stay allocated until the bulk stores have read it
-}
-
 // Persistent, software-pipelined form of the warp-tile prox kernel (the default for D = 2).  One warp walks tiles
 // t = gw, gw + GW, ... of 32 elements.  While tile t is being solved, everything tile t+1 needs except its inverse
 // Hessians is already on its way into the other half of a double buffer: vertex gathers (x, zsrc, Vc) by per-thread
@@ -702,7 +538,7 @@ template <int D> __device__ __forceinline__ void gather_async(double *dst /* [D+
     }
 }
 
-template <int D, int WPB, int MINB, bool COMP>
+template <int D, int WPB, int MINB, bool COMP, int FLAGS>
 __global__ void __launch_bounds__(WPB * 32, MINB) k_prox_p(const __grid_constant__ ElemArgs<D> a, const __grid_constant__ ProxMaps maps) {
     constexpr int n = D * (D + 1);
     constexpr int NN = n * n;
@@ -800,8 +636,8 @@ __global__ void __launch_bounds__(WPB * 32, MINB) k_prox_p(const __grid_constant
             if (tn + GW < nTiles) issue_ids(tn + GW, reinterpret_cast<int *>(b));
         }
         cp_async_commit();
-        // inverse Hessians of this tile, once the previous tile's store has drained out of the shared-memory tile
         if (lane == 0) {
+            // this tile's inverse Hessians, once the previous tile's store has drained out of shared memory
             bulk_wait_read0();
             mbar_expect_tx(barB, (unsigned)(NN * 32 * sizeof(double)));
             tma_load_2d(Bs, &maps.B, t * 32, 0, barB);
@@ -874,13 +710,26 @@ __global__ void __launch_bounds__(WPB * 32, MINB) k_prox_p(const __grid_constant
             const unsigned peers = __match_any_sync(0xffffffffu, bin);
             if (bin >= 0 && lane == __ffs(peers) - 1) atomicAdd(&a.hist[bin], (unsigned long long)__popc(peers));
         }
-        // updated tile back to HBM: generic-proxy writes -> async proxy, then one tensor-map store; the shared-memory
-        // tile may be overwritten (next tile's load) once the store has read it
+        // updated tile back to HBM: generic-proxy writes -> async proxy, then one tensor-map store (TMA stores beat
+        // per-thread STG of the 36 planes by 25 % here: profiles/r01_b_summary.md)
         fence_async_smem();
         __syncwarp();
         if (lane == 0) {
             tma_store_2d(&maps.B, t * 32, 0, Bs);
             bulk_commit();
+        }
+        if (tn < nTiles && (FLAGS & PF_PREFETCH_GRID)) {
+            // the next tile's vertices have landed by now: pull the monitor-grid rows its entry gradient will read into L2
+            cp_async_wait_all();
+            if (haveZ) mbar_wait(&bars[buf ^ 1], (unsigned)(((it + 1) >> 1) & 1));
+            const double *zn = bn + 2 * n * 32;
+#pragma unroll
+            for (int v = 0; v < D + 1; v++) {
+                double pnt[D];
+#pragma unroll
+                for (int l = 0; l < D; l++) pnt[l] = haveZ ? zn[(D * v + l) * 32 + lane] : zn[((size_t)v * 32 + lane) * D + l];
+                prefetch_monitor<D>(a.mg, pnt);
+            }
         }
     }
     cp_async_wait_all();
@@ -942,17 +791,30 @@ __global__ void __launch_bounds__(TPB_V) k_xupdate(int P, size_t Es, const int *
 #pragma unroll
         for (int l = 0; l < D; l++) { s[l] = 0.0; zs[l] = ZSRC ? zsrc[(size_t)D * p + l] : 0.0; }
         const int k0 = incPtr[p], k1 = incPtr[p + 1];
-        for (int k = k0; k < k1; k++) {
-            int slot = __ldg(incIdx + k);
-            size_t e = (size_t)(slot >> 2);
-            int v = slot & 3;
+        // slots in chunks of CH: all index loads, then all value loads, then the (ordered) accumulation
+        constexpr int CH = 4;
+        for (int kb = k0; kb < k1; kb += CH) {
+            int slot[CH];
+            double zv[CH][D], uv[CH][D];
 #pragma unroll
-            for (int l = 0; l < D; l++) {
-                size_t idx = (size_t)(D * v + l) * Es + e;
-                double zv = ZSRC ? zs[l] : __ldg(z + idx);
-                double uv = UZERO ? 0.0 : __ldg(u + idx);
-                s[l] += w * (w * (zv - uv));
+            for (int j = 0; j < CH; j++) slot[j] = (kb + j < k1) ? __ldg(incIdx + kb + j) : -1;
+#pragma unroll
+            for (int j = 0; j < CH; j++) {
+                const size_t e = (size_t)(slot[j] >> 2);
+                const int v = slot[j] & 3;
+#pragma unroll
+                for (int l = 0; l < D; l++) {
+                    const size_t idx = (size_t)(D * v + l) * Es + e;
+                    zv[j][l] = (ZSRC || slot[j] < 0) ? zs[l] : __ldg(z + idx);
+                    uv[j][l] = (UZERO || slot[j] < 0) ? 0.0 : __ldg(u + idx);
+                }
             }
+#pragma unroll
+            for (int j = 0; j < CH; j++)
+                if (slot[j] >= 0) {
+#pragma unroll
+                    for (int l = 0; l < D; l++) s[l] += w * (w * (zv[j][l] - uv[j][l]));
+                }
         }
         double td = tdiag[p];
 #pragma unroll
@@ -1242,8 +1104,10 @@ template <int D> int build_monitor_grid(mmadmm_ctx *ctx, const double *VpHost, c
     CK(cudaMemcpyAsync(ctx->az, hz.data(), sizeof(double) * hz.size(), cudaMemcpyHostToDevice, st));
     ctx->gridRows = (size_t)(ctx->nx + 1) * (ctx->ny + 1) * ((D == 3) ? (ctx->nz + 1) : 1);
     double *gridTmp = nullptr, *monV = nullptr;
-    CK(cudaMalloc(&ctx->grid, sizeof(double) * ctx->gridRows * DD));
-    CK(cudaMalloc(&gridTmp, sizeof(double) * ctx->gridRows * DD));
+    constexpr int RS = GridRow<D>::stride;
+    CK(cudaMalloc(&ctx->grid, sizeof(double) * ctx->gridRows * RS));
+    CK(cudaMalloc(&gridTmp, sizeof(double) * ctx->gridRows * RS));
+    CK(cudaMemsetAsync(ctx->grid, 0, sizeof(double) * ctx->gridRows * RS, st));
     CK(cudaMalloc(&monV, sizeof(double) * (size_t)P * DD));
     CK(cudaMemcpyAsync(monV, monVertexHost, sizeof(double) * (size_t)P * DD, cudaMemcpyHostToDevice, st));
 
@@ -1276,7 +1140,7 @@ template <int D> int build_monitor_grid(mmadmm_ctx *ctx, const double *VpHost, c
     k_nn_grid<D><<<cdiv(ctx->gridRows, 128), 128, 0, st>>>(mg, ctx->grid, ctx->x, monV, bg, binStart, items);
     int nSmooth = (D == 2) ? 5 : 2;  // src/MeshInterpolator.cpp:246-252
     for (int it = 0; it < nSmooth; it++) {
-        CK(cudaMemcpyAsync(gridTmp, ctx->grid, sizeof(double) * ctx->gridRows * DD, cudaMemcpyDeviceToDevice, st));
+        CK(cudaMemcpyAsync(gridTmp, ctx->grid, sizeof(double) * ctx->gridRows * RS, cudaMemcpyDeviceToDevice, st));
         k_smooth<D><<<cdiv(ctx->gridRows * DD, 256), 256, 0, st>>>(ctx->nx, ctx->ny, ctx->nz, gridTmp, ctx->grid);
     }
     ctx->launches += 2 + nSmooth;
@@ -1422,25 +1286,12 @@ template <int D, int TPB_, int MINB> int launch_prox_t(mmadmm_ctx *ctx, const El
 
 // Tile shape / occupancy variants of the prox kernel ("prox_variant" option; 0 is the tuned default)
 template <int D> int launch_prox(mmadmm_ctx *ctx, const ElemArgs<D> &a);
-template <int D, int WPB, int MINB> int launch_prox_w(mmadmm_ctx *ctx, const ElemArgs<D> &a, int slot) {
-    constexpr int n = D * (D + 1);
-    constexpr size_t smem = sizeof(double) * (size_t)WPB * (n * n + 2 * n) * 32 + 16 * WPB + sizeof(double) * 2 * WPB + sizeof(int) * 56;
-    auto kern = ctx->compMesh ? k_prox_w<D, WPB, MINB, true> : k_prox_w<D, WPB, MINB, false>;
-    if (!ctx->smemAttrSet[slot]) {
-        CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        ctx->smemAttrSet[slot] = true;
-    }
-    kern<<<cdiv(ctx->E, WPB * 32), WPB * 32, smem, ctx->stream>>>(a);
-    ctx->nProxPart = cdiv(ctx->E, WPB * 32);
-    ctx->launches++;
-    return MMADMM_OK;
-}
-template <int D, int WPB, int MINB> int launch_prox_p(mmadmm_ctx *ctx, const ElemArgs<D> &a, int slot) {
+template <int D, int WPB, int MINB, int FLAGS> int launch_prox_p(mmadmm_ctx *ctx, const ElemArgs<D> &a, int slot) {
     constexpr int n = D * (D + 1);
     if (!ctx->haveMaps) { ctx->err = "tensor maps unavailable (cuTensorMapEncodeTiled)"; return MMADMM_ECUDA; }
     const size_t slots = ctx->compMesh ? 4 : 3;
     const size_t smem = sizeof(double) * (size_t)WPB * (n * n * 32 + 2 * slots * n * 32) + 32 * WPB;
-    auto kern = ctx->compMesh ? k_prox_p<D, WPB, MINB, true> : k_prox_p<D, WPB, MINB, false>;
+    auto kern = ctx->compMesh ? k_prox_p<D, WPB, MINB, true, FLAGS> : k_prox_p<D, WPB, MINB, false, FLAGS>;
     if (!ctx->smemAttrSet[slot]) {
         CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         ctx->smemAttrSet[slot] = true;
@@ -1453,12 +1304,11 @@ template <int D, int WPB, int MINB> int launch_prox_p(mmadmm_ctx *ctx, const Ele
 }
 template <> int launch_prox<2>(mmadmm_ctx *ctx, const ElemArgs<2> &a) {
     switch (ctx->proxVariant) {
-        case 1: return launch_prox_p<2, 6, 2>(ctx, a, 1);
-        case 2: return launch_prox_p<2, 2, 6>(ctx, a, 2);
-        case 3: return launch_prox_w<2, 8, 2>(ctx, a, 3);
-        case 4: return launch_prox_t<2, 128, 4>(ctx, a, 4);
-        case 5: return launch_prox_w<2, 4, 4>(ctx, a, 5);
-        default: return launch_prox_p<2, 4, 3>(ctx, a, 0);
+        case 1: return launch_prox_p<2, 2, 6, 0>(ctx, a, 1);                  // no monitor-grid prefetch
+        case 2: return launch_prox_p<2, 4, 3, PF_PREFETCH_GRID>(ctx, a, 2);   // 4-warp CTAs
+        case 3: return launch_prox_p<2, 6, 2, PF_PREFETCH_GRID>(ctx, a, 3);   // 6-warp CTAs
+        case 4: return launch_prox_t<2, 128, 4>(ctx, a, 4);                   // CTA-tile form (non-persistent)
+        default: return launch_prox_p<2, 2, 6, PF_PREFETCH_GRID>(ctx, a, 0);
     }
 }
 template <> int launch_prox<3>(mmadmm_ctx *ctx, const ElemArgs<3> &a) {
@@ -1657,8 +1507,12 @@ int mmadmm_get_state(mmadmm_ctx *ctx, int which, double *out) {
         CK(cudaMemcpy(out, which == MMADMM_STATE_XBAR ? ctx->xBar : ctx->xPrev, sizeof(double) * (size_t)ctx->P * ctx->D, cudaMemcpyDeviceToHost));
         return MMADMM_OK;
     }
-    if (which == MMADMM_STATE_MONGRID) {
-        CK(cudaMemcpy(out, ctx->grid, sizeof(double) * ctx->gridRows * ctx->D * ctx->D, cudaMemcpyDeviceToHost));
+    if (which == MMADMM_STATE_MONGRID) {   // rows unpadded to D*D values
+        const int DD = ctx->D * ctx->D, RS = (ctx->D == 2) ? GridRow<2>::stride : GridRow<3>::stride;
+        std::vector<double> tmp(ctx->gridRows * RS);
+        CK(cudaMemcpy(tmp.data(), ctx->grid, sizeof(double) * ctx->gridRows * RS, cudaMemcpyDeviceToHost));
+        for (size_t r = 0; r < ctx->gridRows; r++)
+            for (int k = 0; k < DD; k++) out[r * DD + k] = tmp[r * RS + k];
         return MMADMM_OK;
     }
     return MMADMM_EINVAL;

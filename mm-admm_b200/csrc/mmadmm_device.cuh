@@ -16,8 +16,10 @@ namespace mmadmm {
 enum NodeTypeDev { NT_BOUNDARY_FREE = 0, NT_BOUNDARY_FIXED = 1, NT_INTERIOR = 2 };  // src/NodeType.h:4-8
 enum StatusBits { ST_INVERTED = 1, ST_SINGULAR_HESS = 2, ST_BFGS_MAX = 4, ST_NONFINITE = 8 };
 
-// Monitor grid (read-only after init).  Rows are grid points, D*D doubles each, row index
-// zInd*(nx+1)*(ny+1) + yInd*(nx+1) + xInd exactly as the reference's lookup reads it.
+// Monitor grid (read-only after init).  Rows are grid points, D*D doubles each (3D rows are padded to 10 doubles so
+// that every row is five aligned 16-byte loads), row index zInd*(nx+1)*(ny+1) + yInd*(nx+1) + xInd exactly as the
+// reference's lookup reads it.
+template <int D> struct GridRow { static constexpr int stride = (D == 2) ? 4 : 10; };
 struct MonGrid {
     const double *vals;
     const double *ax, *ay, *az;  // axis coordinates, nx+1 / ny+1 / nz+1 entries (utils::linspace values)
@@ -205,9 +207,35 @@ template <> __device__ __forceinline__ void eval_monitor<3>(const MonGrid &g, co
 #pragma unroll
     for (int cc = 0; cc < 8; cc++) {
         size_t row = base + ((cc & 1) ? 1 : 0) + ((cc & 2) ? (size_t)(g.nx + 1) : 0) + ((cc & 4) ? sl : 0);
-        const double *r = g.vals + row * 9;
+        const double2 *r = reinterpret_cast<const double2 *>(g.vals + row * GridRow<3>::stride);
+        const double2 v0 = __ldg(r), v1 = __ldg(r + 1), v2 = __ldg(r + 2), v3 = __ldg(r + 3), v4 = __ldg(r + 4);
+        mVal.a[0] += c[cc] * v0.x; mVal.a[1] += c[cc] * v0.y; mVal.a[2] += c[cc] * v1.x; mVal.a[3] += c[cc] * v1.y;
+        mVal.a[4] += c[cc] * v2.x; mVal.a[5] += c[cc] * v2.y; mVal.a[6] += c[cc] * v3.x; mVal.a[7] += c[cc] * v3.y;
+        mVal.a[8] += c[cc] * v4.x;
+    }
+}
+
+// L2 prefetch of the grid rows eval_monitor(pnt) will read
+__device__ __forceinline__ void prefetch_l2(const void *p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
+template <int D> __device__ __forceinline__ void prefetch_monitor(const MonGrid &g, const double *pnt) {
+    int xInd = find_cell(pnt[0], g.o[0], g.rh[0], g.nx);
+    int yInd = find_cell(pnt[1], g.o[1], g.rh[1], g.ny);
+    if (D == 2) {
+        const double *r0 = g.vals + 4 * ((size_t)yInd * (g.nx + 1) + xInd);
+        prefetch_l2(r0);
+        prefetch_l2(r0 + 7);
+        prefetch_l2(r0 + 4 * (size_t)(g.nx + 1));
+        prefetch_l2(r0 + 4 * (size_t)(g.nx + 1) + 7);
+    } else {
+        int zInd = find_cell(pnt[2], g.o[2], g.rh[2], g.nz);
+        const size_t sl = (size_t)(g.nx + 1) * (g.ny + 1);
+        const double *r0 = g.vals + GridRow<3>::stride * ((size_t)zInd * sl + (size_t)yInd * (g.nx + 1) + xInd);
 #pragma unroll
-        for (int k = 0; k < 9; k++) mVal.a[k] += c[cc] * __ldg(r + k);
+        for (int cc = 0; cc < 4; cc++) {
+            const double *r = r0 + GridRow<3>::stride * (((cc & 1) ? (size_t)(g.nx + 1) : 0) + ((cc & 2) ? sl : 0));
+            prefetch_l2(r);
+            prefetch_l2(r + 2 * GridRow<3>::stride - 1);
+        }
     }
 }
 
