@@ -56,7 +56,8 @@ int mmadmm_step(mmadmm_ctx *ctx, int nIters, double tol, double *Ih, int *itersT
 /* Replaces MeshIntegrator<D>::getEnergy -> Mesh::computeEnergy (src/Mesh.cpp:496-530). */
 int mmadmm_energy(mmadmm_ctx *ctx, double *I);
 
-/* Replaces Mesh::updateAfterStep / copyX (src/Mesh.cpp:996-1004,1016-1036): current node positions, P x D. */
+/* Replaces Mesh::updateAfterStep / copyX (src/Mesh.cpp:996-1004,1016-1036): current node positions, P x D.
+ * On a distributed context this is a collective call that assembles the GLOBAL vector on every rank. */
 int mmadmm_get_x(mmadmm_ctx *ctx, double *x);
 /* Same, but into a caller-provided *device* pointer (no host copy). */
 int mmadmm_get_x_device(mmadmm_ctx *ctx, double *x_dev);
@@ -94,6 +95,43 @@ int mmadmm_set_option(mmadmm_ctx *ctx, const char *name, int value);
 
 /* The CUDA stream every kernel of this context is launched on (cudaStream_t as void*). */
 void *mmadmm_stream(mmadmm_ctx *ctx);
+
+/* ---- multi-GPU: element-block partition, one process per GPU (the reference has no counterpart, its only
+ * parallelism is the OpenMP loop over simplices at src/Mesh.cpp:945-948) ---- */
+
+/* Host-side partition plan of `rank` out of `nranks` computed from the GLOBAL connectivity (no device needed).
+ * sizes6 = {e0, e1, nLocalVertices, nSharedVertices, nNeighbours, lenNeighbourLists}. */
+typedef struct mmadmm_plan mmadmm_plan;
+enum { MMADMM_PLAN_VERTS = 0,       /* local vertex -> global vertex, ascending            [nLocalVertices] */
+       MMADMM_PLAN_FLOC = 1,        /* owned elements in local vertex ids                  [(e1-e0)*(D+1)]  */
+       MMADMM_PLAN_VALENCE = 2,     /* GLOBAL valence of every local vertex                [nLocalVertices] */
+       MMADMM_PLAN_SHARED = 3,      /* local ids of vertices shared with other ranks       [nSharedVertices] */
+       MMADMM_PLAN_NBR_RANK = 4,    /* neighbour ranks, ascending                          [nNeighbours]    */
+       MMADMM_PLAN_NBR_PTR = 5,     /* segment offsets into NBR_LIST                       [nNeighbours+1]  */
+       MMADMM_PLAN_NBR_LIST = 6,    /* per neighbour: indices into SHARED, ascending global vertex */
+       MMADMM_PLAN_CONTRIB_PTR = 7, /* per shared vertex: offsets into CONTRIB             [nSharedVertices+1] */
+       MMADMM_PLAN_CONTRIB = 8,     /* contributions in ascending rank order: receive-buffer position, or -1 = own */
+       MMADMM_PLAN_OWNER = 9 };     /* 1 if this rank is the lowest rank holding the vertex [nLocalVertices] */
+int mmadmm_plan_create(int D, int P, int E, const int *F, int nranks, int rank, mmadmm_plan **out);
+int mmadmm_plan_sizes(const mmadmm_plan *plan, int *sizes6);
+int mmadmm_plan_get(const mmadmm_plan *plan, int which, int *out);
+void mmadmm_plan_destroy(mmadmm_plan *plan);
+
+/* 128-byte NCCL unique id for the communicator of a distributed context (call on rank 0, broadcast it by any means). */
+int mmadmm_comm_unique_id(void *id128);
+
+/* Distributed form of mmadmm_create: every rank passes the same GLOBAL mesh and its (rank, nranks, id).  The rank keeps
+ * the element block of its plan and private copies of the vertices those elements touch; per ADMM iteration the
+ * shared-vertex partial sums of D^T(w(z-u)) are exchanged with ncclSend/ncclRecv and the three residual scalars with
+ * one ncclAllGather.  mmadmm_step / mmadmm_energy are collective calls and return identical values on every rank. */
+int mmadmm_create_dist(int D, int P, int E, const double *Vp, const double *Vc, const int *F, const int *mask,
+                       const double *monVertex, double rho, double tau, double dt, int gradUse, int device, int rank,
+                       int nranks, const void *id128, mmadmm_ctx **out);
+
+/* Number of local vertices / elements of a context (P, E for a single-GPU context). */
+int mmadmm_local_sizes(mmadmm_ctx *ctx, int *Ploc, int *Eloc);
+/* Local vertices' positions scattered into a caller array of GLOBAL size P x D (other rows untouched; no collective). */
+int mmadmm_get_x_local(mmadmm_ctx *ctx, double *xGlobal);
 
 void mmadmm_destroy(mmadmm_ctx *ctx);
 const char *mmadmm_last_error(mmadmm_ctx *ctx);

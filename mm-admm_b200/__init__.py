@@ -31,7 +31,8 @@ ABI_SYMBOLS = [
     "mmadmm_create", "mmadmm_step", "mmadmm_energy", "mmadmm_get_x", "mmadmm_get_x_device", "mmadmm_get_F",
     "mmadmm_grid_dims", "mmadmm_get_state", "mmadmm_eval_monitor", "mmadmm_block_grad", "mmadmm_get_stats",
     "mmadmm_get_timing", "mmadmm_set_option", "mmadmm_stream", "mmadmm_destroy", "mmadmm_last_error",
-    "mmadmm_version",
+    "mmadmm_version", "mmadmm_plan_create", "mmadmm_plan_sizes", "mmadmm_plan_get", "mmadmm_plan_destroy",
+    "mmadmm_comm_unique_id", "mmadmm_create_dist", "mmadmm_local_sizes", "mmadmm_get_x_local",
 ]
 
 
@@ -82,6 +83,16 @@ def lib():
         L.mmadmm_last_error.restype = C.c_char_p
         L.mmadmm_last_error.argtypes = [vp]
         L.mmadmm_version.restype = C.c_char_p
+        L.mmadmm_plan_create.argtypes = [C.c_int, C.c_int, C.c_int, _c_ip, C.c_int, C.c_int, C.POINTER(vp)]
+        L.mmadmm_plan_sizes.argtypes = [vp, _c_ip]
+        L.mmadmm_plan_get.argtypes = [vp, C.c_int, _c_ip]
+        L.mmadmm_plan_destroy.restype = None
+        L.mmadmm_plan_destroy.argtypes = [vp]
+        L.mmadmm_comm_unique_id.argtypes = [C.c_char_p]
+        L.mmadmm_create_dist.argtypes = [C.c_int, C.c_int, C.c_int, _c_dp, _c_dp, _c_ip, _c_ip, _c_dp, C.c_double, C.c_double,
+                                         C.c_double, C.c_int, C.c_int, C.c_int, C.c_int, C.c_char_p, C.POINTER(vp)]
+        L.mmadmm_local_sizes.argtypes = [vp, _c_ip, _c_ip]
+        L.mmadmm_get_x_local.argtypes = [vp, _c_dp]
         _lib = L
     return _lib
 
@@ -115,6 +126,45 @@ def generate_uniform_rect_mesh(D, nx, ny, nz=0, box=(0, 1, 0, 1, 0, 1), boundary
     if rc:
         raise MMADMMError("bad mesh parameters")
     return Vp, F, mask
+
+
+def partition_plan(D, P, E, F, nranks, rank):
+    """Host-side element-block partition plan of `rank` (include/mmadmm.h, mmadmm_plan_*): no device needed."""
+    L = lib()
+    F = np.ascontiguousarray(F, dtype=np.int32)
+    h = C.c_void_p()
+    rc = L.mmadmm_plan_create(D, P, E, _ip(F), nranks, rank, C.byref(h))
+    if rc:
+        raise MMADMMError("bad partition arguments")
+    try:
+        sz = np.zeros(6, dtype=np.int32)
+        L.mmadmm_plan_sizes(h, _ip(sz))
+        e0, e1, npl, nsh, nnb, nitems = (int(v) for v in sz)
+        lens = {0: npl, 1: (e1 - e0) * (D + 1), 2: npl, 3: nsh, 4: nnb, 5: nnb + 1, 6: nitems, 7: nsh + 1, 9: npl}
+        names = {0: "verts", 1: "Floc", 2: "valence", 3: "shared", 4: "nbr_rank", 5: "nbr_ptr", 6: "nbr_list", 7: "contrib_ptr",
+                 9: "owner"}
+        out = dict(e0=e0, e1=e1)
+        for k, n in lens.items():
+            a = np.zeros(max(n, 1), dtype=np.int32)
+            L.mmadmm_plan_get(h, k, _ip(a))
+            out[names[k]] = a[:n]
+        nc = int(out["contrib_ptr"][-1]) if nsh else 0
+        a = np.zeros(max(nc, 1), dtype=np.int32)
+        L.mmadmm_plan_get(h, 8, _ip(a))
+        out["contrib"] = a[:nc]
+        out["Floc"] = out["Floc"].reshape(-1, D + 1)
+        return out
+    finally:
+        L.mmadmm_plan_destroy(h)
+
+
+def comm_unique_id():
+    """128-byte NCCL unique id (rank 0 creates it; broadcast it with torch.distributed or any other channel)."""
+    buf = C.create_string_buffer(128)
+    rc = lib().mmadmm_comm_unique_id(buf)
+    if rc:
+        raise MMADMMError("NCCL is not available")
+    return buf.raw
 
 
 class TestMonitor:
@@ -166,16 +216,26 @@ class Mesh:
 class MeshIntegrator:
     """Mirror of `MeshIntegrator<D>` (src/MeshIntegrator.h:15-27): step / getEnergy / done."""
 
-    def __init__(self, dt, mesh, device=0, sync_vp=True):
+    def __init__(self, dt, mesh, device=0, sync_vp=True, comm=None):
+        """comm = (rank, nranks, id128) makes this rank one member of an element-block-partitioned solve over nranks
+        GPUs (one process per GPU; every rank passes the same global mesh).  step/getEnergy/done are then collective."""
         self.mesh, self.dt = mesh, float(dt)
         self.sync_vp = sync_vp
         self.L = lib()
         self.h = C.c_void_p()
         m = mesh
-        rc = self.L.mmadmm_create(m.D, m.P, m.E, _dp(m.Vp), _dp(m.Vc), _ip(m.F), _ip(m.boundary_mask), _dp(m.mon_vertex),
-                                  m.rho, m.tau, self.dt, int(m.gradUse), device, C.byref(self.h))
-        self._check(rc)
-        self._check(self.L.mmadmm_get_F(self.h, _ip(m.F)))  # the reference permutes the caller's F in place
+        self.dist = comm is not None and comm[1] > 1
+        if self.dist:
+            rank, nranks, id128 = comm
+            rc = self.L.mmadmm_create_dist(m.D, m.P, m.E, _dp(m.Vp), _dp(m.Vc), _ip(m.F), _ip(m.boundary_mask),
+                                           _dp(m.mon_vertex), m.rho, m.tau, self.dt, int(m.gradUse), device, rank, nranks,
+                                           id128, C.byref(self.h))
+            self._check(rc)
+        else:
+            rc = self.L.mmadmm_create(m.D, m.P, m.E, _dp(m.Vp), _dp(m.Vc), _ip(m.F), _ip(m.boundary_mask), _dp(m.mon_vertex),
+                                      m.rho, m.tau, self.dt, int(m.gradUse), device, C.byref(self.h))
+            self._check(rc)
+            self._check(self.L.mmadmm_get_F(self.h, _ip(m.F)))  # the reference permutes the caller's F in place
         self.n = m.D * (m.D + 1)
         self.last = {}
 
@@ -200,8 +260,16 @@ class MeshIntegrator:
         self._check(self.L.mmadmm_step(self.h, int(nIters), float(tol), C.byref(Ih), C.byref(it), C.byref(pr), C.byref(du)))
         self.last = dict(Ih=Ih.value, iters=it.value, primal=pr.value, dual=du.value)
         if self.sync_vp:  # Mesh::updateAfterStep writes the caller's Vp every step (src/Mesh.cpp:1030-1035)
-            self._check(self.L.mmadmm_get_x(self.h, _dp(self.mesh.Vp)))
+            if self.dist:   # this rank's vertices only; done() assembles the global mesh
+                self._check(self.L.mmadmm_get_x_local(self.h, _dp(self.mesh.Vp)))
+            else:
+                self._check(self.L.mmadmm_get_x(self.h, _dp(self.mesh.Vp)))
         return Ih.value
+
+    def local_sizes(self):
+        p, e = C.c_int(), C.c_int()
+        self._check(self.L.mmadmm_local_sizes(self.h, C.byref(p), C.byref(e)))
+        return p.value, e.value
 
     def getEnergy(self):
         v = C.c_double()

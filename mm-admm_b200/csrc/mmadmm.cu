@@ -21,8 +21,11 @@
 #include <string>
 #include <vector>
 
+#include <dlfcn.h>
+
 #include "../../include/mmadmm.h"
 #include "mmadmm_device.cuh"
+#include "partition.h"
 
 using namespace mmadmm;
 
@@ -126,16 +129,22 @@ __global__ void k_fill(size_t n, double *p, double v) {
     size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n) p[i] = v;
 }
+__global__ void k_scatter_owned(int P, int D, const int *verts, const uint8_t *owner, const double *x, double *xg) {
+    int p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= P || !owner[p]) return;
+    for (int l = 0; l < D; l++) xg[(size_t)verts[p] * D + l] = x[(size_t)p * D + l];
+}
+__global__ void k_status_to_double(const unsigned *st, double *out) { *out = (double)*st; }
 __global__ void k_count_keys(size_t n, const int *keys, int *cnt) {
     size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n) atomicAdd(&cnt[keys[i]], 1);
 }
 // diag(t) = tau + dt^2 * sum_{valence} (w*w)*1.0     (src/MeshIntegrator.cpp:45-51)
-__global__ void k_tdiag(int P, const int *incPtr, double m, double dtsq, double w, double *tdiag) {
+__global__ void k_tdiag(int P, const int *incPtr, const int *valence, double m, double dtsq, double w, double *tdiag) {
     int p = blockIdx.x * blockDim.x + threadIdx.x;
     if (p >= P) return;
     double s = 0.0;
-    int cnt = incPtr[p + 1] - incPtr[p];
+    int cnt = valence ? valence[p] : (incPtr[p + 1] - incPtr[p]);   // distributed: the GLOBAL valence
     for (int k = 0; k < cnt; k++) s += (w * w) * 1.0;
     tdiag[p] = m + dtsq * s;
 }
@@ -782,7 +791,7 @@ template <int D, bool ZSRC, bool UZERO, bool PRIMAL>
 __global__ void __launch_bounds__(TPB_V) k_xupdate(int P, size_t Es, const int *incPtr, const int *incIdx, const double *z,
                                                    const double *u, const double *zsrc, const double *xBar,
                                                    const double *tdiag, double m, double dtsq, double w, double *x,
-                                                   double *partPrimal) {
+                                                   double *partPrimal, const int *sharedSlot, double *sPart) {
     __shared__ double red[32];
     int p = blockIdx.x * TPB_V + threadIdx.x;
     double prim = 0.0;
@@ -816,13 +825,18 @@ __global__ void __launch_bounds__(TPB_V) k_xupdate(int P, size_t Es, const int *
                     for (int l = 0; l < D; l++) s[l] += w * (w * (zv[j][l] - uv[j][l]));
                 }
         }
+        const int sh = sharedSlot ? sharedSlot[p] : -1;
+        if (sh >= 0) {   // shared with another rank: only the partial sum is known here (finished by k_xfinish)
+#pragma unroll
+            for (int l = 0; l < D; l++) sPart[(size_t)sh * D + l] = s[l];
+        }
         double td = tdiag[p];
 #pragma unroll
         for (int l = 0; l < D; l++) {
             xn[l] = ((m * xBar[(size_t)D * p + l]) + dtsq * s[l]) / td;
-            x[(size_t)D * p + l] = xn[l];
+            if (sh < 0) x[(size_t)D * p + l] = xn[l];
         }
-        if (PRIMAL) {   // second pass over the (L1-resident) slots: differences, not expanded squares
+        if (PRIMAL && sh < 0) {   // second pass over the (L1-resident) slots: differences, not expanded squares
             for (int k = k0; k < k1; k++) {
                 int slot = __ldg(incIdx + k);
                 size_t e = (size_t)(slot >> 2);
@@ -842,11 +856,63 @@ __global__ void __launch_bounds__(TPB_V) k_xupdate(int P, size_t Es, const int *
     }
 }
 
+// Distributed x-update, shared vertices: x from the exchanged total, and their share of ||D x - z||^2 over the LOCAL slots
+template <int D, bool ZSRC, bool PRIMAL>
+__global__ void __launch_bounds__(TPB_V) k_xfinish(int nShared, const int *sharedIdx, const double *sTot, size_t Es, const int *incPtr,
+                                                   const int *incIdx, const double *z, const double *zsrc, const double *xBar,
+                                                   const double *tdiag, double m, double dtsq, double *x, double *partPrimal) {
+    __shared__ double red[32];
+    const int i = blockIdx.x * TPB_V + threadIdx.x;
+    double prim = 0.0;
+    if (i < nShared) {
+        const int p = sharedIdx[i];
+        const double td = tdiag[p];
+        double xn[D];
+#pragma unroll
+        for (int l = 0; l < D; l++) {
+            xn[l] = ((m * xBar[(size_t)D * p + l]) + dtsq * sTot[(size_t)i * D + l]) / td;
+            x[(size_t)D * p + l] = xn[l];
+        }
+        if (PRIMAL) {
+            for (int k = incPtr[p]; k < incPtr[p + 1]; k++) {
+                const int slot = __ldg(incIdx + k);
+                const size_t e = (size_t)(slot >> 2);
+                const int v = slot & 3;
+#pragma unroll
+                for (int l = 0; l < D; l++) {
+                    const double zv = ZSRC ? zsrc[(size_t)D * p + l] : __ldg(z + (size_t)(D * v + l) * Es + e);
+                    const double df = xn[l] - zv;
+                    prim += df * df;
+                }
+            }
+        }
+    }
+    if (PRIMAL) {
+        double r = block_sum(prim, red);
+        if (threadIdx.x == 0) partPrimal[blockIdx.x] = r;
+    }
+}
+// Distributed predictor, shared vertices: xBar = x - (dt/tau) * (exchanged gradient total)
+template <int D>
+__global__ void k_predict_finish(int nShared, const int *sharedIdx, const double *sTot, double dtOverTau, const double *x,
+                                 double *xBar, double *xPrev) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= nShared) return;
+    const int p = sharedIdx[i];
+#pragma unroll
+    for (int l = 0; l < D; l++) {
+        const double xv = x[(size_t)D * p + l];
+        xBar[(size_t)D * p + l] = xv - dtOverTau * sTot[(size_t)i * D + l];
+        xPrev[(size_t)D * p + l] = xv;
+    }
+}
+
 // K6b: grad = sum of element gradients (ascending element order, as the reference's serial loop accumulates);
 // xBar = x - (dt/tau)*grad ; xPrev = x     (src/Mesh.cpp:649-674, src/MeshIntegrator.cpp:119)
 template <int D>
 __global__ void __launch_bounds__(TPB_V) k_predict_grad(int P, size_t Es, const int *incPtr, const int *incIdx, const double *gs,
-                                                        double dtOverTau, const double *x, double *xBar, double *xPrev) {
+                                                        double dtOverTau, const double *x, double *xBar, double *xPrev,
+                                                        const int *sharedSlot, double *sPart) {
     int p = blockIdx.x * TPB_V + threadIdx.x;
     if (p >= P) return;
     double s[D];
@@ -859,6 +925,12 @@ __global__ void __launch_bounds__(TPB_V) k_predict_grad(int P, size_t Es, const 
         int v = slot & 3;
 #pragma unroll
         for (int l = 0; l < D; l++) s[l] += __ldg(gs + (size_t)(D * v + l) * Es + e);
+    }
+    const int sh = sharedSlot ? sharedSlot[p] : -1;
+    if (sh >= 0) {
+#pragma unroll
+        for (int l = 0; l < D; l++) sPart[(size_t)sh * D + l] = s[l];
+        return;
     }
 #pragma unroll
     for (int l = 0; l < D; l++) {
@@ -935,6 +1007,17 @@ struct mmadmm_ctx {
     int D = 0, n = 0, P = 0, E = 0, device = 0;
     size_t Es = 0;               // element-plane stride
     int proxVariant = 0;
+    // ---- distributed (element-block partition, one process per GPU) ----
+    bool dist = false;
+    int rank = 0, nranks = 1, Pglobal = 0, Eglobal = 0;
+    void *comm = nullptr;                       // ncclComm_t
+    int nShared = 0, nNbrItems = 0, nblkSh = 0;
+    std::vector<int> nbrRank, nbrPtr;           // host copies of the plan's neighbour segments
+    int *sharedIdx = nullptr, *sharedSlot = nullptr, *nbrList = nullptr, *contribPtr = nullptr, *contrib = nullptr, *verts = nullptr;
+    uint8_t *owner = nullptr;
+    double *xloc_h = nullptr;
+    std::vector<int> verts_h;
+    double *sPart = nullptr, *sTot = nullptr, *sendBuf = nullptr, *recvBuf = nullptr, *scalAll_d = nullptr, *scalAll_h = nullptr;
     int nProxPart = 0;           // number of per-block (or per-warp) partial sums the last prox launch wrote
     int numSMs = 148;
     ProxMaps maps;
@@ -1020,6 +1103,133 @@ namespace {
 
 inline int cdiv(size_t a, size_t b) { return (int)((a + b - 1) / b); }
 
+// ---- NCCL, loaded at run time (single-GPU use of this library needs no NCCL at all) ----
+struct NcclApi {
+    bool ok = false;
+    int (*getUniqueId)(void *) = nullptr;
+    void *commInitRank = nullptr;
+    int (*commDestroy)(void *) = nullptr;
+    int (*groupStart)() = nullptr;
+    int (*groupEnd)() = nullptr;
+    int (*send)(const void *, size_t, int, int, void *, cudaStream_t) = nullptr;
+    int (*recv)(void *, size_t, int, int, void *, cudaStream_t) = nullptr;
+    int (*allGather)(const void *, void *, size_t, int, void *, cudaStream_t) = nullptr;
+    int (*allReduce)(const void *, void *, size_t, int, int, void *, cudaStream_t) = nullptr;
+    const char *(*getErrorString)(int) = nullptr;
+};
+struct NcclIdBlob { char b[128]; };
+constexpr int NCCL_FLOAT64 = 8, NCCL_SUM = 0;   // ncclDataType_t / ncclRedOp_t values (nccl.h)
+
+NcclApi &nccl() {
+    static NcclApi api;
+    static bool tried = false;
+    if (tried) return api;
+    tried = true;
+    const char *cands[] = {"libnccl.so.2", "/opt/prime-rl/.venv/lib/python3.12/site-packages/nvidia/nccl/lib/libnccl.so.2", "libnccl.so"};
+    void *h = nullptr;
+    for (const char *c : cands) {
+        h = dlopen(c, RTLD_NOW | RTLD_GLOBAL);
+        if (h) break;
+    }
+    if (!h) return api;
+    api.getUniqueId = (int (*)(void *))dlsym(h, "ncclGetUniqueId");
+    api.commInitRank = dlsym(h, "ncclCommInitRank");
+    api.commDestroy = (int (*)(void *))dlsym(h, "ncclCommDestroy");
+    api.groupStart = (int (*)())dlsym(h, "ncclGroupStart");
+    api.groupEnd = (int (*)())dlsym(h, "ncclGroupEnd");
+    api.send = (int (*)(const void *, size_t, int, int, void *, cudaStream_t))dlsym(h, "ncclSend");
+    api.recv = (int (*)(void *, size_t, int, int, void *, cudaStream_t))dlsym(h, "ncclRecv");
+    api.allGather = (int (*)(const void *, void *, size_t, int, void *, cudaStream_t))dlsym(h, "ncclAllGather");
+    api.allReduce = (int (*)(const void *, void *, size_t, int, int, void *, cudaStream_t))dlsym(h, "ncclAllReduce");
+    api.getErrorString = (const char *(*)(int))dlsym(h, "ncclGetErrorString");
+    api.ok = api.getUniqueId && api.commInitRank && api.commDestroy && api.groupStart && api.groupEnd && api.send && api.recv &&
+             api.allGather && api.allReduce;
+    return api;
+}
+
+#define NK(call)                                                                                       \
+    do {                                                                                               \
+        int _r = (call);                                                                               \
+        if (_r != 0) {                                                                                 \
+            char _b[512];                                                                              \
+            snprintf(_b, sizeof(_b), "%s:%d: %s -> NCCL error %d (%s)", __FILE__, __LINE__, #call, _r, \
+                     nccl().getErrorString ? nccl().getErrorString(_r) : "?");                         \
+            ctx->err = _b;                                                                             \
+            return MMADMM_ENCCL;                                                                       \
+        }                                                                                              \
+    } while (0)
+
+// ---- shared-vertex partial-sum exchange (see partition.h) ----
+template <int D> __global__ void k_halo_pack(int nItems, const int *nbrList, const double *sPart, double *sendBuf) {
+    int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= nItems) return;
+    const int i = nbrList[j];
+#pragma unroll
+    for (int l = 0; l < D; l++) sendBuf[(size_t)j * D + l] = sPart[(size_t)i * D + l];
+}
+// total = sum of the sharers' partials in ascending rank order (identical on every sharer)
+template <int D>
+__global__ void k_halo_combine(int nShared, const int *contribPtr, const int *contrib, const double *sPart, const double *recvBuf,
+                               double *sTot) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= nShared) return;
+    double s[D];
+#pragma unroll
+    for (int l = 0; l < D; l++) s[l] = 0.0;
+    for (int k = contribPtr[i]; k < contribPtr[i + 1]; k++) {
+        const int c = contrib[k];
+        const double *src = (c < 0) ? (sPart + (size_t)i * D) : (recvBuf + (size_t)c * D);
+#pragma unroll
+        for (int l = 0; l < D; l++) s[l] += src[l];
+    }
+#pragma unroll
+    for (int l = 0; l < D; l++) sTot[(size_t)i * D + l] = s[l];
+}
+
+// sPart (partials of the shared vertices) -> sTot (totals), over NCCL point-to-point
+template <int D> int halo_exchange(mmadmm_ctx *ctx) {
+    if (!ctx->dist || ctx->nShared == 0) return MMADMM_OK;
+    cudaStream_t st = ctx->stream;
+    k_halo_pack<D><<<cdiv(ctx->nNbrItems, 256), 256, 0, st>>>(ctx->nNbrItems, ctx->nbrList, ctx->sPart, ctx->sendBuf);
+    NcclApi &N = nccl();
+    NK(N.groupStart());
+    for (size_t q = 0; q < ctx->nbrRank.size(); q++) {
+        const size_t off = (size_t)ctx->nbrPtr[q] * D, cnt = (size_t)(ctx->nbrPtr[q + 1] - ctx->nbrPtr[q]) * D;
+        NK(N.send(ctx->sendBuf + off, cnt, NCCL_FLOAT64, ctx->nbrRank[q], ctx->comm, st));
+        NK(N.recv(ctx->recvBuf + off, cnt, NCCL_FLOAT64, ctx->nbrRank[q], ctx->comm, st));
+    }
+    NK(N.groupEnd());
+    k_halo_combine<D><<<cdiv(ctx->nShared, 256), 256, 0, st>>>(ctx->nShared, ctx->contribPtr, ctx->contrib, ctx->sPart, ctx->recvBuf,
+                                                               ctx->sTot);
+    ctx->launches += 2;
+    return MMADMM_OK;
+}
+
+// The three residual scalars (+ the status word) of every rank, summed on the host in rank order: the break decision
+// of the ADMM loop is then identical on all ranks (src/MeshIntegrator.cpp:162-169).
+int gather_scalars(mmadmm_ctx *ctx, int nScal) {
+    cudaStream_t st = ctx->stream;
+    if (!ctx->dist) {
+        CK(cudaMemcpyAsync(ctx->scal_h, ctx->scal_d, sizeof(double) * nScal, cudaMemcpyDeviceToHost, st));
+        CK(cudaMemcpyAsync(ctx->status_h, ctx->status_d, sizeof(unsigned), cudaMemcpyDeviceToHost, st));
+        CK(cudaStreamSynchronize(st));
+        return MMADMM_OK;
+    }
+    k_status_to_double<<<1, 1, 0, st>>>(ctx->status_d, ctx->scal_d + 4);
+    NK(nccl().allGather(ctx->scal_d, ctx->scalAll_d, 5, NCCL_FLOAT64, ctx->comm, st));
+    CK(cudaMemcpyAsync(ctx->scalAll_h, ctx->scalAll_d, sizeof(double) * 5 * ctx->nranks, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    unsigned stat = 0;
+    for (int k = 0; k < 4; k++) ctx->scal_h[k] = 0.0;
+    for (int r = 0; r < ctx->nranks; r++) {
+        for (int k = 0; k < 4; k++) ctx->scal_h[k] += ctx->scalAll_h[5 * r + k];
+        stat |= (unsigned)ctx->scalAll_h[5 * r + 4];
+    }
+    *ctx->status_h = stat;
+    ctx->launches += 1;
+    return MMADMM_OK;
+}
+
 // Tensor map over `planes` planes of `Es` doubles (plane stride Es): box = [planes][boxElems] (whole tile in one TMA op).
 // cuTensorMapEncodeTiled is fetched through the runtime so that libcuda is not a link-time dependency.
 bool encode_plane_map(CUtensorMap *map, double *base, size_t Es, int planes, int boxElems) {
@@ -1073,10 +1283,13 @@ int build_csr(mmadmm_ctx *ctx, size_t nItems, int nKeys, int *keys, int *vals, i
     return MMADMM_OK;
 }
 
-template <int D> int build_monitor_grid(mmadmm_ctx *ctx, const double *VpHost, const double *monVertexHost) {
+// VpHost / monVertexHost: the P vertices the grid is built from (the GLOBAL mesh on a distributed context)
+template <int D> int build_monitor_grid(mmadmm_ctx *ctx, int P, const double *VpHost, const double *monVertexHost) {
     cudaStream_t st = ctx->stream;
-    const int P = ctx->P;
     constexpr int DD = D * D;
+    double *xg = nullptr;
+    CK(cudaMalloc(&xg, sizeof(double) * (size_t)P * D));
+    CK(cudaMemcpyAsync(xg, VpHost, sizeof(double) * (size_t)P * D, cudaMemcpyHostToDevice, st));
     // MeshInterpolator::updateMesh (src/MeshInterpolator.cpp:67-130): grid size, bounding box, axes (host, init only)
     ctx->nx = (int)std::pow((double)((size_t)P * D), 1.0 / D);
     ctx->ny = ctx->nx;
@@ -1130,14 +1343,14 @@ template <int D> int build_monitor_grid(mmadmm_ctx *ctx, const double *VpHost, c
     int *bin = nullptr, *ids = nullptr, *binStart = nullptr, *items = nullptr;
     CK(cudaMalloc(&bin, sizeof(int) * (size_t)P));
     CK(cudaMalloc(&ids, sizeof(int) * (size_t)P));
-    k_bin_ids<D><<<cdiv(P, 256), 256, 0, st>>>(P, ctx->x, bg, bin, ids);
+    k_bin_ids<D><<<cdiv(P, 256), 256, 0, st>>>(P, xg, bg, bin, ids);
     int rc = build_csr(ctx, (size_t)P, (int)nbins, bin, ids, &binStart, &items);
     if (rc) return rc;
     ctx->gridO[0] = hx[0]; ctx->gridO[1] = hy[0]; ctx->gridO[2] = hz[0];
     ctx->gridRh[0] = 1.0 / (hx[1] - hx[0]); ctx->gridRh[1] = 1.0 / (hy[1] - hy[0]);
     ctx->gridRh[2] = (D == 3) ? 1.0 / (hz[1] - hz[0]) : 0.0;
     MonGrid mg = ctx->monGrid();
-    k_nn_grid<D><<<cdiv(ctx->gridRows, 128), 128, 0, st>>>(mg, ctx->grid, ctx->x, monV, bg, binStart, items);
+    k_nn_grid<D><<<cdiv(ctx->gridRows, 128), 128, 0, st>>>(mg, ctx->grid, xg, monV, bg, binStart, items);
     int nSmooth = (D == 2) ? 5 : 2;  // src/MeshInterpolator.cpp:246-252
     for (int it = 0; it < nSmooth; it++) {
         CK(cudaMemcpyAsync(gridTmp, ctx->grid, sizeof(double) * ctx->gridRows * RS, cudaMemcpyDeviceToDevice, st));
@@ -1146,12 +1359,20 @@ template <int D> int build_monitor_grid(mmadmm_ctx *ctx, const double *VpHost, c
     ctx->launches += 2 + nSmooth;
     CK(cudaStreamSynchronize(st));
     CK(cudaGetLastError());
-    cudaFree(gridTmp); cudaFree(monV); cudaFree(bin); cudaFree(ids); cudaFree(binStart); cudaFree(items);
+    cudaFree(gridTmp); cudaFree(monV); cudaFree(bin); cudaFree(ids); cudaFree(binStart); cudaFree(items); cudaFree(xg);
     return MMADMM_OK;
 }
 
+// Quantities that differ from the local mesh on a distributed context (null / equal to the local ones otherwise)
+struct InitGlobals {
+    int Eglobal;                 // element count in the reference-simplex scaling (AdaptationFunctional.cpp:190-200)
+    const int *valence;          // global valence of the local vertices (diagonal of t), or null
+    int Pgrid;                   // vertices the monitor grid is built from
+    const double *VpGrid, *monGrid;
+};
+
 template <int D>
-int create_impl(mmadmm_ctx *ctx, const double *Vp, const double *Vc, const int *F, const int *mask, const double *monVertex) {
+int create_impl(mmadmm_ctx *ctx, const double *Vp, const double *Vc, const int *F, const int *mask, const InitGlobals &G) {
     constexpr int n = D * (D + 1);
     const int P = ctx->P, E = ctx->E;
     cudaStream_t st = ctx->stream;
@@ -1210,17 +1431,24 @@ int create_impl(mmadmm_ctx *ctx, const double *Vp, const double *Vc, const int *
             det = Eh[0][0] * (Eh[1][1] * Eh[2][2] - Eh[1][2] * Eh[2][1]) - Eh[0][1] * (Eh[1][0] * Eh[2][2] - Eh[1][2] * Eh[2][0]) +
                   Eh[0][2] * (Eh[1][0] * Eh[2][1] - Eh[1][1] * Eh[2][0]);
         double s1 = std::pow((dFact / std::fabs(det)), 1.0 / ((double)D));
-        double s2 = (double)std::pow(E, 1.0 / D);
+        double s2 = (double)std::pow(G.Eglobal, 1.0 / D);
         for (int a = 0; a < D; a++)
             for (int b = 0; b < D; b++) { double v = Eh[a][b]; v *= s1; v /= s2; ctx->Ehat[a * D + b] = v; }
         ctx->dpow = std::pow((double)D, (double)D * 1.5 / 2.0);
     }
     ctx->w = 0.5 * std::sqrt(ctx->rho);  // src/Mesh.cpp:451 (the JSON "w" is ignored by the reference)
     ctx->m = ctx->tau;
-    k_tdiag<<<cdiv(P, 256), 256, 0, st>>>(P, ctx->incPtr, ctx->m, ctx->dt * ctx->dt, ctx->w, ctx->tdiag);
+    int *valence_d = nullptr;
+    if (G.valence) {
+        CK(cudaMalloc(&valence_d, sizeof(int) * (size_t)P));
+        CK(cudaMemcpyAsync(valence_d, G.valence, sizeof(int) * (size_t)P, cudaMemcpyHostToDevice, st));
+    }
+    k_tdiag<<<cdiv(P, 256), 256, 0, st>>>(P, ctx->incPtr, valence_d, ctx->m, ctx->dt * ctx->dt, ctx->w, ctx->tdiag);
+    CK(cudaStreamSynchronize(st));
+    cudaFree(valence_d);
     ctx->launches++;
 
-    rc = build_monitor_grid<D>(ctx, Vp, monVertex);
+    rc = build_monitor_grid<D>(ctx, G.Pgrid, G.VpGrid, G.monGrid);
     if (rc) return rc;
 
     // element state: z = D x, u = 0, hessInvs = I
@@ -1244,9 +1472,10 @@ int create_impl(mmadmm_ctx *ctx, const double *Vp, const double *Vc, const int *
     ctx->nblkProx = std::max(cdiv(E, 32), 148 * 64);   // upper bound over the prox tile sizes / persistent warps
     CK(cudaMalloc(&ctx->partIh, sizeof(double) * ctx->nblkProx));
     CK(cudaMalloc(&ctx->partDual, sizeof(double) * ctx->nblkProx));
-    CK(cudaMalloc(&ctx->partPrimal, sizeof(double) * std::max(ctx->nblkE, ctx->nblkV)));
-    CK(cudaMalloc(&ctx->scal_d, sizeof(double) * 4));
-    CK(cudaMallocHost(&ctx->scal_h, sizeof(double) * 4));
+    CK(cudaMalloc(&ctx->partPrimal, sizeof(double) * (size_t)(std::max(ctx->nblkE, ctx->nblkV) + ctx->nblkV + 1)));
+    CK(cudaMalloc(&ctx->scal_d, sizeof(double) * 8));
+    CK(cudaMemsetAsync(ctx->scal_d, 0, sizeof(double) * 8, st));
+    CK(cudaMallocHost(&ctx->scal_h, sizeof(double) * 8));
     CK(cudaMalloc(&ctx->status_d, sizeof(unsigned)));
     CK(cudaMallocHost(&ctx->status_h, sizeof(unsigned)));
     CK(cudaMemsetAsync(ctx->status_d, 0, sizeof(unsigned), st));
@@ -1318,12 +1547,23 @@ template <> int launch_prox<3>(mmadmm_ctx *ctx, const ElemArgs<3> &a) {
     }
 }
 
+// x-update (+ primal residual partials).  Distributed: local kernel -> shared-vertex partials -> exchange -> k_xfinish.
 template <int D, bool ZSRC, bool UZERO, bool PRIMAL>
-void launch_xupdate_t(mmadmm_ctx *ctx, const double *zsrc) {
+int launch_xupdate_t(mmadmm_ctx *ctx, const double *zsrc) {
+    const double dtsq = ctx->dt * ctx->dt;
     k_xupdate<D, ZSRC, UZERO, PRIMAL><<<ctx->nblkV, TPB_V, 0, ctx->stream>>>(
-        ctx->P, ctx->Es, ctx->incPtr, ctx->incIdx, ctx->z, ctx->u, zsrc, ctx->xBar, ctx->tdiag, ctx->m, ctx->dt * ctx->dt, ctx->w,
-        ctx->x, ctx->partPrimal);
+        ctx->P, ctx->Es, ctx->incPtr, ctx->incIdx, ctx->z, ctx->u, zsrc, ctx->xBar, ctx->tdiag, ctx->m, dtsq, ctx->w, ctx->x,
+        ctx->partPrimal, ctx->dist ? ctx->sharedSlot : nullptr, ctx->sPart);
     ctx->launches++;
+    if (ctx->dist && ctx->nShared > 0) {
+        int rc = halo_exchange<D>(ctx);
+        if (rc) return rc;
+        k_xfinish<D, ZSRC, PRIMAL><<<ctx->nblkSh, TPB_V, 0, ctx->stream>>>(ctx->nShared, ctx->sharedIdx, ctx->sTot, ctx->Es, ctx->incPtr,
+                                                                          ctx->incIdx, ctx->z, zsrc, ctx->xBar, ctx->tdiag, ctx->m, dtsq,
+                                                                          ctx->x, ctx->partPrimal + ctx->nblkV);
+        ctx->launches++;
+    }
+    return MMADMM_OK;
 }
 
 template <int D> int step_impl(mmadmm_ctx *ctx, int nIters, double tol, double *IhOut, int *itersOut, double *primalOut, double *dualOut) {
@@ -1337,8 +1577,16 @@ template <int D> int step_impl(mmadmm_ctx *ctx, int nIters, double tol, double *
     ctx->phaseBegin(0);
     if (ctx->gradUse || ctx->stepsTaken <= 2) {
         k_euler_elem<D><<<gE, TPB, 0, st>>>(a, ctx->gs);
-        k_predict_grad<D><<<gV, TPB_V, 0, st>>>(P, ctx->Es, ctx->incPtr, ctx->incIdx, ctx->gs, ctx->dt / ctx->tau, ctx->x, ctx->xBar, ctx->xPrev);
+        k_predict_grad<D><<<gV, TPB_V, 0, st>>>(P, ctx->Es, ctx->incPtr, ctx->incIdx, ctx->gs, ctx->dt / ctx->tau, ctx->x, ctx->xBar,
+                                                ctx->xPrev, ctx->dist ? ctx->sharedSlot : nullptr, ctx->sPart);
         ctx->launches += 2;
+        if (ctx->dist && ctx->nShared > 0) {   // assembled gradient of the shared vertices
+            int rcx = halo_exchange<D>(ctx);
+            if (rcx) return rcx;
+            k_predict_finish<D><<<cdiv(ctx->nShared, 256), 256, 0, st>>>(ctx->nShared, ctx->sharedIdx, ctx->sTot, ctx->dt / ctx->tau, ctx->x,
+                                                                         ctx->xBar, ctx->xPrev);
+            ctx->launches++;
+        }
     } else {
         k_predict_extrap<<<cdiv(NV, TPB_V), TPB_V, 0, st>>>(NV, ctx->x, ctx->xBar, ctx->xPrev);
         ctx->launches += 1;
@@ -1350,8 +1598,10 @@ template <int D> int step_impl(mmadmm_ctx *ctx, int nIters, double tol, double *
     const bool uZero = !ctx->stepTaken;
     // first x-solve (:137-138)
     ctx->phaseBegin(2);
-    if (uZero) launch_xupdate_t<D, true, true, false>(ctx, zsrc);
-    else launch_xupdate_t<D, true, false, false>(ctx, zsrc);
+    {
+        int rcx = uZero ? launch_xupdate_t<D, true, true, false>(ctx, zsrc) : launch_xupdate_t<D, true, false, false>(ctx, zsrc);
+        if (rcx) return rcx;
+    }
     ctx->phaseEnd();
 
     double Ihstart = 0, primal = 0, dual = 0;
@@ -1372,19 +1622,22 @@ template <int D> int step_impl(mmadmm_ctx *ctx, int nIters, double tol, double *
         ctx->hessComputed = true;
         ctx->stepTaken = true;
         ctx->phaseBegin(2);
-        launch_xupdate_t<D, false, false, true>(ctx, nullptr);
+        {
+            int rcx = launch_xupdate_t<D, false, false, true>(ctx, nullptr);
+            if (rcx) return rcx;
+        }
         ctx->phaseEnd();
         ctx->phaseBegin(3);
         const int nbp = ctx->nProxPart;
-        k_finalize<<<1, 1024, 0, st>>>(nbp, ctx->partIh, gV, ctx->partPrimal, nbp, ctx->partDual, ctx->scal_d);
-        CK(cudaMemcpyAsync(ctx->scal_h, ctx->scal_d, sizeof(double) * 3, cudaMemcpyDeviceToHost, st));
-        CK(cudaMemcpyAsync(ctx->status_h, ctx->status_d, sizeof(unsigned), cudaMemcpyDeviceToHost, st));
-        ctx->phaseEnd();
+        k_finalize<<<1, 1024, 0, st>>>(nbp, ctx->partIh, gV + ((ctx->dist && ctx->nShared > 0) ? ctx->nblkSh : 0), ctx->partPrimal, nbp,
+                                       ctx->partDual, ctx->scal_d);
         ctx->launches += 1;
-        CK(cudaStreamSynchronize(st));
+        ctx->phaseEnd();
+        int rc = gather_scalars(ctx, 3);   // synchronises; sums over ranks on a distributed context
+        if (rc) return rc;
         ctx->admmIters++;
         ctx->proxCalls += (long long)ctx->E;
-        int rc = check_status(ctx);
+        rc = check_status(ctx);
         if (rc) return rc;
         if (i == 0) Ihstart = ctx->scal_h[0];
         primal = std::sqrt(ctx->scal_h[1]);
@@ -1408,9 +1661,8 @@ template <int D> int energy_impl(mmadmm_ctx *ctx, double *I) {
     k_finalize<<<1, 1024, 0, st>>>(ctx->nblkE, ctx->partPrimal, 0, nullptr, 0, nullptr, ctx->scal_d + 3);
     ctx->launches += 2;
     // k_finalize writes out[0] of its `out` argument => scal_d[3]
-    CK(cudaMemcpyAsync(ctx->scal_h + 3, ctx->scal_d + 3, sizeof(double), cudaMemcpyDeviceToHost, st));
-    CK(cudaMemcpyAsync(ctx->status_h, ctx->status_d, sizeof(unsigned), cudaMemcpyDeviceToHost, st));
-    CK(cudaStreamSynchronize(st));
+    int rcg = gather_scalars(ctx, 4);
+    if (rcg) return rcg;
     CK(cudaGetLastError());
     *I = ctx->scal_h[3];
     return check_status(ctx);
@@ -1441,8 +1693,106 @@ int mmadmm_create(int D, int P, int E, const double *Vp, const double *Vc, const
     CK(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
     for (size_t p = 0; p < (size_t)E * (D + 1); p++)
         if (F[p] < 0 || F[p] >= P) { ctx->err = "connectivity index out of range"; return MMADMM_EINVAL; }
-    int rc = (D == 2) ? create_impl<2>(ctx, Vp, Vc, F, mask, monVertex) : create_impl<3>(ctx, Vp, Vc, F, mask, monVertex);
+    InitGlobals G{E, nullptr, P, Vp, monVertex};
+    int rc = (D == 2) ? create_impl<2>(ctx, Vp, Vc, F, mask, G) : create_impl<3>(ctx, Vp, Vc, F, mask, G);
     return rc;
+}
+
+int mmadmm_comm_unique_id(void *id128) {
+    if (!id128) return MMADMM_EINVAL;
+    NcclApi &N = nccl();
+    if (!N.ok) return MMADMM_ENCCL;
+    NcclIdBlob id;
+    memset(&id, 0, sizeof(id));
+    if (N.getUniqueId(&id) != 0) return MMADMM_ENCCL;
+    memcpy(id128, &id, sizeof(id));
+    return MMADMM_OK;
+}
+
+int mmadmm_create_dist(int D, int P, int E, const double *Vp, const double *Vc, const int *F, const int *mask,
+                       const double *monVertex, double rho, double tau, double dt, int gradUse, int device, int rank, int nranks,
+                       const void *id128, mmadmm_ctx **out) {
+    if (!out) return MMADMM_EINVAL;
+    *out = nullptr;
+    if ((D != 2 && D != 3) || P <= 0 || E <= 0 || !Vp || !F || !mask || !monVertex || nranks < 1 || rank < 0 || rank >= nranks)
+        return MMADMM_EINVAL;
+    if (nranks == 1) return mmadmm_create(D, P, E, Vp, Vc, F, mask, monVertex, rho, tau, dt, gradUse, device, out);
+    if (!id128) return MMADMM_EINVAL;
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) return MMADMM_ENODEVICE;
+    mmadmm_ctx *ctx = new mmadmm_ctx();
+    *out = ctx;
+    NcclApi &N = nccl();
+    if (!N.ok) { ctx->err = "libnccl.so.2 could not be loaded"; return MMADMM_ENCCL; }
+    PartitionPlan plan;
+    if (!build_partition_plan(D, P, E, F, nranks, rank, plan)) { ctx->err = "bad mesh or partition arguments"; return MMADMM_EINVAL; }
+    const int Pl = (int)plan.verts.size(), El = plan.e1 - plan.e0;
+    if (El <= 0) { ctx->err = "empty element block: more ranks than 128-element tiles"; return MMADMM_EINVAL; }
+    ctx->D = D; ctx->n = D * (D + 1); ctx->P = Pl; ctx->E = El; ctx->device = device;
+    ctx->Pglobal = P; ctx->Eglobal = E; ctx->rank = rank; ctx->nranks = nranks; ctx->dist = true;
+    ctx->compMesh = (Vc != nullptr); ctx->gradUse = gradUse != 0;
+    ctx->rho = rho; ctx->tau = tau; ctx->dt = dt;
+    CK(cudaSetDevice(device));
+    CK(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
+    cudaStream_t st = ctx->stream;
+    {   // communicator: ncclCommInitRank(&comm, nranks, id (by value), rank)
+        typedef int (*InitFn)(void **, int, NcclIdBlob, int);
+        NcclIdBlob id;
+        memcpy(&id, id128, sizeof(id));
+        NK(((InitFn)N.commInitRank)(&ctx->comm, nranks, id, rank));
+    }
+    // local mesh
+    std::vector<double> VpL((size_t)Pl * D), VcL;
+    std::vector<int> maskL((size_t)Pl);
+    if (Vc) VcL.resize((size_t)Pl * D);
+    for (int l = 0; l < Pl; l++) {
+        const int g = plan.verts[l];
+        for (int k = 0; k < D; k++) {
+            VpL[(size_t)l * D + k] = Vp[(size_t)g * D + k];
+            if (Vc) VcL[(size_t)l * D + k] = Vc[(size_t)g * D + k];
+        }
+        maskL[l] = mask[g];
+    }
+    // halo structures
+    ctx->nShared = (int)plan.shared.size();
+    ctx->nNbrItems = (int)plan.nbrList.size();
+    ctx->nbrRank = plan.nbrRank;
+    ctx->nbrPtr = plan.nbrPtr;
+    auto upload = [&](int **dst, const std::vector<int> &v) -> cudaError_t {
+        cudaError_t e = cudaMalloc(dst, sizeof(int) * std::max<size_t>(v.size(), 1));
+        if (e != cudaSuccess) return e;
+        return cudaMemcpyAsync(*dst, v.data(), sizeof(int) * v.size(), cudaMemcpyHostToDevice, st);
+    };
+    std::vector<int> slot((size_t)Pl, -1);
+    for (int i = 0; i < ctx->nShared; i++) slot[plan.shared[i]] = i;
+    CK(upload(&ctx->sharedIdx, plan.shared));
+    CK(upload(&ctx->sharedSlot, slot));
+    CK(upload(&ctx->nbrList, plan.nbrList));
+    CK(upload(&ctx->contribPtr, plan.contribPtr));
+    CK(upload(&ctx->contrib, plan.contrib));
+    CK(upload(&ctx->verts, plan.verts));
+    CK(cudaMalloc(&ctx->owner, std::max<size_t>(Pl, 1)));
+    CK(cudaMemcpyAsync(ctx->owner, plan.owner.data(), (size_t)Pl, cudaMemcpyHostToDevice, st));
+    const size_t shD = (size_t)std::max(ctx->nShared, 1) * D, nbD = (size_t)std::max(ctx->nNbrItems, 1) * D;
+    CK(cudaMalloc(&ctx->sPart, sizeof(double) * shD));
+    CK(cudaMalloc(&ctx->sTot, sizeof(double) * shD));
+    CK(cudaMalloc(&ctx->sendBuf, sizeof(double) * nbD));
+    CK(cudaMalloc(&ctx->recvBuf, sizeof(double) * nbD));
+    CK(cudaMalloc(&ctx->scalAll_d, sizeof(double) * 5 * nranks));
+    CK(cudaMallocHost(&ctx->scalAll_h, sizeof(double) * 5 * nranks));
+    ctx->nblkSh = cdiv(std::max(ctx->nShared, 1), TPB_V);
+    CK(cudaStreamSynchronize(st));
+    InitGlobals G{E, plan.valence.data(), P, Vp, monVertex};
+    int rc = (D == 2) ? create_impl<2>(ctx, VpL.data(), Vc ? VcL.data() : nullptr, plan.Floc.data(), maskL.data(), G)
+                      : create_impl<3>(ctx, VpL.data(), Vc ? VcL.data() : nullptr, plan.Floc.data(), maskL.data(), G);
+    return rc;
+}
+
+int mmadmm_local_sizes(mmadmm_ctx *ctx, int *Ploc, int *Eloc) {
+    if (!ctx) return MMADMM_EINVAL;
+    if (Ploc) *Ploc = ctx->P;
+    if (Eloc) *Eloc = ctx->E;
+    return MMADMM_OK;
 }
 
 int mmadmm_step(mmadmm_ctx *ctx, int nIters, double tol, double *Ih, int *itersTaken, double *primal, double *dual) {
@@ -1460,8 +1810,38 @@ int mmadmm_energy(mmadmm_ctx *ctx, double *I) {
 
 int mmadmm_get_x(mmadmm_ctx *ctx, double *x) {
     if (!ctx || !x) return MMADMM_EINVAL;
-    CK(cudaMemcpyAsync(x, ctx->x, sizeof(double) * (size_t)ctx->P * ctx->D, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaSetDevice(ctx->device));
+    if (!ctx->dist) {
+        CK(cudaMemcpyAsync(x, ctx->x, sizeof(double) * (size_t)ctx->P * ctx->D, cudaMemcpyDeviceToHost, ctx->stream));
+        CK(cudaStreamSynchronize(ctx->stream));
+        return MMADMM_OK;
+    }
+    // every rank contributes the vertices it owns (lowest rank holding them); zeros elsewhere; sum == assembly
+    const size_t NG = (size_t)ctx->Pglobal * ctx->D;
+    double *xg = nullptr;
+    CK(cudaMalloc(&xg, sizeof(double) * NG));
+    CK(cudaMemsetAsync(xg, 0, sizeof(double) * NG, ctx->stream));
+    k_scatter_owned<<<cdiv((size_t)ctx->P, 256), 256, 0, ctx->stream>>>(ctx->P, ctx->D, ctx->verts, ctx->owner, ctx->x, xg);
+    ctx->launches++;
+    NK(nccl().allReduce(xg, xg, NG, NCCL_FLOAT64, NCCL_SUM, ctx->comm, ctx->stream));
+    CK(cudaMemcpyAsync(x, xg, sizeof(double) * NG, cudaMemcpyDeviceToHost, ctx->stream));
     CK(cudaStreamSynchronize(ctx->stream));
+    CK(cudaFree(xg));
+    return MMADMM_OK;
+}
+int mmadmm_get_x_local(mmadmm_ctx *ctx, double *xGlobal) {
+    if (!ctx || !xGlobal) return MMADMM_EINVAL;
+    if (!ctx->dist) return mmadmm_get_x(ctx, xGlobal);
+    const int D = ctx->D;
+    if (!ctx->xloc_h) {
+        CK(cudaMallocHost(&ctx->xloc_h, sizeof(double) * (size_t)ctx->P * D));
+        ctx->verts_h.resize(ctx->P);
+        CK(cudaMemcpy(ctx->verts_h.data(), ctx->verts, sizeof(int) * (size_t)ctx->P, cudaMemcpyDeviceToHost));
+    }
+    CK(cudaMemcpyAsync(ctx->xloc_h, ctx->x, sizeof(double) * (size_t)ctx->P * D, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    for (int l = 0; l < ctx->P; l++)
+        for (int k = 0; k < D; k++) xGlobal[(size_t)ctx->verts_h[l] * D + k] = ctx->xloc_h[(size_t)l * D + k];
     return MMADMM_OK;
 }
 int mmadmm_get_x_device(mmadmm_ctx *ctx, double *x_dev) {
@@ -1616,6 +1996,12 @@ void mmadmm_destroy(mmadmm_ctx *ctx) {
     cudaFree(ctx->status_d);
     if (ctx->status_h) cudaFreeHost(ctx->status_h);
     cudaFree(ctx->hist_d);
+    cudaFree(ctx->sharedIdx); cudaFree(ctx->sharedSlot); cudaFree(ctx->nbrList); cudaFree(ctx->contribPtr); cudaFree(ctx->contrib);
+    cudaFree(ctx->verts); cudaFree(ctx->owner); cudaFree(ctx->sPart); cudaFree(ctx->sTot); cudaFree(ctx->sendBuf); cudaFree(ctx->recvBuf);
+    cudaFree(ctx->scalAll_d);
+    if (ctx->scalAll_h) cudaFreeHost(ctx->scalAll_h);
+    if (ctx->xloc_h) cudaFreeHost(ctx->xloc_h);
+    if (ctx->comm && nccl().ok) nccl().commDestroy(ctx->comm);
     for (auto e : ctx->evPool) cudaEventDestroy(e);
     if (ctx->stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
