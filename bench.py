@@ -170,11 +170,23 @@ def main():
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
-    if world > 1:
-        raise SystemExit("multi-GPU element-block partition is not wired into bench.py yet (see DESIGN.md, multi-GPU)")
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a CUDA device: mm-admm_b200 has no CPU fallback")
     torch.cuda.set_device(local)
+    dist = None
+    if world > 1:   # one process per GPU (torchrun); torch.distributed is plumbing only: id broadcast, barrier, max-over-ranks
+        import torch.distributed as dist
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    def new_comm():
+        if world == 1:
+            return None
+        t = torch.zeros(128, dtype=torch.uint8, device="cuda")
+        if rank == 0:
+            t.copy_(torch.frombuffer(bytearray(mm.comm_unique_id()), dtype=torch.uint8))
+        dist.broadcast(t, 0)
+        return (rank, world, bytes(t.cpu().numpy().tobytes()))
     W = min(max(args.warmup, 3), 6)
     K = args.steps
     wl = workload(args.gpus, args.workload)
@@ -195,7 +207,7 @@ def main():
         mesh = mm.Mesh(vp_pinned.numpy(), F.copy(), mask, mon, rho=PARAMS["rho"], tau=PARAMS["tau"])
         mesh.Vp = vp_pinned.numpy()
         t0 = time.perf_counter()
-        solver = mm.MeshIntegrator(PARAMS["dt"], mesh, device=local, sync_vp=False)
+        solver = mm.MeshIntegrator(PARAMS["dt"], mesh, device=local, sync_vp=False, comm=new_comm())
         state["init_s"] = time.perf_counter() - t0
         if args.prox_variant >= 0:
             solver.set_option("prox_variant", args.prox_variant)
@@ -229,6 +241,9 @@ def main():
             st0 = solver.stats()
             ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             torch.cuda.synchronize()
+            if dist:
+                dist.barrier()
+                torch.cuda.synchronize()
             sampler = ClockSampler(local)
             ev0.record(stream)
             for _ in range(kk):
@@ -236,8 +251,16 @@ def main():
                 tot["iters"] += solver.last["iters"]
             ev1.record(stream)
             torch.cuda.synchronize()
+            if dist:
+                dist.barrier()
+                torch.cuda.synchronize()
             tot["clocks"].append(sampler.stop())
-            tot["ms"] += ev0.elapsed_time(ev1)
+            ms = ev0.elapsed_time(ev1)
+            if dist:   # device time, max over ranks
+                tms = torch.tensor([ms], dtype=torch.float64, device="cuda")
+                dist.all_reduce(tms, op=dist.ReduceOp.MAX)
+                ms = float(tms.item())
+            tot["ms"] += ms
             st1 = solver.stats()
             tot["launches"] += st1["kernel_launches"] - st0["kernel_launches"]
             tot["hist"] = tot["hist"] + (st1["bfgs_hist"] - st0["bfgs_hist"])
@@ -259,11 +282,17 @@ def main():
     solver = state["solver"]
     g = solver.grid_dims()[0]
     init_s, e0, warm = state["init_s"], state["e0"], state["warm"]
+    launches = r["launches"]
+    Ploc, Eloc = solver.local_sizes()
+    if dist:
+        tl = torch.tensor([launches], dtype=torch.int64, device="cuda")
+        dist.all_reduce(tl)
+        launches = int(tl.item())
     value = E * r["iters"] / (r["ms"] / 1e3)
     e2e = E * r2["iters"] / (r2["ms"] / 1e3)
     prox_ms, prox_cnt = r["timing"]["prox"]
     peak, peak_src = peaks()
-    bytes_per_launch = algorithmic_bytes_prox(D, P, E, g) * E
+    bytes_per_launch = algorithmic_bytes_prox(D, P, E, g) * Eloc   # this rank's launch (rank 0 reports)
     achieved = bytes_per_launch / (prox_ms / max(prox_cnt, 1) / 1e3) / 1e9
     hist = r["hist"]
     kbar = float((hist * np.arange(52)).sum() / max(hist.sum(), 1))
@@ -271,16 +300,19 @@ def main():
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": K, "warmup": W,
         "ms_per_step": r["ms"] / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
         "data": "synthetic",
-        "config": {"workload": wl["label"], "elements": E, "points": P, "monitor_grid": g, "l2": "inputs_exceed_L2 "
+        "config": {"workload": wl["label"], "elements": E, "points": P, "monitor_grid": g,
+                   "parallelism": (f"element-block partition over {world} GPUs, one process per GPU; NCCL send/recv halo sums of "
+                                   f"shared-vertex partials + 5-double all-gather per ADMM iteration; rank 0 holds {Eloc:,} elements")
+                   if world > 1 else "single GPU", "l2": "inputs_exceed_L2 "
                    f"(element state {8 * E * (D * (D + 1)) * (D * (D + 1) + 2) / 1e9:.2f} GB >> 126 MB L2)",
                    "timed_steps": f"{K} steady-state outer steps in {r['epochs']} epoch(s) of <= {SAFE} (outer steps {W}..{W + min(SAFE, K) - 1} after a "
                    f"fresh start; the reference algorithm itself breaks down at outer step ~12 on this workload, see DESIGN.md)"},
         "steps_per_sec": K / (r["ms"] / 1e3), "admm_iters_per_sec": r["iters"] / (r["ms"] / 1e3),
         "admm_iters": r["iters"], "mean_bfgs_iters_per_element_prox": kbar,
-        "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": P * D * 8 + 32,
+        "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": Ploc * D * 8 + 32,
                 "ms_per_step": r2["ms"] / K, "note": "MeshIntegrator.step incl. per-step write-back of Vp to pinned host memory; "
                 "the step takes no array inputs after construction (state is device-resident), scalars only"},
-        "gpu_launches": r["launches"],
+        "gpu_launches": launches,
         "roofline": {"kernel": "k_prox", "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                      "traffic": None, "peak_source": peak_src, "algorithmic_bytes_per_launch": bytes_per_launch,
                      "avg_launch_ms": prox_ms / max(prox_cnt, 1), "launches_timed": prox_cnt},
@@ -297,6 +329,9 @@ def main():
     if rank == 0:
         print(json.dumps(line))
     solver.close()
+    if dist:
+        dist.barrier()
+        dist.destroy_process_group()
     return 0
 
 

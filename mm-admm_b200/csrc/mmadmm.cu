@@ -1017,6 +1017,7 @@ struct mmadmm_ctx {
     uint8_t *owner = nullptr;
     double *xloc_h = nullptr;
     std::vector<int> verts_h;
+    std::vector<std::pair<int, int>> runs;   // (first local vertex, length) of consecutive global ids
     double *sPart = nullptr, *sTot = nullptr, *sendBuf = nullptr, *recvBuf = nullptr, *scalAll_d = nullptr, *scalAll_h = nullptr;
     int nProxPart = 0;           // number of per-block (or per-warp) partial sums the last prox launch wrote
     int numSMs = 148;
@@ -1833,11 +1834,24 @@ int mmadmm_get_x_local(mmadmm_ctx *ctx, double *xGlobal) {
     if (!ctx || !xGlobal) return MMADMM_EINVAL;
     if (!ctx->dist) return mmadmm_get_x(ctx, xGlobal);
     const int D = ctx->D;
-    if (!ctx->xloc_h) {
-        CK(cudaMallocHost(&ctx->xloc_h, sizeof(double) * (size_t)ctx->P * D));
+    if (ctx->verts_h.empty()) {   // runs of consecutive global ids (a strip / slab partition has two or three)
         ctx->verts_h.resize(ctx->P);
         CK(cudaMemcpy(ctx->verts_h.data(), ctx->verts, sizeof(int) * (size_t)ctx->P, cudaMemcpyDeviceToHost));
+        for (int l = 0; l < ctx->P;) {
+            int m = l + 1;
+            while (m < ctx->P && ctx->verts_h[m] == ctx->verts_h[m - 1] + 1) m++;
+            ctx->runs.push_back({l, m - l});
+            l = m;
+        }
     }
+    if (ctx->runs.size() <= 64) {   // straight into the caller's array, one copy per run
+        for (auto &r : ctx->runs)
+            CK(cudaMemcpyAsync(xGlobal + (size_t)ctx->verts_h[r.first] * D, ctx->x + (size_t)r.first * D,
+                               sizeof(double) * (size_t)r.second * D, cudaMemcpyDeviceToHost, ctx->stream));
+        CK(cudaStreamSynchronize(ctx->stream));
+        return MMADMM_OK;
+    }
+    if (!ctx->xloc_h) CK(cudaMallocHost(&ctx->xloc_h, sizeof(double) * (size_t)ctx->P * D));
     CK(cudaMemcpyAsync(ctx->xloc_h, ctx->x, sizeof(double) * (size_t)ctx->P * D, cudaMemcpyDeviceToHost, ctx->stream));
     CK(cudaStreamSynchronize(ctx->stream));
     for (int l = 0; l < ctx->P; l++)
