@@ -57,42 +57,49 @@ def peaks():
 
 
 class ClockSampler:
-    Q = "clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
-        "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+    """SM clock + throttle reasons sampled through NVML every ~2 ms DURING the timed region (the region is a few
+    milliseconds long, far below nvidia-smi's polling period), in a background thread."""
+    REASONS = {0x8: "hw_slowdown", 0x40: "hw_thermal_slowdown", 0x20: "sw_thermal_slowdown", 0x4: "sw_power_cap"}
 
     def __init__(self, index=0):
-        self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
+        import threading
+        self.sm, self.mask, self.max_mhz, self.stop_flag = [], 0, None, False
         try:
-            self.p = subprocess.Popen(["nvidia-smi", "-i", str(index), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
-                                       "-lms", "100"], stdout=self.f, stderr=subprocess.DEVNULL)
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = float(pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM))
         except Exception:
-            self.p = None
+            self.nv = None
+            return
+        self._sample()
+        self.t = threading.Thread(target=self._run, daemon=True)
+        self.t.start()
+
+    def _sample(self):
+        try:
+            self.sm.append(float(self.nv.nvmlDeviceGetClockInfo(self.h, self.nv.NVML_CLOCK_SM)))
+            self.mask |= int(self.nv.nvmlDeviceGetCurrentClocksEventReasons(self.h))
+        except Exception:
+            pass
+
+    def _run(self):
+        while not self.stop_flag:
+            self._sample()
+            time.sleep(0.002)
 
     def stop(self):
-        out = dict(sm_mhz=None, sm_max_mhz=None, reasons=[])
-        if self.p is None:
+        out = dict(sm_mhz=None, sm_max_mhz=self.max_mhz, reasons=[], samples=0)
+        if self.nv is None:
             return out
-        self.p.terminate()
-        try:
-            self.p.wait(timeout=5)
-        except Exception:
-            self.p.kill()
-        self.f.flush()
-        rows = [r.split(",") for r in open(self.f.name).read().strip().split("\n") if r.strip()]
-        os.unlink(self.f.name)
-        sm, reasons = [], set()
-        for r in rows:
-            try:
-                sm.append(float(r[0])); out["sm_max_mhz"] = float(r[1])
-            except Exception:
-                continue
-            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[3:7]):
-                if v.strip().lower().startswith("active"):
-                    reasons.add(name)
-        if sm:
-            out["sm_mhz"] = statistics.median(sm)
-        out["reasons"] = sorted(reasons)
-        out["samples"] = len(sm)
+        self.stop_flag = True
+        self.t.join(timeout=2)
+        self._sample()
+        if self.sm:
+            out["sm_mhz"] = statistics.median(self.sm)
+        out["reasons"] = sorted(v for k, v in self.REASONS.items() if self.mask & k)
+        out["samples"] = len(self.sm)
         return out
 
 
