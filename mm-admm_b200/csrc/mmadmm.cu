@@ -9,7 +9,6 @@
 //               K5         ||D x - z||^2 partials in the same pass;  k_finalize reduces the three scalars in a fixed order
 // Element state is SoA over elements (component-major planes of length E) so every warp access is
 // one contiguous 256-byte line.
-#include <cuda.h>
 #include <cuda_runtime.h>
 #include <cub/cub.cuh>
 
@@ -125,9 +124,10 @@ template <int D> __global__ void k_inc_pairs(int E, const int *F0, const int *F1
         vals[(size_t)e * (D + 1) + v] = e * 4 + v;
     }
 }
-__global__ void k_fill(size_t n, double *p, double v) {
-    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < n) p[i] = v;
+__global__ void k_fill_identity(size_t Es, int n, double *B) {
+    size_t e = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= Es) return;
+    for (int k = 0; k < n; k++) B[tm_index(e, k * n + k, n * n)] = 1.0;
 }
 __global__ void k_scatter_owned(int P, int D, const int *verts, const uint8_t *owner, const double *x, double *xg) {
     int p = blockIdx.x * blockDim.x + threadIdx.x;
@@ -329,14 +329,14 @@ __device__ __forceinline__ void load_z_dx(const ElemArgs<D> &a, int e, const int
     for (int v = 0; v < D + 1; v++) gather_vertex<D>(a.x, vid[v], dx + D * v);
     if (!a.uZero) {
 #pragma unroll
-        for (int k = 0; k < n; k++) dx[k] += a.u[k * a.Es + e];
+        for (int k = 0; k < n; k++) dx[k] += a.u[tm_index(e, k, n)];
     }
     if (a.zsrc) {
 #pragma unroll
         for (int v = 0; v < D + 1; v++) gather_vertex<D>(a.zsrc, vid[v], z + D * v);
     } else {
 #pragma unroll
-        for (int k = 0; k < n; k++) z[k] = a.z[k * a.Es + e];
+        for (int k = 0; k < n; k++) z[k] = a.z[tm_index(e, k, n)];
     }
 }
 
@@ -403,7 +403,7 @@ template <int D> __global__ void __launch_bounds__(TPB) k_hess_init(ElemArgs<D> 
             for (int j = i + 1; j < n; j++) s -= H[i * n + j] * y[j];
             y[i] = s / H[i * n + i];
         }
-        for (int i = 0; i < n; i++) a.B[(size_t)(i * n + c) * a.Es + e] = y[i];
+        for (int i = 0; i < n; i++) a.B[tm_index(e, i * n + c, n * n)] = y[i];
     }
 }
 
@@ -418,7 +418,7 @@ __global__ void __launch_bounds__(TPB_, MINB) k_prox(ElemArgs<D> a) {
     constexpr int n = D * (D + 1);
     constexpr int NN = n * n;
     extern __shared__ __align__(128) unsigned char smem_raw[];
-    double *Bs = reinterpret_cast<double *>(smem_raw);                 // [NN][TPB_]
+    double *Bs = reinterpret_cast<double *>(smem_raw);                 // [TPB_/32 tiles][NN][32]
     uint64_t *bar = reinterpret_cast<uint64_t *>(Bs + (size_t)NN * TPB_);
     double *red = reinterpret_cast<double *>(bar + 2);                 // 32 doubles
     int *shist = reinterpret_cast<int *>(red + 32);                    // 52 ints
@@ -428,10 +428,8 @@ __global__ void __launch_bounds__(TPB_, MINB) k_prox(ElemArgs<D> a) {
     if (a.hist && tid < 52) shist[tid] = 0;
     __syncthreads();
     if (tid == 0) mbar_expect_tx(bar, (unsigned)(NN * TPB_ * sizeof(double)));
-    if (tid < 32) {
-        for (int k = tid; k < NN; k += 32)
-            bulk_g2s(Bs + (size_t)k * TPB_, a.B + (size_t)k * a.Es + e0, (unsigned)(TPB_ * sizeof(double)), bar);
-    }
+    if (tid < TPB_ / TILE)   // one contiguous block per 32-element tile
+        bulk_g2s(Bs + (size_t)tid * NN * TILE, a.B + (e0 / TILE + tid) * NN * TILE, (unsigned)(NN * TILE * sizeof(double)), bar);
     const int e = (int)e0 + tid;
     double ih = 0.0, dual2 = 0.0;
     const bool active = e < a.E;
@@ -451,8 +449,8 @@ __global__ void __launch_bounds__(TPB_, MINB) k_prox(ElemArgs<D> a) {
     }
     mbar_wait(bar, 0);
     if (active) {
-        double *Bt = Bs + tid;
-#define BS(k) Bt[(k) * TPB_]
+        double *Bt = Bs + (size_t)(tid >> 5) * NN * TILE + (tid & 31);
+#define BS(k) Bt[(k) * TILE]
         double dz[n];
 #pragma unroll
         for (int k = 0; k < n; k++) dz[k] = 0.0;
@@ -512,8 +510,8 @@ __global__ void __launch_bounds__(TPB_, MINB) k_prox(ElemArgs<D> a) {
         if (a.hist) atomicAdd(&shist[(iter == 50) ? 51 : iter + 1], 1);
 #pragma unroll
         for (int k = 0; k < n; k++) {
-            a.z[k * a.Es + e] = z[k];
-            a.u[k * a.Es + e] = dx[k] - z[k];    // u = DXpU - z
+            a.z[tm_index(e, k, n)] = z[k];
+            a.u[tm_index(e, k, n)] = dx[k] - z[k];    // u = DXpU - z
             const double d = z[k] - dz[k];
             dual2 += d * d;
         }
@@ -521,9 +519,8 @@ __global__ void __launch_bounds__(TPB_, MINB) k_prox(ElemArgs<D> a) {
     // updated tile back to HBM: generic-proxy writes -> async proxy, then bulk stores
     fence_async_smem();
     __syncthreads();
-    if (tid < 32) {
-        for (int k = tid; k < NN; k += 32)
-            bulk_s2g(a.B + (size_t)k * a.Es + e0, Bs + (size_t)k * TPB_, (unsigned)(TPB_ * sizeof(double)));
+    if (tid < TPB_ / TILE) {
+        bulk_s2g(a.B + (e0 / TILE + tid) * NN * TILE, Bs + (size_t)tid * NN * TILE, (unsigned)(NN * TILE * sizeof(double)));
         bulk_commit();
     }
     double s1 = block_sum(ih, red);
@@ -533,7 +530,7 @@ __global__ void __launch_bounds__(TPB_, MINB) k_prox(ElemArgs<D> a) {
         __syncthreads();
         if (tid < 52 && shist[tid]) atomicAdd(&a.hist[tid], (unsigned long long)shist[tid]);
     }
-    if (tid < 32) bulk_wait_read0();   // shared memory must stay allocated until the bulk stores have read it
+    if (tid < TPB_ / TILE) bulk_wait_read0();   // shared memory must stay allocated until the bulk stores have read it
 }
 
 // Persistent, software-pipelined form of the warp-tile prox kernel (the default for D = 2).  One warp walks tiles
@@ -542,8 +539,6 @@ __global__ void __launch_bounds__(TPB_, MINB) k_prox(ElemArgs<D> a) {
 // cp.async (LDGSTS, no registers held), the u / z planes by one tensor-map TMA each; the connectivity of tile t+2 is
 // loaded into three registers.  The inverse-Hessian tile itself is single-buffered: its TMA load is issued as soon as
 // the previous tile's TMA store has drained and is covered by the entry-gradient evaluation.
-struct ProxMaps { CUtensorMap B, u, z; };
-
 template <int D> __device__ __forceinline__ void gather_async(double *dst /* [D+1][32][D] */, const double *src, const int *vid, int lane) {
 #pragma unroll
     for (int v = 0; v < D + 1; v++) {
@@ -555,7 +550,7 @@ template <int D> __device__ __forceinline__ void gather_async(double *dst /* [D+
 }
 
 template <int D, int WPB, int MINB, bool COMP, int FLAGS>
-__global__ void __launch_bounds__(WPB * 32, MINB) k_prox_p(const __grid_constant__ ElemArgs<D> a, const __grid_constant__ ProxMaps maps) {
+__global__ void __launch_bounds__(WPB * 32, MINB) k_prox_p(const __grid_constant__ ElemArgs<D> a) {
     constexpr int n = D * (D + 1);
     constexpr int NN = n * n;
     constexpr int SLOTS = COMP ? 4 : 3;                 // per buffer: xg | u->DXpU | z (planes or gathered) | xi
@@ -586,8 +581,8 @@ __global__ void __launch_bounds__(WPB * 32, MINB) k_prox_p(const __grid_constant
         if (COMP) gather_async<D>(b + 3 * n * 32, a.Vc, vid, lane);
         if (lane == 0 && smallBytes) {
             mbar_expect_tx(&bars[buf], smallBytes);
-            if (haveU) tma_load_2d(b + n * 32, &maps.u, tile * 32, 0, &bars[buf]);
-            if (haveZ) tma_load_2d(b + 2 * n * 32, &maps.z, tile * 32, 0, &bars[buf]);
+            if (haveU) bulk_g2s(b + n * 32, a.u + (size_t)tile * n * TILE, (unsigned)(n * TILE * sizeof(double)), &bars[buf]);
+            if (haveZ) bulk_g2s(b + 2 * n * 32, a.z + (size_t)tile * n * TILE, (unsigned)(n * TILE * sizeof(double)), &bars[buf]);
         }
     };
 
@@ -656,7 +651,7 @@ __global__ void __launch_bounds__(WPB * 32, MINB) k_prox_p(const __grid_constant
             // this tile's inverse Hessians, once the previous tile's store has drained out of shared memory
             bulk_wait_read0();
             mbar_expect_tx(barB, (unsigned)(NN * 32 * sizeof(double)));
-            tma_load_2d(Bs, &maps.B, t * 32, 0, barB);
+            bulk_g2s(Bs, a.B + (size_t)t * NN * TILE, (unsigned)(NN * TILE * sizeof(double)), barB);
         }
         if (active) ih = prox_grad_s<D>(z, dxs, xi, COMP, a.mg, a.fc, fb, Gk, inv);   // Ihsave: energy at entry
         mbar_wait(barB, (unsigned)(it & 1));
@@ -714,8 +709,8 @@ __global__ void __launch_bounds__(WPB * 32, MINB) k_prox_p(const __grid_constant
             double dual2 = 0.0;
 #pragma unroll
             for (int k = 0; k < n; k++) {
-                a.z[k * a.Es + e] = z[k];
-                a.u[k * a.Es + e] = dxs[k * 32] - z[k];    // u = DXpU - z
+                a.z[((size_t)t * n + k) * TILE + lane] = z[k];
+                a.u[((size_t)t * n + k) * TILE + lane] = dxs[k * 32] - z[k];    // u = DXpU - z
                 const double d = z[k] - zs[k * 32 + lane];
                 dual2 += d * d;
             }
@@ -731,7 +726,7 @@ __global__ void __launch_bounds__(WPB * 32, MINB) k_prox_p(const __grid_constant
         fence_async_smem();
         __syncwarp();
         if (lane == 0) {
-            tma_store_2d(&maps.B, t * 32, 0, Bs);
+            bulk_s2g(a.B + (size_t)t * NN * TILE, Bs, (unsigned)(NN * TILE * sizeof(double)));
             bulk_commit();
         }
         if (tn < nTiles && (FLAGS & PF_PREFETCH_GRID)) {
@@ -766,7 +761,7 @@ template <int D> __global__ void __launch_bounds__(TPB) k_applyD(ElemArgs<D> a, 
         double p[D];
         gather_vertex<D>(src, vid[v], p);
 #pragma unroll
-        for (int l = 0; l < D; l++) a.z[(size_t)(D * v + l) * a.Es + e] = p[l];
+        for (int l = 0; l < D; l++) a.z[tm_index(e, D * v + l, D * (D + 1))] = p[l];
     }
 }
 
@@ -822,7 +817,7 @@ __global__ void __launch_bounds__(TPB_V) k_xupdate(int P, size_t Es, const int *
                 const int v = slot[j] & 3;
 #pragma unroll
                 for (int l = 0; l < D; l++) {
-                    const size_t idx = (size_t)(D * v + l) * Es + e;
+                    const size_t idx = tm_index(e, D * v + l, D * (D + 1));
                     zv[j][l] = (ZSRC || slot[j] < 0) ? zs[l] : __ldg(z + idx);
                     uv[j][l] = (UZERO || slot[j] < 0) ? 0.0 : __ldg(u + idx);
                 }
@@ -852,7 +847,7 @@ __global__ void __launch_bounds__(TPB_V) k_xupdate(int P, size_t Es, const int *
                 int v = slot & 3;
 #pragma unroll
                 for (int l = 0; l < D; l++) {
-                    double zv = ZSRC ? zs[l] : __ldg(z + (size_t)(D * v + l) * Es + e);
+                    double zv = ZSRC ? zs[l] : __ldg(z + tm_index(e, D * v + l, D * (D + 1)));
                     double df = xn[l] - zv;
                     prim += df * df;
                 }
@@ -889,7 +884,7 @@ __global__ void __launch_bounds__(TPB_V) k_xfinish(int nShared, const int *share
                 const int v = slot & 3;
 #pragma unroll
                 for (int l = 0; l < D; l++) {
-                    const double zv = ZSRC ? zsrc[(size_t)D * p + l] : __ldg(z + (size_t)(D * v + l) * Es + e);
+                    const double zv = ZSRC ? zsrc[(size_t)D * p + l] : __ldg(z + tm_index(e, D * v + l, D * (D + 1)));
                     const double df = xn[l] - zv;
                     prim += df * df;
                 }
@@ -1031,8 +1026,6 @@ struct mmadmm_ctx {
     double *sPart = nullptr, *sTot = nullptr, *sendBuf = nullptr, *recvBuf = nullptr, *scalAll_d = nullptr, *scalAll_h = nullptr;
     int nProxPart = 0;           // number of per-block (or per-warp) partial sums the last prox launch wrote
     int numSMs = 148;
-    ProxMaps maps;
-    bool haveMaps = false;
     bool smemAttrSet[8] = {false, false, false, false, false, false, false, false};
     bool compMesh = false, gradUse = false;
     cudaStream_t stream = nullptr;
@@ -1239,27 +1232,6 @@ int gather_scalars(mmadmm_ctx *ctx, int nScal) {
     *ctx->status_h = stat;
     ctx->launches += 1;
     return MMADMM_OK;
-}
-
-// Tensor map over `planes` planes of `Es` doubles (plane stride Es): box = [planes][boxElems] (whole tile in one TMA op).
-// cuTensorMapEncodeTiled is fetched through the runtime so that libcuda is not a link-time dependency.
-bool encode_plane_map(CUtensorMap *map, double *base, size_t Es, int planes, int boxElems) {
-    typedef CUresult (*EncodeFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *, const cuuint64_t *,
-                                 const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave, CUtensorMapSwizzle,
-                                 CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
-    static EncodeFn fn = nullptr;
-    if (!fn) {
-        void *p = nullptr;
-        cudaDriverEntryPointQueryResult q;
-        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess || !p) return false;
-        fn = (EncodeFn)p;
-    }
-    cuuint64_t dims[2] = {(cuuint64_t)Es, (cuuint64_t)planes};
-    cuuint64_t strides[1] = {(cuuint64_t)Es * sizeof(double)};
-    cuuint32_t box[2] = {(cuuint32_t)boxElems, (cuuint32_t)planes};
-    cuuint32_t estr[2] = {1, 1};
-    return fn(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 2, base, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-              CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 
 // CSR by key: sorted vals (stable => ascending input order inside a key) and ptr[nkeys+1]
@@ -1480,14 +1452,9 @@ int create_impl(mmadmm_ctx *ctx, const double *Vp, const double *Vc, const int *
     CK(cudaMemsetAsync(ctx->z, 0, sizeof(double) * NZ, st));
     CK(cudaMemsetAsync(ctx->u, 0, sizeof(double) * NZ, st));
     CK(cudaMemsetAsync(ctx->B, 0, sizeof(double) * NZ * n, st));
-    for (int k = 0; k < n; k++) {
-        k_fill<<<cdiv(ctx->Es, 256), 256, 0, st>>>(ctx->Es, ctx->B + (size_t)(k * n + k) * ctx->Es, 1.0);
-        ctx->launches++;
-    }
+    k_fill_identity<<<cdiv(ctx->Es, 256), 256, 0, st>>>(ctx->Es, n, ctx->B);   // hessInvs = I (src/Mesh.cpp:456-464)
+    ctx->launches++;
     CK(cudaDeviceGetAttribute(&ctx->numSMs, cudaDevAttrMultiProcessorCount, ctx->device));
-    ctx->haveMaps = encode_plane_map(&ctx->maps.B, ctx->B, ctx->Es, n * n, 32) &&
-                    encode_plane_map(&ctx->maps.u, ctx->u, ctx->Es, n, 32) &&
-                    encode_plane_map(&ctx->maps.z, ctx->z, ctx->Es, n, 32);
     ctx->nblkE = cdiv(E, TPB);
     ctx->nblkV = cdiv(P, TPB_V);
     ctx->nblkProx = std::max(cdiv(E, 32), 148 * 64);   // upper bound over the prox tile sizes / persistent warps
@@ -1538,7 +1505,6 @@ template <int D, int TPB_, int MINB> int launch_prox_t(mmadmm_ctx *ctx, const El
 template <int D> int launch_prox(mmadmm_ctx *ctx, const ElemArgs<D> &a);
 template <int D, int WPB, int MINB, int FLAGS> int launch_prox_p(mmadmm_ctx *ctx, const ElemArgs<D> &a, int slot) {
     constexpr int n = D * (D + 1);
-    if (!ctx->haveMaps) { ctx->err = "tensor maps unavailable (cuTensorMapEncodeTiled)"; return MMADMM_ECUDA; }
     const size_t slots = ctx->compMesh ? 4 : 3;
     const size_t smem = sizeof(double) * (size_t)WPB * (n * n * 32 + 2 * slots * n * 32) + 32 * WPB;
     auto kern = ctx->compMesh ? k_prox_p<D, WPB, MINB, true, FLAGS> : k_prox_p<D, WPB, MINB, false, FLAGS>;
@@ -1547,7 +1513,7 @@ template <int D, int WPB, int MINB, int FLAGS> int launch_prox_p(mmadmm_ctx *ctx
         ctx->smemAttrSet[slot] = true;
     }
     const int grid = std::min(ctx->numSMs * MINB, cdiv(ctx->E, WPB * 32));
-    kern<<<grid, WPB * 32, smem, ctx->stream>>>(a, ctx->maps);
+    kern<<<grid, WPB * 32, smem, ctx->stream>>>(a);
     ctx->nProxPart = grid * WPB;
     ctx->launches++;
     return MMADMM_OK;
@@ -1910,11 +1876,10 @@ int mmadmm_get_state(mmadmm_ctx *ctx, int which, double *out) {
     if (which == MMADMM_STATE_Z || which == MMADMM_STATE_U || which == MMADMM_STATE_HESSINV) {
         int planes = (which == MMADMM_STATE_HESSINV) ? n * n : n;
         const double *src = (which == MMADMM_STATE_Z) ? ctx->z : (which == MMADMM_STATE_U) ? ctx->u : ctx->B;
-        std::vector<double> plane(E);
-        for (int k = 0; k < planes; k++) {
-            CK(cudaMemcpy(plane.data(), src + (size_t)k * ctx->Es, sizeof(double) * E, cudaMemcpyDeviceToHost));
-            for (size_t e = 0; e < E; e++) out[e * planes + k] = plane[e];
-        }
+        std::vector<double> tmp(ctx->Es * planes);   // tile-major on the device -> element-major for the caller
+        CK(cudaMemcpy(tmp.data(), src, sizeof(double) * tmp.size(), cudaMemcpyDeviceToHost));
+        for (size_t e = 0; e < E; e++)
+            for (int k = 0; k < planes; k++) out[e * planes + k] = tmp[tm_index(e, k, planes)];
         return MMADMM_OK;
     }
     if (which == MMADMM_STATE_XBAR || which == MMADMM_STATE_XPREV) {

@@ -13,6 +13,14 @@
 
 namespace mmadmm {
 
+// Element state (z, u, inverse Hessians) is stored TILE-MAJOR: [tile of 32 elements][row][32], so everything one warp
+// needs of a tile is one contiguous block (z, u: n*256 bytes; B: n*n*256 bytes) -- one TMA bulk copy each way, whole
+// DRAM pages, and all rows of an element sit within a few KB for the vertex-centric gathers of the x-update.
+constexpr int TILE = 32;
+__host__ __device__ __forceinline__ size_t tm_index(size_t e, int row, int rows) {
+    return ((e >> 5) * (size_t)rows + (size_t)row) * TILE + (e & 31);
+}
+
 enum NodeTypeDev { NT_BOUNDARY_FREE = 0, NT_BOUNDARY_FIXED = 1, NT_INTERIOR = 2 };  // src/NodeType.h:4-8
 enum StatusBits { ST_INVERTED = 1, ST_SINGULAR_HESS = 2, ST_BFGS_MAX = 4, ST_NONFINITE = 8 };
 
