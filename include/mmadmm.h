@@ -53,6 +53,11 @@ int mmadmm_create(int D, int P, int E, const double *Vp, const double *Vc, const
  * reference (sum of the un-regularised element energies at entry to the first prox sweep). */
 int mmadmm_step(mmadmm_ctx *ctx, int nIters, double tol, double *Ih, int *itersTaken, double *primal, double *dual);
 
+/* The time step belongs to MeshIntegrator<D>, not to Mesh<D> (src/MeshIntegrator.cpp:15-17,45-51): a host Mesh<D> may
+ * create the context before any integrator exists (dt = 0) and the integrator's constructor then sets dt, which
+ * rebuilds the diagonal of t = M + dt^2 (WD)^T(WD).  Must be called before the first mmadmm_step. */
+int mmadmm_set_dt(mmadmm_ctx *ctx, double dt);
+
 /* Replaces MeshIntegrator<D>::getEnergy -> Mesh::computeEnergy (src/Mesh.cpp:496-530). */
 int mmadmm_energy(mmadmm_ctx *ctx, double *I);
 
@@ -78,6 +83,9 @@ int mmadmm_eval_monitor(mmadmm_ctx *ctx, const double *pts, int npts, double *ou
  * (src/Mesh.cpp:755-772 -> src/AdaptationFunctional.cpp:102-287).  zs, dxpu: ne x n. grad/igt may be NULL. */
 int mmadmm_block_grad(mmadmm_ctx *ctx, int ne, const double *zs, const double *dxpu, int computeGrad, int regularize,
                       int applyMask, double *energy, double *grad, double *igt);
+/* Same on mesh elements e0 .. e0+ne-1 (zId of the reference's blockGrad); rows of zs/dxpu/energy/grad/igt are 0..ne-1. */
+int mmadmm_block_grad_at(mmadmm_ctx *ctx, int e0, int ne, const double *zs, const double *dxpu, int computeGrad,
+                         int regularize, int applyMask, double *energy, double *grad, double *igt);
 
 /* Statistics since creation: hist52[k] = number of element-prox solves that ran k BFGS iterations
  * (k = 51: hit the 50-iteration cap, the reference prints "MAX IN BFGS"); proxCalls = element-prox solves;

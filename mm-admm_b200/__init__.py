@@ -28,8 +28,8 @@ ERRORS = {1: "EINVAL", 2: "ECUDA", 3: "EINVERTED", 4: "ESINGULAR", 5: "ENCCL", 6
 
 # every symbol include/mmadmm.h declares (checked by tests/test_abi.py)
 ABI_SYMBOLS = [
-    "mmadmm_create", "mmadmm_step", "mmadmm_energy", "mmadmm_get_x", "mmadmm_get_x_device", "mmadmm_get_F",
-    "mmadmm_grid_dims", "mmadmm_get_state", "mmadmm_eval_monitor", "mmadmm_block_grad", "mmadmm_get_stats",
+    "mmadmm_create", "mmadmm_set_dt", "mmadmm_step", "mmadmm_energy", "mmadmm_get_x", "mmadmm_get_x_device", "mmadmm_get_F",
+    "mmadmm_grid_dims", "mmadmm_get_state", "mmadmm_eval_monitor", "mmadmm_block_grad", "mmadmm_block_grad_at", "mmadmm_get_stats",
     "mmadmm_get_timing", "mmadmm_set_option", "mmadmm_stream", "mmadmm_destroy", "mmadmm_last_error",
     "mmadmm_version", "mmadmm_plan_create", "mmadmm_plan_sizes", "mmadmm_plan_get", "mmadmm_plan_destroy",
     "mmadmm_comm_unique_id", "mmadmm_create_dist", "mmadmm_local_sizes", "mmadmm_get_x_local",
@@ -66,6 +66,7 @@ def lib():
                                     C.c_double, C.c_int, C.c_int, C.POINTER(vp)]
         L.mmadmm_step.argtypes = [vp, C.c_int, C.c_double, _c_dp, _c_ip, _c_dp, _c_dp]
         L.mmadmm_energy.argtypes = [vp, _c_dp]
+        L.mmadmm_set_dt.argtypes = [vp, C.c_double]
         L.mmadmm_get_x.argtypes = [vp, _c_dp]
         L.mmadmm_get_x_device.argtypes = [vp, vp]
         L.mmadmm_get_F.argtypes = [vp, _c_ip]
@@ -73,6 +74,7 @@ def lib():
         L.mmadmm_get_state.argtypes = [vp, C.c_int, _c_dp]
         L.mmadmm_eval_monitor.argtypes = [vp, _c_dp, C.c_int, _c_dp]
         L.mmadmm_block_grad.argtypes = [vp, C.c_int, _c_dp, _c_dp, C.c_int, C.c_int, C.c_int, _c_dp, _c_dp, _c_dp]
+        L.mmadmm_block_grad_at.argtypes = [vp, C.c_int, C.c_int, _c_dp, _c_dp, C.c_int, C.c_int, C.c_int, _c_dp, _c_dp, _c_dp]
         L.mmadmm_get_stats.argtypes = [vp, _c_llp, _c_llp, _c_llp, _c_llp]
         L.mmadmm_get_timing.argtypes = [vp, _c_dp, _c_llp, C.c_int]
         L.mmadmm_set_option.argtypes = [vp, C.c_char_p, C.c_int]

@@ -966,13 +966,13 @@ template <int D> __global__ void k_eval_monitor(MonGrid mg, int npts, const doub
     for (int k = 0; k < D * D; k++) out[(size_t)i * D * D + k] = m.a[k];
 }
 template <int D>
-__global__ void k_block_grad_dbg(ElemArgs<D> a, int ne, const double *zs, const double *dxpu, int computeGrad, int regularize,
-                                 int applyMask, double *energy, double *grad, double *igt) {
+__global__ void k_block_grad_dbg(ElemArgs<D> a, int e0, int ne, const double *zs, const double *dxpu, int computeGrad,
+                                 int regularize, int applyMask, double *energy, double *grad, double *igt) {
     constexpr int n = D * (D + 1);
-    int e = blockIdx.x * blockDim.x + threadIdx.x;
+    int e = blockIdx.x * blockDim.x + threadIdx.x;   // row of the caller's arrays; mesh element e0 + e
     if (e >= ne) return;
     int vid[D + 1];
-    load_elem_ids<D>(a, e, vid);
+    load_elem_ids<D>(a, e0 + e, vid);
     double z[n], xi[n], g[n], dx[n];
 #pragma unroll
     for (int k = 0; k < n; k++) { z[k] = zs[(size_t)e * n + k]; dx[k] = regularize ? dxpu[(size_t)e * n + k] : 0.0; g[k] = 0.0; }
@@ -988,7 +988,7 @@ __global__ void k_block_grad_dbg(ElemArgs<D> a, int ne, const double *zs, const 
         en += 0.5 * a.fc.w2 * sq;
     }
     if (applyMask) {
-        unsigned fb = a.fixedBits[e];
+        unsigned fb = a.fixedBits[e0 + e];
 #pragma unroll
         for (int v = 0; v < D + 1; v++)
             if (fb & (1u << v))
@@ -1033,7 +1033,7 @@ struct mmadmm_ctx {
     uint8_t *mask = nullptr, *fixedBits = nullptr, *nonIntBits = nullptr;
     double *x = nullptr, *xPrev = nullptr, *xBar = nullptr, *Vc = nullptr, *tdiag = nullptr;
     double *z = nullptr, *u = nullptr, *B = nullptr, *gs = nullptr;
-    int *incPtr = nullptr, *incIdx = nullptr, *vorder = nullptr;
+    int *incPtr = nullptr, *incIdx = nullptr, *vorder = nullptr, *valence_d = nullptr;
     double *grid = nullptr, *ax = nullptr, *ay = nullptr, *az = nullptr;
     int nx = 0, ny = 0, nz = 0;
     size_t gridRows = 0;
@@ -1431,14 +1431,12 @@ int create_impl(mmadmm_ctx *ctx, const double *Vp, const double *Vc, const int *
     }
     ctx->w = 0.5 * std::sqrt(ctx->rho);  // src/Mesh.cpp:451 (the JSON "w" is ignored by the reference)
     ctx->m = ctx->tau;
-    int *valence_d = nullptr;
-    if (G.valence) {
-        CK(cudaMalloc(&valence_d, sizeof(int) * (size_t)P));
-        CK(cudaMemcpyAsync(valence_d, G.valence, sizeof(int) * (size_t)P, cudaMemcpyHostToDevice, st));
+    if (G.valence) {   // kept: mmadmm_set_dt rebuilds the diagonal
+        CK(cudaMalloc(&ctx->valence_d, sizeof(int) * (size_t)P));
+        CK(cudaMemcpyAsync(ctx->valence_d, G.valence, sizeof(int) * (size_t)P, cudaMemcpyHostToDevice, st));
     }
-    k_tdiag<<<cdiv(P, 256), 256, 0, st>>>(P, ctx->incPtr, valence_d, ctx->m, ctx->dt * ctx->dt, ctx->w, ctx->tdiag);
+    k_tdiag<<<cdiv(P, 256), 256, 0, st>>>(P, ctx->incPtr, ctx->valence_d, ctx->m, ctx->dt * ctx->dt, ctx->w, ctx->tdiag);
     CK(cudaStreamSynchronize(st));
-    cudaFree(valence_d);
     ctx->launches++;
 
     rc = build_monitor_grid<D>(ctx, G.Pgrid, G.VpGrid, G.monGrid);
@@ -1782,6 +1780,16 @@ int mmadmm_local_sizes(mmadmm_ctx *ctx, int *Ploc, int *Eloc) {
     return MMADMM_OK;
 }
 
+int mmadmm_set_dt(mmadmm_ctx *ctx, double dt) {
+    if (!ctx || !(dt >= 0)) return MMADMM_EINVAL;
+    CK(cudaSetDevice(ctx->device));
+    ctx->dt = dt;
+    k_tdiag<<<cdiv(ctx->P, 256), 256, 0, ctx->stream>>>(ctx->P, ctx->incPtr, ctx->valence_d, ctx->m, dt * dt, ctx->w, ctx->tdiag);
+    ctx->launches++;
+    CK(cudaStreamSynchronize(ctx->stream));
+    return MMADMM_OK;
+}
+
 int mmadmm_step(mmadmm_ctx *ctx, int nIters, double tol, double *Ih, int *itersTaken, double *primal, double *dual) {
     if (!ctx) return MMADMM_EINVAL;
     CK(cudaSetDevice(ctx->device));
@@ -1917,7 +1925,13 @@ int mmadmm_eval_monitor(mmadmm_ctx *ctx, const double *pts, int npts, double *ou
 
 int mmadmm_block_grad(mmadmm_ctx *ctx, int ne, const double *zs, const double *dxpu, int computeGrad, int regularize,
                       int applyMask, double *energy, double *grad, double *igt) {
-    if (!ctx || !zs || !energy || ne <= 0 || ne > ctx->E || (regularize && !dxpu)) return MMADMM_EINVAL;
+    return mmadmm_block_grad_at(ctx, 0, ne, zs, dxpu, computeGrad, regularize, applyMask, energy, grad, igt);
+}
+
+int mmadmm_block_grad_at(mmadmm_ctx *ctx, int e0, int ne, const double *zs, const double *dxpu, int computeGrad, int regularize,
+                         int applyMask, double *energy, double *grad, double *igt) {
+    if (!ctx || !zs || !energy || ne <= 0 || e0 < 0 || e0 > ctx->E - ne || (regularize && !dxpu)) return MMADMM_EINVAL;
+    CK(cudaSetDevice(ctx->device));
     const int n = ctx->n;
     double *dz = nullptr, *dd = nullptr, *de = nullptr, *dg = nullptr, *di = nullptr;
     CK(cudaMalloc(&dz, sizeof(double) * (size_t)ne * n));
@@ -1930,10 +1944,10 @@ int mmadmm_block_grad(mmadmm_ctx *ctx, int ne, const double *zs, const double *d
     CK(cudaMemsetAsync(ctx->status_d, 0, sizeof(unsigned), ctx->stream));
     if (ctx->D == 2) {
         ElemArgs<2> a = ctx->elemArgs<2>(0.0);
-        k_block_grad_dbg<2><<<cdiv(ne, 128), 128, 0, ctx->stream>>>(a, ne, dz, dd, computeGrad, regularize, applyMask, de, dg, di);
+        k_block_grad_dbg<2><<<cdiv(ne, 128), 128, 0, ctx->stream>>>(a, e0, ne, dz, dd, computeGrad, regularize, applyMask, de, dg, di);
     } else {
         ElemArgs<3> a = ctx->elemArgs<3>(0.0);
-        k_block_grad_dbg<3><<<cdiv(ne, 128), 128, 0, ctx->stream>>>(a, ne, dz, dd, computeGrad, regularize, applyMask, de, dg, di);
+        k_block_grad_dbg<3><<<cdiv(ne, 128), 128, 0, ctx->stream>>>(a, e0, ne, dz, dd, computeGrad, regularize, applyMask, de, dg, di);
     }
     ctx->launches++;
     CK(cudaStreamSynchronize(ctx->stream));
@@ -1988,7 +2002,7 @@ void mmadmm_destroy(mmadmm_ctx *ctx) {
     cudaFree(ctx->mask); cudaFree(ctx->fixedBits); cudaFree(ctx->nonIntBits);
     cudaFree(ctx->x); cudaFree(ctx->xPrev); cudaFree(ctx->xBar); cudaFree(ctx->Vc); cudaFree(ctx->tdiag);
     cudaFree(ctx->z); cudaFree(ctx->u); cudaFree(ctx->B); cudaFree(ctx->gs);
-    cudaFree(ctx->incPtr); cudaFree(ctx->incIdx); cudaFree(ctx->vorder);
+    cudaFree(ctx->incPtr); cudaFree(ctx->incIdx); cudaFree(ctx->vorder); cudaFree(ctx->valence_d);
     cudaFree(ctx->grid); cudaFree(ctx->ax); cudaFree(ctx->ay); cudaFree(ctx->az);
     cudaFree(ctx->partIh); cudaFree(ctx->partDual); cudaFree(ctx->partPrimal); cudaFree(ctx->scal_d);
     if (ctx->scal_h) cudaFreeHost(ctx->scal_h);
