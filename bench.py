@@ -32,14 +32,37 @@ METRIC = "ADMM steps/sec & element-prox updates/sec"
 UNIT = "element-prox updates/s"
 PARAMS = dict(rho=50.0, tau=0.5, dt=0.025, admm_iter=10, tol=1e-3, mon2d=4, mon3d=3)
 WEAK_NX_2D = {1: 1024, 2: 1448, 4: 2048, 8: 2896}   # SURVEY 8(d) C5 weak-scaling ladder
+WEAK_N_DISC = {1: 816, 2: 1154, 4: 1632, 8: 2308}   # C3: 6 N^2 triangles = 4.0 / 8.0 / 16.0 / 32.0 M
+WEAK_NX_3D = {1: 80, 2: 101, 4: 127, 8: 160}        # C4: 12 nx^3 tets = 6.1 / 12.4 / 24.6 / 49.2 M
 
 
 def workload(n_gpus, name):
+    """BASELINE.json configs: c2 = configs[1] (the N=1 bench workload; N>1: the C5 weak-scaling ladder), c3 = configs[2]
+    (disc with BOUNDARY_FREE rim), c4 = configs[3] (3DMonitor280)."""
     if name == "c4":
-        return dict(D=3, nx=80, label="SquareGrid 3D nx=ny=nz=80 (6,144,000 tets), MEx33D, rho=50 tau=0.5 dt=0.025 AdmmIter=10")
+        nx = WEAK_NX_3D.get(n_gpus, 80)
+        return dict(D=3, nx=nx, kind="box", mon=3, btype=1, rho=50.0, tau=0.5, dt=0.025, cpu_nx=20,
+                    label=f"SquareGrid 3D nx=ny=nz={nx} ({12 * nx ** 3:,} tets), MEx33D, rho=50 tau=0.5 dt=0.025 AdmmIter=10")
+    if name == "c3":
+        N = WEAK_N_DISC.get(n_gpus, 816)
+        return dict(D=2, nx=N, kind="disc", mon=5, btype=0, rho=5.0, tau=0.1, dt=0.05, cpu_nx=200,
+                    label=f"unit disc of {N} hexagonal rings ({6 * N * N:,} triangles), rim nodes BOUNDARY_FREE (reference semantics: "
+                          f"gradient live, no projection), MEx5 spiral monitor, rho=5 tau=0.1 dt=0.05 AdmmIter=10 (Monitor310's parameters)")
     nx = WEAK_NX_2D.get(n_gpus, 1024)
-    return dict(D=2, nx=nx, label=f"SquareGrid 2D nx=ny={nx} ({4 * nx * nx:,} triangles), MEx4 shock-layer monitor, "
-                                  f"rho=50 tau=0.5 dt=0.025 AdmmIter=10 tol=1e-3")
+    return dict(D=2, nx=nx, kind="box", mon=4, btype=1, rho=50.0, tau=0.5, dt=0.025, cpu_nx=256,
+                label=f"SquareGrid 2D nx=ny={nx} ({4 * nx * nx:,} triangles), MEx4 shock-layer monitor, "
+                      f"rho=50 tau=0.5 dt=0.025 AdmmIter=10 tol=1e-3")
+
+
+def make_mesh(wl, nx):
+    """(Vp, F, mask, monitor table) of a workload at resolution nx, from the package's host-side generators."""
+    mm = importlib.import_module("mm-admm_b200")
+    D = wl["D"]
+    if wl["kind"] == "disc":
+        Vp, F, mask = mm.generate_disc_mesh(nx, 1.0, (0.0, 0.0), wl["btype"])
+    else:
+        Vp, F, mask = mm.generate_uniform_rect_mesh(D, nx, nx, nx if D == 3 else 0, boundary_type=wl["btype"])
+    return Vp, F, mask, mm.TestMonitor(D, wl["mon"]).evaluate_at_vertices(Vp)
 
 
 def algorithmic_bytes_prox(D, P, E, g):
@@ -103,15 +126,15 @@ class ClockSampler:
         return out
 
 
-def run_oracle_sample(D, nx, steps, warmup, threads, safe):
+def run_oracle_sample(wl, nx, steps, warmup, threads, safe):
     """CPU oracle port on a bounded sample, in the same epochs of <= `safe` steady-state steps as the GPU arm;
     returns (element-prox updates/s over the timed steps, ms/step, description, E, ADMM iterations)."""
     import oracle_lib as O
-    Vp, F, mask = O.uniform_rect_mesh(D, nx, nx, nx if D == 3 else 0)
-    mon = O.monitor_eval(D, PARAMS["mon2d"] if D == 2 else PARAMS["mon3d"], Vp)
+    D = wl["D"]
+    Vp, F, mask, mon = make_mesh(wl, nx)
     iters, dt, done, epochs = 0, 0.0, 0, 0
     while done < steps:
-        orc = O.Oracle(Vp, F, mask, mon, PARAMS["rho"], PARAMS["tau"], PARAMS["dt"], nthreads=threads)
+        orc = O.Oracle(Vp, F, mask, mon, wl["rho"], wl["tau"], wl["dt"], nthreads=threads)
         for _ in range(warmup):
             orc.step(PARAMS["admm_iter"], PARAMS["tol"])
         kk = min(safe, steps - done)
@@ -125,7 +148,8 @@ def run_oracle_sample(D, nx, steps, warmup, threads, safe):
         done += kk
         epochs += 1
     E = F.shape[0]
-    desc = (f"oracle port (C++/OpenMP, {threads} threads) on SquareGrid {D}D nx={nx} ({E:,} elements), same monitor/"
+    shape = f"disc of {nx} rings" if wl["kind"] == "disc" else f"SquareGrid {D}D nx={nx}"
+    desc = (f"oracle port (C++/OpenMP, {threads} threads) on {shape} ({E:,} elements), same monitor/"
             f"parameters, {steps} steady-state outer steps in {epochs} epoch(s) after {warmup} warm-up steps ({iters} ADMM iterations)")
     return E * iters / dt, dt / steps * 1e3, desc, E, iters
 
@@ -142,9 +166,9 @@ def reference_arm(args):
     wl = workload(args.gpus, args.workload)
     D = wl["D"]
     threads = os.cpu_count() or 1
-    nx = args.cpu_nx or (256 if D == 2 else 20)
+    nx = args.cpu_nx or wl["cpu_nx"]
     W = min(max(args.warmup, 3), 6)
-    v, ms, desc, E, iters = run_oracle_sample(D, nx, args.steps, W, threads, safe_steps(args.workload, W))
+    v, ms, desc, E, iters = run_oracle_sample(wl, nx, args.steps, W, threads, safe_steps(args.workload, W))
     line = {"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
             "warmup": W, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f64", "data": "synthetic",
@@ -162,7 +186,7 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--workload", default="c2", choices=["c2", "c4"])
+    ap.add_argument("--workload", default="c2", choices=["c2", "c3", "c4"])
     ap.add_argument("--nx", type=int, default=0, help="override the mesh resolution (debugging)")
     ap.add_argument("--cpu-nx", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -199,8 +223,7 @@ def main():
     wl = workload(args.gpus, args.workload)
     D = wl["D"]
     nx = args.nx or wl["nx"]
-    Vp, F, mask = mm.generate_uniform_rect_mesh(D, nx, nx, nx if D == 3 else 0)
-    mon = mm.TestMonitor(D, PARAMS["mon2d"] if D == 2 else PARAMS["mon3d"]).evaluate_at_vertices(Vp)
+    Vp, F, mask, mon = make_mesh(wl, nx)
     P, E = Vp.shape[0], F.shape[0]
     # caller-owned Vp in pinned host memory (what the reference's Mesh writes back every step)
     vp_pinned = torch.empty((P, D), dtype=torch.float64).pin_memory()
@@ -211,10 +234,10 @@ def main():
         if state.get("solver") is not None:
             state["solver"].close()
         vp_pinned.numpy()[:] = Vp
-        mesh = mm.Mesh(vp_pinned.numpy(), F.copy(), mask, mon, rho=PARAMS["rho"], tau=PARAMS["tau"])
+        mesh = mm.Mesh(vp_pinned.numpy(), F.copy(), mask, mon, rho=wl["rho"], tau=wl["tau"])
         mesh.Vp = vp_pinned.numpy()
         t0 = time.perf_counter()
-        solver = mm.MeshIntegrator(PARAMS["dt"], mesh, device=local, sync_vp=False, comm=new_comm())
+        solver = mm.MeshIntegrator(wl["dt"], mesh, device=local, sync_vp=False, comm=new_comm())
         state["init_s"] = time.perf_counter() - t0
         if args.prox_variant >= 0:
             solver.set_option("prox_variant", args.prox_variant)
@@ -312,8 +335,9 @@ def main():
                                    f"shared-vertex partials + 5-double all-gather per ADMM iteration; rank 0 holds {Eloc:,} elements")
                    if world > 1 else "single GPU", "l2": "inputs_exceed_L2 "
                    f"(element state {8 * E * (D * (D + 1)) * (D * (D + 1) + 2) / 1e9:.2f} GB >> 126 MB L2)",
-                   "timed_steps": f"{K} steady-state outer steps in {r['epochs']} epoch(s) of <= {SAFE} (outer steps {W}..{W + min(SAFE, K) - 1} after a "
-                   f"fresh start; the reference algorithm itself breaks down at outer step ~12 on this workload, see DESIGN.md)"},
+                   "timed_steps": (f"{K} steady-state outer steps in {r['epochs']} epoch(s) of <= {SAFE} (outer steps {W}..{W + min(SAFE, K) - 1} after a "
+                                   f"fresh start; the reference algorithm itself breaks down at outer step ~12 on this workload, see DESIGN.md)")
+                   if args.workload == "c2" else f"{K} steady-state outer steps {W}..{W + K - 1} after {W} warm-up steps"},
         "steps_per_sec": K / (r["ms"] / 1e3), "admm_iters_per_sec": r["iters"] / (r["ms"] / 1e3),
         "admm_iters": r["iters"], "mean_bfgs_iters_per_element_prox": kbar,
         "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": Ploc * D * 8 + 32,
@@ -330,8 +354,8 @@ def main():
     }
     if rank == 0 and not args.no_cpu_baseline:
         threads = os.cpu_count() or 1
-        cnx = args.cpu_nx or (256 if D == 2 else 20)
-        v, ms, desc, _, _ = run_oracle_sample(D, cnx, 6, 3, threads, safe_steps(args.workload, 3))
+        cnx = args.cpu_nx or wl["cpu_nx"]
+        v, ms, desc, _, _ = run_oracle_sample(wl, cnx, 6, 3, threads, safe_steps(args.workload, 3))
         line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": threads, "kind": "port", "sample": desc, "ms_per_step": ms}
     if rank == 0:
         print(json.dumps(line))

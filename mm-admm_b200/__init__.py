@@ -107,6 +107,7 @@ def host_lib():
         H = C.CDLL(HOST_LIB_PATH)
         H.mmadmm_host_monitor_eval.argtypes = [C.c_int, C.c_int, C.c_int, _c_dp, _c_dp]
         H.mmadmm_host_uniform_rect_mesh.argtypes = [C.c_int] * 4 + [C.c_double] * 6 + [C.c_int, _c_dp, _c_ip, _c_ip]
+        H.mmadmm_host_disc_mesh.argtypes = [C.c_int, C.c_double, C.c_double, C.c_double, C.c_int, _c_dp, _c_ip, _c_ip]
         _host = H
     return _host
 
@@ -127,6 +128,16 @@ def generate_uniform_rect_mesh(D, nx, ny, nz=0, box=(0, 1, 0, 1, 0, 1), boundary
                                                   _dp(Vp), _ip(F), _ip(mask))
     if rc:
         raise MMADMMError("bad mesh parameters")
+    return Vp, F, mask
+
+
+def generate_disc_mesh(N, R=1.0, center=(0.0, 0.0), boundary_type=BOUNDARY_FREE):
+    """Disc of N hexagonal rings (6 N^2 triangles, 1 + 3N(N+1) points), outer ring marked `boundary_type`; the scalable
+    stand-in for the reference's BaseCircle fixtures (BASELINE config 3).  -> (Vp, F, mask)."""
+    P, E = 1 + 3 * N * (N + 1), 6 * N * N
+    Vp = np.zeros((P, 2)); F = np.zeros((E, 3), dtype=np.int32); mask = np.zeros(P, dtype=np.int32)
+    if host_lib().mmadmm_host_disc_mesh(N, float(R), float(center[0]), float(center[1]), boundary_type, _dp(Vp), _ip(F), _ip(mask)):
+        raise MMADMMError("bad disc parameters")
     return Vp, F, mask
 
 

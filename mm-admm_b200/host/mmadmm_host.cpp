@@ -111,4 +111,41 @@ int mmadmm_host_uniform_rect_mesh(int D, int nx, int ny, int nz, double xa_, dou
     return 0;
 }
 
+// Disc of radius R around (cx, cy) as N concentric hexagonal rings: ring k has 6k points at radius k R / N, so arc and ring
+// spacing stay within 5 % of each other and every triangle is close to equilateral.  P = 1 + 3N(N+1), E = 6 N^2; elements
+// are emitted ring by ring (spatially coherent, so contiguous element blocks are annuli).  Outer-ring nodes get bType.
+// This is the scalable stand-in for the reference's BaseCircle fixtures (Experiments/Results/BaseCircle/CircleEx*.txt,
+// unit discs of unknown origin): utils::meshFromLevelSetFun cannot provide it, the reference algorithm inverts an element
+// of its meshes in the first step (tests/test_gpu_dropin.py).  Used by BASELINE config 3 (bench.py --workload c3).
+int mmadmm_host_disc_mesh(int N, double R, double cx, double cy, int bType, double *Vp, int *F, int *mask) {
+    if (N <= 0 || !(R > 0) || !Vp || !F || !mask) return 1;
+    const double PI = 3.14159265358979323846;
+    auto start = [](long long k) { return 1 + 3 * k * (k - 1); };   // first point of ring k >= 1
+    Vp[0] = cx; Vp[1] = cy; mask[0] = 2;
+    size_t t = 0;
+    for (int k = 1; k <= N; k++) {
+        const long long s0 = start(k), s1 = (k > 1) ? start(k - 1) : 0;
+        const int nk = 6 * k, nk1 = 6 * (k - 1);
+        const double r = R * k / N;
+        for (int j = 0; j < nk; j++) {
+            const double th = 2.0 * PI * j / nk;
+            Vp[2 * (s0 + j)] = cx + r * std::cos(th);
+            Vp[2 * (s0 + j) + 1] = cy + r * std::sin(th);
+            mask[s0 + j] = (k == N) ? bType : 2;
+        }
+        for (int sec = 0; sec < 6; sec++)
+            for (int i = 0; i < k; i++) {
+                const int o0 = (int)(s0 + (sec * k + i) % nk), o1 = (int)(s0 + (sec * k + i + 1) % nk);
+                if (k == 1) { F[3 * t] = 0; F[3 * t + 1] = o0; F[3 * t + 2] = o1; t++; continue; }
+                const int ia = (int)(s1 + (sec * (k - 1) + i) % nk1);
+                F[3 * t] = ia; F[3 * t + 1] = o0; F[3 * t + 2] = o1; t++;
+                if (i < k - 1) {
+                    const int ib = (int)(s1 + (sec * (k - 1) + i + 1) % nk1);
+                    F[3 * t] = ia; F[3 * t + 1] = o1; F[3 * t + 2] = ib; t++;
+                }
+            }
+    }
+    return 0;
+}
+
 }  // extern "C"

@@ -13,14 +13,24 @@ pytestmark = pytest.mark.gpu
 mm = importlib.import_module("mm-admm_b200")
 
 
+def _case_mesh(m, case):
+    """case = (D, nx, monitor, rho, boundary type, compMesh[, "disc"]) -> Vp, F, mask, tau, dt.  A disc case is BASELINE
+    config 3 at test size: nx hexagonal rings, Monitor310's tau/dt; its element blocks are annuli, so every rank has two
+    neighbours whose interfaces are whole rings of different lengths."""
+    D, nx, kind, rho, btype, comp = case[:6]
+    if len(case) > 6 and case[6] == "disc":
+        return m.generate_disc_mesh(nx, 1.0, (0.0, 0.0), btype) + (0.1, 0.05)
+    return m.generate_uniform_rect_mesh(D, nx, nx, nx if D == 3 else 0, boundary_type=btype) + (0.5, 0.025)
+
+
 def _worker(rank, world, id128, case, nsteps, q):
     import importlib as il
     m = il.import_module("mm-admm_b200")
-    D, nx, kind, rho, btype, comp = case
-    Vp, F, mask = m.generate_uniform_rect_mesh(D, nx, nx, nx if D == 3 else 0, boundary_type=btype)
+    D, nx, kind, rho, btype, comp = case[:6]
+    Vp, F, mask, tau, dt = _case_mesh(m, case)
     mon = m.TestMonitor(D, kind).evaluate_at_vertices(Vp)
-    mesh = m.Mesh(Vp.copy(), F.copy(), mask, mon, rho=rho, tau=0.5, Vc=Vp.copy() if comp else None)
-    s = m.MeshIntegrator(0.025, mesh, device=rank, comm=(rank, world, id128))
+    mesh = m.Mesh(Vp.copy(), F.copy(), mask, mon, rho=rho, tau=tau, Vc=Vp.copy() if comp else None)
+    s = m.MeshIntegrator(dt, mesh, device=rank, comm=(rank, world, id128))
     e0 = s.getEnergy()
     ihs, its = [], []
     for _ in range(nsteps):
@@ -52,25 +62,26 @@ def ngpus():
     return torch.cuda.device_count()
 
 
-@pytest.mark.parametrize("case,nsteps", [((2, 48, 3, 100.0, 1, False), 6), ((2, 40, 1, 50.0, 0, True), 5), ((3, 8, 3, 50.0, 1, False), 4)])
+@pytest.mark.parametrize("case,nsteps", [((2, 48, 3, 100.0, 1, False), 6), ((2, 40, 1, 50.0, 0, True), 5), ((3, 8, 3, 50.0, 1, False), 4),
+                                         ((2, 40, 5, 5.0, 0, False, "disc"), 5)])
 @pytest.mark.parametrize("world", [2, 4])
 def test_partitioned_solve_matches_single_gpu_and_oracle(case, nsteps, world):
     if ngpus() < world:
         pytest.skip(f"needs {world} GPUs")
-    D, nx, kind, rho, btype, comp = case
+    D, nx, kind, rho, btype, comp = case[:6]
     res = run_dist(world, case, nsteps)
     # every rank returns the same scalars and the same assembled mesh
     for r in res[1:]:
         assert r[1] == res[0][1] and r[2] == res[0][2] and r[3] == res[0][3] and r[4] == res[0][4]
         assert np.array_equal(r[5], res[0][5])
-    assert sum(r[6][1] for r in res) == (4 * nx * nx if D == 2 else 12 * nx ** 3)
     # single GPU
-    Vp, F, mask = mm.generate_uniform_rect_mesh(D, nx, nx, nx if D == 3 else 0, boundary_type=btype)
+    Vp, F, mask, tau, dt = _case_mesh(mm, case)
+    assert sum(r[6][1] for r in res) == F.shape[0]
     mon = mm.TestMonitor(D, kind).evaluate_at_vertices(Vp)
     Vc = Vp.copy() if comp else None
-    mesh = mm.Mesh(Vp.copy(), F.copy(), mask, mon, rho=rho, tau=0.5, Vc=Vc)
-    s = mm.MeshIntegrator(0.025, mesh)
-    orc = O.Oracle(Vp, F, mask, mon, rho, 0.5, 0.025, Vc=Vc, nthreads=4)
+    mesh = mm.Mesh(Vp.copy(), F.copy(), mask, mon, rho=rho, tau=tau, Vc=Vc)
+    s = mm.MeshIntegrator(dt, mesh)
+    orc = O.Oracle(Vp, F, mask, mon, rho, tau, dt, Vc=Vc, nthreads=4)
     assert abs(res[0][1] - s.getEnergy()) <= 1e-12 * abs(res[0][1])
     for k in range(nsteps):
         ih = s.step(10, 1e-3)

@@ -161,3 +161,28 @@ def test_inverted_element_is_reported():
     mesh2 = mm.Mesh(Vp2, mm.generate_uniform_rect_mesh(2, 4, 4)[1], mask, mon, rho=50.0, tau=0.5)
     s2 = mm.MeshIntegrator(0.025, mesh2)   # reOrient flips the damaged elements, so energy is still defined
     s2.getEnergy()
+
+
+@pytest.mark.parametrize("N,kind", [(12, 5), (24, 1)])
+def test_disc_with_free_rim_matches_oracle(N, kind):
+    """BASELINE config 3 at oracle size: unit disc of hexagonal rings, rim nodes BOUNDARY_FREE (reference semantics,
+    SURVEY F5), Monitor310's parameters.  Also exercises block_grad_at on an element that touches the rim."""
+    Vp, F, mask = mm.generate_disc_mesh(N, 1.0, (0.0, 0.0), mm.BOUNDARY_FREE)
+    assert F.shape[0] == 6 * N * N and Vp.shape[0] == 1 + 3 * N * (N + 1) and (mask == 0).sum() == 6 * N
+    assert np.array_equal(np.unique(F), np.arange(Vp.shape[0]))
+    mon = mm.TestMonitor(2, kind).evaluate_at_vertices(Vp)
+    orc, mesh, solver = pair(Vp, F, mask, mon, 5.0, 0.1, 0.05)
+    for s in range(8):
+        ih = solver.step(10, 1e-3); ro = orc.step(10, 1e-3)
+        assert ro["status"] == 0 and solver.last["iters"] == ro["iters"]
+        assert abs(ih - ro["Ih"]) <= TOL_E2E * abs(ro["Ih"])
+    assert rel(mesh.Vp, orc.x()) < TOL_E2E
+    assert np.array_equal(solver.stats()["bfgs_hist"], orc.stats()[0])
+    e0 = F.shape[0] - 5
+    z = mesh.Vp[mesh.F[e0:e0 + 3]].reshape(3, -1)
+    L = mm.lib()
+    en = np.zeros(3); g = np.zeros((3, 6)); igt = np.zeros(3)
+    assert L.mmadmm_block_grad_at(solver.h, e0, 3, mm._dp(np.ascontiguousarray(z)), None, 1, 0, 1, mm._dp(en), mm._dp(g), mm._dp(igt)) == 0
+    zo = np.zeros((F.shape[0], 6)); zo[:] = mesh.Vp[mesh.F].reshape(-1, 6)
+    eo, go, _ = orc.block_grad(zo, apply_mask=True)
+    assert rel(en, eo[e0:e0 + 3]) < TOL_UNIT and rel(g, go[e0:e0 + 3]) < 1e-10
