@@ -190,6 +190,7 @@ def main():
     ap.add_argument("--nx", type=int, default=0, help="override the mesh resolution (debugging)")
     ap.add_argument("--cpu-nx", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--iso-grid", type=int, default=1, help="0: disable the scalar monitor-grid fast path (A/B runs)")
     ap.add_argument("--prox-variant", type=int, default=-1, help="prox kernel tile/occupancy variant (debugging; -1 = library default)")
     args = ap.parse_args()
     if args.impl == "reference":
@@ -241,6 +242,8 @@ def main():
         state["init_s"] = time.perf_counter() - t0
         if args.prox_variant >= 0:
             solver.set_option("prox_variant", args.prox_variant)
+        if not args.iso_grid:
+            solver.set_option("iso_grid", 0)
         state["e0"] = solver.getEnergy()
         warm = []
         for _ in range(W):
@@ -330,7 +333,7 @@ def main():
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": K, "warmup": W,
         "ms_per_step": r["ms"] / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
         "data": "synthetic",
-        "config": {"workload": wl["label"], "elements": E, "points": P, "monitor_grid": g,
+        "config": {"workload": wl["label"], "elements": E, "points": P, "monitor_grid": g, "monitor_grid_isotropic_fast_path": bool(args.iso_grid) and solver.iso_grid_active(),
                    "parallelism": (f"element-block partition over {world} GPUs, one process per GPU; NCCL send/recv halo sums of "
                                    f"shared-vertex partials + 5-double all-gather per ADMM iteration; rank 0 holds {Eloc:,} elements")
                    if world > 1 else "single GPU", "l2": "inputs_exceed_L2 "

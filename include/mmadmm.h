@@ -98,7 +98,9 @@ int mmadmm_get_stats(mmadmm_ctx *ctx, long long *hist52, long long *proxCalls, l
  * Enabled with mmadmm_set_option(ctx, "timing", 1); counts[i] = launches timed. */
 int mmadmm_get_timing(mmadmm_ctx *ctx, double *ms5, long long *counts5, int reset);
 
-/* Options: "timing" (0/1), "stats" (0/1, default 1). */
+/* Options: "timing" (0/1), "stats" (0/1, default 1), "prox_variant" (kernel tile/occupancy variant, debugging),
+ * "iso_grid" (0/1, default 1): when every tensor of the monitor grid is m*I bitwise, look m up in a scalar grid
+ * (bit-identical results, D*D..10x fewer bytes per lookup); "iso_grid_active" is a query: returns 0 iff that path is on. */
 int mmadmm_set_option(mmadmm_ctx *ctx, const char *name, int value);
 
 /* The CUDA stream every kernel of this context is launched on (cudaStream_t as void*). */

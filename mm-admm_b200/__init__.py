@@ -339,6 +339,10 @@ class MeshIntegrator:
     def set_option(self, name, value):
         self._check(self.L.mmadmm_set_option(self.h, name.encode(), int(value)))
 
+    def iso_grid_active(self):
+        """True when the monitor grid is isotropic (m*I everywhere) and lookups use the scalar grid."""
+        return self.L.mmadmm_set_option(self.h, b"iso_grid_active", 0) == 0
+
     def timing(self, reset=False):
         ms = (C.c_double * 5)(); cnt = (C.c_longlong * 5)()
         self._check(self.L.mmadmm_get_timing(self.h, ms, cnt, int(reset)))

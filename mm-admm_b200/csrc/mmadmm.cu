@@ -44,7 +44,7 @@ namespace {
 constexpr int TPB = 128;       // element kernels: threads per block
 constexpr int TPB_V = 256;     // vertex kernels
 constexpr int MAXV = 4;        // D+1 <= 4
-enum ProxFlags { PF_PREFETCH_GRID = 1 };   // template switches of the persistent prox kernel
+enum ProxFlags { PF_PREFETCH_GRID = 1, PF_ISO = 2 };   // PF_ISO: scalar monitor grid (isotropic monitors), compile-time path   // template switches of the persistent prox kernel
 constexpr int ES_ALIGN = 128;  // element planes are padded to full prox tiles (TMA bulk copies need whole, aligned tiles)
 
 template <int D> struct ElemArgs {
@@ -413,7 +413,7 @@ template <int D> __global__ void __launch_bounds__(TPB) k_hess_init(ElemArgs<D> 
 // Bkinv (pk = -B g; B y and y^T B; rank-2 update) run out of shared memory ([plane][thread]: conflict-free), and the
 // updated tile goes back with TMA bulk stores.  Also: DXpU = D x + u (K1), u = DXpU - z (K3a), sum(Ih) and
 // ||z - zPrev||^2 partials (K5).
-template <int D, int TPB_, int MINB, bool COMP>
+template <int D, int TPB_, int MINB, bool COMP, bool ISO>
 __global__ void __launch_bounds__(TPB_, MINB) k_prox(ElemArgs<D> a) {
     constexpr int n = D * (D + 1);
     constexpr int NN = n * n;
@@ -445,7 +445,7 @@ __global__ void __launch_bounds__(TPB_, MINB) k_prox(ElemArgs<D> a) {
 #pragma unroll
             for (int v = 0; v < D + 1; v++) gather_vertex<D>(a.Vc, vid[v], xi + D * v);
         }
-        ih = prox_grad<D>(z, dx, xi, COMP, a.mg, a.fc, fb, Gk, inv);   // Ihsave: energy at entry
+        ih = prox_grad<D, ISO>(z, dx, xi, COMP, a.mg, a.fc, fb, Gk, inv);   // Ihsave: energy at entry
     }
     mbar_wait(bar, 0);
     if (active) {
@@ -471,7 +471,7 @@ __global__ void __launch_bounds__(TPB_, MINB) k_prox(ElemArgs<D> a) {
 #pragma unroll
                 for (int k = 0; k < n; k++) z[k] += pk[k];
             }
-            prox_grad<D>(z, dx, xi, COMP, a.mg, a.fc, fb, G1, inv);
+            prox_grad<D, ISO>(z, dx, xi, COMP, a.mg, a.fc, fb, G1, inv);
             double Ix = 0.0, yk[n];
 #pragma unroll
             for (int k = 0; k < n; k++) { Ix += fabs(G1[k]); yk[k] = G1[k] - Gk[k]; Gk[k] = G1[k]; }
@@ -531,6 +531,273 @@ __global__ void __launch_bounds__(TPB_, MINB) k_prox(ElemArgs<D> a) {
         if (tid < 52 && shist[tid]) atomicAdd(&a.hist[tid], (unsigned long long)shist[tid]);
     }
     if (tid < TPB_ / TILE) bulk_wait_read0();   // shared memory must stay allocated until the bulk stores have read it
+}
+
+// Vertex-warp form of the prox kernel (the default for D = 3).  One CTA of D+1 warps owns one tile of 32 elements:
+// warp q is vertex q of all 32 elements, lane = element.  A thread holds only its vertex's D components of every BFGS
+// vector (z, DXpU, Gk, pk, yk, B*yk) and works on rows D*q .. D*q+D-1 of the element's inverse Hessian, which sits in
+// shared memory as [row*n+col][lane] (conflict-free for every access below; one TMA bulk copy each way).  What the other
+// vertices hold travels through small [component][lane] exchange buffers between CTA barriers.  The part of blockGrad after
+// the monitor lookups is evaluated redundantly by every warp (it needs all of z); the lookups themselves, the three passes
+// over B and all loads/stores are split D+1 ways.  Compared with the thread-per-element form in 3D (255 registers, 2.8 KB of
+// spills per thread, 31.8 GB of local-memory traffic per launch on C4, 6 warps per SM) nothing spills and 12 warps fit.
+template <int D, bool COMP, bool ISO, int MINB>
+__global__ void __launch_bounds__((D + 1) * 32, MINB) k_prox_vw(const __grid_constant__ ElemArgs<D> a) {
+    constexpr int n = D * (D + 1), NN = n * n, NV = D + 1, DD = D * D;
+    constexpr int MS = ISO ? 1 : DD;                  // doubles per vertex lookup
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    double *Bs = reinterpret_cast<double *>(smem_raw);     // [NN][32]
+    double *Zs = Bs + NN * 32;                             // [n][32]  z
+    double *Gs = Zs + n * 32;                              // [n][32]  Gk
+    double *Ps = Gs + n * 32;                              // [n][32]  pk
+    double *Ys = Ps + n * 32;                              // [n][32]  yk
+    double *YB = Ys + n * 32;                              // [n][32]  yk^T B
+    double *Ms = YB + n * 32;                              // [NV][MS][32]  monitor lookups
+    double *Sc = Ms + NV * MS * 32;                        // [NV][3][32]  per-vertex partial sums: |G1|, pk.yk, yk.B yk
+    double *Xn = Sc + NV * 3 * 32;                         // [n][32]  next tile: x gather   (thread-private slots, cp.async)
+    double *Un = Xn + n * 32;                              // [n][32]  next tile: u
+    double *Zn = Un + n * 32;                              // [n][32]  next tile: z
+    int *Vn = reinterpret_cast<int *>(Zn + n * 32);        // [NV][32] ints  connectivity of the tile after next
+    double *red = reinterpret_cast<double *>(Vn + NV * 32);   // 32
+    uint64_t *bar = reinterpret_cast<uint64_t *>(red + 32);
+    int *shist = reinterpret_cast<int *>(bar + 2);         // 52
+    const int tid = threadIdx.x, lane = tid & 31, q = tid >> 5;
+    const int nTiles = (a.E + 31) >> 5;
+    if (tid == 0) mbar_init(bar, 1);
+    if (a.hist && tid < 52) shist[tid] = 0;
+    __syncthreads();
+
+    // Inputs of a tile (own vertex: x gather, u, z) are fetched one tile ahead by per-thread cp.async into thread-private
+    // shared-memory slots, the connectivity two tiles ahead into a register: no global-load latency at the head of a tile.
+    auto prefetch = [&](int tile, int vid) {
+        const int e = tile * 32 + lane;
+        if (e < a.E) {
+#pragma unroll
+            for (int l = 0; l < D; l++) {
+                const int s = (D * q + l) * 32 + lane;
+                cp_async8(Xn + s, a.x + (size_t)D * vid + l);
+                if (!a.uZero) cp_async8(Un + s, a.u + tm_index(e, D * q + l, n));
+                if (a.zsrc) cp_async8(Zn + s, a.zsrc + (size_t)D * vid + l);
+                else cp_async8(Zn + s, a.z + tm_index(e, D * q + l, n));
+            }
+        }
+    };
+    auto prefetch_vid = [&](int tile) {     // connectivity of `tile` into this thread's slot
+        const int e = tile * 32 + lane;
+        if (tile < nTiles && e < a.E) cp_async4(Vn + q * 32 + lane, a.F[q] + e);
+    };
+    int tile = blockIdx.x;
+    if (tile < nTiles) {
+        const int e0 = tile * 32 + lane;
+        prefetch(tile, e0 < a.E ? __ldg(a.F[q] + e0) : 0);
+        prefetch_vid(tile + gridDim.x);
+        cp_async_commit();
+    }
+    double ihAcc = 0.0, dualAcc = 0.0;     // meaningful in thread 0
+    for (int it = 0; tile < nTiles; tile += gridDim.x, it++) {
+        const int e = tile * 32 + lane;
+        const bool active = e < a.E;
+        if (tid == 0) {
+            if (it > 0) bulk_wait_read0();     // the previous tile's store has finished reading Bs
+            mbar_expect_tx(bar, (unsigned)(NN * 32 * sizeof(double)));
+            bulk_g2s(Bs, a.B + (size_t)tile * NN * 32, (unsigned)(NN * 32 * sizeof(double)), bar);
+        }
+        double zo[D], dxo[D], zprev[D], Gk[D], xi[COMP ? n : 1];
+        bool inv = false;
+        cp_async_wait_all();
+#pragma unroll
+        for (int l = 0; l < D; l++) {
+            const int s = (D * q + l) * 32 + lane;
+            zo[l] = active ? Zn[s] : 0.0;
+            dxo[l] = active ? (a.uZero ? Xn[s] : Xn[s] + Un[s]) : 0.0;
+            zprev[l] = zo[l];
+            Gk[l] = 0.0;
+        }
+        const bool ownFixed = active && ((a.fixedBits[e] >> q) & 1u);
+        const int vidNext = Vn[q * 32 + lane];
+        if (COMP && active) {
+#pragma unroll
+            for (int v = 0; v < NV; v++) gather_vertex<D>(a.Vc, __ldg(a.F[v] + e), xi + D * v);
+        }
+        {   // next tile's inputs (the slots just read are this thread's own)
+            const int tn = tile + gridDim.x;
+            if (tn < nTiles) {
+                prefetch(tn, vidNext);
+                prefetch_vid(tn + gridDim.x);
+            }
+            cp_async_commit();
+        }
+        // own-vertex lookup + own z into the exchange buffers
+        auto publish_z = [&]() {
+#pragma unroll
+            for (int l = 0; l < D; l++) Zs[(D * q + l) * 32 + lane] = zo[l];
+            if (ISO) {
+                Ms[q * 32 + lane] = eval_monitor_iso<D>(a.mg, zo);
+            } else {
+                SMat<D> m;
+                eval_monitor<D>(a.mg, zo, m);
+#pragma unroll
+                for (int k = 0; k < DD; k++) Ms[(q * DD + k) * 32 + lane] = m.a[k];
+            }
+        };
+        // regularised, masked gradient of the own vertex at the published z (Mesh::computeBlockGrad, regularize = true);
+        // returns the un-regularised element energy
+        auto own_gradient = [&](double *g) -> double {
+            double z[n], grad[n];
+#pragma unroll
+            for (int k = 0; k < n; k++) z[k] = Zs[k * 32 + lane];
+            SMat<D> mPre[ISO ? 1 : NV];
+            double mIso[ISO ? NV : 1];
+#pragma unroll
+            for (int v = 0; v < NV; v++) {
+                if (ISO) mIso[v] = Ms[v * 32 + lane];
+                else {
+#pragma unroll
+                    for (int k = 0; k < DD; k++) mPre[v].a[k] = Ms[(v * DD + k) * 32 + lane];
+                }
+            }
+            const double en = block_grad_core<D, true, ISO>(z, xi, COMP, mPre, mIso, a.fc, grad, inv);
+#pragma unroll
+            for (int l = 0; l < D; l++) g[l] = 0.0;
+#pragma unroll
+            for (int v = 0; v < NV; v++)
+                if (v == q) {
+#pragma unroll
+                    for (int l = 0; l < D; l++) g[l] = grad[D * v + l];
+                }
+#pragma unroll
+            for (int l = 0; l < D; l++) g[l] = ownFixed ? 0.0 : g[l] + a.fc.w2 * (-dxo[l] + zo[l]);
+            return en;
+        };
+        if (active) publish_z();
+        __syncthreads();
+        double ih = 0.0;
+        if (active) {
+            ih = own_gradient(Gk);     // Ihsave: energy at entry (identical on all D+1 warps)
+#pragma unroll
+            for (int l = 0; l < D; l++) Gs[(D * q + l) * 32 + lane] = Gk[l];
+        }
+        mbar_wait(bar, (unsigned)(it & 1));
+        __syncthreads();
+        bool done = !active;
+        int iters = 0;
+        const double *Brow = Bs + (size_t)(D * q) * n * 32 + lane;     // own rows: Brow[(rl*n + c)*32]
+        for (int iter = 0; iter < 50; iter++) {
+            double pk[D], yk[D], By[D];
+            if (!done) {                      // pass 1: pk = -B Gk (own rows), step, publish
+#pragma unroll
+                for (int rl = 0; rl < D; rl++) {
+                    double sacc = Brow[(rl * n) * 32] * Gs[lane];
+#pragma unroll
+                    for (int c = 1; c < n; c++) sacc += Brow[(rl * n + c) * 32] * Gs[c * 32 + lane];
+                    pk[rl] = -sacc;
+                }
+#pragma unroll
+                for (int l = 0; l < D; l++) { zo[l] += pk[l]; Ps[(D * q + l) * 32 + lane] = pk[l]; }
+                publish_z();
+            }
+            __syncthreads();
+            if (!done) {                      // gradient at the new point, yk, partial sums
+                double G1[D];
+                own_gradient(G1);
+                double ix = 0.0, c2 = 0.0;
+#pragma unroll
+                for (int l = 0; l < D; l++) {
+                    ix += fabs(G1[l]);
+                    yk[l] = G1[l] - Gk[l];
+                    Gk[l] = G1[l];
+                    c2 = (l == 0) ? pk[0] * yk[0] : c2 + pk[l] * yk[l];
+                    Ys[(D * q + l) * 32 + lane] = yk[l];
+                    Gs[(D * q + l) * 32 + lane] = G1[l];
+                }
+                Sc[(q * 3 + 0) * 32 + lane] = ix;
+                Sc[(q * 3 + 1) * 32 + lane] = c2;
+            }
+            __syncthreads();
+            bool conv = false;
+            if (!done) {                      // pass 2: B yk (own rows), yk^T B (own columns)
+                double yB[D];
+#pragma unroll
+                for (int rl = 0; rl < D; rl++) {
+                    double sacc = Brow[(rl * n) * 32] * Ys[lane];
+#pragma unroll
+                    for (int c = 1; c < n; c++) sacc += Brow[(rl * n + c) * 32] * Ys[c * 32 + lane];
+                    By[rl] = sacc;
+                }
+#pragma unroll
+                for (int cl = 0; cl < D; cl++) {
+                    const double *Bcol = Bs + (size_t)(D * q + cl) * 32 + lane;   // Bcol[r*n*32]
+                    double sacc = Ys[lane] * Bcol[0];
+#pragma unroll
+                    for (int r = 1; r < n; r++) sacc += Ys[r * 32 + lane] * Bcol[(size_t)r * n * 32];
+                    yB[cl] = sacc;
+                }
+                double yBy = yk[0] * By[0];
+#pragma unroll
+                for (int l = 1; l < D; l++) yBy += yk[l] * By[l];
+#pragma unroll
+                for (int l = 0; l < D; l++) YB[(D * q + l) * 32 + lane] = yB[l];
+                Sc[(q * 3 + 2) * 32 + lane] = yBy;
+                double Ix = Sc[lane];
+#pragma unroll
+                for (int v = 1; v < NV; v++) Ix += Sc[(v * 3) * 32 + lane];
+                conv = Ix < a.tol;
+            }
+            const int more = __syncthreads_or((!done && !conv && iter + 1 < 50) ? 1 : 0);
+            if (!done) {                      // pass 3: rank-2 update of the own rows (src/Mesh.cpp:846-856)
+                double c2 = Sc[(1) * 32 + lane], yBy = Sc[(2) * 32 + lane];
+#pragma unroll
+                for (int v = 1; v < NV; v++) { c2 += Sc[(v * 3 + 1) * 32 + lane]; yBy += Sc[(v * 3 + 2) * 32 + lane]; }
+                const double ic2 = 1.0 / c2;
+                const double c1 = (c2 + yBy) * (ic2 * ic2);
+                double *Bw = Bs + (size_t)(D * q) * n * 32 + lane;
+#pragma unroll
+                for (int rl = 0; rl < D; rl++) {
+                    const double a1 = c1 * pk[rl], a3 = pk[rl] * ic2, a2 = By[rl] * ic2;
+#pragma unroll
+                    for (int c = 0; c < n; c++) {
+                        const double pc = Ps[c * 32 + lane];
+                        Bw[(rl * n + c) * 32] += (a1 * pc - a2 * pc) - a3 * YB[c * 32 + lane];
+                    }
+                }
+                iters = iter + 1;
+                if (conv) done = true;
+            }
+            if (!more) break;
+            __syncthreads();   // pass 3 reads Ps / YB, the next pass 1 overwrites Ps (steady state: one iteration, never reached)
+        }
+        double dual2 = 0.0;
+        if (active) {
+            if (q == 0) {
+                if (inv) atomicOr(a.status, ST_INVERTED);
+                if (!done) atomicOr(a.status, ST_BFGS_MAX);
+                if (a.hist) atomicAdd(&shist[done ? iters : 51], 1);
+            }
+#pragma unroll
+            for (int l = 0; l < D; l++) {
+                a.z[tm_index(e, D * q + l, n)] = zo[l];
+                a.u[tm_index(e, D * q + l, n)] = dxo[l] - zo[l];    // u = DXpU - z
+                const double dd = zo[l] - zprev[l];
+                dual2 += dd * dd;
+            }
+        }
+        fence_async_smem();
+        __syncthreads();
+        if (tid == 0) {
+            bulk_s2g(a.B + (size_t)tile * NN * 32, Bs, (unsigned)(NN * 32 * sizeof(double)));
+            bulk_commit();
+        }
+        const double s1 = block_sum(q == 0 ? ih : 0.0, red);
+        const double s2 = block_sum(dual2, red);
+        if (tid == 0) { ihAcc += s1; dualAcc += s2; }
+    }
+    cp_async_wait_all();
+    if (tid == 0) { a.partIh[blockIdx.x] = ihAcc; a.partDual[blockIdx.x] = dualAcc; }
+    if (a.hist) {
+        __syncthreads();
+        if (tid < 52 && shist[tid]) atomicAdd(&a.hist[tid], (unsigned long long)shist[tid]);
+    }
+    if (tid == 0) bulk_wait_read0();   // shared memory must stay allocated until the last bulk store has read it
 }
 
 // Persistent, software-pipelined form of the warp-tile prox kernel (the default for D = 2).  One warp walks tiles
@@ -653,7 +920,7 @@ __global__ void __launch_bounds__(WPB * 32, MINB) k_prox_p(const __grid_constant
             mbar_expect_tx(barB, (unsigned)(NN * 32 * sizeof(double)));
             bulk_g2s(Bs, a.B + (size_t)t * NN * TILE, (unsigned)(NN * TILE * sizeof(double)), barB);
         }
-        if (active) ih = prox_grad_s<D>(z, dxs, xi, COMP, a.mg, a.fc, fb, Gk, inv);   // Ihsave: energy at entry
+        if (active) ih = prox_grad_s<D, (FLAGS & PF_ISO) != 0>(z, dxs, xi, COMP, a.mg, a.fc, fb, Gk, inv);   // Ihsave: energy at entry
         mbar_wait(barB, (unsigned)(it & 1));
         int bin = -1;
         if (active) {
@@ -670,7 +937,7 @@ __global__ void __launch_bounds__(WPB * 32, MINB) k_prox_p(const __grid_constant
                     pk[r] = -s;
                     z[r] += pk[r];
                 }
-                prox_grad_s<D>(z, dxs, xi, COMP, a.mg, a.fc, fb, G1, inv);
+                prox_grad_s<D, (FLAGS & PF_ISO) != 0>(z, dxs, xi, COMP, a.mg, a.fc, fb, G1, inv);
                 double Ix = 0.0, yk[n];
 #pragma unroll
                 for (int k = 0; k < n; k++) { Ix += fabs(G1[k]); yk[k] = G1[k] - Gk[k]; Gk[k] = G1[k]; }
@@ -739,7 +1006,7 @@ __global__ void __launch_bounds__(WPB * 32, MINB) k_prox_p(const __grid_constant
                 double pnt[D];
 #pragma unroll
                 for (int l = 0; l < D; l++) pnt[l] = haveZ ? zn[(D * v + l) * 32 + lane] : zn[((size_t)v * 32 + lane) * D + l];
-                prefetch_monitor<D>(a.mg, pnt);
+                prefetch_monitor<D, (FLAGS & PF_ISO) != 0>(a.mg, pnt);
             }
         }
     }
@@ -953,6 +1220,22 @@ __global__ void __launch_bounds__(TPB_V) k_predict_extrap(size_t N, const double
     xPrev[i] = xv;
 }
 
+// Isotropy of the monitor grid: flag stays 1 iff every row is m*I bitwise (equal diagonal, zero off-diagonal); the scalars
+// go to `iso`.  All analytic monitors of the reference's driver except MEx2 are of this form (Experiments/TestMonitors).
+template <int D> __global__ void k_iso_extract(size_t rows, const double *grid, double *iso, int *flag) {
+    size_t r = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= rows) return;
+    const double *g = grid + r * GridRow<D>::stride;
+    const double m = g[0];
+    bool ok = true;
+#pragma unroll
+    for (int a = 0; a < D; a++)
+#pragma unroll
+        for (int b = 0; b < D; b++) ok = ok && (a == b ? (g[a * D + b] == m) : (g[a * D + b] == 0.0));
+    iso[r] = m;
+    if (!ok) *flag = 0;
+}
+
 // ---- unit-parity helpers ----
 template <int D> __global__ void k_eval_monitor(MonGrid mg, int npts, const double *pts, double *out) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -961,7 +1244,7 @@ template <int D> __global__ void k_eval_monitor(MonGrid mg, int npts, const doub
 #pragma unroll
     for (int l = 0; l < D; l++) p[l] = pts[(size_t)i * D + l];
     SMat<D> m;
-    eval_monitor<D>(mg, p, m);
+    eval_monitor_any<D>(mg, p, m);
 #pragma unroll
     for (int k = 0; k < D * D; k++) out[(size_t)i * D * D + k] = m.a[k];
 }
@@ -1026,7 +1309,7 @@ struct mmadmm_ctx {
     double *sPart = nullptr, *sTot = nullptr, *sendBuf = nullptr, *recvBuf = nullptr, *scalAll_d = nullptr, *scalAll_h = nullptr;
     int nProxPart = 0;           // number of per-block (or per-warp) partial sums the last prox launch wrote
     int numSMs = 148;
-    bool smemAttrSet[8] = {false, false, false, false, false, false, false, false};
+    bool smemAttrSet[16] = {false};
     bool compMesh = false, gradUse = false;
     cudaStream_t stream = nullptr;
     int *F[4] = {nullptr, nullptr, nullptr, nullptr};
@@ -1035,6 +1318,8 @@ struct mmadmm_ctx {
     double *z = nullptr, *u = nullptr, *B = nullptr, *gs = nullptr;
     int *incPtr = nullptr, *incIdx = nullptr, *vorder = nullptr, *valence_d = nullptr;
     double *grid = nullptr, *ax = nullptr, *ay = nullptr, *az = nullptr;
+    double *gridIso = nullptr;          // scalar monitor grid (isotropic monitors only)
+    bool gridIsIso = false, isoOn = true;
     int nx = 0, ny = 0, nz = 0;
     size_t gridRows = 0;
     double rho = 0, w = 0, tau = 0, m = 0, dt = 0;
@@ -1057,7 +1342,7 @@ struct mmadmm_ctx {
     double gridO[3] = {0, 0, 0}, gridRh[3] = {0, 0, 0};
     MonGrid monGrid() const {
         MonGrid mg;
-        mg.vals = grid; mg.ax = ax; mg.ay = ay; mg.az = az; mg.nx = nx; mg.ny = ny; mg.nz = nz;
+        mg.vals = grid; mg.iso = (isoOn && gridIsIso) ? gridIso : nullptr; mg.ax = ax; mg.ay = ay; mg.az = az; mg.nx = nx; mg.ny = ny; mg.nz = nz;
         for (int l = 0; l < 3; l++) { mg.o[l] = gridO[l]; mg.rh[l] = gridRh[l]; }
         return mg;
     }
@@ -1339,7 +1624,19 @@ template <int D> int build_monitor_grid(mmadmm_ctx *ctx, int P, const double *Vp
         CK(cudaMemcpyAsync(gridTmp, ctx->grid, sizeof(double) * ctx->gridRows * RS, cudaMemcpyDeviceToDevice, st));
         k_smooth<D><<<cdiv(ctx->gridRows * DD, 256), 256, 0, st>>>(ctx->nx, ctx->ny, ctx->nz, gridTmp, ctx->grid);
     }
-    ctx->launches += 2 + nSmooth;
+    {   // isotropic fast path of the lookups
+        int *flag = nullptr, one = 1;
+        CK(cudaMalloc(&flag, sizeof(int)));
+        CK(cudaMalloc(&ctx->gridIso, sizeof(double) * ctx->gridRows));
+        CK(cudaMemcpyAsync(flag, &one, sizeof(int), cudaMemcpyHostToDevice, st));
+        k_iso_extract<D><<<cdiv(ctx->gridRows, 256), 256, 0, st>>>(ctx->gridRows, ctx->grid, ctx->gridIso, flag);
+        CK(cudaMemcpyAsync(&one, flag, sizeof(int), cudaMemcpyDeviceToHost, st));
+        CK(cudaStreamSynchronize(st));
+        cudaFree(flag);
+        ctx->gridIsIso = one != 0;
+        if (!ctx->gridIsIso) { cudaFree(ctx->gridIso); ctx->gridIso = nullptr; }
+    }
+    ctx->launches += 3 + nSmooth;
     CK(cudaStreamSynchronize(st));
     CK(cudaGetLastError());
     cudaFree(gridTmp); cudaFree(monV); cudaFree(bin); cudaFree(ids); cudaFree(binStart); cudaFree(items); cudaFree(xg);
@@ -1488,10 +1785,12 @@ template <int D, int TPB_> constexpr size_t prox_smem_bytes() {
 
 template <int D, int TPB_, int MINB> int launch_prox_t(mmadmm_ctx *ctx, const ElemArgs<D> &a, int slot) {
     constexpr size_t smem = prox_smem_bytes<D, TPB_>();
-    auto kern = ctx->compMesh ? k_prox<D, TPB_, MINB, true> : k_prox<D, TPB_, MINB, false>;
-    if (!ctx->smemAttrSet[slot]) {
+    const bool iso = a.mg.iso != nullptr;
+    auto kern = ctx->compMesh ? (iso ? k_prox<D, TPB_, MINB, true, true> : k_prox<D, TPB_, MINB, true, false>)
+                              : (iso ? k_prox<D, TPB_, MINB, false, true> : k_prox<D, TPB_, MINB, false, false>);
+    if (!ctx->smemAttrSet[slot + (iso ? 8 : 0)]) {
         CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        ctx->smemAttrSet[slot] = true;
+        ctx->smemAttrSet[slot + (iso ? 8 : 0)] = true;
     }
     kern<<<cdiv(ctx->E, TPB_), TPB_, smem, ctx->stream>>>(a);
     ctx->nProxPart = cdiv(ctx->E, TPB_);
@@ -1505,10 +1804,12 @@ template <int D, int WPB, int MINB, int FLAGS> int launch_prox_p(mmadmm_ctx *ctx
     constexpr int n = D * (D + 1);
     const size_t slots = ctx->compMesh ? 4 : 3;
     const size_t smem = sizeof(double) * (size_t)WPB * (n * n * 32 + 2 * slots * n * 32) + 32 * WPB;
-    auto kern = ctx->compMesh ? k_prox_p<D, WPB, MINB, true, FLAGS> : k_prox_p<D, WPB, MINB, false, FLAGS>;
-    if (!ctx->smemAttrSet[slot]) {
+    const bool iso = a.mg.iso != nullptr;
+    auto kern = ctx->compMesh ? (iso ? k_prox_p<D, WPB, MINB, true, FLAGS | PF_ISO> : k_prox_p<D, WPB, MINB, true, FLAGS>)
+                              : (iso ? k_prox_p<D, WPB, MINB, false, FLAGS | PF_ISO> : k_prox_p<D, WPB, MINB, false, FLAGS>);
+    if (!ctx->smemAttrSet[slot + (iso ? 8 : 0)]) {
         CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        ctx->smemAttrSet[slot] = true;
+        ctx->smemAttrSet[slot + (iso ? 8 : 0)] = true;
     }
     const int grid = std::min(ctx->numSMs * MINB, cdiv(ctx->E, WPB * 32));
     kern<<<grid, WPB * 32, smem, ctx->stream>>>(a);
@@ -1525,10 +1826,29 @@ template <> int launch_prox<2>(mmadmm_ctx *ctx, const ElemArgs<2> &a) {
         default: return launch_prox_p<2, 2, 6, PF_PREFETCH_GRID>(ctx, a, 0);
     }
 }
+template <int D, int MINB> int launch_prox_vw(mmadmm_ctx *ctx, const ElemArgs<D> &a, int slot) {
+    constexpr int n = D * (D + 1);
+    const bool iso = a.mg.iso != nullptr;
+    const size_t smem = sizeof(double) * 32 * (size_t)(n * n + 8 * n + (D + 1) * (iso ? 1 : D * D) + (D + 1) * 3 + 1) + 16 + (52 + 32 * (D + 1)) * sizeof(int);
+    auto kern = ctx->compMesh ? (iso ? k_prox_vw<D, true, true, MINB> : k_prox_vw<D, true, false, MINB>)
+                              : (iso ? k_prox_vw<D, false, true, MINB> : k_prox_vw<D, false, false, MINB>);
+    if (!ctx->smemAttrSet[slot + (iso ? 8 : 0)]) {
+        CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        ctx->smemAttrSet[slot + (iso ? 8 : 0)] = true;
+    }
+    const int grid = std::min(ctx->numSMs * MINB, cdiv(ctx->E, 32));    // persistent: each CTA walks tiles with this stride
+    kern<<<grid, (D + 1) * 32, smem, ctx->stream>>>(a);
+    ctx->nProxPart = grid;
+    ctx->launches++;
+    return MMADMM_OK;
+}
 template <> int launch_prox<3>(mmadmm_ctx *ctx, const ElemArgs<3> &a) {
     switch (ctx->proxVariant) {
         case 1: return launch_prox_t<3, 32, 6>(ctx, a, 1);
-        default: return launch_prox_t<3, 64, 3>(ctx, a, 0);
+        case 2: return launch_prox_t<3, 64, 3>(ctx, a, 2);     // thread per element (spills; kept for A/B runs)
+        case 3: return launch_prox_vw<3, 2>(ctx, a, 3);
+        case 4: return launch_prox_vw<3, 4>(ctx, a, 4);
+        default: return launch_prox_vw<3, 3>(ctx, a, 0);       // one warp per vertex, one CTA per 32-element tile
     }
 }
 
@@ -1989,6 +2309,8 @@ int mmadmm_set_option(mmadmm_ctx *ctx, const char *name, int value) {
     if (!strcmp(name, "timing")) { ctx->timingOn = value != 0; return MMADMM_OK; }
     if (!strcmp(name, "stats")) { ctx->statsOn = value != 0; return MMADMM_OK; }
     if (!strcmp(name, "prox_variant")) { ctx->proxVariant = value; return MMADMM_OK; }
+    if (!strcmp(name, "iso_grid")) { ctx->isoOn = value != 0; return MMADMM_OK; }   // 0: always interpolate the full tensors
+    if (!strcmp(name, "iso_grid_active")) return (ctx->isoOn && ctx->gridIsIso) ? MMADMM_OK : MMADMM_EINVAL;   // query
     return MMADMM_EINVAL;
 }
 
@@ -2003,7 +2325,7 @@ void mmadmm_destroy(mmadmm_ctx *ctx) {
     cudaFree(ctx->x); cudaFree(ctx->xPrev); cudaFree(ctx->xBar); cudaFree(ctx->Vc); cudaFree(ctx->tdiag);
     cudaFree(ctx->z); cudaFree(ctx->u); cudaFree(ctx->B); cudaFree(ctx->gs);
     cudaFree(ctx->incPtr); cudaFree(ctx->incIdx); cudaFree(ctx->vorder); cudaFree(ctx->valence_d);
-    cudaFree(ctx->grid); cudaFree(ctx->ax); cudaFree(ctx->ay); cudaFree(ctx->az);
+    cudaFree(ctx->grid); cudaFree(ctx->gridIso); cudaFree(ctx->ax); cudaFree(ctx->ay); cudaFree(ctx->az);
     cudaFree(ctx->partIh); cudaFree(ctx->partDual); cudaFree(ctx->partPrimal); cudaFree(ctx->scal_d);
     if (ctx->scal_h) cudaFreeHost(ctx->scal_h);
     cudaFree(ctx->status_d);

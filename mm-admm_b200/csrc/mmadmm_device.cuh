@@ -30,6 +30,9 @@ enum StatusBits { ST_INVERTED = 1, ST_SINGULAR_HESS = 2, ST_BFGS_MAX = 4, ST_NON
 template <int D> struct GridRow { static constexpr int stride = (D == 2) ? 4 : 10; };
 struct MonGrid {
     const double *vals;
+    const double *iso;           // non-null when every grid tensor is m*I (checked bitwise at init): the (g+1)^D scalars m.
+                                 // Interpolating m and forming m*I is bit-identical to interpolating the D*D entries and
+                                 // reads D*D (2D) / 10 (3D) times fewer bytes per lookup.
     const double *ax, *ay, *az;  // axis coordinates, nx+1 / ny+1 / nz+1 entries (utils::linspace values)
     int nx, ny, nz;
     double o[3];                 // axis origin a[0]
@@ -223,11 +226,74 @@ template <> __device__ __forceinline__ void eval_monitor<3>(const MonGrid &g, co
     }
 }
 
-// L2 prefetch of the grid rows eval_monitor(pnt) will read
-__device__ __forceinline__ void prefetch_l2(const void *p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
-template <int D> __device__ __forceinline__ void prefetch_monitor(const MonGrid &g, const double *pnt) {
+// Isotropic grids (every tensor m*I): the scalar m by the same bi/tri-linear expressions, term order included, so that
+// m*I equals what eval_monitor<D> returns bit for bit.
+template <int D> __device__ __forceinline__ double eval_monitor_iso(const MonGrid &g, const double *pnt);
+template <> __device__ __forceinline__ double eval_monitor_iso<2>(const MonGrid &g, const double *pnt) {
     int xInd = find_cell(pnt[0], g.o[0], g.rh[0], g.nx);
     int yInd = find_cell(pnt[1], g.o[1], g.rh[1], g.ny);
+    double x0 = __ldg(g.ax + xInd), x1 = __ldg(g.ax + xInd + 1);
+    double y0 = __ldg(g.ay + yInd), y1 = __ldg(g.ay + yInd + 1);
+    double x = pnt[0], y = pnt[1];
+    double norm = (1 / ((x1 - x0) * (y1 - y0)));
+    double c0 = norm * (x1 - x) * (y1 - y);
+    double c1 = norm * (x - x0) * (y1 - y);
+    double c2 = norm * (x1 - x) * (y - y0);
+    double c3 = norm * (x - x0) * (y - y0);
+    const double *r0 = g.iso + (size_t)yInd * (g.nx + 1) + xInd;
+    const double *r1 = r0 + (g.nx + 1);
+    const double m00 = __ldg(r0), m10 = __ldg(r0 + 1), m01 = __ldg(r1), m11 = __ldg(r1 + 1);
+    return c0 * m00 + c1 * m10 + c2 * m01 + c3 * m11;
+}
+template <> __device__ __forceinline__ double eval_monitor_iso<3>(const MonGrid &g, const double *pnt) {
+    int xInd = find_cell(pnt[0], g.o[0], g.rh[0], g.nx);
+    int yInd = find_cell(pnt[1], g.o[1], g.rh[1], g.ny);
+    int zInd = find_cell(pnt[2], g.o[2], g.rh[2], g.nz);
+    double x0 = __ldg(g.ax + xInd), x1 = __ldg(g.ax + xInd + 1);
+    double y0 = __ldg(g.ay + yInd), y1 = __ldg(g.ay + yInd + 1);
+    double z0 = __ldg(g.az + zInd), z1 = __ldg(g.az + zInd + 1);
+    double xd = (pnt[0] - x0) / (x1 - x0);
+    double yd = (pnt[1] - y0) / (y1 - y0);
+    double zd = (pnt[2] - z0) / (z1 - z0);
+    const size_t sl = (size_t)(g.nx + 1) * (g.ny + 1);
+    const double *b = g.iso + (size_t)zInd * sl + (size_t)yInd * (g.nx + 1) + xInd;
+    const double v0 = __ldg(b), v1 = __ldg(b + 1), v2 = __ldg(b + (g.nx + 1)), v3 = __ldg(b + (g.nx + 1) + 1);
+    const double v4 = __ldg(b + sl), v5 = __ldg(b + sl + 1), v6 = __ldg(b + sl + (g.nx + 1)), v7 = __ldg(b + sl + (g.nx + 1) + 1);
+    double m = 0.0;
+    m += ((1 - xd) * (1 - yd) * (1 - zd)) * v0;
+    m += (xd * (1 - yd) * (1 - zd)) * v1;
+    m += ((1 - xd) * yd * (1 - zd)) * v2;
+    m += (xd * yd * (1 - zd)) * v3;
+    m += ((1 - xd) * (1 - yd) * zd) * v4;
+    m += (xd * (1 - yd) * zd) * v5;
+    m += ((1 - xd) * yd * zd) * v6;
+    m += (xd * yd * zd) * v7;
+    return m;
+}
+// run-time selection (unit tests / ABI lookups only; the hot kernels are compiled per path)
+template <int D> __device__ __forceinline__ void eval_monitor_any(const MonGrid &g, const double *pnt, SMat<D> &mVal) {
+    if (g.iso) {
+        const double m = eval_monitor_iso<D>(g, pnt);
+#pragma unroll
+        for (int k = 0; k < D * D; k++) mVal.a[k] = (k % (D + 1) == 0) ? m : 0.0;
+    } else {
+        eval_monitor<D>(g, pnt, mVal);
+    }
+}
+
+// L2 prefetch of the grid rows eval_monitor(pnt) will read
+__device__ __forceinline__ void prefetch_l2(const void *p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
+template <int D, bool ISO = false> __device__ __forceinline__ void prefetch_monitor(const MonGrid &g, const double *pnt) {
+    int xInd = find_cell(pnt[0], g.o[0], g.rh[0], g.nx);
+    int yInd = find_cell(pnt[1], g.o[1], g.rh[1], g.ny);
+    if (ISO) {
+        const size_t sl = (size_t)(g.nx + 1) * (g.ny + 1);
+        const double *r0 = g.iso + (size_t)yInd * (g.nx + 1) + xInd + ((D == 3) ? (size_t)find_cell(pnt[2], g.o[2], g.rh[2], g.nz) * sl : 0);
+        prefetch_l2(r0); prefetch_l2(r0 + 1);
+        prefetch_l2(r0 + (g.nx + 1)); prefetch_l2(r0 + (g.nx + 1) + 1);
+        if (D == 3) { prefetch_l2(r0 + sl); prefetch_l2(r0 + sl + 1); prefetch_l2(r0 + sl + (g.nx + 1)); prefetch_l2(r0 + sl + (g.nx + 1) + 1); }
+        return;
+    }
     if (D == 2) {
         const double *r0 = g.vals + 4 * ((size_t)yInd * (g.nx + 1) + xInd);
         prefetch_l2(r0);
@@ -257,24 +323,29 @@ template <int D> struct FuncConsts {
 
 // Energy G*|K| and (optionally) the unregularised element gradient.  z: n = D(D+1) doubles, vertex-major.
 // Returns absK*G.  `inverted` is set when det(E) <= 0 (the reference asserts there, :174).
-template <int D, bool GRAD>
-__device__ __forceinline__ double block_grad(const double *z, const double *xi, bool compMesh, const MonGrid &mg,
-                                             const FuncConsts<D> &fc, double *grad, bool &inverted) {
+// Everything of blockGrad after the D+1 monitor lookups: mPre[i] (general) or mIso[i] (ISO: tensor i is mIso[i]*I) are the
+// monitor values at the D+1 vertices.  Split out so that a kernel may obtain the lookups elsewhere (the 3D prox kernel
+// evaluates one vertex per warp and exchanges them through shared memory).
+template <int D, bool GRAD, bool ISO>
+__device__ __forceinline__ double block_grad_core(const double *z, const double *xi, bool compMesh, const SMat<D> *mPre,
+                                                  const double *mIso, const FuncConsts<D> &fc, double *grad, bool &inverted) {
     constexpr int n = D * (D + 1);
     const double dFact = (D == 2) ? 2.0 : 6.0;
     const double d = (double)D;
     const double p = 1.5;
     const double theta = 1.0 / 3.0;
-
-    SMat<D> mPre[D + 1];
     SMat<D> M;
 #pragma unroll
     for (int k = 0; k < D * D; k++) M.a[k] = 0.0;
 #pragma unroll
     for (int i = 0; i < D + 1; i++) {
-        eval_monitor<D>(mg, z + i * D, mPre[i]);
+        if (ISO) {
 #pragma unroll
-        for (int k = 0; k < D * D; k++) M.a[k] += mPre[i].a[k];
+            for (int k = 0; k < D; k++) M.a[k * (D + 1)] += mIso[i];
+        } else {
+#pragma unroll
+            for (int k = 0; k < D * D; k++) M.a[k] += mPre[i].a[k];
+        }
     }
     SMat<D> Minv = sinv_scaled<D>(M, (double)D + 1);  // sic: M^{-1}/(D+1), :157
 
@@ -331,10 +402,16 @@ __device__ __forceinline__ double block_grad(const double *z, const double *xi, 
     for (int j = 0; j < D; j++) {
         // trace(dGdM * (mPre[j+1] - mPre[0]))
         double tr = 0.0;
+        if (ISO) {
+            const double dm = mIso[j + 1] - mIso[0];
 #pragma unroll
-        for (int a = 0; a < D; a++)
+            for (int a = 0; a < D; a++) tr += dGdM(a, a) * dm;
+        } else {
 #pragma unroll
-            for (int b = 0; b < D; b++) tr += dGdM(a, b) * (mPre[j + 1](b, a) - mPre[0](b, a));
+            for (int a = 0; a < D; a++)
+#pragma unroll
+                for (int b = 0; b < D; b++) tr += dGdM(a, b) * (mPre[j + 1](b, a) - mPre[0](b, a));
+        }
 #pragma unroll
         for (int l = 0; l < D; l++) basisComb[l] += Einv(j, l) * tr;
     }
@@ -363,14 +440,31 @@ __device__ __forceinline__ double block_grad(const double *z, const double *xi, 
     return absK * G;
 }
 
+// Energy G*|K| and (optionally) the unregularised element gradient.  z: n = D(D+1) doubles, vertex-major.
+// Returns absK*G.  `inverted` is set when det(E) <= 0 (the reference asserts there, :174).
+// ISO (compile-time): every grid tensor is m*I, so the D+1 vertex tensors are D+1 scalars (4 instead of 36 live doubles
+// in 3D) and M = (sum m_i) I; the arithmetic downstream is the general one on that M.
+template <int D, bool GRAD, bool ISO = false>
+__device__ __forceinline__ double block_grad(const double *z, const double *xi, bool compMesh, const MonGrid &mg,
+                                             const FuncConsts<D> &fc, double *grad, bool &inverted) {
+    SMat<D> mPre[ISO ? 1 : D + 1];
+    double mIso[ISO ? D + 1 : 1];
+#pragma unroll
+    for (int i = 0; i < D + 1; i++) {
+        if (ISO) mIso[i] = eval_monitor_iso<D>(mg, z + i * D);
+        else eval_monitor<D>(mg, z + i * D, mPre[i]);
+    }
+    return block_grad_core<D, GRAD, ISO>(z, xi, compMesh, mPre, mIso, fc, grad, inverted);
+}
+
 // Regularised + masked gradient as Mesh::computeBlockGrad(.., regularize=true) returns it
 // (src/Mesh.cpp:755-772 on top of AdaptationFunctional.cpp:279-282).  Returns the UNregularised energy (Igt).
-template <int D>
+template <int D, bool ISO = false>
 __device__ __forceinline__ double prox_grad(const double *z, const double *dxpu, const double *xi, bool compMesh,
                                             const MonGrid &mg, const FuncConsts<D> &fc, unsigned fixedBits, double *grad,
                                             bool &inverted) {
     constexpr int n = D * (D + 1);
-    double Igt = block_grad<D, true>(z, xi, compMesh, mg, fc, grad, inverted);
+    double Igt = block_grad<D, true, ISO>(z, xi, compMesh, mg, fc, grad, inverted);
 #pragma unroll
     for (int k = 0; k < n; k++) grad[k] += fc.w2 * (-dxpu[k] + z[k]);
 #pragma unroll
@@ -384,12 +478,12 @@ __device__ __forceinline__ double prox_grad(const double *z, const double *dxpu,
 
 // Same as prox_grad, with DXpU read from shared memory (dxs[k*32], one column per lane) after the gradient is formed,
 // so that it is not live in registers across block_grad.
-template <int D>
+template <int D, bool ISO = false>
 __device__ __forceinline__ double prox_grad_s(const double *z, const double *dxs, const double *xi, bool compMesh,
                                               const MonGrid &mg, const FuncConsts<D> &fc, unsigned fixedBits, double *grad,
                                               bool &inverted) {
     constexpr int n = D * (D + 1);
-    double Igt = block_grad<D, true>(z, xi, compMesh, mg, fc, grad, inverted);
+    double Igt = block_grad<D, true, ISO>(z, xi, compMesh, mg, fc, grad, inverted);
 #pragma unroll
     for (int k = 0; k < n; k++) grad[k] += fc.w2 * (-dxs[k * 32] + z[k]);
 #pragma unroll

@@ -186,3 +186,26 @@ def test_disc_with_free_rim_matches_oracle(N, kind):
     zo = np.zeros((F.shape[0], 6)); zo[:] = mesh.Vp[mesh.F].reshape(-1, 6)
     eo, go, _ = orc.block_grad(zo, apply_mask=True)
     assert rel(en, eo[e0:e0 + 3]) < TOL_UNIT and rel(g, go[e0:e0 + 3]) < 1e-10
+
+
+@pytest.mark.parametrize("D,nx,kind,iso", [(2, 16, 4, True), (3, 5, 3, True), (2, 16, 2, False)])
+def test_isotropic_grid_fast_path_is_equivalent(D, nx, kind, iso):
+    """Monitors of the form m*I (all of the driver's but MEx2) are looked up in a scalar grid; the general tensor path must
+    give the same lookups bit for bit and the same trajectories to rounding."""
+    Vp, F, mask = mm.generate_uniform_rect_mesh(D, nx, nx, nx if D == 3 else 0)
+    mon = mm.TestMonitor(D, kind).evaluate_at_vertices(Vp)
+    rng = np.random.default_rng(3)
+    pts = np.vstack([rng.uniform(-0.05, 1.05, size=(400, D)), Vp[:50]])
+    out, xs = [], []
+    for flag in (1, 0):
+        mesh = mm.Mesh(Vp.copy(), F.copy(), mask, mon, rho=50.0, tau=0.5)
+        s = mm.MeshIntegrator(0.025, mesh)
+        s.set_option("iso_grid", flag)
+        assert s.iso_grid_active() == (iso and flag == 1)
+        out.append(s.eval_monitor(pts))
+        for _ in range(4):
+            s.step(10, 1e-3)
+        xs.append(mesh.Vp.copy())
+        s.close()
+    assert np.array_equal(out[0], out[1])
+    assert rel(xs[0], xs[1]) < 1e-13
