@@ -143,6 +143,31 @@ int mmadmm_local_sizes(mmadmm_ctx *ctx, int *Ploc, int *Eloc);
 /* Local vertices' positions scattered into a caller array of GLOBAL size P x D (other rows untouched; no collective). */
 int mmadmm_get_x_local(mmadmm_ctx *ctx, double *xGlobal);
 
+/* ---- general sparse path of the x-update: preconditioned CG on a fixed CSR matrix (mm-admm_b200/csrc/pcg.cu) ----
+ * Replaces Eigen::ConjugateGradient<SparseMatrix, Lower|Upper> with its default Jacobi preconditioner
+ * (src/MeshIntegrator.cpp:54-55,138,160: compute(t), solve(vec); zero initial guess, stop at ||r|| <= tol ||b||) and, with
+ * precond = 1, the level-0 ILU + CG path of lib/LASolver (ILU_class.cpp:98-527, accel_class.cpp:402-491) that the
+ * reference's Method 2 uses.  On the ADMM matrix itself t is diagonal and mmadmm_step does not call this.
+ * CSR: rowptr[n+1], strictly ascending col[] per row, stored diagonal required.  precond: 0 = Jacobi, 1 = ILU(0). */
+typedef struct mmadmm_pcg mmadmm_pcg;
+int mmadmm_pcg_create(int n, const int *rowptr, const int *col, const double *val, int precond, int device, mmadmm_pcg **out);
+/* x = A^{-1} b from host arrays; iters = CG iterations taken, relres = ||r|| / ||b|| at exit. */
+int mmadmm_pcg_solve(mmadmm_pcg *h, const double *b, double *x, double tol, int maxit, int *iters, double *relres);
+/* Same with device pointers on the solver's device (no host copies). */
+int mmadmm_pcg_solve_device(mmadmm_pcg *h, const double *b_dev, double *x_dev, double tol, int maxit, int *iters, double *relres);
+/* y = A x (host arrays): the SpMV kernel alone (reference: matmult, accel_class.cpp:521-549). */
+int mmadmm_pcg_spmv(mmadmm_pcg *h, const double *x, double *y);
+/* z = M^{-1} r: Jacobi scaling or the level-scheduled ILU(0) triangular solves (reference: scaler_ILU::solve, ILU_class.cpp:447-527). */
+int mmadmm_pcg_precond(mmadmm_pcg *h, const double *r, double *z);
+/* ILU(0) factor values in A's CSR pattern (unit lower below the diagonal, U on and above it). */
+int mmadmm_pcg_get_ilu(mmadmm_pcg *h, double *lu);
+/* info4 = {threads per row of the SpMV kernel, lower levels, upper levels, kernels launched so far}. */
+int mmadmm_pcg_info(mmadmm_pcg *h, int *info4);
+/* Average device time (ms, CUDA events) of one SpMV + dot launch over `reps` launches. */
+int mmadmm_pcg_time_spmv(mmadmm_pcg *h, int reps, double *ms);
+const char *mmadmm_pcg_last_error(mmadmm_pcg *h);
+void mmadmm_pcg_destroy(mmadmm_pcg *h);
+
 void mmadmm_destroy(mmadmm_ctx *ctx);
 const char *mmadmm_last_error(mmadmm_ctx *ctx);
 const char *mmadmm_version(void);

@@ -33,6 +33,8 @@ ABI_SYMBOLS = [
     "mmadmm_get_timing", "mmadmm_set_option", "mmadmm_stream", "mmadmm_destroy", "mmadmm_last_error",
     "mmadmm_version", "mmadmm_plan_create", "mmadmm_plan_sizes", "mmadmm_plan_get", "mmadmm_plan_destroy",
     "mmadmm_comm_unique_id", "mmadmm_create_dist", "mmadmm_local_sizes", "mmadmm_get_x_local",
+    "mmadmm_pcg_create", "mmadmm_pcg_solve", "mmadmm_pcg_solve_device", "mmadmm_pcg_spmv", "mmadmm_pcg_precond",
+    "mmadmm_pcg_get_ilu", "mmadmm_pcg_info", "mmadmm_pcg_time_spmv", "mmadmm_pcg_last_error", "mmadmm_pcg_destroy",
 ]
 
 
@@ -95,6 +97,18 @@ def lib():
                                          C.c_double, C.c_int, C.c_int, C.c_int, C.c_int, C.c_char_p, C.POINTER(vp)]
         L.mmadmm_local_sizes.argtypes = [vp, _c_ip, _c_ip]
         L.mmadmm_get_x_local.argtypes = [vp, _c_dp]
+        L.mmadmm_pcg_create.argtypes = [C.c_int, _c_ip, _c_ip, _c_dp, C.c_int, C.c_int, C.POINTER(vp)]
+        L.mmadmm_pcg_solve.argtypes = [vp, _c_dp, _c_dp, C.c_double, C.c_int, _c_ip, _c_dp]
+        L.mmadmm_pcg_solve_device.argtypes = [vp, vp, vp, C.c_double, C.c_int, _c_ip, _c_dp]
+        L.mmadmm_pcg_spmv.argtypes = [vp, _c_dp, _c_dp]
+        L.mmadmm_pcg_precond.argtypes = [vp, _c_dp, _c_dp]
+        L.mmadmm_pcg_get_ilu.argtypes = [vp, _c_dp]
+        L.mmadmm_pcg_info.argtypes = [vp, _c_ip]
+        L.mmadmm_pcg_time_spmv.argtypes = [vp, C.c_int, _c_dp]
+        L.mmadmm_pcg_last_error.restype = C.c_char_p
+        L.mmadmm_pcg_last_error.argtypes = [vp]
+        L.mmadmm_pcg_destroy.restype = None
+        L.mmadmm_pcg_destroy.argtypes = [vp]
         _lib = L
     return _lib
 
@@ -178,6 +192,70 @@ def comm_unique_id():
     if rc:
         raise MMADMMError("NCCL is not available")
     return buf.raw
+
+
+class PCG:
+    """Preconditioned CG on a fixed CSR matrix (include/mmadmm.h, mmadmm_pcg_*): the general form of the ADMM x-update that
+    the reference runs through Eigen::ConjugateGradient (Jacobi) / lib/LASolver (ILU(0) + CG).  precond: "jacobi" | "ilu0"."""
+
+    def __init__(self, rowptr, col, val, precond="jacobi", device=0):
+        self.L = lib()
+        self.rowptr = np.ascontiguousarray(rowptr, dtype=np.int32)
+        self.col = np.ascontiguousarray(col, dtype=np.int32)
+        self.val = np.ascontiguousarray(val, dtype=np.float64)
+        self.n = self.rowptr.shape[0] - 1
+        self.h = C.c_void_p()
+        rc = self.L.mmadmm_pcg_create(self.n, _ip(self.rowptr), _ip(self.col), _dp(self.val), {"jacobi": 0, "ilu0": 1}[precond],
+                                      device, C.byref(self.h))
+        self._check(rc)
+
+    def _check(self, rc):
+        if rc:
+            msg = self.L.mmadmm_pcg_last_error(self.h).decode() if self.h else ""
+            raise MMADMMError(f"mmadmm_pcg error {ERRORS.get(rc, rc)}: {msg}")
+
+    def solve(self, b, tol=2.220446049250313e-16, maxit=None):
+        """-> (x, iterations, ||r||/||b||); defaults are Eigen's: tol = machine epsilon, maxit = 2n."""
+        b = np.ascontiguousarray(b, dtype=np.float64)
+        x = np.zeros(self.n); it = C.c_int(); rr = C.c_double()
+        self._check(self.L.mmadmm_pcg_solve(self.h, _dp(b), _dp(x), float(tol), int(maxit or 2 * self.n), C.byref(it), C.byref(rr)))
+        return x, it.value, rr.value
+
+    def spmv(self, x):
+        x = np.ascontiguousarray(x, dtype=np.float64); y = np.zeros(self.n)
+        self._check(self.L.mmadmm_pcg_spmv(self.h, _dp(x), _dp(y)))
+        return y
+
+    def precond(self, r):
+        r = np.ascontiguousarray(r, dtype=np.float64); z = np.zeros(self.n)
+        self._check(self.L.mmadmm_pcg_precond(self.h, _dp(r), _dp(z)))
+        return z
+
+    def ilu(self):
+        lu = np.zeros(self.val.shape[0])
+        self._check(self.L.mmadmm_pcg_get_ilu(self.h, _dp(lu)))
+        return lu
+
+    def info(self):
+        a = np.zeros(4, dtype=np.int32)
+        self._check(self.L.mmadmm_pcg_info(self.h, _ip(a)))
+        return dict(lanes=int(a[0]), lower_levels=int(a[1]), upper_levels=int(a[2]), launches=int(a[3]))
+
+    def time_spmv(self, reps=20):
+        ms = C.c_double()
+        self._check(self.L.mmadmm_pcg_time_spmv(self.h, reps, C.byref(ms)))
+        return ms.value
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.L.mmadmm_pcg_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
 
 
 class TestMonitor:
