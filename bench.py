@@ -325,6 +325,7 @@ def main():
     e2e = E * r2["iters"] / (r2["ms"] / 1e3)
     prox_ms, prox_cnt = r["timing"]["prox"]
     peak, peak_src = peaks()
+    fp64_peak = mm.measure_fp64_peak(local)
     bytes_per_launch = algorithmic_bytes_prox(D, P, E, g) * Eloc   # this rank's launch (rank 0 reports)
     achieved = bytes_per_launch / (prox_ms / max(prox_cnt, 1) / 1e3) / 1e9
     hist = r["hist"]
@@ -350,6 +351,8 @@ def main():
         "roofline": {"kernel": "k_prox", "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                      "traffic": None, "peak_source": peak_src, "algorithmic_bytes_per_launch": bytes_per_launch,
                      "avg_launch_ms": prox_ms / max(prox_cnt, 1), "launches_timed": prox_cnt},
+        "fp64": {"peak_tflops_measured": fp64_peak, "how": "DFMA microbenchmark, 8 independent chains per thread (mmadmm_measure_fp64_peak); "
+                 "the prox kernel's FP64 pipe utilisation is the ncu figure sm__inst_executed_pipe_fp64 in profiles/"},
         "phase_ms_per_step": {k: v[0] / K for k, v in r["timing"].items()},
         "clocks": r["clocks"],
         "init_seconds": init_s, "energy_initial": e0, "energy_last": r2["ih"][-1],

@@ -166,6 +166,8 @@ int mmadmm_pcg_info(mmadmm_pcg *h, int *info4);
 /* Average device time (ms, CUDA events) of one SpMV + dot launch over `reps` launches. */
 int mmadmm_pcg_time_spmv(mmadmm_pcg *h, int reps, double *ms);
 const char *mmadmm_pcg_last_error(mmadmm_pcg *h);
+/* Measured FP64 FMA peak of the device in TFLOP/s (DFMA microbenchmark, 8 independent chains per thread). */
+int mmadmm_measure_fp64_peak(int device, double *tflops);
 void mmadmm_pcg_destroy(mmadmm_pcg *h);
 
 void mmadmm_destroy(mmadmm_ctx *ctx);

@@ -34,7 +34,7 @@ ABI_SYMBOLS = [
     "mmadmm_version", "mmadmm_plan_create", "mmadmm_plan_sizes", "mmadmm_plan_get", "mmadmm_plan_destroy",
     "mmadmm_comm_unique_id", "mmadmm_create_dist", "mmadmm_local_sizes", "mmadmm_get_x_local",
     "mmadmm_pcg_create", "mmadmm_pcg_solve", "mmadmm_pcg_solve_device", "mmadmm_pcg_spmv", "mmadmm_pcg_precond",
-    "mmadmm_pcg_get_ilu", "mmadmm_pcg_info", "mmadmm_pcg_time_spmv", "mmadmm_pcg_last_error", "mmadmm_pcg_destroy",
+    "mmadmm_pcg_get_ilu", "mmadmm_pcg_info", "mmadmm_pcg_time_spmv", "mmadmm_pcg_last_error", "mmadmm_pcg_destroy", "mmadmm_measure_fp64_peak",
 ]
 
 
@@ -107,6 +107,7 @@ def lib():
         L.mmadmm_pcg_time_spmv.argtypes = [vp, C.c_int, _c_dp]
         L.mmadmm_pcg_last_error.restype = C.c_char_p
         L.mmadmm_pcg_last_error.argtypes = [vp]
+        L.mmadmm_measure_fp64_peak.argtypes = [C.c_int, _c_dp]
         L.mmadmm_pcg_destroy.restype = None
         L.mmadmm_pcg_destroy.argtypes = [vp]
         _lib = L
@@ -192,6 +193,15 @@ def comm_unique_id():
     if rc:
         raise MMADMMError("NCCL is not available")
     return buf.raw
+
+
+def measure_fp64_peak(device=0):
+    """DFMA microbenchmark on `device` -> TFLOP/s (2 flops per FMA)."""
+    v = C.c_double()
+    rc = lib().mmadmm_measure_fp64_peak(device, C.byref(v))
+    if rc:
+        raise MMADMMError(f"mmadmm_measure_fp64_peak: {ERRORS.get(rc, rc)}")
+    return v.value
 
 
 class PCG:

@@ -171,6 +171,18 @@ __global__ void __launch_bounds__(TPB) k_xpay(int n, const double *scal, const d
     if (i < n) p[i] = z[i] + scal[S_BETA] * p[i];
 }
 
+// FP64 pipe peak: 8 independent DFMA chains per thread, no memory traffic
+__global__ void __launch_bounds__(256) k_dfma_peak(int iters, double seed, double *out) {
+    double a0 = seed + threadIdx.x, a1 = a0 + 1, a2 = a0 + 2, a3 = a0 + 3, a4 = a0 + 4, a5 = a0 + 5, a6 = a0 + 6, a7 = a0 + 7;
+    const double m = 1.0000001, c = 1e-9;
+    for (int i = 0; i < iters; i++) {
+        a0 = fma(a0, m, c); a1 = fma(a1, m, c); a2 = fma(a2, m, c); a3 = fma(a3, m, c);
+        a4 = fma(a4, m, c); a5 = fma(a5, m, c); a6 = fma(a6, m, c); a7 = fma(a7, m, c);
+    }
+    const double s = ((a0 + a1) + (a2 + a3)) + ((a4 + a5) + (a6 + a7));
+    if (s == 123.456) out[0] = s;   // never true: keeps the chains alive
+}
+
 }  // namespace
 
 struct mmadmm_pcg {
@@ -447,6 +459,38 @@ int mmadmm_pcg_time_spmv(mmadmm_pcg *h, int reps, double *ms) {
     PCK(cudaEventElapsedTime(&t, e0, e1));
     *ms = t / reps;
     cudaEventDestroy(e0); cudaEventDestroy(e1);
+    return MMADMM_OK;
+}
+
+// Measured FP64 FMA throughput of the device (TFLOP/s, 2 flops per DFMA): the denominator of the prox kernel's FP64-pipe
+// figure (MEASURED_PEAKS.json has no FP64 entry; SURVEY.md 8d asks for a DFMA microbenchmark on the box).
+int mmadmm_measure_fp64_peak(int device, double *tflops) {
+    if (!tflops) return MMADMM_EINVAL;
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) return MMADMM_ENODEVICE;
+    if (cudaSetDevice(device) != cudaSuccess) return MMADMM_ECUDA;
+    int sms = 0;
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
+    double *out = nullptr;
+    if (cudaMalloc(&out, 8) != cudaSuccess) return MMADMM_ECUDA;
+    const int iters = 1 << 16, grid = sms * 8, tpb = 256;
+    cudaEvent_t e0, e1;
+    cudaEventCreate(&e0); cudaEventCreate(&e1);
+    k_dfma_peak<<<grid, tpb>>>(iters, 1.0, out);
+    double best = 0.0;
+    for (int rep = 0; rep < 3; rep++) {
+        cudaEventRecord(e0);
+        k_dfma_peak<<<grid, tpb>>>(iters, 1.0 + rep, out);
+        cudaEventRecord(e1);
+        if (cudaEventSynchronize(e1) != cudaSuccess) { cudaFree(out); return MMADMM_ECUDA; }
+        float ms = 0;
+        cudaEventElapsedTime(&ms, e0, e1);
+        const double tf = 2.0 * 8.0 * (double)iters * grid * tpb / (ms * 1e-3) / 1e12;
+        best = tf > best ? tf : best;
+    }
+    cudaEventDestroy(e0); cudaEventDestroy(e1);
+    cudaFree(out);
+    *tflops = best;
     return MMADMM_OK;
 }
 
