@@ -277,7 +277,7 @@ def main():
             if dist:
                 dist.barrier()
                 torch.cuda.synchronize()
-            sampler = ClockSampler(local)
+            sampler = ClockSampler(local) if rank == 0 else None   # rank 0 reports; NVML polling from 8 processes contends on a driver lock
             ev0.record(stream)
             for _ in range(kk):
                 tot["ih"].append(solver.step(PARAMS["admm_iter"], PARAMS["tol"]))
@@ -287,7 +287,7 @@ def main():
             if dist:
                 dist.barrier()
                 torch.cuda.synchronize()
-            tot["clocks"].append(sampler.stop())
+            tot["clocks"].append(sampler.stop() if sampler else {})
             ms = ev0.elapsed_time(ev1)
             if dist:   # device time, max over ranks
                 tms = torch.tensor([ms], dtype=torch.float64, device="cuda")
@@ -306,7 +306,7 @@ def main():
         cl = [c for c in tot["clocks"] if c.get("sm_mhz")]
         tot["clocks"] = dict(sm_mhz=statistics.median([c["sm_mhz"] for c in cl]) if cl else None,
                              sm_max_mhz=cl[0]["sm_max_mhz"] if cl else None,
-                             reasons=sorted(set(sum([c["reasons"] for c in tot["clocks"]], []))),
+                             reasons=sorted(set(sum([c.get("reasons", []) for c in tot["clocks"]], []))),
                              samples=sum(c.get("samples", 0) for c in tot["clocks"]))
         return tot
 
@@ -335,8 +335,11 @@ def main():
         "ms_per_step": r["ms"] / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
         "data": "synthetic",
         "config": {"workload": wl["label"], "elements": E, "points": P, "monitor_grid": g, "monitor_grid_isotropic_fast_path": bool(args.iso_grid) and solver.iso_grid_active(),
-                   "parallelism": (f"element-block partition over {world} GPUs, one process per GPU; NCCL send/recv halo sums of "
-                                   f"shared-vertex partials + 5-double all-gather per ADMM iteration; rank 0 holds {Eloc:,} elements")
+                   "parallelism": (f"element-block partition over {world} GPUs, one process per GPU; halo sums of shared-vertex partials + "
+                                   f"5-double all-gather per ADMM iteration by "
+                                   + ("NVLink peer stores into the neighbours' mailboxes (CUDA IPC) with epoch flags"
+                                      if solver.p2p_active() else "NCCL send/recv + ncclAllGather")
+                                   + f"; rank 0 holds {Eloc:,} elements")
                    if world > 1 else "single GPU", "l2": "inputs_exceed_L2 "
                    f"(element state {8 * E * (D * (D + 1)) * (D * (D + 1) + 2) / 1e9:.2f} GB >> 126 MB L2)",
                    "timed_steps": (f"{K} steady-state outer steps in {r['epochs']} epoch(s) of <= {SAFE} (outer steps {W}..{W + min(SAFE, K) - 1} after a "

@@ -427,6 +427,10 @@ class MeshIntegrator:
     def set_option(self, name, value):
         self._check(self.L.mmadmm_set_option(self.h, name.encode(), int(value)))
 
+    def p2p_active(self):
+        """True when a distributed context exchanges halo sums / scalars by NVLink peer stores (CUDA IPC) instead of NCCL."""
+        return self.L.mmadmm_set_option(self.h, b"p2p_active", 0) == 0
+
     def iso_grid_active(self):
         """True when the monitor grid is isotropic (m*I everywhere) and lookups use the scalar grid."""
         return self.L.mmadmm_set_option(self.h, b"iso_grid_active", 0) == 0

@@ -1299,6 +1299,19 @@ struct mmadmm_ctx {
     bool dist = false;
     int rank = 0, nranks = 1, Pglobal = 0, Eglobal = 0;
     void *comm = nullptr;                       // ncclComm_t
+    // NVLink peer-memory exchange (CUDA IPC): every rank owns a mailbox that its neighbours store into directly
+    bool p2p = false;
+    unsigned char *mailbox = nullptr;           // this rank's mailbox (device memory, exported through cudaIpcMemHandle)
+    std::vector<void *> peerMap;                // opened mailboxes of the other ranks (null for self / unopened)
+    double **peerRecv_d = nullptr;              // [nNbr] neighbour's receive segment for this rank (parity 0)
+    size_t *peerRecvStride_d = nullptr;         // [nNbr] doubles between the two parity halves of that neighbour's receive area
+    unsigned long long **peerHaloFlag_d = nullptr;   // [nNbr] neighbour's flag slot for this rank
+    double **peerScal_d = nullptr;              // [nranks] every rank's scalar table row for this rank (parity 0)
+    unsigned long long **peerScalFlag_d = nullptr;   // [nranks]
+    unsigned long long *haloFlags_d = nullptr, *scalFlags_d = nullptr;   // inside the own mailbox
+    double *mbScal_d = nullptr, *mbRecv_d = nullptr;                      // inside the own mailbox
+    int *nbrPtr_d = nullptr;
+    unsigned long long haloEpoch = 0, scalEpoch = 0;
     int nShared = 0, nNbrItems = 0, nblkSh = 0;
     std::vector<int> nbrRank, nbrPtr;           // host copies of the plan's neighbour segments
     int *sharedIdx = nullptr, *sharedSlot = nullptr, *nbrList = nullptr, *contribPtr = nullptr, *contrib = nullptr, *verts = nullptr;
@@ -1475,10 +1488,98 @@ __global__ void k_halo_combine(int nShared, const int *contribPtr, const int *co
     for (int l = 0; l < D; l++) sTot[(size_t)i * D + l] = s[l];
 }
 
-// sPart (partials of the shared vertices) -> sTot (totals), over NCCL point-to-point
+
+// ---- NVLink peer-memory exchange ----------------------------------------------------------------------------------
+// Flags are monotonically increasing epochs written with system scope after the data; readers spin (bounded) on them.
+__device__ __forceinline__ void flag_release(unsigned long long *flag, unsigned long long v) {
+    __threadfence_system();
+    asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(flag), "l"(v) : "memory");
+}
+__device__ __forceinline__ void flag_wait(const unsigned long long *flag, unsigned long long v) {
+    unsigned long long cur;
+    for (long long spin = 0; spin < (1ll << 27); spin++) {
+        asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(cur) : "l"(flag) : "memory");
+        if (cur >= v) return;
+        __nanosleep(64);
+    }
+    __trap();   // a peer never arrived: surface as a CUDA error instead of hanging the GPU
+}
+// One block per neighbour: store this rank's partials of the vertices shared with neighbour q straight into q's mailbox
+// (receive half `epoch & 1`), then publish the epoch in q's flag slot for this rank.
+template <int D>
+__global__ void __launch_bounds__(1024) k_halo_push(const int *nbrPtr, const int *nbrList, const double *sPart, double *const *peerRecv,
+                                                    const size_t *peerStride, unsigned long long *const *peerFlag,
+                                                    unsigned long long epoch) {
+    const int q = blockIdx.x;
+    const int j0 = nbrPtr[q], j1 = nbrPtr[q + 1];
+    double *dst = peerRecv[q] + ((epoch & 1ull) ? peerStride[q] : 0);
+    for (int j = j0 + threadIdx.x; j < j1; j += blockDim.x) {
+        const int i = nbrList[j];
+#pragma unroll
+        for (int l = 0; l < D; l++) dst[(size_t)(j - j0) * D + l] = sPart[(size_t)i * D + l];
+    }
+    __threadfence_system();
+    __syncthreads();
+    if (threadIdx.x == 0) flag_release(peerFlag[q], epoch);
+}
+// total = sum of the sharers' partials in ascending rank order, reading the partials the neighbours pushed
+template <int D>
+__global__ void k_halo_combine_p2p(int nShared, int nNbr, const int *contribPtr, const int *contrib, const double *sPart,
+                                   const double *recvBase, size_t recvStride, const unsigned long long *flags,
+                                   unsigned long long epoch, double *sTot) {
+    if (threadIdx.x < nNbr) flag_wait(flags + threadIdx.x, epoch);
+    for (int q = blockDim.x + threadIdx.x; q < nNbr; q += blockDim.x) flag_wait(flags + q, epoch);
+    __syncthreads();
+    const double *recvBuf = recvBase + ((epoch & 1ull) ? recvStride : 0);
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= nShared) return;
+    double s[D];
+#pragma unroll
+    for (int l = 0; l < D; l++) s[l] = 0.0;
+    for (int k = contribPtr[i]; k < contribPtr[i + 1]; k++) {
+        const int c = contrib[k];
+#pragma unroll
+        for (int l = 0; l < D; l++) s[l] += (c < 0) ? sPart[(size_t)i * D + l] : __ldcg(recvBuf + (size_t)c * D + l);
+    }
+#pragma unroll
+    for (int l = 0; l < D; l++) sTot[(size_t)i * D + l] = s[l];
+}
+// all-gather of the 5 per-rank scalars through the mailboxes: thread r stores this rank's row into rank r's table
+__global__ void k_scal_push(int nranks, int rank, const double *scal, const unsigned *status, double *const *peerScal,
+                            unsigned long long *const *peerFlag, unsigned long long epoch) {
+    const int r = threadIdx.x;
+    if (r >= nranks) return;
+    double *dst = peerScal[r] + ((epoch & 1ull) ? (size_t)nranks * 8 : 0);
+#pragma unroll
+    for (int k = 0; k < 4; k++) dst[k] = scal[k];
+    dst[4] = (double)*status;
+    flag_release(peerFlag[r], epoch);
+    (void)rank;
+}
+__global__ void k_scal_wait(int nranks, const double *mbScal, const unsigned long long *flags, unsigned long long epoch, double *scalAll) {
+    const int r = threadIdx.x;
+    if (r >= nranks) return;
+    flag_wait(flags + r, epoch);
+    const double *src = mbScal + ((epoch & 1ull) ? (size_t)nranks * 8 : 0) + (size_t)r * 8;
+#pragma unroll
+    for (int k = 0; k < 5; k++) scalAll[5 * r + k] = __ldcg(src + k);
+}
+
+// sPart (partials of the shared vertices) -> sTot (totals): NVLink peer stores (default) or NCCL point-to-point
 template <int D> int halo_exchange(mmadmm_ctx *ctx) {
     if (!ctx->dist || ctx->nShared == 0) return MMADMM_OK;
     cudaStream_t st = ctx->stream;
+    if (ctx->p2p) {
+        const unsigned long long ep = ++ctx->haloEpoch;
+        const int nNbr = (int)ctx->nbrRank.size();
+        k_halo_push<D><<<nNbr, 1024, 0, st>>>(ctx->nbrPtr_d, ctx->nbrList, ctx->sPart, ctx->peerRecv_d, ctx->peerRecvStride_d,
+                                              ctx->peerHaloFlag_d, ep);
+        k_halo_combine_p2p<D><<<cdiv(ctx->nShared, 256), 256, 0, st>>>(ctx->nShared, nNbr, ctx->contribPtr, ctx->contrib, ctx->sPart,
+                                                                      ctx->mbRecv_d, (size_t)std::max(ctx->nNbrItems, 1) * D,
+                                                                      ctx->haloFlags_d, ep, ctx->sTot);
+        ctx->launches += 2;
+        return MMADMM_OK;
+    }
     k_halo_pack<D><<<cdiv(ctx->nNbrItems, 256), 256, 0, st>>>(ctx->nNbrItems, ctx->nbrList, ctx->sPart, ctx->sendBuf);
     NcclApi &N = nccl();
     NK(N.groupStart());
@@ -1504,8 +1605,15 @@ int gather_scalars(mmadmm_ctx *ctx, int nScal) {
         CK(cudaStreamSynchronize(st));
         return MMADMM_OK;
     }
-    k_status_to_double<<<1, 1, 0, st>>>(ctx->status_d, ctx->scal_d + 4);
-    NK(nccl().allGather(ctx->scal_d, ctx->scalAll_d, 5, NCCL_FLOAT64, ctx->comm, st));
+    if (ctx->p2p) {
+        const unsigned long long ep = ++ctx->scalEpoch;
+        k_scal_push<<<1, 32, 0, st>>>(ctx->nranks, ctx->rank, ctx->scal_d, ctx->status_d, ctx->peerScal_d, ctx->peerScalFlag_d, ep);
+        k_scal_wait<<<1, 32, 0, st>>>(ctx->nranks, ctx->mbScal_d, ctx->scalFlags_d, ep, ctx->scalAll_d);
+        ctx->launches += 1;
+    } else {
+        k_status_to_double<<<1, 1, 0, st>>>(ctx->status_d, ctx->scal_d + 4);
+        NK(nccl().allGather(ctx->scal_d, ctx->scalAll_d, 5, NCCL_FLOAT64, ctx->comm, st));
+    }
     CK(cudaMemcpyAsync(ctx->scalAll_h, ctx->scalAll_d, sizeof(double) * 5 * ctx->nranks, cudaMemcpyDeviceToHost, st));
     CK(cudaStreamSynchronize(st));
     unsigned stat = 0;
@@ -1516,6 +1624,122 @@ int gather_scalars(mmadmm_ctx *ctx, int nScal) {
     }
     *ctx->status_h = stat;
     ctx->launches += 1;
+    return MMADMM_OK;
+}
+
+
+// NVLink peer-memory exchange set-up (collective over the communicator).  Every rank exports a mailbox through CUDA IPC;
+// the handles and the neighbour tables travel once through ncclAllGather; afterwards halo sums and the scalar all-gather
+// are plain stores into the neighbours' mailboxes + epoch flags (k_halo_push / k_scal_push), no NCCL call per iteration.
+// Falls back to the NCCL path on every rank if any rank cannot take part (MMADMM_NO_P2P=1, too many neighbours, IPC
+// refused by the platform).
+constexpr int P2P_MAXNBR = 16, P2P_MAXRANKS = 32, P2P_TAB = 48;
+constexpr size_t MB_OFF_HALOFLAG = 0, MB_OFF_SCALFLAG = 128, MB_OFF_SCAL = 384;
+inline size_t mb_off_recv(int nranks) { return MB_OFF_SCAL + (size_t)2 * nranks * 64; }
+
+int setup_p2p(mmadmm_ctx *ctx, int D) {
+    cudaStream_t st = ctx->stream;
+    NcclApi &N = nccl();
+    const int nranks = ctx->nranks, me = ctx->rank, nNbr = (int)ctx->nbrRank.size();
+    const char *env = getenv("MMADMM_NO_P2P");
+    bool can = !(env && env[0] == '1') && nNbr <= P2P_MAXNBR && nranks <= P2P_MAXRANKS;
+    const size_t recvHalf = (size_t)std::max(ctx->nNbrItems, 1) * D;
+    const size_t mbBytes = mb_off_recv(nranks) + sizeof(double) * 2 * recvHalf;
+    cudaIpcMemHandle_t hnd;
+    memset(&hnd, 0, sizeof(hnd));
+    if (can) {
+        if (cudaMalloc(&ctx->mailbox, mbBytes) != cudaSuccess || cudaMemset(ctx->mailbox, 0, mbBytes) != cudaSuccess ||
+            cudaIpcGetMemHandle(&hnd, ctx->mailbox) != cudaSuccess) {
+            cudaGetLastError();
+            can = false;
+        }
+    }
+    CK(cudaDeviceSynchronize());
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+    std::vector<double> tab(P2P_TAB, 0.0), all((size_t)P2P_TAB * nranks, 0.0);
+    tab[0] = can ? 1.0 : 0.0; tab[1] = nNbr; tab[2] = ctx->nNbrItems;
+    for (int q = 0; q < nNbr && q < P2P_MAXNBR; q++) { tab[3 + q] = ctx->nbrRank[q]; tab[19 + q] = ctx->nbrPtr[q]; }
+    memcpy(&tab[40], &hnd, 64);
+    double *tab_d = nullptr, *all_d = nullptr;
+    CK(cudaMalloc(&tab_d, sizeof(double) * P2P_TAB));
+    CK(cudaMalloc(&all_d, sizeof(double) * P2P_TAB * nranks));
+    auto allgather = [&]() -> int {
+        CK(cudaMemcpyAsync(tab_d, tab.data(), sizeof(double) * P2P_TAB, cudaMemcpyHostToDevice, st));
+        NK(N.allGather(tab_d, all_d, P2P_TAB, NCCL_FLOAT64, ctx->comm, st));
+        CK(cudaMemcpyAsync(all.data(), all_d, sizeof(double) * P2P_TAB * nranks, cudaMemcpyDeviceToHost, st));
+        CK(cudaStreamSynchronize(st));
+        return MMADMM_OK;
+    };
+    int rc = allgather();
+    if (rc) return rc;
+    bool every = true;
+    for (int r = 0; r < nranks; r++) every = every && all[(size_t)r * P2P_TAB] == 1.0;
+    ctx->peerMap.assign(nranks, nullptr);
+    bool opened = every;
+    if (every) {
+        for (int r = 0; r < nranks && opened; r++) {
+            if (r == me) { ctx->peerMap[r] = ctx->mailbox; continue; }
+            cudaIpcMemHandle_t h;
+            memcpy(&h, &all[(size_t)r * P2P_TAB + 40], 64);
+            if (cudaIpcOpenMemHandle(&ctx->peerMap[r], h, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) {
+                cudaGetLastError();
+                ctx->peerMap[r] = nullptr;
+                opened = false;
+            }
+        }
+    }
+    // consensus on the outcome (second, tiny collective: reuse slot 0 of the table)
+    std::vector<double> keep(all);
+    tab[0] = opened ? 1.0 : 0.0;
+    rc = allgather();
+    if (rc) return rc;
+    bool ok = true;
+    for (int r = 0; r < nranks; r++) ok = ok && all[(size_t)r * P2P_TAB] == 1.0;
+    cudaFree(tab_d); cudaFree(all_d);
+    if (!ok) {
+        for (int r = 0; r < nranks; r++)
+            if (r != me && ctx->peerMap[r]) cudaIpcCloseMemHandle(ctx->peerMap[r]);
+        ctx->peerMap.assign(nranks, nullptr);
+        if (ctx->mailbox) { cudaFree(ctx->mailbox); ctx->mailbox = nullptr; }
+        ctx->p2p = false;
+        return MMADMM_OK;
+    }
+    all = keep;
+    std::vector<double *> peerRecv(std::max(nNbr, 1), nullptr), peerScal(nranks, nullptr);
+    std::vector<size_t> peerStride(std::max(nNbr, 1), 0);
+    std::vector<unsigned long long *> peerHF(std::max(nNbr, 1), nullptr), peerSF(nranks, nullptr);
+    for (int q = 0; q < nNbr; q++) {
+        const int r = ctx->nbrRank[q];
+        const double *tr = &all[(size_t)r * P2P_TAB];
+        int qq = -1;
+        for (int k = 0; k < (int)tr[1]; k++) if ((int)tr[3 + k] == me) qq = k;
+        if (qq < 0) { ctx->err = "asymmetric neighbour lists in the partition plan"; return MMADMM_EINVAL; }
+        unsigned char *base = (unsigned char *)ctx->peerMap[r];
+        peerRecv[q] = (double *)(base + mb_off_recv(nranks)) + (size_t)tr[19 + qq] * D;
+        peerStride[q] = (size_t)std::max((int)tr[2], 1) * D;
+        peerHF[q] = (unsigned long long *)(base + MB_OFF_HALOFLAG) + qq;
+    }
+    for (int r = 0; r < nranks; r++) {
+        unsigned char *base = (unsigned char *)ctx->peerMap[r];
+        peerScal[r] = (double *)(base + MB_OFF_SCAL) + (size_t)me * 8;
+        peerSF[r] = (unsigned long long *)(base + MB_OFF_SCALFLAG) + me;
+    }
+    auto up = [&](void **dst, const void *src, size_t bytes) -> cudaError_t {
+        cudaError_t e = cudaMalloc(dst, std::max<size_t>(bytes, 8));
+        if (e != cudaSuccess) return e;
+        return cudaMemcpy(*dst, src, bytes, cudaMemcpyHostToDevice);
+    };
+    CK(up((void **)&ctx->peerRecv_d, peerRecv.data(), sizeof(double *) * peerRecv.size()));
+    CK(up((void **)&ctx->peerRecvStride_d, peerStride.data(), sizeof(size_t) * peerStride.size()));
+    CK(up((void **)&ctx->peerHaloFlag_d, peerHF.data(), sizeof(void *) * peerHF.size()));
+    CK(up((void **)&ctx->peerScal_d, peerScal.data(), sizeof(double *) * nranks));
+    CK(up((void **)&ctx->peerScalFlag_d, peerSF.data(), sizeof(void *) * nranks));
+    CK(up((void **)&ctx->nbrPtr_d, ctx->nbrPtr.data(), sizeof(int) * ctx->nbrPtr.size()));
+    ctx->haloFlags_d = (unsigned long long *)(ctx->mailbox + MB_OFF_HALOFLAG);
+    ctx->scalFlags_d = (unsigned long long *)(ctx->mailbox + MB_OFF_SCALFLAG);
+    ctx->mbScal_d = (double *)(ctx->mailbox + MB_OFF_SCAL);
+    ctx->mbRecv_d = (double *)(ctx->mailbox + mb_off_recv(nranks));
+    ctx->p2p = true;
     return MMADMM_OK;
 }
 
@@ -2087,6 +2311,10 @@ int mmadmm_create_dist(int D, int P, int E, const double *Vp, const double *Vc, 
     CK(cudaMallocHost(&ctx->scalAll_h, sizeof(double) * 5 * nranks));
     ctx->nblkSh = cdiv(std::max(ctx->nShared, 1), TPB_V);
     CK(cudaStreamSynchronize(st));
+    {
+        int rcp = setup_p2p(ctx, D);
+        if (rcp) return rcp;
+    }
     InitGlobals G{E, plan.valence.data(), P, Vp, monVertex};
     int rc = (D == 2) ? create_impl<2>(ctx, VpL.data(), Vc ? VcL.data() : nullptr, plan.Floc.data(), maskL.data(), G)
                       : create_impl<3>(ctx, VpL.data(), Vc ? VcL.data() : nullptr, plan.Floc.data(), maskL.data(), G);
@@ -2310,6 +2538,7 @@ int mmadmm_set_option(mmadmm_ctx *ctx, const char *name, int value) {
     if (!strcmp(name, "stats")) { ctx->statsOn = value != 0; return MMADMM_OK; }
     if (!strcmp(name, "prox_variant")) { ctx->proxVariant = value; return MMADMM_OK; }
     if (!strcmp(name, "iso_grid")) { ctx->isoOn = value != 0; return MMADMM_OK; }   // 0: always interpolate the full tensors
+    if (!strcmp(name, "p2p_active")) return ctx->p2p ? MMADMM_OK : MMADMM_EINVAL;   // query: NVLink peer-memory exchange in use
     if (!strcmp(name, "iso_grid_active")) return (ctx->isoOn && ctx->gridIsIso) ? MMADMM_OK : MMADMM_EINVAL;   // query
     return MMADMM_EINVAL;
 }
@@ -2325,6 +2554,10 @@ void mmadmm_destroy(mmadmm_ctx *ctx) {
     cudaFree(ctx->x); cudaFree(ctx->xPrev); cudaFree(ctx->xBar); cudaFree(ctx->Vc); cudaFree(ctx->tdiag);
     cudaFree(ctx->z); cudaFree(ctx->u); cudaFree(ctx->B); cudaFree(ctx->gs);
     cudaFree(ctx->incPtr); cudaFree(ctx->incIdx); cudaFree(ctx->vorder); cudaFree(ctx->valence_d);
+    for (size_t r = 0; r < ctx->peerMap.size(); r++)
+        if ((int)r != ctx->rank && ctx->peerMap[r]) cudaIpcCloseMemHandle(ctx->peerMap[r]);
+    cudaFree(ctx->mailbox); cudaFree(ctx->peerRecv_d); cudaFree(ctx->peerRecvStride_d); cudaFree(ctx->peerHaloFlag_d);
+    cudaFree(ctx->peerScal_d); cudaFree(ctx->peerScalFlag_d); cudaFree(ctx->nbrPtr_d);
     cudaFree(ctx->grid); cudaFree(ctx->gridIso); cudaFree(ctx->ax); cudaFree(ctx->ay); cudaFree(ctx->az);
     cudaFree(ctx->partIh); cudaFree(ctx->partDual); cudaFree(ctx->partPrimal); cudaFree(ctx->scal_d);
     if (ctx->scal_h) cudaFreeHost(ctx->scal_h);

@@ -347,8 +347,6 @@ __device__ __forceinline__ double block_grad_core(const double *z, const double 
             for (int k = 0; k < D * D; k++) M.a[k] += mPre[i].a[k];
         }
     }
-    SMat<D> Minv = sinv_scaled<D>(M, (double)D + 1);  // sic: M^{-1}/(D+1), :157
-
     SMat<D> E, Ehat;
 #pragma unroll
     for (int j = 0; j < D; j++)
@@ -364,12 +362,26 @@ __device__ __forceinline__ double block_grad_core(const double *z, const double 
     SMat<D> FJ = smul<D>(Ehat, Einv);
     double detFJ = sdet<D>(FJ);
 
-    SMat<D> MinvJt = smul_nt<D>(Minv, FJ);  // Minv * FJ^T
-    SMat<D> JMJt = smul<D>(FJ, MinvJt);
-    double trJMJt = JMJt(0, 0);
+    // Monitor-dependent pieces.  General: Minv = M^{-1}/(D+1) (sic, :157), MinvJt = Minv FJ^T, tr(FJ Minv FJ^T), det.
+    // ISO: M = ms I, so Minv = mu I with mu = 1/(ms (D+1)), tr = mu |FJ|_F^2, det(Minv) = mu^D -- the same quantities
+    // without the 3x3 inverse and four of the 3x3 products (rounding-level differences only).
+    SMat<D> Minv, MinvJt;
+    double mu = 0.0, fro = 0.0, trJMJt, detM;
+    if (ISO) {
+        mu = 1.0 / (M.a[0] * ((double)D + 1));
 #pragma unroll
-    for (int i = 1; i < D; i++) trJMJt += JMJt(i, i);
-    double detM = rsqrt(sdet<D>(Minv));   // sqrt(1/det(Minv))
+        for (int k = 0; k < D * D; k++) fro = (k == 0) ? FJ.a[0] * FJ.a[0] : fro + FJ.a[k] * FJ.a[k];
+        trJMJt = mu * fro;
+        detM = rsqrt((D == 2) ? mu * mu : mu * mu * mu);
+    } else {
+        Minv = sinv_scaled<D>(M, (double)D + 1);
+        MinvJt = smul_nt<D>(Minv, FJ);  // Minv * FJ^T
+        SMat<D> JMJt = smul<D>(FJ, MinvJt);
+        trJMJt = JMJt(0, 0);
+#pragma unroll
+        for (int i = 1; i < D; i++) trJMJt += JMJt(i, i);
+        detM = rsqrt(sdet<D>(Minv));   // sqrt(1/det(Minv))
+    }
 
     double trp, trpm1;
     pow_pair<D>(trJMJt, trp, trpm1);
@@ -379,44 +391,51 @@ __device__ __forceinline__ double block_grad_core(const double *z, const double 
     if (!GRAD) return absK * G;
 
     double sJ = d * p * theta * detM * trpm1;
-    SMat<D> dGdJ;
-#pragma unroll
-    for (int k = 0; k < D * D; k++) dGdJ.a[k] = sJ * MinvJt.a[k];
     double rsDetM = rsqrt(detM);        // detM^(1-p)
     double sDetFJ = sqrt(detFJ);        // detFJ^(p-1)
     double dGddet = p * (1.0 - 2.0 * theta) * fc.dpow * rsDetM * sDetFJ;
-    SMat<D> dGdM;
-    {
-        double s1 = -0.5 * theta * d * p * detM * trpm1;
-        // Minv^T * FJ^T * FJ * Minv
-        SMat<D> A = smul_tn<D>(Minv, smul_tn<D>(FJ, smul<D>(FJ, Minv)));
-        // note: reference order ((Minv^T FJ^T) FJ) Minv; reassociated (rounding-level) to reuse FJ*Minv
-        double s2 = (0.5 * theta * detM * trp + ((0.5 - theta) * (1.0 - p) * fc.dpow) * rsDetM * (detFJ * sDetFJ));
-#pragma unroll
-        for (int k = 0; k < D * D; k++) dGdM.a[k] = s1 * A.a[k] + s2 * Minv.a[k];
-    }
+    const double s1 = -0.5 * theta * d * p * detM * trpm1;
+    const double s2 = (0.5 * theta * detM * trp + ((0.5 - theta) * (1.0 - p) * fc.dpow) * rsDetM * (detFJ * sDetFJ));
     double basisComb[D];
 #pragma unroll
     for (int l = 0; l < D; l++) basisComb[l] = 0.0;
+    SMat<D> T;     // Einv * dGdJ * FJ with dGdJ = sJ Minv FJ^T
+    if (ISO) {
+        // dGdM = s1 mu^2 FJ^T FJ + s2 mu I and mPre[j+1] - mPre[0] = (m_{j+1} - m_0) I: only tr(dGdM) is needed
+        const double trdGdM = s1 * (mu * mu) * fro + (double)D * (s2 * mu);
 #pragma unroll
-    for (int j = 0; j < D; j++) {
-        // trace(dGdM * (mPre[j+1] - mPre[0]))
-        double tr = 0.0;
-        if (ISO) {
-            const double dm = mIso[j + 1] - mIso[0];
+        for (int j = 0; j < D; j++) {
+            const double tr = trdGdM * (mIso[j + 1] - mIso[0]);
 #pragma unroll
-            for (int a = 0; a < D; a++) tr += dGdM(a, a) * dm;
-        } else {
+            for (int l = 0; l < D; l++) basisComb[l] += Einv(j, l) * tr;
+        }
+        SMat<D> ES = smul<D>(Einv, smul_tn<D>(FJ, FJ));
+        const double sJm = sJ * mu;
+#pragma unroll
+        for (int k = 0; k < D * D; k++) T.a[k] = sJm * ES.a[k];
+    } else {
+        SMat<D> dGdJ;
+#pragma unroll
+        for (int k = 0; k < D * D; k++) dGdJ.a[k] = sJ * MinvJt.a[k];
+        // Minv^T * FJ^T * FJ * Minv; reference order ((Minv^T FJ^T) FJ) Minv, reassociated (rounding-level) to reuse FJ*Minv
+        SMat<D> A = smul_tn<D>(Minv, smul_tn<D>(FJ, smul<D>(FJ, Minv)));
+        SMat<D> dGdM;
+#pragma unroll
+        for (int k = 0; k < D * D; k++) dGdM.a[k] = s1 * A.a[k] + s2 * Minv.a[k];
+#pragma unroll
+        for (int j = 0; j < D; j++) {
+            // trace(dGdM * (mPre[j+1] - mPre[0]))
+            double tr = 0.0;
 #pragma unroll
             for (int a = 0; a < D; a++)
 #pragma unroll
                 for (int b = 0; b < D; b++) tr += dGdM(a, b) * (mPre[j + 1](b, a) - mPre[0](b, a));
-        }
 #pragma unroll
-        for (int l = 0; l < D; l++) basisComb[l] += Einv(j, l) * tr;
+            for (int l = 0; l < D; l++) basisComb[l] += Einv(j, l) * tr;
+        }
+        T = smul<D>(smul<D>(Einv, dGdJ), FJ);
     }
     double c1 = (-G + dGddet * detFJ);
-    SMat<D> T = smul<D>(smul<D>(Einv, dGdJ), FJ);
     SMat<D> vLoc;
 #pragma unroll
     for (int r = 0; r < D; r++)

@@ -1,14 +1,22 @@
 #!/bin/bash
-# usage: gpu_profile.sh <tag>   -- bench line + ncu launch list + ncu full capture of the prox kernel (C2), bench line for C4
+# usage: gpu_profile.sh <tag>   -- bench lines (c2, c3, c4, reference arm), ncu launch lists (c2, c4), ncu full captures of the
+# prox kernels (2D on c2, 3D on c4) and of the x-update
 TAG=$1; O=gpurun_out/$TAG; mkdir -p $O
 python bench.py --steps 10 --warmup 3 > $O/bench_c2.json 2> $O/bench_c2.err; echo "bench c2 rc=$?"
+python bench.py --workload c3 --steps 10 --warmup 3 > $O/bench_c3.json 2> $O/bench_c3.err; echo "bench c3 rc=$?"
 python bench.py --workload c4 --steps 6 --warmup 3 > $O/bench_c4.json 2> $O/bench_c4.err; echo "bench c4 rc=$?"
 python bench.py --impl reference --steps 4 --warmup 3 > $O/bench_ref.json 2> $O/bench_ref.err; echo "bench ref rc=$?"
 CMD="python bench.py --steps 3 --warmup 3 --no-cpu-baseline"
 $CMD > $O/plain.log 2>&1 &&
 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $O/launches_c2.csv $CMD > $O/ncu_list.log 2>&1
-echo "ncu list rc=$?"
+echo "ncu list c2 rc=$?"
 ncu --set full --clock-control none --import-source on -k regex:k_prox -s 8 -c 1 -f -o $O/prof_c2 $CMD > $O/ncu_full.log 2>&1
-echo "ncu full rc=$?"
+echo "ncu full c2 rc=$?"
 ncu --set full --clock-control none -k regex:k_xupdate -s 12 -c 2 -f -o $O/prof_xup $CMD > $O/ncu_xup.log 2>&1
 echo "ncu xup rc=$?"
+CMD4="python bench.py --workload c4 --steps 3 --warmup 3 --no-cpu-baseline"
+$CMD4 > $O/plain_c4.log 2>&1 &&
+ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $O/launches_c4.csv $CMD4 > $O/ncu_list_c4.log 2>&1
+echo "ncu list c4 rc=$?"
+ncu --set full --clock-control none --import-source on -k regex:k_prox -s 8 -c 1 -f -o $O/prof_c4 $CMD4 > $O/ncu_full_c4.log 2>&1
+echo "ncu full c4 rc=$?"

@@ -208,4 +208,4 @@ def test_isotropic_grid_fast_path_is_equivalent(D, nx, kind, iso):
         xs.append(mesh.Vp.copy())
         s.close()
     assert np.array_equal(out[0], out[1])
-    assert rel(xs[0], xs[1]) < 1e-13
+    assert rel(xs[0], xs[1]) < 1e-10      # the scalar path also skips the 3x3 inverse and products of M = m I (rounding-level)
