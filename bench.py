@@ -262,7 +262,7 @@ def main():
     SAFE = safe_steps(args.workload, W)
 
     def timed(k, sync_vp):
-        tot = dict(ms=0.0, iters=0, ih=[], launches=0, timing={}, hist=0, clocks=[], epochs=0)
+        tot = dict(ms=0.0, iters=0, ih=[], launches=0, timing={}, hist=0, clocks=[], epochs=0, step_ms=[])
         done = 0
         while done < k:
             solver = fresh_solver()
@@ -273,15 +273,19 @@ def main():
             solver.timing(reset=True)
             st0 = solver.stats()
             ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            # NVML set-up (nvmlInit takes milliseconds) happens BEFORE the barrier: anything between the barrier and ev0 on
+            # one rank shows up as waiting time inside the first collective of every other rank.
+            sampler = ClockSampler(local) if rank == 0 else None   # rank 0 reports; NVML polling from 8 processes contends on a driver lock
             torch.cuda.synchronize()
             if dist:
                 dist.barrier()
                 torch.cuda.synchronize()
-            sampler = ClockSampler(local) if rank == 0 else None   # rank 0 reports; NVML polling from 8 processes contends on a driver lock
+            marks = [torch.cuda.Event(enable_timing=True) for _ in range(kk)]
             ev0.record(stream)
-            for _ in range(kk):
+            for i in range(kk):
                 tot["ih"].append(solver.step(PARAMS["admm_iter"], PARAMS["tol"]))
                 tot["iters"] += solver.last["iters"]
+                marks[i].record(stream)
             ev1.record(stream)
             torch.cuda.synchronize()
             if dist:
@@ -289,6 +293,7 @@ def main():
                 torch.cuda.synchronize()
             tot["clocks"].append(sampler.stop() if sampler else {})
             ms = ev0.elapsed_time(ev1)
+            tot["step_ms"] += [round(a.elapsed_time(b), 4) for a, b in zip([ev0] + marks[:-1], marks)]   # this rank, per step
             if dist:   # device time, max over ranks
                 tms = torch.tensor([ms], dtype=torch.float64, device="cuda")
                 dist.all_reduce(tms, op=dist.ReduceOp.MAX)
@@ -357,6 +362,7 @@ def main():
         "fp64": {"peak_tflops_measured": fp64_peak, "how": "DFMA microbenchmark, 8 independent chains per thread (mmadmm_measure_fp64_peak); "
                  "the prox kernel's FP64 pipe utilisation is the ncu figure sm__inst_executed_pipe_fp64 in profiles/"},
         "phase_ms_per_step": {k: v[0] / K for k, v in r["timing"].items()},
+        "step_ms_rank0": r["step_ms"],
         "clocks": r["clocks"],
         "init_seconds": init_s, "energy_initial": e0, "energy_last": r2["ih"][-1],
         "warmup_steps": warm,
