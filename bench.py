@@ -72,6 +72,22 @@ def algorithmic_bytes_prox(D, P, E, g):
     return 8 * (2 * n * n + 3 * n) + 4 * (D + 1) + 8 * D * D * (g + 1) ** D / E
 
 
+def ncu_traffic(workload_name):
+    """dram__bytes_read.sum + dram__bytes_write.sum of the prox kernel, per launch, from the committed `ncu --set full`
+    capture of this workload (profiles/*_prof_<workload>_raw.json, newest round), or None."""
+    import glob
+    units = {"Gbyte": 1e9, "Mbyte": 1e6, "Kbyte": 1e3, "byte": 1.0}
+    for f in sorted(glob.glob(os.path.join(ROOT, "profiles", f"*_prof_{workload_name}_raw.json")), reverse=True):
+        try:
+            for m in json.load(open(f)):
+                if "k_prox" in m.get("kernel", ""):
+                    rd, wr = m["dram__bytes_read.sum"], m["dram__bytes_write.sum"]
+                    return float(rd[0]) * units[rd[1]] + float(wr[0]) * units[wr[1]], os.path.relpath(f, ROOT)
+        except Exception:
+            pass
+    return None, None
+
+
 def peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -333,6 +349,7 @@ def main():
     fp64_peak = mm.measure_fp64_peak(local)
     bytes_per_launch = algorithmic_bytes_prox(D, P, E, g) * Eloc   # this rank's launch (rank 0 reports)
     achieved = bytes_per_launch / (prox_ms / max(prox_cnt, 1) / 1e3) / 1e9
+    traffic, traffic_src = ncu_traffic(args.workload) if world == 1 and not args.nx else (None, None)
     hist = r["hist"]
     kbar = float((hist * np.arange(52)).sum() / max(hist.sum(), 1))
     line = {
@@ -357,7 +374,7 @@ def main():
                 "the step takes no array inputs after construction (state is device-resident), scalars only"},
         "gpu_launches": launches,
         "roofline": {"kernel": "k_prox", "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                     "traffic": None, "peak_source": peak_src, "algorithmic_bytes_per_launch": bytes_per_launch,
+                     "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src, "algorithmic_bytes_per_launch": bytes_per_launch,
                      "avg_launch_ms": prox_ms / max(prox_cnt, 1), "launches_timed": prox_cnt},
         "fp64": {"peak_tflops_measured": fp64_peak, "how": "DFMA microbenchmark, 8 independent chains per thread (mmadmm_measure_fp64_peak); "
                  "the prox kernel's FP64 pipe utilisation is the ncu figure sm__inst_executed_pipe_fp64 in profiles/"},

@@ -473,7 +473,7 @@ int mmadmm_measure_fp64_peak(int device, double *tflops) {
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
     double *out = nullptr;
     if (cudaMalloc(&out, 8) != cudaSuccess) return MMADMM_ECUDA;
-    const int iters = 1 << 16, grid = sms * 8, tpb = 256;
+    const int iters = 1 << 13, grid = sms * 8, tpb = 256;   // ~1 ms per launch
     cudaEvent_t e0, e1;
     cudaEventCreate(&e0); cudaEventCreate(&e1);
     k_dfma_peak<<<grid, tpb>>>(iters, 1.0, out);
