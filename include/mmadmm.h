@@ -67,6 +67,15 @@ int mmadmm_get_x(mmadmm_ctx *ctx, double *x);
 /* Same, but into a caller-provided *device* pointer (no host copy). */
 int mmadmm_get_x_device(mmadmm_ctx *ctx, double *x_dev);
 
+/* Same into a COLUMN-major P x D host array -- the storage of the caller's Eigen::MatrixXd Vp that Mesh::updateAfterStep
+ * writes (src/Mesh.cpp:1030-1035): the transposition runs on the device, the copy goes straight into the caller's matrix.
+ * Single-GPU contexts only. */
+int mmadmm_get_x_colmajor(mmadmm_ctx *ctx, double *VpColMajor);
+/* Page-lock / unlock a caller-owned host range (cudaHostRegister) so that the per-step write-back of Vp runs at PCIe speed.
+ * Optional: failure only means the copy is staged by the driver. */
+int mmadmm_host_register(void *p, unsigned long bytes);
+int mmadmm_host_unregister(void *p);
+
 /* The re-oriented connectivity (the reference permutes the caller's F in place). */
 int mmadmm_get_F(mmadmm_ctx *ctx, int *F);
 

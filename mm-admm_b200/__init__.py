@@ -28,7 +28,7 @@ ERRORS = {1: "EINVAL", 2: "ECUDA", 3: "EINVERTED", 4: "ESINGULAR", 5: "ENCCL", 6
 
 # every symbol include/mmadmm.h declares (checked by tests/test_abi.py)
 ABI_SYMBOLS = [
-    "mmadmm_create", "mmadmm_set_dt", "mmadmm_step", "mmadmm_energy", "mmadmm_get_x", "mmadmm_get_x_device", "mmadmm_get_F",
+    "mmadmm_create", "mmadmm_set_dt", "mmadmm_step", "mmadmm_energy", "mmadmm_get_x", "mmadmm_get_x_device", "mmadmm_get_x_colmajor", "mmadmm_host_register", "mmadmm_host_unregister", "mmadmm_get_F",
     "mmadmm_grid_dims", "mmadmm_get_state", "mmadmm_eval_monitor", "mmadmm_block_grad", "mmadmm_block_grad_at", "mmadmm_get_stats",
     "mmadmm_get_timing", "mmadmm_set_option", "mmadmm_stream", "mmadmm_destroy", "mmadmm_last_error",
     "mmadmm_version", "mmadmm_plan_create", "mmadmm_plan_sizes", "mmadmm_plan_get", "mmadmm_plan_destroy",
@@ -72,6 +72,9 @@ def lib():
         L.mmadmm_get_x.argtypes = [vp, _c_dp]
         L.mmadmm_get_x_device.argtypes = [vp, vp]
         L.mmadmm_get_F.argtypes = [vp, _c_ip]
+        L.mmadmm_get_x_colmajor.argtypes = [vp, _c_dp]
+        L.mmadmm_host_register.argtypes = [vp, C.c_ulong]
+        L.mmadmm_host_unregister.argtypes = [vp]
         L.mmadmm_grid_dims.argtypes = [vp, _c_ip]
         L.mmadmm_get_state.argtypes = [vp, C.c_int, _c_dp]
         L.mmadmm_eval_monitor.argtypes = [vp, _c_dp, C.c_int, _c_dp]

@@ -1236,6 +1236,13 @@ template <int D> __global__ void k_iso_extract(size_t rows, const double *grid, 
     if (!ok) *flag = 0;
 }
 
+// x (P x D interleaved) -> column-major P x D (Eigen's default storage of the caller's Vp)
+__global__ void k_x_to_colmajor(int P, int D, const double *x, double *xT) {
+    int p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= P) return;
+    for (int l = 0; l < D; l++) xT[(size_t)l * P + p] = x[(size_t)D * p + l];
+}
+
 // ---- unit-parity helpers ----
 template <int D> __global__ void k_eval_monitor(MonGrid mg, int npts, const double *pts, double *out) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -1331,6 +1338,7 @@ struct mmadmm_ctx {
     double *z = nullptr, *u = nullptr, *B = nullptr, *gs = nullptr;
     int *incPtr = nullptr, *incIdx = nullptr, *vorder = nullptr, *valence_d = nullptr;
     double *grid = nullptr, *ax = nullptr, *ay = nullptr, *az = nullptr;
+    double *xT = nullptr;               // column-major staging of x for mmadmm_get_x_colmajor
     double *gridIso = nullptr;          // scalar monitor grid (isotropic monitors only)
     bool gridIsIso = false, isoOn = true;
     int nx = 0, ny = 0, nz = 0;
@@ -2372,6 +2380,29 @@ int mmadmm_get_x(mmadmm_ctx *ctx, double *x) {
     CK(cudaFree(xg));
     return MMADMM_OK;
 }
+int mmadmm_get_x_colmajor(mmadmm_ctx *ctx, double *VpColMajor) {
+    if (!ctx || !VpColMajor || ctx->dist) return MMADMM_EINVAL;
+    CK(cudaSetDevice(ctx->device));
+    const size_t bytes = sizeof(double) * (size_t)ctx->P * ctx->D;
+    if (!ctx->xT) CK(cudaMalloc(&ctx->xT, bytes));
+    k_x_to_colmajor<<<cdiv(ctx->P, 256), 256, 0, ctx->stream>>>(ctx->P, ctx->D, ctx->x, ctx->xT);
+    ctx->launches++;
+    CK(cudaMemcpyAsync(VpColMajor, ctx->xT, bytes, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    return MMADMM_OK;
+}
+
+int mmadmm_host_register(void *p, unsigned long bytes) {
+    if (!p || !bytes) return MMADMM_EINVAL;
+    if (cudaHostRegister(p, bytes, cudaHostRegisterDefault) != cudaSuccess) { cudaGetLastError(); return MMADMM_ECUDA; }
+    return MMADMM_OK;
+}
+int mmadmm_host_unregister(void *p) {
+    if (!p) return MMADMM_EINVAL;
+    if (cudaHostUnregister(p) != cudaSuccess) { cudaGetLastError(); return MMADMM_ECUDA; }
+    return MMADMM_OK;
+}
+
 int mmadmm_get_x_local(mmadmm_ctx *ctx, double *xGlobal) {
     if (!ctx || !xGlobal) return MMADMM_EINVAL;
     if (!ctx->dist) return mmadmm_get_x(ctx, xGlobal);
@@ -2558,7 +2589,7 @@ void mmadmm_destroy(mmadmm_ctx *ctx) {
         if ((int)r != ctx->rank && ctx->peerMap[r]) cudaIpcCloseMemHandle(ctx->peerMap[r]);
     cudaFree(ctx->mailbox); cudaFree(ctx->peerRecv_d); cudaFree(ctx->peerRecvStride_d); cudaFree(ctx->peerHaloFlag_d);
     cudaFree(ctx->peerScal_d); cudaFree(ctx->peerScalFlag_d); cudaFree(ctx->nbrPtr_d);
-    cudaFree(ctx->grid); cudaFree(ctx->gridIso); cudaFree(ctx->ax); cudaFree(ctx->ay); cudaFree(ctx->az);
+    cudaFree(ctx->grid); cudaFree(ctx->gridIso); cudaFree(ctx->xT); cudaFree(ctx->ax); cudaFree(ctx->ay); cudaFree(ctx->az);
     cudaFree(ctx->partIh); cudaFree(ctx->partDual); cudaFree(ctx->partPrimal); cudaFree(ctx->scal_d);
     if (ctx->scal_h) cudaFreeHost(ctx->scal_h);
     cudaFree(ctx->status_d);

@@ -50,6 +50,7 @@ public:
         meshInit(Xp, Xp, F, boundaryMask, M, numThreads, rho, w, tau, gradUse);
     }
     ~Mesh() {
+        if (vpRegistered) mmadmm_host_unregister(Vp->data());
         if (ctx) mmadmm_destroy(ctx);
         delete monitorEvals;
     }
@@ -105,7 +106,8 @@ public:
         // the reference permutes the caller's F (positive orientation)
         check(mmadmm_get_F(ctx, f.data()), "mmadmm_get_F");
         for (int e = 0; e < E; e++) for (int v = 0; v <= D; v++) F(e, v) = f[(size_t)e * (D + 1) + v];
-        xHost.resize((size_t)P * D);
+        // page-lock the caller's Vp: updateAfterStep then copies straight into it at PCIe speed
+        vpRegistered = mmadmm_host_register(Xp.data(), sizeof(double) * (unsigned long)P * D) == MMADMM_OK;
     }
 
     // evalMonitorOnGrid at one point (src/MeshInterpolator.cpp:286-342): the GPU-resident interpolation
@@ -135,11 +137,8 @@ public:
         (void)dt; (void)xPrev; (void)x;
         syncVp();
     }
-    void syncVp() {
-        check(mmadmm_get_x(ctx, xHost.data()), "mmadmm_get_x");
-        const int P = Vp->rows();
-        for (int l = 0; l < D; l++) for (int p = 0; p < P; p++) (*Vp)(p, l) = xHost[(size_t)p * D + l];
-    }
+    // Vp is column-major (Eigen's default): the transposition runs on the device
+    void syncVp() { check(mmadmm_get_x_colmajor(ctx, Vp->data()), "mmadmm_get_x_colmajor"); }
 
     // result writers, formats of src/Mesh.cpp:1049-1095
     void outputSimplices(const char *fname) {
@@ -193,7 +192,7 @@ public:
     double Ihcur = 0, Ihprev = 0;
 
 private:
-    vector<double> xHost;
+    bool vpRegistered = false;
 };
 
 #endif
