@@ -206,6 +206,7 @@ def main():
     ap.add_argument("--nx", type=int, default=0, help="override the mesh resolution (debugging)")
     ap.add_argument("--cpu-nx", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--opt", action="append", default=[], help="library option name=value (A/B runs), e.g. b_evict_first=1")
     ap.add_argument("--iso-grid", type=int, default=1, help="0: disable the scalar monitor-grid fast path (A/B runs)")
     ap.add_argument("--prox-variant", type=int, default=-1, help="prox kernel tile/occupancy variant (debugging; -1 = library default)")
     args = ap.parse_args()
@@ -260,6 +261,8 @@ def main():
             solver.set_option("prox_variant", args.prox_variant)
         if not args.iso_grid:
             solver.set_option("iso_grid", 0)
+        for kv in args.opt:
+            solver.set_option(kv.split("=")[0], int(kv.split("=")[1]))
         state["e0"] = solver.getEnergy()
         warm = []
         for _ in range(W):

@@ -1056,21 +1056,29 @@ __global__ void __launch_bounds__(1024) k_finalize(int n0, const double *p0, int
 //   UZERO: u == 0 (before the first step; u planes not read)
 //   PRIMAL: also accumulate ||D x - z||^2 = sum_p sum_{slots of p} |x_p - z_slot|^2 from the z values already in
 //           registers (src/MeshIntegrator.cpp:162) -> per-block partials
-template <int D, bool ZSRC, bool UZERO, bool PRIMAL>
+//   UREC : the dual planes are not read either.  usum_p = sum of u over the slots of p is carried per vertex: the prox sweep
+//          set u+ = (x_p + u) - z+ in every slot, so usum+ = usum + val_p*x_p - zsum_p, and the right-hand side is
+//          w(w(zsum - usum+)).  Vertices shared with another rank keep the slot-by-slot form (their sums are partial).
+//          The exact form (UREC = false) also stores usum, which re-anchors the recurrence ("usum_period" option).
+template <int D, bool ZSRC, bool UZERO, bool PRIMAL, bool UREC>
 __global__ void __launch_bounds__(TPB_V) k_xupdate(int P, size_t Es, const int *incPtr, const int *incIdx, const double *z,
                                                    const double *u, const double *zsrc, const double *xBar,
                                                    const double *tdiag, double m, double dtsq, double w, double *x,
-                                                   double *partPrimal, const int *sharedSlot, double *sPart, const int *vorder) {
+                                                   double *partPrimal, const int *sharedSlot, double *sPart, const int *vorder,
+                                                   double *usum) {
+    static_assert(!UREC || (PRIMAL && !ZSRC && !UZERO), "the recurrence belongs to the update that follows a prox sweep");
     __shared__ double red[32];
     const int tix = blockIdx.x * TPB_V + threadIdx.x;
     double prim = 0.0;
     if (tix < P) {
         const int p = vorder[tix];   // vertices in the order of their first incident element: neighbouring threads
                                      // read neighbouring element slots in every plane (2.4x less DRAM traffic)
-        double s[D], zs[D], xn[D];
+        double s[D], zs[D], xn[D], us[D];
 #pragma unroll
-        for (int l = 0; l < D; l++) { s[l] = 0.0; zs[l] = ZSRC ? zsrc[(size_t)D * p + l] : 0.0; }
+        for (int l = 0; l < D; l++) { s[l] = 0.0; us[l] = 0.0; zs[l] = ZSRC ? zsrc[(size_t)D * p + l] : 0.0; }
         const int k0 = incPtr[p], k1 = incPtr[p + 1];
+        const int sh = sharedSlot ? sharedSlot[p] : -1;
+        const bool rec = UREC && sh < 0;
         // slots in chunks of CH: all index loads, then all value loads, then the (ordered) accumulation
         constexpr int CH = 4;
         for (int kb = k0; kb < k1; kb += CH) {
@@ -1086,17 +1094,31 @@ __global__ void __launch_bounds__(TPB_V) k_xupdate(int P, size_t Es, const int *
                 for (int l = 0; l < D; l++) {
                     const size_t idx = tm_index(e, D * v + l, D * (D + 1));
                     zv[j][l] = (ZSRC || slot[j] < 0) ? zs[l] : __ldg(z + idx);
-                    uv[j][l] = (UZERO || slot[j] < 0) ? 0.0 : __ldg(u + idx);
+                    uv[j][l] = (UZERO || rec || slot[j] < 0) ? 0.0 : __ldg(u + idx);
                 }
             }
 #pragma unroll
             for (int j = 0; j < CH; j++)
                 if (slot[j] >= 0) {
 #pragma unroll
-                    for (int l = 0; l < D; l++) s[l] += w * (w * (zv[j][l] - uv[j][l]));
+                    for (int l = 0; l < D; l++) {
+                        if (rec) s[l] += zv[j][l];   // zsum
+                        else { s[l] += w * (w * (zv[j][l] - uv[j][l])); us[l] += uv[j][l]; }
+                    }
                 }
         }
-        const int sh = sharedSlot ? sharedSlot[p] : -1;
+        if (PRIMAL && sh < 0) {
+#pragma unroll
+            for (int l = 0; l < D; l++) {
+                if (rec) {
+                    const double un = (usum[(size_t)D * p + l] + (double)(k1 - k0) * x[(size_t)D * p + l]) - s[l];
+                    usum[(size_t)D * p + l] = un;
+                    s[l] = w * (w * (s[l] - un));
+                } else {
+                    usum[(size_t)D * p + l] = us[l];
+                }
+            }
+        }
         if (sh >= 0) {   // shared with another rank: only the partial sum is known here (finished by k_xfinish)
 #pragma unroll
             for (int l = 0; l < D; l++) sPart[(size_t)sh * D + l] = s[l];
@@ -1218,6 +1240,34 @@ __global__ void __launch_bounds__(TPB_V) k_predict_extrap(size_t N, const double
     double xv = x[i];
     xBar[i] = 2 * xv - xPrev[i];
     xPrev[i] = xv;
+}
+
+// First x-solve of a step (src/MeshIntegrator.cpp:137-138) without touching element state: z = D zsrc there, so
+// sum_slots w(w(z - u)) = w(w(val_p*zsrc_p - usum_p)) with the per-vertex dual sums that k_xupdate keeps.  One thread per
+// component, natural vertex order (everything coalesced).  EXTRAP: fused with K7 (xBar = 2x - xPrev, xPrev = x; zsrc = xBar).
+// Vertices shared with another rank only get the predictor; their x comes from k_xupdate<ZSRC> over the shared list.
+template <int D, bool EXTRAP>
+__global__ void __launch_bounds__(TPB_V) k_xfirst(size_t N, const int *incPtr, const double *usum, const double *zsrc, double *xBar,
+                                                  double *xPrev, const double *tdiag, double m, double dtsq, double w, double *x,
+                                                  const int *sharedSlot) {
+    const size_t i = (size_t)blockIdx.x * TPB_V + threadIdx.x;
+    if (i >= N) return;
+    const int p = (int)(i / D);
+    double xb, zs;
+    if (EXTRAP) {
+        const double xv = x[i];
+        xb = 2 * xv - xPrev[i];
+        xBar[i] = xb;
+        xPrev[i] = xv;
+        zs = xb;
+    } else {
+        xb = xBar[i];
+        zs = zsrc[i];
+    }
+    if (sharedSlot && sharedSlot[p] >= 0) return;
+    const double val = (double)(incPtr[p + 1] - incPtr[p]);
+    const double sv = w * (w * (val * zs - usum[i]));
+    x[i] = ((m * xb) + dtsq * sv) / tdiag[p];
 }
 
 // Isotropy of the monitor grid: flag stays 1 iff every row is m*I bitwise (equal diagonal, zero off-diagonal); the scalars
@@ -1347,6 +1397,9 @@ struct mmadmm_ctx {
     double Ehat[9] = {0}, dpow = 0;
     bool stepTaken = false, hessComputed = false;
     int stepsTaken = 0;
+    double *usum = nullptr;   // per-vertex sum of the dual over the vertex's slots (k_xupdate / k_xfirst)
+    int usumPeriod = 64;      // every usumPeriod-th x-update after a prox sweep re-gathers usum exactly; 0: slot-by-slot x-updates only
+    int usumAge = 0;
     int nblkE = 0, nblkV = 0, nblkProx = 0;
     double *partIh = nullptr, *partDual = nullptr, *partPrimal = nullptr, *scal_d = nullptr, *scal_h = nullptr;
     unsigned *status_d = nullptr, *status_h = nullptr;
@@ -2002,6 +2055,8 @@ int create_impl(mmadmm_ctx *ctx, const double *Vp, const double *Vc, const int *
     CK(cudaMalloc(&ctx->gs, sizeof(double) * NZ));
     CK(cudaMemsetAsync(ctx->z, 0, sizeof(double) * NZ, st));
     CK(cudaMemsetAsync(ctx->u, 0, sizeof(double) * NZ, st));
+    CK(cudaMalloc(&ctx->usum, sizeof(double) * (size_t)P * D));
+    CK(cudaMemsetAsync(ctx->usum, 0, sizeof(double) * (size_t)P * D, st));
     CK(cudaMemsetAsync(ctx->B, 0, sizeof(double) * NZ * n, st));
     k_fill_identity<<<cdiv(ctx->Es, 256), 256, 0, st>>>(ctx->Es, n, ctx->B);   // hessInvs = I (src/Mesh.cpp:456-464)
     ctx->launches++;
@@ -2109,13 +2164,21 @@ template <> int launch_prox<3>(mmadmm_ctx *ctx, const ElemArgs<3> &a) {
 }
 
 // x-update (+ primal residual partials).  Distributed: local kernel -> shared-vertex partials -> exchange -> k_xfinish.
-template <int D, bool ZSRC, bool UZERO, bool PRIMAL>
-int launch_xupdate_t(mmadmm_ctx *ctx, const double *zsrc) {
+//   sharedOnly: the vertices that are not shared were already solved by k_xfirst
+template <int D, bool ZSRC, bool UZERO, bool PRIMAL, bool UREC = false>
+int launch_xupdate_t(mmadmm_ctx *ctx, const double *zsrc, bool sharedOnly = false) {
     const double dtsq = ctx->dt * ctx->dt;
-    k_xupdate<D, ZSRC, UZERO, PRIMAL><<<ctx->nblkV, TPB_V, 0, ctx->stream>>>(
-        ctx->P, ctx->Es, ctx->incPtr, ctx->incIdx, ctx->z, ctx->u, zsrc, ctx->xBar, ctx->tdiag, ctx->m, dtsq, ctx->w, ctx->x,
-        ctx->partPrimal, ctx->dist ? ctx->sharedSlot : nullptr, ctx->sPart, ctx->vorder);
-    ctx->launches++;
+    if (!sharedOnly) {
+        k_xupdate<D, ZSRC, UZERO, PRIMAL, UREC><<<ctx->nblkV, TPB_V, 0, ctx->stream>>>(
+            ctx->P, ctx->Es, ctx->incPtr, ctx->incIdx, ctx->z, ctx->u, zsrc, ctx->xBar, ctx->tdiag, ctx->m, dtsq, ctx->w, ctx->x,
+            ctx->partPrimal, ctx->dist ? ctx->sharedSlot : nullptr, ctx->sPart, ctx->vorder, ctx->usum);
+        ctx->launches++;
+    } else if (ctx->dist && ctx->nShared > 0) {
+        k_xupdate<D, ZSRC, UZERO, PRIMAL, UREC><<<ctx->nblkSh, TPB_V, 0, ctx->stream>>>(
+            ctx->nShared, ctx->Es, ctx->incPtr, ctx->incIdx, ctx->z, ctx->u, zsrc, ctx->xBar, ctx->tdiag, ctx->m, dtsq, ctx->w, ctx->x,
+            ctx->partPrimal, ctx->sharedSlot, ctx->sPart, ctx->sharedIdx, ctx->usum);
+        ctx->launches++;
+    }
     if (ctx->dist && ctx->nShared > 0) {
         int rc = halo_exchange<D>(ctx);
         if (rc) return rc;
@@ -2133,6 +2196,8 @@ template <int D> int step_impl(mmadmm_ctx *ctx, int nIters, double tol, double *
     const size_t NV = (size_t)P * D;
     ElemArgs<D> a = ctx->elemArgs<D>(tol / 100);   // BFGS tolerance tol/100, 50 iterations (src/Mesh.cpp:968)
     const int gE = ctx->nblkE, gV = ctx->nblkV;
+    const bool fast = ctx->usumPeriod > 0;   // x-updates on the per-vertex dual sums (k_xfirst, k_xupdate<UREC>)
+    bool firstSolved = false;
 
     // predictX (src/Mesh.cpp:649-674) fused with xPrev = x (src/MeshIntegrator.cpp:119)
     ctx->phaseBegin(0);
@@ -2148,6 +2213,11 @@ template <int D> int step_impl(mmadmm_ctx *ctx, int nIters, double tol, double *
                                                                          ctx->xBar, ctx->xPrev);
             ctx->launches++;
         }
+    } else if (fast) {   // predictor and first x-solve in one vertex-local pass
+        k_xfirst<D, true><<<cdiv(NV, TPB_V), TPB_V, 0, st>>>(NV, ctx->incPtr, ctx->usum, nullptr, ctx->xBar, ctx->xPrev, ctx->tdiag, ctx->m,
+                                                             ctx->dt * ctx->dt, ctx->w, ctx->x, ctx->dist ? ctx->sharedSlot : nullptr);
+        ctx->launches += 1;
+        firstSolved = true;
     } else {
         k_predict_extrap<<<cdiv(NV, TPB_V), TPB_V, 0, st>>>(NV, ctx->x, ctx->xBar, ctx->xPrev);
         ctx->launches += 1;
@@ -2160,7 +2230,12 @@ template <int D> int step_impl(mmadmm_ctx *ctx, int nIters, double tol, double *
     // first x-solve (:137-138)
     ctx->phaseBegin(2);
     {
-        int rcx = uZero ? launch_xupdate_t<D, true, true, false>(ctx, zsrc) : launch_xupdate_t<D, true, false, false>(ctx, zsrc);
+        if (fast && !firstSolved) {
+            k_xfirst<D, false><<<cdiv(NV, TPB_V), TPB_V, 0, st>>>(NV, ctx->incPtr, ctx->usum, zsrc, ctx->xBar, ctx->xPrev, ctx->tdiag, ctx->m,
+                                                                  ctx->dt * ctx->dt, ctx->w, ctx->x, ctx->dist ? ctx->sharedSlot : nullptr);
+            ctx->launches += 1;
+        }
+        int rcx = uZero ? launch_xupdate_t<D, true, true, false>(ctx, zsrc, fast) : launch_xupdate_t<D, true, false, false>(ctx, zsrc, fast);
         if (rcx) return rcx;
     }
     ctx->phaseEnd();
@@ -2184,7 +2259,9 @@ template <int D> int step_impl(mmadmm_ctx *ctx, int nIters, double tol, double *
         ctx->stepTaken = true;
         ctx->phaseBegin(2);
         {
-            int rcx = launch_xupdate_t<D, false, false, true>(ctx, nullptr);
+            const bool rec = fast && ctx->usumAge + 1 < ctx->usumPeriod;
+            ctx->usumAge = rec ? ctx->usumAge + 1 : 0;
+            int rcx = rec ? launch_xupdate_t<D, false, false, true, true>(ctx, nullptr) : launch_xupdate_t<D, false, false, true>(ctx, nullptr);
             if (rcx) return rcx;
         }
         ctx->phaseEnd();
@@ -2592,6 +2669,11 @@ int mmadmm_set_option(mmadmm_ctx *ctx, const char *name, int value) {
     if (!strcmp(name, "timing")) { ctx->timingOn = value != 0; return MMADMM_OK; }
     if (!strcmp(name, "stats")) { ctx->statsOn = value != 0; return MMADMM_OK; }
     if (!strcmp(name, "prox_variant")) { ctx->proxVariant = value; return MMADMM_OK; }
+    if (!strcmp(name, "usum_period")) {
+        if (value < 0) return MMADMM_EINVAL;
+        ctx->usumPeriod = value; ctx->usumAge = 0;
+        return MMADMM_OK;
+    }
     if (!strcmp(name, "iso_grid")) { ctx->isoOn = value != 0; return MMADMM_OK; }   // 0: always interpolate the full tensors
     if (!strcmp(name, "p2p_active")) return ctx->p2p ? MMADMM_OK : MMADMM_EINVAL;   // query: NVLink peer-memory exchange in use
     if (!strcmp(name, "iso_grid_active")) return (ctx->isoOn && ctx->gridIsIso) ? MMADMM_OK : MMADMM_EINVAL;   // query
@@ -2607,7 +2689,7 @@ void mmadmm_destroy(mmadmm_ctx *ctx) {
     for (int v = 0; v < 4; v++) cudaFree(ctx->F[v]);
     cudaFree(ctx->mask); cudaFree(ctx->fixedBits); cudaFree(ctx->nonIntBits);
     cudaFree(ctx->x); cudaFree(ctx->xPrev); cudaFree(ctx->xBar); cudaFree(ctx->Vc); cudaFree(ctx->tdiag);
-    cudaFree(ctx->z); cudaFree(ctx->u); cudaFree(ctx->B); cudaFree(ctx->gs);
+    cudaFree(ctx->z); cudaFree(ctx->u); cudaFree(ctx->usum); cudaFree(ctx->B); cudaFree(ctx->gs);
     cudaFree(ctx->incPtr); cudaFree(ctx->incIdx); cudaFree(ctx->vorder); cudaFree(ctx->valence_d);
     for (size_t r = 0; r < ctx->peerMap.size(); r++)
         if ((int)r != ctx->rank && ctx->peerMap[r]) cudaIpcCloseMemHandle(ctx->peerMap[r]);

@@ -209,3 +209,27 @@ def test_isotropic_grid_fast_path_is_equivalent(D, nx, kind, iso):
         s.close()
     assert np.array_equal(out[0], out[1])
     assert rel(xs[0], xs[1]) < 1e-10      # the scalar path also skips the 3x3 inverse and products of M = m I (rounding-level)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("D,nx,kind", [(2, 24, 4), (3, 6, 4), (2, 20, 2)])
+def test_dual_sum_xupdates_match_slotwise(D, nx, kind):
+    """The x-updates work on per-vertex sums of the dual (k_xfirst, k_xupdate<UREC>) instead of re-reading the u planes; the
+    sums follow a recurrence that is re-anchored every `usum_period` updates.  Period 0 is the slot-by-slot form of
+    src/MeshIntegrator.cpp:137-138,159-160; every period must give the same trajectory to rounding."""
+    Vp, F, mask = mm.generate_uniform_rect_mesh(D, nx, nx, nx if D == 3 else 0)
+    mon = mm.TestMonitor(D, kind).evaluate_at_vertices(Vp)
+    xs, Is, us = [], [], []
+    for period in (0, 1, 3, 64):
+        mesh = mm.Mesh(Vp.copy(), F.copy(), mask, mon, rho=50.0, tau=0.5)
+        s = mm.MeshIntegrator(0.025, mesh)
+        s.set_option("usum_period", period)
+        Is.append([s.step(10, 1e-3) for _ in range(8)])      # several ADMM iterations per step: the recurrence runs across them too
+        assert s.stats()["admm_iters"] > 8
+        xs.append(mesh.Vp.copy())
+        us.append(s.state(1))
+        s.close()
+    for k in range(1, 4):
+        assert rel(xs[0], xs[k]) < 1e-12
+        assert np.allclose(Is[0], Is[k], rtol=1e-12, atol=0)
+        assert np.abs(us[0] - us[k]).max() < 1e-12 * max(1.0, np.abs(us[0]).max())
