@@ -53,6 +53,12 @@ int mmadmm_create(int D, int P, int E, const double *Vp, const double *Vc, const
  * reference (sum of the un-regularised element energies at entry to the first prox sweep). */
 int mmadmm_step(mmadmm_ctx *ctx, int nIters, double tol, double *Ih, int *itersTaken, double *primal, double *dual);
 
+/* Replaces MeshIntegrator<D>::eulerStep (Method 1, src/MeshIntegrator.cpp:87-95): grad = Mesh::eulerStepMod
+ * (src/Mesh.cpp:533-579: element gradients without regularisation, collected by INTERIOR vertices only), then
+ * x -= (dt/tau) grad.  Ih = energy at entry.  Like the reference, this path does not go through updateAfterStep:
+ * the caller reads the positions with mmadmm_get_x when it wants them. */
+int mmadmm_euler_step(mmadmm_ctx *ctx, double *Ih);
+
 /* The time step belongs to MeshIntegrator<D>, not to Mesh<D> (src/MeshIntegrator.cpp:15-17,45-51): a host Mesh<D> may
  * create the context before any integrator exists (dt = 0) and the integrator's constructor then sets dt, which
  * rebuilds the diagonal of t = M + dt^2 (WD)^T(WD).  Must be called before the first mmadmm_step. */

@@ -29,7 +29,7 @@ ERRORS = {1: "EINVAL", 2: "ECUDA", 3: "EINVERTED", 4: "ESINGULAR", 5: "ENCCL", 6
 # every symbol include/mmadmm.h declares (checked by tests/test_abi.py)
 ABI_SYMBOLS = [
     "mmadmm_create", "mmadmm_set_dt", "mmadmm_step", "mmadmm_energy", "mmadmm_get_x", "mmadmm_get_x_device", "mmadmm_get_x_colmajor", "mmadmm_host_register", "mmadmm_host_unregister", "mmadmm_get_F",
-    "mmadmm_grid_dims", "mmadmm_get_state", "mmadmm_eval_monitor", "mmadmm_block_grad", "mmadmm_block_grad_at", "mmadmm_get_stats",
+    "mmadmm_euler_step", "mmadmm_grid_dims", "mmadmm_get_state", "mmadmm_eval_monitor", "mmadmm_block_grad", "mmadmm_block_grad_at", "mmadmm_get_stats",
     "mmadmm_get_timing", "mmadmm_set_option", "mmadmm_stream", "mmadmm_destroy", "mmadmm_last_error",
     "mmadmm_version", "mmadmm_plan_create", "mmadmm_plan_sizes", "mmadmm_plan_get", "mmadmm_plan_destroy",
     "mmadmm_comm_unique_id", "mmadmm_create_dist", "mmadmm_local_sizes", "mmadmm_get_x_local",
@@ -69,6 +69,7 @@ def lib():
         L.mmadmm_step.argtypes = [vp, C.c_int, C.c_double, _c_dp, _c_ip, _c_dp, _c_dp]
         L.mmadmm_energy.argtypes = [vp, _c_dp]
         L.mmadmm_set_dt.argtypes = [vp, C.c_double]
+        L.mmadmm_euler_step.argtypes = [vp, _c_dp]
         L.mmadmm_get_x.argtypes = [vp, _c_dp]
         L.mmadmm_get_x_device.argtypes = [vp, vp]
         L.mmadmm_get_F.argtypes = [vp, _c_ip]
@@ -368,6 +369,13 @@ class MeshIntegrator:
                 self._check(self.L.mmadmm_get_x_local(self.h, _dp(self.mesh.Vp)))
             else:
                 self._check(self.L.mmadmm_get_x(self.h, _dp(self.mesh.Vp)))
+        return Ih.value
+
+    def eulerStep(self, tol=1e-3):
+        """Method 1, MeshIntegrator<D>::eulerStep(tol) (src/MeshIntegrator.cpp:87-95; `tol` is unused there too).  The caller's
+        Vp is not refreshed on this path (no updateAfterStep in the reference): use x() or done()."""
+        Ih = C.c_double()
+        self._check(self.L.mmadmm_euler_step(self.h, C.byref(Ih)))
         return Ih.value
 
     def local_sizes(self):

@@ -300,25 +300,34 @@ template <int D> __global__ void __launch_bounds__(TPB) k_energy(ElemArgs<D> a, 
     if (threadIdx.x == 0) part[blockIdx.x] = s;
 }
 
-// K6a: element part of Mesh::eulerGrad (src/Mesh.cpp:582-624): masked, un-regularised element gradients -> scratch planes
-template <int D> __global__ void __launch_bounds__(TPB) k_euler_elem(ElemArgs<D> a, double *gs) {
+// K6a: element part of Mesh::eulerGrad (src/Mesh.cpp:582-624): masked, un-regularised element gradients -> scratch planes.
+// `bits` selects the slices that are dropped: fixedBits for eulerGrad (computeBlockGrad zeroes FIXED slices), nonIntBits for
+// eulerStepMod (src/Mesh.cpp:533-579: only INTERIOR vertices collect).  ENERGY: also the block sums of the element energies.
+template <int D, bool ENERGY> __global__ void __launch_bounds__(TPB) k_euler_elem(ElemArgs<D> a, double *gs, const uint8_t *bits, double *part) {
     constexpr int n = D * (D + 1);
+    __shared__ double red[32];
     int e = blockIdx.x * TPB + threadIdx.x;
-    if (e >= a.E) return;
-    int vid[D + 1];
-    load_elem_ids<D>(a, e, vid);
-    double z[n], xi[n], g[n];
+    double en = 0.0;
+    if (e < a.E) {
+        int vid[D + 1];
+        load_elem_ids<D>(a, e, vid);
+        double z[n], xi[n], g[n];
 #pragma unroll
-    for (int v = 0; v < D + 1; v++) gather_vertex<D>(a.x, vid[v], z + D * v);
-    load_xi<D>(a, vid, xi);
-    bool inv = false;
-    block_grad<D, true>(z, xi, a.compMesh, a.mg, a.fc, g, inv);
-    if (inv) atomicOr(a.status, ST_INVERTED);
-    unsigned fb = a.fixedBits[e];
+        for (int v = 0; v < D + 1; v++) gather_vertex<D>(a.x, vid[v], z + D * v);
+        load_xi<D>(a, vid, xi);
+        bool inv = false;
+        en = block_grad<D, true>(z, xi, a.compMesh, a.mg, a.fc, g, inv);
+        if (inv) atomicOr(a.status, ST_INVERTED);
+        unsigned fb = bits[e];
 #pragma unroll
-    for (int v = 0; v < D + 1; v++)
+        for (int v = 0; v < D + 1; v++)
 #pragma unroll
-        for (int l = 0; l < D; l++) gs[(size_t)(D * v + l) * a.Es + e] = (fb & (1u << v)) ? 0.0 : g[D * v + l];
+            for (int l = 0; l < D; l++) gs[(size_t)(D * v + l) * a.Es + e] = (fb & (1u << v)) ? 0.0 : g[D * v + l];
+    }
+    if (ENERGY) {
+        double s = block_sum(en, red);
+        if (threadIdx.x == 0) part[blockIdx.x] = s;
+    }
 }
 
 // DXpU = D x + u and the sweep's entry z for element e (src/MeshIntegrator.cpp:120-127,146)
@@ -2202,7 +2211,7 @@ template <int D> int step_impl(mmadmm_ctx *ctx, int nIters, double tol, double *
     // predictX (src/Mesh.cpp:649-674) fused with xPrev = x (src/MeshIntegrator.cpp:119)
     ctx->phaseBegin(0);
     if (ctx->gradUse || ctx->stepsTaken <= 2) {
-        k_euler_elem<D><<<gE, TPB, 0, st>>>(a, ctx->gs);
+        k_euler_elem<D, false><<<gE, TPB, 0, st>>>(a, ctx->gs, a.fixedBits, nullptr);
         k_predict_grad<D><<<gV, TPB_V, 0, st>>>(P, ctx->Es, ctx->incPtr, ctx->incIdx, ctx->gs, ctx->dt / ctx->tau, ctx->x, ctx->xBar,
                                                 ctx->xPrev, ctx->dist ? ctx->sharedSlot : nullptr, ctx->sPart, ctx->vorder);
         ctx->launches += 2;
@@ -2303,6 +2312,31 @@ template <int D> int energy_impl(mmadmm_ctx *ctx, double *I) {
     if (rcg) return rcg;
     CK(cudaGetLastError());
     *I = ctx->scal_h[3];
+    return check_status(ctx);
+}
+
+// Method 1: MeshIntegrator::eulerStep (src/MeshIntegrator.cpp:87-95) = Mesh::eulerStepMod (src/Mesh.cpp:533-579) + x -= (dt/tau) grad.
+// Returns the energy at entry.  K6a with the INTERIOR-only mask, then K6b writing into x itself.
+template <int D> int euler_impl(mmadmm_ctx *ctx, double *IhOut) {
+    cudaStream_t st = ctx->stream;
+    ElemArgs<D> a = ctx->elemArgs<D>(0.0);
+    k_euler_elem<D, true><<<ctx->nblkE, TPB, 0, st>>>(a, ctx->gs, a.nonIntBits, ctx->partPrimal);
+    k_predict_grad<D><<<ctx->nblkV, TPB_V, 0, st>>>(ctx->P, ctx->Es, ctx->incPtr, ctx->incIdx, ctx->gs, ctx->dt / ctx->tau, ctx->x, ctx->x,
+                                                    ctx->xPrev, ctx->dist ? ctx->sharedSlot : nullptr, ctx->sPart, ctx->vorder);
+    ctx->launches += 2;
+    if (ctx->dist && ctx->nShared > 0) {
+        int rcx = halo_exchange<D>(ctx);
+        if (rcx) return rcx;
+        k_predict_finish<D><<<cdiv(ctx->nShared, 256), 256, 0, st>>>(ctx->nShared, ctx->sharedIdx, ctx->sTot, ctx->dt / ctx->tau, ctx->x,
+                                                                     ctx->x, ctx->xPrev);
+        ctx->launches++;
+    }
+    k_finalize<<<1, 1024, 0, st>>>(ctx->nblkE, ctx->partPrimal, 0, nullptr, 0, nullptr, ctx->scal_d + 3);
+    ctx->launches++;
+    int rcg = gather_scalars(ctx, 4);
+    if (rcg) return rcg;
+    CK(cudaGetLastError());
+    if (IhOut) *IhOut = ctx->scal_h[3];
     return check_status(ctx);
 }
 
@@ -2452,6 +2486,12 @@ int mmadmm_step(mmadmm_ctx *ctx, int nIters, double tol, double *Ih, int *itersT
     CK(cudaSetDevice(ctx->device));
     return (ctx->D == 2) ? step_impl<2>(ctx, nIters, tol, Ih, itersTaken, primal, dual)
                          : step_impl<3>(ctx, nIters, tol, Ih, itersTaken, primal, dual);
+}
+
+int mmadmm_euler_step(mmadmm_ctx *ctx, double *Ih) {
+    if (!ctx) return MMADMM_EINVAL;
+    CK(cudaSetDevice(ctx->device));
+    return (ctx->D == 2) ? euler_impl<2>(ctx, Ih) : euler_impl<3>(ctx, Ih);
 }
 
 int mmadmm_energy(mmadmm_ctx *ctx, double *I) {

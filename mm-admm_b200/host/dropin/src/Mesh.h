@@ -9,8 +9,8 @@
 //
 // What the reference's Mesh does on the host and this one does not: the D/W/M sparse matrices, face lists and
 // simplex maps are never formed (the ADMM system matrix is diagonal, incidence replaces D).
-// Methods 1 and 2 (explicit / backward Euler) are out of scope: integrationMode != 0 aborts with a
-// message.
+// Method 2 (backward Euler, the LASolver path) is out of scope: integrationMode == 2 aborts with a
+// message.  Method 1 (explicit Euler) runs on the device through mmadmm_euler_step.
 #ifndef MESH_H
 #define MESH_H
 
@@ -73,8 +73,8 @@ public:
         this->rho = rho;
         this->w = 0.5 * sqrt(rho);
         this->nPnts = Xp.rows();
-        if (integrationMode != 0) {
-            cerr << "mm-admm_b200: only Method 0 (ADMM, MeshIntegrator::step) is built; Methods 1/2 are not implemented on this build" << endl;
+        if (integrationMode != 0 && integrationMode != 1) {
+            cerr << "mm-admm_b200: Methods 0 (ADMM, MeshIntegrator::step) and 1 (eulerStep) are built; Method 2 is not implemented on this build" << endl;
             exit(1);
         }
         const int P = Xp.rows(), E = F.rows();

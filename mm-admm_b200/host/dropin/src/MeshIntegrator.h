@@ -46,7 +46,13 @@ public:
         a->nSteps = stepsTaken;
         return Ih;
     }
-    double eulerStep(double tol) { (void)tol; notBuilt("eulerStep (Method 1)"); return 0; }
+    // Method 1 (src/MeshIntegrator.cpp:87-95).  As in the reference there is no updateAfterStep on this path: Vp follows at done().
+    double eulerStep(double tol) {
+        (void)tol;
+        double Ih = 0;
+        a->check(mmadmm_euler_step(a->ctx, &Ih), "mmadmm_euler_step");
+        return Ih;
+    }
     double backwardsEulerStep(double dt, double tol) { (void)dt; (void)tol; notBuilt("backwardsEulerStep (Method 2)"); return 0; }
     double getEnergy() { return a->computeEnergy(xUnused); }
     void done() { a->updateAfterStep(dt, xPrevUnused, xUnused); }
@@ -88,7 +94,7 @@ public:
 private:
     Eigen::VectorXd xUnused, xPrevUnused;
     void notBuilt(const char *what) {
-        cerr << "mm-admm_b200: " << what << " is not implemented on this build (only Method 0, the ADMM step)" << endl;
+        cerr << "mm-admm_b200: " << what << " is not implemented on this build (Methods 0 and 1 are)" << endl;
         exit(1);
     }
 };

@@ -527,6 +527,39 @@ static double eulerGrad(Oracle &o, const std::vector<double> &x, std::vector<dou
     return Ihorig;
 }
 
+// Method 1 (explicit Euler).  src/Mesh.cpp:533-579 eulerStepMod: blockGrad directly (no FIXED zeroing), but only INTERIOR
+// vertices collect gradient, so FIXED and FREE boundary vertices both stay put; src/MeshIntegrator.cpp:87-95 eulerStep:
+// x -= (dt/tau) grad, returns the energy at entry.  Vp is NOT refreshed (no updateAfterStep on this path).
+template <int D>
+static double eulerStepMod(Oracle &o, const std::vector<double> &x, std::vector<double> &grad) {
+    constexpr int n = D * (D + 1);
+    std::fill(grad.begin(), grad.end(), 0.0);
+    double Ihorig = 0.0, Igt;
+    for (int i = 0; i < o.E; i++) {
+        double x_i[n], xi_i[n], gradSimp[n];
+        for (int nn = 0; nn < D + 1; nn++) {
+            int v = o.F[(size_t)i * (D + 1) + nn];
+            for (int l = 0; l < D; l++) {
+                if (o.compMesh) xi_i[nn * D + l] = o.Vc[(size_t)v * D + l];
+                x_i[nn * D + l] = x[(size_t)D * v + l];
+            }
+        }
+        Ihorig += blockGrad<D>(o, i, x_i, xi_i, gradSimp, true, false, Igt);
+        for (int nn = 0; nn < D + 1; nn++) {
+            int off = o.F[(size_t)i * (D + 1) + nn];
+            if (o.mask[off] != INTERIOR) continue;
+            for (int l = 0; l < D; l++) grad[(size_t)D * off + l] += gradSimp[D * nn + l];
+        }
+    }
+    return Ihorig;
+}
+template <int D>
+static double eulerStep(Oracle &o) {
+    double Ih = eulerStepMod<D>(o, o.x, o.grad);
+    for (size_t i = 0; i < o.x.size(); i++) o.x[i] -= (o.dt / o.tau) * o.grad[i];
+    return Ih;
+}
+
 // src/Mesh.cpp:496-530 (reads *Vp, ignores its argument)
 template <int D>
 static double computeEnergy(Oracle &o) {
@@ -954,6 +987,12 @@ int orc_step(void *h, int nIters, double tol, double *Ih, int *iters, double *pr
     if (iters) *iters = o.lastAdmmIters;
     if (primal) *primal = o.lastPrimal;
     if (dual) *dual = o.lastDual;
+    return o.error;
+}
+int orc_euler_step(void *h, double *Ih) {
+    Oracle &o = *(Oracle *)h;
+    double v = (o.D == 2) ? eulerStep<2>(o) : eulerStep<3>(o);
+    if (Ih) *Ih = v;
     return o.error;
 }
 double orc_energy(void *h) {

@@ -42,6 +42,8 @@ def lib():
         L.orc_destroy.argtypes = [C.c_void_p]
         L.orc_step.restype = C.c_int
         L.orc_step.argtypes = [C.c_void_p, C.c_int, C.c_double, c_dp, c_ip, c_dp, c_dp]
+        L.orc_euler_step.restype = C.c_int
+        L.orc_euler_step.argtypes = [C.c_void_p, c_dp]
         L.orc_energy.restype = C.c_double
         L.orc_energy.argtypes = [C.c_void_p]
         for nm in ("orc_get_x", "orc_get_z", "orc_get_u", "orc_get_hess", "orc_get_grid"):
@@ -113,6 +115,12 @@ class Oracle:
         Ih = C.c_double(); it = C.c_int(); pr = C.c_double(); du = C.c_double()
         rc = self.L.orc_step(self.h, n_iters, tol, C.byref(Ih), C.byref(it), C.byref(pr), C.byref(du))
         return dict(Ih=Ih.value, iters=it.value, primal=pr.value, dual=du.value, status=rc)
+
+    def euler_step(self):
+        """Method 1 (MeshIntegrator::eulerStep): returns the energy at entry; Vp is not refreshed."""
+        Ih = C.c_double()
+        rc = self.L.orc_euler_step(self.h, C.byref(Ih))
+        return dict(Ih=Ih.value, status=rc)
 
     def energy(self):
         return self.L.orc_energy(self.h)

@@ -21,7 +21,7 @@ GOLD = os.path.join(ROOT, "tests", "golden")
 TRACES = json.load(open(os.path.join(GOLD, "ih_traces.json")))
 
 
-def run_driver(tmp_path, name, nsteps, extra=None):
+def run_driver(tmp_path, name, nsteps, extra=None, method=0):
     spec = dict(TRACES[name]["input"])
     spec["nSteps"] = nsteps
     spec["DtTol"] = 0          # never stop early: compare a fixed number of steps
@@ -36,10 +36,10 @@ def run_driver(tmp_path, name, nsteps, extra=None):
             shutil.copy(os.path.join(GOLD, fn), base / fn)
             spec[key] = "./" + os.path.relpath(base / fn, wd)
     json.dump(spec, open(wd / "Experiments" / "InputFiles" / f"{name}.json", "w"))
-    r = subprocess.run([EXE, name, "0", "1"], cwd=wd, capture_output=True, text=True, timeout=600)
+    r = subprocess.run([EXE, name, str(method), "1"], cwd=wd, capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
     out = wd / "Experiments" / "Results" / name
-    rows = [ln.split(",") for ln in open(out / "Ih0.txt").read().split("\n") if ln.strip()]
+    rows = [ln.split(",") for ln in open(out / f"Ih{method}.txt").read().split("\n") if ln.strip()]
     ih = [row[1].strip() for row in rows]
     return spec, out, ih, r.stdout
 
@@ -61,6 +61,19 @@ def test_reference_driver_reproduces_committed_trace(tmp_path, name, nsteps):
     assert len(pts[0].split(",")) == spec["Dim"] and len(tris[0].split(",")) == spec["Dim"] + 1
     assert f"Number of simplices = {len(tris)}" in stdout and f"Number of points = {len(pts)}" in stdout
     assert os.path.exists(out / "IhPara1.txt")
+
+
+@pytest.mark.gpu
+def test_reference_driver_explicit_euler_reproduces_committed_trace(tmp_path):
+    """`mesh.exe Monitor220 1 1`: Method 1 = MeshIntegrator::eulerStep (main.cpp:186-188) -> mmadmm_euler_step; the reference
+    commits Experiments/Results/Monitor220/Ih1.txt for the shipped input (49 steps, 6 digits)."""
+    if not os.path.exists(EXE):
+        pytest.skip("build/dropin/mesh.exe not built")
+    ref = TRACES["Monitor220"]["Ih1"]
+    spec, out, ih, stdout = run_driver(tmp_path, "Monitor220", len(ref) - 1, method=1)
+    assert len(ih) == len(ref) == 50
+    for i, (g, e) in enumerate(zip(ih, ref)):
+        assert g == ("%g" % e), f"euler step {i}: drop-in driver wrote {g}, reference trace has {e:g}"
 
 
 @pytest.mark.gpu

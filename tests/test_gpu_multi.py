@@ -23,7 +23,7 @@ def _case_mesh(m, case):
     return m.generate_uniform_rect_mesh(D, nx, nx, nx if D == 3 else 0, boundary_type=btype) + (0.5, 0.025)
 
 
-def _worker(rank, world, id128, case, nsteps, q):
+def _worker(rank, world, id128, case, nsteps, q, neuler=0):
     import importlib as il
     m = il.import_module("mm-admm_b200")
     D, nx, kind, rho, btype, comp = case[:6]
@@ -33,6 +33,9 @@ def _worker(rank, world, id128, case, nsteps, q):
     s = m.MeshIntegrator(dt, mesh, device=rank, comm=(rank, world, id128))
     e0 = s.getEnergy()
     ihs, its = [], []
+    for _ in range(neuler):   # Method 1 steps first (collective too: assembled gradient of the shared vertices)
+        ihs.append(s.eulerStep())
+        its.append(0)
     for _ in range(nsteps):
         ihs.append(s.step(10, 1e-3))
         its.append(s.last["iters"])
@@ -42,12 +45,12 @@ def _worker(rank, world, id128, case, nsteps, q):
     s.close()
 
 
-def run_dist(world, case, nsteps):
+def run_dist(world, case, nsteps, neuler=0):
     import torch.multiprocessing as mp
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
     id128 = mm.comm_unique_id()
-    procs = [ctx.Process(target=_worker, args=(r, world, id128, case, nsteps, q)) for r in range(world)]
+    procs = [ctx.Process(target=_worker, args=(r, world, id128, case, nsteps, q, neuler)) for r in range(world)]
     for p in procs:
         p.start()
     res = sorted([q.get(timeout=600) for _ in procs], key=lambda r: r[0])
@@ -94,4 +97,29 @@ def test_partitioned_solve_matches_single_gpu_and_oracle(case, nsteps, world):
     assert np.abs(xd - xs).max() <= 1e-12 * np.abs(xs).max()
     assert np.abs(xd - xo).max() <= 1e-9 * np.abs(xo).max()
     assert abs(res[0][4] - orc.energy()) <= 1e-9 * abs(orc.energy())
+    s.close()
+
+
+@pytest.mark.parametrize("case", [(2, 48, 3, 100.0, 1, False), (3, 8, 3, 50.0, 1, False)])
+def test_partitioned_explicit_euler_matches_single_gpu_and_oracle(case):
+    """Method 1 on a partitioned mesh: 5 eulerStep calls, then 3 ADMM steps from that state."""
+    if ngpus() < 2:
+        pytest.skip("needs 2 GPUs")
+    D, nx, kind, rho, btype, comp = case[:6]
+    res = run_dist(2, case, 3, neuler=5)
+    assert res[0][2] == res[1][2] and np.array_equal(res[0][5], res[1][5])
+    Vp, F, mask, tau, dt = _case_mesh(mm, case)
+    mon = mm.TestMonitor(D, kind).evaluate_at_vertices(Vp)
+    mesh = mm.Mesh(Vp.copy(), F.copy(), mask, mon, rho=rho, tau=tau)
+    s = mm.MeshIntegrator(dt, mesh)
+    orc = O.Oracle(Vp, F, mask, mon, rho, tau, dt, nthreads=4)
+    for k in range(8):
+        ih = s.eulerStep() if k < 5 else s.step(10, 1e-3)
+        ro = orc.euler_step() if k < 5 else orc.step(10, 1e-3)
+        assert ro["status"] == 0
+        assert abs(res[0][2][k] - ih) <= 1e-12 * abs(ih)
+        assert abs(res[0][2][k] - ro["Ih"]) <= 1e-9 * abs(ro["Ih"])
+    s.done()
+    assert np.abs(res[0][5] - mesh.Vp).max() <= 1e-12 * np.abs(mesh.Vp).max()
+    assert np.abs(res[0][5] - orc.x()).max() <= 1e-9 * np.abs(orc.x()).max()
     s.close()

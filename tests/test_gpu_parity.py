@@ -233,3 +233,31 @@ def test_dual_sum_xupdates_match_slotwise(D, nx, kind):
         assert rel(xs[0], xs[k]) < 1e-12
         assert np.allclose(Is[0], Is[k], rtol=1e-12, atol=0)
         assert np.abs(us[0] - us[k]).max() < 1e-12 * max(1.0, np.abs(us[0]).max())
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("D,nx,kind,btype", [(2, 20, 3, 1), (2, 16, 1, 0), (3, 5, 4, 1)])
+def test_explicit_euler_matches_oracle(D, nx, kind, btype):
+    """Method 1 (MeshIntegrator::eulerStep -> Mesh::eulerStepMod, src/MeshIntegrator.cpp:87-95, src/Mesh.cpp:533-579): only
+    INTERIOR vertices move, FREE boundary vertices included in the freeze.  Then ADMM steps continue from the Euler state."""
+    Vp, F, mask = O.uniform_rect_mesh(D, nx, nx, nx if D == 3 else 0, btype=btype)
+    mon = O.monitor_eval(D, kind, Vp)
+    orc = O.Oracle(Vp.copy(), F.copy(), mask, mon, 50.0, 0.5, 0.025)
+    mesh = mm.Mesh(Vp.copy(), F.copy(), mask, mon, rho=50.0, tau=0.5)
+    s = mm.MeshIntegrator(0.025, mesh)
+    for k in range(10):
+        r = orc.euler_step()
+        Ih = s.eulerStep()
+        assert r["status"] == 0
+        assert abs(Ih - r["Ih"]) <= 1e-9 * abs(r["Ih"])
+    assert rel(s.x(), orc.x().reshape(-1, D)) < 1e-9
+    bnd = mask != mm.INTERIOR
+    assert np.array_equal(s.x()[bnd], Vp[bnd])            # FIXED and FREE boundary vertices are frozen on this path
+    assert np.array_equal(mesh.Vp, Vp)                    # no updateAfterStep here, as in the reference
+    for k in range(3):
+        r = orc.step(10, 1e-3)
+        assert r["status"] == 0
+        Ih = s.step(10, 1e-3)
+        assert abs(Ih - r["Ih"]) <= 1e-9 * abs(r["Ih"])
+    assert rel(s.x(), orc.x().reshape(-1, D)) < 1e-9
+    s.close()

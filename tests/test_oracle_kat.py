@@ -74,3 +74,17 @@ def test_monitor_quirks():
     r = np.sqrt((X[:, 0] - .5) ** 2 + (X[:, 1] - .5) ** 2)
     assert np.allclose(m3[:, 0], np.sqrt(0.01 / (2 + np.cos(8 * np.pi * r))), rtol=1e-14)
     assert np.all(m3[:, 1] == 0) and np.array_equal(m3[:, 0], m3[:, 3])
+
+
+def test_explicit_euler_trace_matches_reference(golden_dir):
+    """Method 1 (MeshIntegrator::eulerStep, src/MeshIntegrator.cpp:87-95): Experiments/Results/Monitor220/Ih1.txt, all 49 steps."""
+    orc, spec = build_from_input("Monitor220", golden_dir)
+    ref = TRACES["Monitor220"]["Ih1"]
+    got = [orc.energy()]
+    for _ in range(len(ref) - 1):
+        r = orc.euler_step()
+        assert r["status"] == 0
+        got.append(r["Ih"])
+    assert len(ref) == 50
+    for i, (g, e) in enumerate(zip(got, ref)):
+        assert fmt6(g) == e, f"euler step {i}: oracle {g!r} vs reference {e}"
