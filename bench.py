@@ -203,7 +203,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="c2", choices=["c2", "c3", "c4"])
-    ap.add_argument("--nx", type=int, default=0, help="override the mesh resolution (debugging)")
+    ap.add_argument("--nx", type=int, default=0, help="override the mesh resolution (with --gpus N: strong scaling at that size, e.g. SURVEY C5 = --nx 2048)")
+    ap.add_argument("--per-step", action="store_true", help="also record one event per step (step_ms_rank0); adds host work between steps")
     ap.add_argument("--cpu-nx", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--opt", action="append", default=[], help="library option name=value (A/B runs), e.g. b_evict_first=1")
@@ -299,12 +300,14 @@ def main():
             if dist:
                 dist.barrier()
                 torch.cuda.synchronize()
-            marks = [torch.cuda.Event(enable_timing=True) for _ in range(kk)]
+            marks = [torch.cuda.Event(enable_timing=True) for _ in range(kk)] if args.per_step else []
+            nit, tol = PARAMS["admm_iter"], PARAMS["tol"]
             ev0.record(stream)
             for i in range(kk):
-                tot["ih"].append(solver.step(PARAMS["admm_iter"], PARAMS["tol"]))
+                tot["ih"].append(solver.step(nit, tol))
                 tot["iters"] += solver.last["iters"]
-                marks[i].record(stream)
+                if marks:
+                    marks[i].record(stream)
             ev1.record(stream)
             torch.cuda.synchronize()
             if dist:
@@ -312,7 +315,8 @@ def main():
                 torch.cuda.synchronize()
             tot["clocks"].append(sampler.stop() if sampler else {})
             ms = ev0.elapsed_time(ev1)
-            tot["step_ms"] += [round(a.elapsed_time(b), 4) for a, b in zip([ev0] + marks[:-1], marks)]   # this rank, per step
+            if marks:
+                tot["step_ms"] += [round(a.elapsed_time(b), 4) for a, b in zip([ev0] + marks[:-1], marks)]   # this rank, per step
             if dist:   # device time, max over ranks
                 tms = torch.tensor([ms], dtype=torch.float64, device="cuda")
                 dist.all_reduce(tms, op=dist.ReduceOp.MAX)
@@ -357,7 +361,7 @@ def main():
     kbar = float((hist * np.arange(52)).sum() / max(hist.sum(), 1))
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": K, "warmup": W,
-        "ms_per_step": r["ms"] / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+        "ms_per_step": r["ms"] / K, "higher_is_better": True, "scaling": "strong" if (args.nx and world > 1) else "weak", "vs_baseline": None, "dtype": "f64",
         "data": "synthetic",
         "config": {"workload": wl["label"], "elements": E, "points": P, "monitor_grid": g, "monitor_grid_isotropic_fast_path": bool(args.iso_grid) and solver.iso_grid_active(),
                    "parallelism": (f"element-block partition over {world} GPUs, one process per GPU; halo sums of shared-vertex partials + "

@@ -567,7 +567,8 @@ __global__ void __launch_bounds__((D + 1) * 32, MINB) k_prox_vw(const __grid_con
     double *Un = Xn + n * 32;                              // [n][32]  next tile: u
     double *Zn = Un + n * 32;                              // [n][32]  next tile: z
     int *Vn = reinterpret_cast<int *>(Zn + n * 32);        // [NV][32] ints  connectivity of the tile after next
-    double *red = reinterpret_cast<double *>(Vn + NV * 32);   // 32
+    int *Fn = Vn + NV * 32;                                // [NV][32] ints  next tile: the word of fixedBits that holds the element's byte
+    double *red = reinterpret_cast<double *>(Fn + NV * 32);   // 32
     uint64_t *bar = reinterpret_cast<uint64_t *>(red + 32);
     int *shist = reinterpret_cast<int *>(bar + 2);         // 52
     const int tid = threadIdx.x, lane = tid & 31, q = tid >> 5;
@@ -589,6 +590,7 @@ __global__ void __launch_bounds__((D + 1) * 32, MINB) k_prox_vw(const __grid_con
                 if (a.zsrc) cp_async8(Zn + s, a.zsrc + (size_t)D * vid + l);
                 else cp_async8(Zn + s, a.z + tm_index(e, D * q + l, n));
             }
+            cp_async4(Fn + q * 32 + lane, reinterpret_cast<const int *>(a.fixedBits) + (e >> 2));
         }
     };
     auto prefetch_vid = [&](int tile) {     // connectivity of `tile` into this thread's slot
@@ -622,7 +624,7 @@ __global__ void __launch_bounds__((D + 1) * 32, MINB) k_prox_vw(const __grid_con
             zprev[l] = zo[l];
             Gk[l] = 0.0;
         }
-        const bool ownFixed = active && ((a.fixedBits[e] >> q) & 1u);
+        const bool ownFixed = active && (((unsigned)Fn[q * 32 + lane] >> (8 * (e & 3) + q)) & 1u);
         const int vidNext = Vn[q * 32 + lane];
         if (COMP && active) {
 #pragma unroll
@@ -1458,8 +1460,10 @@ struct mmadmm_ctx {
         cudaEventRecord(evPool[evUsed + 1], stream);
         evUsed += 2;
     }
+    // Elapsed times are read when somebody asks (mmadmm_get_timing) or when the pool is large, not after every step: the
+    // synchronise + query per phase would sit in the host gap between two steps.
     void phaseResolve() {
-        if (!timingOn) return;
+        if (evUsed == 0) return;
         for (size_t i = 0; i + 1 < evUsed; i += 2) {
             float ms = 0;
             cudaEventSynchronize(evPool[i + 1]);
@@ -1998,7 +2002,8 @@ int create_impl(mmadmm_ctx *ctx, const double *Vp, const double *Vc, const int *
         CK(cudaMalloc(&ctx->F[v], sizeof(int) * ctx->Es));
         CK(cudaMemsetAsync(ctx->F[v], 0, sizeof(int) * ctx->Es, st));
     }
-    CK(cudaMalloc(&ctx->fixedBits, (size_t)E));
+    CK(cudaMalloc(&ctx->fixedBits, ctx->Es));   // whole tiles: k_prox_vw fetches the aligned word around an element's byte
+    CK(cudaMemsetAsync(ctx->fixedBits, 0, ctx->Es, st));
     CK(cudaMalloc(&ctx->nonIntBits, (size_t)E));
     k_setup_F<D><<<cdiv(E, 256), 256, 0, st>>>(E, Frow, ctx->F[0], ctx->F[1], ctx->F[2], ctx->F[3], ctx->x, ctx->mask,
                                                ctx->fixedBits, ctx->nonIntBits);
@@ -2149,7 +2154,7 @@ template <> int launch_prox<2>(mmadmm_ctx *ctx, const ElemArgs<2> &a) {
 template <int D, int MINB> int launch_prox_vw(mmadmm_ctx *ctx, const ElemArgs<D> &a, int slot) {
     constexpr int n = D * (D + 1);
     const bool iso = a.mg.iso != nullptr;
-    const size_t smem = sizeof(double) * 32 * (size_t)(n * n + 8 * n + (D + 1) * (iso ? 1 : D * D) + (D + 1) * 3 + 1) + 16 + (52 + 32 * (D + 1)) * sizeof(int);
+    const size_t smem = sizeof(double) * 32 * (size_t)(n * n + 8 * n + (D + 1) * (iso ? 1 : D * D) + (D + 1) * 3 + 1) + 16 + (52 + 64 * (D + 1)) * sizeof(int);
     auto kern = ctx->compMesh ? (iso ? k_prox_vw<D, true, true, MINB> : k_prox_vw<D, true, false, MINB>)
                               : (iso ? k_prox_vw<D, false, true, MINB> : k_prox_vw<D, false, false, MINB>);
     if (!ctx->smemAttrSet[slot + (iso ? 8 : 0)]) {
@@ -2291,7 +2296,7 @@ template <int D> int step_impl(mmadmm_ctx *ctx, int nIters, double tol, double *
         dual = std::sqrt(ctx->scal_h[2]);
         if (primal < tol && dual < tol) break;
     }
-    ctx->phaseResolve();
+    if (ctx->evUsed >= 4096) ctx->phaseResolve();
     CK(cudaGetLastError());
     ctx->stepsTaken++;
     if (IhOut) *IhOut = Ihstart;
@@ -2696,6 +2701,8 @@ int mmadmm_get_stats(mmadmm_ctx *ctx, long long *hist52, long long *proxCalls, l
 
 int mmadmm_get_timing(mmadmm_ctx *ctx, double *ms5, long long *counts5, int reset) {
     if (!ctx) return MMADMM_EINVAL;
+    CK(cudaSetDevice(ctx->device));
+    ctx->phaseResolve();
     for (int i = 0; i < 5; i++) {
         if (ms5) ms5[i] = ctx->phaseMs[i];
         if (counts5) counts5[i] = ctx->phaseCnt[i];
@@ -2706,7 +2713,14 @@ int mmadmm_get_timing(mmadmm_ctx *ctx, double *ms5, long long *counts5, int rese
 
 int mmadmm_set_option(mmadmm_ctx *ctx, const char *name, int value) {
     if (!ctx || !name) return MMADMM_EINVAL;
-    if (!strcmp(name, "timing")) { ctx->timingOn = value != 0; return MMADMM_OK; }
+    if (!strcmp(name, "timing")) {
+        ctx->timingOn = value != 0;
+        if (ctx->timingOn) {   // event pool up front: creating events is not something to do between two steps
+            CK(cudaSetDevice(ctx->device));
+            while (ctx->evPool.size() < 1024) { cudaEvent_t e; CK(cudaEventCreate(&e)); ctx->evPool.push_back(e); ctx->evPhase.push_back(0); }
+        }
+        return MMADMM_OK;
+    }
     if (!strcmp(name, "stats")) { ctx->statsOn = value != 0; return MMADMM_OK; }
     if (!strcmp(name, "prox_variant")) { ctx->proxVariant = value; return MMADMM_OK; }
     if (!strcmp(name, "usum_period")) {
