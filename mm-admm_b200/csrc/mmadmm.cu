@@ -1071,8 +1071,8 @@ __global__ void __launch_bounds__(1024) k_finalize(int n0, const double *p0, int
 //          set u+ = (x_p + u) - z+ in every slot, so usum+ = usum + val_p*x_p - zsum_p, and the right-hand side is
 //          w(w(zsum - usum+)).  Vertices shared with another rank keep the slot-by-slot form (their sums are partial).
 //          The exact form (UREC = false) also stores usum, which re-anchors the recurrence ("usum_period" option).
-template <int D, bool ZSRC, bool UZERO, bool PRIMAL, bool UREC>
-__global__ void __launch_bounds__(TPB_V) k_xupdate(int P, size_t Es, const int *incPtr, const int *incIdx, const double *z,
+template <int D, bool ZSRC, bool UZERO, bool PRIMAL, bool UREC, int CH = 4, int MINB = 1>
+__global__ void __launch_bounds__(TPB_V, MINB) k_xupdate(int P, size_t Es, const int *incPtr, const int *incIdx, const double *z,
                                                    const double *u, const double *zsrc, const double *xBar,
                                                    const double *tdiag, double m, double dtsq, double w, double *x,
                                                    double *partPrimal, const int *sharedSlot, double *sPart, const int *vorder,
@@ -1090,33 +1090,45 @@ __global__ void __launch_bounds__(TPB_V) k_xupdate(int P, size_t Es, const int *
         const int k0 = incPtr[p], k1 = incPtr[p + 1];
         const int sh = sharedSlot ? sharedSlot[p] : -1;
         const bool rec = UREC && sh < 0;
-        // slots in chunks of CH: all index loads, then all value loads, then the (ordered) accumulation
-        constexpr int CH = 4;
-        for (int kb = k0; kb < k1; kb += CH) {
-            int slot[CH];
-            double zv[CH][D], uv[CH][D];
-#pragma unroll
-            for (int j = 0; j < CH; j++) slot[j] = (kb + j < k1) ? __ldg(incIdx + kb + j) : -1;
-#pragma unroll
-            for (int j = 0; j < CH; j++) {
-                const size_t e = (size_t)(slot[j] >> 2);
-                const int v = slot[j] & 3;
+        if (UREC && sh >= 0) {   // shared with another rank: slot-by-slot form, plain loop (few vertices)
+            for (int k = k0; k < k1; k++) {
+                const int slot = __ldg(incIdx + k);
+                const size_t e = (size_t)(slot >> 2);
+                const int v = slot & 3;
 #pragma unroll
                 for (int l = 0; l < D; l++) {
                     const size_t idx = tm_index(e, D * v + l, D * (D + 1));
-                    zv[j][l] = (ZSRC || slot[j] < 0) ? zs[l] : __ldg(z + idx);
-                    uv[j][l] = (UZERO || rec || slot[j] < 0) ? 0.0 : __ldg(u + idx);
+                    s[l] += w * (w * (__ldg(z + idx) - __ldg(u + idx)));
                 }
             }
+        } else {
+            // slots in chunks of CH: all index loads, then all value loads, then the (ordered) accumulation
+            for (int kb = k0; kb < k1; kb += CH) {
+                int slot[CH];
+                double zv[CH][D], uv[UREC ? 1 : CH][D];
 #pragma unroll
-            for (int j = 0; j < CH; j++)
-                if (slot[j] >= 0) {
+                for (int j = 0; j < CH; j++) slot[j] = (kb + j < k1) ? __ldg(incIdx + kb + j) : -1;
+#pragma unroll
+                for (int j = 0; j < CH; j++) {
+                    const size_t e = (size_t)(slot[j] >> 2);
+                    const int v = slot[j] & 3;
 #pragma unroll
                     for (int l = 0; l < D; l++) {
-                        if (rec) s[l] += zv[j][l];   // zsum
-                        else { s[l] += w * (w * (zv[j][l] - uv[j][l])); us[l] += uv[j][l]; }
+                        const size_t idx = tm_index(e, D * v + l, D * (D + 1));
+                        zv[j][l] = (ZSRC || slot[j] < 0) ? zs[l] : __ldg(z + idx);
+                        if (!UREC) uv[j][l] = (UZERO || slot[j] < 0) ? 0.0 : __ldg(u + idx);
                     }
                 }
+#pragma unroll
+                for (int j = 0; j < CH; j++)
+                    if (slot[j] >= 0) {
+#pragma unroll
+                        for (int l = 0; l < D; l++) {
+                            if (UREC) s[l] += zv[j][l];   // zsum
+                            else { s[l] += w * (w * (zv[j][l] - uv[j][l])); us[l] += uv[j][l]; }
+                        }
+                    }
+            }
         }
         if (PRIMAL && sh < 0) {
 #pragma unroll
@@ -2183,7 +2195,11 @@ template <int D, bool ZSRC, bool UZERO, bool PRIMAL, bool UREC = false>
 int launch_xupdate_t(mmadmm_ctx *ctx, const double *zsrc, bool sharedOnly = false) {
     const double dtsq = ctx->dt * ctx->dt;
     if (!sharedOnly) {
-        k_xupdate<D, ZSRC, UZERO, PRIMAL, UREC><<<ctx->nblkV, TPB_V, 0, ctx->stream>>>(
+        // chunk size / occupancy of the recurrence form, measured on C2 and C4: 2D 2 slots per chunk at full occupancy
+        // (32 registers), 3D 8 slots per chunk (80 registers); the differences are a few per cent of the kernel
+        auto kern = !UREC ? k_xupdate<D, ZSRC, UZERO, PRIMAL, UREC>
+                          : (D == 2 ? k_xupdate<D, ZSRC, UZERO, PRIMAL, UREC, 2, 8> : k_xupdate<D, ZSRC, UZERO, PRIMAL, UREC, 8, 1>);
+        kern<<<ctx->nblkV, TPB_V, 0, ctx->stream>>>(
             ctx->P, ctx->Es, ctx->incPtr, ctx->incIdx, ctx->z, ctx->u, zsrc, ctx->xBar, ctx->tdiag, ctx->m, dtsq, ctx->w, ctx->x,
             ctx->partPrimal, ctx->dist ? ctx->sharedSlot : nullptr, ctx->sPart, ctx->vorder, ctx->usum);
         ctx->launches++;

@@ -1,8 +1,9 @@
 #!/bin/bash
 TAG=$1; N=${2:-8}; O=gpurun_out/$TAG; mkdir -p $O
 nproc > $O/nproc.txt
-for wl in c2 c4; do
-timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29517 bench.py --gpus $N --workload $wl --steps 6 --warmup 3 --no-cpu-baseline > $O/bench_${wl}_n$N.json 2> $O/bench_${wl}_n$N.err
+for wl in ${3:-c2 c4 c5}; do
+if [ $wl = c5 ]; then ARGS="--workload c2 --nx 2048"; else ARGS="--workload $wl"; fi   # c5 = SURVEY C5 strong scaling (16.8 M triangles at every N)
+timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29517 bench.py --gpus $N $ARGS --steps 6 --warmup 3 --no-cpu-baseline > $O/bench_${wl}_n$N.json 2> $O/bench_${wl}_n$N.err
 python - <<PY
 import json
 try:

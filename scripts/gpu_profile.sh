@@ -5,6 +5,7 @@ TAG=$1; O=gpurun_out/$TAG; mkdir -p $O
 python bench.py --steps 10 --warmup 3 > $O/bench_c2.json 2> $O/bench_c2.err; echo "bench c2 rc=$?"
 python bench.py --workload c3 --steps 10 --warmup 3 > $O/bench_c3.json 2> $O/bench_c3.err; echo "bench c3 rc=$?"
 python bench.py --workload c4 --steps 6 --warmup 3 > $O/bench_c4.json 2> $O/bench_c4.err; echo "bench c4 rc=$?"
+python bench.py --nx 2048 --steps 6 --warmup 3 --no-cpu-baseline > $O/bench_c5_n1.json 2> $O/bench_c5_n1.err; echo "bench c5 (nx=2048, strong-scaling base) rc=$?"
 python bench.py --impl reference --steps 4 --warmup 3 > $O/bench_ref.json 2> $O/bench_ref.err; echo "bench ref rc=$?"
 CMD="python bench.py --steps 3 --warmup 3 --no-cpu-baseline"
 $CMD > $O/plain.log 2>&1 &&

@@ -87,7 +87,10 @@ for wl in ("c2", "c4"):
     pick = lambda pat: next((a for k, a in avg.items() if pat in k), 0.0)
     D = "3" if wl == "c4" else "2"
     prox = pick("k_prox_vw") if wl == "c4" else pick("k_prox_p")
-    step = prox + pick(f"k_xupdate<{D}, 0, 0, 1>") + pick(f"k_xupdate<{D}, 1, 0, 0>") + pick("k_predict_extrap") + pick("k_finalize")
+    # (k_xfirst<D,1> = predictor + first x-solve, k_xupdate<D,0,0,1,1> = the x-update after the sweep on the dual sums; the
+    # pre-"usum" names are kept so that older captures still summarise)
+    step = (prox + pick(f"k_xupdate<{D}, 0, 0, 1, 1>") + pick(f"k_xfirst<{D}, 1>") + pick(f"k_xupdate<{D}, 0, 0, 1>(") +
+            pick(f"k_xupdate<{D}, 1, 0, 0>(") + pick("k_predict_extrap") + pick("k_finalize"))
     if step > 0:
         bj = json.loads(open(os.path.join(src, f"bench_{wl}.json")).read().strip().split("\n")[-1])
         ph = bj["phase_ms_per_step"]
