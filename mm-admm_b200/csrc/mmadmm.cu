@@ -1044,8 +1044,10 @@ template <int D> __global__ void __launch_bounds__(TPB) k_applyD(ElemArgs<D> a, 
 }
 
 // fixed-order final reduction of up to 3 partial arrays (lengths n0,n1,n2) -> out[0..2]
+// `out` may be mapped host memory (single-GPU contexts: the host reads the scalars after a stream synchronise, no copy is
+// queued); then the status word travels the same way.
 __global__ void __launch_bounds__(1024) k_finalize(int n0, const double *p0, int n1, const double *p1, int n2, const double *p2,
-                                                   double *out) {
+                                                   double *out, const unsigned *statusIn = nullptr, unsigned *statusOut = nullptr) {
     __shared__ double red[32];
     const double *ps[3] = {p0, p1, p2};
     const int ns[3] = {n0, n1, n2};
@@ -1057,6 +1059,7 @@ __global__ void __launch_bounds__(1024) k_finalize(int n0, const double *p0, int
         if (threadIdx.x == 0) out[q] = r;
         __syncthreads();
     }
+    if (statusOut && threadIdx.x == 0) *statusOut = *statusIn;
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -1424,8 +1427,8 @@ struct mmadmm_ctx {
     int usumPeriod = 64;      // every usumPeriod-th x-update after a prox sweep re-gathers usum exactly; 0: slot-by-slot x-updates only
     int usumAge = 0;
     int nblkE = 0, nblkV = 0, nblkProx = 0;
-    double *partIh = nullptr, *partDual = nullptr, *partPrimal = nullptr, *scal_d = nullptr, *scal_h = nullptr;
-    unsigned *status_d = nullptr, *status_h = nullptr;
+    double *partIh = nullptr, *partDual = nullptr, *partPrimal = nullptr, *scal_d = nullptr, *scal_h = nullptr, *scal_hd = nullptr;
+    unsigned *status_d = nullptr, *status_h = nullptr, *status_hd = nullptr;   // *_hd: device-side address of the mapped host buffer
     unsigned long long *hist_d = nullptr;
     bool statsOn = true, timingOn = false;
     long long admmIters = 0, proxCalls = 0, launches = 0;
@@ -1459,6 +1462,11 @@ struct mmadmm_ctx {
         a.status = status_d;
         return a;
     }
+    // where k_finalize puts its results: device scalars on a distributed context (they are combined across ranks on the
+    // device), the mapped host buffers otherwise
+    double *scalOut(int off) { return (dist ? scal_d : scal_hd) + off; }
+    const unsigned *statusIn() { return dist ? nullptr : status_d; }
+    unsigned *statusOut() { return dist ? nullptr : status_hd; }
     void phaseBegin(int ph) {
         if (!timingOn) return;
         if (evUsed + 2 > evPool.size()) {
@@ -1685,9 +1693,8 @@ template <int D> int halo_exchange(mmadmm_ctx *ctx) {
 // of the ADMM loop is then identical on all ranks (src/MeshIntegrator.cpp:162-169).
 int gather_scalars(mmadmm_ctx *ctx, int nScal) {
     cudaStream_t st = ctx->stream;
-    if (!ctx->dist) {
-        CK(cudaMemcpyAsync(ctx->scal_h, ctx->scal_d, sizeof(double) * nScal, cudaMemcpyDeviceToHost, st));
-        CK(cudaMemcpyAsync(ctx->status_h, ctx->status_d, sizeof(unsigned), cudaMemcpyDeviceToHost, st));
+    if (!ctx->dist) {   // k_finalize wrote the scalars and the status word straight into the mapped host buffers
+        (void)nScal;
         CK(cudaStreamSynchronize(st));
         return MMADMM_OK;
     }
@@ -2095,9 +2102,13 @@ int create_impl(mmadmm_ctx *ctx, const double *Vp, const double *Vc, const int *
     CK(cudaMalloc(&ctx->partPrimal, sizeof(double) * (size_t)(std::max(ctx->nblkE, ctx->nblkV) + ctx->nblkV + 1)));
     CK(cudaMalloc(&ctx->scal_d, sizeof(double) * 8));
     CK(cudaMemsetAsync(ctx->scal_d, 0, sizeof(double) * 8, st));
-    CK(cudaMallocHost(&ctx->scal_h, sizeof(double) * 8));
+    CK(cudaHostAlloc(&ctx->scal_h, sizeof(double) * 8, cudaHostAllocMapped));
+    CK(cudaHostGetDevicePointer(&ctx->scal_hd, ctx->scal_h, 0));
+    std::memset(ctx->scal_h, 0, sizeof(double) * 8);
     CK(cudaMalloc(&ctx->status_d, sizeof(unsigned)));
-    CK(cudaMallocHost(&ctx->status_h, sizeof(unsigned)));
+    CK(cudaHostAlloc(&ctx->status_h, sizeof(unsigned), cudaHostAllocMapped));
+    CK(cudaHostGetDevicePointer(&ctx->status_hd, ctx->status_h, 0));
+    *ctx->status_h = 0;
     CK(cudaMemsetAsync(ctx->status_d, 0, sizeof(unsigned), st));
     CK(cudaMalloc(&ctx->hist_d, sizeof(unsigned long long) * 52));
     CK(cudaMemsetAsync(ctx->hist_d, 0, sizeof(unsigned long long) * 52, st));
@@ -2298,7 +2309,7 @@ template <int D> int step_impl(mmadmm_ctx *ctx, int nIters, double tol, double *
         ctx->phaseBegin(3);
         const int nbp = ctx->nProxPart;
         k_finalize<<<1, 1024, 0, st>>>(nbp, ctx->partIh, gV + ((ctx->dist && ctx->nShared > 0) ? ctx->nblkSh : 0), ctx->partPrimal, nbp,
-                                       ctx->partDual, ctx->scal_d);
+                                       ctx->partDual, ctx->scalOut(0), ctx->statusIn(), ctx->statusOut());
         ctx->launches += 1;
         ctx->phaseEnd();
         int rc = gather_scalars(ctx, 3);   // synchronises; sums over ranks on a distributed context
@@ -2326,7 +2337,7 @@ template <int D> int energy_impl(mmadmm_ctx *ctx, double *I) {
     cudaStream_t st = ctx->stream;
     ElemArgs<D> a = ctx->elemArgs<D>(0.0);
     k_energy<D><<<ctx->nblkE, TPB, 0, st>>>(a, ctx->partPrimal);
-    k_finalize<<<1, 1024, 0, st>>>(ctx->nblkE, ctx->partPrimal, 0, nullptr, 0, nullptr, ctx->scal_d + 3);
+    k_finalize<<<1, 1024, 0, st>>>(ctx->nblkE, ctx->partPrimal, 0, nullptr, 0, nullptr, ctx->scalOut(3), ctx->statusIn(), ctx->statusOut());
     ctx->launches += 2;
     // k_finalize writes out[0] of its `out` argument => scal_d[3]
     int rcg = gather_scalars(ctx, 4);
@@ -2352,7 +2363,7 @@ template <int D> int euler_impl(mmadmm_ctx *ctx, double *IhOut) {
                                                                      ctx->x, ctx->xPrev);
         ctx->launches++;
     }
-    k_finalize<<<1, 1024, 0, st>>>(ctx->nblkE, ctx->partPrimal, 0, nullptr, 0, nullptr, ctx->scal_d + 3);
+    k_finalize<<<1, 1024, 0, st>>>(ctx->nblkE, ctx->partPrimal, 0, nullptr, 0, nullptr, ctx->scalOut(3), ctx->statusIn(), ctx->statusOut());
     ctx->launches++;
     int rcg = gather_scalars(ctx, 4);
     if (rcg) return rcg;
