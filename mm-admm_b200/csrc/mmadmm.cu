@@ -1402,7 +1402,7 @@ struct mmadmm_ctx {
     double *xloc_h = nullptr;
     std::vector<int> verts_h;
     std::vector<std::pair<int, int>> runs;   // (first local vertex, length) of consecutive global ids
-    double *sPart = nullptr, *sTot = nullptr, *sendBuf = nullptr, *recvBuf = nullptr, *scalAll_d = nullptr, *scalAll_h = nullptr;
+    double *sPart = nullptr, *sTot = nullptr, *sendBuf = nullptr, *recvBuf = nullptr, *scalAll_d = nullptr, *scalAll_h = nullptr, *scalAll_hd = nullptr;
     int nProxPart = 0;           // number of per-block (or per-warp) partial sums the last prox launch wrote
     int numSMs = 148;
     bool smemAttrSet[16] = {false};
@@ -1701,14 +1701,17 @@ int gather_scalars(mmadmm_ctx *ctx, int nScal) {
     if (ctx->p2p) {
         const unsigned long long ep = ++ctx->scalEpoch;
         k_scal_push<<<1, 32, 0, st>>>(ctx->nranks, ctx->rank, ctx->scal_d, ctx->status_d, ctx->peerScal_d, ctx->peerScalFlag_d, ep);
-        k_scal_wait<<<1, 32, 0, st>>>(ctx->nranks, ctx->mbScal_d, ctx->scalFlags_d, ep, ctx->scalAll_d);
+        k_scal_wait<<<1, 32, 0, st>>>(ctx->nranks, ctx->mbScal_d, ctx->scalFlags_d, ep, ctx->scalAll_hd);   // mapped host memory: no copy
         ctx->launches += 1;
+        CK(cudaStreamSynchronize(st));
     } else {
         k_status_to_double<<<1, 1, 0, st>>>(ctx->status_d, ctx->scal_d + 4);
         NK(nccl().allGather(ctx->scal_d, ctx->scalAll_d, 5, NCCL_FLOAT64, ctx->comm, st));
     }
-    CK(cudaMemcpyAsync(ctx->scalAll_h, ctx->scalAll_d, sizeof(double) * 5 * ctx->nranks, cudaMemcpyDeviceToHost, st));
-    CK(cudaStreamSynchronize(st));
+    if (!ctx->p2p) {
+        CK(cudaMemcpyAsync(ctx->scalAll_h, ctx->scalAll_d, sizeof(double) * 5 * ctx->nranks, cudaMemcpyDeviceToHost, st));
+        CK(cudaStreamSynchronize(st));
+    }
     unsigned stat = 0;
     for (int k = 0; k < 4; k++) ctx->scal_h[k] = 0.0;
     for (int r = 0; r < ctx->nranks; r++) {
@@ -2483,7 +2486,8 @@ int mmadmm_create_dist(int D, int P, int E, const double *Vp, const double *Vc, 
     CK(cudaMalloc(&ctx->sendBuf, sizeof(double) * nbD));
     CK(cudaMalloc(&ctx->recvBuf, sizeof(double) * nbD));
     CK(cudaMalloc(&ctx->scalAll_d, sizeof(double) * 5 * nranks));
-    CK(cudaMallocHost(&ctx->scalAll_h, sizeof(double) * 5 * nranks));
+    CK(cudaHostAlloc(&ctx->scalAll_h, sizeof(double) * 5 * nranks, cudaHostAllocMapped));
+    CK(cudaHostGetDevicePointer(&ctx->scalAll_hd, ctx->scalAll_h, 0));
     ctx->nblkSh = cdiv(std::max(ctx->nShared, 1), TPB_V);
     CK(cudaStreamSynchronize(st));
     {
