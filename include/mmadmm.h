@@ -115,7 +115,11 @@ int mmadmm_get_timing(mmadmm_ctx *ctx, double *ms5, long long *counts5, int rese
 
 /* Options: "timing" (0/1), "stats" (0/1, default 1), "prox_variant" (kernel tile/occupancy variant, debugging),
  * "iso_grid" (0/1, default 1): when every tensor of the monitor grid is m*I bitwise, look m up in a scalar grid
- * (bit-identical results, D*D..10x fewer bytes per lookup); "iso_grid_active" is a query: returns 0 iff that path is on. */
+ * (bit-identical results, D*D..10x fewer bytes per lookup); "iso_grid_active" is a query: returns 0 iff that path is on;
+ * "usum_period" (default 64): the x-updates work on per-vertex sums of the dual variable that follow a recurrence
+ *  and are re-gathered exactly every usum_period-th update; 0 = every x-update gathers z - u slot by slot,
+ * the literal form of src/MeshIntegrator.cpp:137-138,159-160 (results agree to rounding, tests hold 1e-12);
+ * "p2p_active" is a query: returns 0 iff a distributed context exchanges through NVLink peer stores. */
 int mmadmm_set_option(mmadmm_ctx *ctx, const char *name, int value);
 
 /* The CUDA stream every kernel of this context is launched on (cudaStream_t as void*). */
