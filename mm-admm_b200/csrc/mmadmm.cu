@@ -667,15 +667,20 @@ __global__ void __launch_bounds__((D + 1) * 32, MINB) k_prox_vw(const __grid_con
                     for (int k = 0; k < DD; k++) mPre[v].a[k] = Ms[(v * DD + k) * 32 + lane];
                 }
             }
-            const double en = block_grad_core<D, true, ISO>(z, xi, COMP, mPre, mIso, a.fc, grad, inv);
+            double en;
+            if constexpr (ISO) {     // only the own vertex's block of the gradient is formed
+                en = block_grad_own_iso<D>(z, xi, COMP, mIso, a.fc, q, g, inv);
+            } else {
+                en = block_grad_core<D, true, ISO>(z, xi, COMP, mPre, mIso, a.fc, grad, inv);
 #pragma unroll
-            for (int l = 0; l < D; l++) g[l] = 0.0;
+                for (int l = 0; l < D; l++) g[l] = 0.0;
 #pragma unroll
-            for (int v = 0; v < NV; v++)
-                if (v == q) {
+                for (int v = 0; v < NV; v++)
+                    if (v == q) {
 #pragma unroll
-                    for (int l = 0; l < D; l++) g[l] = grad[D * v + l];
-                }
+                        for (int l = 0; l < D; l++) g[l] = grad[D * v + l];
+                    }
+            }
 #pragma unroll
             for (int l = 0; l < D; l++) g[l] = ownFixed ? 0.0 : g[l] + a.fc.w2 * (-dxo[l] + zo[l]);
             return en;

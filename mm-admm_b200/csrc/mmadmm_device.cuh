@@ -459,6 +459,86 @@ __device__ __forceinline__ double block_grad_core(const double *z, const double 
     return absK * G;
 }
 
+// Isotropic blockGrad for ONE vertex q of the element (k_prox_vw: warp q owns vertex q).  Same quantities as
+// block_grad_core<D, true, true>, but the gradient block of vertex q needs only one row vector a of Einv:
+//   q >= 1: grad_q = -vLoc(q-1, :) |K|,  vLoc(r, :) = c1 Einv(r, :) + sJ mu Einv(r, :) (FJ^T FJ) - bc/(D+1)       (a = Einv(q-1, :))
+//   q == 0: grad_0 = (sum_r vLoc(r, :) + bc) |K|                                                            (a = sum_r Einv(r, :))
+// so the 3x3 products Einv*(FJ^T FJ), the scaled T and the full vLoc are replaced by one vector-matrix product.  For q >= 1 the
+// arithmetic is the reference's operation for operation; for q == 0 the row sum is taken before the product (rounding level).
+template <int D>
+__device__ __forceinline__ double block_grad_own_iso(const double *z, const double *xi, bool compMesh, const double *mIso,
+                                                     const FuncConsts<D> &fc, int q, double *g, bool &inverted) {
+    const double dFact = (D == 2) ? 2.0 : 6.0;
+    const double d = (double)D;
+    const double p = 1.5;
+    const double theta = 1.0 / 3.0;
+    double ms = mIso[0];
+#pragma unroll
+    for (int i = 1; i < D + 1; i++) ms += mIso[i];
+    SMat<D> E, Ehat;
+#pragma unroll
+    for (int j = 0; j < D; j++)
+#pragma unroll
+        for (int l = 0; l < D; l++) {
+            E(l, j) = z[D * (j + 1) + l] - z[l];
+            Ehat(l, j) = compMesh ? (xi[D * (j + 1) + l] - xi[l]) : fc.Ehat[l * D + j];
+        }
+    const double Edet = sdet<D>(E);
+    if (!(Edet > 0)) inverted = true;
+    const SMat<D> Einv = sinv<D>(E);
+    const SMat<D> FJ = smul<D>(Ehat, Einv);
+    const double detFJ = sdet<D>(FJ);
+    const double mu = 1.0 / (ms * ((double)D + 1));
+    double fro = 0.0;
+#pragma unroll
+    for (int k = 0; k < D * D; k++) fro = (k == 0) ? FJ.a[0] * FJ.a[0] : fro + FJ.a[k] * FJ.a[k];
+    const double trJMJt = mu * fro;
+    const double detM = rsqrt((D == 2) ? mu * mu : mu * mu * mu);
+    double trp, trpm1;
+    pow_pair<D>(trJMJt, trp, trpm1);
+    const double qq = detFJ / detM;
+    const double G = theta * detM * trp + (1.0 - 2.0 * theta) * fc.dpow * detM * (qq * sqrt(qq));
+    const double absK = fabs(Edet / dFact);
+    const double sJ = d * p * theta * detM * trpm1;
+    const double rsDetM = rsqrt(detM);
+    const double sDetFJ = sqrt(detFJ);
+    const double dGddet = p * (1.0 - 2.0 * theta) * fc.dpow * rsDetM * sDetFJ;
+    const double s1 = -0.5 * theta * d * p * detM * trpm1;
+    const double s2 = (0.5 * theta * detM * trp + ((0.5 - theta) * (1.0 - p) * fc.dpow) * rsDetM * (detFJ * sDetFJ));
+    const double trdGdM = s1 * (mu * mu) * fro + (double)D * (s2 * mu);
+    double bc[D];
+#pragma unroll
+    for (int l = 0; l < D; l++) bc[l] = 0.0;
+#pragma unroll
+    for (int j = 0; j < D; j++) {
+        const double tr = trdGdM * (mIso[j + 1] - mIso[0]);
+#pragma unroll
+        for (int l = 0; l < D; l++) bc[l] += Einv(j, l) * tr;
+    }
+    double a[D];
+#pragma unroll
+    for (int k = 0; k < D; k++) {
+        double sum = Einv(0, k);
+        double row = Einv(0, k);
+#pragma unroll
+        for (int r = 1; r < D; r++) { sum += Einv(r, k); row = (q == r + 1) ? Einv(r, k) : row; }
+        a[k] = (q == 0) ? sum : row;
+    }
+    const SMat<D> S = smul_tn<D>(FJ, FJ);
+    const double sJm = sJ * mu;
+    const double c1 = (-G + dGddet * detFJ);
+    const double inv = 1.0 / ((double)D + 1.0);
+#pragma unroll
+    for (int l = 0; l < D; l++) {
+        double es = a[0] * S(0, l);
+#pragma unroll
+        for (int k = 1; k < D; k++) es += a[k] * S(k, l);
+        const double v = (c1 * a[l] + sJm * es);
+        g[l] = ((q == 0) ? ((v - d * (bc[l] * inv)) + bc[l]) : -(v - bc[l] * inv)) * absK;
+    }
+    return absK * G;
+}
+
 // Energy G*|K| and (optionally) the unregularised element gradient.  z: n = D(D+1) doubles, vertex-major.
 // Returns absK*G.  `inverted` is set when det(E) <= 0 (the reference asserts there, :174).
 // ISO (compile-time): every grid tensor is m*I, so the D+1 vertex tensors are D+1 scalars (4 instead of 36 live doubles
