@@ -560,6 +560,65 @@ static double eulerStep(Oracle &o) {
     return Ih;
 }
 
+// Method 2 (backward Euler), Jacobian of the residual.  src/Mesh.cpp:1111-1135 buildEulerJac + :1161-1261 FSubJac on
+// the CSR pattern (ia, ja) that buildMatrix (src/Mesh.cpp:305-337) gives LASolver: rows D*v+p couple to all D columns of
+// every vertex sharing a simplex with v.  Quirks kept: the finite differences (h = 10 sqrt(eps), forward) are taken at
+// *Vp, which this method never refreshes (no updateAfterStep on the path), not at the iterate x; the perturbed direction
+// i fills ROW i of `derivs` (d grad / d x_{off,i}, i.e. the Hessian column used as a row); for a BOUNDARY_FIXED vertex
+// derivs is the identity only when the vertex is local vertex 0 of the simplex (r == c with c in [D off, D off + D));
+// values are summed in ascending simplex order, then scaled by dt/tau, then 1 is added on the diagonal.
+template <int D>
+static void buildEulerJac(Oracle &o, const int *ia, const int *ja, double *a) {
+    constexpr int n = D * (D + 1);
+    const double h = 10.0 * std::sqrt(std::numeric_limits<double>::epsilon());
+    const int N = o.P * D;
+    for (int k = 0; k < ia[N]; k++) a[k] = 0.0;
+    for (int pntId = 0; pntId < o.P; pntId++) {
+        for (int q = o.incPtr[pntId]; q < o.incPtr[pntId + 1]; q++) {
+            const int sId = o.incIdx[q] / (D + 1);  // ascending element order == std::set iteration order
+            double xiLoc[n], xLoc[n], Gk[n], Gkp1[n], xPurt[n], derivs[D][n], Igt;
+            int off = 0;
+            for (int nn = 0; nn < D + 1; nn++) {
+                int v = o.F[(size_t)sId * (D + 1) + nn];
+                if (v == pntId) off = nn;
+                for (int l = 0; l < D; l++) {
+                    if (o.compMesh) xiLoc[nn * D + l] = o.Vc[(size_t)v * D + l];
+                    xLoc[nn * D + l] = o.Vp[(size_t)v * D + l];
+                }
+            }
+            blockGrad<D>(o, sId, xLoc, xiLoc, Gk, true, false, Igt);
+            for (int c = 0; c < n; c++) xPurt[c] = xLoc[c];
+            if (o.mask[pntId] == BOUNDARY_FIXED) {
+                for (int r = 0; r < D; r++)
+                    for (int c = 0; c < n; c++) derivs[r][c] = 0.0;
+                for (int r = 0; r < D; r++)
+                    for (int c = D * off; c < D * (off + 1); c++)
+                        if (r == c) derivs[r][c] = 1.0;
+            } else {
+                for (int i = 0; i < D; i++) {
+                    xPurt[D * off + i] += h;
+                    blockGrad<D>(o, sId, xPurt, xiLoc, Gkp1, true, false, Igt);
+                    for (int c = 0; c < n; c++) derivs[i][c] = (Gkp1[c] - Gk[c]) / h;
+                    xPurt[D * off + i] = xLoc[D * off + i];
+                }
+            }
+            for (int p = 0; p < D; p++) {
+                const int row = D * pntId + p;
+                for (int k = ia[row]; k < ia[row + 1]; k++) {
+                    const int colIndex = ja[k] / D, colOff = ja[k] % D;
+                    for (int j = 0; j < D + 1; j++)
+                        if (o.F[(size_t)sId * (D + 1) + j] == colIndex) a[k] += derivs[p][D * j + colOff];
+                }
+            }
+        }
+    }
+    for (int r = 0; r < N; r++)
+        for (int k = ia[r]; k < ia[r + 1]; k++) {
+            a[k] *= (o.dt / o.tau);
+            if (ja[k] == r) a[k] += 1.0;
+        }
+}
+
 // src/Mesh.cpp:496-530 (reads *Vp, ignores its argument)
 template <int D>
 static double computeEnergy(Oracle &o) {
@@ -995,6 +1054,22 @@ int orc_euler_step(void *h, double *Ih) {
     if (Ih) *Ih = v;
     return o.error;
 }
+// Method 2 primitives (the Newton loop of src/Mesh.cpp:1263-1341 is driven from tests/oracle_lib.py, with the linear
+// solves done by the reference's own LASolver in oracle/_ref or by the restated ILU(0)/CGSTAB of tests/pcg_oracle.py).
+int orc_euler_step_mod(void *h, const double *x, double *grad, double *Ih) {
+    Oracle &o = *(Oracle *)h;
+    std::vector<double> xv(x, x + (size_t)o.P * o.D), g((size_t)o.P * o.D);
+    double v = (o.D == 2) ? eulerStepMod<2>(o, xv, g) : eulerStepMod<3>(o, xv, g);
+    std::memcpy(grad, g.data(), g.size() * sizeof(double));
+    if (Ih) *Ih = v;
+    return o.error;
+}
+int orc_build_euler_jac(void *h, const int *ia, const int *ja, double *a) {
+    Oracle &o = *(Oracle *)h;
+    if (o.D == 2) buildEulerJac<2>(o, ia, ja, a); else buildEulerJac<3>(o, ia, ja, a);
+    return o.error;
+}
+void orc_set_x(void *h, const double *x) { Oracle &o = *(Oracle *)h; std::memcpy(o.x.data(), x, o.x.size() * sizeof(double)); }
 double orc_energy(void *h) {
     Oracle &o = *(Oracle *)h;
     return (o.D == 2) ? computeEnergy<2>(o) : computeEnergy<3>(o);

@@ -1,7 +1,7 @@
 """Regenerates tests/golden/ from the reference checkout (run in the build container only;
 /root/reference does not exist on the GPU box).  Copies DATA fixtures, never sources:
   * the committed energy traces Experiments/Results/<Name>/Ih0.txt (6 printed digits) that pin the oracle
-    (+ Monitor220/Ih1.txt, the explicit-Euler trace),
+    (+ Monitor220/Ih1.txt, the explicit-Euler trace; + Ih2.txt of four inputs, the backward-Euler traces),
   * the full-precision input mesh Experiments/Results/BaseCircle/CircleEx12{points,triangles,mask}.txt
     and BaseCircle/CircleEx6*, BaseCircle3D/3DCircleEx6* used by the FromFile experiments.
 """
@@ -19,6 +19,9 @@ for name, k in [("Monitor210", 20), ("Monitor220", 34), ("Monitor310", 57), ("Mo
     p1 = f"{REF}/Results/{name}/Ih1.txt"   # Method 1 (explicit Euler) trace, where the reference commits one for the shipped input
     if name == "Monitor220" and os.path.exists(p1):
         traces[name]["Ih1"] = [float(l.split(",")[1]) for l in open(p1).read().strip().split("\n")]
+    p2 = f"{REF}/Results/{name}/Ih2.txt"   # Method 2 (backward Euler) traces: all steps (52 / 18 / 355 / 86)
+    if name in ("Monitor210", "Monitor220", "Monitor310", "3DMonitor210") and os.path.exists(p2):
+        traces[name]["Ih2"] = [float(l.split(",")[1]) for l in open(p2).read().strip().split("\n")]
 json.dump(traces, open(f"{HERE}/ih_traces.json", "w"), indent=1)
 for stem in ["BaseCircle/CircleEx12", "BaseCircle/CircleEx6", "BaseCircle3D/3DCircleEx6"]:
     for suf in ["points", "triangles", "mask"]:

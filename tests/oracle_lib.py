@@ -59,6 +59,11 @@ def lib():
         L.orc_monitor_eval.argtypes = [C.c_int, C.c_int, C.c_int, c_dp, c_dp]
         L.orc_lu_inverse.restype = C.c_int
         L.orc_lu_inverse.argtypes = [C.c_int, c_dp, c_dp]
+        L.orc_euler_step_mod.restype = C.c_int
+        L.orc_euler_step_mod.argtypes = [C.c_void_p, c_dp, c_dp, c_dp]
+        L.orc_build_euler_jac.restype = C.c_int
+        L.orc_build_euler_jac.argtypes = [C.c_void_p, c_ip, c_ip, c_dp]
+        L.orc_set_x.argtypes = [C.c_void_p, c_dp]
         L.orc_uniform_rect_mesh.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int] + [C.c_double] * 6 + [C.c_int, c_dp, c_ip, c_ip]
         _LIB = L
     return _LIB
@@ -105,6 +110,8 @@ class Oracle:
         self.Vc = None if Vc is None else np.ascontiguousarray(Vc, dtype=np.float64)
         self.h = self.L.orc_create(self.D, self.P, self.E, _dp(self.Vp), _dp(self.Vc), _ip(self.F), _ip(self.mask),
                                    _dp(self.mon), rho, tau, dt, int(grad_use), nthreads)
+        self._dt, self._tau = dt, tau
+        self._m2_step_taken, self._m2_a = False, None
 
     def __del__(self):
         if getattr(self, "h", None):
@@ -124,6 +131,76 @@ class Oracle:
 
     def energy(self):
         return self.L.orc_energy(self.h)
+
+    # ---- Method 2 (backward Euler): Mesh::backwardsEulerStep, src/Mesh.cpp:1263-1341 ----
+    def euler_step_mod(self, x):
+        """Mesh::eulerStepMod (src/Mesh.cpp:533-579): energy and INTERIOR-only assembled gradient at x."""
+        x = np.ascontiguousarray(x, dtype=np.float64).reshape(-1)
+        g = np.zeros_like(x); Ih = C.c_double()
+        rc = self.L.orc_euler_step_mod(self.h, _dp(x), _dp(g), C.byref(Ih))
+        return Ih.value, g, rc
+
+    def jacobian_entries(self):
+        """The set_entry sequence of Mesh::buildMatrix (src/Mesh.cpp:305-337): per element, each rotation of its vertex
+        list couples the D rows of the leading vertex with the D columns of every vertex of the element."""
+        D = self.D
+        Fo = self.F_oriented()
+        rows, cols = [], []
+        rr, cc = np.meshgrid(np.arange(D), np.arange(D), indexing="ij")
+        for it in range(D + 1):
+            lead = Fo[:, it]
+            for nn in range(D + 1):
+                other = Fo[:, (it + nn) % (D + 1)]
+                rows.append((lead[:, None] * D + rr.reshape(1, -1)).reshape(self.E, -1))
+                cols.append((other[:, None] * D + cc.reshape(1, -1)).reshape(self.E, -1))
+        # element-major order like the reference's loop nest (the packed CSR does not depend on it)
+        rows = np.concatenate(rows, axis=1).reshape(-1).astype(np.int32)
+        cols = np.concatenate(cols, axis=1).reshape(-1).astype(np.int32)
+        return rows, cols
+
+    def build_euler_jac(self, ia, ja):
+        """Mesh::buildEulerJac + FSubJac (src/Mesh.cpp:1111-1261) on the CSR pattern (ia, ja): I + (dt/tau) * FD Hessian
+        taken at Vp."""
+        a = np.zeros(int(ia[-1]))
+        rc = self.L.orc_build_euler_jac(self.h, _ip(ia), _ip(ja), _dp(a))
+        return a, rc
+
+    def backwards_euler_step(self, solver, tol=1e-3, max_iters=1000):
+        """One Mesh::backwardsEulerStep(dt, x, grad, tol) (src/Mesh.cpp:1263-1341) with `solver` doing what
+        jac->sfac / jac->solve do there (tests/pcg_oracle.LASolverJac = the reference's own LASolver from oracle/_ref).
+        Returns the energy of the last evaluated iterate, the Newton iteration count and the inner iteration counts."""
+        dt_tau = self._dt / self._tau
+        x = self.x().reshape(-1).copy()
+        xn = x.copy()
+        Ih, grad, rc = self.euler_step_mod(x)
+        x -= dt_tau * grad
+        if not self._m2_step_taken:
+            self._m2_a, rc2 = self.build_euler_jac(solver.ia, solver.ja)
+            rc |= rc2
+            solver.sfac()
+        n_iter, g1_prev, inner = 0, np.inf, []
+        while True:
+            Ih, grad, rc2 = self.euler_step_mod(x)
+            rc |= rc2
+            grad *= dt_tau
+            grad += (x - xn)
+            g1 = float(np.sum(np.abs(grad)))
+            if g1 < 0.1 * tol:
+                break
+            if (not self._m2_step_taken) or abs(g1 - g1_prev) / g1 < 0.25:
+                self._m2_a, rc2 = self.build_euler_jac(solver.ia, solver.ja)
+                rc |= rc2
+                self._m2_step_taken = True
+            dx, nit = solver.solve(self._m2_a, -grad)
+            assert nit > 0
+            inner.append(nit)
+            x += dx
+            n_iter += 1
+            g1_prev = g1
+            if n_iter >= max_iters:
+                break
+        self.L.orc_set_x(self.h, _dp(x))
+        return dict(Ih=Ih, newton_iters=n_iter, inner_iters=inner, res1=g1, status=rc)
 
     def _vec(self, fn, size):
         out = np.zeros(size)

@@ -117,3 +117,101 @@ def laplacian_like_matrix(F, P, D, tau, dt, rho):
     A = (tau * sp.identity(P * D, format="csr") + (dt * dt * w * w) * L).tocsr()
     A.sort_indices()
     return A
+
+
+class LASolverJac:
+    """The reference's LASolver matrix object driven as Method 2 drives it (oracle/lasolver_shim.cpp las_*): structure from
+    the set_entry sequence of Mesh::buildMatrix, ParamIter of src/Mesh.cpp:266-304 (ILU(0), CGSTAB, resid_reduc 1e-6)."""
+
+    def __init__(self, n, rows, cols):
+        L = C.CDLL(REF_SO)
+        L.las_open.restype = C.c_void_p
+        L.las_open.argtypes = [C.c_int, C.c_longlong, C.POINTER(C.c_int), C.POINTER(C.c_int)]
+        L.las_nnz.argtypes = [C.c_void_p]
+        L.las_pattern.argtypes = [C.c_void_p, C.POINTER(C.c_int), C.POINTER(C.c_int)]
+        L.las_sfac.argtypes = [C.c_void_p]
+        L.las_solve.argtypes = [C.c_void_p, C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(C.c_double),
+                                C.POINTER(C.c_int)]
+        L.las_close.argtypes = [C.c_void_p]
+        self.L, self.n = L, n
+        rows = np.ascontiguousarray(rows, dtype=np.int32); cols = np.ascontiguousarray(cols, dtype=np.int32)
+        ip = lambda a: a.ctypes.data_as(C.POINTER(C.c_int))
+        self.h = L.las_open(n, len(rows), ip(rows), ip(cols))
+        assert self.h
+        nnz = L.las_nnz(self.h)
+        self.ia = np.zeros(n + 1, dtype=np.int32); self.ja = np.zeros(nnz, dtype=np.int32)
+        L.las_pattern(self.h, ip(self.ia), ip(self.ja))
+
+    def sfac(self):
+        assert self.L.las_sfac(self.h) == 0
+
+    def solve(self, a, b):
+        dp = lambda v: v.ctypes.data_as(C.POINTER(C.c_double))
+        a = np.ascontiguousarray(a, dtype=np.float64); b = np.ascontiguousarray(b, dtype=np.float64)
+        x = np.zeros(self.n); nit = C.c_int()
+        assert self.L.las_solve(self.h, dp(a), dp(b), dp(x), C.byref(nit)) == 0
+        return x, nit.value
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            self.L.las_close(self.h)
+            self.h = None
+
+
+def cgstab(A, b, ctol, nitmax, prec):
+    """LASolver's scaler_cgstab restated (accel_class.cpp:229-273 init, :280-399 one iteration; driver loop
+    MatrixIter.cpp:693-800 with a zero initial guess and toler = 0): right-preconditioned BiCGSTAB with rhat = r0,
+    alpha = rholst = omega = 1 and p = A vbar = 0 at the start, `tiny` = 1e-300 guards in beta and omega, stop when
+    ||r|| / ||r0|| < ctol (or when no component moved)."""
+    tiny = 1.e-300
+    n = len(b)
+    x = np.zeros(n); res = b.astype(np.float64).copy(); res0 = res.copy()
+    pvec = np.zeros(n); avbar = np.zeros(n)
+    alpha = rholst = omega = 1.0
+    rmsi = np.sqrt(res @ res)
+    nitr = 0
+    for _ in range(nitmax):
+        nitr += 1
+        rho = res0 @ res
+        beta = rho / (rholst + tiny)
+        beta *= alpha / (omega + tiny)
+        rholst = rho
+        pvec = res + beta * (pvec - omega * avbar)
+        vbar = prec(pvec)
+        avbar = A @ vbar
+        alpha = rho / (res0 @ avbar)
+        svec = res - alpha * avbar
+        zvec = prec(svec)
+        tvec = A @ zvec
+        omega = (tvec @ svec) / (tvec @ tvec + tiny)
+        step = alpha * vbar + omega * zvec
+        x += step
+        res = svec - omega * tvec
+        rms = np.sqrt(res @ res)
+        if not np.any(np.abs(step) > 0.0) or rms / rmsi < ctol:
+            return x, nitr
+    return x, -1
+
+
+class RestatedJac:
+    """Same interface as LASolverJac with nothing from the reference behind it: numpy ILU(0) (`ilu0`) applied through two
+    scipy triangular solves, and `cgstab`.  Used where oracle/_ref is the thing being cross-checked, and as the Method 2
+    linear-solve oracle that needs no reference build."""
+
+    def __init__(self, n, rows, cols):
+        pat = sp.csr_matrix((np.ones(len(rows)), (rows, cols)), shape=(n, n))
+        pat.sum_duplicates(); pat.sort_indices()
+        self.n, self.ia, self.ja = n, pat.indptr.astype(np.int32), pat.indices.astype(np.int32)
+
+    def sfac(self):
+        pass  # level-0 fill: the factor lives on A's own pattern
+
+    def solve(self, a, b, resid_reduc=1.e-6, nitmax=10000):
+        from scipy.sparse.linalg import spsolve_triangular
+        A = sp.csr_matrix((np.asarray(a, dtype=np.float64), self.ja, self.ia), shape=(self.n, self.n))
+        lu, diag = ilu0(A)
+        M = sp.csr_matrix((lu, self.ja, self.ia), shape=(self.n, self.n))
+        Lm = (sp.tril(M, -1) + sp.identity(self.n)).tocsr()
+        Um = sp.triu(M, 0).tocsr()
+        prec = lambda r: spsolve_triangular(Um, spsolve_triangular(Lm, r, lower=True), lower=False)
+        return cgstab(A, np.asarray(b, dtype=np.float64), resid_reduc, nitmax, prec)

@@ -88,3 +88,87 @@ def test_explicit_euler_trace_matches_reference(golden_dir):
     assert len(ref) == 50
     for i, (g, e) in enumerate(zip(got, ref)):
         assert fmt6(g) == e, f"euler step {i}: oracle {g!r} vs reference {e}"
+
+
+def _method2_solver(orc, restated=False):
+    import pcg_oracle as PO
+    rows, cols = orc.jacobian_entries()
+    cls = PO.RestatedJac if (restated or not PO.have_lasolver()) else PO.LASolverJac
+    return cls(orc.P * orc.D, rows, cols)
+
+
+@pytest.mark.parametrize("name,restated", [("Monitor210", False), ("Monitor220", False), ("Monitor310", False),
+                                           ("3DMonitor210", False), ("Monitor210", True)])
+def test_backward_euler_trace_matches_reference(name, restated, golden_dir):
+    """Method 2 (Mesh::backwardsEulerStep, src/Mesh.cpp:1263-1341: Newton on x - xn + (dt/tau) grad I = 0 with the
+    finite-difference Jacobian of FSubJac and LASolver's ILU(0) + CGSTAB): Experiments/Results/<name>/Ih2.txt, ALL
+    committed steps (18 / 52 / 355 / 86), linear solves by the reference's own LASolver (oracle/_ref) or, `restated`,
+    by the numpy ILU(0) + CGSTAB restatement."""
+    if name == "3DMonitor210":
+        import pcg_oracle as PO
+        if not PO.have_lasolver():
+            pytest.skip("3D trace needs oracle/_ref (the numpy ILU(0) is too slow at this size)")
+    orc, spec = build_from_input(name, golden_dir)
+    ref = TRACES[name]["Ih2"]
+    S = _method2_solver(orc, restated)
+    got = [orc.energy()]
+    for _ in range(len(ref) - 1):
+        r = orc.backwards_euler_step(S, 1e-3)  # tol hard-coded in main.cpp:190
+        assert r["status"] == 0 and r["newton_iters"] < 1000
+        got.append(r["Ih"])
+    for i, (g, e) in enumerate(zip(got, ref)):
+        assert fmt6(g) == e, f"{name} backward-Euler step {i}: oracle {g!r} vs reference {e}"
+
+
+def test_restated_cgstab_equals_lasolver(golden_dir):
+    """The numpy ILU(0) + CGSTAB restatement against the reference's LASolver on the Method 2 Jacobian of Monitor220:
+    same CSR pattern from the same set_entry sequence, same iteration counts, iterates equal to rounding."""
+    import pcg_oracle as PO
+    if not PO.have_lasolver():
+        pytest.skip("oracle/_ref not built")
+    a, _ = build_from_input("Monitor220", golden_dir)
+    b, _ = build_from_input("Monitor220", golden_dir)
+    S, R = _method2_solver(a), _method2_solver(b, restated=True)
+    assert np.array_equal(S.ia, R.ia) and np.array_equal(S.ja, R.ja)
+    for _ in range(3):
+        ra, rb = a.backwards_euler_step(S), b.backwards_euler_step(R)
+        assert ra["inner_iters"] == rb["inner_iters"] and ra["newton_iters"] == rb["newton_iters"]
+        assert abs(ra["Ih"] - rb["Ih"]) <= 1e-13 * abs(ra["Ih"])
+        assert np.abs(a.x() - b.x()).max() <= 1e-13
+
+
+def test_backward_euler_jacobian_is_fd_hessian(golden_dir):
+    """FSubJac structure: FIXED rows carry 1 + (dt/tau) * (#incident elements in which the vertex is local vertex 0) on
+    the diagonal and nothing else; INTERIOR rows are I + (dt/tau) * (forward-difference derivative of the assembled
+    gradient at Vp), checked against a directional difference of eulerStepMod."""
+    orc, spec = build_from_input("Monitor220", golden_dir)
+    S = _method2_solver(orc, restated=True)
+    a, rc = orc.build_euler_jac(S.ia, S.ja)
+    assert rc == 0
+    import scipy.sparse as sp
+    n = orc.P * orc.D
+    J = sp.csr_matrix((a, S.ja, S.ia), shape=(n, n)).toarray()
+    D = orc.D
+    Fo = orc.F_oriented()
+    lead = np.bincount(Fo[:, 0], minlength=orc.P)
+    s = spec["dt"] / spec["tau"]
+    inter = np.repeat(orc.mask == 2, D)
+    for v in np.nonzero(orc.mask == 1)[0]:
+        for p in range(D):
+            row = J[D * v + p].copy()
+            assert row[D * v + p] == 1.0 + s * lead[v]
+            row[D * v + p] = 0.0
+            assert not row.any()
+    # INTERIOR rows: row (v, p) holds d grad / d x_{v,p} (FSubJac stores the perturbed direction as the row), so for a
+    # perturbation dv of the interior vertices  J^T dv = dv + (dt/tau) * (g(Vp + eps dv) - g(Vp)) / eps  on interior dofs,
+    # g = the assembled INTERIOR gradient of eulerStepMod.  (J is NOT symmetric: blockGrad is not an exact gradient.)
+    Ji = J[np.ix_(inter, inter)]
+    x0 = orc.x().reshape(-1)
+    rng = np.random.default_rng(5)
+    dv = np.where(inter, rng.standard_normal(n), 0.0)
+    eps = 10.0 * np.sqrt(np.finfo(float).eps)
+    _, g0, _ = orc.euler_step_mod(x0)
+    _, g1, _ = orc.euler_step_mod(x0 + eps * dv)
+    want = dv[inter] + s * (g1 - g0)[inter] / eps
+    got = Ji.T @ dv[inter]
+    assert np.abs(got - want).max() < 1e-5 * np.abs(want).max()
