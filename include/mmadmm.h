@@ -59,6 +59,20 @@ int mmadmm_step(mmadmm_ctx *ctx, int nIters, double tol, double *Ih, int *itersT
  * the caller reads the positions with mmadmm_get_x when it wants them. */
 int mmadmm_euler_step(mmadmm_ctx *ctx, double *Ih);
 
+/* Method 2: one MeshIntegrator::backwardsEulerStep(dt, tol) (src/MeshIntegrator.cpp:68-76 -> Mesh::backwardsEulerStep,
+ * src/Mesh.cpp:1263-1341): Newton iteration on F(x) = x - xn + (dt/tau) grad I(x) = 0 from the explicit-Euler guess, gradient
+ * by eulerStepMod (INTERIOR vertices only), Jacobian I + (dt/tau) * forward differences of the element gradients (FSubJac,
+ * src/Mesh.cpp:1161-1261; h = 10 sqrt(eps); taken at the vertex positions Vp of construction / the last Method-0 step, which
+ * this method never refreshes; rebuilt only while no step has been taken or when the 1-norm of F stalls), linear solves by
+ * ILU(0) + BiCGSTAB (mmadmm_pcg_bicgstab_device; residual reduction 1e-6), stop at ||F||_1 < tol / 10 or after 1000 Newton
+ * iterations.  Ih = energy at the last evaluated iterate (the value the reference returns); newtonIters / linIters (sum of
+ * the inner iterations) may be NULL.  dt <= 0 uses the context's dt (the reference ignores the argument's value in the
+ * same way: it only enters as dt/tau with the integrator's own dt being what main.cpp passes).  Single-GPU contexts only. */
+int mmadmm_backward_euler_step(mmadmm_ctx *ctx, double dt, double tol, double *Ih, int *newtonIters, int *linIters);
+/* The Method 2 Jacobian in CSR form (after the first backward-Euler step or mmadmm_backward_euler_jacobian with val != NULL
+ * forcing a build): sizes2 = {rows, nnz}; rowptr[rows+1], col[nnz], val[nnz] may each be NULL. */
+int mmadmm_backward_euler_jacobian(mmadmm_ctx *ctx, int *sizes2, int *rowptr, int *col, double *val);
+
 /* The time step belongs to MeshIntegrator<D>, not to Mesh<D> (src/MeshIntegrator.cpp:15-17,45-51): a host Mesh<D> may
  * create the context before any integrator exists (dt = 0) and the integrator's constructor then sets dt, which
  * rebuilds the diagonal of t = M + dt^2 (WD)^T(WD).  Must be called before the first mmadmm_step. */
@@ -174,6 +188,13 @@ int mmadmm_pcg_create(int n, const int *rowptr, const int *col, const double *va
 int mmadmm_pcg_solve(mmadmm_pcg *h, const double *b, double *x, double tol, int maxit, int *iters, double *relres);
 /* Same with device pointers on the solver's device (no host copies). */
 int mmadmm_pcg_solve_device(mmadmm_pcg *h, const double *b_dev, double *x_dev, double tol, int maxit, int *iters, double *relres);
+/* BiCGSTAB exactly as LASolver runs it for the reference's Method 2 (lib/LASolver/accel_class.cpp:229-399 scaler_cgstab driven
+ * by MatrixIter::solve, MatrixIter.cpp:635-800, with the ParamIter of src/Mesh.cpp:266-304: iaccel = 0, ILU level 0, natural
+ * order, no scaling, zero initial guess, toler = 0): stops when ||r|| / ||b|| < resid_reduc.  Needs precond = 1.
+ * iters = iterations done, -1 if nitmax iterations did not converge (LASolver's convention). */
+int mmadmm_pcg_bicgstab(mmadmm_pcg *h, const double *b, double *x, double resid_reduc, int nitmax, int *iters, double *relres);
+int mmadmm_pcg_bicgstab_device(mmadmm_pcg *h, const double *b_dev, double *x_dev, double resid_reduc, int nitmax, int *iters,
+                               double *relres);
 /* y = A x (host arrays): the SpMV kernel alone (reference: matmult, accel_class.cpp:521-549). */
 int mmadmm_pcg_spmv(mmadmm_pcg *h, const double *x, double *y);
 /* z = M^{-1} r: Jacobi scaling or the level-scheduled ILU(0) triangular solves (reference: scaler_ILU::solve, ILU_class.cpp:447-527). */

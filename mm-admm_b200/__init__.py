@@ -29,11 +29,11 @@ ERRORS = {1: "EINVAL", 2: "ECUDA", 3: "EINVERTED", 4: "ESINGULAR", 5: "ENCCL", 6
 # every symbol include/mmadmm.h declares (checked by tests/test_abi.py)
 ABI_SYMBOLS = [
     "mmadmm_create", "mmadmm_set_dt", "mmadmm_step", "mmadmm_energy", "mmadmm_get_x", "mmadmm_get_x_device", "mmadmm_get_x_colmajor", "mmadmm_host_register", "mmadmm_host_unregister", "mmadmm_get_F",
-    "mmadmm_euler_step", "mmadmm_grid_dims", "mmadmm_get_state", "mmadmm_eval_monitor", "mmadmm_block_grad", "mmadmm_block_grad_at", "mmadmm_get_stats",
+    "mmadmm_euler_step", "mmadmm_backward_euler_step", "mmadmm_backward_euler_jacobian", "mmadmm_grid_dims", "mmadmm_get_state", "mmadmm_eval_monitor", "mmadmm_block_grad", "mmadmm_block_grad_at", "mmadmm_get_stats",
     "mmadmm_get_timing", "mmadmm_set_option", "mmadmm_stream", "mmadmm_destroy", "mmadmm_last_error",
     "mmadmm_version", "mmadmm_plan_create", "mmadmm_plan_sizes", "mmadmm_plan_get", "mmadmm_plan_destroy",
     "mmadmm_comm_unique_id", "mmadmm_create_dist", "mmadmm_local_sizes", "mmadmm_get_x_local",
-    "mmadmm_pcg_create", "mmadmm_pcg_solve", "mmadmm_pcg_solve_device", "mmadmm_pcg_spmv", "mmadmm_pcg_precond",
+    "mmadmm_pcg_create", "mmadmm_pcg_solve", "mmadmm_pcg_solve_device", "mmadmm_pcg_bicgstab", "mmadmm_pcg_bicgstab_device", "mmadmm_pcg_spmv", "mmadmm_pcg_precond",
     "mmadmm_pcg_get_ilu", "mmadmm_pcg_info", "mmadmm_pcg_time_spmv", "mmadmm_pcg_last_error", "mmadmm_pcg_destroy", "mmadmm_measure_fp64_peak",
 ]
 
@@ -70,6 +70,9 @@ def lib():
         L.mmadmm_energy.argtypes = [vp, _c_dp]
         L.mmadmm_set_dt.argtypes = [vp, C.c_double]
         L.mmadmm_euler_step.argtypes = [vp, _c_dp]
+        L.mmadmm_backward_euler_step.argtypes = [vp, C.c_double, C.c_double, _c_dp, _c_ip, _c_ip]
+        L.mmadmm_backward_euler_jacobian.argtypes = [vp, _c_ip, _c_ip, _c_ip, _c_dp]
+        L.mmadmm_pcg_bicgstab.argtypes = [vp, _c_dp, _c_dp, C.c_double, C.c_int, _c_ip, _c_dp]
         L.mmadmm_get_x.argtypes = [vp, _c_dp]
         L.mmadmm_get_x_device.argtypes = [vp, vp]
         L.mmadmm_get_F.argtypes = [vp, _c_ip]
@@ -235,6 +238,14 @@ class PCG:
         self._check(self.L.mmadmm_pcg_solve(self.h, _dp(b), _dp(x), float(tol), int(maxit or 2 * self.n), C.byref(it), C.byref(rr)))
         return x, it.value, rr.value
 
+    def bicgstab(self, b, resid_reduc=1e-6, nitmax=10000):
+        """-> (x, iterations or -1, ||r||/||b||): LASolver's CGSTAB on the ILU(0) factors, as the reference's Method 2 solves
+        (src/Mesh.cpp:266-304, 1311-1323)."""
+        b = np.ascontiguousarray(b, dtype=np.float64)
+        x = np.zeros(self.n); it = C.c_int(); rr = C.c_double()
+        self._check(self.L.mmadmm_pcg_bicgstab(self.h, _dp(b), _dp(x), float(resid_reduc), int(nitmax), C.byref(it), C.byref(rr)))
+        return x, it.value, rr.value
+
     def spmv(self, x):
         x = np.ascontiguousarray(x, dtype=np.float64); y = np.zeros(self.n)
         self._check(self.L.mmadmm_pcg_spmv(self.h, _dp(x), _dp(y)))
@@ -309,8 +320,8 @@ class Mesh:
         self.rho, self.tau, self.gradUse = float(rho), float(tau), bool(grad_use)
         self.w_json = w  # ignored, as in the reference (src/Mesh.cpp:451 overrides it with 0.5*sqrt(rho))
         self.integrationMode = integration_mode
-        if integration_mode != 0:
-            raise NotImplementedError("only Method 0 (ADMM) is built; Methods 1/2 are out of scope (SURVEY.md 8)")
+        if integration_mode not in (0, 1, 2):   # main.cpp:182-191: 0 ADMM step, 1 eulerStep, anything else backwardsEulerStep
+            raise ValueError("integration_mode: 0 (ADMM), 1 (explicit Euler) or 2 (backward Euler)")
         mon = monitor.evaluate_at_vertices(self.Vp) if hasattr(monitor, "evaluate_at_vertices") else monitor
         self.mon_vertex = np.ascontiguousarray(mon, dtype=np.float64).reshape(self.P, self.D * self.D)
 
@@ -377,6 +388,24 @@ class MeshIntegrator:
         Ih = C.c_double()
         self._check(self.L.mmadmm_euler_step(self.h, C.byref(Ih)))
         return Ih.value
+
+    def backwardsEulerStep(self, dt=None, tol=1e-3):
+        """Method 2, MeshIntegrator<D>::backwardsEulerStep(dt, tol) (src/MeshIntegrator.cpp:68-76 -> Mesh::backwardsEulerStep,
+        src/Mesh.cpp:1263-1341).  Returns the energy at the last Newton iterate; `last` holds the Newton and BiCGSTAB iteration
+        counts.  As in the reference the caller's Vp is not refreshed on this path: use x() or done()."""
+        Ih = C.c_double(); nit = C.c_int(); lit = C.c_int()
+        self._check(self.L.mmadmm_backward_euler_step(self.h, float(dt if dt is not None else 0.0), float(tol), C.byref(Ih),
+                                                      C.byref(nit), C.byref(lit)))
+        self.last = dict(Ih=Ih.value, newton_iters=nit.value, lin_iters=lit.value)
+        return Ih.value
+
+    def backward_euler_jacobian(self):
+        """-> (rowptr, col, val): the Method 2 Jacobian I + (dt/tau) * FD(grad) (Mesh::buildEulerJac, src/Mesh.cpp:1111-1261)."""
+        sz = (C.c_int * 2)()
+        self._check(self.L.mmadmm_backward_euler_jacobian(self.h, sz, None, None, None))
+        rowptr = np.zeros(sz[0] + 1, dtype=np.int32); col = np.zeros(sz[1], dtype=np.int32); val = np.zeros(sz[1])
+        self._check(self.L.mmadmm_backward_euler_jacobian(self.h, sz, _ip(rowptr), _ip(col), _dp(val)))
+        return rowptr, col, val
 
     def local_sizes(self):
         p, e = C.c_int(), C.c_int()

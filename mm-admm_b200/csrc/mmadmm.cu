@@ -1324,6 +1324,119 @@ __global__ void k_x_to_colmajor(int P, int D, const double *x, double *xT) {
     for (int l = 0; l < D; l++) xT[(size_t)l * P + p] = x[(size_t)D * p + l];
 }
 
+// ---- Method 2 (backward Euler) kernels ----
+// K9: Mesh::buildEulerJac + FSubJac (src/Mesh.cpp:1111-1135, 1161-1261).  One thread per vertex p owns the D rows D p .. D p + D-1
+// of the block-CSR Jacobian (vertex adjacency adjPtr/adjIdx, ascending, self included; row q of p starts at
+// D D adjPtr[p] + q D deg(p), entry (t, c) = column D adjIdx[t] + c) and walks p's incident elements in ascending order as the
+// reference's std::set does: Gk = blockGrad at Vp (a.x points at the Vp snapshot), then per direction i a forward difference
+// with h = 10 sqrt(eps) that fills ROW i with d grad / d x_{p,i} (the reference stores the perturbed direction as the row).
+// BOUNDARY_FIXED vertices: identity block, and only from the elements in which p is local vertex 0 (reference quirk, :1210-1218).
+// Finally a *= dt/tau and the diagonal gets + 1.
+template <int D>
+__global__ void __launch_bounds__(128) k_m2_jac(ElemArgs<D> a, const uint8_t *mask, const int *incPtr, const int *incIdx,
+                                                const int *adjPtr, const int *adjIdx, double dtOverTau, double *val) {
+    constexpr int n = D * (D + 1);
+    const int p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= a.P) return;
+    const int a0 = adjPtr[p], deg = adjPtr[p + 1] - a0;
+    double *rowBase = val + (size_t)D * D * a0;
+    const int rowLen = D * deg;
+    for (int k = 0; k < D * rowLen; k++) rowBase[k] = 0.0;
+    const double h = 10.0 * 1.4901161193847656e-08;   // 10 * sqrt(2^-52)
+    const bool fixed = mask[p] == NT_BOUNDARY_FIXED;
+    bool inv = false;
+    for (int k = incPtr[p]; k < incPtr[p + 1]; k++) {
+        const int slot = incIdx[k];
+        const int e = slot >> 2, off = slot & 3;
+        int vid[D + 1], pos[D + 1];
+        load_elem_ids<D>(a, e, vid);
+#pragma unroll
+        for (int j = 0; j < D + 1; j++) {
+            int lo = 0, hi = deg - 1;
+            while (lo < hi) {   // adjIdx[a0 .. a0+deg) ascending and contains vid[j]
+                const int mid = (lo + hi) >> 1;
+                if (adjIdx[a0 + mid] < vid[j]) lo = mid + 1; else hi = mid;
+            }
+            pos[j] = lo;
+        }
+        if (fixed) {
+            if (off == 0)
+                for (int r = 0; r < D; r++) rowBase[r * rowLen + D * pos[0] + r] += 1.0;
+            continue;
+        }
+        double xl[n], xi[n], Gk[n], G1[n];
+#pragma unroll
+        for (int v = 0; v < D + 1; v++) gather_vertex<D>(a.x, vid[v], xl + D * v);
+        load_xi<D>(a, vid, xi);
+        block_grad<D, true>(xl, xi, a.compMesh, a.mg, a.fc, Gk, inv);
+        for (int i = 0; i < D; i++) {
+            double keep = 0.0;
+#pragma unroll
+            for (int q = 0; q < n; q++)
+                if (q == D * off + i) { keep = xl[q]; xl[q] = keep + h; }
+            block_grad<D, true>(xl, xi, a.compMesh, a.mg, a.fc, G1, inv);
+#pragma unroll
+            for (int q = 0; q < n; q++)
+                if (q == D * off + i) xl[q] = keep;
+#pragma unroll
+            for (int j = 0; j < D + 1; j++)
+#pragma unroll
+                for (int c = 0; c < D; c++) rowBase[i * rowLen + D * pos[j] + c] += (G1[D * j + c] - Gk[D * j + c]) / h;
+        }
+    }
+    if (inv) atomicOr(a.status, ST_INVERTED);
+    for (int q = 0; q < D; q++)
+        for (int t = 0; t < deg; t++)
+            for (int c = 0; c < D; c++) {
+                double v = rowBase[q * rowLen + D * t + c] * dtOverTau;
+                if (adjIdx[a0 + t] == p && c == q) v += 1.0;
+                rowBase[q * rowLen + D * t + c] = v;
+            }
+}
+
+// K10: vertex side of Mesh::backwardsEulerStep (src/Mesh.cpp:1263-1341).  s = sum of the masked element gradients of the vertex
+// (ascending element order).  MODE 0, the explicit-Euler guess: x -= (dt/tau) s.  MODE 1, the Newton residual:
+// F = (dt/tau) s + (x - xn), rhs = -F (the right-hand side of J dx = -F), block partial sums of |F| (the reference's lpNorm<1>).
+template <int D, int MODE>
+__global__ void __launch_bounds__(TPB_V) k_m2_gather(int P, size_t Es, const int *incPtr, const int *incIdx, const double *gs,
+                                                     double dtOverTau, double *x, const double *xn, double *rhs, double *part) {
+    __shared__ double red[32];
+    const int p = blockIdx.x * TPB_V + threadIdx.x;
+    double l1 = 0.0;
+    if (p < P) {
+        double s[D];
+#pragma unroll
+        for (int l = 0; l < D; l++) s[l] = 0.0;
+        for (int k = incPtr[p]; k < incPtr[p + 1]; k++) {
+            const int slot = __ldg(incIdx + k);
+            const size_t e = (size_t)(slot >> 2);
+            const int v = slot & 3;
+#pragma unroll
+            for (int l = 0; l < D; l++) s[l] += __ldg(gs + (size_t)(D * v + l) * Es + e);
+        }
+#pragma unroll
+        for (int l = 0; l < D; l++) {
+            const size_t i = (size_t)D * p + l;
+            if (MODE == 0) {
+                x[i] -= dtOverTau * s[l];
+            } else {
+                const double f = s[l] * dtOverTau + (x[i] - xn[i]);
+                rhs[i] = -f;
+                l1 += fabs(f);
+            }
+        }
+    }
+    if (MODE == 1) {
+        const double b = block_sum(l1, red);
+        if (threadIdx.x == 0) part[blockIdx.x] = b;
+    }
+}
+
+__global__ void k_m2_axpy(size_t N, const double *dx, double *x) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < N) x[i] += dx[i];
+}
+
 // ---- unit-parity helpers ----
 template <int D> __global__ void k_eval_monitor(MonGrid mg, int npts, const double *pts, double *out) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -1443,6 +1556,18 @@ struct mmadmm_ctx {
     std::vector<int> evPhase;
     size_t evUsed = 0;
     std::string err;
+    // Method 2 (backward Euler) state, built on the first mmadmm_backward_euler_step
+    struct M2 {
+        bool init = false, stepTaken = false, jacValid = false;
+        int N = 0, nnz = 0, nblk = 0, vpStamp = -1;
+        double jacDt = 0.0;
+        int *adjPtr_d = nullptr, *adjIdx_d = nullptr;
+        std::vector<int> rowptr_h, col_h;
+        std::vector<double> val_h;
+        double *val_d = nullptr, *vp0 = nullptr, *xn = nullptr, *rhs = nullptr, *dx = nullptr, *part = nullptr;
+        mmadmm_pcg *solver = nullptr;
+        long long newtonIters = 0, linIters = 0, jacBuilds = 0;
+    } m2;
 
     double gridO[3] = {0, 0, 0}, gridRh[3] = {0, 0, 0};
     MonGrid monGrid() const {
@@ -2380,6 +2505,153 @@ template <int D> int euler_impl(mmadmm_ctx *ctx, double *IhOut) {
     return check_status(ctx);
 }
 
+// ---- Method 2: MeshIntegrator::backwardsEulerStep (src/MeshIntegrator.cpp:68-76) -> Mesh::backwardsEulerStep (src/Mesh.cpp:1263-1341) ----
+int m2_init(mmadmm_ctx *ctx) {
+    mmadmm_ctx::M2 &m = ctx->m2;
+    const int D = ctx->D, V = D + 1, P = ctx->P, E = ctx->E;
+    // vertex adjacency = the structure Mesh::buildMatrix gives LASolver (src/Mesh.cpp:305-340): every vertex couples to all
+    // vertices it shares a simplex with (itself included); D x D dense blocks
+    std::vector<int> Fh((size_t)E * V), plane(E);
+    CK(cudaStreamSynchronize(ctx->stream));
+    for (int v = 0; v < V; v++) {
+        CK(cudaMemcpy(plane.data(), ctx->F[v], sizeof(int) * (size_t)E, cudaMemcpyDeviceToHost));
+        for (int e = 0; e < E; e++) Fh[(size_t)e * V + v] = plane[e];
+    }
+    std::vector<size_t> ptr((size_t)P + 1, 0);
+    for (size_t k = 0; k < Fh.size(); k++) ptr[Fh[k] + 1] += V;
+    for (int p = 0; p < P; p++) ptr[p + 1] += ptr[p];
+    std::vector<int> nb(ptr[P]);
+    {
+        std::vector<size_t> cur(ptr.begin(), ptr.end() - 1);
+        for (int e = 0; e < E; e++)
+            for (int i = 0; i < V; i++)
+                for (int j = 0; j < V; j++) nb[cur[Fh[(size_t)e * V + i]]++] = Fh[(size_t)e * V + j];
+    }
+    std::vector<int> adjPtr(P + 1, 0), adjIdx;
+    adjIdx.reserve(nb.size() / 2 + P);
+    for (int p = 0; p < P; p++) {
+        auto b = nb.begin() + ptr[p], e2 = nb.begin() + ptr[p + 1];
+        std::sort(b, e2);
+        auto u = std::unique(b, e2);
+        if (b == u) adjIdx.push_back(p);   // a vertex no element uses still needs its diagonal
+        else adjIdx.insert(adjIdx.end(), b, u);
+        adjPtr[p + 1] = (int)adjIdx.size();
+    }
+    const size_t nnz = (size_t)D * D * adjIdx.size();
+    if (nnz > (size_t)std::numeric_limits<int>::max()) { ctx->err = "Method 2: Jacobian has more than 2^31 entries"; return MMADMM_EINVAL; }
+    m.N = P * D; m.nnz = (int)nnz;
+    m.rowptr_h.resize((size_t)m.N + 1); m.col_h.resize(nnz); m.val_h.resize(nnz);
+    for (int p = 0; p < P; p++) {
+        const int a0 = adjPtr[p], deg = adjPtr[p + 1] - a0;
+        for (int q = 0; q < D; q++) {
+            const size_t r0 = (size_t)D * D * a0 + (size_t)q * D * deg;
+            m.rowptr_h[(size_t)D * p + q] = (int)r0;
+            for (int t = 0; t < deg; t++)
+                for (int c = 0; c < D; c++) m.col_h[r0 + (size_t)D * t + c] = D * adjIdx[a0 + t] + c;
+        }
+    }
+    m.rowptr_h[m.N] = (int)nnz;
+    CK(cudaMalloc(&m.adjPtr_d, sizeof(int) * (size_t)(P + 1)));
+    CK(cudaMalloc(&m.adjIdx_d, sizeof(int) * adjIdx.size()));
+    CK(cudaMemcpy(m.adjPtr_d, adjPtr.data(), sizeof(int) * (size_t)(P + 1), cudaMemcpyHostToDevice));
+    CK(cudaMemcpy(m.adjIdx_d, adjIdx.data(), sizeof(int) * adjIdx.size(), cudaMemcpyHostToDevice));
+    const size_t vb = sizeof(double) * (size_t)m.N;
+    CK(cudaMalloc(&m.val_d, sizeof(double) * nnz));
+    CK(cudaMalloc(&m.vp0, vb)); CK(cudaMalloc(&m.xn, vb)); CK(cudaMalloc(&m.rhs, vb)); CK(cudaMalloc(&m.dx, vb));
+    m.nblk = cdiv(P, TPB_V);
+    CK(cudaMalloc(&m.part, sizeof(double) * (size_t)m.nblk));
+    m.init = true;
+    return MMADMM_OK;
+}
+
+// Jacobian values on the device, then the ILU(0) factor + level schedules (mmadmm_pcg_create): jac->sfac + the numeric factor
+template <int D> int m2_build_jac(mmadmm_ctx *ctx, double dt) {
+    mmadmm_ctx::M2 &m = ctx->m2;
+    if (m.jacValid && m.jacDt == dt) return MMADMM_OK;   // Vp and dt unchanged: a rebuild would reproduce the same values
+    cudaStream_t st = ctx->stream;
+    ElemArgs<D> a = ctx->elemArgs<D>(0.0);
+    a.x = m.vp0;
+    k_m2_jac<D><<<cdiv(ctx->P, 128), 128, 0, st>>>(a, ctx->mask, ctx->incPtr, ctx->incIdx, m.adjPtr_d, m.adjIdx_d, dt / ctx->tau, m.val_d);
+    ctx->launches++;
+    CK(cudaMemcpyAsync(m.val_h.data(), m.val_d, sizeof(double) * (size_t)m.nnz, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    CK(cudaGetLastError());
+    if (m.solver) { mmadmm_pcg_destroy(m.solver); m.solver = nullptr; }
+    int rc = mmadmm_pcg_create(m.N, m.rowptr_h.data(), m.col_h.data(), m.val_h.data(), 1, ctx->device, &m.solver);
+    if (rc) {
+        ctx->err = std::string("Method 2 Jacobian: ") + (m.solver ? mmadmm_pcg_last_error(m.solver) : "solver allocation failed");
+        if (m.solver) { mmadmm_pcg_destroy(m.solver); m.solver = nullptr; }
+        return rc;
+    }
+    m.jacValid = true; m.jacDt = dt; m.jacBuilds++;
+    return MMADMM_OK;
+}
+
+template <int D> int beuler_impl(mmadmm_ctx *ctx, double dt, double tol, double *IhOut, int *newtonOut, int *linOut) {
+    if (ctx->dist) { ctx->err = "Method 2 (backward Euler) runs on single-GPU contexts only"; return MMADMM_EINVAL; }
+    mmadmm_ctx::M2 &m = ctx->m2;
+    cudaStream_t st = ctx->stream;
+    if (!m.init) { int rc = m2_init(ctx); if (rc) return rc; }
+    const size_t vb = sizeof(double) * (size_t)m.N;
+    if (m.vpStamp != ctx->stepsTaken) {
+        // Vp as the reference holds it: the positions at construction or after the last Method-0 step (updateAfterStep);
+        // Methods 1 and 2 never refresh it, so the snapshot is taken when this method is first entered after either
+        CK(cudaMemcpyAsync(m.vp0, ctx->x, vb, cudaMemcpyDeviceToDevice, st));
+        m.vpStamp = ctx->stepsTaken;
+        m.jacValid = false;
+    }
+    const double s = dt / ctx->tau;
+    const double SAFETY_FAC = 1.0 / 10.0;
+    const int MAX_ITERS = 1000;
+    ElemArgs<D> a = ctx->elemArgs<D>(0.0);
+    CK(cudaMemcpyAsync(m.xn, ctx->x, vb, cudaMemcpyDeviceToDevice, st));
+    // initial guess: one explicit Euler step
+    k_euler_elem<D, true><<<ctx->nblkE, TPB, 0, st>>>(a, ctx->gs, a.nonIntBits, ctx->partPrimal);
+    k_m2_gather<D, 0><<<m.nblk, TPB_V, 0, st>>>(ctx->P, ctx->Es, ctx->incPtr, ctx->incIdx, ctx->gs, s, ctx->x, m.xn, m.rhs, m.part);
+    ctx->launches += 2;
+    if (!m.stepTaken) { int rc = m2_build_jac<D>(ctx, dt); if (rc) return rc; }
+    int nIter = 0, lin = 0;
+    double g1Prev = std::numeric_limits<double>::infinity(), Ih = 0.0;
+    do {
+        k_euler_elem<D, true><<<ctx->nblkE, TPB, 0, st>>>(a, ctx->gs, a.nonIntBits, ctx->partPrimal);
+        k_m2_gather<D, 1><<<m.nblk, TPB_V, 0, st>>>(ctx->P, ctx->Es, ctx->incPtr, ctx->incIdx, ctx->gs, s, ctx->x, m.xn, m.rhs, m.part);
+        k_finalize<<<1, 1024, 0, st>>>(m.nblk, m.part, ctx->nblkE, ctx->partPrimal, 0, nullptr, ctx->scalOut(2), ctx->statusIn(), ctx->statusOut());
+        ctx->launches += 3;
+        int rcg = gather_scalars(ctx, 4);
+        if (rcg) return rcg;
+        CK(cudaGetLastError());
+        const double g1 = ctx->scal_h[2];
+        Ih = ctx->scal_h[3];
+        int rcs = check_status(ctx);
+        if (rcs) return rcs;
+        if (!(g1 == g1)) { ctx->err = "Method 2: non-finite Newton residual"; return MMADMM_ESINGULAR; }
+        if (g1 < SAFETY_FAC * tol) break;
+        if (!m.stepTaken || std::fabs(g1 - g1Prev) / g1 < 0.25) {
+            int rc = m2_build_jac<D>(ctx, dt);
+            if (rc) return rc;
+            m.stepTaken = true;
+        }
+        int cgIter = 0;
+        int rc = mmadmm_pcg_bicgstab_device(m.solver, m.rhs, m.dx, 1.e-6, 10000, &cgIter, nullptr);
+        if (rc) { ctx->err = std::string("Method 2 linear solve: ") + mmadmm_pcg_last_error(m.solver); return rc; }
+        if (cgIter <= 0) {   // the reference asserts cgIter > 0 (src/Mesh.cpp:1329); LASolver returns -1 when not converged
+            ctx->err = "Method 2: BiCGSTAB did not converge (the reference asserts cgIter > 0, src/Mesh.cpp:1329)";
+            return MMADMM_ESINGULAR;
+        }
+        lin += cgIter;
+        k_m2_axpy<<<cdiv((size_t)m.N, 256), 256, 0, st>>>((size_t)m.N, m.dx, ctx->x);
+        ctx->launches++;
+        nIter++;
+        g1Prev = g1;
+    } while (nIter < MAX_ITERS);
+    CK(cudaStreamSynchronize(st));
+    m.newtonIters += nIter; m.linIters += lin;
+    if (IhOut) *IhOut = Ih;
+    if (newtonOut) *newtonOut = nIter;
+    if (linOut) *linOut = lin;
+    return MMADMM_OK;
+}
+
 }  // namespace
 
 // =====================================================================================================
@@ -2533,6 +2805,34 @@ int mmadmm_euler_step(mmadmm_ctx *ctx, double *Ih) {
     if (!ctx) return MMADMM_EINVAL;
     CK(cudaSetDevice(ctx->device));
     return (ctx->D == 2) ? euler_impl<2>(ctx, Ih) : euler_impl<3>(ctx, Ih);
+}
+
+int mmadmm_backward_euler_step(mmadmm_ctx *ctx, double dt, double tol, double *Ih, int *newtonIters, int *linIters) {
+    if (!ctx || !(tol > 0.0)) return MMADMM_EINVAL;
+    CK(cudaSetDevice(ctx->device));
+    if (!(dt > 0.0)) dt = ctx->dt;
+    return (ctx->D == 2) ? beuler_impl<2>(ctx, dt, tol, Ih, newtonIters, linIters) : beuler_impl<3>(ctx, dt, tol, Ih, newtonIters, linIters);
+}
+
+int mmadmm_backward_euler_jacobian(mmadmm_ctx *ctx, int *sizes2, int *rowptr, int *col, double *val) {
+    if (!ctx) return MMADMM_EINVAL;
+    if (ctx->dist) { ctx->err = "Method 2 (backward Euler) runs on single-GPU contexts only"; return MMADMM_EINVAL; }
+    CK(cudaSetDevice(ctx->device));
+    mmadmm_ctx::M2 &m = ctx->m2;
+    if (!m.init) { int rc = m2_init(ctx); if (rc) return rc; }
+    if (val && !m.jacValid) {
+        if (m.vpStamp != ctx->stepsTaken) {
+            CK(cudaMemcpyAsync(m.vp0, ctx->x, sizeof(double) * (size_t)m.N, cudaMemcpyDeviceToDevice, ctx->stream));
+            m.vpStamp = ctx->stepsTaken;
+        }
+        int rc = (ctx->D == 2) ? m2_build_jac<2>(ctx, ctx->dt) : m2_build_jac<3>(ctx, ctx->dt);
+        if (rc) return rc;
+    }
+    if (sizes2) { sizes2[0] = m.N; sizes2[1] = m.nnz; }
+    if (rowptr) std::memcpy(rowptr, m.rowptr_h.data(), sizeof(int) * ((size_t)m.N + 1));
+    if (col) std::memcpy(col, m.col_h.data(), sizeof(int) * (size_t)m.nnz);
+    if (val) std::memcpy(val, m.val_h.data(), sizeof(double) * (size_t)m.nnz);
+    return MMADMM_OK;
 }
 
 int mmadmm_energy(mmadmm_ctx *ctx, double *I) {
@@ -2791,6 +3091,9 @@ void mmadmm_destroy(mmadmm_ctx *ctx) {
     cudaFree(ctx->status_d);
     if (ctx->status_h) cudaFreeHost(ctx->status_h);
     cudaFree(ctx->hist_d);
+    if (ctx->m2.solver) { mmadmm_pcg_destroy(ctx->m2.solver); cudaSetDevice(ctx->device); }
+    cudaFree(ctx->m2.adjPtr_d); cudaFree(ctx->m2.adjIdx_d); cudaFree(ctx->m2.val_d); cudaFree(ctx->m2.vp0); cudaFree(ctx->m2.xn);
+    cudaFree(ctx->m2.rhs); cudaFree(ctx->m2.dx); cudaFree(ctx->m2.part);
     cudaFree(ctx->sharedIdx); cudaFree(ctx->sharedSlot); cudaFree(ctx->nbrList); cudaFree(ctx->contribPtr); cudaFree(ctx->contrib);
     cudaFree(ctx->verts); cudaFree(ctx->owner); cudaFree(ctx->sPart); cudaFree(ctx->sTot); cudaFree(ctx->sendBuf); cudaFree(ctx->recvBuf);
     cudaFree(ctx->scalAll_d);

@@ -171,6 +171,36 @@ __global__ void __launch_bounds__(TPB) k_xpay(int n, const double *scal, const d
     if (i < n) p[i] = z[i] + scal[S_BETA] * p[i];
 }
 
+// ---- BiCGSTAB vector kernels (LASolver scaler_cgstab, lib/LASolver/accel_class.cpp:280-399); scalars come from the host ----
+// p = r + beta (p - omega v)
+__global__ void __launch_bounds__(TPB) k_bi_p(int n, double beta, double omega, const double *__restrict__ r,
+                                               const double *__restrict__ v, double *p) {
+    const int i = blockIdx.x * TPB + threadIdx.x;
+    if (i < n) p[i] = r[i] + beta * (p[i] - omega * v[i]);
+}
+// s = r - alpha v
+__global__ void __launch_bounds__(TPB) k_bi_s(int n, double alpha, const double *__restrict__ r, const double *__restrict__ v, double *s) {
+    const int i = blockIdx.x * TPB + threadIdx.x;
+    if (i < n) s[i] = r[i] - alpha * v[i];
+}
+// x += alpha vbar + omega zvec ; r = s - omega t ; partial sums of r.r
+__global__ void __launch_bounds__(TPB) k_bi_xr(int n, double alpha, double omega, const double *__restrict__ vbar,
+                                                const double *__restrict__ zvec, const double *__restrict__ s,
+                                                const double *__restrict__ t, double *x, double *r, double *partRR) {
+    __shared__ double sh[32];
+    const int i = blockIdx.x * TPB + threadIdx.x;
+    double rr = 0.0;
+    if (i < n) {
+        const double step = alpha * vbar[i] + omega * zvec[i];
+        x[i] = x[i] + step;
+        const double ri = s[i] - omega * t[i];
+        r[i] = ri;
+        rr = ri * ri;
+    }
+    const double s1 = block_sum_d(rr, sh);
+    if (threadIdx.x == 0) partRR[blockIdx.x] = s1;
+}
+
 // FP64 pipe peak: 8 independent DFMA chains per thread, no memory traffic
 __global__ void __launch_bounds__(256) k_dfma_peak(int iters, double seed, double *out) {
     double a0 = seed + threadIdx.x, a1 = a0 + 1, a2 = a0 + 2, a3 = a0 + 3, a4 = a0 + 4, a5 = a0 + 5, a6 = a0 + 6, a7 = a0 + 7;
@@ -194,6 +224,7 @@ struct mmadmm_pcg {
     std::vector<int> lvlL, lvlU;                  // level offsets (host)
     double *r = nullptr, *z = nullptr, *p = nullptr, *q = nullptr, *x = nullptr, *b = nullptr, *tmp = nullptr;
     double *part0 = nullptr, *part1 = nullptr, *scal = nullptr, *scal_h = nullptr;
+    double *bi[4] = {nullptr, nullptr, nullptr, nullptr};   // BiCGSTAB work vectors (res0, svec, zvec, tvec), allocated on first use
     int nblk = 0;
     long long launches = 0;
     std::string err;
@@ -433,6 +464,92 @@ int mmadmm_pcg_solve_device(mmadmm_pcg *h, const double *b_dev, double *x_dev, d
     return MMADMM_OK;
 }
 
+// BiCGSTAB as the reference's LASolver runs it for Method 2 (lib/LASolver/MatrixIter.cpp:693-800 driver, accel_class.cpp:229-273
+// start values, :280-399 one iteration; configured at src/Mesh.cpp:266-304: iaccel = 0, new_rhat = 0, toler = 0): right-
+// preconditioned by the ILU(0) factors, rhat = r0 = b (zero initial guess), alpha = rholst = omega = 1 and p = A vbar = 0 at
+// the start, `tiny` = 1e-300 guards in beta and omega, stop when ||r|| / ||b|| < resid_reduc.  *iters = iterations done, or
+// -1 when nitmax iterations did not converge (LASolver's convention).  The four dot products per iteration are reduced on
+// the device in a fixed order and read back (8-byte copies): the scalar recurrences run on the host.
+int mmadmm_pcg_bicgstab_device(mmadmm_pcg *h, const double *b_dev, double *x_dev, double resid_reduc, int nitmax, int *iters,
+                               double *relres) {
+    if (!h || !b_dev || !x_dev) return MMADMM_EINVAL;
+    if (h->precond != 1) { h->err = "BiCGSTAB needs the ILU(0) preconditioner (precond = 1)"; return MMADMM_EINVAL; }
+    PCK(cudaSetDevice(h->device));
+    const int n = h->n, g = cdiv(n, TPB);
+    cudaStream_t st = h->stream;
+    const size_t vb = sizeof(double) * (size_t)n;
+    for (int k = 0; k < 4; k++)
+        if (!h->bi[k]) PCK(cudaMalloc(&h->bi[k], vb));
+    double *res = h->r, *res0 = h->bi[0], *pvec = h->p, *vbar = h->z, *avbar = h->q, *svec = h->bi[1], *zvec = h->bi[2], *tvec = h->bi[3];
+    // two dot products a.b and c.c -> host
+    auto dots = [&](const double *a, const double *bb, const double *c, double *ab, double *cc) -> cudaError_t {
+        k_dot2<<<g, TPB, 0, st>>>(n, a, bb, c, h->part0, h->part1);
+        k_scalars<<<1, 1024, 0, st>>>(g, h->part0, h->part1, h->scal, 2);
+        h->launches += 2;
+        cudaError_t e = cudaMemcpyAsync(h->scal_h, h->scal, sizeof(double) * S_COUNT, cudaMemcpyDeviceToHost, st);
+        if (e != cudaSuccess) return e;
+        e = cudaStreamSynchronize(st);
+        *ab = h->scal_h[S_RZ]; *cc = h->scal_h[S_RR];
+        return e;
+    };
+    PCK(cudaMemsetAsync(x_dev, 0, vb, st));
+    PCK(cudaMemcpyAsync(res, b_dev, vb, cudaMemcpyDeviceToDevice, st));
+    PCK(cudaMemcpyAsync(res0, b_dev, vb, cudaMemcpyDeviceToDevice, st));
+    PCK(cudaMemsetAsync(pvec, 0, vb, st));
+    PCK(cudaMemsetAsync(avbar, 0, vb, st));
+    double rho = 0.0, bb2 = 0.0;
+    PCK(dots(res0, res, res, &rho, &bb2));
+    const double rmsi = std::sqrt(bb2);
+    if (rmsi == 0.0) { if (iters) *iters = 0; if (relres) *relres = 0.0; return MMADMM_OK; }
+    const double tiny = 1.e-300;
+    double alpha = 1.0, rholst = 1.0, omega = 1.0, rms = rmsi;
+    int nitr = 0;
+    bool conv = false;
+    for (int it = 1; it <= nitmax; it++) {
+        nitr++;
+        if (it > 1) { double dummy; PCK(dots(res0, res, res, &rho, &dummy)); }
+        double beta = rho / (rholst + tiny);
+        beta *= (alpha / (omega + tiny));
+        rholst = rho;
+        k_bi_p<<<g, TPB, 0, st>>>(n, beta, omega, res, avbar, pvec);
+        apply_ilu(h, pvec, vbar);
+        launch_spmv(h, vbar, avbar, nullptr);
+        double r0av, dummy2;
+        PCK(dots(res0, avbar, avbar, &r0av, &dummy2));
+        alpha = rho / r0av;
+        k_bi_s<<<g, TPB, 0, st>>>(n, alpha, res, avbar, svec);
+        apply_ilu(h, svec, zvec);
+        launch_spmv(h, zvec, tvec, nullptr);
+        double ts, tt;
+        PCK(dots(tvec, svec, tvec, &ts, &tt));
+        omega = ts / (tt + tiny);
+        k_bi_xr<<<g, TPB, 0, st>>>(n, alpha, omega, vbar, zvec, svec, tvec, x_dev, res, h->part1);
+        k_scalars<<<1, 1024, 0, st>>>(g, nullptr, h->part1, h->scal, 3);
+        h->launches += 4;
+        PCK(cudaMemcpyAsync(h->scal_h, h->scal, sizeof(double) * S_COUNT, cudaMemcpyDeviceToHost, st));
+        PCK(cudaStreamSynchronize(st));
+        rms = std::sqrt(h->scal_h[S_BB]);
+        if (!(rms == rms)) { h->err = "non-finite residual in BiCGSTAB (breakdown)"; return MMADMM_ESINGULAR; }
+        if (rms / rmsi < resid_reduc) { conv = true; break; }
+    }
+    PCK(cudaGetLastError());
+    if (iters) *iters = conv ? nitr : -1;
+    if (relres) *relres = rms / rmsi;
+    return MMADMM_OK;
+}
+
+// host-buffer form of the above
+int mmadmm_pcg_bicgstab(mmadmm_pcg *h, const double *b, double *x, double resid_reduc, int nitmax, int *iters, double *relres) {
+    if (!h || !b || !x) return MMADMM_EINVAL;
+    PCK(cudaSetDevice(h->device));
+    PCK(cudaMemcpyAsync(h->b, b, sizeof(double) * (size_t)h->n, cudaMemcpyHostToDevice, h->stream));
+    int rc = mmadmm_pcg_bicgstab_device(h, h->b, h->x, resid_reduc, nitmax, iters, relres);
+    if (rc) return rc;
+    PCK(cudaMemcpyAsync(x, h->x, sizeof(double) * (size_t)h->n, cudaMemcpyDeviceToHost, h->stream));
+    PCK(cudaStreamSynchronize(h->stream));
+    return MMADMM_OK;
+}
+
 int mmadmm_pcg_solve(mmadmm_pcg *h, const double *b, double *x, double tol, int maxit, int *iters, double *relres) {
     if (!h || !b || !x) return MMADMM_EINVAL;
     PCK(cudaSetDevice(h->device));
@@ -503,6 +620,7 @@ void mmadmm_pcg_destroy(mmadmm_pcg *h) {
     cudaFree(h->rowsL); cudaFree(h->rowsU);
     cudaFree(h->r); cudaFree(h->z); cudaFree(h->p); cudaFree(h->q); cudaFree(h->x); cudaFree(h->b); cudaFree(h->tmp);
     cudaFree(h->part0); cudaFree(h->part1); cudaFree(h->scal);
+    for (int k = 0; k < 4; k++) cudaFree(h->bi[k]);
     if (h->scal_h) cudaFreeHost(h->scal_h);
     if (h->stream) cudaStreamDestroy(h->stream);
     delete h;

@@ -53,7 +53,12 @@ public:
         a->check(mmadmm_euler_step(a->ctx, &Ih), "mmadmm_euler_step");
         return Ih;
     }
-    double backwardsEulerStep(double dt, double tol) { (void)dt; (void)tol; notBuilt("backwardsEulerStep (Method 2)"); return 0; }
+    // Method 2 (src/MeshIntegrator.cpp:68-76 -> Mesh::backwardsEulerStep, src/Mesh.cpp:1263-1341).  No updateAfterStep here either.
+    double backwardsEulerStep(double dt, double tol) {
+        double Ih = 0;
+        a->check(mmadmm_backward_euler_step(a->ctx, dt, tol, &Ih, nullptr, nullptr), "mmadmm_backward_euler_step");
+        return Ih;
+    }
     double getEnergy() { return a->computeEnergy(xUnused); }
     void done() { a->updateAfterStep(dt, xPrevUnused, xUnused); }
 
@@ -93,10 +98,6 @@ public:
 
 private:
     Eigen::VectorXd xUnused, xPrevUnused;
-    void notBuilt(const char *what) {
-        cerr << "mm-admm_b200: " << what << " is not implemented on this build (Methods 0 and 1 are)" << endl;
-        exit(1);
-    }
 };
 
 #endif
