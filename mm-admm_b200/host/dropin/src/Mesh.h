@@ -9,8 +9,8 @@
 //
 // What the reference's Mesh does on the host and this one does not: the D/W/M sparse matrices, face lists and
 // simplex maps are never formed (the ADMM system matrix is diagonal, incidence replaces D).
-// Method 2 (backward Euler, the LASolver path) is out of scope: integrationMode == 2 aborts with a
-// message.  Method 1 (explicit Euler) runs on the device through mmadmm_euler_step.
+// Method 1 (explicit Euler) runs on the device through mmadmm_euler_step, Method 2 (backward Euler, the reference's
+// LASolver path) through mmadmm_backward_euler_step (FD Jacobian kernel + ILU(0)/BiCGSTAB kernels).
 #ifndef MESH_H
 #define MESH_H
 
@@ -73,10 +73,8 @@ public:
         this->rho = rho;
         this->w = 0.5 * sqrt(rho);
         this->nPnts = Xp.rows();
-        if (integrationMode != 0 && integrationMode != 1) {
-            cerr << "mm-admm_b200: Methods 0 (ADMM, MeshIntegrator::step) and 1 (eulerStep) are built; Method 2 is not implemented on this build" << endl;
-            exit(1);
-        }
+        // integrationMode: 0 ADMM (step), 1 explicit Euler (eulerStep), anything else backward Euler (main.cpp:182-191);
+        // the device context serves all three, the Method 2 state is built on the first backwardsEulerStep
         const int P = Xp.rows(), E = F.rows();
         if ((int)boundaryMask.size() < P) {
             cerr << "mm-admm_b200: boundary mask has " << boundaryMask.size() << " entries for " << P << " points" << endl;

@@ -66,6 +66,7 @@ def test_bicgstab_matches_lasolver():
     a, rc = orc.build_euler_jac(S.ia, S.ja)
     rng = np.random.default_rng(3)
     b = rng.standard_normal(orc.P * orc.D) * 1e-3
+    S.sfac()
     x_ref, it_ref = S.solve(a, b)
     pcg = mm.PCG(S.ia, S.ja, a, precond="ilu0")
     x, it, relres = pcg.bicgstab(b, 1e-6, 10000)
