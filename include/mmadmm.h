@@ -201,6 +201,10 @@ int mmadmm_pcg_spmv(mmadmm_pcg *h, const double *x, double *y);
 int mmadmm_pcg_precond(mmadmm_pcg *h, const double *r, double *z);
 /* ILU(0) factor values in A's CSR pattern (unit lower below the diagonal, U on and above it). */
 int mmadmm_pcg_get_ilu(mmadmm_pcg *h, double *lu);
+/* "tri_mode": 1 (default) = in the ILU(0) triangular solves every run of consecutive levels of at most 32768 rows is ONE launch
+ * of a thread-block cluster that walks the levels with cluster barriers (wider levels keep a launch each); 0 = one launch
+ * per level.  Results are bit-identical. */
+int mmadmm_pcg_set_option(mmadmm_pcg *h, const char *name, int value);
 /* info4 = {threads per row of the SpMV kernel, lower levels, upper levels, kernels launched so far}. */
 int mmadmm_pcg_info(mmadmm_pcg *h, int *info4);
 /* Average device time (ms, CUDA events) of one SpMV + dot launch over `reps` launches. */

@@ -34,7 +34,7 @@ ABI_SYMBOLS = [
     "mmadmm_version", "mmadmm_plan_create", "mmadmm_plan_sizes", "mmadmm_plan_get", "mmadmm_plan_destroy",
     "mmadmm_comm_unique_id", "mmadmm_create_dist", "mmadmm_local_sizes", "mmadmm_get_x_local",
     "mmadmm_pcg_create", "mmadmm_pcg_solve", "mmadmm_pcg_solve_device", "mmadmm_pcg_bicgstab", "mmadmm_pcg_bicgstab_device", "mmadmm_pcg_spmv", "mmadmm_pcg_precond",
-    "mmadmm_pcg_get_ilu", "mmadmm_pcg_info", "mmadmm_pcg_time_spmv", "mmadmm_pcg_last_error", "mmadmm_pcg_destroy", "mmadmm_measure_fp64_peak",
+    "mmadmm_pcg_get_ilu", "mmadmm_pcg_set_option", "mmadmm_pcg_info", "mmadmm_pcg_time_spmv", "mmadmm_pcg_last_error", "mmadmm_pcg_destroy", "mmadmm_measure_fp64_peak",
 ]
 
 
@@ -72,6 +72,7 @@ def lib():
         L.mmadmm_euler_step.argtypes = [vp, _c_dp]
         L.mmadmm_backward_euler_step.argtypes = [vp, C.c_double, C.c_double, _c_dp, _c_ip, _c_ip]
         L.mmadmm_backward_euler_jacobian.argtypes = [vp, _c_ip, _c_ip, _c_ip, _c_dp]
+        L.mmadmm_pcg_set_option.argtypes = [vp, C.c_char_p, C.c_int]
         L.mmadmm_pcg_bicgstab.argtypes = [vp, _c_dp, _c_dp, C.c_double, C.c_int, _c_ip, _c_dp]
         L.mmadmm_get_x.argtypes = [vp, _c_dp]
         L.mmadmm_get_x_device.argtypes = [vp, vp]
@@ -245,6 +246,9 @@ class PCG:
         x = np.zeros(self.n); it = C.c_int(); rr = C.c_double()
         self._check(self.L.mmadmm_pcg_bicgstab(self.h, _dp(b), _dp(x), float(resid_reduc), int(nitmax), C.byref(it), C.byref(rr)))
         return x, it.value, rr.value
+
+    def set_option(self, name, value):
+        self._check(self.L.mmadmm_pcg_set_option(self.h, name.encode(), int(value)))
 
     def spmv(self, x):
         x = np.ascontiguousarray(x, dtype=np.float64); y = np.zeros(self.n)

@@ -1567,6 +1567,7 @@ struct mmadmm_ctx {
         double *val_d = nullptr, *vp0 = nullptr, *xn = nullptr, *rhs = nullptr, *dx = nullptr, *part = nullptr;
         mmadmm_pcg *solver = nullptr;
         long long newtonIters = 0, linIters = 0, jacBuilds = 0;
+        int triMode = 1;   // mmadmm_pcg "tri_mode" of the Method 2 solver (option "m2_tri_mode")
     } m2;
 
     double gridO[3] = {0, 0, 0}, gridRh[3] = {0, 0, 0};
@@ -2583,6 +2584,7 @@ template <int D> int m2_build_jac(mmadmm_ctx *ctx, double dt) {
         if (m.solver) { mmadmm_pcg_destroy(m.solver); m.solver = nullptr; }
         return rc;
     }
+    mmadmm_pcg_set_option(m.solver, "tri_mode", m.triMode);
     m.jacValid = true; m.jacDt = dt; m.jacBuilds++;
     return MMADMM_OK;
 }
@@ -3058,6 +3060,11 @@ int mmadmm_set_option(mmadmm_ctx *ctx, const char *name, int value) {
         return MMADMM_OK;
     }
     if (!strcmp(name, "stats")) { ctx->statsOn = value != 0; return MMADMM_OK; }
+    if (!strcmp(name, "m2_tri_mode")) {   // Method 2 triangular solves: 1 = one cluster launch per solve, 0 = one launch per level
+        ctx->m2.triMode = value ? 1 : 0;
+        if (ctx->m2.solver) mmadmm_pcg_set_option(ctx->m2.solver, "tri_mode", ctx->m2.triMode);
+        return MMADMM_OK;
+    }
     if (!strcmp(name, "prox_variant")) { ctx->proxVariant = value; return MMADMM_OK; }
     if (!strcmp(name, "usum_period")) {
         if (value < 0) return MMADMM_EINVAL;

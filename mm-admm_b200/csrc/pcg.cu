@@ -9,6 +9,9 @@
 //
 //   k_spmv_dot<LANES>   y = A x with LANES threads per row (warp-shuffle row reduction) fused with the partial sums of x.y
 //   k_tri_level<LOWER>  one level of the level-scheduled ILU(0) triangular solves (rows of a level are independent)
+//   k_tri_cluster<LOWER> ALL levels of one triangular solve in ONE launch: a thread-block cluster of 8 x 1024 threads walks the
+//                       levels with a hardware cluster barrier between them instead of a kernel boundary (natural-order ILU(0)
+//                       on a structured 2D mesh has thousands of levels of a few hundred rows: launch latency was the cost)
 //   k_cg_update         x += alpha p, r -= alpha q, z = r / diag (Jacobi) fused with the partial sums of r.z and r.r
 //   k_dot2              partial sums of a.b and c.c                      (ILU path: after the triangular solves)
 //   k_scalars           fixed-order final reduction + the CG scalars (alpha, beta) kept on the device
@@ -96,6 +99,65 @@ __global__ void __launch_bounds__(TPB) k_tri_level(int lo, int hi, const int *__
     } else {
         for (int k = dp + 1; k < rowptr[i + 1]; k++) s -= lu[k] * out[col[k]];
         out[i] = s / lu[dp];
+    }
+}
+
+// All levels [l0, l1) of one triangular solve in one launch by ONE thread-block cluster (TC_CLUSTER CTAs x TC_THREADS threads).
+// Rows of a level are spread over the cluster's threads; levels are separated by the hardware cluster barrier, split into
+// its two halves: after a thread has stored its row's result it ARRIVES (release), then fetches the NEXT level's row --
+// extent (kbe: row extents stored in level order, so they are indexed by t, not through rows[t]), right-hand side and up to
+// TC_CACHE (column, factor) pairs into registers -- and only then WAITS (acquire).  None of that data is written by this
+// kernel, so issuing those loads inside the barrier is safe, and their latency overlaps the barrier's.  After the wait a row
+// costs one round trip to L2 for its `out` operands (ld.global.cg: values written by other CTAs, never a stale L1 line),
+// the FMA chain in ascending k (same order, same bits as k_tri_level) and the store.
+constexpr int TC_THREADS = 1024, TC_CLUSTER = 8, TC_CACHE = 12;
+__device__ __forceinline__ void cluster_arrive_release() { asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory"); }
+__device__ __forceinline__ void cluster_wait_acquire() { asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory"); }
+template <bool LOWER>
+__global__ void __cluster_dims__(TC_CLUSTER, 1, 1) __launch_bounds__(TC_THREADS)
+k_tri_cluster(int l0, int l1, const int *__restrict__ lvlOff, const int *__restrict__ rows, const int2 *__restrict__ kbe,
+              const int *__restrict__ col, const double *__restrict__ lu, const double *__restrict__ rhs, double *out) {
+    const int tid = blockIdx.x * TC_THREADS + threadIdx.x;
+    constexpr int NTHR = TC_THREADS * TC_CLUSTER;
+    int lo = lvlOff[l0], hi = lvlOff[l0 + 1];
+    int i = 0, kb = 0, ke = 0, c[TC_CACHE];
+    double s = 0.0, dv = 1.0, a[TC_CACHE];
+    // registers <- this thread's first row of the level starting at lo
+    auto fetch = [&](int t) {
+        const int2 e = kbe[t];
+        i = rows[t];
+        kb = e.x; ke = e.y;
+        s = rhs[i];
+        if (!LOWER) dv = lu[kb - 1];   // U rows start right after the diagonal
+#pragma unroll
+        for (int j = 0; j < TC_CACHE; j++)
+            if (kb + j < ke) { c[j] = col[kb + j]; a[j] = lu[kb + j]; }
+    };
+    if (lo + tid < hi) fetch(lo + tid);
+    for (int l = l0; l < l1; l++) {
+        if (lo + tid < hi) {
+            double o[TC_CACHE];
+#pragma unroll
+            for (int j = 0; j < TC_CACHE; j++) o[j] = (kb + j < ke) ? __ldcg(out + c[j]) : 0.0;
+#pragma unroll
+            for (int j = 0; j < TC_CACHE; j++)
+                if (kb + j < ke) s -= a[j] * o[j];
+            for (int k = kb + TC_CACHE; k < ke; k++) s -= lu[k] * __ldcg(out + col[k]);
+            out[i] = LOWER ? s : s / dv;
+        }
+        for (int t = lo + tid + NTHR; t < hi; t += NTHR) {   // levels wider than the cluster: further passes, no register cache
+            const int2 e = kbe[t];
+            const int r = rows[t];
+            double sr = rhs[r];
+            for (int k = e.x; k < e.y; k++) sr -= lu[k] * __ldcg(out + col[k]);
+            out[r] = LOWER ? sr : sr / lu[e.x - 1];
+        }
+        cluster_arrive_release();
+        if (l + 1 < l1) {
+            lo = hi; hi = lvlOff[l + 2];
+            if (lo + tid < hi) fetch(lo + tid);
+        }
+        cluster_wait_acquire();
     }
 }
 
@@ -221,6 +283,9 @@ struct mmadmm_pcg {
     int *rowptr = nullptr, *col = nullptr, *diagPos = nullptr;
     double *val = nullptr, *lu = nullptr, *invDiag = nullptr;
     int *rowsL = nullptr, *rowsU = nullptr;       // rows ordered by level
+    int *lvlL_d = nullptr, *lvlU_d = nullptr;     // level offsets on the device (k_tri_cluster)
+    int2 *kbeL = nullptr, *kbeU = nullptr;        // off-diagonal extent [kb, ke) of the rows in level order (k_tri_cluster)
+    int triMode = 1;                              // 1: one cluster launch per triangular solve; 0: one launch per level
     std::vector<int> lvlL, lvlU;                  // level offsets (host)
     double *r = nullptr, *z = nullptr, *p = nullptr, *q = nullptr, *x = nullptr, *b = nullptr, *tmp = nullptr;
     double *part0 = nullptr, *part1 = nullptr, *scal = nullptr, *scal_h = nullptr;
@@ -257,17 +322,39 @@ void launch_spmv(mmadmm_pcg *h, const double *x, double *y, double *part) {
 }
 int spmv_parts(const mmadmm_pcg *h) { return cdiv((size_t)h->n * h->lanes, TPB); }
 
+// One triangular solve.  tri_mode 1: runs of consecutive levels that each fit a few passes of the cluster's 8192 threads go
+// out as ONE k_tri_cluster launch (natural-order ILU(0) on a structured 2D mesh: thousands of levels of a few hundred rows);
+// wider levels (e.g. all cell-centre rows of the upper factor, plane-sized levels in 3D) keep one full-width launch each.
+template <bool LOWER>
+void tri_solve(mmadmm_pcg *h, const std::vector<int> &lvl, const int *lvl_d, const int *rows, const int2 *kbe, const double *rhs,
+               double *out) {
+    const int nlev = (int)lvl.size() - 1;
+    const int wide = 4 * TC_THREADS * TC_CLUSTER;
+    auto level = [&](int l) {
+        const int lo = lvl[l], hi = lvl[l + 1];
+        k_tri_level<LOWER><<<cdiv(hi - lo, TPB), TPB, 0, h->stream>>>(lo, hi, rows, h->rowptr, h->col, h->diagPos, h->lu, rhs, out);
+        h->launches++;
+    };
+    int l = 0;
+    while (l < nlev) {
+        int e = l;
+        if (h->triMode == 1 && lvl_d && kbe)
+            while (e < nlev && lvl[e + 1] - lvl[e] <= wide) e++;
+        if (e - l >= 4) {
+            k_tri_cluster<LOWER><<<TC_CLUSTER, TC_THREADS, 0, h->stream>>>(l, e, lvl_d, rows, kbe, h->col, h->lu, rhs, out);
+            h->launches++;
+            l = e;
+        } else {
+            level(l);
+            l++;
+        }
+    }
+}
+
 // z = (LU)^{-1} r by level-scheduled forward and backward substitution
 void apply_ilu(mmadmm_pcg *h, const double *r, double *z) {
-    for (size_t l = 0; l + 1 < h->lvlL.size(); l++) {
-        const int lo = h->lvlL[l], hi = h->lvlL[l + 1];
-        k_tri_level<true><<<cdiv(hi - lo, TPB), TPB, 0, h->stream>>>(lo, hi, h->rowsL, h->rowptr, h->col, h->diagPos, h->lu, r, h->tmp);
-    }
-    for (size_t l = 0; l + 1 < h->lvlU.size(); l++) {
-        const int lo = h->lvlU[l], hi = h->lvlU[l + 1];
-        k_tri_level<false><<<cdiv(hi - lo, TPB), TPB, 0, h->stream>>>(lo, hi, h->rowsU, h->rowptr, h->col, h->diagPos, h->lu, h->tmp, z);
-    }
-    h->launches += (long long)(h->lvlL.size() + h->lvlU.size()) - 2;
+    tri_solve<true>(h, h->lvlL, h->lvlL_d, h->rowsL, h->kbeL, r, h->tmp);
+    tri_solve<false>(h, h->lvlU, h->lvlU_d, h->rowsU, h->kbeU, h->tmp, z);
 }
 
 }  // namespace
@@ -361,6 +448,18 @@ int mmadmm_pcg_create(int n, const int *rowptr, const int *col, const double *va
         PCK(up((void **)&h->lu, lu.data(), sizeof(double) * (size_t)nnz));
         PCK(up((void **)&h->rowsL, rowsL.data(), sizeof(int) * (size_t)n));
         PCK(up((void **)&h->rowsU, rowsU.data(), sizeof(int) * (size_t)n));
+        {
+            std::vector<int2> eL(n), eU(n);
+            for (int t = 0; t < n; t++) {
+                eL[t] = make_int2(rowptr[rowsL[t]], diagPos[rowsL[t]]);
+                eU[t] = make_int2(diagPos[rowsU[t]] + 1, rowptr[rowsU[t] + 1]);
+            }
+            PCK(up((void **)&h->kbeL, eL.data(), sizeof(int2) * (size_t)n));
+            PCK(up((void **)&h->kbeU, eU.data(), sizeof(int2) * (size_t)n));
+            PCK(cudaStreamSynchronize(h->stream));   // eL / eU go out of scope
+        }
+        PCK(up((void **)&h->lvlL_d, h->lvlL.data(), sizeof(int) * h->lvlL.size()));
+        PCK(up((void **)&h->lvlU_d, h->lvlU.data(), sizeof(int) * h->lvlU.size()));
     }
     const size_t vb = sizeof(double) * (size_t)n;
     PCK(up((void **)&h->r, nullptr, vb)); PCK(up((void **)&h->z, nullptr, vb)); PCK(up((void **)&h->p, nullptr, vb));
@@ -373,6 +472,13 @@ int mmadmm_pcg_create(int n, const int *rowptr, const int *col, const double *va
     PCK(cudaMallocHost(&h->scal_h, sizeof(double) * S_COUNT));
     PCK(cudaStreamSynchronize(h->stream));
     return MMADMM_OK;
+}
+
+int mmadmm_pcg_set_option(mmadmm_pcg *h, const char *name, int value) {
+    if (!h || !name) return MMADMM_EINVAL;
+    if (!std::strcmp(name, "tri_mode")) { h->triMode = value ? 1 : 0; return MMADMM_OK; }
+    h->err = std::string("unknown option ") + name;
+    return MMADMM_EINVAL;
 }
 
 int mmadmm_pcg_info(mmadmm_pcg *h, int *info4) {
@@ -617,7 +723,7 @@ void mmadmm_pcg_destroy(mmadmm_pcg *h) {
     if (!h) return;
     cudaSetDevice(h->device);
     cudaFree(h->rowptr); cudaFree(h->col); cudaFree(h->diagPos); cudaFree(h->val); cudaFree(h->lu); cudaFree(h->invDiag);
-    cudaFree(h->rowsL); cudaFree(h->rowsU);
+    cudaFree(h->rowsL); cudaFree(h->rowsU); cudaFree(h->lvlL_d); cudaFree(h->lvlU_d); cudaFree(h->kbeL); cudaFree(h->kbeU);
     cudaFree(h->r); cudaFree(h->z); cudaFree(h->p); cudaFree(h->q); cudaFree(h->x); cudaFree(h->b); cudaFree(h->tmp);
     cudaFree(h->part0); cudaFree(h->part1); cudaFree(h->scal);
     for (int k = 0; k < 4; k++) cudaFree(h->bi[k]);

@@ -78,6 +78,36 @@ def test_bicgstab_matches_lasolver():
     pcg.close()
 
 
+@pytest.mark.parametrize("nx", [20, 96, 192])
+def test_cluster_triangular_solve_is_bit_identical_to_per_level_launches(nx):
+    """k_tri_cluster (one thread-block-cluster launch per triangular solve, cluster barriers between levels) against
+    k_tri_level (one launch per level) on the Method 2 Jacobian of an nx x nx square: same bits, and BiCGSTAB takes the same
+    iterations to the same solution."""
+    Vp, F, mask = mm.generate_uniform_rect_mesh(2, nx, nx, 0)
+    mon = mm.TestMonitor(2, 4).evaluate_at_vertices(Vp)
+    mesh = mm.Mesh(Vp.copy(), F.copy(), mask, mon, rho=50.0, tau=0.5, integration_mode=2)
+    solver = mm.MeshIntegrator(0.025, mesh)
+    rowptr, col, val = solver.backward_euler_jacobian()
+    pcg = mm.PCG(rowptr, col, val, precond="ilu0")
+    info = pcg.info()
+    nl, nu = info["lower_levels"], info["upper_levels"]
+    assert nl + nu >= 16
+    rng = np.random.default_rng(11)
+    r = rng.standard_normal(len(rowptr) - 1)
+    out = {}
+    for mode in (0, 1):
+        pcg.set_option("tri_mode", mode)
+        l0 = pcg.info()["launches"]
+        z = pcg.precond(r)
+        launches = pcg.info()["launches"] - l0
+        x, it, relres = pcg.bicgstab(r * 1e-3, 1e-6, 10000)
+        out[mode] = (z, x, it, launches)
+    assert out[0][3] == nl + nu and out[1][3] <= 8, (out[0][3], out[1][3], nl, nu)
+    assert np.array_equal(out[0][0], out[1][0])
+    assert np.array_equal(out[0][1], out[1][1]) and out[0][2] == out[1][2] > 0
+    pcg.close()
+
+
 @pytest.mark.parametrize("name,nsteps", [("Monitor220", 52), ("Monitor210", 18), ("Monitor310", 60), ("3DMonitor210", 8)])
 def test_backward_euler_trace_and_positions(name, nsteps):
     """Per-step energies: equal to the committed Ih2.txt at its 6 digits AND within 1e-9 of the oracle; Newton and BiCGSTAB
