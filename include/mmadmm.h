@@ -201,7 +201,7 @@ int mmadmm_pcg_spmv(mmadmm_pcg *h, const double *x, double *y);
 int mmadmm_pcg_precond(mmadmm_pcg *h, const double *r, double *z);
 /* ILU(0) factor values in A's CSR pattern (unit lower below the diagonal, U on and above it). */
 int mmadmm_pcg_get_ilu(mmadmm_pcg *h, double *lu);
-/* "tri_mode": 1 (default) = in the ILU(0) triangular solves every run of consecutive levels of at most 32768 rows is ONE launch
+/* "tri_mode": 1 (default) = in the ILU(0) triangular solves every run of consecutive levels of at most 8192 rows is ONE launch
  * of a thread-block cluster that walks the levels with cluster barriers (wider levels keep a launch each); 0 = one launch
  * per level.  Results are bit-identical. */
 int mmadmm_pcg_set_option(mmadmm_pcg *h, const char *name, int value);

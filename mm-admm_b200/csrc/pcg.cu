@@ -9,7 +9,7 @@
 //
 //   k_spmv_dot<LANES>   y = A x with LANES threads per row (warp-shuffle row reduction) fused with the partial sums of x.y
 //   k_tri_level<LOWER>  one level of the level-scheduled ILU(0) triangular solves (rows of a level are independent)
-//   k_tri_cluster<LOWER> ALL levels of one triangular solve in ONE launch: a thread-block cluster of 8 x 1024 threads walks the
+//   k_tri_cluster<LOWER> ALL levels of one triangular solve in ONE launch: a thread-block cluster of 8 x 256 threads walks the
 //                       levels with a hardware cluster barrier between them instead of a kernel boundary (natural-order ILU(0)
 //                       on a structured 2D mesh has thousands of levels of a few hundred rows: launch latency was the cost)
 //   k_cg_update         x += alpha p, r -= alpha q, z = r / diag (Jacobi) fused with the partial sums of r.z and r.r
@@ -110,7 +110,7 @@ __global__ void __launch_bounds__(TPB) k_tri_level(int lo, int hi, const int *__
 // kernel, so issuing those loads inside the barrier is safe, and their latency overlaps the barrier's.  After the wait a row
 // costs one round trip to L2 for its `out` operands (ld.global.cg: values written by other CTAs, never a stale L1 line),
 // the FMA chain in ascending k (same order, same bits as k_tri_level) and the store.
-constexpr int TC_THREADS = 1024, TC_CLUSTER = 8, TC_CACHE = 12;
+constexpr int TC_THREADS = 256, TC_CLUSTER = 8, TC_CACHE = 12;
 __device__ __forceinline__ void cluster_arrive_release() { asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory"); }
 __device__ __forceinline__ void cluster_wait_acquire() { asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory"); }
 template <bool LOWER>
@@ -322,7 +322,7 @@ void launch_spmv(mmadmm_pcg *h, const double *x, double *y, double *part) {
 }
 int spmv_parts(const mmadmm_pcg *h) { return cdiv((size_t)h->n * h->lanes, TPB); }
 
-// One triangular solve.  tri_mode 1: runs of consecutive levels that each fit a few passes of the cluster's 8192 threads go
+// One triangular solve.  tri_mode 1: runs of consecutive levels that each fit a few passes of the cluster's 2048 threads go
 // out as ONE k_tri_cluster launch (natural-order ILU(0) on a structured 2D mesh: thousands of levels of a few hundred rows);
 // wider levels (e.g. all cell-centre rows of the upper factor, plane-sized levels in 3D) keep one full-width launch each.
 template <bool LOWER>
