@@ -172,3 +172,23 @@ def test_backward_euler_jacobian_is_fd_hessian(golden_dir):
     want = dv[inter] + s * (g1 - g0)[inter] / eps
     got = Ji.T @ dv[inter]
     assert np.abs(got - want).max() < 1e-5 * np.abs(want).max()
+
+
+def test_restated_cgstab_equals_lasolver_3d():
+    """Same cross-check on a small 3D Jacobian (cube nx = 3, MEx33D, 3 x 3 blocks): pattern, iteration counts and iterates of
+    the numpy ILU(0) + CGSTAB restatement against the reference's LASolver."""
+    import pcg_oracle as PO
+    if not PO.have_lasolver():
+        pytest.skip("oracle/_ref not built")
+    Vp, F, mask = O.uniform_rect_mesh(3, 3, 3, 3)
+    mon = O.monitor_eval(3, 3, Vp)
+    a = O.Oracle(Vp, F, mask, mon, 50.0, 0.5, 0.025)
+    b = O.Oracle(Vp, F, mask, mon, 50.0, 0.5, 0.025)
+    S, R = _method2_solver(a), _method2_solver(b, restated=True)
+    assert np.array_equal(S.ia, R.ia) and np.array_equal(S.ja, R.ja)
+    for _ in range(3):
+        ra, rb = a.backwards_euler_step(S), b.backwards_euler_step(R)
+        assert ra["status"] == 0 and rb["status"] == 0
+        assert ra["inner_iters"] == rb["inner_iters"] and ra["newton_iters"] == rb["newton_iters"] >= 1
+        assert abs(ra["Ih"] - rb["Ih"]) <= 1e-13 * abs(ra["Ih"])
+        assert np.abs(a.x() - b.x()).max() <= 1e-13
