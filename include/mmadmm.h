@@ -66,8 +66,8 @@ int mmadmm_euler_step(mmadmm_ctx *ctx, double *Ih);
  * this method never refreshes; rebuilt only while no step has been taken or when the 1-norm of F stalls), linear solves by
  * ILU(0) + BiCGSTAB (mmadmm_pcg_bicgstab_device; residual reduction 1e-6), stop at ||F||_1 < tol / 10 or after 1000 Newton
  * iterations.  Ih = energy at the last evaluated iterate (the value the reference returns); newtonIters / linIters (sum of
- * the inner iterations) may be NULL.  dt <= 0 uses the context's dt (the reference ignores the argument's value in the
- * same way: it only enters as dt/tau with the integrator's own dt being what main.cpp passes).  Single-GPU contexts only. */
+ * the inner iterations) may be NULL.  dt is the step the reference's driver passes (main.cpp:190; it enters as dt/tau in the
+ * guess, the residual and the Jacobian); dt <= 0 uses the context's dt.  Single-GPU contexts only (MMADMM_EINVAL otherwise). */
 int mmadmm_backward_euler_step(mmadmm_ctx *ctx, double dt, double tol, double *Ih, int *newtonIters, int *linIters);
 /* The Method 2 Jacobian in CSR form (after the first backward-Euler step or mmadmm_backward_euler_jacobian with val != NULL
  * forcing a build): sizes2 = {rows, nnz}; rowptr[rows+1], col[nnz], val[nnz] may each be NULL. */
