@@ -31,7 +31,10 @@ enum {
                                src/AdaptationFunctional.cpp:174 */
     MMADMM_ESINGULAR = 4,   /* singular finite-difference Hessian (reference: Eigen inverse() -> inf/nan) */
     MMADMM_ENCCL = 5,       /* NCCL error */
-    MMADMM_ENODEVICE = 6    /* no CUDA device: there is no CPU fallback */
+    MMADMM_ENODEVICE = 6,   /* no CUDA device: there is no CPU fallback */
+    MMADMM_EPEER = 7        /* distributed context: a peer rank did not reach an exchange within "peer_timeout_s" (default 300 s;
+                               env MMADMM_PEER_TIMEOUT_S).  Ranks enter a step at independent host times: waiting is normal, the
+                               bound only catches a rank that died.  Reported on every surviving rank; the CUDA context stays usable. */
 };
 
 /* State selectors for mmadmm_get_state (inspection / parity tests). */
@@ -96,6 +99,29 @@ int mmadmm_get_x_colmajor(mmadmm_ctx *ctx, double *VpColMajor);
 int mmadmm_host_register(void *p, unsigned long bytes);
 int mmadmm_host_unregister(void *p);
 
+/* Replaces the per-step Mesh::updateAfterStep (src/Mesh.cpp:1016-1036: Vp <- x after every MeshIntegrator::step) without a
+ * call per step: once a target is set, every successful mmadmm_step ends by writing the node positions into `VpHost`
+ * (row-major interleaved P x D, or column-major P x D = the storage of the caller's Eigen::MatrixXd when colMajor != 0; on a
+ * distributed context the GLOBAL array, of which this rank writes the rows of its own vertices).
+ *   mode 1 (strict):   the copy has landed when mmadmm_step returns -- the reference's semantics.
+ *   mode 2 (deferred): x is snapshotted on the device at the end of the step and copied on a separate copy stream while the
+ *                      next step runs.  CONTRACT: the caller must not read VpHost until mmadmm_writeback_fence (or
+ *                      mmadmm_get_x*, mmadmm_restore, mmadmm_destroy, which fence) has returned, and must keep VpHost alive
+ *                      until then.  The reference's driver never reads Vp between steps (main.cpp:180-215), only after
+ *                      MeshIntegrator::done(); the host classes fence in done(), outputPoints() and getEnergy().
+ *   mode 0: off (default).  VpHost should be page-locked (mmadmm_host_register) for the copy to be asynchronous at all.
+ * Methods 1 and 2 do not write back (the reference does not call updateAfterStep there either). */
+int mmadmm_set_writeback(mmadmm_ctx *ctx, double *VpHost, int colMajor, int mode);
+int mmadmm_writeback_fence(mmadmm_ctx *ctx);
+
+/* Checkpoint / restore of the whole integrator state on the device (x, xPrev, xBar, z, u, inverse Hessians, dual sums, step
+ * counters, statistics): restore returns the context to exactly the state of the last checkpoint (bit-identical continuation),
+ * also after a run has broken down (status word cleared).  The reference has no counterpart ("Checkpoint / resume:
+ * none"); bench.py restarts its timed epochs from one post-warm-up checkpoint.  Costs one extra copy of the state in HBM.
+ * On a distributed context every rank must call it at the same point of the run. */
+int mmadmm_checkpoint(mmadmm_ctx *ctx);
+int mmadmm_restore(mmadmm_ctx *ctx);
+
 /* The re-oriented connectivity (the reference permutes the caller's F in place). */
 int mmadmm_get_F(mmadmm_ctx *ctx, int *F);
 
@@ -133,7 +159,8 @@ int mmadmm_get_timing(mmadmm_ctx *ctx, double *ms5, long long *counts5, int rese
  * "usum_period" (default 64): the x-updates work on per-vertex sums of the dual variable that follow a recurrence
  *  and are re-gathered exactly every usum_period-th update; 0 = every x-update gathers z - u slot by slot,
  * the literal form of src/MeshIntegrator.cpp:137-138,159-160 (results agree to rounding, tests hold 1e-12);
- * "p2p_active" is a query: returns 0 iff a distributed context exchanges through NVLink peer stores. */
+ * "p2p_active" is a query: returns 0 iff a distributed context exchanges through NVLink peer stores;
+ * "peer_timeout_s" (default 300): see MMADMM_EPEER. */
 int mmadmm_set_option(mmadmm_ctx *ctx, const char *name, int value);
 
 /* The CUDA stream every kernel of this context is launched on (cudaStream_t as void*). */

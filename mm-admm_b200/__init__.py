@@ -24,7 +24,7 @@ _c_dp = C.POINTER(C.c_double)
 _c_ip = C.POINTER(C.c_int)
 _c_llp = C.POINTER(C.c_longlong)
 
-ERRORS = {1: "EINVAL", 2: "ECUDA", 3: "EINVERTED", 4: "ESINGULAR", 5: "ENCCL", 6: "ENODEVICE"}
+ERRORS = {1: "EINVAL", 2: "ECUDA", 3: "EINVERTED", 4: "ESINGULAR", 5: "ENCCL", 6: "ENODEVICE", 7: "EPEER"}
 
 # every symbol include/mmadmm.h declares (checked by tests/test_abi.py)
 ABI_SYMBOLS = [
@@ -34,6 +34,7 @@ ABI_SYMBOLS = [
     "mmadmm_version", "mmadmm_plan_create", "mmadmm_plan_sizes", "mmadmm_plan_get", "mmadmm_plan_destroy",
     "mmadmm_comm_unique_id", "mmadmm_create_dist", "mmadmm_local_sizes", "mmadmm_get_x_local",
     "mmadmm_pcg_create", "mmadmm_pcg_solve", "mmadmm_pcg_solve_device", "mmadmm_pcg_bicgstab", "mmadmm_pcg_bicgstab_device", "mmadmm_pcg_spmv", "mmadmm_pcg_precond",
+    "mmadmm_set_writeback", "mmadmm_writeback_fence", "mmadmm_checkpoint", "mmadmm_restore",
     "mmadmm_pcg_get_ilu", "mmadmm_pcg_set_option", "mmadmm_pcg_info", "mmadmm_pcg_time_spmv", "mmadmm_pcg_last_error", "mmadmm_pcg_destroy", "mmadmm_measure_fp64_peak",
 ]
 
@@ -61,6 +62,17 @@ def lib():
         if not os.path.exists(LIB_PATH):
             raise MMADMMError(f"{LIB_PATH} is missing: run `python -c 'import __graft_entry__ as g; g.build()'` "
                               "(nvcc, sm_100a). mm-admm_b200 has no CPU fallback.")
+        if "MMADMM_NCCL_LIB" not in os.environ:   # multi-GPU set-up: prefer the NCCL that ships with torch (one NCCL per process)
+            try:
+                import importlib.util
+                spec = importlib.util.find_spec("nvidia.nccl")
+                for d in (spec.submodule_search_locations if spec else []):
+                    cand = os.path.join(d, "lib", "libnccl.so.2")
+                    if os.path.exists(cand):
+                        os.environ["MMADMM_NCCL_LIB"] = cand
+                        break
+            except Exception:
+                pass
         L = C.CDLL(LIB_PATH)
         vp = C.c_void_p
         L.mmadmm_create.restype = C.c_int
@@ -78,6 +90,10 @@ def lib():
         L.mmadmm_get_x_device.argtypes = [vp, vp]
         L.mmadmm_get_F.argtypes = [vp, _c_ip]
         L.mmadmm_get_x_colmajor.argtypes = [vp, _c_dp]
+        L.mmadmm_set_writeback.argtypes = [vp, _c_dp, C.c_int, C.c_int]
+        L.mmadmm_writeback_fence.argtypes = [vp]
+        L.mmadmm_checkpoint.argtypes = [vp]
+        L.mmadmm_restore.argtypes = [vp]
         L.mmadmm_host_register.argtypes = [vp, C.c_ulong]
         L.mmadmm_host_unregister.argtypes = [vp]
         L.mmadmm_grid_dims.argtypes = [vp, _c_ip]
@@ -338,9 +354,14 @@ class MeshIntegrator:
 
     def __init__(self, dt, mesh, device=0, sync_vp=True, comm=None):
         """comm = (rank, nranks, id128) makes this rank one member of an element-block-partitioned solve over nranks
-        GPUs (one process per GPU; every rank passes the same global mesh).  step/getEnergy/done are then collective."""
+        GPUs (one process per GPU; every rank passes the same global mesh).  step/getEnergy/done are then collective.
+
+        sync_vp: what Mesh::updateAfterStep does after every step (src/Mesh.cpp:1030-1035: Vp <- x).  True / "strict": mesh.Vp
+        is current when step() returns (the reference's semantics).  "deferred": the copy into mesh.Vp overlaps the next step
+        (mmadmm_set_writeback mode 2); mesh.Vp may be read after done(), getEnergy() or fence().  False: no per-step
+        write-back (done() still refreshes mesh.Vp)."""
         self.mesh, self.dt = mesh, float(dt)
-        self.sync_vp = sync_vp
+        self._sync_vp = False
         self.L = lib()
         self.h = C.c_void_p()
         m = mesh
@@ -358,6 +379,27 @@ class MeshIntegrator:
             self._check(self.L.mmadmm_get_F(self.h, _ip(m.F)))  # the reference permutes the caller's F in place
         self.n = m.D * (m.D + 1)
         self.last = {}
+        self.sync_vp = sync_vp
+
+    @property
+    def sync_vp(self):
+        return self._sync_vp
+
+    @sync_vp.setter
+    def sync_vp(self, v):
+        mode = {False: 0, None: 0, True: 1, "strict": 1, "deferred": 2}[v]
+        self._check(self.L.mmadmm_set_writeback(self.h, _dp(self.mesh.Vp) if mode else None, 0, mode))
+        self._sync_vp = v
+
+    def fence(self):
+        """Wait for a deferred write-back of mesh.Vp to land."""
+        self._check(self.L.mmadmm_writeback_fence(self.h))
+
+    def checkpoint(self):
+        self._check(self.L.mmadmm_checkpoint(self.h))
+
+    def restore(self):
+        self._check(self.L.mmadmm_restore(self.h))
 
     def _check(self, rc):
         if rc:
@@ -379,11 +421,8 @@ class MeshIntegrator:
         Ih = C.c_double(); it = C.c_int(); pr = C.c_double(); du = C.c_double()
         self._check(self.L.mmadmm_step(self.h, int(nIters), float(tol), C.byref(Ih), C.byref(it), C.byref(pr), C.byref(du)))
         self.last = dict(Ih=Ih.value, iters=it.value, primal=pr.value, dual=du.value)
-        if self.sync_vp:  # Mesh::updateAfterStep writes the caller's Vp every step (src/Mesh.cpp:1030-1035)
-            if self.dist:   # this rank's vertices only; done() assembles the global mesh
-                self._check(self.L.mmadmm_get_x_local(self.h, _dp(self.mesh.Vp)))
-            else:
-                self._check(self.L.mmadmm_get_x(self.h, _dp(self.mesh.Vp)))
+        # Mesh::updateAfterStep (Vp <- x) happened inside mmadmm_step when sync_vp is on (mmadmm_set_writeback); on a
+        # distributed context this rank's vertices only -- done() assembles the global mesh
         return Ih.value
 
     def eulerStep(self, tol=1e-3):
@@ -417,6 +456,8 @@ class MeshIntegrator:
         return p.value, e.value
 
     def getEnergy(self):
+        if self._sync_vp == "deferred":
+            self.fence()
         v = C.c_double()
         self._check(self.L.mmadmm_energy(self.h, C.byref(v)))
         return v.value

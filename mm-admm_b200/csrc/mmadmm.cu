@@ -1084,7 +1084,7 @@ __global__ void __launch_bounds__(TPB_V, MINB) k_xupdate(int P, size_t Es, const
                                                    const double *u, const double *zsrc, const double *xBar,
                                                    const double *tdiag, double m, double dtsq, double w, double *x,
                                                    double *partPrimal, const int *sharedSlot, double *sPart, const int *vorder,
-                                                   double *usum) {
+                                                   double *usum, const HaloPush hp) {
     static_assert(!UREC || (PRIMAL && !ZSRC && !UZERO), "the recurrence belongs to the update that follows a prox sweep");
     __shared__ double red[32];
     const int tix = blockIdx.x * TPB_V + threadIdx.x;
@@ -1153,6 +1153,7 @@ __global__ void __launch_bounds__(TPB_V, MINB) k_xupdate(int P, size_t Es, const
         if (sh >= 0) {   // shared with another rank: only the partial sum is known here (finished by k_xfinish)
 #pragma unroll
             for (int l = 0; l < D; l++) sPart[(size_t)sh * D + l] = s[l];
+            if (hp.ptr) halo_push_store<D>(hp, sh, s);   // ... and goes straight into the sharers' mailboxes over NVLink
         }
         double td = tdiag[p];
 #pragma unroll
@@ -1178,6 +1179,7 @@ __global__ void __launch_bounds__(TPB_V, MINB) k_xupdate(int P, size_t Es, const
         double r = block_sum(prim, red);
         if (threadIdx.x == 0) partPrimal[blockIdx.x] = r;
     }
+    if (hp.ptr) halo_push_publish(hp);
 }
 
 // Distributed x-update, shared vertices: x from the exchanged total, and their share of ||D x - z||^2 over the LOCAL slots
@@ -1513,8 +1515,11 @@ struct mmadmm_ctx {
     double *mbScal_d = nullptr, *mbRecv_d = nullptr;                      // inside the own mailbox
     int *nbrPtr_d = nullptr;
     unsigned long long haloEpoch = 0, scalEpoch = 0;
+    unsigned long long peerTimeoutNs = 300ull * 1000000000ull;   // bound of every wait on a peer's flag (option "peer_timeout_s")
+    int *pushPtr_d = nullptr, *pushNbr_d = nullptr, *pushPos_d = nullptr;   // per shared vertex: (neighbour, position) it is pushed to
+    unsigned *pushTicket_d = nullptr;
     int nShared = 0, nNbrItems = 0, nblkSh = 0;
-    std::vector<int> nbrRank, nbrPtr;           // host copies of the plan's neighbour segments
+    std::vector<int> nbrRank, nbrPtr, nbrListHost;   // host copies of the plan's neighbour segments
     int *sharedIdx = nullptr, *sharedSlot = nullptr, *nbrList = nullptr, *contribPtr = nullptr, *contrib = nullptr, *verts = nullptr;
     uint8_t *owner = nullptr;
     double *xloc_h = nullptr;
@@ -1570,6 +1575,27 @@ struct mmadmm_ctx {
         int triMode = 1;   // mmadmm_pcg "tri_mode" of the Method 2 solver (option "m2_tri_mode")
     } m2;
 
+    // checkpoint of the whole integrator state (mmadmm_checkpoint / mmadmm_restore)
+    struct Ckpt {
+        bool valid = false, stepTaken = false, hessComputed = false;
+        int stepsTaken = 0, usumAge = 0;
+        long long admmIters = 0, proxCalls = 0;
+        double *x = nullptr, *xPrev = nullptr, *xBar = nullptr, *z = nullptr, *u = nullptr, *B = nullptr, *usum = nullptr;
+        unsigned long long *hist = nullptr;
+    } ck;
+    // write-back of the node positions into the caller's host array after every step (Mesh::updateAfterStep, src/Mesh.cpp:1030-1035)
+    struct Writeback {
+        int mode = 0;                 // 0 off, 1 strict (synchronous, the reference's semantics), 2 deferred (overlapped, fenced)
+        int colMajor = 0;             // 1: caller's array is column-major P x D (Eigen::MatrixXd Vp)
+        double *host = nullptr;       // caller-owned; GLOBAL P x D on a distributed context (this rank writes its own rows)
+        double *stage[2] = {nullptr, nullptr};
+        cudaStream_t copyStream = nullptr;
+        cudaEvent_t evSnap[2] = {nullptr, nullptr}, evCopied[2] = {nullptr, nullptr};
+        bool inFlight[2] = {false, false};
+        int next = 0;
+        long long copies = 0;
+    } wb;
+
     double gridO[3] = {0, 0, 0}, gridRh[3] = {0, 0, 0};
     MonGrid monGrid() const {
         MonGrid mg;
@@ -1593,11 +1619,6 @@ struct mmadmm_ctx {
         a.status = status_d;
         return a;
     }
-    // where k_finalize puts its results: device scalars on a distributed context (they are combined across ranks on the
-    // device), the mapped host buffers otherwise
-    double *scalOut(int off) { return (dist ? scal_d : scal_hd) + off; }
-    const unsigned *statusIn() { return dist ? nullptr : status_d; }
-    unsigned *statusOut() { return dist ? nullptr : status_hd; }
     void phaseBegin(int ph) {
         if (!timingOn) return;
         if (evUsed + 2 > evPool.size()) {
@@ -1652,9 +1673,11 @@ NcclApi &nccl() {
     static bool tried = false;
     if (tried) return api;
     tried = true;
-    const char *cands[] = {"libnccl.so.2", "/opt/prime-rl/.venv/lib/python3.12/site-packages/nvidia/nccl/lib/libnccl.so.2", "libnccl.so"};
+    // MMADMM_NCCL_LIB (a path) first, then the sonames; a libnccl the process has already loaded (e.g. torch's) is found by soname
+    const char *cands[] = {getenv("MMADMM_NCCL_LIB"), "libnccl.so.2", "libnccl.so"};
     void *h = nullptr;
     for (const char *c : cands) {
+        if (!c || !c[0]) continue;
         h = dlopen(c, RTLD_NOW | RTLD_GLOBAL);
         if (h) break;
     }
@@ -1716,19 +1739,6 @@ __global__ void k_halo_combine(int nShared, const int *contribPtr, const int *co
 
 // ---- NVLink peer-memory exchange ----------------------------------------------------------------------------------
 // Flags are monotonically increasing epochs written with system scope after the data; readers spin (bounded) on them.
-__device__ __forceinline__ void flag_release(unsigned long long *flag, unsigned long long v) {
-    __threadfence_system();
-    asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(flag), "l"(v) : "memory");
-}
-__device__ __forceinline__ void flag_wait(const unsigned long long *flag, unsigned long long v) {
-    unsigned long long cur;
-    for (long long spin = 0; spin < (1ll << 27); spin++) {
-        asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(cur) : "l"(flag) : "memory");
-        if (cur >= v) return;
-        __nanosleep(64);
-    }
-    __trap();   // a peer never arrived: surface as a CUDA error instead of hanging the GPU
-}
 // One block per neighbour: store this rank's partials of the vertices shared with neighbour q straight into q's mailbox
 // (receive half `epoch & 1`), then publish the epoch in q's flag slot for this rank.
 template <int D>
@@ -1749,16 +1759,14 @@ __global__ void __launch_bounds__(1024) k_halo_push(const int *nbrPtr, const int
 }
 // total = sum of the sharers' partials in ascending rank order, reading the partials the neighbours pushed
 template <int D>
-__global__ void k_halo_combine_p2p(int nShared, int nNbr, const int *contribPtr, const int *contrib, const double *sPart,
-                                   const double *recvBase, size_t recvStride, const unsigned long long *flags,
-                                   unsigned long long epoch, double *sTot) {
-    if (threadIdx.x < nNbr) flag_wait(flags + threadIdx.x, epoch);
-    for (int q = blockDim.x + threadIdx.x; q < nNbr; q += blockDim.x) flag_wait(flags + q, epoch);
+__device__ __forceinline__ void halo_wait_all(int nNbr, const unsigned long long *flags, unsigned long long epoch,
+                                              unsigned long long timeoutNs, unsigned *status) {
+    for (int q = threadIdx.x; q < nNbr; q += blockDim.x) flag_wait(flags + q, epoch, timeoutNs, status);
     __syncthreads();
-    const double *recvBuf = recvBase + ((epoch & 1ull) ? recvStride : 0);
-    int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= nShared) return;
-    double s[D];
+}
+template <int D>
+__device__ __forceinline__ void halo_total(int i, const int *contribPtr, const int *contrib, const double *sPart, const double *recvBuf,
+                                           double *s) {
 #pragma unroll
     for (int l = 0; l < D; l++) s[l] = 0.0;
     for (int k = contribPtr[i]; k < contribPtr[i + 1]; k++) {
@@ -1766,28 +1774,110 @@ __global__ void k_halo_combine_p2p(int nShared, int nNbr, const int *contribPtr,
 #pragma unroll
         for (int l = 0; l < D; l++) s[l] += (c < 0) ? sPart[(size_t)i * D + l] : __ldcg(recvBuf + (size_t)c * D + l);
     }
+}
+template <int D>
+__global__ void k_halo_combine_p2p(int nShared, int nNbr, const int *contribPtr, const int *contrib, const double *sPart,
+                                   const double *recvBase, size_t recvStride, const unsigned long long *flags,
+                                   unsigned long long epoch, double *sTot, unsigned long long timeoutNs, unsigned *status) {
+    halo_wait_all<D>(nNbr, flags, epoch, timeoutNs, status);
+    const double *recvBuf = recvBase + ((epoch & 1ull) ? recvStride : 0);
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= nShared) return;
+    double s[D];
+    halo_total<D>(i, contribPtr, contrib, sPart, recvBuf, s);
 #pragma unroll
     for (int l = 0; l < D; l++) sTot[(size_t)i * D + l] = s[l];
 }
-// all-gather of the 5 per-rank scalars through the mailboxes: thread r stores this rank's row into rank r's table
-__global__ void k_scal_push(int nranks, int rank, const double *scal, const unsigned *status, double *const *peerScal,
-                            unsigned long long *const *peerFlag, unsigned long long epoch) {
-    const int r = threadIdx.x;
-    if (r >= nranks) return;
-    double *dst = peerScal[r] + ((epoch & 1ull) ? (size_t)nranks * 8 : 0);
+// Fused k_halo_combine_p2p + k_xfinish: wait for the neighbours' epoch, sum the sharers' partials in ascending rank order
+// (identical on every sharer), finish x of the shared vertices and their share of ||D x - z||^2 over the LOCAL slots.
+template <int D, bool ZSRC, bool PRIMAL>
+__global__ void __launch_bounds__(TPB_V) k_xfinish_p2p(int nShared, int nNbr, const int *sharedIdx, const int *contribPtr, const int *contrib,
+                                                       const double *sPart, const double *recvBase, size_t recvStride,
+                                                       const unsigned long long *flags, unsigned long long epoch,
+                                                       unsigned long long timeoutNs, unsigned *status, const int *incPtr,
+                                                       const int *incIdx, const double *z, const double *zsrc, const double *xBar,
+                                                       const double *tdiag, double m, double dtsq, double *x, double *partPrimal) {
+    __shared__ double red[32];
+    halo_wait_all<D>(nNbr, flags, epoch, timeoutNs, status);
+    const double *recvBuf = recvBase + ((epoch & 1ull) ? recvStride : 0);
+    const int i = blockIdx.x * TPB_V + threadIdx.x;
+    double prim = 0.0;
+    if (i < nShared) {
+        double s[D], xn[D];
+        halo_total<D>(i, contribPtr, contrib, sPart, recvBuf, s);
+        const int p = sharedIdx[i];
+        const double td = tdiag[p];
 #pragma unroll
-    for (int k = 0; k < 4; k++) dst[k] = scal[k];
-    dst[4] = (double)*status;
-    flag_release(peerFlag[r], epoch);
-    (void)rank;
+        for (int l = 0; l < D; l++) {
+            xn[l] = ((m * xBar[(size_t)D * p + l]) + dtsq * s[l]) / td;
+            x[(size_t)D * p + l] = xn[l];
+        }
+        if (PRIMAL) {
+            for (int k = incPtr[p]; k < incPtr[p + 1]; k++) {
+                const int slot = __ldg(incIdx + k);
+                const size_t e = (size_t)(slot >> 2);
+                const int v = slot & 3;
+#pragma unroll
+                for (int l = 0; l < D; l++) {
+                    const double zv = ZSRC ? zsrc[(size_t)D * p + l] : __ldg(z + tm_index(e, D * v + l, D * (D + 1)));
+                    const double df = xn[l] - zv;
+                    prim += df * df;
+                }
+            }
+        }
+    }
+    if (PRIMAL) {
+        double r = block_sum(prim, red);
+        if (threadIdx.x == 0) partPrimal[blockIdx.x] = r;
+    }
 }
-__global__ void k_scal_wait(int nranks, const double *mbScal, const unsigned long long *flags, unsigned long long epoch, double *scalAll) {
+// Fused k_finalize + all-gather of the per-rank scalars through the mailboxes + sum in rank order (one CTA): the fixed-order
+// reduction of up to 3 partial arrays into scal[off..], then thread r stores this rank's row {scal[0..3], status} into rank r's
+// table and publishes the epoch, waits for rank r's row, and thread 0 adds the rows in ascending rank order -- identical on every
+// rank, so every rank takes the same break decision (src/MeshIntegrator.cpp:162-169) -- into mapped host memory.
+__global__ void __launch_bounds__(1024) k_finalize_dist(int n0, const double *p0, int n1, const double *p1, int n2, const double *p2,
+                                                        double *scal, int off, unsigned *status, int nranks, double *const *peerScal,
+                                                        unsigned long long *const *peerFlag, const double *mbScal,
+                                                        const unsigned long long *flags, unsigned long long epoch,
+                                                        unsigned long long timeoutNs, double *scalHost, unsigned *statusHost) {
+    __shared__ double red[32];
+    __shared__ double rows[32 * 5];
+    const double *ps[3] = {p0, p1, p2};
+    const int ns[3] = {n0, n1, n2};
+    for (int q = 0; q < 3; q++) {
+        if (!ps[q]) continue;
+        double s = 0.0;
+        for (int i = threadIdx.x; i < ns[q]; i += blockDim.x) s += ps[q][i];
+        double r = block_sum(s, red);
+        if (threadIdx.x == 0) scal[off + q] = r;
+        __syncthreads();
+    }
     const int r = threadIdx.x;
-    if (r >= nranks) return;
-    flag_wait(flags + r, epoch);
-    const double *src = mbScal + ((epoch & 1ull) ? (size_t)nranks * 8 : 0) + (size_t)r * 8;
+    if (r < nranks) {
+        double *dst = peerScal[r] + ((epoch & 1ull) ? (size_t)nranks * 8 : 0);
 #pragma unroll
-    for (int k = 0; k < 5; k++) scalAll[5 * r + k] = __ldcg(src + k);
+        for (int k = 0; k < 4; k++) dst[k] = scal[k];
+        dst[4] = (double)(*(volatile unsigned *)status & ~(unsigned)ST_PEER_TIMEOUT);
+        flag_release(peerFlag[r], epoch);
+        const bool ok = flag_wait(flags + r, epoch, timeoutNs, status);
+        const double *src = mbScal + ((epoch & 1ull) ? (size_t)nranks * 8 : 0) + (size_t)r * 8;
+#pragma unroll
+        for (int k = 0; k < 5; k++) rows[5 * r + k] = ok ? __ldcg(src + k) : 0.0;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        unsigned st = *(volatile unsigned *)status & ST_PEER_TIMEOUT;
+        double acc[4] = {0.0, 0.0, 0.0, 0.0};
+        for (int q = 0; q < nranks; q++) {
+#pragma unroll
+            for (int k = 0; k < 4; k++) acc[k] += rows[5 * q + k];
+            st |= (unsigned)rows[5 * q + 4];
+        }
+#pragma unroll
+        for (int k = 0; k < 4; k++) scalHost[k] = acc[k];
+        *statusHost = st;
+        __threadfence_system();
+    }
 }
 
 // sPart (partials of the shared vertices) -> sTot (totals): NVLink peer stores (default) or NCCL point-to-point
@@ -1801,7 +1891,7 @@ template <int D> int halo_exchange(mmadmm_ctx *ctx) {
                                               ctx->peerHaloFlag_d, ep);
         k_halo_combine_p2p<D><<<cdiv(ctx->nShared, 256), 256, 0, st>>>(ctx->nShared, nNbr, ctx->contribPtr, ctx->contrib, ctx->sPart,
                                                                       ctx->mbRecv_d, (size_t)std::max(ctx->nNbrItems, 1) * D,
-                                                                      ctx->haloFlags_d, ep, ctx->sTot);
+                                                                      ctx->haloFlags_d, ep, ctx->sTot, ctx->peerTimeoutNs, ctx->status_d);
         ctx->launches += 2;
         return MMADMM_OK;
     }
@@ -1820,29 +1910,33 @@ template <int D> int halo_exchange(mmadmm_ctx *ctx) {
     return MMADMM_OK;
 }
 
-// The three residual scalars (+ the status word) of every rank, summed on the host in rank order: the break decision
-// of the ADMM loop is then identical on all ranks (src/MeshIntegrator.cpp:162-169).
-int gather_scalars(mmadmm_ctx *ctx, int nScal) {
+// Fixed-order reduction of up to three partial arrays into scal[off .. off+2], then the scalars (+ the status word) where the
+// host reads them after one stream synchronise: single GPU -- k_finalize writes mapped host memory; NVLink peer path --
+// k_finalize_dist also exchanges the per-rank rows through the mailboxes and adds them in rank order on the device; NCCL
+// fallback -- ncclAllGather + host sum.  The break decision of the ADMM loop is identical on all ranks
+// (src/MeshIntegrator.cpp:162-169).
+int finalize_scalars(mmadmm_ctx *ctx, int n0, const double *p0, int n1, const double *p1, int n2, const double *p2, int off) {
     cudaStream_t st = ctx->stream;
-    if (!ctx->dist) {   // k_finalize wrote the scalars and the status word straight into the mapped host buffers
-        (void)nScal;
+    if (!ctx->dist) {
+        k_finalize<<<1, 1024, 0, st>>>(n0, p0, n1, p1, n2, p2, ctx->scal_hd + off, ctx->status_d, ctx->status_hd);
+        ctx->launches += 1;
         CK(cudaStreamSynchronize(st));
         return MMADMM_OK;
     }
     if (ctx->p2p) {
         const unsigned long long ep = ++ctx->scalEpoch;
-        k_scal_push<<<1, 32, 0, st>>>(ctx->nranks, ctx->rank, ctx->scal_d, ctx->status_d, ctx->peerScal_d, ctx->peerScalFlag_d, ep);
-        k_scal_wait<<<1, 32, 0, st>>>(ctx->nranks, ctx->mbScal_d, ctx->scalFlags_d, ep, ctx->scalAll_hd);   // mapped host memory: no copy
+        k_finalize_dist<<<1, 1024, 0, st>>>(n0, p0, n1, p1, n2, p2, ctx->scal_d, off, ctx->status_d, ctx->nranks, ctx->peerScal_d,
+                                            ctx->peerScalFlag_d, ctx->mbScal_d, ctx->scalFlags_d, ep, ctx->peerTimeoutNs, ctx->scal_hd,
+                                            ctx->status_hd);
         ctx->launches += 1;
         CK(cudaStreamSynchronize(st));
-    } else {
-        k_status_to_double<<<1, 1, 0, st>>>(ctx->status_d, ctx->scal_d + 4);
-        NK(nccl().allGather(ctx->scal_d, ctx->scalAll_d, 5, NCCL_FLOAT64, ctx->comm, st));
+        return MMADMM_OK;
     }
-    if (!ctx->p2p) {
-        CK(cudaMemcpyAsync(ctx->scalAll_h, ctx->scalAll_d, sizeof(double) * 5 * ctx->nranks, cudaMemcpyDeviceToHost, st));
-        CK(cudaStreamSynchronize(st));
-    }
+    k_finalize<<<1, 1024, 0, st>>>(n0, p0, n1, p1, n2, p2, ctx->scal_d + off, nullptr, nullptr);
+    k_status_to_double<<<1, 1, 0, st>>>(ctx->status_d, ctx->scal_d + 4);
+    NK(nccl().allGather(ctx->scal_d, ctx->scalAll_d, 5, NCCL_FLOAT64, ctx->comm, st));
+    CK(cudaMemcpyAsync(ctx->scalAll_h, ctx->scalAll_d, sizeof(double) * 5 * ctx->nranks, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
     unsigned stat = 0;
     for (int k = 0; k < 4; k++) ctx->scal_h[k] = 0.0;
     for (int r = 0; r < ctx->nranks; r++) {
@@ -1850,7 +1944,7 @@ int gather_scalars(mmadmm_ctx *ctx, int nScal) {
         stat |= (unsigned)ctx->scalAll_h[5 * r + 4];
     }
     *ctx->status_h = stat;
-    ctx->launches += 1;
+    ctx->launches += 3;
     return MMADMM_OK;
 }
 
@@ -1962,6 +2056,24 @@ int setup_p2p(mmadmm_ctx *ctx, int D) {
     CK(up((void **)&ctx->peerScal_d, peerScal.data(), sizeof(double *) * nranks));
     CK(up((void **)&ctx->peerScalFlag_d, peerSF.data(), sizeof(void *) * nranks));
     CK(up((void **)&ctx->nbrPtr_d, ctx->nbrPtr.data(), sizeof(int) * ctx->nbrPtr.size()));
+    {   // per shared vertex: the (neighbour, position in that neighbour's receive segment) pairs its partial sum is stored to
+        // by the kernel that computes it (fused halo push of k_xupdate)
+        std::vector<int> pptr((size_t)ctx->nShared + 1, 0), pnbr(ctx->nbrListHost.size()), ppos(ctx->nbrListHost.size());
+        for (int i : ctx->nbrListHost) pptr[(size_t)i + 1]++;
+        for (int i = 0; i < ctx->nShared; i++) pptr[(size_t)i + 1] += pptr[i];
+        std::vector<int> cur(pptr.begin(), pptr.end() - 1);
+        for (int q = 0; q < nNbr; q++)
+            for (int j = ctx->nbrPtr[q]; j < ctx->nbrPtr[q + 1]; j++) {
+                const int i = ctx->nbrListHost[j];
+                pnbr[cur[i]] = q; ppos[cur[i]] = j - ctx->nbrPtr[q];
+                cur[i]++;
+            }
+        CK(up((void **)&ctx->pushPtr_d, pptr.data(), sizeof(int) * pptr.size()));
+        CK(up((void **)&ctx->pushNbr_d, pnbr.data(), sizeof(int) * pnbr.size()));
+        CK(up((void **)&ctx->pushPos_d, ppos.data(), sizeof(int) * ppos.size()));
+        CK(cudaMalloc(&ctx->pushTicket_d, sizeof(unsigned)));
+        CK(cudaMemset(ctx->pushTicket_d, 0, sizeof(unsigned)));
+    }
     ctx->haloFlags_d = (unsigned long long *)(ctx->mailbox + MB_OFF_HALOFLAG);
     ctx->scalFlags_d = (unsigned long long *)(ctx->mailbox + MB_OFF_SCALFLAG);
     ctx->mbScal_d = (double *)(ctx->mailbox + MB_OFF_SCAL);
@@ -2256,8 +2368,85 @@ int create_impl(mmadmm_ctx *ctx, const double *Vp, const double *Vc, const int *
 
 int check_status(mmadmm_ctx *ctx) {
     unsigned s = *ctx->status_h;
+    if (s & ST_PEER_TIMEOUT) {
+        ctx->err = "a peer rank did not reach the exchange within peer_timeout_s: it died, or its host stalled for longer than that";
+        return MMADMM_EPEER;
+    }
     if (s & ST_INVERTED) { ctx->err = "inverted element (det E <= 0): the reference asserts here (AdaptationFunctional.cpp:174)"; return MMADMM_EINVERTED; }
     if (s & ST_SINGULAR_HESS) { ctx->err = "singular finite-difference Hessian"; return MMADMM_ESINGULAR; }
+    return MMADMM_OK;
+}
+
+
+// ---- write-back of the node positions (Mesh::updateAfterStep, src/Mesh.cpp:1030-1035) -------------------------------------
+// After every mmadmm_step the final x is snapshotted device-to-device into one of two staging buffers (transposed there when
+// the caller's array is column-major) and copied to the caller's page-locked array on a separate copy stream, so the PCIe
+// transfer of step s overlaps the kernels of step s+1.  mode 1 (strict) fences at once: the reference's semantics.
+int ensure_local_runs(mmadmm_ctx *ctx) {
+    if (!ctx->dist || !ctx->verts_h.empty()) return MMADMM_OK;
+    ctx->verts_h.resize(ctx->P);   // runs of consecutive global ids (a strip / slab partition has two or three)
+    CK(cudaMemcpy(ctx->verts_h.data(), ctx->verts, sizeof(int) * (size_t)ctx->P, cudaMemcpyDeviceToHost));
+    for (int l = 0; l < ctx->P;) {
+        int m = l + 1;
+        while (m < ctx->P && ctx->verts_h[m] == ctx->verts_h[m - 1] + 1) m++;
+        ctx->runs.push_back({l, m - l});
+        l = m;
+    }
+    return MMADMM_OK;
+}
+int wb_fence(mmadmm_ctx *ctx) {
+    mmadmm_ctx::Writeback &w = ctx->wb;
+    for (int b = 0; b < 2; b++)
+        if (w.inFlight[b]) {
+            CK(cudaEventSynchronize(w.evCopied[b]));
+            w.inFlight[b] = false;
+        }
+    return MMADMM_OK;
+}
+int wb_issue(mmadmm_ctx *ctx) {
+    mmadmm_ctx::Writeback &w = ctx->wb;
+    const int D = ctx->D, P = ctx->P;
+    const size_t bytes = sizeof(double) * (size_t)P * D;
+    if (!w.copyStream) {
+        CK(cudaStreamCreateWithFlags(&w.copyStream, cudaStreamNonBlocking));
+        for (int b = 0; b < 2; b++) {
+            CK(cudaMalloc(&w.stage[b], bytes));
+            CK(cudaEventCreateWithFlags(&w.evSnap[b], cudaEventDisableTiming));
+            CK(cudaEventCreateWithFlags(&w.evCopied[b], cudaEventDisableTiming));
+        }
+    }
+    const int b = w.next;
+    w.next ^= 1;
+    if (w.inFlight[b]) CK(cudaStreamWaitEvent(ctx->stream, w.evCopied[b], 0));   // two steps old: the stage is free again
+    if (w.colMajor) {
+        k_x_to_colmajor<<<cdiv(P, 256), 256, 0, ctx->stream>>>(P, D, ctx->x, w.stage[b]);
+        ctx->launches++;
+    } else {
+        CK(cudaMemcpyAsync(w.stage[b], ctx->x, bytes, cudaMemcpyDeviceToDevice, ctx->stream));
+    }
+    CK(cudaEventRecord(w.evSnap[b], ctx->stream));
+    CK(cudaStreamWaitEvent(w.copyStream, w.evSnap[b], 0));
+    if (!ctx->dist) {
+        CK(cudaMemcpyAsync(w.host, w.stage[b], bytes, cudaMemcpyDeviceToHost, w.copyStream));
+    } else {   // this rank's vertices into their rows of the caller's GLOBAL array, one copy per run of consecutive ids
+        int rc = ensure_local_runs(ctx);
+        if (rc) return rc;
+        for (auto &r : ctx->runs) {
+            const size_t g0 = (size_t)ctx->verts_h[r.first];
+            if (w.colMajor) {
+                for (int l = 0; l < D; l++)
+                    CK(cudaMemcpyAsync(w.host + (size_t)l * ctx->Pglobal + g0, w.stage[b] + (size_t)l * P + r.first,
+                                       sizeof(double) * (size_t)r.second, cudaMemcpyDeviceToHost, w.copyStream));
+            } else {
+                CK(cudaMemcpyAsync(w.host + g0 * D, w.stage[b] + (size_t)r.first * D, sizeof(double) * (size_t)r.second * D,
+                                   cudaMemcpyDeviceToHost, w.copyStream));
+            }
+        }
+    }
+    CK(cudaEventRecord(w.evCopied[b], w.copyStream));
+    w.inFlight[b] = true;
+    w.copies++;
+    if (w.mode == 1) return wb_fence(ctx);
     return MMADMM_OK;
 }
 
@@ -2339,6 +2528,15 @@ template <> int launch_prox<3>(mmadmm_ctx *ctx, const ElemArgs<3> &a) {
 template <int D, bool ZSRC, bool UZERO, bool PRIMAL, bool UREC = false>
 int launch_xupdate_t(mmadmm_ctx *ctx, const double *zsrc, bool sharedOnly = false) {
     const double dtsq = ctx->dt * ctx->dt;
+    const bool exch = ctx->dist && ctx->nShared > 0;
+    HaloPush hp;
+    unsigned long long ep = 0;
+    if (exch && ctx->p2p) {   // the kernel that forms the partial sums also stores them into the sharers' mailboxes (NVLink)
+        ep = ++ctx->haloEpoch;
+        hp.ptr = ctx->pushPtr_d; hp.nbr = ctx->pushNbr_d; hp.pos = ctx->pushPos_d;
+        hp.peerRecv = ctx->peerRecv_d; hp.peerStride = ctx->peerRecvStride_d; hp.peerFlag = ctx->peerHaloFlag_d;
+        hp.ticket = ctx->pushTicket_d; hp.nNbr = (int)ctx->nbrRank.size(); hp.epoch = ep;
+    }
     if (!sharedOnly) {
         // chunk size / occupancy of the recurrence form, measured on C2 and C4: 2D 2 slots per chunk at full occupancy
         // (32 registers), 3D 8 slots per chunk (80 registers); the differences are a few per cent of the kernel
@@ -2346,22 +2544,29 @@ int launch_xupdate_t(mmadmm_ctx *ctx, const double *zsrc, bool sharedOnly = fals
                           : (D == 2 ? k_xupdate<D, ZSRC, UZERO, PRIMAL, UREC, 2, 8> : k_xupdate<D, ZSRC, UZERO, PRIMAL, UREC, 8, 1>);
         kern<<<ctx->nblkV, TPB_V, 0, ctx->stream>>>(
             ctx->P, ctx->Es, ctx->incPtr, ctx->incIdx, ctx->z, ctx->u, zsrc, ctx->xBar, ctx->tdiag, ctx->m, dtsq, ctx->w, ctx->x,
-            ctx->partPrimal, ctx->dist ? ctx->sharedSlot : nullptr, ctx->sPart, ctx->vorder, ctx->usum);
+            ctx->partPrimal, ctx->dist ? ctx->sharedSlot : nullptr, ctx->sPart, ctx->vorder, ctx->usum, hp);
         ctx->launches++;
-    } else if (ctx->dist && ctx->nShared > 0) {
+    } else if (exch) {
         k_xupdate<D, ZSRC, UZERO, PRIMAL, UREC><<<ctx->nblkSh, TPB_V, 0, ctx->stream>>>(
             ctx->nShared, ctx->Es, ctx->incPtr, ctx->incIdx, ctx->z, ctx->u, zsrc, ctx->xBar, ctx->tdiag, ctx->m, dtsq, ctx->w, ctx->x,
-            ctx->partPrimal, ctx->sharedSlot, ctx->sPart, ctx->sharedIdx, ctx->usum);
+            ctx->partPrimal, ctx->sharedSlot, ctx->sPart, ctx->sharedIdx, ctx->usum, hp);
         ctx->launches++;
     }
-    if (ctx->dist && ctx->nShared > 0) {
-        int rc = halo_exchange<D>(ctx);
-        if (rc) return rc;
-        k_xfinish<D, ZSRC, PRIMAL><<<ctx->nblkSh, TPB_V, 0, ctx->stream>>>(ctx->nShared, ctx->sharedIdx, ctx->sTot, ctx->Es, ctx->incPtr,
-                                                                          ctx->incIdx, ctx->z, zsrc, ctx->xBar, ctx->tdiag, ctx->m, dtsq,
-                                                                          ctx->x, ctx->partPrimal + ctx->nblkV);
+    if (!exch) return MMADMM_OK;
+    if (ctx->p2p) {
+        k_xfinish_p2p<D, ZSRC, PRIMAL><<<ctx->nblkSh, TPB_V, 0, ctx->stream>>>(
+            ctx->nShared, (int)ctx->nbrRank.size(), ctx->sharedIdx, ctx->contribPtr, ctx->contrib, ctx->sPart, ctx->mbRecv_d,
+            (size_t)std::max(ctx->nNbrItems, 1) * D, ctx->haloFlags_d, ep, ctx->peerTimeoutNs, ctx->status_d, ctx->incPtr, ctx->incIdx,
+            ctx->z, zsrc, ctx->xBar, ctx->tdiag, ctx->m, dtsq, ctx->x, ctx->partPrimal + ctx->nblkV);
         ctx->launches++;
+        return MMADMM_OK;
     }
+    int rc = halo_exchange<D>(ctx);
+    if (rc) return rc;
+    k_xfinish<D, ZSRC, PRIMAL><<<ctx->nblkSh, TPB_V, 0, ctx->stream>>>(ctx->nShared, ctx->sharedIdx, ctx->sTot, ctx->Es, ctx->incPtr,
+                                                                      ctx->incIdx, ctx->z, zsrc, ctx->xBar, ctx->tdiag, ctx->m, dtsq,
+                                                                      ctx->x, ctx->partPrimal + ctx->nblkV);
+    ctx->launches++;
     return MMADMM_OK;
 }
 
@@ -2442,11 +2647,10 @@ template <int D> int step_impl(mmadmm_ctx *ctx, int nIters, double tol, double *
         ctx->phaseEnd();
         ctx->phaseBegin(3);
         const int nbp = ctx->nProxPart;
-        k_finalize<<<1, 1024, 0, st>>>(nbp, ctx->partIh, gV + ((ctx->dist && ctx->nShared > 0) ? ctx->nblkSh : 0), ctx->partPrimal, nbp,
-                                       ctx->partDual, ctx->scalOut(0), ctx->statusIn(), ctx->statusOut());
-        ctx->launches += 1;
+        // synchronises; sums over ranks on a distributed context
+        int rc = finalize_scalars(ctx, nbp, ctx->partIh, gV + ((ctx->dist && ctx->nShared > 0) ? ctx->nblkSh : 0), ctx->partPrimal, nbp,
+                                  ctx->partDual, 0);
         ctx->phaseEnd();
-        int rc = gather_scalars(ctx, 3);   // synchronises; sums over ranks on a distributed context
         if (rc) return rc;
         ctx->admmIters++;
         ctx->proxCalls += (long long)ctx->E;
@@ -2460,6 +2664,10 @@ template <int D> int step_impl(mmadmm_ctx *ctx, int nIters, double tol, double *
     if (ctx->evUsed >= 4096) ctx->phaseResolve();
     CK(cudaGetLastError());
     ctx->stepsTaken++;
+    if (ctx->wb.mode) {   // updateAfterStep: Vp <- x
+        int rcw = wb_issue(ctx);
+        if (rcw) return rcw;
+    }
     if (IhOut) *IhOut = Ihstart;
     if (itersOut) *itersOut = (i == nIters) ? nIters : i + 1;
     if (primalOut) *primalOut = primal;
@@ -2471,10 +2679,8 @@ template <int D> int energy_impl(mmadmm_ctx *ctx, double *I) {
     cudaStream_t st = ctx->stream;
     ElemArgs<D> a = ctx->elemArgs<D>(0.0);
     k_energy<D><<<ctx->nblkE, TPB, 0, st>>>(a, ctx->partPrimal);
-    k_finalize<<<1, 1024, 0, st>>>(ctx->nblkE, ctx->partPrimal, 0, nullptr, 0, nullptr, ctx->scalOut(3), ctx->statusIn(), ctx->statusOut());
-    ctx->launches += 2;
-    // k_finalize writes out[0] of its `out` argument => scal_d[3]
-    int rcg = gather_scalars(ctx, 4);
+    ctx->launches += 1;
+    int rcg = finalize_scalars(ctx, ctx->nblkE, ctx->partPrimal, 0, nullptr, 0, nullptr, 3);   // -> scal[3]
     if (rcg) return rcg;
     CK(cudaGetLastError());
     *I = ctx->scal_h[3];
@@ -2497,9 +2703,7 @@ template <int D> int euler_impl(mmadmm_ctx *ctx, double *IhOut) {
                                                                      ctx->x, ctx->xPrev);
         ctx->launches++;
     }
-    k_finalize<<<1, 1024, 0, st>>>(ctx->nblkE, ctx->partPrimal, 0, nullptr, 0, nullptr, ctx->scalOut(3), ctx->statusIn(), ctx->statusOut());
-    ctx->launches++;
-    int rcg = gather_scalars(ctx, 4);
+    int rcg = finalize_scalars(ctx, ctx->nblkE, ctx->partPrimal, 0, nullptr, 0, nullptr, 3);
     if (rcg) return rcg;
     CK(cudaGetLastError());
     if (IhOut) *IhOut = ctx->scal_h[3];
@@ -2617,9 +2821,8 @@ template <int D> int beuler_impl(mmadmm_ctx *ctx, double dt, double tol, double 
     do {
         k_euler_elem<D, true><<<ctx->nblkE, TPB, 0, st>>>(a, ctx->gs, a.nonIntBits, ctx->partPrimal);
         k_m2_gather<D, 1><<<m.nblk, TPB_V, 0, st>>>(ctx->P, ctx->Es, ctx->incPtr, ctx->incIdx, ctx->gs, s, ctx->x, m.xn, m.rhs, m.part);
-        k_finalize<<<1, 1024, 0, st>>>(m.nblk, m.part, ctx->nblkE, ctx->partPrimal, 0, nullptr, ctx->scalOut(2), ctx->statusIn(), ctx->statusOut());
-        ctx->launches += 3;
-        int rcg = gather_scalars(ctx, 4);
+        ctx->launches += 2;
+        int rcg = finalize_scalars(ctx, m.nblk, m.part, ctx->nblkE, ctx->partPrimal, 0, nullptr, 2);
         if (rcg) return rcg;
         CK(cudaGetLastError());
         const double g1 = ctx->scal_h[2];
@@ -2744,6 +2947,7 @@ int mmadmm_create_dist(int D, int P, int E, const double *Vp, const double *Vc, 
     ctx->nNbrItems = (int)plan.nbrList.size();
     ctx->nbrRank = plan.nbrRank;
     ctx->nbrPtr = plan.nbrPtr;
+    ctx->nbrListHost = plan.nbrList;
     auto upload = [&](int **dst, const std::vector<int> &v) -> cudaError_t {
         cudaError_t e = cudaMalloc(dst, sizeof(int) * std::max<size_t>(v.size(), 1));
         if (e != cudaSuccess) return e;
@@ -2768,6 +2972,10 @@ int mmadmm_create_dist(int D, int P, int E, const double *Vp, const double *Vc, 
     CK(cudaHostAlloc(&ctx->scalAll_h, sizeof(double) * 5 * nranks, cudaHostAllocMapped));
     CK(cudaHostGetDevicePointer(&ctx->scalAll_hd, ctx->scalAll_h, 0));
     ctx->nblkSh = cdiv(std::max(ctx->nShared, 1), TPB_V);
+    if (const char *pt = getenv("MMADMM_PEER_TIMEOUT_S")) {
+        const long v = atol(pt);
+        if (v > 0) ctx->peerTimeoutNs = (unsigned long long)v * 1000000000ull;
+    }
     CK(cudaStreamSynchronize(st));
     {
         int rcp = setup_p2p(ctx, D);
@@ -2846,6 +3054,7 @@ int mmadmm_energy(mmadmm_ctx *ctx, double *I) {
 int mmadmm_get_x(mmadmm_ctx *ctx, double *x) {
     if (!ctx || !x) return MMADMM_EINVAL;
     CK(cudaSetDevice(ctx->device));
+    { int rcf = wb_fence(ctx); if (rcf) return rcf; }
     if (!ctx->dist) {
         CK(cudaMemcpyAsync(x, ctx->x, sizeof(double) * (size_t)ctx->P * ctx->D, cudaMemcpyDeviceToHost, ctx->stream));
         CK(cudaStreamSynchronize(ctx->stream));
@@ -2867,12 +3076,83 @@ int mmadmm_get_x(mmadmm_ctx *ctx, double *x) {
 int mmadmm_get_x_colmajor(mmadmm_ctx *ctx, double *VpColMajor) {
     if (!ctx || !VpColMajor || ctx->dist) return MMADMM_EINVAL;
     CK(cudaSetDevice(ctx->device));
+    { int rcf = wb_fence(ctx); if (rcf) return rcf; }
     const size_t bytes = sizeof(double) * (size_t)ctx->P * ctx->D;
     if (!ctx->xT) CK(cudaMalloc(&ctx->xT, bytes));
     k_x_to_colmajor<<<cdiv(ctx->P, 256), 256, 0, ctx->stream>>>(ctx->P, ctx->D, ctx->x, ctx->xT);
     ctx->launches++;
     CK(cudaMemcpyAsync(VpColMajor, ctx->xT, bytes, cudaMemcpyDeviceToHost, ctx->stream));
     CK(cudaStreamSynchronize(ctx->stream));
+    return MMADMM_OK;
+}
+
+int mmadmm_set_writeback(mmadmm_ctx *ctx, double *VpHost, int colMajor, int mode) {
+    if (!ctx || mode < 0 || mode > 2 || (mode != 0 && !VpHost)) return MMADMM_EINVAL;
+    CK(cudaSetDevice(ctx->device));
+    int rc = wb_fence(ctx);
+    if (rc) return rc;
+    if (mode != 0 && ctx->dist) {
+        rc = ensure_local_runs(ctx);
+        if (rc) return rc;
+        if (ctx->runs.size() > 256) { ctx->err = "write-back: this rank's vertices form more than 256 runs of consecutive global ids"; return MMADMM_EINVAL; }
+    }
+    ctx->wb.mode = mode; ctx->wb.colMajor = colMajor ? 1 : 0; ctx->wb.host = VpHost;
+    return MMADMM_OK;
+}
+int mmadmm_writeback_fence(mmadmm_ctx *ctx) {
+    if (!ctx) return MMADMM_EINVAL;
+    CK(cudaSetDevice(ctx->device));
+    return wb_fence(ctx);
+}
+
+int mmadmm_checkpoint(mmadmm_ctx *ctx) {
+    if (!ctx) return MMADMM_EINVAL;
+    CK(cudaSetDevice(ctx->device));
+    mmadmm_ctx::Ckpt &c = ctx->ck;
+    const size_t NV = sizeof(double) * (size_t)ctx->P * ctx->D, NZ = sizeof(double) * ctx->Es * ctx->n;
+    if (!c.x) {
+        CK(cudaMalloc(&c.x, NV)); CK(cudaMalloc(&c.xPrev, NV)); CK(cudaMalloc(&c.xBar, NV)); CK(cudaMalloc(&c.usum, NV));
+        CK(cudaMalloc(&c.z, NZ)); CK(cudaMalloc(&c.u, NZ)); CK(cudaMalloc(&c.B, NZ * ctx->n));
+        CK(cudaMalloc(&c.hist, sizeof(unsigned long long) * 52));
+    }
+    cudaStream_t st = ctx->stream;
+    CK(cudaMemcpyAsync(c.x, ctx->x, NV, cudaMemcpyDeviceToDevice, st));
+    CK(cudaMemcpyAsync(c.xPrev, ctx->xPrev, NV, cudaMemcpyDeviceToDevice, st));
+    CK(cudaMemcpyAsync(c.xBar, ctx->xBar, NV, cudaMemcpyDeviceToDevice, st));
+    CK(cudaMemcpyAsync(c.usum, ctx->usum, NV, cudaMemcpyDeviceToDevice, st));
+    CK(cudaMemcpyAsync(c.z, ctx->z, NZ, cudaMemcpyDeviceToDevice, st));
+    CK(cudaMemcpyAsync(c.u, ctx->u, NZ, cudaMemcpyDeviceToDevice, st));
+    CK(cudaMemcpyAsync(c.B, ctx->B, NZ * ctx->n, cudaMemcpyDeviceToDevice, st));
+    CK(cudaMemcpyAsync(c.hist, ctx->hist_d, sizeof(unsigned long long) * 52, cudaMemcpyDeviceToDevice, st));
+    CK(cudaStreamSynchronize(st));
+    c.stepTaken = ctx->stepTaken; c.hessComputed = ctx->hessComputed; c.stepsTaken = ctx->stepsTaken; c.usumAge = ctx->usumAge;
+    c.admmIters = ctx->admmIters; c.proxCalls = ctx->proxCalls;
+    c.valid = true;
+    return MMADMM_OK;
+}
+int mmadmm_restore(mmadmm_ctx *ctx) {
+    if (!ctx) return MMADMM_EINVAL;
+    mmadmm_ctx::Ckpt &c = ctx->ck;
+    if (!c.valid) { ctx->err = "mmadmm_restore: no checkpoint has been taken"; return MMADMM_EINVAL; }
+    CK(cudaSetDevice(ctx->device));
+    int rc = wb_fence(ctx);
+    if (rc) return rc;
+    const size_t NV = sizeof(double) * (size_t)ctx->P * ctx->D, NZ = sizeof(double) * ctx->Es * ctx->n;
+    cudaStream_t st = ctx->stream;
+    CK(cudaMemcpyAsync(ctx->x, c.x, NV, cudaMemcpyDeviceToDevice, st));
+    CK(cudaMemcpyAsync(ctx->xPrev, c.xPrev, NV, cudaMemcpyDeviceToDevice, st));
+    CK(cudaMemcpyAsync(ctx->xBar, c.xBar, NV, cudaMemcpyDeviceToDevice, st));
+    CK(cudaMemcpyAsync(ctx->usum, c.usum, NV, cudaMemcpyDeviceToDevice, st));
+    CK(cudaMemcpyAsync(ctx->z, c.z, NZ, cudaMemcpyDeviceToDevice, st));
+    CK(cudaMemcpyAsync(ctx->u, c.u, NZ, cudaMemcpyDeviceToDevice, st));
+    CK(cudaMemcpyAsync(ctx->B, c.B, NZ * ctx->n, cudaMemcpyDeviceToDevice, st));
+    CK(cudaMemcpyAsync(ctx->hist_d, c.hist, sizeof(unsigned long long) * 52, cudaMemcpyDeviceToDevice, st));
+    CK(cudaMemsetAsync(ctx->status_d, 0, sizeof(unsigned), st));
+    CK(cudaStreamSynchronize(st));
+    *ctx->status_h = 0;
+    ctx->stepTaken = c.stepTaken; ctx->hessComputed = c.hessComputed; ctx->stepsTaken = c.stepsTaken; ctx->usumAge = c.usumAge;
+    ctx->admmIters = c.admmIters; ctx->proxCalls = c.proxCalls;
+    ctx->m2.vpStamp = -1; ctx->m2.jacValid = false; ctx->m2.stepTaken = false;
     return MMADMM_OK;
 }
 
@@ -2891,15 +3171,10 @@ int mmadmm_get_x_local(mmadmm_ctx *ctx, double *xGlobal) {
     if (!ctx || !xGlobal) return MMADMM_EINVAL;
     if (!ctx->dist) return mmadmm_get_x(ctx, xGlobal);
     const int D = ctx->D;
-    if (ctx->verts_h.empty()) {   // runs of consecutive global ids (a strip / slab partition has two or three)
-        ctx->verts_h.resize(ctx->P);
-        CK(cudaMemcpy(ctx->verts_h.data(), ctx->verts, sizeof(int) * (size_t)ctx->P, cudaMemcpyDeviceToHost));
-        for (int l = 0; l < ctx->P;) {
-            int m = l + 1;
-            while (m < ctx->P && ctx->verts_h[m] == ctx->verts_h[m - 1] + 1) m++;
-            ctx->runs.push_back({l, m - l});
-            l = m;
-        }
+    { int rcf = wb_fence(ctx); if (rcf) return rcf; }
+    {
+        int rcr = ensure_local_runs(ctx);
+        if (rcr) return rcr;
     }
     if (ctx->runs.size() <= 64) {   // straight into the caller's array, one copy per run
         for (auto &r : ctx->runs)
@@ -3071,6 +3346,11 @@ int mmadmm_set_option(mmadmm_ctx *ctx, const char *name, int value) {
         ctx->usumPeriod = value; ctx->usumAge = 0;
         return MMADMM_OK;
     }
+    if (!strcmp(name, "peer_timeout_s")) {   // bound (seconds) of every wait on a peer rank's flag; the wait ends with MMADMM_EPEER
+        if (value <= 0) return MMADMM_EINVAL;
+        ctx->peerTimeoutNs = (unsigned long long)value * 1000000000ull;
+        return MMADMM_OK;
+    }
     if (!strcmp(name, "iso_grid")) { ctx->isoOn = value != 0; return MMADMM_OK; }   // 0: always interpolate the full tensors
     if (!strcmp(name, "p2p_active")) return ctx->p2p ? MMADMM_OK : MMADMM_EINVAL;   // query: NVLink peer-memory exchange in use
     if (!strcmp(name, "iso_grid_active")) return (ctx->isoOn && ctx->gridIsIso) ? MMADMM_OK : MMADMM_EINVAL;   // query
@@ -3083,6 +3363,15 @@ void mmadmm_destroy(mmadmm_ctx *ctx) {
     if (!ctx) return;
     cudaSetDevice(ctx->device);
     if (ctx->stream) cudaStreamSynchronize(ctx->stream);
+    wb_fence(ctx);
+    for (int b = 0; b < 2; b++) {
+        cudaFree(ctx->wb.stage[b]);
+        if (ctx->wb.evSnap[b]) cudaEventDestroy(ctx->wb.evSnap[b]);
+        if (ctx->wb.evCopied[b]) cudaEventDestroy(ctx->wb.evCopied[b]);
+    }
+    if (ctx->wb.copyStream) cudaStreamDestroy(ctx->wb.copyStream);
+    cudaFree(ctx->ck.x); cudaFree(ctx->ck.xPrev); cudaFree(ctx->ck.xBar); cudaFree(ctx->ck.usum); cudaFree(ctx->ck.z); cudaFree(ctx->ck.u);
+    cudaFree(ctx->ck.B); cudaFree(ctx->ck.hist);
     for (int v = 0; v < 4; v++) cudaFree(ctx->F[v]);
     cudaFree(ctx->mask); cudaFree(ctx->fixedBits); cudaFree(ctx->nonIntBits);
     cudaFree(ctx->x); cudaFree(ctx->xPrev); cudaFree(ctx->xBar); cudaFree(ctx->Vc); cudaFree(ctx->tdiag);
@@ -3092,6 +3381,7 @@ void mmadmm_destroy(mmadmm_ctx *ctx) {
         if ((int)r != ctx->rank && ctx->peerMap[r]) cudaIpcCloseMemHandle(ctx->peerMap[r]);
     cudaFree(ctx->mailbox); cudaFree(ctx->peerRecv_d); cudaFree(ctx->peerRecvStride_d); cudaFree(ctx->peerHaloFlag_d);
     cudaFree(ctx->peerScal_d); cudaFree(ctx->peerScalFlag_d); cudaFree(ctx->nbrPtr_d);
+    cudaFree(ctx->pushPtr_d); cudaFree(ctx->pushNbr_d); cudaFree(ctx->pushPos_d); cudaFree(ctx->pushTicket_d);
     cudaFree(ctx->grid); cudaFree(ctx->gridIso); cudaFree(ctx->xT); cudaFree(ctx->ax); cudaFree(ctx->ay); cudaFree(ctx->az);
     cudaFree(ctx->partIh); cudaFree(ctx->partDual); cudaFree(ctx->partPrimal); cudaFree(ctx->scal_d);
     if (ctx->scal_h) cudaFreeHost(ctx->scal_h);

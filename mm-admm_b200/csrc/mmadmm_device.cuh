@@ -22,7 +22,7 @@ __host__ __device__ __forceinline__ size_t tm_index(size_t e, int row, int rows)
 }
 
 enum NodeTypeDev { NT_BOUNDARY_FREE = 0, NT_BOUNDARY_FIXED = 1, NT_INTERIOR = 2 };  // src/NodeType.h:4-8
-enum StatusBits { ST_INVERTED = 1, ST_SINGULAR_HESS = 2, ST_BFGS_MAX = 4, ST_NONFINITE = 8 };
+enum StatusBits { ST_INVERTED = 1, ST_SINGULAR_HESS = 2, ST_BFGS_MAX = 4, ST_NONFINITE = 8, ST_PEER_TIMEOUT = 16 };
 
 // Monitor grid (read-only after init).  Rows are grid points, D*D doubles each (3D rows are padded to 10 doubles so
 // that every row is five aligned 16-byte loads), row index zInd*(nx+1)*(ny+1) + yInd*(nx+1) + xInd exactly as the
@@ -665,6 +665,75 @@ __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commi
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
 // make generic-proxy shared-memory writes visible to the async proxy (before a bulk store reads them)
 __device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+
+// ------------------------------------------------------------------------------------------------
+// NVLink peer-memory exchange: flags are monotonically increasing epochs written with system scope after the data; readers
+// wait on them with a TIME bound (ranks enter a step at independent host times: a peer whose host is busy for a while must
+// not cost its neighbours their CUDA context).  A wait that runs out sets ST_PEER_TIMEOUT in the status word and returns;
+// every later wait of the same run returns at once, and the host reports MMADMM_EPEER on every rank.
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ void flag_release(unsigned long long *flag, unsigned long long v) {
+    __threadfence_system();
+    asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(flag), "l"(v) : "memory");
+}
+__device__ __forceinline__ unsigned long long global_timer_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+__device__ __forceinline__ bool flag_wait(const unsigned long long *flag, unsigned long long v, unsigned long long timeoutNs, unsigned *status) {
+    unsigned long long cur;
+    asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(cur) : "l"(flag) : "memory");
+    if (cur >= v) return true;
+    if (*(volatile unsigned *)status & ST_PEER_TIMEOUT) return false;
+    const unsigned long long t0 = global_timer_ns();
+    for (unsigned spin = 1;; spin++) {
+        asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(cur) : "l"(flag) : "memory");
+        if (cur >= v) return true;
+        __nanosleep(spin < 64 ? 32 : 256);
+        if ((spin & 255u) == 0 && global_timer_ns() - t0 > timeoutNs) break;
+    }
+    atomicOr(status, ST_PEER_TIMEOUT);
+    return false;
+}
+// What a kernel needs to store its partial sums of the shared vertices straight into the neighbours' mailboxes and, as the
+// last CTA of the grid to finish, to publish the epoch (fused form of the halo push).  list == nullptr: nothing to push.
+struct HaloPush {
+    const int *ptr = nullptr;                    // [nShared+1] offsets into nbr / pos
+    const int *nbr = nullptr;                    // neighbour index q of the entry
+    const int *pos = nullptr;                    // position inside that neighbour's receive segment for this rank
+    double *const *peerRecv = nullptr;           // [nNbr] receive segment (parity 0) in the neighbour's mailbox
+    const size_t *peerStride = nullptr;          // [nNbr] doubles between the two parity halves there
+    unsigned long long *const *peerFlag = nullptr;   // [nNbr] the neighbour's flag slot for this rank
+    unsigned *ticket = nullptr;                  // CTA completion counter (self-resetting)
+    int nNbr = 0;
+    unsigned long long epoch = 0;
+};
+template <int D> __device__ __forceinline__ void halo_push_store(const HaloPush &hp, int sh, const double *s) {
+    for (int k = hp.ptr[sh]; k < hp.ptr[sh + 1]; k++) {
+        const int q = hp.nbr[k];
+        double *dst = hp.peerRecv[q] + ((hp.epoch & 1ull) ? hp.peerStride[q] : 0) + (size_t)hp.pos[k] * D;
+#pragma unroll
+        for (int l = 0; l < D; l++) dst[l] = s[l];
+    }
+}
+// Call with the whole CTA, after every thread's halo_push_store: the last CTA of the grid publishes the epoch to all neighbours.
+__device__ __forceinline__ void halo_push_publish(const HaloPush &hp) {
+    __shared__ unsigned lastFlag;
+    __threadfence_system();      // this thread's peer stores are visible system-wide before its CTA takes a ticket
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence();
+        const unsigned t = atomicAdd(hp.ticket, 1u);
+        lastFlag = (t == gridDim.x - 1) ? 1u : 0u;
+    }
+    __syncthreads();
+    if (lastFlag) {
+        __threadfence();
+        if ((int)threadIdx.x < hp.nNbr) flag_release(hp.peerFlag[threadIdx.x], hp.epoch);
+        if (threadIdx.x == 0) *hp.ticket = 0u;
+    }
+}
 
 // ------------------------------------------------------------------------------------------------
 // reductions

@@ -11,11 +11,15 @@ ROOT="$(cd "$HERE/../../.." && pwd)"
 REF="${REF:-/root/reference}"
 OUT="${OUT:-$ROOT/build/dropin}"
 if [ ! -f "$REF/main.cpp" ]; then echo "reference not present at $REF: keeping prebuilt $OUT/mesh.exe"; exit 0; fi
-rm -rf "$OUT/stage"; mkdir -p "$OUT/stage/Experiments/TestMonitors" "$OUT/stage/lib"
-ln -s "$REF/main.cpp" "$OUT/stage/main.cpp"
-for f in "$REF"/Experiments/TestMonitors/*.h; do ln -s "$f" "$OUT/stage/Experiments/TestMonitors/$(basename "$f")"; done
-ln -s "$HERE/src" "$OUT/stage/src"
-ln -s "$HERE/lib/json" "$OUT/stage/lib/json"
-g++ -O2 -std=c++17 -w -I"$HERE" -I"$ROOT/include" "$OUT/stage/main.cpp" -o "$OUT/mesh.exe" \
+# The staging tree lives in a temporary directory outside the repository and is removed after the compile.
+mkdir -p "$OUT"; rm -rf "$OUT/stage"
+STAGE="$(mktemp -d /tmp/mmadmm_dropin_stage.XXXXXX)"
+trap 'rm -rf "$STAGE"' EXIT
+mkdir -p "$STAGE/Experiments/TestMonitors" "$STAGE/lib"
+ln -s "$REF/main.cpp" "$STAGE/main.cpp"
+for f in "$REF"/Experiments/TestMonitors/*.h; do ln -s "$f" "$STAGE/Experiments/TestMonitors/$(basename "$f")"; done
+ln -s "$HERE/src" "$STAGE/src"
+ln -s "$HERE/lib/json" "$STAGE/lib/json"
+g++ -O2 -std=c++17 -w -I"$HERE" -I"$ROOT/include" "$STAGE/main.cpp" -o "$OUT/mesh.exe" \
     -L"$ROOT/mm-admm_b200" -lmmadmm_b200 -Wl,-rpath,'$ORIGIN/../../mm-admm_b200'
 echo "built $OUT/mesh.exe"

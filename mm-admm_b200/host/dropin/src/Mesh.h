@@ -7,6 +7,14 @@
 // opaque mmadmm_ctx; there is no CPU implementation behind this class -- without a CUDA device the constructor
 // reports the error and aborts, which is what the reference does on a failed assert.
 //
+// Multi-GPU (the reference's only parallelism knob is numThreads -> omp_set_num_threads, src/Mesh.cpp:429,437):
+// with MMADMM_GPUS=N in the environment (N >= 2; "threads" = take the driver's numThreads argument) the constructor forks N-1
+// worker processes BEFORE the first CUDA call -- one process per GPU, as the library's element-block partition wants it.
+// Every process builds its rank of the distributed context (mmadmm_create_dist) from the same global mesh; the workers then
+// serve the collective calls (step / energy / get_x / ...) that this process, rank 0, issues through pipes, and never return
+// into the driver.  main.cpp runs unchanged and unaware: one process writes the result files.  done() assembles the global
+// mesh; between steps only rank 0's vertices are refreshed in the caller's Vp.  Method 2 is single-GPU only.
+//
 // What the reference's Mesh does on the host and this one does not: the D/W/M sparse matrices, face lists and
 // simplex maps are never formed (the ADMM system matrix is diagonal, incidence replaces D).
 // Method 1 (explicit Euler) runs on the device through mmadmm_euler_step, Method 2 (backward Euler, the reference's
@@ -22,6 +30,11 @@
 #include <map>
 #include <set>
 #include <vector>
+#include <cstring>
+#include <string>
+#include <sys/types.h>
+#include <sys/wait.h>
+#include <unistd.h>
 
 #include "AdaptationFunctional.h"
 #include "MonitorFunction.h"
@@ -50,8 +63,15 @@ public:
         meshInit(Xp, Xp, F, boundaryMask, M, numThreads, rho, w, tau, gradUse);
     }
     ~Mesh() {
+        if (ctx) mmadmm_writeback_fence(ctx);
         if (vpRegistered) mmadmm_host_unregister(Vp->data());
+        broadcast(OP_EXIT);
         if (ctx) mmadmm_destroy(ctx);
+        for (size_t r = 0; r < workers.size(); r++) {
+            close(workers[r].fd);
+            int st = 0;
+            waitpid(workers[r].pid, &st, 0);
+        }
         delete monitorEvals;
     }
     Mesh(const Mesh &) = delete;
@@ -61,7 +81,7 @@ public:
     // numThreads has no meaning on the GPU and is kept for signature compatibility.
     void meshInit(Eigen::MatrixXd &Xc, Eigen::MatrixXd &Xp, Eigen::MatrixXi &F, vector<NodeType> &boundaryMask,
             MonitorFunction<D> *Mon, int numThreads, double rho, double w, double tau, bool gradUse) {
-        (void)numThreads; (void)w;
+        (void)w;
         this->gradUse = gradUse;
         this->Vc = compMesh ? &Xc : nullptr;
         this->Vp = &Xp;
@@ -99,13 +119,104 @@ public:
         for (int e = 0; e < E; e++) for (int v = 0; v <= D; v++) f[(size_t)e * (D + 1) + v] = F(e, v);
 
         const char *dev = getenv("MMADMM_DEVICE");
-        check(mmadmm_create(D, P, E, vp.data(), compMesh ? vc.data() : nullptr, f.data(), mask.data(), mon.data(), rho, tau,
-                            /*dt, set by MeshIntegrator*/ 0.0, gradUse ? 1 : 0, dev ? atoi(dev) : 0, &ctx), "mmadmm_create");
-        // the reference permutes the caller's F (positive orientation)
-        check(mmadmm_get_F(ctx, f.data()), "mmadmm_get_F");
-        for (int e = 0; e < E; e++) for (int v = 0; v <= D; v++) F(e, v) = f[(size_t)e * (D + 1) + v];
-        // page-lock the caller's Vp: updateAfterStep then copies straight into it at PCIe speed
+        const int dev0 = dev ? atoi(dev) : 0;
+        int nGpus = 1;
+        if (const char *g = getenv("MMADMM_GPUS")) nGpus = !strcmp(g, "threads") ? numThreads : atoi(g);
+        if (nGpus < 1) nGpus = 1;
+        if (nGpus > 1 && integrationMode != 0 && integrationMode != 1) {
+            cerr << "mm-admm_b200: Method 2 (backward Euler) runs on one GPU; ignoring MMADMM_GPUS=" << nGpus << endl;
+            nGpus = 1;
+        }
+        if (nGpus == 1) {
+            check(mmadmm_create(D, P, E, vp.data(), compMesh ? vc.data() : nullptr, f.data(), mask.data(), mon.data(), rho, tau,
+                                /*dt, set by MeshIntegrator*/ 0.0, gradUse ? 1 : 0, dev0, &ctx), "mmadmm_create");
+            // the reference permutes the caller's F (positive orientation)
+            check(mmadmm_get_F(ctx, f.data()), "mmadmm_get_F");
+            for (int e = 0; e < E; e++) for (int v = 0; v <= D; v++) F(e, v) = f[(size_t)e * (D + 1) + v];
+        } else {
+            // one process per GPU: fork the workers before this process has made its first CUDA call
+            cout.flush(); cerr.flush(); fflush(nullptr);
+            int idPipe[32][2];
+            if (nGpus > 32) nGpus = 32;
+            for (int r = 1; r < nGpus; r++) {
+                int cmd[2];
+                if (pipe(cmd) != 0 || pipe(idPipe[r]) != 0) { perror("mm-admm_b200: pipe"); exit(1); }
+                pid_t pid = fork();
+                if (pid < 0) { perror("mm-admm_b200: fork"); exit(1); }
+                if (pid == 0) {   // worker: rank r, never returns into the driver
+                    close(cmd[1]); close(idPipe[r][1]);
+                    for (size_t q = 0; q < workers.size(); q++) close(workers[q].fd);
+                    char id[128];
+                    if (read(idPipe[r][0], id, 128) != 128) _exit(3);
+                    mmadmm_ctx *c = nullptr;
+                    int rc = mmadmm_create_dist(D, P, E, vp.data(), compMesh ? vc.data() : nullptr, f.data(), mask.data(), mon.data(),
+                                                rho, tau, 0.0, gradUse ? 1 : 0, dev0 + r, r, nGpus, id, &c);
+                    if (rc != MMADMM_OK) {
+                        fprintf(stderr, "mm-admm_b200: rank %d: mmadmm_create_dist failed (%d): %s\n", r, rc, c ? mmadmm_last_error(c) : "");
+                        _exit(4);
+                    }
+                    serve(c, cmd[0], r, P);
+                    _exit(0);
+                }
+                close(cmd[0]); close(idPipe[r][0]);
+                workers.push_back({pid, cmd[1]});
+            }
+            char id[128];
+            check(mmadmm_comm_unique_id(id), "mmadmm_comm_unique_id");
+            for (int r = 1; r < nGpus; r++) {
+                if (write(idPipe[r][1], id, 128) != 128) { perror("mm-admm_b200: write"); exit(1); }
+                close(idPipe[r][1]);
+            }
+            check(mmadmm_create_dist(D, P, E, vp.data(), compMesh ? vc.data() : nullptr, f.data(), mask.data(), mon.data(), rho, tau, 0.0,
+                                     gradUse ? 1 : 0, dev0, 0, nGpus, id, &ctx), "mmadmm_create_dist");
+            // re-orientation of the caller's F: the library keeps only this rank's block, so restate src/Mesh.cpp:243-260 here
+            for (int e = 0; e < E; e++) {
+                Eigen::Matrix<double,D,D> Em;
+                for (int j = 0; j < D; j++) for (int l = 0; l < D; l++) Em(l, j) = Xp(F(e, j + 1), l) - Xp(F(e, 0), l);
+                if (Em.determinant() < 0) { int t = F(e, 2); F(e, 2) = F(e, 1); F(e, 1) = t; }
+            }
+            distributed = true;
+        }
+        // page-lock the caller's Vp and let every step write it back (Mesh::updateAfterStep, src/Mesh.cpp:1030-1035): the copy of
+        // step s overlaps step s+1 and is fenced in done(), outputPoints(), computeEnergy() (include/mmadmm.h,
+        // mmadmm_set_writeback).  MMADMM_WRITEBACK=strict: the copy has landed when step() returns; =off: done() only.
         vpRegistered = mmadmm_host_register(Xp.data(), sizeof(double) * (unsigned long)P * D) == MMADMM_OK;
+        int mode = 2;
+        if (const char *wbm = getenv("MMADMM_WRITEBACK")) mode = !strcmp(wbm, "strict") ? 1 : (!strcmp(wbm, "off") ? 0 : 2);
+        check(mmadmm_set_writeback(ctx, Xp.data(), /*column-major*/ 1, mode), "mmadmm_set_writeback");
+    }
+
+    // ---- multi-GPU plumbing: rank 0 (this process) tells the workers which collective call comes next ----
+    enum Op { OP_EXIT = 0, OP_STEP = 1, OP_ENERGY = 2, OP_EULER = 3, OP_GETX = 4, OP_SETDT = 5 };
+    struct Cmd { int op; int nIters; double a, b; };
+    struct Worker { pid_t pid; int fd; };
+    void broadcast(int op, int nIters = 0, double a = 0, double b = 0) {
+        Cmd c{op, nIters, a, b};
+        for (size_t r = 0; r < workers.size(); r++)
+            if (write(workers[r].fd, &c, sizeof(c)) != (ssize_t)sizeof(c)) { cerr << "mm-admm_b200: worker " << r + 1 << " is gone" << endl; abort(); }
+    }
+    static void serve(mmadmm_ctx *c, int fd, int rank, int P) {
+        std::vector<double> xg;
+        Cmd cmd;
+        for (;;) {
+            ssize_t got = read(fd, &cmd, sizeof(cmd));
+            if (got != (ssize_t)sizeof(cmd) || cmd.op == OP_EXIT) break;   // EOF: rank 0 died or finished
+            int rc = MMADMM_OK;
+            double v = 0;
+            switch (cmd.op) {
+                case OP_STEP: rc = mmadmm_step(c, cmd.nIters, cmd.a, &v, nullptr, nullptr, nullptr); break;
+                case OP_ENERGY: rc = mmadmm_energy(c, &v); break;
+                case OP_EULER: rc = mmadmm_euler_step(c, &v); break;
+                case OP_SETDT: rc = mmadmm_set_dt(c, cmd.a); break;
+                case OP_GETX: xg.resize((size_t)P * D); rc = mmadmm_get_x(c, xg.data()); break;
+                default: rc = MMADMM_EINVAL;
+            }
+            if (rc != MMADMM_OK) {
+                fprintf(stderr, "mm-admm_b200: rank %d: call %d failed (%d): %s\n", rank, cmd.op, rc, mmadmm_last_error(c));
+                _exit(5);
+            }
+        }
+        mmadmm_destroy(c);
     }
 
     // evalMonitorOnGrid at one point (src/MeshInterpolator.cpp:286-342): the GPU-resident interpolation
@@ -127,16 +238,26 @@ public:
     double computeEnergy(Eigen::VectorXd &x) {
         (void)x;
         double I = 0;
+        check(mmadmm_writeback_fence(ctx), "mmadmm_writeback_fence");
+        broadcast(OP_ENERGY);
         check(mmadmm_energy(ctx, &I), "mmadmm_energy");
         return I;
     }
-    // src/Mesh.cpp:1016-1036: Vp <- x.  x lives on the device; the arguments are kept for the signature.
+    // src/Mesh.cpp:1016-1036: Vp <- x.  After a step the library has already queued the write-back (mmadmm_set_writeback in
+    // meshInit); the arguments are kept for the signature.
     void updateAfterStep(double dt, Eigen::VectorXd &xPrev, Eigen::VectorXd &x) {
         (void)dt; (void)xPrev; (void)x;
-        syncVp();
     }
-    // Vp is column-major (Eigen's default): the transposition runs on the device
-    void syncVp() { check(mmadmm_get_x_colmajor(ctx, Vp->data()), "mmadmm_get_x_colmajor"); }
+    // Vp <- x now, whole mesh (done(); also after Method 1 / 2 steps, which do not write back).  Vp is column-major (Eigen's
+    // default): the transposition runs on the device; a distributed context assembles the global vector first.
+    void syncVp() {
+        if (!distributed) { check(mmadmm_get_x_colmajor(ctx, Vp->data()), "mmadmm_get_x_colmajor"); return; }
+        std::vector<double> xg((size_t)Vp->rows() * D);
+        broadcast(OP_GETX);
+        check(mmadmm_get_x(ctx, xg.data()), "mmadmm_get_x");
+        for (int p = 0; p < Vp->rows(); p++) for (int l = 0; l < D; l++) (*Vp)(p, l) = xg[(size_t)p * D + l];
+    }
+    void fenceVp() { check(mmadmm_writeback_fence(ctx), "mmadmm_writeback_fence"); }
 
     // result writers, formats of src/Mesh.cpp:1049-1095
     void outputSimplices(const char *fname) {
@@ -147,6 +268,7 @@ public:
         }
     }
     void outputPoints(const char *fname) {
+        fenceVp();
         std::ofstream out(fname);
         for (int i = 0; i < Vp->rows(); i++) {
             for (int j = 0; j < D-1; j++) out << (*Vp)(i, j) << ", ";
@@ -154,6 +276,7 @@ public:
         }
     }
     void outputBoundaryNodes(const char *fname) {
+        fenceVp();
         std::ofstream out(fname);
         for (int i = 0; i < Vp->rows(); i++) {
             if (boundaryMask->at(i) == INTERIOR) continue;
@@ -165,8 +288,8 @@ public:
     // status code of the C ABI -> the reference's behaviour on a failed assert / exit(1): message + abort
     void check(int rc, const char *what) {
         if (rc == MMADMM_OK) return;
-        static const char *names[] = {"OK", "EINVAL", "ECUDA", "EINVERTED", "ESINGULAR", "ENCCL", "ENODEVICE"};
-        cerr << "mm-admm_b200: " << what << " failed: " << (rc >= 0 && rc <= 6 ? names[rc] : "?")
+        static const char *names[] = {"OK", "EINVAL", "ECUDA", "EINVERTED", "ESINGULAR", "ENCCL", "ENODEVICE", "EPEER"};
+        cerr << "mm-admm_b200: " << what << " failed: " << (rc >= 0 && rc <= 7 ? names[rc] : "?")
              << (ctx && mmadmm_last_error(ctx) ? string(" -- ") + mmadmm_last_error(ctx) : string()) << endl;
         if (rc == MMADMM_ENODEVICE) cerr << "mm-admm_b200: no CUDA device; this build has no CPU path" << endl;
         abort();
@@ -188,6 +311,8 @@ public:
     double w = 0;
     int nPnts = 0;
     double Ihcur = 0, Ihprev = 0;
+    bool distributed = false;
+    std::vector<Worker> workers;
 
 private:
     bool vpRegistered = false;

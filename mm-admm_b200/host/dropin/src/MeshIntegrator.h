@@ -23,6 +23,7 @@ public:
         this->dtPrev = dt;
         stepsTaken = 0;
         proxTime = cgTime = multTime = predTime = 0;
+        a.broadcast(Mesh<D>::OP_SETDT, 0, dt);
         a.check(mmadmm_set_dt(a.ctx, dt), "mmadmm_set_dt");   // diagonal of t = M + dt^2 (WD)^T(WD), :45-51
         a.check(mmadmm_set_option(a.ctx, "timing", 1), "mmadmm_set_option");
     }
@@ -32,6 +33,7 @@ public:
     double step(int nIters, double tol) {
         double Ih = 0, primal = 0, dual = 0;
         int iters = 0;
+        a->broadcast(Mesh<D>::OP_STEP, nIters, tol);
         a->check(mmadmm_step(a->ctx, nIters, tol, &Ih, &iters, &primal, &dual), "mmadmm_step");
         lastIters = iters; lastPrimal = primal; lastDual = dual;
         a->stepTaken = true;
@@ -50,6 +52,7 @@ public:
     double eulerStep(double tol) {
         (void)tol;
         double Ih = 0;
+        a->broadcast(Mesh<D>::OP_EULER);
         a->check(mmadmm_euler_step(a->ctx, &Ih), "mmadmm_euler_step");
         return Ih;
     }
@@ -60,11 +63,12 @@ public:
         return Ih;
     }
     double getEnergy() { return a->computeEnergy(xUnused); }
-    void done() { a->updateAfterStep(dt, xPrevUnused, xUnused); }
+    void done() { a->syncVp(); }
 
     // x / z writers (src/MeshIntegrator.cpp:217-243); x is read back from the device
     void outputX(const char *fname) {
         std::vector<double> x((size_t)a->getNPnts() * D);
+        a->broadcast(Mesh<D>::OP_GETX);
         a->check(mmadmm_get_x(a->ctx, x.data()), "mmadmm_get_x");
         std::ofstream out(fname);
         for (int i = 0; i < a->getNPnts(); i++) {
@@ -74,6 +78,7 @@ public:
     }
     void outputZ(const char *fname) {
         const int n = D*(D+1), E = a->F->rows();
+        if (a->distributed) { cerr << "mm-admm_b200: outputZ is not available on a multi-GPU run (element state stays on its rank)" << endl; return; }
         std::vector<double> z((size_t)E * n);
         a->check(mmadmm_get_state(a->ctx, MMADMM_STATE_Z, z.data()), "mmadmm_get_state");
         std::ofstream out(fname);

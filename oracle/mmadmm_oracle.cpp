@@ -1038,6 +1038,10 @@ void *orc_create(int D, int P, int E, const double *Vp, const double *Vc, const 
     return o;
 }
 void orc_destroy(void *h) { delete (Oracle *)h; }
+// Deep copy of the whole state (bench.py: every timed epoch restarts from the same post-warm-up snapshot instead of
+// repeating the warm-up steps) and the OpenMP thread count of the prox loop (src/Mesh.cpp:429,437 omp_set_num_threads).
+void *orc_clone(void *h) { return new Oracle(*(Oracle *)h); }
+void orc_set_threads(void *h, int nthreads) { ((Oracle *)h)->nthreads = nthreads > 0 ? nthreads : 1; }
 
 int orc_step(void *h, int nIters, double tol, double *Ih, int *iters, double *primal, double *dual) {
     Oracle &o = *(Oracle *)h;

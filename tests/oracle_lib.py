@@ -40,6 +40,9 @@ def lib():
         L.orc_create.argtypes = [C.c_int, C.c_int, C.c_int, c_dp, c_dp, c_ip, c_ip, c_dp,
                                  C.c_double, C.c_double, C.c_double, C.c_int, C.c_int]
         L.orc_destroy.argtypes = [C.c_void_p]
+        L.orc_clone.restype = C.c_void_p
+        L.orc_clone.argtypes = [C.c_void_p]
+        L.orc_set_threads.argtypes = [C.c_void_p, C.c_int]
         L.orc_step.restype = C.c_int
         L.orc_step.argtypes = [C.c_void_p, C.c_int, C.c_double, c_dp, c_ip, c_dp, c_dp]
         L.orc_euler_step.restype = C.c_int
@@ -117,6 +120,16 @@ class Oracle:
         if getattr(self, "h", None):
             self.L.orc_destroy(self.h)
             self.h = None
+
+    def clone(self):
+        """Deep copy of the whole oracle state (mesh, monitor grid, integrator vectors, inverse Hessians, counters)."""
+        import copy
+        other = copy.copy(self)
+        other.h = self.L.orc_clone(self.h)
+        return other
+
+    def set_threads(self, nthreads):
+        self.L.orc_set_threads(self.h, int(nthreads))
 
     def step(self, n_iters, tol=1e-3):
         Ih = C.c_double(); it = C.c_int(); pr = C.c_double(); du = C.c_double()

@@ -104,3 +104,27 @@ def test_reference_driver_level_set_mesh_aborts_like_the_reference(tmp_path):
     assert r.returncode != 0 and "EINVERTED" in r.stderr
     phi = np.loadtxt(wd / "Experiments" / "Results" / "ls" / "phi.txt", delimiter=",")
     assert phi.shape == (25 * 25, 3)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name,nsteps,wb", [("Monitor210", 12, "deferred"), ("Monitor210", 12, "strict"), ("3DMonitor210", 5, "deferred")])
+def test_reference_driver_final_points_match_oracle(tmp_path, name, nsteps, wb, monkeypatch):
+    """points.txt written by the reference's driver after done() (main.cpp:225-236: Mesh::outputPoints of the caller's Vp, which
+    the library refreshed through its column-major write-back) equals the oracle's final node positions at the 6 printed digits,
+    with the per-step write-back overlapped (default) or strict (MMADMM_WRITEBACK=strict)."""
+    if not os.path.exists(EXE):
+        pytest.skip("build/dropin/mesh.exe not built")
+    import numpy as np
+    import oracle_lib as O
+    from test_oracle_kat import build_from_input
+    monkeypatch.setenv("MMADMM_WRITEBACK", wb)
+    spec, out, ih, stdout = run_driver(tmp_path, name, nsteps)
+    orc, _ = build_from_input(name, GOLD, nthreads=4)
+    for _ in range(nsteps):
+        assert orc.step(spec["AdmmIter"], 1e-3)["status"] == 0
+    xo = orc.x()
+    pts = np.array([[float(w) for w in ln.split(",")] for ln in open(out / "points.txt").read().split("\n") if ln.strip()])
+    assert pts.shape == xo.shape
+    want = np.array([[float("%g" % v) for v in row] for row in xo])
+    assert np.abs(pts - want).max() <= 1e-6 * np.abs(want).max()      # one unit of the 6th printed digit at most
+    assert (pts == want).mean() > 0.999

@@ -1,5 +1,5 @@
 """Full-size runs (BASELINE.json configs 1 and 3: 4.19 M triangles / 6.14 M tetrahedra) checked through size-independent
-properties, since the CPU oracle cannot finish these sizes in seconds:
+properties.  (The side-by-side comparison with the CPU oracle at these sizes is tests/test_gpu_parity_large.py.)
 
 * fixed point: with the identity monitor the uniform 2D box mesh is an equilibrium of Huang's functional (every vertex
   star is symmetric), so ADMM steps must leave every node where it is and the energy unchanged;

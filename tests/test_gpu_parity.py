@@ -147,20 +147,35 @@ def test_boundary_free_and_comp_mesh_and_graduse():
 
 
 def test_inverted_element_is_reported():
+    """det(E) <= 0 is where the reference asserts (src/AdaptationFunctional.cpp:174): the library must answer MMADMM_EINVERTED
+    (status word -> error code), the oracle status 1, from every entry point that evaluates the functional."""
     Vp, F, mask = mm.generate_uniform_rect_mesh(2, 4, 4)
     mon = mm.TestMonitor(2, 0).evaluate_at_vertices(Vp)
-    mesh = mm.Mesh(Vp, F, mask, mon, rho=50.0, tau=0.5)
+    # (a) a degenerate element by construction: the first cell-centre vertex moved onto the cell's bottom edge => det(E) == 0
+    #     exactly for the element on that edge (re-orientation only flips det < 0, src/Mesh.cpp:253-257)
+    Vp2 = Vp.copy()
+    c = (4 + 1) * (4 + 1)
+    Vp2[c] = [0.125, 0.0]
+    mesh2 = mm.Mesh(Vp2, F.copy(), mask, mon, rho=50.0, tau=0.5)
+    s2 = mm.MeshIntegrator(0.025, mesh2)
+    with pytest.raises(mm.MMADMMError, match="EINVERTED"):
+        s2.getEnergy()
+    with pytest.raises(mm.MMADMMError, match="EINVERTED"):
+        s2.step(10, 1e-3)
+    orc2 = O.Oracle(Vp2, F.copy(), mask, mon, 50.0, 0.5, 0.025)
+    assert orc2.step(10, 1e-3)["status"] == 1
+    s2.close()
+    # (b) a valid mesh stays clean, and probing an inverted simplex through the unit-test entry point (legal there: it resets
+    #     the status word) must not poison the context
+    mesh = mm.Mesh(Vp.copy(), F.copy(), mask, mon, rho=50.0, tau=0.5)
     solver = mm.MeshIntegrator(0.025, mesh)
     z = Vp[mesh.F[:4]].reshape(4, -1).copy()
-    z[0, 2:4], z[0, 4:6] = z[0, 4:6].copy(), z[0, 2:4].copy()  # flip orientation
-    en, _, _ = solver.block_grad(z)
-    assert not np.isfinite(en[0]) or en[0] != en[0] or True  # value is meaningless; the status path is what matters
-    # a mesh whose element is inverted by construction must fail like the reference's assert
-    Vp2 = Vp.copy(); c = (4 + 1) * (4 + 1)  # first cell-centre vertex
-    Vp2[c] = [-0.3, -0.3]
-    mesh2 = mm.Mesh(Vp2, mm.generate_uniform_rect_mesh(2, 4, 4)[1], mask, mon, rho=50.0, tau=0.5)
-    s2 = mm.MeshIntegrator(0.025, mesh2)   # reOrient flips the damaged elements, so energy is still defined
-    s2.getEnergy()
+    z[0, 2:4], z[0, 4:6] = z[0, 4:6].copy(), z[0, 2:4].copy()  # flip the orientation of element 0
+    solver.block_grad(z)
+    e0 = solver.getEnergy()
+    assert np.isfinite(e0)
+    solver.step(10, 1e-3)
+    solver.close()
 
 
 @pytest.mark.parametrize("N,kind", [(12, 5), (24, 1)])
@@ -290,3 +305,71 @@ def test_3d_free_boundary_comp_mesh_and_graduse(btype, kind):
         ill = btype == 0 and "Vc" not in kw
         assert rel(mesh.Vp, orc.x()) < (1e-7 if ill else TOL_E2E)
         solver.close()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("D,nx,kind", [(2, 32, 4), (3, 6, 3)])
+def test_checkpoint_restore_continues_bit_identically(D, nx, kind):
+    """mmadmm_checkpoint / mmadmm_restore (include/mmadmm.h): the continuation after a restore is bit-identical to the original
+    continuation, statistics included -- also when the restore follows a breakdown of the run (status word cleared)."""
+    Vp, F, mask = mm.generate_uniform_rect_mesh(D, nx, nx, nx if D == 3 else 0)
+    mon = mm.TestMonitor(D, kind).evaluate_at_vertices(Vp)
+    mesh = mm.Mesh(Vp.copy(), F.copy(), mask, mon, rho=50.0, tau=0.5)
+    s = mm.MeshIntegrator(0.025, mesh)
+    with pytest.raises(mm.MMADMMError):
+        s.restore()                       # nothing to restore yet
+    for _ in range(3):
+        s.step(10, 1e-3)
+    s.checkpoint()
+    runs = []
+    for rep in range(3):
+        if rep:
+            s.restore()
+        out = [(s.step(10, 1e-3), s.last["iters"], s.last["primal"], s.last["dual"]) for _ in range(4)]
+        runs.append((out, mesh.Vp.copy(), s.state(0), s.state(1), s.state(2), s.stats()["bfgs_hist"].copy(), s.getEnergy()))
+        if rep == 1 and D == 2:           # run on into the breakdown of the reference algorithm on this workload (MEx4, outer
+            with pytest.raises(mm.MMADMMError, match="EINVERTED"):     # step ~15, test_reference_breakdown_is_reproduced)
+                for _ in range(30):
+                    s.step(10, 1e-3)
+    for r in runs[1:]:
+        assert r[0] == runs[0][0] and r[6] == runs[0][6]
+        for a, b in zip(r[1:6], runs[0][1:6]):
+            assert np.array_equal(a, b)
+    s.close()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("D,nx,kind", [(2, 48, 3), (3, 6, 3)])
+def test_deferred_writeback_equals_strict(D, nx, kind):
+    """Mesh::updateAfterStep (Vp <- x after every step, src/Mesh.cpp:1030-1035) as mmadmm_set_writeback: strict = landed when step()
+    returns; deferred = overlapped with the next step, valid after a fence; off = done() only.  Same numbers every way."""
+    Vp, F, mask = mm.generate_uniform_rect_mesh(D, nx, nx, nx if D == 3 else 0)
+    mon = mm.TestMonitor(D, kind).evaluate_at_vertices(Vp)
+    res = {}
+    for mode in (True, "deferred", False):
+        mesh = mm.Mesh(Vp.copy(), F.copy(), mask, mon, rho=50.0, tau=0.5)
+        s = mm.MeshIntegrator(0.025, mesh, sync_vp=mode)
+        per_step = []
+        for k in range(5):
+            s.step(10, 1e-3)
+            if mode == "deferred":
+                s.fence()
+            if mode:
+                assert np.array_equal(mesh.Vp, s.x()), (mode, k)
+            per_step.append(s.x())
+        if not mode:
+            assert np.array_equal(mesh.Vp, Vp)            # untouched until done()
+        if mode == "deferred":                            # without a fence per step: the last state must land by done() / fence()
+            for k in range(3):
+                s.step(10, 1e-3)
+            s.fence()
+            assert np.array_equal(mesh.Vp, s.x())
+        else:
+            for k in range(3):
+                s.step(10, 1e-3)
+        s.done()
+        res[mode] = (per_step, mesh.Vp.copy())
+        s.close()
+    for mode in ("deferred", False):
+        assert all(np.array_equal(a, b) for a, b in zip(res[mode][0], res[True][0]))
+        assert np.array_equal(res[mode][1], res[True][1])

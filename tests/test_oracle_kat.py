@@ -50,6 +50,38 @@ def test_energy_trace_matches_reference(name, nsteps, nthreads, golden_dir):
         assert fmt6(g) == e, f"{name} step {i}: oracle {g!r} vs reference {e}"
 
 
+@pytest.mark.parametrize("name,max_steps", [("Monitor2160", None), ("3DMonitor220", None), ("Monitor2320", 40)])
+def test_large_committed_traces_match_reference_including_run_length(name, max_steps, golden_dir):
+    """The reference's large committed runs (SquareGrid 160^2 = 102,400 triangles, 162 lines; 3D 20^3 = 96,000 tets, 101 lines;
+    320^2 = 409,600 triangles, 327 lines -- the first 40 here, ALL of them on the GPU through mesh.exe in
+    tests/test_gpu_parity_large.py and, for the oracle, by tests/golden/check_full_traces.py): the driver loop of
+    main.cpp:180-209 with the shipped DtTol, so the step at which the run stops is pinned too."""
+    orc, spec = build_from_input(name, golden_dir, nthreads=os.cpu_count() or 1)
+    ref = TRACES[name]["Ih"]
+    got, prev = [orc.energy()], float("inf")
+    for i in range(spec["nSteps"] if max_steps is None else max_steps):
+        r = orc.step(spec["AdmmIter"], 1e-3)
+        assert r["status"] == 0
+        got.append(r["Ih"])
+        if i != 0 and abs((r["Ih"] - prev) / spec["dt"]) < spec["DtTol"]:     # main.cpp:203-206
+            break
+        prev = r["Ih"]
+    if max_steps is None:
+        assert len(got) == len(ref) == TRACES[name]["lines_committed"]
+    for i, (g, e) in enumerate(zip(got, ref)):
+        assert fmt6(g) == e, f"{name} step {i}: oracle {g!r} vs reference {e}"
+
+
+def test_oracle_clone_is_a_deep_copy(golden_dir):
+    a, spec = build_from_input("Monitor210", golden_dir, 1)
+    a.step(spec["AdmmIter"])
+    b = a.clone()
+    b.set_threads(3)
+    ra = [a.step(spec["AdmmIter"]) for _ in range(3)]
+    rb = [b.step(spec["AdmmIter"]) for _ in range(3)]
+    assert ra == rb and np.array_equal(a.x(), b.x()) and np.array_equal(a.hess(), b.hess())
+
+
 def test_oracle_threads_do_not_change_results(golden_dir):
     a, spec = build_from_input("Monitor210", golden_dir, 1)
     b, _ = build_from_input("Monitor210", golden_dir, 4)
