@@ -454,7 +454,7 @@ def run_workload(env, args, wl, K, W, cpu_baseline):
         "steps_per_sec": K / (r["ms"] / 1e3), "admm_iters_per_sec": r["iters"] / (r["ms"] / 1e3),
         "admm_iters": r["iters"], "mean_bfgs_iters_per_element_prox": kbar,
         "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": Ploc * D * 8 + 32,
-                "ms_per_step": r2["ms"] / K,
+                "ms_per_step": r2["ms"] / K, "phase_ms_per_step": {k: v[0] / K for k, v in r2["timing"].items()},
                 "strict": {"value": e2e_strict, "ms_per_step": r3["ms"] / K,
                            "note": "write-back fenced after every step (the reference's updateAfterStep semantics)"},
                 "writeback_verified": wb_ok,

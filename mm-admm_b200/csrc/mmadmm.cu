@@ -21,6 +21,7 @@
 #include <vector>
 
 #include <dlfcn.h>
+#include <time.h>
 
 #include "../../include/mmadmm.h"
 #include "mmadmm_device.cuh"
@@ -124,10 +125,10 @@ template <int D> __global__ void k_inc_pairs(int E, const int *F0, const int *F1
         vals[(size_t)e * (D + 1) + v] = e * 4 + v;
     }
 }
-__global__ void k_fill_identity(size_t Es, int n, double *B) {
+template <int D> __global__ void k_fill_identity(size_t Es, double *B) {
     size_t e = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (e >= Es) return;
-    for (int k = 0; k < n; k++) B[tm_index(e, k * n + k, n * n)] = 1.0;
+    for (int k = 0; k < D * (D + 1); k++) B[b_index<D>(e, k, k)] = 1.0;
 }
 __global__ void k_scatter_owned(int P, int D, const int *verts, const uint8_t *owner, const double *x, double *xg) {
     int p = blockIdx.x * blockDim.x + threadIdx.x;
@@ -412,7 +413,7 @@ template <int D> __global__ void __launch_bounds__(TPB) k_hess_init(ElemArgs<D> 
             for (int j = i + 1; j < n; j++) s -= H[i * n + j] * y[j];
             y[i] = s / H[i * n + i];
         }
-        for (int i = 0; i < n; i++) a.B[tm_index(e, i * n + c, n * n)] = y[i];
+        for (int i = 0; i < n; i++) a.B[b_index<D>(e, i, c)] = y[i];
     }
 }
 
@@ -542,136 +543,146 @@ __global__ void __launch_bounds__(TPB_, MINB) k_prox(ElemArgs<D> a) {
     if (tid < TPB_ / TILE) bulk_wait_read0();   // shared memory must stay allocated until the bulk stores have read it
 }
 
-// Vertex-warp form of the prox kernel (the default for D = 3).  One CTA of D+1 warps owns one tile of 32 elements:
-// warp q is vertex q of all 32 elements, lane = element.  A thread holds only its vertex's D components of every BFGS
-// vector (z, DXpU, Gk, pk, yk, B*yk) and works on rows D*q .. D*q+D-1 of the element's inverse Hessian, which sits in
-// shared memory as [row*n+col][lane] (conflict-free for every access below; one TMA bulk copy each way).  What the other
-// vertices hold travels through small [component][lane] exchange buffers between CTA barriers.  The part of blockGrad after
-// the monitor lookups is evaluated redundantly by every warp (it needs all of z); the lookups themselves, the three passes
-// over B and all loads/stores are split D+1 ways.  Compared with the thread-per-element form in 3D (255 registers, 2.8 KB of
-// spills per thread, 31.8 GB of local-memory traffic per launch on C4, 6 warps per SM) nothing spills and 12 warps fit.
-template <int D, bool COMP, bool ISO, int MINB>
-__global__ void __launch_bounds__((D + 1) * 32, MINB) k_prox_vw(const __grid_constant__ ElemArgs<D> a) {
-    constexpr int n = D * (D + 1), NN = n * n, NV = D + 1, DD = D * D;
-    constexpr int MS = ISO ? 1 : DD;                  // doubles per vertex lookup
+// The 3D prox kernel (D = 3: n = 12, a 12 x 12 inverse Hessian = 1152 bytes per tet).  Thread-per-element cannot work here -- the
+// eight 12-vectors of the BFGS update plus blockGrad's 3x3 temporaries need ~300 registers -- so every element gets FOUR lanes,
+// one per vertex: a warp owns a sub-tile of 8 elements, lane = el + 8 q (el = element of the sub-tile, q = vertex).  A thread
+// keeps its vertex's D components of every BFGS vector and works on rows 3q..3q+2 of its element's inverse Hessian, which sits
+// in the warp's shared memory as [entry][8] (one contiguous 9216-byte block per sub-tile in HBM: one TMA bulk copy each way,
+// SASS UBLKCP; layout b3_pos, mmadmm_device.cuh).  What the other three vertices hold arrives by warp shuffles.  There is no CTA
+// barrier and no shared-memory exchange buffer: warps are independent, persistent, and software-pipelined like the 2D kernel --
+// the own-vertex inputs of the next sub-tile (x gather, u, z, mask byte) are fetched by per-thread cp.async while this one is
+// solved, the connectivity two sub-tiles ahead, and the sub-tile's inverse Hessians land while the entry gradient is evaluated.
+// The part of blockGrad after the monitor lookups is evaluated by all four lanes of an element (it needs all of z); each lane
+// forms only its own vertex's block of the gradient (block_grad_own_iso).
+// (Round 1's k_prox_vw gave a CTA of four vertex WARPS one 32-element tile and paid four CTA barriers per BFGS iteration:
+// 3.81 ms on C4; this form: see DESIGN.md 3.2.)
+template <bool COMP, bool ISO, int WPB, int MINB>
+__global__ void __launch_bounds__(WPB * 32, MINB) k_prox_q(const __grid_constant__ ElemArgs<3> a) {
+    constexpr int D = 3, n = 12, NN = 144, NV = 4, DD = 9;
+    constexpr unsigned FULL = 0xffffffffu;
+    constexpr int WARP_DOUBLES = NN * SUB3 + (COMP ? 4 : 3) * D * 32;           // B sub-tile | next x | next u | next z | (next Vc)
+    constexpr int WARP_BYTES = WARP_DOUBLES * 8 + 2 * 32 * 4 + 16;                // + connectivity slot, mask-word slot, mbarrier
     extern __shared__ __align__(128) unsigned char smem_raw[];
-    double *Bs = reinterpret_cast<double *>(smem_raw);     // [NN][32]
-    double *Zs = Bs + NN * 32;                             // [n][32]  z
-    double *Gs = Zs + n * 32;                              // [n][32]  Gk
-    double *Ps = Gs + n * 32;                              // [n][32]  pk
-    double *Ys = Ps + n * 32;                              // [n][32]  yk
-    double *YB = Ys + n * 32;                              // [n][32]  yk^T B
-    double *Ms = YB + n * 32;                              // [NV][MS][32]  monitor lookups
-    double *Sc = Ms + NV * MS * 32;                        // [NV][3][32]  per-vertex partial sums: |G1|, pk.yk, yk.B yk
-    double *Xn = Sc + NV * 3 * 32;                         // [n][32]  next tile: x gather   (thread-private slots, cp.async)
-    double *Un = Xn + n * 32;                              // [n][32]  next tile: u
-    double *Zn = Un + n * 32;                              // [n][32]  next tile: z
-    int *Vn = reinterpret_cast<int *>(Zn + n * 32);        // [NV][32] ints  connectivity of the tile after next
-    int *Fn = Vn + NV * 32;                                // [NV][32] ints  next tile: the word of fixedBits that holds the element's byte
-    double *red = reinterpret_cast<double *>(Fn + NV * 32);   // 32
-    uint64_t *bar = reinterpret_cast<uint64_t *>(red + 32);
-    int *shist = reinterpret_cast<int *>(bar + 2);         // 52
-    const int tid = threadIdx.x, lane = tid & 31, q = tid >> 5;
-    const int nTiles = (a.E + 31) >> 5;
-    if (tid == 0) mbar_init(bar, 1);
-    if (a.hist && tid < 52) shist[tid] = 0;
-    __syncthreads();
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int el = lane & 7, q = lane >> 3;
+    unsigned char *wbase = smem_raw + (size_t)warp * ((WARP_BYTES + 127) / 128 * 128);
+    double *Bs = reinterpret_cast<double *>(wbase);           // [144][8]
+    double *Xn = Bs + NN * SUB3;                               // [3][32]  thread-private slots
+    double *Un = Xn + D * 32;
+    double *Zn = Un + D * 32;
+    double *Cn = Zn + D * 32;                                  // COMP only
+    int *Vn = reinterpret_cast<int *>(Bs + WARP_DOUBLES);      // [32] own vertex id of the sub-tile after next
+    int *Fn = Vn + 32;                                         // [32] the word of fixedBits that holds the element's byte
+    uint64_t *barB = reinterpret_cast<uint64_t *>(Fn + 32);
+    const int gw = blockIdx.x * WPB + warp, GW = gridDim.x * WPB;
+    const int nSub = (a.E + SUB3 - 1) / SUB3;
+    if (lane == 0) mbar_init(barB, 1);
+    __syncwarp();
 
-    // Inputs of a tile (own vertex: x gather, u, z) are fetched one tile ahead by per-thread cp.async into thread-private
-    // shared-memory slots, the connectivity two tiles ahead into a register: no global-load latency at the head of a tile.
-    auto prefetch = [&](int tile, int vid) {
-        const int e = tile * 32 + lane;
-        if (e < a.E) {
+    // own rows of the element's B, all columns: entry (3q+rl, c) at ((3q+rl)*12 + (c ^ (q&1)))*8 + el
+    const int qodd = q & 1;
+    const double *rowE = Bs + (size_t)(3 * q) * 12 * SUB3 + el + (qodd ? SUB3 : 0);    // even c
+    const double *rowO = Bs + (size_t)(3 * q) * 12 * SUB3 + el - (qodd ? SUB3 : 0);    // odd c
+#define BROW(rl, c) ((((c) & 1) ? rowO : rowE)[((rl) * 12 + (c)) * SUB3])
+    // own columns, all rows: entry (r, 3q+cl) at (r*12 + ((3q+cl) ^ ((r/3)&1)))*8 + el
+    const double *colE = Bs + (size_t)(3 * q) * SUB3 + el;                              // rows of even vertices; + cl*8
+    int coff[D];
 #pragma unroll
-            for (int l = 0; l < D; l++) {
-                const int s = (D * q + l) * 32 + lane;
-                cp_async8(Xn + s, a.x + (size_t)D * vid + l);
-                if (!a.uZero) cp_async8(Un + s, a.u + tm_index(e, D * q + l, n));
-                if (a.zsrc) cp_async8(Zn + s, a.zsrc + (size_t)D * vid + l);
-                else cp_async8(Zn + s, a.z + tm_index(e, D * q + l, n));
-            }
-            cp_async4(Fn + q * 32 + lane, reinterpret_cast<const int *>(a.fixedBits) + (e >> 2));
-        }
-    };
-    auto prefetch_vid = [&](int tile) {     // connectivity of `tile` into this thread's slot
-        const int e = tile * 32 + lane;
-        if (tile < nTiles && e < a.E) cp_async4(Vn + q * 32 + lane, a.F[q] + e);
-    };
-    int tile = blockIdx.x;
-    if (tile < nTiles) {
-        const int e0 = tile * 32 + lane;
-        prefetch(tile, e0 < a.E ? __ldg(a.F[q] + e0) : 0);
-        prefetch_vid(tile + gridDim.x);
-        cp_async_commit();
-    }
-    double ihAcc = 0.0, dualAcc = 0.0;     // meaningful in thread 0
-    for (int it = 0; tile < nTiles; tile += gridDim.x, it++) {
-        const int e = tile * 32 + lane;
-        const bool active = e < a.E;
-        if (tid == 0) {
-            if (it > 0) bulk_wait_read0();     // the previous tile's store has finished reading Bs
-            mbar_expect_tx(bar, (unsigned)(NN * 32 * sizeof(double)));
-            bulk_g2s(Bs, a.B + (size_t)tile * NN * 32, (unsigned)(NN * 32 * sizeof(double)), bar);
-        }
-        double zo[D], dxo[D], zprev[D], Gk[D], xi[COMP ? n : 1];
-        bool inv = false;
-        cp_async_wait_all();
+    for (int cl = 0; cl < D; cl++) coff[cl] = ((3 * q + cl) ^ 1) * SUB3 + el;            // rows of odd vertices
+#define BCOL(r, cl) (((((r) / 3) & 1) ? (Bs + coff[cl]) : (colE + (cl) * SUB3))[(r) * 12 * SUB3])
+
+    auto prefetch = [&](int t, int vid) {   // own-vertex inputs of sub-tile t (planes and F are padded to whole tiles: always in bounds)
+        const int e = t * SUB3 + el;
 #pragma unroll
         for (int l = 0; l < D; l++) {
-            const int s = (D * q + l) * 32 + lane;
-            zo[l] = active ? Zn[s] : 0.0;
-            dxo[l] = active ? (a.uZero ? Xn[s] : Xn[s] + Un[s]) : 0.0;
-            zprev[l] = zo[l];
-            Gk[l] = 0.0;
+            const int sl = l * 32 + lane;
+            cp_async8(Xn + sl, a.x + (size_t)D * vid + l);
+            if (!a.uZero) cp_async8(Un + sl, a.u + tm_index(e, D * q + l, n));
+            if (a.zsrc) cp_async8(Zn + sl, a.zsrc + (size_t)D * vid + l);
+            else cp_async8(Zn + sl, a.z + tm_index(e, D * q + l, n));
+            if (COMP) cp_async8(Cn + sl, a.Vc + (size_t)D * vid + l);
         }
-        const bool ownFixed = active && (((unsigned)Fn[q * 32 + lane] >> (8 * (e & 3) + q)) & 1u);
-        const int vidNext = Vn[q * 32 + lane];
-        if (COMP && active) {
+        cp_async4(Fn + lane, reinterpret_cast<const int *>(a.fixedBits) + (e >> 2));
+    };
+    auto prefetch_vid = [&](int t) {
+        if (t < nSub) cp_async4(Vn + lane, a.F[q] + (size_t)t * SUB3 + el);
+    };
+    // the D components every vertex of the element holds -> all n of them (vertex-major), by shuffles
+    auto all_of = [&](const double *own, double *all) {
 #pragma unroll
-            for (int v = 0; v < NV; v++) gather_vertex<D>(a.Vc, __ldg(a.F[v] + e), xi + D * v);
+        for (int v = 0; v < NV; v++)
+#pragma unroll
+            for (int l = 0; l < D; l++) all[D * v + l] = __shfl_sync(FULL, own[l], el + 8 * v);
+    };
+    auto sum4 = [&](double part) {   // sum over the element's vertices in the order v = 0..3 (identical on its four lanes)
+        double sacc = __shfl_sync(FULL, part, el);
+#pragma unroll
+        for (int v = 1; v < NV; v++) sacc += __shfl_sync(FULL, part, el + 8 * v);
+        return sacc;
+    };
+
+    int t = gw;
+    if (t < nSub) {
+        prefetch(t, __ldg(a.F[q] + (size_t)t * SUB3 + el));
+        prefetch_vid(t + GW);
+    }
+    cp_async_commit();
+    double ihAcc = 0.0, dualAcc = 0.0;
+    for (int it = 0; t < nSub; t += GW, it++) {
+        const int e = t * SUB3 + el;
+        const bool active = e < a.E;
+        if (lane == 0) {   // this sub-tile's inverse Hessians, once the previous store has drained out of shared memory
+            bulk_wait_read0();
+            mbar_expect_tx(barB, (unsigned)(NN * SUB3 * sizeof(double)));
+            bulk_g2s(Bs, a.B + (size_t)t * NN * SUB3, (unsigned)(NN * SUB3 * sizeof(double)), barB);
         }
-        {   // next tile's inputs (the slots just read are this thread's own)
-            const int tn = tile + gridDim.x;
-            if (tn < nTiles) {
+        cp_async_wait_all();
+        double zo[D], dxo[D], zprev[D], Gk[D], xi[COMP ? n : 1];
+#pragma unroll
+        for (int l = 0; l < D; l++) {
+            const int sl = l * 32 + lane;
+            zo[l] = Zn[sl];
+            dxo[l] = a.uZero ? Xn[sl] : Xn[sl] + Un[sl];
+            zprev[l] = zo[l];
+        }
+        if (COMP) {
+            double co[D];
+#pragma unroll
+            for (int l = 0; l < D; l++) co[l] = Cn[l * 32 + lane];
+            all_of(co, xi);
+        }
+        const bool ownFixed = ((unsigned)Fn[lane] >> (8 * (e & 3) + q)) & 1u;
+        const int vidNext = Vn[lane];
+        {   // next sub-tile's inputs (the slots just read are this thread's own), connectivity of the one after
+            const int tn = t + GW;
+            if (tn < nSub) {
                 prefetch(tn, vidNext);
-                prefetch_vid(tn + gridDim.x);
+                prefetch_vid(tn + GW);
             }
             cp_async_commit();
         }
-        // own-vertex lookup + own z into the exchange buffers
-        auto publish_z = [&]() {
-#pragma unroll
-            for (int l = 0; l < D; l++) Zs[(D * q + l) * 32 + lane] = zo[l];
-            if (ISO) {
-                Ms[q * 32 + lane] = eval_monitor_iso<D>(a.mg, zo);
-            } else {
-                SMat<D> m;
-                eval_monitor<D>(a.mg, zo, m);
-#pragma unroll
-                for (int k = 0; k < DD; k++) Ms[(q * DD + k) * 32 + lane] = m.a[k];
-            }
-        };
-        // regularised, masked gradient of the own vertex at the published z (Mesh::computeBlockGrad, regularize = true);
-        // returns the un-regularised element energy
+        bool inv = false;
+        // regularised, masked gradient of the own vertex at z = (zo of the four lanes) (Mesh::computeBlockGrad, regularize = true);
+        // returns the un-regularised element energy.  Executed by all lanes (shuffles inside).
         auto own_gradient = [&](double *g) -> double {
-            double z[n], grad[n];
-#pragma unroll
-            for (int k = 0; k < n; k++) z[k] = Zs[k * 32 + lane];
-            SMat<D> mPre[ISO ? 1 : NV];
-            double mIso[ISO ? NV : 1];
-#pragma unroll
-            for (int v = 0; v < NV; v++) {
-                if (ISO) mIso[v] = Ms[v * 32 + lane];
-                else {
-#pragma unroll
-                    for (int k = 0; k < DD; k++) mPre[v].a[k] = Ms[(v * DD + k) * 32 + lane];
-                }
-            }
+            double z[n];
+            all_of(zo, z);
             double en;
-            if constexpr (ISO) {     // only the own vertex's block of the gradient is formed
+            if constexpr (ISO) {
+                const double mOwn = eval_monitor_iso<D>(a.mg, zo);
+                double mIso[NV];
+#pragma unroll
+                for (int v = 0; v < NV; v++) mIso[v] = __shfl_sync(FULL, mOwn, el + 8 * v);
                 en = block_grad_own_iso<D>(z, xi, COMP, mIso, a.fc, q, g, inv);
             } else {
-                en = block_grad_core<D, true, ISO>(z, xi, COMP, mPre, mIso, a.fc, grad, inv);
+                SMat<D> mOwn, mPre[NV];
+                eval_monitor<D>(a.mg, zo, mOwn);
+#pragma unroll
+                for (int v = 0; v < NV; v++)
+#pragma unroll
+                    for (int k = 0; k < DD; k++) mPre[v].a[k] = __shfl_sync(FULL, mOwn.a[k], el + 8 * v);
+                double grad[n], mDummy[1] = {0.0};
+                en = block_grad_core<D, true, false>(z, xi, COMP, mPre, mDummy, a.fc, grad, inv);
 #pragma unroll
                 for (int l = 0; l < D; l++) g[l] = 0.0;
 #pragma unroll
@@ -685,135 +696,113 @@ __global__ void __launch_bounds__((D + 1) * 32, MINB) k_prox_vw(const __grid_con
             for (int l = 0; l < D; l++) g[l] = ownFixed ? 0.0 : g[l] + a.fc.w2 * (-dxo[l] + zo[l]);
             return en;
         };
-        if (active) publish_z();
-        __syncthreads();
-        double ih = 0.0;
-        if (active) {
-            ih = own_gradient(Gk);     // Ihsave: energy at entry (identical on all D+1 warps)
-#pragma unroll
-            for (int l = 0; l < D; l++) Gs[(D * q + l) * 32 + lane] = Gk[l];
-        }
-        mbar_wait(bar, (unsigned)(it & 1));
-        __syncthreads();
+        const double ih = own_gradient(Gk);     // Ihsave: energy at entry (identical on the element's four lanes)
+        mbar_wait(barB, (unsigned)(it & 1));
         bool done = !active;
         int iters = 0;
-        const double *Brow = Bs + (size_t)(D * q) * n * 32 + lane;     // own rows: Brow[(rl*n + c)*32]
         for (int iter = 0; iter < 50; iter++) {
-            double pk[D], yk[D], By[D];
-            if (!done) {                      // pass 1: pk = -B Gk (own rows), step, publish
+            double pk[D], yk[D], By[D], yB[D], G1[D];
+            {   // pass 1: pk = -B Gk (own rows), full step
+                double Gall[n];
+                all_of(Gk, Gall);
 #pragma unroll
                 for (int rl = 0; rl < D; rl++) {
-                    double sacc = Brow[(rl * n) * 32] * Gs[lane];
+                    double sacc = BROW(rl, 0) * Gall[0];
 #pragma unroll
-                    for (int c = 1; c < n; c++) sacc += Brow[(rl * n + c) * 32] * Gs[c * 32 + lane];
+                    for (int c = 1; c < n; c++) sacc += BROW(rl, c) * Gall[c];
                     pk[rl] = -sacc;
                 }
-#pragma unroll
-                for (int l = 0; l < D; l++) { zo[l] += pk[l]; Ps[(D * q + l) * 32 + lane] = pk[l]; }
-                publish_z();
             }
-            __syncthreads();
-            if (!done) {                      // gradient at the new point, yk, partial sums
-                double G1[D];
-                own_gradient(G1);
-                double ix = 0.0, c2 = 0.0;
+            if (!done) {
 #pragma unroll
-                for (int l = 0; l < D; l++) {
-                    ix += fabs(G1[l]);
-                    yk[l] = G1[l] - Gk[l];
-                    Gk[l] = G1[l];
-                    c2 = (l == 0) ? pk[0] * yk[0] : c2 + pk[l] * yk[l];
-                    Ys[(D * q + l) * 32 + lane] = yk[l];
-                    Gs[(D * q + l) * 32 + lane] = G1[l];
-                }
-                Sc[(q * 3 + 0) * 32 + lane] = ix;
-                Sc[(q * 3 + 1) * 32 + lane] = c2;
+                for (int l = 0; l < D; l++) zo[l] += pk[l];
             }
-            __syncthreads();
-            bool conv = false;
-            if (!done) {                      // pass 2: B yk (own rows), yk^T B (own columns)
-                double yB[D];
+            own_gradient(G1);
+            double ixp = 0.0, c2p = 0.0;
+#pragma unroll
+            for (int l = 0; l < D; l++) {
+                ixp += fabs(G1[l]);
+                yk[l] = G1[l] - Gk[l];
+                c2p = (l == 0) ? pk[0] * yk[0] : c2p + pk[l] * yk[l];
+                if (!done) Gk[l] = G1[l];
+            }
+            {   // pass 2: B yk (own rows), yk^T B (own columns)
+                double Yall[n];
+                all_of(yk, Yall);
 #pragma unroll
                 for (int rl = 0; rl < D; rl++) {
-                    double sacc = Brow[(rl * n) * 32] * Ys[lane];
+                    double sacc = BROW(rl, 0) * Yall[0];
 #pragma unroll
-                    for (int c = 1; c < n; c++) sacc += Brow[(rl * n + c) * 32] * Ys[c * 32 + lane];
+                    for (int c = 1; c < n; c++) sacc += BROW(rl, c) * Yall[c];
                     By[rl] = sacc;
                 }
 #pragma unroll
                 for (int cl = 0; cl < D; cl++) {
-                    const double *Bcol = Bs + (size_t)(D * q + cl) * 32 + lane;   // Bcol[r*n*32]
-                    double sacc = Ys[lane] * Bcol[0];
+                    double sacc = Yall[0] * BCOL(0, cl);
 #pragma unroll
-                    for (int r = 1; r < n; r++) sacc += Ys[r * 32 + lane] * Bcol[(size_t)r * n * 32];
+                    for (int r = 1; r < n; r++) sacc += Yall[r] * BCOL(r, cl);
                     yB[cl] = sacc;
                 }
-                double yBy = yk[0] * By[0];
-#pragma unroll
-                for (int l = 1; l < D; l++) yBy += yk[l] * By[l];
-#pragma unroll
-                for (int l = 0; l < D; l++) YB[(D * q + l) * 32 + lane] = yB[l];
-                Sc[(q * 3 + 2) * 32 + lane] = yBy;
-                double Ix = Sc[lane];
-#pragma unroll
-                for (int v = 1; v < NV; v++) Ix += Sc[(v * 3) * 32 + lane];
-                conv = Ix < a.tol;
             }
-            const int more = __syncthreads_or((!done && !conv && iter + 1 < 50) ? 1 : 0);
-            if (!done) {                      // pass 3: rank-2 update of the own rows (src/Mesh.cpp:846-856)
-                double c2 = Sc[(1) * 32 + lane], yBy = Sc[(2) * 32 + lane];
+            double yByp = yk[0] * By[0];
 #pragma unroll
-                for (int v = 1; v < NV; v++) { c2 += Sc[(v * 3 + 1) * 32 + lane]; yBy += Sc[(v * 3 + 2) * 32 + lane]; }
-                const double ic2 = 1.0 / c2;
-                const double c1 = (c2 + yBy) * (ic2 * ic2);
-                double *Bw = Bs + (size_t)(D * q) * n * 32 + lane;
+            for (int l = 1; l < D; l++) yByp += yk[l] * By[l];
+            const double Ix = sum4(ixp), c2 = sum4(c2p), yBy = sum4(yByp);
+            const bool conv = Ix < a.tol;
+            {   // pass 3: rank-2 update of the own rows (src/Mesh.cpp:846-856)
+                double Pall[n], YBall[n];
+                all_of(pk, Pall);
+                all_of(yB, YBall);
+                if (!done) {
+                    const double ic2 = 1.0 / c2;
+                    const double c1 = (c2 + yBy) * (ic2 * ic2);
 #pragma unroll
-                for (int rl = 0; rl < D; rl++) {
-                    const double a1 = c1 * pk[rl], a3 = pk[rl] * ic2, a2 = By[rl] * ic2;
+                    for (int rl = 0; rl < D; rl++) {
+                        const double a1 = c1 * pk[rl], a3 = pk[rl] * ic2, a2 = By[rl] * ic2;
 #pragma unroll
-                    for (int c = 0; c < n; c++) {
-                        const double pc = Ps[c * 32 + lane];
-                        Bw[(rl * n + c) * 32] += (a1 * pc - a2 * pc) - a3 * YB[c * 32 + lane];
+                        for (int c = 0; c < n; c++) {
+                            double *bp = const_cast<double *>(&BROW(rl, c));
+                            *bp += (a1 * Pall[c] - a2 * Pall[c]) - a3 * YBall[c];
+                        }
                     }
+                    iters = iter + 1;
+                    if (conv) done = true;
                 }
-                iters = iter + 1;
-                if (conv) done = true;
             }
-            if (!more) break;
-            __syncthreads();   // pass 3 reads Ps / YB, the next pass 1 overwrites Ps (steady state: one iteration, never reached)
+            if (__all_sync(FULL, done)) break;
         }
-        double dual2 = 0.0;
+        int bin = -1;
         if (active) {
-            if (q == 0) {
-                if (inv) atomicOr(a.status, ST_INVERTED);
-                if (!done) atomicOr(a.status, ST_BFGS_MAX);
-                if (a.hist) atomicAdd(&shist[done ? iters : 51], 1);
-            }
+            if (inv) atomicOr(a.status, ST_INVERTED);
+            if (!done) atomicOr(a.status, ST_BFGS_MAX);
+            if (q == 0) { bin = done ? iters : 51; ihAcc += ih; }
 #pragma unroll
             for (int l = 0; l < D; l++) {
                 a.z[tm_index(e, D * q + l, n)] = zo[l];
                 a.u[tm_index(e, D * q + l, n)] = dxo[l] - zo[l];    // u = DXpU - z
                 const double dd = zo[l] - zprev[l];
-                dual2 += dd * dd;
+                dualAcc += dd * dd;
             }
         }
+        if (a.hist) {   // one atomic per distinct iteration count in the warp
+            const unsigned peers = __match_any_sync(FULL, bin);
+            if (bin >= 0 && lane == __ffs(peers) - 1) atomicAdd(&a.hist[bin], (unsigned long long)__popc(peers));
+        }
+        // updated sub-tile back to HBM: generic-proxy writes -> async proxy, then one bulk store
         fence_async_smem();
-        __syncthreads();
-        if (tid == 0) {
-            bulk_s2g(a.B + (size_t)tile * NN * 32, Bs, (unsigned)(NN * 32 * sizeof(double)));
+        __syncwarp();
+        if (lane == 0) {
+            bulk_s2g(a.B + (size_t)t * NN * SUB3, Bs, (unsigned)(NN * SUB3 * sizeof(double)));
             bulk_commit();
         }
-        const double s1 = block_sum(q == 0 ? ih : 0.0, red);
-        const double s2 = block_sum(dual2, red);
-        if (tid == 0) { ihAcc += s1; dualAcc += s2; }
     }
+#undef BROW
+#undef BCOL
     cp_async_wait_all();
-    if (tid == 0) { a.partIh[blockIdx.x] = ihAcc; a.partDual[blockIdx.x] = dualAcc; }
-    if (a.hist) {
-        __syncthreads();
-        if (tid < 52 && shist[tid]) atomicAdd(&a.hist[tid], (unsigned long long)shist[tid]);
-    }
-    if (tid == 0) bulk_wait_read0();   // shared memory must stay allocated until the last bulk store has read it
+    if (lane == 0) bulk_wait_read0();   // shared memory must stay allocated until the last store has read it
+    ihAcc = warp_sum(ihAcc);
+    dualAcc = warp_sum(dualAcc);
+    if (lane == 0) { a.partIh[gw] = ihAcc; a.partDual[gw] = dualAcc; }
 }
 
 // Persistent, software-pipelined form of the warp-tile prox kernel (the default for D = 2).  One warp walks tiles
@@ -1319,6 +1308,10 @@ template <int D> __global__ void k_iso_extract(size_t rows, const double *grid, 
     if (!ok) *flag = 0;
 }
 
+__global__ void k_copy(size_t n, const double *src, double *dst) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) dst[i] = src[i];
+}
 // x (P x D interleaved) -> column-major P x D (Eigen's default storage of the caller's Vp)
 __global__ void k_x_to_colmajor(int P, int D, const double *x, double *xT) {
     int p = blockIdx.x * blockDim.x + threadIdx.x;
@@ -1593,7 +1586,7 @@ struct mmadmm_ctx {
         cudaEvent_t evSnap[2] = {nullptr, nullptr}, evCopied[2] = {nullptr, nullptr};
         bool inFlight[2] = {false, false};
         int next = 0;
-        long long copies = 0;
+        long long copies = 0, hostNs = 0;
     } wb;
 
     double gridO[3] = {0, 0, 0}, gridRh[3] = {0, 0, 0};
@@ -2337,7 +2330,7 @@ int create_impl(mmadmm_ctx *ctx, const double *Vp, const double *Vc, const int *
     CK(cudaMalloc(&ctx->usum, sizeof(double) * (size_t)P * D));
     CK(cudaMemsetAsync(ctx->usum, 0, sizeof(double) * (size_t)P * D, st));
     CK(cudaMemsetAsync(ctx->B, 0, sizeof(double) * NZ * n, st));
-    k_fill_identity<<<cdiv(ctx->Es, 256), 256, 0, st>>>(ctx->Es, n, ctx->B);   // hessInvs = I (src/Mesh.cpp:456-464)
+    k_fill_identity<D><<<cdiv(ctx->Es, 256), 256, 0, st>>>(ctx->Es, ctx->B);   // hessInvs = I (src/Mesh.cpp:456-464)
     ctx->launches++;
     CK(cudaDeviceGetAttribute(&ctx->numSMs, cudaDevAttrMultiProcessorCount, ctx->device));
     ctx->nblkE = cdiv(E, TPB);
@@ -2406,6 +2399,11 @@ int wb_fence(mmadmm_ctx *ctx) {
 int wb_issue(mmadmm_ctx *ctx) {
     mmadmm_ctx::Writeback &w = ctx->wb;
     const int D = ctx->D, P = ctx->P;
+    struct HostTimer {   // MMADMM_DEBUG_WB=1: host time spent queueing the write-back, reported at destroy
+        mmadmm_ctx::Writeback &w; timespec t0;
+        HostTimer(mmadmm_ctx::Writeback &w_) : w(w_) { clock_gettime(CLOCK_MONOTONIC, &t0); }
+        ~HostTimer() { timespec t1; clock_gettime(CLOCK_MONOTONIC, &t1); w.hostNs += (t1.tv_sec - t0.tv_sec) * 1000000000ll + (t1.tv_nsec - t0.tv_nsec); }
+    } timer(w);
     const size_t bytes = sizeof(double) * (size_t)P * D;
     if (!w.copyStream) {
         CK(cudaStreamCreateWithFlags(&w.copyStream, cudaStreamNonBlocking));
@@ -2418,12 +2416,10 @@ int wb_issue(mmadmm_ctx *ctx) {
     const int b = w.next;
     w.next ^= 1;
     if (w.inFlight[b]) CK(cudaStreamWaitEvent(ctx->stream, w.evCopied[b], 0));   // two steps old: the stage is free again
-    if (w.colMajor) {
-        k_x_to_colmajor<<<cdiv(P, 256), 256, 0, ctx->stream>>>(P, D, ctx->x, w.stage[b]);
-        ctx->launches++;
-    } else {
-        CK(cudaMemcpyAsync(w.stage[b], ctx->x, bytes, cudaMemcpyDeviceToDevice, ctx->stream));
-    }
+    // snapshot by a kernel, not a copy-engine memcpy: the stream stays on the compute engine between two steps
+    if (w.colMajor) k_x_to_colmajor<<<cdiv(P, 256), 256, 0, ctx->stream>>>(P, D, ctx->x, w.stage[b]);
+    else k_copy<<<cdiv((size_t)P * D, 256), 256, 0, ctx->stream>>>((size_t)P * D, ctx->x, w.stage[b]);
+    ctx->launches++;
     CK(cudaEventRecord(w.evSnap[b], ctx->stream));
     CK(cudaStreamWaitEvent(w.copyStream, w.evSnap[b], 0));
     if (!ctx->dist) {
@@ -2497,29 +2493,27 @@ template <> int launch_prox<2>(mmadmm_ctx *ctx, const ElemArgs<2> &a) {
         default: return launch_prox_p<2, 2, 6, PF_PREFETCH_GRID>(ctx, a, 0);
     }
 }
-template <int D, int MINB> int launch_prox_vw(mmadmm_ctx *ctx, const ElemArgs<D> &a, int slot) {
-    constexpr int n = D * (D + 1);
+template <int WPB, int MINB> int launch_prox_q(mmadmm_ctx *ctx, const ElemArgs<3> &a, int slot) {
     const bool iso = a.mg.iso != nullptr;
-    const size_t smem = sizeof(double) * 32 * (size_t)(n * n + 8 * n + (D + 1) * (iso ? 1 : D * D) + (D + 1) * 3 + 1) + 16 + (52 + 64 * (D + 1)) * sizeof(int);
-    auto kern = ctx->compMesh ? (iso ? k_prox_vw<D, true, true, MINB> : k_prox_vw<D, true, false, MINB>)
-                              : (iso ? k_prox_vw<D, false, true, MINB> : k_prox_vw<D, false, false, MINB>);
+    const size_t warpBytes = ((size_t)(144 * SUB3 + (ctx->compMesh ? 4 : 3) * 3 * 32) * 8 + 2 * 32 * 4 + 16 + 127) / 128 * 128;
+    const size_t smem = warpBytes * WPB;
+    auto kern = ctx->compMesh ? (iso ? k_prox_q<true, true, WPB, MINB> : k_prox_q<true, false, WPB, MINB>)
+                              : (iso ? k_prox_q<false, true, WPB, MINB> : k_prox_q<false, false, WPB, MINB>);
     if (!ctx->smemAttrSet[slot + (iso ? 8 : 0)]) {
         CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         ctx->smemAttrSet[slot + (iso ? 8 : 0)] = true;
     }
-    const int grid = std::min(ctx->numSMs * MINB, cdiv(ctx->E, 32));    // persistent: each CTA walks tiles with this stride
-    kern<<<grid, (D + 1) * 32, smem, ctx->stream>>>(a);
-    ctx->nProxPart = grid;
+    const int grid = std::min(ctx->numSMs * MINB, cdiv(ctx->E, WPB * SUB3));    // persistent: each warp walks sub-tiles with this stride
+    kern<<<grid, WPB * 32, smem, ctx->stream>>>(a);
+    ctx->nProxPart = grid * WPB;
     ctx->launches++;
     return MMADMM_OK;
 }
 template <> int launch_prox<3>(mmadmm_ctx *ctx, const ElemArgs<3> &a) {
     switch (ctx->proxVariant) {
-        case 1: return launch_prox_t<3, 32, 6>(ctx, a, 1);
-        case 2: return launch_prox_t<3, 64, 3>(ctx, a, 2);     // thread per element (spills; kept for A/B runs)
-        case 3: return launch_prox_vw<3, 2>(ctx, a, 3);
-        case 4: return launch_prox_vw<3, 4>(ctx, a, 4);
-        default: return launch_prox_vw<3, 3>(ctx, a, 0);       // one warp per vertex, one CTA per 32-element tile
+        case 1: return launch_prox_q<2, 6>(ctx, a, 1);         // 2-warp CTAs
+        case 2: return launch_prox_q<4, 4>(ctx, a, 2);         // 16 warps per SM at 128 registers
+        default: return launch_prox_q<4, 3>(ctx, a, 0);        // 12 warps per SM
     }
 }
 
@@ -3225,7 +3219,11 @@ int mmadmm_get_state(mmadmm_ctx *ctx, int which, double *out) {
         std::vector<double> tmp(ctx->Es * planes);   // tile-major on the device -> element-major for the caller
         CK(cudaMemcpy(tmp.data(), src, sizeof(double) * tmp.size(), cudaMemcpyDeviceToHost));
         for (size_t e = 0; e < E; e++)
-            for (int k = 0; k < planes; k++) out[e * planes + k] = tmp[tm_index(e, k, planes)];
+            for (int k = 0; k < planes; k++) {
+                size_t src_i = tm_index(e, k, planes);
+                if (which == MMADMM_STATE_HESSINV) src_i = (ctx->D == 2) ? b_index<2>(e, k / n, k % n) : b_index<3>(e, k / n, k % n);
+                out[e * planes + k] = tmp[src_i];
+            }
         return MMADMM_OK;
     }
     if (which == MMADMM_STATE_XBAR || which == MMADMM_STATE_XPREV) {
@@ -3364,6 +3362,8 @@ void mmadmm_destroy(mmadmm_ctx *ctx) {
     cudaSetDevice(ctx->device);
     if (ctx->stream) cudaStreamSynchronize(ctx->stream);
     wb_fence(ctx);
+    if (getenv("MMADMM_DEBUG_WB") && ctx->wb.copies)
+        fprintf(stderr, "mmadmm: write-back: %lld copies, %.1f us of host time each to queue\n", ctx->wb.copies, ctx->wb.hostNs * 1e-3 / ctx->wb.copies);
     for (int b = 0; b < 2; b++) {
         cudaFree(ctx->wb.stage[b]);
         if (ctx->wb.evSnap[b]) cudaEventDestroy(ctx->wb.evSnap[b]);

@@ -21,6 +21,18 @@ __host__ __device__ __forceinline__ size_t tm_index(size_t e, int row, int rows)
     return ((e >> 5) * (size_t)rows + (size_t)row) * TILE + (e & 31);
 }
 
+// Inverse Hessians (n x n per element).  2D: tile-major like z / u ([tile of 32][n*n entries][32]).  3D: sub-tiles of 8 elements,
+// [sub-tile][144 entries][8], entry (row, col) at position row*12 + (col ^ ((row/3) & 1)): the 3D prox kernel gives every element
+// four lanes (one per vertex) that read different rows (or columns) of the same sub-tile at the same time, and this pairwise swap
+// of the columns in the rows of odd vertices spreads those four groups over both halves of the shared-memory banks (a sub-tile is
+// one contiguous 9216-byte block: one TMA bulk copy each way).
+constexpr int SUB3 = 8;
+__host__ __device__ __forceinline__ int b3_pos(int row, int col) { return row * 12 + (col ^ ((row / 3) & 1)); }
+template <int D> __host__ __device__ __forceinline__ size_t b_index(size_t e, int row, int col) {
+    if (D == 2) return tm_index(e, row * 6 + col, 36);
+    return ((e >> 3) * 144 + (size_t)b3_pos(row, col)) * SUB3 + (e & 7);
+}
+
 enum NodeTypeDev { NT_BOUNDARY_FREE = 0, NT_BOUNDARY_FIXED = 1, NT_INTERIOR = 2 };  // src/NodeType.h:4-8
 enum StatusBits { ST_INVERTED = 1, ST_SINGULAR_HESS = 2, ST_BFGS_MAX = 4, ST_NONFINITE = 8, ST_PEER_TIMEOUT = 16 };
 
