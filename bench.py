@@ -373,7 +373,8 @@ def run_workload(env, args, wl, K, W, cpu_baseline):
             solver.restore()
             kk = min(SAFE, k - done)
             solver.sync_vp = sync_vp
-            solver.set_option("timing", 1)
+            # per-phase CUDA events only in the device-timed run (and on request in the e2e runs: they cost ~0.1 ms per step there)
+            solver.set_option("timing", 1 if (not sync_vp or args.e2e_phases) else 0)
             solver.timing(reset=True)
             st0 = solver.stats()
             ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -454,7 +455,7 @@ def run_workload(env, args, wl, K, W, cpu_baseline):
         "steps_per_sec": K / (r["ms"] / 1e3), "admm_iters_per_sec": r["iters"] / (r["ms"] / 1e3),
         "admm_iters": r["iters"], "mean_bfgs_iters_per_element_prox": kbar,
         "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": Ploc * D * 8 + 32,
-                "ms_per_step": r2["ms"] / K, "phase_ms_per_step": {k: v[0] / K for k, v in r2["timing"].items()},
+                "ms_per_step": r2["ms"] / K, "phase_ms_per_step": {k: v[0] / K for k, v in r2["timing"].items()} if args.e2e_phases else None,
                 "strict": {"value": e2e_strict, "ms_per_step": r3["ms"] / K,
                            "note": "write-back fenced after every step (the reference's updateAfterStep semantics)"},
                 "writeback_verified": wb_ok,
@@ -495,6 +496,7 @@ def main():
     ap.add_argument("--per-step", action="store_true", help="also record one event per step (step_ms_rank0); adds host work between steps")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-extra-workloads", action="store_true", help="skip the c3 / c4 sub-records of the default (c2) line")
+    ap.add_argument("--e2e-phases", action="store_true", help="per-phase CUDA events inside the e2e runs too (diagnostics)")
     ap.add_argument("--no-parity", action="store_true", help="N > 1: skip the multi-GPU parity check against the oracle")
     ap.add_argument("--opt", action="append", default=[], help="library option name=value (A/B runs), e.g. usum_period=0")
     ap.add_argument("--iso-grid", type=int, default=1, help="0: disable the scalar monitor-grid fast path (A/B runs)")

@@ -1586,7 +1586,14 @@ struct mmadmm_ctx {
         cudaEvent_t evSnap[2] = {nullptr, nullptr}, evCopied[2] = {nullptr, nullptr};
         bool inFlight[2] = {false, false};
         int next = 0;
-        long long copies = 0, hostNs = 0;
+        long long copies = 0;
+        // MMADMM_DEBUG_WB=1 / MMADMM_WB_SNAP=ce (experiments)
+        bool debug = getenv("MMADMM_DEBUG_WB") != nullptr;
+        bool snapByCE = getenv("MMADMM_WB_SNAP") && !strcmp(getenv("MMADMM_WB_SNAP"), "ce");
+        cudaEvent_t evCopyStart[2] = {nullptr, nullptr};
+        long long dbgNs[7] = {0, 0, 0, 0, 0, 0, 0}, dbgMax[7] = {0, 0, 0, 0, 0, 0, 0};
+        double dbgCopyMs = 0, dbgCopyMax = 0;
+        long long dbgCopyN = 0, dbgSyncNs[3] = {0, 0, 0}, dbgSyncN[3] = {0, 0, 0};
     } wb;
 
     double gridO[3] = {0, 0, 0}, gridRh[3] = {0, 0, 0};
@@ -1913,6 +1920,15 @@ int finalize_scalars(mmadmm_ctx *ctx, int n0, const double *p0, int n1, const do
     if (!ctx->dist) {
         k_finalize<<<1, 1024, 0, st>>>(n0, p0, n1, p1, n2, p2, ctx->scal_hd + off, ctx->status_d, ctx->status_hd);
         ctx->launches += 1;
+        if (ctx->wb.debug) {
+            timespec t0, t1;
+            clock_gettime(CLOCK_MONOTONIC, &t0);
+            CK(cudaStreamSynchronize(st));
+            clock_gettime(CLOCK_MONOTONIC, &t1);
+            ctx->wb.dbgSyncNs[ctx->wb.mode] += (t1.tv_sec - t0.tv_sec) * 1000000000ll + (t1.tv_nsec - t0.tv_nsec);
+            ctx->wb.dbgSyncN[ctx->wb.mode]++;
+            return MMADMM_OK;
+        }
         CK(cudaStreamSynchronize(st));
         return MMADMM_OK;
     }
@@ -2399,29 +2415,51 @@ int wb_fence(mmadmm_ctx *ctx) {
 int wb_issue(mmadmm_ctx *ctx) {
     mmadmm_ctx::Writeback &w = ctx->wb;
     const int D = ctx->D, P = ctx->P;
-    struct HostTimer {   // MMADMM_DEBUG_WB=1: host time spent queueing the write-back, reported at destroy
-        mmadmm_ctx::Writeback &w; timespec t0;
-        HostTimer(mmadmm_ctx::Writeback &w_) : w(w_) { clock_gettime(CLOCK_MONOTONIC, &t0); }
-        ~HostTimer() { timespec t1; clock_gettime(CLOCK_MONOTONIC, &t1); w.hostNs += (t1.tv_sec - t0.tv_sec) * 1000000000ll + (t1.tv_nsec - t0.tv_nsec); }
-    } timer(w);
+    // MMADMM_DEBUG_WB=1: host time of every queueing call and device time of every copy, reported at destroy
+    auto now = []() { timespec t; clock_gettime(CLOCK_MONOTONIC, &t); return t.tv_sec * 1000000000ll + t.tv_nsec; };
+    const bool dbg = w.debug;
+    long long tPrev = dbg ? now() : 0;
+    auto lap = [&](int k) {
+        if (!dbg) return;
+        const long long t = now();
+        w.dbgNs[k] += t - tPrev;
+        if (t - tPrev > w.dbgMax[k]) w.dbgMax[k] = t - tPrev;
+        tPrev = t;
+    };
     const size_t bytes = sizeof(double) * (size_t)P * D;
     if (!w.copyStream) {
         CK(cudaStreamCreateWithFlags(&w.copyStream, cudaStreamNonBlocking));
         for (int b = 0; b < 2; b++) {
             CK(cudaMalloc(&w.stage[b], bytes));
             CK(cudaEventCreateWithFlags(&w.evSnap[b], cudaEventDisableTiming));
-            CK(cudaEventCreateWithFlags(&w.evCopied[b], cudaEventDisableTiming));
+            CK(cudaEventCreateWithFlags(&w.evCopied[b], dbg ? cudaEventDefault : cudaEventDisableTiming));
+            if (dbg) CK(cudaEventCreate(&w.evCopyStart[b]));
         }
+        lap(0);
     }
     const int b = w.next;
     w.next ^= 1;
-    if (w.inFlight[b]) CK(cudaStreamWaitEvent(ctx->stream, w.evCopied[b], 0));   // two steps old: the stage is free again
+    if (w.inFlight[b]) {
+        if (dbg && w.copies >= 2) {   // duration of the copy that used this stage two steps ago
+            float ms = 0;
+            if (cudaEventSynchronize(w.evCopied[b]) == cudaSuccess && cudaEventElapsedTime(&ms, w.evCopyStart[b], w.evCopied[b]) == cudaSuccess) {
+                w.dbgCopyMs += ms; w.dbgCopyN++;
+                if (ms > w.dbgCopyMax) w.dbgCopyMax = ms;
+            }
+        }
+        CK(cudaStreamWaitEvent(ctx->stream, w.evCopied[b], 0));   // two steps old: the stage is free again
+    }
+    lap(1);
     // snapshot by a kernel, not a copy-engine memcpy: the stream stays on the compute engine between two steps
-    if (w.colMajor) k_x_to_colmajor<<<cdiv(P, 256), 256, 0, ctx->stream>>>(P, D, ctx->x, w.stage[b]);
+    if (w.snapByCE && !w.colMajor) CK(cudaMemcpyAsync(w.stage[b], ctx->x, bytes, cudaMemcpyDeviceToDevice, ctx->stream));
+    else if (w.colMajor) k_x_to_colmajor<<<cdiv(P, 256), 256, 0, ctx->stream>>>(P, D, ctx->x, w.stage[b]);
     else k_copy<<<cdiv((size_t)P * D, 256), 256, 0, ctx->stream>>>((size_t)P * D, ctx->x, w.stage[b]);
     ctx->launches++;
+    lap(2);
     CK(cudaEventRecord(w.evSnap[b], ctx->stream));
     CK(cudaStreamWaitEvent(w.copyStream, w.evSnap[b], 0));
+    if (dbg) CK(cudaEventRecord(w.evCopyStart[b], w.copyStream));
+    lap(3);
     if (!ctx->dist) {
         CK(cudaMemcpyAsync(w.host, w.stage[b], bytes, cudaMemcpyDeviceToHost, w.copyStream));
     } else {   // this rank's vertices into their rows of the caller's GLOBAL array, one copy per run of consecutive ids
@@ -2439,10 +2477,12 @@ int wb_issue(mmadmm_ctx *ctx) {
             }
         }
     }
+    lap(4);
     CK(cudaEventRecord(w.evCopied[b], w.copyStream));
     w.inFlight[b] = true;
     w.copies++;
-    if (w.mode == 1) return wb_fence(ctx);
+    lap(5);
+    if (w.mode == 1) { int rc = wb_fence(ctx); lap(6); return rc; }
     return MMADMM_OK;
 }
 
@@ -3362,8 +3402,17 @@ void mmadmm_destroy(mmadmm_ctx *ctx) {
     cudaSetDevice(ctx->device);
     if (ctx->stream) cudaStreamSynchronize(ctx->stream);
     wb_fence(ctx);
-    if (getenv("MMADMM_DEBUG_WB") && ctx->wb.copies)
-        fprintf(stderr, "mmadmm: write-back: %lld copies, %.1f us of host time each to queue\n", ctx->wb.copies, ctx->wb.hostNs * 1e-3 / ctx->wb.copies);
+    if (ctx->wb.debug && ctx->wb.copies) {
+        const mmadmm_ctx::Writeback &w = ctx->wb;
+        static const char *nm[7] = {"setup", "wait-stage", "snapshot", "events", "memcpyAsync", "record", "fence(strict)"};
+        fprintf(stderr, "mmadmm: write-back: %lld copies; copy duration on the copy stream: avg %.3f ms, max %.3f ms over %lld\n", w.copies,
+                w.dbgCopyN ? w.dbgCopyMs / w.dbgCopyN : 0.0, w.dbgCopyMax, w.dbgCopyN);
+        for (int m = 0; m < 3; m++)
+            if (w.dbgSyncN[m]) fprintf(stderr, "mmadmm:   host wait in the per-iteration stream synchronise, write-back mode %d: avg %.1f us over %lld\n", m,
+                                       w.dbgSyncNs[m] * 1e-3 / w.dbgSyncN[m], w.dbgSyncN[m]);
+        for (int k = 0; k < 7; k++)
+            fprintf(stderr, "mmadmm:   host %-14s avg %8.1f us  max %8.1f us\n", nm[k], w.dbgNs[k] * 1e-3 / w.copies, w.dbgMax[k] * 1e-3);
+    }
     for (int b = 0; b < 2; b++) {
         cudaFree(ctx->wb.stage[b]);
         if (ctx->wb.evSnap[b]) cudaEventDestroy(ctx->wb.evSnap[b]);
