@@ -108,8 +108,9 @@ class ClockSampler:
     milliseconds long, far below nvidia-smi's polling period), in a background thread."""
     REASONS = {0x8: "hw_slowdown", 0x40: "hw_thermal_slowdown", 0x20: "sw_thermal_slowdown", 0x4: "sw_power_cap"}
 
-    def __init__(self, index=0):
+    def __init__(self, index=0, period_s=0.002):
         import threading
+        self.period_s = period_s
         self.sm, self.mask, self.max_mhz, self.stop_flag = [], 0, None, False
         try:
             import pynvml
@@ -134,7 +135,7 @@ class ClockSampler:
     def _run(self):
         while not self.stop_flag:
             self._sample()
-            time.sleep(0.002)
+            time.sleep(self.period_s)
 
     def stop(self):
         out = dict(sm_mhz=None, sm_max_mhz=self.max_mhz, reasons=[], samples=0)
@@ -380,7 +381,7 @@ def run_workload(env, args, wl, K, W, cpu_baseline):
             ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             # NVML set-up (nvmlInit takes milliseconds) happens BEFORE the barrier: anything between the barrier and ev0 on
             # one rank shows up as waiting time inside the first collective of every other rank.
-            sampler = ClockSampler(env.local) if env.rank == 0 else None   # NVML polling from 8 processes contends on a driver lock
+            sampler = ClockSampler(env.local, args.clock_period_ms * 1e-3) if (env.rank == 0 and args.clock_period_ms > 0) else None   # NVML polling from 8 processes contends on a driver lock
             env.barrier()
             marks = [torch.cuda.Event(enable_timing=True) for _ in range(kk)] if args.per_step else []
             ev0.record(stream)
@@ -458,7 +459,7 @@ def run_workload(env, args, wl, K, W, cpu_baseline):
                 "ms_per_step": r2["ms"] / K, "phase_ms_per_step": {k: v[0] / K for k, v in r2["timing"].items()} if args.e2e_phases else None,
                 "strict": {"value": e2e_strict, "ms_per_step": r3["ms"] / K,
                            "note": "write-back fenced after every step (the reference's updateAfterStep semantics)"},
-                "writeback_verified": wb_ok,
+                "writeback_verified": wb_ok, "step_ms_rank0": r2["step_ms"],
                 "note": "MeshIntegrator.step incl. the per-step write-back of Vp into the caller's pinned host array: device-side snapshot + "
                         "copy on a copy stream overlapped with the next step (mmadmm_set_writeback mode 2), last copy fenced inside the timed "
                         "region.  h2d is 0 by design: like the reference's step(), the call takes no arrays after construction (state is "
@@ -496,6 +497,7 @@ def main():
     ap.add_argument("--per-step", action="store_true", help="also record one event per step (step_ms_rank0); adds host work between steps")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-extra-workloads", action="store_true", help="skip the c3 / c4 sub-records of the default (c2) line")
+    ap.add_argument("--clock-period-ms", type=float, default=2.0, help="NVML clock sampling period inside the timed region (0: off)")
     ap.add_argument("--e2e-phases", action="store_true", help="per-phase CUDA events inside the e2e runs too (diagnostics)")
     ap.add_argument("--no-parity", action="store_true", help="N > 1: skip the multi-GPU parity check against the oracle")
     ap.add_argument("--opt", action="append", default=[], help="library option name=value (A/B runs), e.g. usum_period=0")

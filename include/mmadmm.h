@@ -160,7 +160,15 @@ int mmadmm_get_timing(mmadmm_ctx *ctx, double *ms5, long long *counts5, int rese
  *  and are re-gathered exactly every usum_period-th update; 0 = every x-update gathers z - u slot by slot,
  * the literal form of src/MeshIntegrator.cpp:137-138,159-160 (results agree to rounding, tests hold 1e-12);
  * "p2p_active" is a query: returns 0 iff a distributed context exchanges through NVLink peer stores;
- * "peer_timeout_s" (default 300): see MMADMM_EPEER. */
+ * "peer_timeout_s" (default 300): see MMADMM_EPEER;
+ * "boundary_projection" (default 0): REAL BOUNDARY SLIDING, new behaviour.  The reference carries Mesh::projectOntoBoundary ->
+ * projection2D / projection3D and the face lists of buildFaceList (src/Mesh.cpp:61-241), but all three call sites are commented
+ * out (:636-642, :975-984, :1020-1026), so what it executes for BOUNDARY_FREE nodes is "gradient live, Hessian diagonal 1, no
+ * projection" -- the default here too.  Bit 0 re-enables the call in Mesh::prox (the z slots of the FREE vertices of an element are
+ * projected onto the boundary faces meeting at that vertex, after the element's BFGS solve); bit 1 the call in updateAfterStep
+ * (x of every FREE node, before Vp <- x).  Face geometry comes from the node positions at the end of the previous outer step
+ * (the reference's *Vp).  No reference result exists with it enabled: parity is GPU vs the CPU oracle only (unpinned beyond it).
+ * Single-GPU contexts. */
 int mmadmm_set_option(mmadmm_ctx *ctx, const char *name, int value);
 
 /* The CUDA stream every kernel of this context is launched on (cudaStream_t as void*). */

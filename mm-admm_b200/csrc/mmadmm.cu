@@ -66,8 +66,19 @@ template <int D> struct ElemArgs {
     double *partIh, *partDual;   // per-block partial sums
     unsigned long long *hist;    // 52 bins (may be null)
     unsigned *status;
+    FaceArgs fa;                 // boundary sliding option (fa.mask & 1: project the FREE vertices' z after the BFGS solve)
 };
 
+// the D components of slot (element e, local vertex v) of a z / u array (zu_index layout: adjacent doubles)
+template <int D> __device__ __forceinline__ void load_slot(const double *zu, size_t e, int v, double *out) {
+    const double *p = zu + zu_index<D>(e, D * v);
+    if (D == 2) {
+        const double2 t = __ldg(reinterpret_cast<const double2 *>(p));
+        out[0] = t.x; out[1] = t.y;
+    } else {
+        out[0] = __ldg(p); out[1] = __ldg(p + 1); out[2] = __ldg(p + 2);
+    }
+}
 template <int D> __device__ __forceinline__ void gather_vertex(const double *x, int v, double *out) {
     if (D == 2) {
         double2 t = __ldg(reinterpret_cast<const double2 *>(x) + v);
@@ -339,14 +350,14 @@ __device__ __forceinline__ void load_z_dx(const ElemArgs<D> &a, int e, const int
     for (int v = 0; v < D + 1; v++) gather_vertex<D>(a.x, vid[v], dx + D * v);
     if (!a.uZero) {
 #pragma unroll
-        for (int k = 0; k < n; k++) dx[k] += a.u[tm_index(e, k, n)];
+        for (int k = 0; k < n; k++) dx[k] += a.u[zu_index<D>(e, k)];
     }
     if (a.zsrc) {
 #pragma unroll
         for (int v = 0; v < D + 1; v++) gather_vertex<D>(a.zsrc, vid[v], z + D * v);
     } else {
 #pragma unroll
-        for (int k = 0; k < n; k++) z[k] = a.z[tm_index(e, k, n)];
+        for (int k = 0; k < n; k++) z[k] = a.z[zu_index<D>(e, k)];
     }
 }
 
@@ -518,10 +529,23 @@ __global__ void __launch_bounds__(TPB_, MINB) k_prox(ElemArgs<D> a) {
         if (inv) atomicOr(a.status, ST_INVERTED);
         if (iter == 50) atomicOr(a.status, ST_BFGS_MAX);
         if (a.hist) atomicAdd(&shist[(iter == 50) ? 51 : iter + 1], 1);
+        if (a.fa.mask & 1) {
+            const unsigned fr = (unsigned)a.nonIntBits[e] & ~fb;
+#pragma unroll
+            for (int v = 0; v < D + 1; v++)
+                if (fr & (1u << v)) {
+                    double pt[D];
+#pragma unroll
+                    for (int l = 0; l < D; l++) pt[l] = z[D * v + l];
+                    project_onto_boundary<D>(a.fa, __ldg(a.F[v] + e), pt);
+#pragma unroll
+                    for (int l = 0; l < D; l++) z[D * v + l] = pt[l];
+                }
+        }
 #pragma unroll
         for (int k = 0; k < n; k++) {
-            a.z[tm_index(e, k, n)] = z[k];
-            a.u[tm_index(e, k, n)] = dx[k] - z[k];    // u = DXpU - z
+            a.z[zu_index<D>(e, k)] = z[k];
+            a.u[zu_index<D>(e, k)] = dx[k] - z[k];    // u = DXpU - z
             const double d = z[k] - dz[k];
             dual2 += d * d;
         }
@@ -597,9 +621,9 @@ __global__ void __launch_bounds__(WPB * 32, MINB) k_prox_q(const __grid_constant
         for (int l = 0; l < D; l++) {
             const int sl = l * 32 + lane;
             cp_async8(Xn + sl, a.x + (size_t)D * vid + l);
-            if (!a.uZero) cp_async8(Un + sl, a.u + tm_index(e, D * q + l, n));
+            if (!a.uZero) cp_async8(Un + sl, a.u + zu_index<D>(e, D * q + l));
             if (a.zsrc) cp_async8(Zn + sl, a.zsrc + (size_t)D * vid + l);
-            else cp_async8(Zn + sl, a.z + tm_index(e, D * q + l, n));
+            else cp_async8(Zn + sl, a.z + zu_index<D>(e, D * q + l));
             if (COMP) cp_async8(Cn + sl, a.Vc + (size_t)D * vid + l);
         }
         cp_async4(Fn + lane, reinterpret_cast<const int *>(a.fixedBits) + (e >> 2));
@@ -776,10 +800,18 @@ __global__ void __launch_bounds__(WPB * 32, MINB) k_prox_q(const __grid_constant
             if (inv) atomicOr(a.status, ST_INVERTED);
             if (!done) atomicOr(a.status, ST_BFGS_MAX);
             if (q == 0) { bin = done ? iters : 51; ihAcc += ih; }
+            if ((a.fa.mask & 1) && !ownFixed && (((unsigned)a.nonIntBits[e] >> q) & 1u)) {   // own vertex BOUNDARY_FREE
+                double pt[D];
+#pragma unroll
+                for (int l = 0; l < D; l++) pt[l] = zo[l];
+                project_onto_boundary<D>(a.fa, __ldg(a.F[q] + e), pt);
+#pragma unroll
+                for (int l = 0; l < D; l++) zo[l] = pt[l];
+            }
 #pragma unroll
             for (int l = 0; l < D; l++) {
-                a.z[tm_index(e, D * q + l, n)] = zo[l];
-                a.u[tm_index(e, D * q + l, n)] = dxo[l] - zo[l];    // u = DXpU - z
+                a.z[zu_index<D>(e, D * q + l)] = zo[l];
+                a.u[zu_index<D>(e, D * q + l)] = dxo[l] - zo[l];    // u = DXpU - z
                 const double dd = zo[l] - zprev[l];
                 dualAcc += dd * dd;
             }
@@ -878,30 +910,17 @@ __global__ void __launch_bounds__(WPB * 32, MINB) k_prox_p(const __grid_constant
         const unsigned fb = active ? (unsigned)a.fixedBits[e] : 0u;   // consumed after the first gradient evaluation
         cp_async_wait_all();                                            // this tile's gathers and the next tile's connectivity
         if (smallBytes) mbar_wait(&bars[buf], (unsigned)((it >> 1) & 1));
-        double *xg = b + lane * D, *dxs = b + n * 32 + lane, *zs = b + 2 * n * 32, *xis = b + 3 * n * 32 + lane * D;
+        // every per-tile operand sits in shared memory as a tile image in the zu_index layout ([vertex][32][D]); X = base + lane*D
+        double *xg = b + lane * D, *dxs = b + n * 32 + lane * D, *zs = b + 2 * n * 32 + lane * D, *xis = b + 3 * n * 32 + lane * D;
         double z[n], xi[COMP ? n : 1], Gk[n];
         bool inv = false;
         double ih = 0.0;
-        // DXpU = D x + u  -> dxs[k*32];  z at entry -> z[] and (plane layout) zs[k*32 + lane]
+        // DXpU = D x + u -> dxs;  z at entry -> z[] (zs keeps it: zPrev of the dual residual)
 #pragma unroll
-        for (int v = 0; v < D + 1; v++)
-#pragma unroll
-            for (int l = 0; l < D; l++) {
-                const int k = D * v + l;
-                const double xv = xg[(size_t)v * 32 * D + l];
-                dxs[k * 32] = haveU ? xv + dxs[k * 32] : xv;
-            }
-        if (haveZ) {
-#pragma unroll
-            for (int k = 0; k < n; k++) z[k] = zs[k * 32 + lane];
-        } else {
-#pragma unroll
-            for (int v = 0; v < D + 1; v++)
-#pragma unroll
-                for (int l = 0; l < D; l++) z[D * v + l] = zs[((size_t)v * 32 + lane) * D + l];
-            __syncwarp();   // gathered layout is read by every lane before it is overwritten in plane layout
-#pragma unroll
-            for (int k = 0; k < n; k++) zs[k * 32 + lane] = z[k];
+        for (int k = 0; k < n; k++) {
+            const double xv = xg[zu_off<D>(k)];
+            dxs[zu_off<D>(k)] = haveU ? xv + dxs[zu_off<D>(k)] : xv;
+            z[k] = zs[zu_off<D>(k)];
         }
         if (COMP) {
 #pragma unroll
@@ -978,12 +997,27 @@ __global__ void __launch_bounds__(WPB * 32, MINB) k_prox_p(const __grid_constant
             if (inv) atomicOr(a.status, ST_INVERTED);
             if (iter == 50) atomicOr(a.status, ST_BFGS_MAX);
             bin = (iter == 50) ? 51 : iter + 1;
+            if (a.fa.mask & 1) {   // "Moving boundary points" (src/Mesh.cpp:975-984): rare, boundary elements only
+                const unsigned fr = (unsigned)a.nonIntBits[e] & ~fb;
+                if (fr) {
+#pragma unroll
+                    for (int v = 0; v < D + 1; v++)
+                        if (fr & (1u << v)) {
+                            double pt[D];     // only this copy has its address taken: z stays in registers
+#pragma unroll
+                            for (int l = 0; l < D; l++) pt[l] = z[D * v + l];
+                            project_onto_boundary<D>(a.fa, __ldg(a.F[v] + e), pt);
+#pragma unroll
+                            for (int l = 0; l < D; l++) z[D * v + l] = pt[l];
+                        }
+                }
+            }
             double dual2 = 0.0;
 #pragma unroll
             for (int k = 0; k < n; k++) {
-                a.z[((size_t)t * n + k) * TILE + lane] = z[k];
-                a.u[((size_t)t * n + k) * TILE + lane] = dxs[k * 32] - z[k];    // u = DXpU - z
-                const double d = z[k] - zs[k * 32 + lane];
+                a.z[(size_t)t * n * TILE + lane * D + zu_off<D>(k)] = z[k];
+                a.u[(size_t)t * n * TILE + lane * D + zu_off<D>(k)] = dxs[zu_off<D>(k)] - z[k];    // u = DXpU - z
+                const double d = z[k] - zs[zu_off<D>(k)];
                 dual2 += d * d;
             }
             ihAcc += ih;
@@ -1010,7 +1044,7 @@ __global__ void __launch_bounds__(WPB * 32, MINB) k_prox_p(const __grid_constant
             for (int v = 0; v < D + 1; v++) {
                 double pnt[D];
 #pragma unroll
-                for (int l = 0; l < D; l++) pnt[l] = haveZ ? zn[(D * v + l) * 32 + lane] : zn[((size_t)v * 32 + lane) * D + l];
+                for (int l = 0; l < D; l++) pnt[l] = zn[((size_t)v * 32 + lane) * D + l];
                 prefetch_monitor<D, (FLAGS & PF_ISO) != 0>(a.mg, pnt);
             }
         }
@@ -1033,7 +1067,7 @@ template <int D> __global__ void __launch_bounds__(TPB) k_applyD(ElemArgs<D> a, 
         double p[D];
         gather_vertex<D>(src, vid[v], p);
 #pragma unroll
-        for (int l = 0; l < D; l++) a.z[tm_index(e, D * v + l, D * (D + 1))] = p[l];
+        for (int l = 0; l < D; l++) a.z[zu_index<D>(e, D * v + l)] = p[l];
     }
 }
 
@@ -1092,11 +1126,11 @@ __global__ void __launch_bounds__(TPB_V, MINB) k_xupdate(int P, size_t Es, const
                 const int slot = __ldg(incIdx + k);
                 const size_t e = (size_t)(slot >> 2);
                 const int v = slot & 3;
+                double zq[D], uq[D];
+                load_slot<D>(z, e, v, zq);
+                load_slot<D>(u, e, v, uq);
 #pragma unroll
-                for (int l = 0; l < D; l++) {
-                    const size_t idx = tm_index(e, D * v + l, D * (D + 1));
-                    s[l] += w * (w * (__ldg(z + idx) - __ldg(u + idx)));
-                }
+                for (int l = 0; l < D; l++) s[l] += w * (w * (zq[l] - uq[l]));
             }
         } else {
             // slots in chunks of CH: all index loads, then all value loads, then the (ordered) accumulation
@@ -1109,11 +1143,19 @@ __global__ void __launch_bounds__(TPB_V, MINB) k_xupdate(int P, size_t Es, const
                 for (int j = 0; j < CH; j++) {
                     const size_t e = (size_t)(slot[j] >> 2);
                     const int v = slot[j] & 3;
+                    if (ZSRC || slot[j] < 0) {
 #pragma unroll
-                    for (int l = 0; l < D; l++) {
-                        const size_t idx = tm_index(e, D * v + l, D * (D + 1));
-                        zv[j][l] = (ZSRC || slot[j] < 0) ? zs[l] : __ldg(z + idx);
-                        if (!UREC) uv[j][l] = (UZERO || slot[j] < 0) ? 0.0 : __ldg(u + idx);
+                        for (int l = 0; l < D; l++) zv[j][l] = zs[l];
+                    } else {
+                        load_slot<D>(z, e, v, zv[j]);
+                    }
+                    if (!UREC) {
+                        if (UZERO || slot[j] < 0) {
+#pragma unroll
+                            for (int l = 0; l < D; l++) uv[j][l] = 0.0;
+                        } else {
+                            load_slot<D>(u, e, v, uv[j]);
+                        }
                     }
                 }
 #pragma unroll
@@ -1155,10 +1197,16 @@ __global__ void __launch_bounds__(TPB_V, MINB) k_xupdate(int P, size_t Es, const
                 int slot = __ldg(incIdx + k);
                 size_t e = (size_t)(slot >> 2);
                 int v = slot & 3;
+                double zv[D];
+                if (ZSRC) {
+#pragma unroll
+                    for (int l = 0; l < D; l++) zv[l] = zs[l];
+                } else {
+                    load_slot<D>(z, e, v, zv);
+                }
 #pragma unroll
                 for (int l = 0; l < D; l++) {
-                    double zv = ZSRC ? zs[l] : __ldg(z + tm_index(e, D * v + l, D * (D + 1)));
-                    double df = xn[l] - zv;
+                    double df = xn[l] - zv[l];
                     prim += df * df;
                 }
             }
@@ -1195,7 +1243,7 @@ __global__ void __launch_bounds__(TPB_V) k_xfinish(int nShared, const int *share
                 const int v = slot & 3;
 #pragma unroll
                 for (int l = 0; l < D; l++) {
-                    const double zv = ZSRC ? zsrc[(size_t)D * p + l] : __ldg(z + tm_index(e, D * v + l, D * (D + 1)));
+                    const double zv = ZSRC ? zsrc[(size_t)D * p + l] : __ldg(z + zu_index<D>(e, D * v + l));
                     const double df = xn[l] - zv;
                     prim += df * df;
                 }
@@ -1308,6 +1356,17 @@ template <int D> __global__ void k_iso_extract(size_t rows, const double *grid, 
     if (!ok) *flag = 0;
 }
 
+// updateAfterStep with the projection of the BOUNDARY_FREE nodes enabled (src/Mesh.cpp:1020-1026): x_p <- projectOntoBoundary(p, x_p)
+template <int D> __global__ void k_project_x(int P, const uint8_t *mask, FaceArgs fa, double *x) {
+    const int p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= P || mask[p] != NT_BOUNDARY_FREE) return;
+    double pt[D];
+#pragma unroll
+    for (int l = 0; l < D; l++) pt[l] = x[(size_t)D * p + l];
+    project_onto_boundary<D>(fa, p, pt);
+#pragma unroll
+    for (int l = 0; l < D; l++) x[(size_t)D * p + l] = pt[l];
+}
 __global__ void k_copy(size_t n, const double *src, double *dst) {
     const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n) dst[i] = src[i];
@@ -1539,6 +1598,9 @@ struct mmadmm_ctx {
     double Ehat[9] = {0}, dpow = 0;
     bool stepTaken = false, hessComputed = false;
     int stepsTaken = 0;
+    int projMask = 0;         // option "boundary_projection" (FaceArgs::mask)
+    int *facePtr_d = nullptr, *faceIdx_d = nullptr, *faceList_d = nullptr;
+    int nFaces = 0;
     double *usum = nullptr;   // per-vertex sum of the dual over the vertex's slots (k_xupdate / k_xfirst)
     int usumPeriod = 64;      // every usumPeriod-th x-update after a prox sweep re-gathers usum exactly; 0: slot-by-slot x-updates only
     int usumAge = 0;
@@ -1617,6 +1679,7 @@ struct mmadmm_ctx {
         a.partIh = partIh; a.partDual = partDual;
         a.hist = statsOn ? hist_d : nullptr;
         a.status = status_d;
+        a.fa.ptr = facePtr_d; a.fa.idx = faceIdx_d; a.fa.list = faceList_d; a.fa.vp = xPrev; a.fa.mask = projMask;
         return a;
     }
     void phaseBegin(int ph) {
@@ -1819,7 +1882,7 @@ __global__ void __launch_bounds__(TPB_V) k_xfinish_p2p(int nShared, int nNbr, co
                 const int v = slot & 3;
 #pragma unroll
                 for (int l = 0; l < D; l++) {
-                    const double zv = ZSRC ? zsrc[(size_t)D * p + l] : __ldg(z + tm_index(e, D * v + l, D * (D + 1)));
+                    const double zv = ZSRC ? zsrc[(size_t)D * p + l] : __ldg(z + zu_index<D>(e, D * v + l));
                     const double df = xn[l] - zv;
                     prim += df * df;
                 }
@@ -2375,6 +2438,55 @@ int create_impl(mmadmm_ctx *ctx, const double *Vp, const double *Vc, const int *
     return MMADMM_OK;
 }
 
+// Mesh::buildFaceList (src/Mesh.cpp:61-112) for the boundary-sliding option: a simplex with exactly D non-INTERIOR vertices
+// contributes one boundary face (those vertices in local order); per vertex the faces it belongs to in ascending face id.
+int build_face_lists(mmadmm_ctx *ctx) {
+    if (ctx->facePtr_d) return MMADMM_OK;
+    const int D = ctx->D, V = D + 1, P = ctx->P, E = ctx->E;
+    std::vector<int> Fh((size_t)E * V), plane(E);
+    std::vector<uint8_t> mask(P);
+    CK(cudaStreamSynchronize(ctx->stream));
+    for (int v = 0; v < V; v++) {
+        CK(cudaMemcpy(plane.data(), ctx->F[v], sizeof(int) * (size_t)E, cudaMemcpyDeviceToHost));
+        for (int e = 0; e < E; e++) Fh[(size_t)e * V + v] = plane[e];
+    }
+    CK(cudaMemcpy(mask.data(), ctx->mask, (size_t)P, cudaMemcpyDeviceToHost));
+    std::vector<int> faces;
+    for (int e = 0; e < E; e++) {
+        int sum = 0;
+        for (int j = 0; j < V; j++) sum += mask[Fh[(size_t)e * V + j]] != NT_INTERIOR;
+        if (sum == D)
+            for (int j = 0; j < V; j++)
+                if (mask[Fh[(size_t)e * V + j]] != NT_INTERIOR) faces.push_back(Fh[(size_t)e * V + j]);
+    }
+    const int nF = (int)(faces.size() / D);
+    std::vector<int> ptr((size_t)P + 1, 0), idx;
+    for (int pass = 0; pass < 2; pass++) {
+        std::vector<int> fill;
+        if (pass == 1) {
+            for (int p = 0; p < P; p++) ptr[p + 1] += ptr[p];
+            idx.resize(ptr[P]);
+            fill.assign(ptr.begin(), ptr.end() - 1);
+        }
+        for (int f = 0; f < nF; f++)
+            for (int j = 0; j < D; j++) {
+                bool dup = false;
+                for (int jj = 0; jj < j; jj++) dup = dup || faces[(size_t)f * D + jj] == faces[(size_t)f * D + j];
+                if (dup) continue;
+                if (pass == 0) ptr[faces[(size_t)f * D + j] + 1]++;
+                else idx[fill[faces[(size_t)f * D + j]]++] = f;
+            }
+    }
+    CK(cudaMalloc(&ctx->facePtr_d, sizeof(int) * ptr.size()));
+    CK(cudaMalloc(&ctx->faceIdx_d, sizeof(int) * std::max<size_t>(idx.size(), 1)));
+    CK(cudaMalloc(&ctx->faceList_d, sizeof(int) * std::max<size_t>(faces.size(), 1)));
+    CK(cudaMemcpy(ctx->facePtr_d, ptr.data(), sizeof(int) * ptr.size(), cudaMemcpyHostToDevice));
+    CK(cudaMemcpy(ctx->faceIdx_d, idx.data(), sizeof(int) * idx.size(), cudaMemcpyHostToDevice));
+    CK(cudaMemcpy(ctx->faceList_d, faces.data(), sizeof(int) * faces.size(), cudaMemcpyHostToDevice));
+    ctx->nFaces = nF;
+    return MMADMM_OK;
+}
+
 int check_status(mmadmm_ctx *ctx) {
     unsigned s = *ctx->status_h;
     if (s & ST_PEER_TIMEOUT) {
@@ -2412,6 +2524,20 @@ int wb_fence(mmadmm_ctx *ctx) {
         }
     return MMADMM_OK;
 }
+// staging buffers, copy stream and events: allocated when a write-back target is set (mmadmm_set_writeback), never inside a step
+int wb_setup(mmadmm_ctx *ctx) {
+    mmadmm_ctx::Writeback &w = ctx->wb;
+    if (w.copyStream) return MMADMM_OK;
+    const size_t bytes = sizeof(double) * (size_t)ctx->P * ctx->D;
+    CK(cudaStreamCreateWithFlags(&w.copyStream, cudaStreamNonBlocking));
+    for (int b = 0; b < 2; b++) {
+        CK(cudaMalloc(&w.stage[b], bytes));
+        CK(cudaEventCreateWithFlags(&w.evSnap[b], cudaEventDisableTiming));
+        CK(cudaEventCreateWithFlags(&w.evCopied[b], w.debug ? cudaEventDefault : cudaEventDisableTiming));
+        if (w.debug) CK(cudaEventCreate(&w.evCopyStart[b]));
+    }
+    return MMADMM_OK;
+}
 int wb_issue(mmadmm_ctx *ctx) {
     mmadmm_ctx::Writeback &w = ctx->wb;
     const int D = ctx->D, P = ctx->P;
@@ -2427,14 +2553,9 @@ int wb_issue(mmadmm_ctx *ctx) {
         tPrev = t;
     };
     const size_t bytes = sizeof(double) * (size_t)P * D;
-    if (!w.copyStream) {
-        CK(cudaStreamCreateWithFlags(&w.copyStream, cudaStreamNonBlocking));
-        for (int b = 0; b < 2; b++) {
-            CK(cudaMalloc(&w.stage[b], bytes));
-            CK(cudaEventCreateWithFlags(&w.evSnap[b], cudaEventDisableTiming));
-            CK(cudaEventCreateWithFlags(&w.evCopied[b], dbg ? cudaEventDefault : cudaEventDisableTiming));
-            if (dbg) CK(cudaEventCreate(&w.evCopyStart[b]));
-        }
+    {
+        int rcs = wb_setup(ctx);
+        if (rcs) return rcs;
         lap(0);
     }
     const int b = w.next;
@@ -2696,6 +2817,10 @@ template <int D> int step_impl(mmadmm_ctx *ctx, int nIters, double tol, double *
         if (primal < tol && dual < tol) break;
     }
     if (ctx->evUsed >= 4096) ctx->phaseResolve();
+    if (ctx->projMask & 2) {   // updateAfterStep's projection of the FREE nodes (option), face geometry from the old Vp = xPrev
+        k_project_x<D><<<cdiv(P, 256), 256, 0, st>>>(P, ctx->mask, a.fa, ctx->x);
+        ctx->launches++;
+    }
     CK(cudaGetLastError());
     ctx->stepsTaken++;
     if (ctx->wb.mode) {   // updateAfterStep: Vp <- x
@@ -3131,6 +3256,7 @@ int mmadmm_set_writeback(mmadmm_ctx *ctx, double *VpHost, int colMajor, int mode
         if (ctx->runs.size() > 256) { ctx->err = "write-back: this rank's vertices form more than 256 runs of consecutive global ids"; return MMADMM_EINVAL; }
     }
     ctx->wb.mode = mode; ctx->wb.colMajor = colMajor ? 1 : 0; ctx->wb.host = VpHost;
+    if (mode != 0) return wb_setup(ctx);
     return MMADMM_OK;
 }
 int mmadmm_writeback_fence(mmadmm_ctx *ctx) {
@@ -3260,8 +3386,9 @@ int mmadmm_get_state(mmadmm_ctx *ctx, int which, double *out) {
         CK(cudaMemcpy(tmp.data(), src, sizeof(double) * tmp.size(), cudaMemcpyDeviceToHost));
         for (size_t e = 0; e < E; e++)
             for (int k = 0; k < planes; k++) {
-                size_t src_i = tm_index(e, k, planes);
+                size_t src_i;
                 if (which == MMADMM_STATE_HESSINV) src_i = (ctx->D == 2) ? b_index<2>(e, k / n, k % n) : b_index<3>(e, k / n, k % n);
+                else src_i = (ctx->D == 2) ? zu_index<2>(e, k) : zu_index<3>(e, k);
                 out[e * planes + k] = tmp[src_i];
             }
         return MMADMM_OK;
@@ -3384,6 +3511,18 @@ int mmadmm_set_option(mmadmm_ctx *ctx, const char *name, int value) {
         ctx->usumPeriod = value; ctx->usumAge = 0;
         return MMADMM_OK;
     }
+    if (!strcmp(name, "boundary_projection")) {   // real boundary sliding: see include/mmadmm.h
+        if (value < 0 || value > 3) return MMADMM_EINVAL;
+        if (value && ctx->dist) { ctx->err = "boundary_projection is available on single-GPU contexts only"; return MMADMM_EINVAL; }
+        if (value) {
+            CK(cudaSetDevice(ctx->device));
+            int rcf = build_face_lists(ctx);
+            if (rcf) return rcf;
+        }
+        ctx->projMask = value;
+        return MMADMM_OK;
+    }
+    if (!strcmp(name, "boundary_faces")) return ctx->nFaces;   // query: number of boundary faces (after boundary_projection was set)
     if (!strcmp(name, "peer_timeout_s")) {   // bound (seconds) of every wait on a peer rank's flag; the wait ends with MMADMM_EPEER
         if (value <= 0) return MMADMM_EINVAL;
         ctx->peerTimeoutNs = (unsigned long long)value * 1000000000ull;
@@ -3430,6 +3569,7 @@ void mmadmm_destroy(mmadmm_ctx *ctx) {
         if ((int)r != ctx->rank && ctx->peerMap[r]) cudaIpcCloseMemHandle(ctx->peerMap[r]);
     cudaFree(ctx->mailbox); cudaFree(ctx->peerRecv_d); cudaFree(ctx->peerRecvStride_d); cudaFree(ctx->peerHaloFlag_d);
     cudaFree(ctx->peerScal_d); cudaFree(ctx->peerScalFlag_d); cudaFree(ctx->nbrPtr_d);
+    cudaFree(ctx->facePtr_d); cudaFree(ctx->faceIdx_d); cudaFree(ctx->faceList_d);
     cudaFree(ctx->pushPtr_d); cudaFree(ctx->pushNbr_d); cudaFree(ctx->pushPos_d); cudaFree(ctx->pushTicket_d);
     cudaFree(ctx->grid); cudaFree(ctx->gridIso); cudaFree(ctx->xT); cudaFree(ctx->ax); cudaFree(ctx->ay); cudaFree(ctx->az);
     cudaFree(ctx->partIh); cudaFree(ctx->partDual); cudaFree(ctx->partPrimal); cudaFree(ctx->scal_d);

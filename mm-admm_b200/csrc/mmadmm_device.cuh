@@ -21,6 +21,16 @@ __host__ __device__ __forceinline__ size_t tm_index(size_t e, int row, int rows)
     return ((e >> 5) * (size_t)rows + (size_t)row) * TILE + (e & 31);
 }
 
+// z and u (n = D(D+1) doubles per element, vertex-major inside an element): [tile of 32 elements][vertex v][32][D] -- a tile is
+// one contiguous n*256-byte block (one bulk copy), and the D components of a slot (element, vertex) are adjacent, so the
+// vertex-centric gathers of the x-update fetch a slot with one 16-byte load (2D) / from one or two sectors (3D) instead of D
+// loads from D different 256-byte rows.  k = D*v + l.
+template <int D> __host__ __device__ __forceinline__ size_t zu_index(size_t e, int k) {
+    return (((e >> 5) * (D + 1) + (size_t)(k / D)) * TILE + (e & 31)) * D + (k % D);
+}
+// offset of component k inside a tile image, relative to the lane's base (lane * D)
+template <int D> __host__ __device__ constexpr int zu_off(int k) { return (k / D) * TILE * D + (k % D); }
+
 // Inverse Hessians (n x n per element).  2D: tile-major like z / u ([tile of 32][n*n entries][32]).  3D: sub-tiles of 8 elements,
 // [sub-tile][144 entries][8], entry (row, col) at position row*12 + (col ^ ((row/3) & 1)): the 3D prox kernel gives every element
 // four lanes (one per vertex) that read different rows (or columns) of the same sub-tile at the same time, and this pairwise swap
@@ -325,6 +335,91 @@ template <int D, bool ISO = false> __device__ __forceinline__ void prefetch_moni
     }
 }
 
+// Boundary sliding (OPTION, off by default): Mesh::projectOntoBoundary -> projection2D / projection3D (src/Mesh.cpp:118-241) on the
+// face lists of Mesh::buildFaceList (:61-112).  All three call sites are commented out in the reference (:636-642, :975-984,
+// :1020-1026); option "boundary_projection" re-enables the two on the ADMM path.  Face geometry comes from `vp`, the node
+// positions at the end of the previous outer step (the reference's *Vp).
+struct FaceArgs {
+    const int *ptr = nullptr, *idx = nullptr;    // vertex -> boundary faces (ascending face id, the reference's std::set order)
+    const int *list = nullptr;                   // nFaces x D vertex ids
+    const double *vp = nullptr;                  // P x D
+    int mask = 0;                                // bit 0: after every element's BFGS solve in prox; bit 1: in updateAfterStep
+};
+__device__ __forceinline__ int sgn_d(double v) { return (0.0 < v) - (v < 0.0); }
+template <int D> __device__ __noinline__ void project_onto_boundary(const FaceArgs &fa, int nodeId, double *nodeIn);
+template <> __device__ __noinline__ void project_onto_boundary<2>(const FaceArgs &fa, int nodeId, double *nodeIn) {
+    const double node[2] = {nodeIn[0], nodeIn[1]};
+    double best[2] = {node[0], node[1]};
+    double minDist = INFINITY;
+    for (int q = fa.ptr[nodeId]; q < fa.ptr[nodeId + 1]; q++) {
+        const int *pid = fa.list + (size_t)fa.idx[q] * 2;
+        const double x1[2] = {fa.vp[(size_t)pid[0] * 2], fa.vp[(size_t)pid[0] * 2 + 1]};
+        const double x2[2] = {fa.vp[(size_t)pid[1] * 2], fa.vp[(size_t)pid[1] * 2 + 1]};
+        const double u[2] = {x2[0] - x1[0], x2[1] - x1[1]};
+        const double w[2] = {node[0] - x1[0], node[1] - x1[1]};
+        const double c = __ddiv_rn(__dadd_rn(__dmul_rn(u[0], w[0]), __dmul_rn(u[1], w[1])), __dadd_rn(__dmul_rn(u[0], u[0]), __dmul_rn(u[1], u[1])));
+        const double proj[2] = {c * u[0], c * u[1]};
+        const double d0 = proj[0] - w[0], d1 = proj[1] - w[1];
+        double dist = sqrt(__dadd_rn(__dmul_rn(d0, d0), __dmul_rn(d1, d1)));
+        const double t = __ddiv_rn(sqrt(__dadd_rn(__dmul_rn(proj[0], proj[0]), __dmul_rn(proj[1], proj[1]))),
+                                   sqrt(__dadd_rn(__dmul_rn(u[0], u[0]), __dmul_rn(u[1], u[1]))));
+        const bool same = sgn_d(u[0]) == sgn_d(proj[0]) && sgn_d(u[1]) == sgn_d(proj[1]);
+        if (dist < minDist && same && t > 0.0 && t < 1.0) {
+            minDist = dist;
+            best[0] = __dadd_rn(__dmul_rn(1.0 - t, x1[0]), __dmul_rn(t, x2[0]));
+            best[1] = __dadd_rn(__dmul_rn(1.0 - t, x1[1]), __dmul_rn(t, x2[1]));
+        } else if (!same) {
+            const double e0 = x1[0] - node[0], e1 = x1[1] - node[1];
+            dist = sqrt(__dadd_rn(__dmul_rn(e0, e0), __dmul_rn(e1, e1)));
+            if (dist < minDist) { minDist = dist; best[0] = x1[0]; best[1] = x1[1]; }
+        } else if (t > 1.0) {
+            const double e0 = x2[0] - node[0], e1 = x2[1] - node[1];
+            dist = sqrt(__dadd_rn(__dmul_rn(e0, e0), __dmul_rn(e1, e1)));
+            if (dist < minDist) { minDist = dist; best[0] = x2[0]; best[1] = x2[1]; }
+        }
+    }
+    nodeIn[0] = best[0]; nodeIn[1] = best[1];
+}
+template <> __device__ __noinline__ void project_onto_boundary<3>(const FaceArgs &fa, int nodeId, double *nodeIn) {
+    const double node[3] = {nodeIn[0], nodeIn[1], nodeIn[2]};
+    double best[3] = {0.0, 0.0, 0.0};
+    bool projWorked = false;
+    const double CHECK_EPS = 1e-10;
+    double minDist = INFINITY;
+    // explicit non-fused arithmetic: which face wins (dist < minDist, b >= 1e-10) is a comparison of nearly equal numbers
+    auto cross = [](const double *a, const double *b, double *c) {
+        c[0] = __dsub_rn(__dmul_rn(a[1], b[2]), __dmul_rn(a[2], b[1]));
+        c[1] = __dsub_rn(__dmul_rn(a[2], b[0]), __dmul_rn(a[0], b[2]));
+        c[2] = __dsub_rn(__dmul_rn(a[0], b[1]), __dmul_rn(a[1], b[0]));
+    };
+    auto dot = [](const double *a, const double *b) { return __dadd_rn(__dadd_rn(__dmul_rn(a[0], b[0]), __dmul_rn(a[1], b[1])), __dmul_rn(a[2], b[2])); };
+    for (int qi = fa.ptr[nodeId]; qi < fa.ptr[nodeId + 1]; qi++) {
+        const int *pid = fa.list + (size_t)fa.idx[qi] * 3;
+        const double *p0 = fa.vp + (size_t)pid[0] * 3, *p1 = fa.vp + (size_t)pid[1] * 3, *p2 = fa.vp + (size_t)pid[2] * 3;
+        double u[3], v[3], w[3], n[3], uw[3], wv[3], b[3];
+#pragma unroll
+        for (int l = 0; l < 3; l++) { u[l] = p1[l] - p0[l]; v[l] = p2[l] - p0[l]; w[l] = node[l] - p0[l]; }
+        cross(u, v, n);
+        const double temp = __ddiv_rn(1.0, dot(n, n));
+        cross(u, w, uw);
+        cross(w, v, wv);
+        b[2] = __dmul_rn(dot(uw, n), temp);
+        b[1] = __dmul_rn(dot(wv, n), temp);
+        b[0] = __dsub_rn(__dsub_rn(1.0, b[1]), b[2]);
+        double np[3];
+#pragma unroll
+        for (int l = 0; l < 3; l++) np[l] = __dadd_rn(__dadd_rn(__dmul_rn(b[0], p0[l]), __dmul_rn(b[1], p1[l])), __dmul_rn(b[2], p2[l]));
+        const double f0 = np[0] - node[0], f1 = np[1] - node[1], f2 = np[2] - node[2];
+        const double dist = sqrt(__dadd_rn(__dadd_rn(__dmul_rn(f0, f0), __dmul_rn(f1, f1)), __dmul_rn(f2, f2)));
+        if (dist < minDist && b[0] >= CHECK_EPS && b[1] >= CHECK_EPS && b[2] >= CHECK_EPS) {
+            minDist = dist;
+            best[0] = np[0]; best[1] = np[1]; best[2] = np[2];
+            projWorked = true;
+        }
+    }
+    if (projWorked) { nodeIn[0] = best[0]; nodeIn[1] = best[1]; nodeIn[2] = best[2]; }
+}
+
 // Constants of the functional that the reference recomputes per call (AdaptationFunctional.cpp:176-201,
 // 219-220): computed once on the host with the reference's own expressions (libm pow) and passed by value.
 template <int D> struct FuncConsts {
@@ -587,7 +682,7 @@ __device__ __forceinline__ double prox_grad(const double *z, const double *dxpu,
     return Igt;
 }
 
-// Same as prox_grad, with DXpU read from shared memory (dxs[k*32], one column per lane) after the gradient is formed,
+// Same as prox_grad, with DXpU read from shared memory (tile image in the zu_index layout, dxs = tile + lane*D) after the gradient is formed,
 // so that it is not live in registers across block_grad.
 template <int D, bool ISO = false>
 __device__ __forceinline__ double prox_grad_s(const double *z, const double *dxs, const double *xi, bool compMesh,
@@ -596,7 +691,7 @@ __device__ __forceinline__ double prox_grad_s(const double *z, const double *dxs
     constexpr int n = D * (D + 1);
     double Igt = block_grad<D, true, ISO>(z, xi, compMesh, mg, fc, grad, inverted);
 #pragma unroll
-    for (int k = 0; k < n; k++) grad[k] += fc.w2 * (-dxs[k * 32] + z[k]);
+    for (int k = 0; k < n; k++) grad[k] += fc.w2 * (-dxs[zu_off<D>(k)] + z[k]);
 #pragma unroll
     for (int v = 0; v < D + 1; v++)
         if (fixedBits & (1u << v)) {

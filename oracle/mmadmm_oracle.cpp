@@ -203,6 +203,13 @@ struct Oracle {
     double lastPrimal = 0, lastDual = 0;
     int nthreads = 1;
     int error = 0;  // 1 = inverted element seen (reference would assert), 2 = singular FD Hessian
+    // Boundary sliding (src/Mesh.cpp:61-241).  The reference builds the face lists at init (buildFaceList, :420) but all three call
+    // sites of projectOntoBoundary are commented out (:636-642 old eulerStep, :975-984 prox, :1020-1026 updateAfterStep); projMask
+    // re-enables them as an OPTION: bit 0 = after every element's BFGS solve in prox, bit 1 = in updateAfterStep.  Default 0 = what
+    // the reference executes.  No reference result exists with it on: new behaviour, parity GPU vs this oracle only.
+    int projMask = 0;
+    std::vector<int> faceList;             // nFaces x D vertex ids
+    std::vector<int> facePtr, faceIdx;     // faceConnects: vertex -> faces, ascending face id (std::set<int> order)
 };
 
 // src/MeshInterpolator.cpp:286-342
@@ -397,6 +404,107 @@ static double computeBlockGrad(Oracle &o, int zId, const double *z, const double
     return Ix;
 }
 
+// src/Mesh.cpp:61-112 buildFaceList: a simplex with exactly D non-INTERIOR vertices contributes one boundary face (its non-interior
+// vertices in local order); faceConnects = per vertex the set of faces it belongs to.
+template <int D>
+static void buildFaceList(Oracle &o) {
+    o.faceList.clear();
+    for (int i = 0; i < o.E; i++) {
+        int sum = 0;
+        for (int j = 0; j < D + 1; j++) sum += (o.mask[o.F[(size_t)i * (D + 1) + j]] != INTERIOR) ? 1 : 0;
+        if (sum == D)
+            for (int j = 0; j < D + 1; j++)
+                if (o.mask[o.F[(size_t)i * (D + 1) + j]] != INTERIOR) o.faceList.push_back(o.F[(size_t)i * (D + 1) + j]);
+    }
+    const int nF = (int)(o.faceList.size() / D);
+    o.facePtr.assign(o.P + 1, 0);
+    for (int f = 0; f < nF; f++)
+        for (int j = 0; j < D; j++) {
+            bool dup = false;   // a set: a face lists a vertex once
+            for (int jj = 0; jj < j; jj++) dup = dup || o.faceList[(size_t)f * D + jj] == o.faceList[(size_t)f * D + j];
+            if (!dup) o.facePtr[o.faceList[(size_t)f * D + j] + 1]++;
+        }
+    for (int p = 0; p < o.P; p++) o.facePtr[p + 1] += o.facePtr[p];
+    o.faceIdx.resize(o.facePtr[o.P]);
+    std::vector<int> fill(o.facePtr.begin(), o.facePtr.end() - 1);
+    for (int f = 0; f < nF; f++)
+        for (int j = 0; j < D; j++) {
+            bool dup = false;
+            for (int jj = 0; jj < j; jj++) dup = dup || o.faceList[(size_t)f * D + jj] == o.faceList[(size_t)f * D + j];
+            if (!dup) o.faceIdx[fill[o.faceList[(size_t)f * D + j]]++] = f;
+        }
+}
+static inline int sgn(double val) { return (0.0 < val) - (val < 0.0); }   // src/Mesh.cpp:114-116
+// src/Mesh.cpp:118-177 projection2D: closest point on the boundary edges that meet at the node, edge geometry from Vp
+static void projection2D(const Oracle &o, int nodeId, double *nodeIn) {
+    const double node[2] = {nodeIn[0], nodeIn[1]};
+    double best[2] = {node[0], node[1]};
+    double minDist = INFINITY;
+    for (int q = o.facePtr[nodeId]; q < o.facePtr[nodeId + 1]; q++) {
+        const int *pid = &o.faceList[(size_t)o.faceIdx[q] * 2];
+        const double x1[2] = {o.Vp[(size_t)pid[0] * 2], o.Vp[(size_t)pid[0] * 2 + 1]};
+        const double x2[2] = {o.Vp[(size_t)pid[1] * 2], o.Vp[(size_t)pid[1] * 2 + 1]};
+        const double u[2] = {x2[0] - x1[0], x2[1] - x1[1]};
+        const double w[2] = {node[0] - x1[0], node[1] - x1[1]};
+        const double c = (u[0] * w[0] + u[1] * w[1]) / (u[0] * u[0] + u[1] * u[1]);
+        const double proj[2] = {c * u[0], c * u[1]};
+        double dist = std::sqrt((proj[0] - w[0]) * (proj[0] - w[0]) + (proj[1] - w[1]) * (proj[1] - w[1]));
+        const double t = std::sqrt(proj[0] * proj[0] + proj[1] * proj[1]) / std::sqrt(u[0] * u[0] + u[1] * u[1]);
+        const bool same = sgn(u[0]) == sgn(proj[0]) && sgn(u[1]) == sgn(proj[1]);
+        if (dist < minDist && same && t > 0.0 && t < 1.0) {
+            minDist = dist;
+            best[0] = (1.0 - t) * x1[0] + t * x2[0];
+            best[1] = (1.0 - t) * x1[1] + t * x2[1];
+        } else if (!same) {
+            dist = std::sqrt((x1[0] - node[0]) * (x1[0] - node[0]) + (x1[1] - node[1]) * (x1[1] - node[1]));
+            if (dist < minDist) { minDist = dist; best[0] = x1[0]; best[1] = x1[1]; }
+        } else if (t > 1.0) {
+            dist = std::sqrt((x2[0] - node[0]) * (x2[0] - node[0]) + (x2[1] - node[1]) * (x2[1] - node[1]));
+            if (dist < minDist) { minDist = dist; best[0] = x2[0]; best[1] = x2[1]; }
+        }
+    }
+    nodeIn[0] = best[0]; nodeIn[1] = best[1];
+}
+// src/Mesh.cpp:179-231 projection3D: barycentric projection onto the boundary triangles that meet at the node; the node stays
+// where it is when no projection lands inside a triangle (all b >= 1e-10)
+static void projection3D(const Oracle &o, int nodeId, double *nodeIn) {
+    const double node[3] = {nodeIn[0], nodeIn[1], nodeIn[2]};
+    double best[3] = {0, 0, 0};
+    bool projWorked = false;
+    const double CHECK_EPS = 1e-10;
+    double minDist = INFINITY;
+    auto cross = [](const double *a, const double *b, double *c) {
+        c[0] = a[1] * b[2] - a[2] * b[1]; c[1] = a[2] * b[0] - a[0] * b[2]; c[2] = a[0] * b[1] - a[1] * b[0];
+    };
+    auto dot = [](const double *a, const double *b) { return a[0] * b[0] + a[1] * b[1] + a[2] * b[2]; };
+    for (int qi = o.facePtr[nodeId]; qi < o.facePtr[nodeId + 1]; qi++) {
+        const int *pid = &o.faceList[(size_t)o.faceIdx[qi] * 3];
+        const double *p0 = &o.Vp[(size_t)pid[0] * 3], *p1 = &o.Vp[(size_t)pid[1] * 3], *p2 = &o.Vp[(size_t)pid[2] * 3];
+        double u[3], v[3], w[3], n[3], uw[3], wv[3], b[3];
+        for (int l = 0; l < 3; l++) { u[l] = p1[l] - p0[l]; v[l] = p2[l] - p0[l]; w[l] = node[l] - p0[l]; }
+        cross(u, v, n);
+        const double temp = 1.0 / dot(n, n);
+        cross(u, w, uw);
+        cross(w, v, wv);
+        b[2] = dot(uw, n) * temp;
+        b[1] = dot(wv, n) * temp;
+        b[0] = 1.0 - b[1] - b[2];
+        double np[3];
+        for (int l = 0; l < 3; l++) np[l] = b[0] * p0[l] + b[1] * p1[l] + b[2] * p2[l];
+        const double dist = std::sqrt((np[0] - node[0]) * (np[0] - node[0]) + (np[1] - node[1]) * (np[1] - node[1]) +
+                                      (np[2] - node[2]) * (np[2] - node[2]));
+        if (dist < minDist && b[0] >= CHECK_EPS && b[1] >= CHECK_EPS && b[2] >= CHECK_EPS) {
+            minDist = dist;
+            best[0] = np[0]; best[1] = np[1]; best[2] = np[2];
+            projWorked = true;
+        }
+    }
+    if (projWorked) { nodeIn[0] = best[0]; nodeIn[1] = best[1]; nodeIn[2] = best[2]; }
+}
+template <int D> static inline void projectOntoBoundary(const Oracle &o, int nodeId, double *node) {   // src/Mesh.cpp:233-241
+    if (D == 2) projection2D(o, nodeId, node); else projection3D(o, nodeId, node);
+}
+
 // src/Mesh.cpp:777-872
 template <int D>
 static double bfgsOptSimplex(Oracle &o, int zId, double *z, const double *xi, int nIter, double tol, int &itersOut) {
@@ -488,6 +596,11 @@ static double prox(Oracle &o, double tol) {
         for (int k = 0; k < n; k++) z_i[k] = o.z[(size_t)n * i + k];
         int its = 0;
         o.Ih[i] = bfgsOptSimplex<D>(o, i, z_i, xi_i, 50, tol / 100, its);
+        if (o.projMask & 1)   // "Moving boundary points" (src/Mesh.cpp:975-984, commented out in the reference)
+            for (int nn = 0; nn < D + 1; nn++) {
+                const int v = o.F[(size_t)i * (D + 1) + nn];
+                if (o.mask[v] == BOUNDARY_FREE) projectOntoBoundary<D>(o, v, z_i + nn * D);
+            }
         for (int l = 0; l < n; l++) o.z[(size_t)n * i + l] = z_i[l];
         int tid = 0;
 #ifdef _OPENMP
@@ -725,7 +838,10 @@ static double step(Oracle &o, int nIters, double tol) {
     }
     o.lastAdmmIters = (i == nIters) ? nIters : i + 1;
     o.lastPrimal = primal; o.lastDual = duel;
-    // updateAfterStep: Vp <- x  (src/Mesh.cpp:1016-1036)
+    // updateAfterStep: Vp <- x  (src/Mesh.cpp:1016-1036); the projection of the FREE nodes there (:1020-1026) is commented out
+    if (o.projMask & 2)
+        for (int p = 0; p < o.P; p++)
+            if (o.mask[p] == BOUNDARY_FREE) projectOntoBoundary<D>(o, p, &o.x[(size_t)D * p]);
     o.Vp = o.x;
     o.stepsTaken++;
     return Ihstart;
@@ -1041,6 +1157,18 @@ void orc_destroy(void *h) { delete (Oracle *)h; }
 // Deep copy of the whole state (bench.py: every timed epoch restarts from the same post-warm-up snapshot instead of
 // repeating the warm-up steps) and the OpenMP thread count of the prox loop (src/Mesh.cpp:429,437 omp_set_num_threads).
 void *orc_clone(void *h) { return new Oracle(*(Oracle *)h); }
+// Boundary sliding option (see Oracle::projMask); builds the face lists (Mesh::buildFaceList) on first use.
+void orc_set_projection(void *h, int mask) {
+    Oracle &o = *(Oracle *)h;
+    if (mask && o.facePtr.empty()) { if (o.D == 2) buildFaceList<2>(o); else buildFaceList<3>(o); }
+    o.projMask = mask;
+}
+int orc_face_count(void *h) { Oracle &o = *(Oracle *)h; return (int)(o.faceList.size() / o.D); }
+void orc_project(void *h, int nodeId, double *node) {
+    Oracle &o = *(Oracle *)h;
+    if (o.facePtr.empty()) { if (o.D == 2) buildFaceList<2>(o); else buildFaceList<3>(o); }
+    if (o.D == 2) projection2D(o, nodeId, node); else projection3D(o, nodeId, node);
+}
 void orc_set_threads(void *h, int nthreads) { ((Oracle *)h)->nthreads = nthreads > 0 ? nthreads : 1; }
 
 int orc_step(void *h, int nIters, double tol, double *Ih, int *iters, double *primal, double *dual) {

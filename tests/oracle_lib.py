@@ -43,6 +43,9 @@ def lib():
         L.orc_clone.restype = C.c_void_p
         L.orc_clone.argtypes = [C.c_void_p]
         L.orc_set_threads.argtypes = [C.c_void_p, C.c_int]
+        L.orc_set_projection.argtypes = [C.c_void_p, C.c_int]
+        L.orc_face_count.argtypes = [C.c_void_p]
+        L.orc_project.argtypes = [C.c_void_p, C.c_int, c_dp]
         L.orc_step.restype = C.c_int
         L.orc_step.argtypes = [C.c_void_p, C.c_int, C.c_double, c_dp, c_ip, c_dp, c_dp]
         L.orc_euler_step.restype = C.c_int
@@ -127,6 +130,19 @@ class Oracle:
         other = copy.copy(self)
         other.h = self.L.orc_clone(self.h)
         return other
+
+    def set_projection(self, mask):
+        """Boundary sliding option (projectOntoBoundary, src/Mesh.cpp:118-241): bit 0 = after every element's BFGS solve in prox
+        (:975-984), bit 1 = in updateAfterStep (:1020-1026).  0 (default) = what the reference executes: no projection."""
+        self.L.orc_set_projection(self.h, int(mask))
+
+    def project(self, node_id, pnt):
+        p = np.ascontiguousarray(pnt, dtype=np.float64).copy()
+        self.L.orc_project(self.h, int(node_id), _dp(p))
+        return p
+
+    def face_count(self):
+        return self.L.orc_face_count(self.h)
 
     def set_threads(self, nthreads):
         self.L.orc_set_threads(self.h, int(nthreads))

@@ -373,3 +373,42 @@ def test_deferred_writeback_equals_strict(D, nx, kind):
     for mode in ("deferred", False):
         assert all(np.array_equal(a, b) for a, b in zip(res[mode][0], res[True][0]))
         assert np.array_equal(res[mode][1], res[True][1])
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("D,nx,kind,disc", [(2, 16, 1, False), (2, 20, 5, True), (3, 5, 4, False)])
+@pytest.mark.parametrize("mask_bits", [1, 2, 3])
+def test_boundary_sliding_matches_oracle(D, nx, kind, disc, mask_bits):
+    """Option "boundary_projection": Mesh::projectOntoBoundary (src/Mesh.cpp:118-241) at the two call sites of the ADMM path the
+    reference has commented out (:975-984 prox, :1020-1026 updateAfterStep).  NEW behaviour -- no reference result exists with it
+    on, so parity is GPU vs the CPU oracle only: 1e-9 on energies and positions, equal iteration counts, and the FREE nodes end
+    ON the boundary when the updateAfterStep site is active."""
+    if disc:
+        Vp, F, mask = mm.generate_disc_mesh(nx, 1.0, (0.0, 0.0), mm.BOUNDARY_FREE)
+        rho, tau, dt = 5.0, 0.1, 0.05
+    else:
+        Vp, F, mask = mm.generate_uniform_rect_mesh(D, nx, nx, nx if D == 3 else 0, boundary_type=mm.BOUNDARY_FREE)
+        rho, tau, dt = 50.0, 0.5, 0.025
+    mon = mm.TestMonitor(D, kind).evaluate_at_vertices(Vp)
+    orc, mesh, solver = pair(Vp, F, mask, mon, rho, tau, dt)
+    orc.set_projection(mask_bits)
+    solver.set_option("boundary_projection", mask_bits)
+    assert solver.L.mmadmm_set_option(solver.h, b"boundary_faces", 0) == orc.face_count() > 0
+    for s in range(6):
+        ih = solver.step(10, 1e-3); ro = orc.step(10, 1e-3)
+        assert ro["status"] == 0 and solver.last["iters"] == ro["iters"], (s, solver.last, ro)
+        assert abs(ih - ro["Ih"]) <= TOL_E2E * abs(ro["Ih"])
+        assert rel(mesh.Vp, orc.x()) < TOL_E2E, s
+    assert rel(solver.state(0), orc.z()) < TOL_E2E
+    free = mask == mm.BOUNDARY_FREE
+    moved = np.abs(mesh.Vp[free] - Vp[free]).max()
+    assert moved > 1e-6                              # the rim really slides
+    if mask_bits & 2 and not disc:
+        x = mesh.Vp[free]
+        assert np.abs(np.minimum(x, 1 - x).min(axis=1)).max() < 1e-14     # ... along the faces of the box
+    # the default (what the reference executes) is unchanged: a different trajectory
+    orc0, mesh0, solver0 = pair(Vp, F, mask, mon, rho, tau, dt)
+    for s in range(6):
+        solver0.step(10, 1e-3)
+    assert rel(mesh0.Vp, mesh.Vp) > 1e-6
+    solver.close(); solver0.close()
