@@ -81,6 +81,14 @@ int mmadmm_backward_euler_jacobian(mmadmm_ctx *ctx, int *sizes2, int *rowptr, in
  * rebuilds the diagonal of t = M + dt^2 (WD)^T(WD).  Must be called before the first mmadmm_step. */
 int mmadmm_set_dt(mmadmm_ctx *ctx, double dt);
 
+/* What the commented-out body of Mesh<D>::setUp would do every step (src/Mesh.cpp:1006-1014: mapEvaluator->updateMesh(Vp, F);
+ * mapEvaluator->interpolateMonitor(*Mon)): rebuild the monitor interpolation grid (bounding box, axes, exact 1-NN vertex -> grid
+ * map, Jacobi smoothing; src/MeshInterpolator.cpp:67-130,165-259,365-404) on the device from the CURRENT node positions, with the
+ * monitor tensors monVertex (P x D*D; GLOBAL P on a distributed context, same array on every rank: collective call) that the
+ * caller evaluated at those positions (mmadmm_get_x).  For moving-front problems; the reference itself never re-interpolates
+ *  and the default path does not call this. */
+int mmadmm_update_monitor(mmadmm_ctx *ctx, const double *monVertex);
+
 /* Replaces MeshIntegrator<D>::getEnergy -> Mesh::computeEnergy (src/Mesh.cpp:496-530). */
 int mmadmm_energy(mmadmm_ctx *ctx, double *I);
 

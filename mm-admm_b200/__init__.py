@@ -34,7 +34,7 @@ ABI_SYMBOLS = [
     "mmadmm_version", "mmadmm_plan_create", "mmadmm_plan_sizes", "mmadmm_plan_get", "mmadmm_plan_destroy",
     "mmadmm_comm_unique_id", "mmadmm_create_dist", "mmadmm_local_sizes", "mmadmm_get_x_local",
     "mmadmm_pcg_create", "mmadmm_pcg_solve", "mmadmm_pcg_solve_device", "mmadmm_pcg_bicgstab", "mmadmm_pcg_bicgstab_device", "mmadmm_pcg_spmv", "mmadmm_pcg_precond",
-    "mmadmm_set_writeback", "mmadmm_writeback_fence", "mmadmm_checkpoint", "mmadmm_restore",
+    "mmadmm_update_monitor", "mmadmm_set_writeback", "mmadmm_writeback_fence", "mmadmm_checkpoint", "mmadmm_restore",
     "mmadmm_pcg_get_ilu", "mmadmm_pcg_set_option", "mmadmm_pcg_info", "mmadmm_pcg_time_spmv", "mmadmm_pcg_last_error", "mmadmm_pcg_destroy", "mmadmm_measure_fp64_peak",
 ]
 
@@ -90,6 +90,7 @@ def lib():
         L.mmadmm_get_x_device.argtypes = [vp, vp]
         L.mmadmm_get_F.argtypes = [vp, _c_ip]
         L.mmadmm_get_x_colmajor.argtypes = [vp, _c_dp]
+        L.mmadmm_update_monitor.argtypes = [vp, _c_dp]
         L.mmadmm_set_writeback.argtypes = [vp, _c_dp, C.c_int, C.c_int]
         L.mmadmm_writeback_fence.argtypes = [vp]
         L.mmadmm_checkpoint.argtypes = [vp]
@@ -390,6 +391,14 @@ class MeshIntegrator:
         mode = {False: 0, None: 0, True: 1, "strict": 1, "deferred": 2}[v]
         self._check(self.L.mmadmm_set_writeback(self.h, _dp(self.mesh.Vp) if mode else None, 0, mode))
         self._sync_vp = v
+
+    def update_monitor(self, monitor):
+        """Rebuild the monitor grid from the current node positions (what the commented-out Mesh::setUp would do,
+        src/Mesh.cpp:1006-1014).  `monitor`: object with evaluate_at_vertices(X), or the table (P, D*D) evaluated at x()."""
+        mon = monitor.evaluate_at_vertices(self.x()) if hasattr(monitor, "evaluate_at_vertices") else monitor
+        mon = np.ascontiguousarray(mon, dtype=np.float64).reshape(self.mesh.P, self.mesh.D ** 2)
+        self._check(self.L.mmadmm_update_monitor(self.h, _dp(mon)))
+        self.mesh.mon_vertex = mon
 
     def fence(self):
         """Wait for a deferred write-back of mesh.Vp to land."""

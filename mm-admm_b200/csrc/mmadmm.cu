@@ -3245,6 +3245,20 @@ int mmadmm_get_x_colmajor(mmadmm_ctx *ctx, double *VpColMajor) {
     return MMADMM_OK;
 }
 
+int mmadmm_update_monitor(mmadmm_ctx *ctx, const double *monVertex) {
+    if (!ctx || !monVertex) return MMADMM_EINVAL;
+    CK(cudaSetDevice(ctx->device));
+    const int Pg = ctx->dist ? ctx->Pglobal : ctx->P;
+    std::vector<double> xh((size_t)Pg * ctx->D);
+    int rc = mmadmm_get_x(ctx, xh.data());     // current node positions (assembled over the ranks on a distributed context)
+    if (rc) return rc;
+    CK(cudaStreamSynchronize(ctx->stream));
+    cudaFree(ctx->grid); cudaFree(ctx->gridIso); cudaFree(ctx->ax); cudaFree(ctx->ay); cudaFree(ctx->az);
+    ctx->grid = ctx->gridIso = ctx->ax = ctx->ay = ctx->az = nullptr;
+    ctx->gridIsIso = false;
+    return (ctx->D == 2) ? build_monitor_grid<2>(ctx, Pg, xh.data(), monVertex) : build_monitor_grid<3>(ctx, Pg, xh.data(), monVertex);
+}
+
 int mmadmm_set_writeback(mmadmm_ctx *ctx, double *VpHost, int colMajor, int mode) {
     if (!ctx || mode < 0 || mode > 2 || (mode != 0 && !VpHost)) return MMADMM_EINVAL;
     CK(cudaSetDevice(ctx->device));

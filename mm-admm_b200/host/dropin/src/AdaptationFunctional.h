@@ -1,5 +1,6 @@
 // AdaptationFunctional<D> / HuangFunctional<D>: interface types of the reference (src/AdaptationFunctional.h:8-54,
-// src/HuangFunctional.h:11-39) kept for source compatibility.  In the reference the virtual G/dGdJ/... members are
+// src/HuangFunctional.h:11-39) kept for source compatibility, virtual G / dGdJ / dGddet / dGdM / dGdX included (HuangFunctional.h
+// holds their Huang-functional bodies, restated from src/HuangFunctional.cpp:35-90).  In the reference those virtuals are
 // never called -- blockGrad inlines Huang's functional with p = 3/2, theta = 1/3 (src/AdaptationFunctional.cpp:210-211)
 // -- and the same arithmetic is the device function block_grad<D> in mm-admm_b200/csrc/mmadmm_device.cuh.
 // blockGrad here evaluates element zId of a live Mesh through the C ABI (mmadmm_block_grad_at).
@@ -31,12 +32,18 @@ public:
     }
 protected:
     mmadmm_ctx *ctx;
+    // the functional's pieces as the reference declares them (src/AdaptationFunctional.h:19-31); M is the INVERSE monitor
+    // tensor in every implementation the reference ships
+    virtual double G(Eigen::Matrix<double,D,D> &J, double det, Eigen::Matrix<double,D,D> &M, Eigen::Vector<double,D> &x) = 0;
+    virtual void dGdJ(Eigen::Matrix<double,D,D> &J, double det, Eigen::Matrix<double,D,D> &M, Eigen::Vector<double,D> &x,
+                      Eigen::Matrix<double,D,D> &out) = 0;
+    virtual double dGddet(Eigen::Matrix<double,D,D> &J, double det, Eigen::Matrix<double,D,D> &M, Eigen::Vector<double,D> &x) = 0;
+    virtual void dGdM(Eigen::Matrix<double,D,D> &J, double det, Eigen::Matrix<double,D,D> &M, Eigen::Vector<double,D> &x,
+                      Eigen::Matrix<double,D,D> &out) = 0;
+    virtual void dGdX(Eigen::Matrix<double,D,D> &J, double det, Eigen::Matrix<double,D,D> &M, Eigen::Vector<double,D> &x,
+                      Eigen::Vector<double,D> &out) = 0;
 };
 
-template <int D>
-class HuangFunctional : public AdaptationFunctional<D> {
-public:
-    explicit HuangFunctional(mmadmm_ctx *ctx_) : AdaptationFunctional<D>(ctx_) {}
-};
+#include "HuangFunctional.h"
 
 #endif

@@ -39,6 +39,7 @@
 #include "AdaptationFunctional.h"
 #include "MonitorFunction.h"
 #include "NodeType.h"
+#include "MeshIO.h"
 #include "mmadmm.h"
 
 using namespace std;
@@ -259,30 +260,24 @@ public:
     }
     void fenceVp() { check(mmadmm_writeback_fence(ctx), "mmadmm_writeback_fence"); }
 
-    // result writers, formats of src/Mesh.cpp:1049-1095
+    // result writers, formats of src/Mesh.cpp:1049-1095 (byte-identical text; formatted by all host threads, MeshIO.h);
+    // MMADMM_BINARY_IO=1 also writes the exact binary twin "<fname>.bin"
     void outputSimplices(const char *fname) {
-        std::ofstream out(fname);
-        for (int i = 0; i < F->rows(); i++) {
-            for (int j = 0; j < D; j++) out << (*F)(i, j) << ", ";
-            out << (*F)(i, D) << endl;
-        }
+        std::function<int(long, int)> v = [this](long i, int j) { return (*F)(i, j); };
+        if (!meshio::write_text<int>(fname, F->rows(), D + 1, v)) cerr << "mm-admm_b200: cannot write " << fname << endl;
+        if (meshio::binary_twin()) meshio::write_bin<int>((string(fname) + ".bin").c_str(), F->rows(), D + 1, v);
     }
     void outputPoints(const char *fname) {
         fenceVp();
-        std::ofstream out(fname);
-        for (int i = 0; i < Vp->rows(); i++) {
-            for (int j = 0; j < D-1; j++) out << (*Vp)(i, j) << ", ";
-            out << (*Vp)(i, D-1) << endl;
-        }
+        std::function<double(long, int)> v = [this](long i, int j) { return (*Vp)(i, j); };
+        if (!meshio::write_text<double>(fname, Vp->rows(), D, v)) cerr << "mm-admm_b200: cannot write " << fname << endl;
+        if (meshio::binary_twin()) meshio::write_bin<double>((string(fname) + ".bin").c_str(), Vp->rows(), D, v);
     }
     void outputBoundaryNodes(const char *fname) {
         fenceVp();
-        std::ofstream out(fname);
-        for (int i = 0; i < Vp->rows(); i++) {
-            if (boundaryMask->at(i) == INTERIOR) continue;
-            for (int j = 0; j < D-1; j++) out << (*Vp)(i, j) << ", ";
-            out << (*Vp)(i, D-1) << endl;
-        }
+        std::function<double(long, int)> v = [this](long i, int j) { return (*Vp)(i, j); };
+        std::function<bool(long)> keep = [this](long i) { return boundaryMask->at(i) != INTERIOR; };
+        if (!meshio::write_text<double>(fname, Vp->rows(), D, v, keep)) cerr << "mm-admm_b200: cannot write " << fname << endl;
     }
 
     // status code of the C ABI -> the reference's behaviour on a failed assert / exit(1): message + abort

@@ -7,6 +7,7 @@
 #define MESH_UTILS_H
 
 #include <Eigen/Dense>
+#include "MeshIO.h"
 #include <algorithm>
 #include <cassert>
 #include <cmath>
@@ -25,6 +26,7 @@
 
 #include "Mesh.h"
 #include "NodeType.h"
+#include "MeshIO.h"
 
 using namespace std;
 
@@ -309,35 +311,22 @@ inline void meshFromLevelSetFun(std::function<double(double, double, double)> ph
 
 // Comma-separated simplices and points, one mask value per line (src/MeshUtils.h:669-733).  The mask reader of the
 // reference pushes one extra (repeated) entry at end of file; kept, the Mesh only reads the first P entries.
+// utils::readTriangles (src/MeshUtils.h:669-733).  Whole-file scans instead of a stringstream per line (MeshIO.h); each of the
+// three files may also be the binary table Mesh::output* writes with MMADMM_BINARY_IO=1.  The mask keeps the reference's quirk:
+// its `while (fin) { fin >> tmp; push_back(tmp); }` loop pushes one entry more than the file holds (the failed extraction
+// at end of file stores 0 since C++11), so the mask has P + 1 entries.
 inline void readTriangles(int D, const char *triFileName, const char *pntFileName, const char *maskFileName,
         Eigen::MatrixXi &F, Eigen::MatrixXd &Vp, vector<NodeType> &boundaryMask) {
     vector<double> pntData;
-    vector<int> triData;
-    string line, word;
-    {
-        ifstream fin(triFileName);
-        if (!fin) { cerr << "cannot open " << triFileName << endl; assert(false); exit(1); }
-        while (getline(fin, line)) {
-            stringstream s(line);
-            while (getline(s, word, ',')) triData.push_back(stoi(word));
-        }
-    }
-    {
-        ifstream fin(pntFileName);
-        if (!fin) { cerr << "cannot open " << pntFileName << endl; exit(1); }
-        while (getline(fin, line)) {
-            stringstream s(line);
-            while (getline(s, word, ',')) pntData.push_back(stod(word));
-        }
-    }
-    {
-        ifstream fin(maskFileName);
-        boundaryMask.clear();
-        int tmp = 0;
-        while (fin) {
-            fin >> tmp;
-            boundaryMask.push_back((NodeType)tmp);
-        }
+    vector<int> triData, maskData;
+    if (!meshio::read_ints(triFileName, triData)) { cerr << "cannot open " << triFileName << endl; assert(false); exit(1); }
+    if (!meshio::read_doubles(pntFileName, pntData)) { cerr << "cannot open " << pntFileName << endl; exit(1); }
+    boundaryMask.clear();
+    if (meshio::read_ints(maskFileName, maskData)) {
+        for (size_t i = 0; i < maskData.size(); i++) boundaryMask.push_back((NodeType)maskData[i]);
+        boundaryMask.push_back((NodeType)0);
+    } else {
+        boundaryMask.push_back((NodeType)0);     // unreadable file: the reference's loop still pushes one (zero) entry
     }
     F.resize(triData.size() / (D + 1), D + 1);
     Vp.resize(pntData.size() / D, D);

@@ -1163,6 +1163,15 @@ void orc_set_projection(void *h, int mask) {
     if (mask && o.facePtr.empty()) { if (o.D == 2) buildFaceList<2>(o); else buildFaceList<3>(o); }
     o.projMask = mask;
 }
+// What the commented-out body of Mesh::setUp would do (src/Mesh.cpp:1006-1014: mapEvaluator->updateMesh(Vp, F);
+// mapEvaluator->interpolateMonitor(*Mon)): rebuild the monitor interpolation grid from the CURRENT node positions Vp with the
+// monitor evaluated there.  (In the reference interpolateMonitor can run only once -- it deletes monGridTemp,
+// src/MeshInterpolator.cpp:243-259 -- so this is a "next" row of SURVEY 8f, not something the reference executes.)
+void orc_update_monitor(void *h, const double *monVertex) {
+    Oracle &o = *(Oracle *)h;
+    o.monVals.assign(monVertex, monVertex + (size_t)o.P * o.D * o.D);
+    buildMonitorGrid(o);
+}
 int orc_face_count(void *h) { Oracle &o = *(Oracle *)h; return (int)(o.faceList.size() / o.D); }
 void orc_project(void *h, int nodeId, double *node) {
     Oracle &o = *(Oracle *)h;

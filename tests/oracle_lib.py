@@ -45,6 +45,7 @@ def lib():
         L.orc_set_threads.argtypes = [C.c_void_p, C.c_int]
         L.orc_set_projection.argtypes = [C.c_void_p, C.c_int]
         L.orc_face_count.argtypes = [C.c_void_p]
+        L.orc_update_monitor.argtypes = [C.c_void_p, c_dp]
         L.orc_project.argtypes = [C.c_void_p, C.c_int, c_dp]
         L.orc_step.restype = C.c_int
         L.orc_step.argtypes = [C.c_void_p, C.c_int, C.c_double, c_dp, c_ip, c_dp, c_dp]
@@ -143,6 +144,11 @@ class Oracle:
 
     def face_count(self):
         return self.L.orc_face_count(self.h)
+
+    def update_monitor(self, mon_vertex):
+        """Rebuild the monitor grid from the current node positions (the commented-out Mesh::setUp, src/Mesh.cpp:1006-1014)."""
+        self.mon = np.ascontiguousarray(mon_vertex, dtype=np.float64)
+        self.L.orc_update_monitor(self.h, _dp(self.mon))
 
     def set_threads(self, nthreads):
         self.L.orc_set_threads(self.h, int(nthreads))

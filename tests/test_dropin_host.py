@@ -93,7 +93,10 @@ def test_level_set_mesh_matches_reference_algorithm(checker):
 
 def test_shims(checker):
     _, out = checker
-    lines = dict((ln.split(" ", 1)[0], ln.split(" ", 1)[1]) for ln in out.strip().split("\n") if not ln.startswith("mon"))
+    lines = dict((ln.split(" ", 1)[0], ln.split(" ", 1)[1]) for ln in out.strip().split("\n") if not ln.startswith(("mon", "huang", "meshio")))
+    # MeshIO.h: the parallel writers give the bytes of the reference's per-line ostream loops (src/Mesh.cpp:1049-1095), the binary
+    # twin round-trips exactly, readTriangles takes both formats
+    assert "meshio text identical" in out and "meshio bin exact" in out and "meshio read ok" in out
     assert lines["removeRow"] == "ok"
     mons = [[float(v) for v in ln.split()[1:]] for ln in out.split("\n") if ln.startswith("mon ")]
     X = np.array([[0.1, 0.2], [0.5, 0.5], [0.9, 0.3]])
@@ -104,3 +107,29 @@ def test_shims(checker):
     assert lines["json"] == "40 0.025000000000000001 0 SquareGrid SquareGrid 0 1"   # cout precision 17
     # nlohmann's compact dump: keys sorted, integers stay integers
     assert lines["dump"] == '{"CompMesh":false,"Method":2,"TestType":"SquareGrid","dt":0.025,"nx":40,"rho":5,"tau":0.1}'
+
+
+def test_huang_functional_virtual_interface(checker):
+    """HuangFunctional<D>::G / dGdJ / dGddet / dGdM / dGdX (src/HuangFunctional.h:26-38, src/HuangFunctional.cpp:35-90) kept in the
+    drop-in headers: values against a numpy restatement of the same formulas (p = 3/2, theta = 1/3 hard-coded; dGddet's
+    theta = 1/2 quirk makes it 0), and dGdJ against a central difference of G at fixed determinant."""
+    _, out = checker
+    h = {}
+    for ln in out.split("\n"):
+        if ln.startswith("huang "):
+            w = ln.split()
+            h[w[1]] = w[2:]
+    J = np.array([[1.3, 0.2], [-0.1, 0.9]]); Minv = np.array([[0.7, 0.1], [0.1, 1.4]])
+    d, p, th = 2.0, 1.5, 1.0 / 3.0
+    det = np.linalg.det(J)
+    detM = np.sqrt(1.0 / np.linalg.det(Minv))
+    tr = np.trace(J @ Minv @ J.T)
+    G = th * detM * tr ** (d * p / 2) + (1 - 2 * th) * d ** (d * p / 2) * detM * (det / detM) ** p
+    assert abs(float(h["G"][0]) - G) <= 1e-13 * abs(G)
+    assert float(h["G"][2]) == 0.0 and [float(v) for v in h["G"][4:6]] == [0.0, 0.0]        # dGddet (quirk), dGdX
+    dJ = d * p * th * detM * tr ** (d * p / 2 - 1) * (Minv @ J.T)
+    assert np.allclose([float(v) for v in h["dGdJ"]], dJ.reshape(-1), rtol=1e-13)
+    dM = (-0.5 * th * d * p * detM * tr ** (d * p / 2 - 1) * (Minv.T @ J.T @ J @ Minv) + 0.5 * th * detM * tr ** (d * p / 2) * Minv
+          + ((0.5 - th) * (1 - p) * d ** (d * p / 2)) * detM ** (1 - p) * det ** p * Minv)
+    assert np.allclose([float(v) for v in h["dGdM"]], dM.reshape(-1), rtol=1e-13)
+    assert np.allclose([float(v) for v in h["fdJ"]], dJ.reshape(-1), rtol=1e-7)            # out(j, i) = dG/dJ(i, j)

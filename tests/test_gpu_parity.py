@@ -415,3 +415,28 @@ def test_boundary_sliding_matches_oracle(D, nx, kind, disc, mask_bits):
         solver0.step(10, 1e-3)
     assert rel(mesh0.Vp, mesh.Vp) > 1e-6
     solver.close(); solver0.close()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("D,nx,kind", [(2, 24, 4), (3, 6, 3)])
+def test_monitor_reinterpolation_matches_oracle(D, nx, kind):
+    """mmadmm_update_monitor = the body the reference commented out of Mesh::setUp (src/Mesh.cpp:1006-1014): after a few steps the
+    grid is rebuilt from the moved mesh with the monitor evaluated at the new vertices -- bit-identical to the oracle's rebuild
+    (same exact 1-NN, same Jacobi sweeps) -- and the run continues within 1e-9."""
+    Vp, F, mask = mm.generate_uniform_rect_mesh(D, nx, nx, nx if D == 3 else 0)
+    M = mm.TestMonitor(D, kind)
+    mon = M.evaluate_at_vertices(Vp)
+    orc, mesh, solver = pair(Vp, F, mask, mon, 50.0, 0.5, 0.025)
+    for rounds in range(2):
+        for s in range(3):
+            ih = solver.step(10, 1e-3); ro = orc.step(10, 1e-3)
+            assert ro["status"] == 0 and solver.last["iters"] == ro["iters"]
+            assert abs(ih - ro["Ih"]) <= TOL_E2E * abs(ro["Ih"])
+        assert rel(mesh.Vp, orc.x()) < TOL_E2E
+        xo = orc.x()
+        orc.update_monitor(M.evaluate_at_vertices(xo))
+        solver.update_monitor(M.evaluate_at_vertices(xo))       # the same table on both sides: the grids must be bit-identical
+        assert solver.grid_dims() == orc.grid_dims()
+        g = solver.state(5)
+        assert np.array_equal(g, orc.grid()[: g.shape[0]])
+    solver.close()
