@@ -1107,12 +1107,14 @@ __global__ void __launch_bounds__(TPB_V, MINB) k_xupdate(int P, size_t Es, const
                                                    const double *u, const double *zsrc, const double *xBar,
                                                    const double *tdiag, double m, double dtsq, double w, double *x,
                                                    double *partPrimal, const int *sharedSlot, double *sPart, const int *vorder,
-                                                   double *usum, const HaloPush hp) {
+                                                   double *usum, const HaloPush hp, const int skipShared) {
     static_assert(!UREC || (PRIMAL && !ZSRC && !UZERO), "the recurrence belongs to the update that follows a prox sweep");
     __shared__ double red[32];
     const int tix = blockIdx.x * TPB_V + threadIdx.x;
     double prim = 0.0;
-    if (tix < P) {
+    // skipShared: the vertices shared with other ranks were handled by an earlier launch over the shared list (their partial
+    // sums are already on their way to the neighbours while this launch does the bulk of the vertices)
+    if (tix < P && !(skipShared && sharedSlot[vorder[tix]] >= 0)) {
         const int p = vorder[tix];   // vertices in the order of their first incident element: neighbouring threads
                                      // read neighbouring element slots in every plane (2.4x less DRAM traffic)
         double s[D], zs[D], xn[D], us[D];
@@ -1319,10 +1321,11 @@ __global__ void __launch_bounds__(TPB_V) k_predict_extrap(size_t N, const double
 template <int D, bool EXTRAP>
 __global__ void __launch_bounds__(TPB_V) k_xfirst(size_t N, const int *incPtr, const double *usum, const double *zsrc, double *xBar,
                                                   double *xPrev, const double *tdiag, double m, double dtsq, double w, double *x,
-                                                  const int *sharedSlot) {
+                                                  const int *sharedSlot, const int skipShared) {
     const size_t i = (size_t)blockIdx.x * TPB_V + threadIdx.x;
     if (i >= N) return;
     const int p = (int)(i / D);
+    if (skipShared && sharedSlot[p] >= 0) return;   // predictor of the shared vertices already done (k_predict_shared)
     double xb, zs;
     if (EXTRAP) {
         const double xv = x[i];
@@ -1338,6 +1341,19 @@ __global__ void __launch_bounds__(TPB_V) k_xfirst(size_t N, const int *incPtr, c
     const double val = (double)(incPtr[p + 1] - incPtr[p]);
     const double sv = w * (w * (val * zs - usum[i]));
     x[i] = ((m * xb) + dtsq * sv) / tdiag[p];
+}
+
+// K7 for the vertices shared with other ranks only (so that their partial sums can be formed and pushed before the bulk pass)
+template <int D> __global__ void k_predict_shared(int nShared, const int *sharedIdx, const double *x, double *xBar, double *xPrev) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= nShared) return;
+    const int p = sharedIdx[i];
+#pragma unroll
+    for (int l = 0; l < D; l++) {
+        const double xv = x[(size_t)D * p + l];
+        xBar[(size_t)D * p + l] = 2 * xv - xPrev[(size_t)D * p + l];
+        xPrev[(size_t)D * p + l] = xv;
+    }
 }
 
 // Isotropy of the monitor grid: flag stays 1 iff every row is m*I bitwise (equal diagonal, zero off-diagonal); the scalars
@@ -1659,6 +1675,7 @@ struct mmadmm_ctx {
     } wb;
 
     double gridO[3] = {0, 0, 0}, gridRh[3] = {0, 0, 0};
+    double locMin[3] = {0, 0, 0}, locMax[3] = {-1, -1, -1};   // bounding box of this rank's vertices (create_impl)
     MonGrid monGrid() const {
         MonGrid mg;
         mg.vals = grid; mg.iso = (isoOn && gridIsIso) ? gridIso : nullptr; mg.ax = ax; mg.ay = ay; mg.az = az; mg.nx = nx; mg.ny = ny; mg.nz = nz;
@@ -2280,13 +2297,23 @@ template <int D> int build_monitor_grid(mmadmm_ctx *ctx, int P, const double *Vp
             int maxPersist = 0, maxWin = 0;
             cudaDeviceGetAttribute(&maxPersist, cudaDevAttrMaxPersistingL2CacheSize, ctx->device);
             cudaDeviceGetAttribute(&maxWin, cudaDevAttrMaxAccessPolicyWindowSize, ctx->device);
-            const size_t bytes = sizeof(double) * ctx->gridRows;
+            // On a distributed context every rank holds the whole grid (built from the global vertex set) but looks up only the
+            // slab its own vertices live in: element blocks of the box mesh cut along z, the slowest grid index, so that slab is
+            // one contiguous range of planes.  The window covers those planes (+2 on either side: nodes move) instead of a
+            // fraction of everything -- at N = 8 on the C4 ladder the grid is 199 MB, the slab 25 MB.
+            const size_t sl = (size_t)(ctx->nx + 1) * (ctx->ny + 1);
+            long z0 = 0, z1 = ctx->nz;
+            if (ctx->dist && ctx->locMax[2] >= ctx->locMin[2]) {
+                z0 = std::max(0l, (long)std::floor((ctx->locMin[2] - ctx->gridO[2]) * ctx->gridRh[2]) - 2);
+                z1 = std::min((long)ctx->nz, (long)std::floor((ctx->locMax[2] - ctx->gridO[2]) * ctx->gridRh[2]) + 3);
+            }
+            const size_t bytes = sizeof(double) * sl * (size_t)(z1 - z0 + 1);
             if (maxPersist > 0 && maxWin > 0) {
                 const size_t lim = std::min<size_t>((size_t)maxPersist, bytes);
                 cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, lim);
                 cudaStreamAttrValue av;
                 memset(&av, 0, sizeof(av));
-                av.accessPolicyWindow.base_ptr = ctx->gridIso;
+                av.accessPolicyWindow.base_ptr = ctx->gridIso + sl * (size_t)z0;
                 av.accessPolicyWindow.num_bytes = std::min<size_t>(bytes, (size_t)maxWin);
                 av.accessPolicyWindow.hitRatio = (float)std::min(1.0, (double)lim / (double)av.accessPolicyWindow.num_bytes);
                 av.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
@@ -2396,6 +2423,11 @@ int create_impl(mmadmm_ctx *ctx, const double *Vp, const double *Vc, const int *
     CK(cudaStreamSynchronize(st));
     ctx->launches++;
 
+    for (int l = 0; l < D; l++) {
+        double lo = INFINITY, hi = -INFINITY;
+        for (int pp = 0; pp < P; pp++) { const double v = Vp[(size_t)pp * D + l]; lo = v < lo ? v : lo; hi = v > hi ? v : hi; }
+        ctx->locMin[l] = lo; ctx->locMax[l] = hi;
+    }
     rc = build_monitor_grid<D>(ctx, G.Pgrid, G.VpGrid, G.monGrid);
     if (rc) return rc;
 
@@ -2417,7 +2449,7 @@ int create_impl(mmadmm_ctx *ctx, const double *Vp, const double *Vc, const int *
     ctx->nblkProx = std::max(cdiv(E, 32), 148 * 64);   // upper bound over the prox tile sizes / persistent warps
     CK(cudaMalloc(&ctx->partIh, sizeof(double) * ctx->nblkProx));
     CK(cudaMalloc(&ctx->partDual, sizeof(double) * ctx->nblkProx));
-    CK(cudaMalloc(&ctx->partPrimal, sizeof(double) * (size_t)(std::max(ctx->nblkE, ctx->nblkV) + ctx->nblkV + 1)));
+    CK(cudaMalloc(&ctx->partPrimal, sizeof(double) * (size_t)(std::max(ctx->nblkE, ctx->nblkV) + 3 * ctx->nblkV + 1)));
     CK(cudaMalloc(&ctx->scal_d, sizeof(double) * 8));
     CK(cudaMemsetAsync(ctx->scal_d, 0, sizeof(double) * 8, st));
     CK(cudaHostAlloc(&ctx->scal_h, sizeof(double) * 8, cudaHostAllocMapped));
@@ -2680,34 +2712,44 @@ template <> int launch_prox<3>(mmadmm_ctx *ctx, const ElemArgs<3> &a) {
 
 // x-update (+ primal residual partials).  Distributed: local kernel -> shared-vertex partials -> exchange -> k_xfinish.
 //   sharedOnly: the vertices that are not shared were already solved by k_xfirst
-template <int D, bool ZSRC, bool UZERO, bool PRIMAL, bool UREC = false>
-int launch_xupdate_t(mmadmm_ctx *ctx, const double *zsrc, bool sharedOnly = false) {
+// The x-update in three pieces.  On a distributed context with the NVLink mailbox exchange they run in the order
+//   xupdate_shared (partial sums of the shared vertices -> sPart AND straight into the neighbours' mailboxes)
+//   bulk pass over all other vertices            <- the halo is in flight meanwhile
+//   xupdate_finish (wait for the neighbours' epoch, rank-ordered sum, x and primal share of the shared vertices)
+// so the latency of the exchange and the skew between the ranks hide behind the bulk pass.
+template <int D, bool ZSRC, bool UZERO, bool PRIMAL, bool UREC>
+int xupdate_shared(mmadmm_ctx *ctx, const double *zsrc, bool push, unsigned long long &ep) {
     const double dtsq = ctx->dt * ctx->dt;
-    const bool exch = ctx->dist && ctx->nShared > 0;
     HaloPush hp;
-    unsigned long long ep = 0;
-    if (exch && ctx->p2p) {   // the kernel that forms the partial sums also stores them into the sharers' mailboxes (NVLink)
+    if (push) {
         ep = ++ctx->haloEpoch;
         hp.ptr = ctx->pushPtr_d; hp.nbr = ctx->pushNbr_d; hp.pos = ctx->pushPos_d;
         hp.peerRecv = ctx->peerRecv_d; hp.peerStride = ctx->peerRecvStride_d; hp.peerFlag = ctx->peerHaloFlag_d;
         hp.ticket = ctx->pushTicket_d; hp.nNbr = (int)ctx->nbrRank.size(); hp.epoch = ep;
     }
-    if (!sharedOnly) {
-        // chunk size / occupancy of the recurrence form, measured on C2 and C4: 2D 2 slots per chunk at full occupancy
-        // (32 registers), 3D 8 slots per chunk (80 registers); the differences are a few per cent of the kernel
-        auto kern = !UREC ? k_xupdate<D, ZSRC, UZERO, PRIMAL, UREC>
-                          : (D == 2 ? k_xupdate<D, ZSRC, UZERO, PRIMAL, UREC, 2, 8> : k_xupdate<D, ZSRC, UZERO, PRIMAL, UREC, 8, 1>);
-        kern<<<ctx->nblkV, TPB_V, 0, ctx->stream>>>(
-            ctx->P, ctx->Es, ctx->incPtr, ctx->incIdx, ctx->z, ctx->u, zsrc, ctx->xBar, ctx->tdiag, ctx->m, dtsq, ctx->w, ctx->x,
-            ctx->partPrimal, ctx->dist ? ctx->sharedSlot : nullptr, ctx->sPart, ctx->vorder, ctx->usum, hp);
-        ctx->launches++;
-    } else if (exch) {
-        k_xupdate<D, ZSRC, UZERO, PRIMAL, UREC><<<ctx->nblkSh, TPB_V, 0, ctx->stream>>>(
-            ctx->nShared, ctx->Es, ctx->incPtr, ctx->incIdx, ctx->z, ctx->u, zsrc, ctx->xBar, ctx->tdiag, ctx->m, dtsq, ctx->w, ctx->x,
-            ctx->partPrimal, ctx->sharedSlot, ctx->sPart, ctx->sharedIdx, ctx->usum, hp);
-        ctx->launches++;
-    }
-    if (!exch) return MMADMM_OK;
+    // primal partials of this launch are all zero (shared vertices leave theirs to xupdate_finish): scratch region
+    k_xupdate<D, ZSRC, UZERO, PRIMAL, UREC><<<ctx->nblkSh, TPB_V, 0, ctx->stream>>>(
+        ctx->nShared, ctx->Es, ctx->incPtr, ctx->incIdx, ctx->z, ctx->u, zsrc, ctx->xBar, ctx->tdiag, ctx->m, dtsq, ctx->w, ctx->x,
+        ctx->partPrimal + ctx->nblkV + ctx->nblkSh, ctx->sharedSlot, ctx->sPart, ctx->sharedIdx, ctx->usum, hp, 0);
+    ctx->launches++;
+    return MMADMM_OK;
+}
+template <int D, bool ZSRC, bool UZERO, bool PRIMAL, bool UREC>
+int xupdate_bulk(mmadmm_ctx *ctx, const double *zsrc, bool skipShared) {
+    const double dtsq = ctx->dt * ctx->dt;
+    // chunk size / occupancy of the recurrence form, measured on C2 and C4: 2D 2 slots per chunk at full occupancy
+    // (32 registers), 3D 8 slots per chunk (80 registers); the differences are a few per cent of the kernel
+    auto kern = !UREC ? k_xupdate<D, ZSRC, UZERO, PRIMAL, UREC>
+                      : (D == 2 ? k_xupdate<D, ZSRC, UZERO, PRIMAL, UREC, 2, 8> : k_xupdate<D, ZSRC, UZERO, PRIMAL, UREC, 8, 1>);
+    kern<<<ctx->nblkV, TPB_V, 0, ctx->stream>>>(
+        ctx->P, ctx->Es, ctx->incPtr, ctx->incIdx, ctx->z, ctx->u, zsrc, ctx->xBar, ctx->tdiag, ctx->m, dtsq, ctx->w, ctx->x,
+        ctx->partPrimal, ctx->dist ? ctx->sharedSlot : nullptr, ctx->sPart, ctx->vorder, ctx->usum, HaloPush(), skipShared ? 1 : 0);
+    ctx->launches++;
+    return MMADMM_OK;
+}
+template <int D, bool ZSRC, bool PRIMAL>
+int xupdate_finish(mmadmm_ctx *ctx, const double *zsrc, unsigned long long ep) {
+    const double dtsq = ctx->dt * ctx->dt;
     if (ctx->p2p) {
         k_xfinish_p2p<D, ZSRC, PRIMAL><<<ctx->nblkSh, TPB_V, 0, ctx->stream>>>(
             ctx->nShared, (int)ctx->nbrRank.size(), ctx->sharedIdx, ctx->contribPtr, ctx->contrib, ctx->sPart, ctx->mbRecv_d,
@@ -2724,6 +2766,28 @@ int launch_xupdate_t(mmadmm_ctx *ctx, const double *zsrc, bool sharedOnly = fals
     ctx->launches++;
     return MMADMM_OK;
 }
+// x-update (+ primal residual partials).  sharedOnly: the other vertices were (or, with `mid`, are being) solved by k_xfirst;
+// `mid` is launched between the push of the shared vertices' partials and the wait for the neighbours'.
+struct NoMid { void operator()() const {} };
+template <int D, bool ZSRC, bool UZERO, bool PRIMAL, bool UREC = false, class Mid = NoMid>
+int launch_xupdate_t(mmadmm_ctx *ctx, const double *zsrc, bool sharedOnly = false, Mid mid = Mid()) {
+    const bool exch = ctx->dist && ctx->nShared > 0;
+    unsigned long long ep = 0;
+    int rc = MMADMM_OK;
+    if (exch && ctx->p2p) {
+        rc = xupdate_shared<D, ZSRC, UZERO, PRIMAL, UREC>(ctx, zsrc, true, ep);
+        if (rc) return rc;
+        if (!sharedOnly) rc = xupdate_bulk<D, ZSRC, UZERO, PRIMAL, UREC>(ctx, zsrc, true);
+        if (rc) return rc;
+        mid();
+        return xupdate_finish<D, ZSRC, PRIMAL>(ctx, zsrc, ep);
+    }
+    mid();
+    if (!sharedOnly) rc = xupdate_bulk<D, ZSRC, UZERO, PRIMAL, UREC>(ctx, zsrc, false);   // shared vertices: partial sums into sPart
+    else if (exch) rc = xupdate_shared<D, ZSRC, UZERO, PRIMAL, UREC>(ctx, zsrc, false, ep);
+    if (rc || !exch) return rc;
+    return xupdate_finish<D, ZSRC, PRIMAL>(ctx, zsrc, ep);
+}
 
 template <int D> int step_impl(mmadmm_ctx *ctx, int nIters, double tol, double *IhOut, int *itersOut, double *primalOut, double *dualOut) {
     cudaStream_t st = ctx->stream;
@@ -2732,7 +2796,8 @@ template <int D> int step_impl(mmadmm_ctx *ctx, int nIters, double tol, double *
     ElemArgs<D> a = ctx->elemArgs<D>(tol / 100);   // BFGS tolerance tol/100, 50 iterations (src/Mesh.cpp:968)
     const int gE = ctx->nblkE, gV = ctx->nblkV;
     const bool fast = ctx->usumPeriod > 0;   // x-updates on the per-vertex dual sums (k_xfirst, k_xupdate<UREC>)
-    bool firstSolved = false;
+    const bool ovl = ctx->dist && ctx->nShared > 0 && ctx->p2p;   // exchange overlapped with the bulk vertex passes
+    bool extrapFused = false;
 
     // predictX (src/Mesh.cpp:649-674) fused with xPrev = x (src/MeshIntegrator.cpp:119)
     ctx->phaseBegin(0);
@@ -2748,11 +2813,12 @@ template <int D> int step_impl(mmadmm_ctx *ctx, int nIters, double tol, double *
                                                                          ctx->xBar, ctx->xPrev);
             ctx->launches++;
         }
-    } else if (fast) {   // predictor and first x-solve in one vertex-local pass
-        k_xfirst<D, true><<<cdiv(NV, TPB_V), TPB_V, 0, st>>>(NV, ctx->incPtr, ctx->usum, nullptr, ctx->xBar, ctx->xPrev, ctx->tdiag, ctx->m,
-                                                             ctx->dt * ctx->dt, ctx->w, ctx->x, ctx->dist ? ctx->sharedSlot : nullptr);
-        ctx->launches += 1;
-        firstSolved = true;
+    } else if (fast) {   // predictor and first x-solve in one vertex-local pass (k_xfirst<EXTRAP>), launched in the next section
+        extrapFused = true;
+        if (ovl) {       // the shared vertices' predictor first: their partial sums are pushed before the bulk pass
+            k_predict_shared<D><<<cdiv(ctx->nShared, 256), 256, 0, st>>>(ctx->nShared, ctx->sharedIdx, ctx->x, ctx->xBar, ctx->xPrev);
+            ctx->launches += 1;
+        }
     } else {
         k_predict_extrap<<<cdiv(NV, TPB_V), TPB_V, 0, st>>>(NV, ctx->x, ctx->xBar, ctx->xPrev);
         ctx->launches += 1;
@@ -2765,12 +2831,19 @@ template <int D> int step_impl(mmadmm_ctx *ctx, int nIters, double tol, double *
     // first x-solve (:137-138)
     ctx->phaseBegin(2);
     {
-        if (fast && !firstSolved) {
-            k_xfirst<D, false><<<cdiv(NV, TPB_V), TPB_V, 0, st>>>(NV, ctx->incPtr, ctx->usum, zsrc, ctx->xBar, ctx->xPrev, ctx->tdiag, ctx->m,
-                                                                  ctx->dt * ctx->dt, ctx->w, ctx->x, ctx->dist ? ctx->sharedSlot : nullptr);
+        auto xfirst = [&]() {   // all vertices that are not shared with another rank; no element state is read
+            if (!fast) return;
+            const int *ss = ctx->dist ? ctx->sharedSlot : nullptr;
+            if (extrapFused)
+                k_xfirst<D, true><<<cdiv(NV, TPB_V), TPB_V, 0, st>>>(NV, ctx->incPtr, ctx->usum, nullptr, ctx->xBar, ctx->xPrev, ctx->tdiag,
+                                                                     ctx->m, ctx->dt * ctx->dt, ctx->w, ctx->x, ss, ovl ? 1 : 0);
+            else
+                k_xfirst<D, false><<<cdiv(NV, TPB_V), TPB_V, 0, st>>>(NV, ctx->incPtr, ctx->usum, zsrc, ctx->xBar, ctx->xPrev, ctx->tdiag,
+                                                                      ctx->m, ctx->dt * ctx->dt, ctx->w, ctx->x, ss, 0);
             ctx->launches += 1;
-        }
-        int rcx = uZero ? launch_xupdate_t<D, true, true, false>(ctx, zsrc, fast) : launch_xupdate_t<D, true, false, false>(ctx, zsrc, fast);
+        };
+        int rcx = uZero ? launch_xupdate_t<D, true, true, false, false>(ctx, zsrc, fast, xfirst)
+                        : launch_xupdate_t<D, true, false, false, false>(ctx, zsrc, fast, xfirst);
         if (rcx) return rcx;
     }
     ctx->phaseEnd();
