@@ -486,6 +486,88 @@ def run_workload(env, args, wl, K, W, cpu_baseline):
     return rec
 
 
+def method2_line(args):
+    """`--method 2`: MeshIntegrator::backwardsEulerStep (Method 2, src/Mesh.cpp:1263-1341: Newton on the backward-Euler residual,
+    finite-difference Jacobian, ILU(0) + BiCGSTAB as LASolver runs them) on SquareGrid 2D nx (default C2's 1024), MEx4.  One GPU.
+    The first step builds the Jacobian and the ILU(0) factor and is the warm-up.  The Newton loop is host-driven, so the timed
+    region is wall clock around K steps bracketed by device synchronises (CUDA events on the library's stream agree with it)."""
+    env = Env()
+    if env.world > 1:
+        raise SystemExit("--method 2 runs on one GPU (mmadmm_backward_euler_step is single-GPU)")
+    import numpy as np
+    torch, mm = env.torch, env.mm
+    nx = args.nx or 1024
+    Vp, F, mask = mm.generate_uniform_rect_mesh(2, nx, nx, 0)
+    mon = mm.TestMonitor(2, 4).evaluate_at_vertices(Vp)
+    mesh = mm.Mesh(Vp.copy(), F.copy(), mask, mon, rho=50.0, tau=0.5, integration_mode=2)
+    solver = mm.MeshIntegrator(0.025, mesh, sync_vp=False)
+    warm = []
+    for _ in range(max(1, min(args.warmup, 2))):
+        t0 = time.perf_counter()
+        solver.backwardsEulerStep(0.025, 1e-3)
+        warm.append(dict(ms=(time.perf_counter() - t0) * 1e3, **solver.last))
+    stream = torch.cuda.ExternalStream(solver.stream())
+    K = args.steps
+    st0 = solver.stats()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    sampler = ClockSampler(env.local, 0.002)
+    torch.cuda.synchronize()
+    newton = lin = 0
+    t0 = time.perf_counter()
+    ev0.record(stream)
+    for _ in range(K):
+        ih = solver.backwardsEulerStep(0.025, 1e-3)
+        newton += solver.last["newton_iters"]; lin += solver.last["lin_iters"]
+    ev1.record(stream)
+    torch.cuda.synchronize()
+    wall = time.perf_counter() - t0
+    clocks = sampler.stop()
+    ms = ev0.elapsed_time(ev1)
+    rowptr, col, val = solver.backward_euler_jacobian()
+    n, nnz = len(rowptr) - 1, len(val)
+    launches = solver.stats()["kernel_launches"] - st0["kernel_launches"]
+    # algorithmic bytes of one BiCGSTAB iteration: 2 ILU(0) applications (factor values + column indices once each, lower and
+    # upper half together = nnz entries) + 2 SpMV (nnz entries) + ~14 vector passes
+    bytes_iter = 2 * nnz * 12 + 2 * nnz * 12 + 14 * n * 8
+    peak, peak_src = peaks()
+    achieved = bytes_iter * lin / (ms * 1e-3) / 1e9 if lin else 0.0
+    line = {"metric": "backward-Euler steps/sec (Method 2)", "value": K / (ms * 1e-3), "unit": "outer steps/s", "n_gpus": 1, "steps": K,
+            "warmup": len(warm), "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+            "data": "synthetic",
+            "config": {"workload": f"Method 2 (backward Euler) on SquareGrid 2D nx=ny={nx} ({F.shape[0]:,} triangles), MEx4, dt=0.025 tau=0.5, tol 1e-3",
+                       "unknowns": n, "jacobian_nnz": nnz, "newton_iters": newton, "bicgstab_iters": lin},
+            "wall_ms_per_step": wall / K * 1e3, "gpu_launches": launches,
+            "e2e": {"value": K / wall, "unit": "outer steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 64 * max(lin, 1) // K,
+                    "note": "wall clock through MeshIntegrator.backwardsEulerStep; as in the reference this path does not write Vp back per step"},
+            "roofline": {"kernel": "ILU(0)+BiCGSTAB iteration (k_tri_cluster x4, k_spmv_dot x2, vector kernels)", "bound": "hbm", "achieved": achieved,
+                         "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                         "algorithmic_bytes_per_launch": bytes_iter,
+                         "note": "latency-bound by construction: natural-order ILU(0) on a structured mesh has thousands of levels of a few "
+                                 "hundred rows (DESIGN.md 3.5); the fraction is reported, not claimed"},
+            "clocks": clocks, "warmup_steps": warm, "energy_last": ih}
+    solver.close()
+    if not args.no_cpu_baseline:
+        import oracle_lib as O
+        import pcg_oracle as PO
+        cnx = 256
+        Vc, Fc, mc = O.uniform_rect_mesh(2, cnx, cnx)
+        orc = O.Oracle(Vc, Fc, mc, O.monitor_eval(2, 4, Vc), 50.0, 0.5, 0.025)
+        rows, cols = orc.jacobian_entries()
+        S = PO.LASolverJac(orc.P * orc.D, rows, cols) if PO.have_lasolver() else PO.RestatedJac(orc.P * orc.D, rows, cols)
+        orc.backwards_euler_step(S, 1e-3)
+        t0 = time.perf_counter()
+        for _ in range(2):
+            orc.backwards_euler_step(S, 1e-3)
+        cms = (time.perf_counter() - t0) / 2 * 1e3
+        line["cpu_baseline"] = {"value": 1e3 / cms, "unit": "outer steps/s", "cores": 1, "kind": "reference" if PO.have_lasolver() else "port",
+                                "ms_per_step": cms,
+                                "sample": f"oracle backward-Euler step (serial, like the reference's loops) with the linear solves by "
+                                          f"{type(S).__name__} on SquareGrid 2D nx={cnx} ({Fc.shape[0]:,} triangles = 1/{(nx * nx) // (cnx * cnx)} of the GPU "
+                                          f"arm's mesh: a bounded sample), 2 steps after 1 warm-up"}
+    print(json.dumps(line))
+    return 0
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -493,6 +575,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="c2", choices=["c2", "c3", "c4"])
+    ap.add_argument("--method", type=int, default=0, choices=[0, 2], help="0: ADMM step (the benchmark); 2: backward Euler (Method 2) line")
     ap.add_argument("--nx", type=int, default=0, help="override the mesh resolution (with --gpus N: strong scaling at that size, e.g. SURVEY C5 = --nx 2048)")
     ap.add_argument("--per-step", action="store_true", help="also record one event per step (step_ms_rank0); adds host work between steps")
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -506,6 +589,8 @@ def main():
     args = ap.parse_args()
     if args.impl == "reference":
         return reference_arm(args)
+    if args.method == 2:
+        return method2_line(args)
 
     env = Env()
     W = min(max(args.warmup, 3), 6)

@@ -244,7 +244,11 @@ int mmadmm_pcg_spmv(mmadmm_pcg *h, const double *x, double *y);
 int mmadmm_pcg_precond(mmadmm_pcg *h, const double *r, double *z);
 /* ILU(0) factor values in A's CSR pattern (unit lower below the diagonal, U on and above it). */
 int mmadmm_pcg_get_ilu(mmadmm_pcg *h, double *lu);
-/* "tri_mode": 1 (default) = in the ILU(0) triangular solves every run of consecutive levels of at most 8192 rows is ONE launch
+/* "spmv_format": 0 (default) = CSR with a sub-warp per row; 1 = SELL-C-sigma (C = 32 rows per slice = one warp, sigma = 4096-row
+ * sorting window, column-major slices: every value / index load is one coalesced line; a thread owns a row and accumulates in
+ * ascending column order like LASolver's matmult, accel_class.cpp:521-549), built from the CSR arrays on first use.  Both serve
+ * every solver entry point.  "sell_padding_permille" is a query: padding entries per 1000 stored entries.
+ * "tri_mode": 1 (default) = in the ILU(0) triangular solves every run of consecutive levels of at most 8192 rows is ONE launch
  * of a thread-block cluster that walks the levels with cluster barriers (wider levels keep a launch each); 0 = one launch
  * per level.  Results are bit-identical. */
 int mmadmm_pcg_set_option(mmadmm_pcg *h, const char *name, int value);

@@ -82,6 +82,37 @@ __global__ void __launch_bounds__(TPB) k_spmv_dot(int n, const int *__restrict__
     }
 }
 
+// SELL-C-sigma form of the same product (C = 32: one warp per slice of 32 rows, sigma = 4096: rows are sorted
+// by length inside windows of 4096 rows so that a slice pads little).  A slice stores its entries column-major
+// ([entry j of the row][32 rows]): every load of values / column indices is one coalesced 256 / 128-byte line, one thread owns a
+// row and accumulates in ascending column order (the order of LASolver's matmult, accel_class.cpp:521-549).  Padding: value 0,
+// column 0.
+__global__ void __launch_bounds__(TPB) k_spmv_sell(int nSlices, const int *__restrict__ slicePtr, const int *__restrict__ scol,
+                                                    const double *__restrict__ sval, const int *__restrict__ perm,
+                                                    const double *__restrict__ x, double *__restrict__ y, double *part) {
+    __shared__ double sh[32];
+    const int gt = blockIdx.x * TPB + threadIdx.x;
+    const int slice = gt >> 5, lane = gt & 31;
+    double d = 0.0;
+    if (slice < nSlices) {
+        const int row = perm[slice * 32 + lane];
+        const int p0 = slicePtr[slice], w = (slicePtr[slice + 1] - p0) >> 5;
+        double acc = 0.0;
+        for (int j = 0; j < w; j++) {
+            const int k = p0 + j * 32 + lane;
+            acc += sval[k] * __ldg(x + scol[k]);
+        }
+        if (row >= 0) {
+            y[row] = acc;
+            d = acc * x[row];
+        }
+    }
+    if (part) {
+        const double s = block_sum_d(d, sh);
+        if (threadIdx.x == 0) part[blockIdx.x] = s;
+    }
+}
+
 // One level of a triangular solve with the ILU(0) factors stored in A's pattern (unit lower, upper with diagonal):
 // rows[lo..hi) are mutually independent.  LOWER: y_i = b_i - sum_{j<i} L_ij y_j ; UPPER: x_i = (y_i - sum_{j>i} U_ij x_j) / U_ii.
 template <bool LOWER>
@@ -286,6 +317,13 @@ struct mmadmm_pcg {
     int *lvlL_d = nullptr, *lvlU_d = nullptr;     // level offsets on the device (k_tri_cluster)
     int2 *kbeL = nullptr, *kbeU = nullptr;        // off-diagonal extent [kb, ke) of the rows in level order (k_tri_cluster)
     int triMode = 1;                              // 1: one cluster launch per triangular solve; 0: one launch per level
+    int spmvFormat = 0;                           // 0: CSR, sub-warp per row; 1: SELL-32-4096 (built on first use)
+    int nSlices = 0;
+    long long sellEntries = 0;
+    int *slicePtr = nullptr, *scol = nullptr, *perm = nullptr;
+    double *sval = nullptr;
+    std::vector<int> rowptr_h, col_h;             // host copy of the pattern (SELL build)
+    std::vector<double> val_h;
     std::vector<int> lvlL, lvlU;                  // level offsets (host)
     double *r = nullptr, *z = nullptr, *p = nullptr, *q = nullptr, *x = nullptr, *b = nullptr, *tmp = nullptr;
     double *part0 = nullptr, *part1 = nullptr, *scal = nullptr, *scal_h = nullptr;
@@ -308,6 +346,11 @@ namespace {
 
 void launch_spmv(mmadmm_pcg *h, const double *x, double *y, double *part) {
     const int n = h->n;
+    if (h->spmvFormat == 1) {
+        k_spmv_sell<<<cdiv((size_t)h->nSlices * 32, TPB), TPB, 0, h->stream>>>(h->nSlices, h->slicePtr, h->scol, h->sval, h->perm, x, y, part);
+        h->launches++;
+        return;
+    }
     const size_t threads = (size_t)n * h->lanes;
     const int g = cdiv(threads, TPB);
     switch (h->lanes) {
@@ -320,7 +363,52 @@ void launch_spmv(mmadmm_pcg *h, const double *x, double *y, double *part) {
     }
     h->launches++;
 }
-int spmv_parts(const mmadmm_pcg *h) { return cdiv((size_t)h->n * h->lanes, TPB); }
+int spmv_parts(const mmadmm_pcg *h) {
+    return h->spmvFormat == 1 ? cdiv((size_t)h->nSlices * 32, TPB) : cdiv((size_t)h->n * h->lanes, TPB);
+}
+// CSR -> SELL-32-4096 on the host (once), uploaded next to the CSR arrays
+int build_sell(mmadmm_pcg *h) {
+    if (h->slicePtr) return MMADMM_OK;
+    const int n = h->n, C = 32, SIGMA = 4096;
+    const std::vector<int> &rp = h->rowptr_h, &cl = h->col_h;
+    const std::vector<double> &vl = h->val_h;
+    const int nSlices = (n + C - 1) / C;
+    std::vector<int> perm((size_t)nSlices * C, -1);
+    for (int i = 0; i < n; i++) perm[i] = i;
+    for (int w0 = 0; w0 < n; w0 += SIGMA) {
+        const int w1 = std::min(n, w0 + SIGMA);
+        std::stable_sort(perm.begin() + w0, perm.begin() + w1, [&](int a, int b) { return rp[a + 1] - rp[a] > rp[b + 1] - rp[b]; });
+    }
+    std::vector<int> sp(nSlices + 1, 0);
+    for (int s = 0; s < nSlices; s++) {
+        int w = 0;
+        for (int r = 0; r < C; r++) { const int row = perm[(size_t)s * C + r]; if (row >= 0) w = std::max(w, rp[row + 1] - rp[row]); }
+        sp[s + 1] = sp[s] + w * C;
+    }
+    std::vector<int> scol((size_t)sp[nSlices], 0);
+    std::vector<double> sval((size_t)sp[nSlices], 0.0);
+    for (int s = 0; s < nSlices; s++)
+        for (int r = 0; r < C; r++) {
+            const int row = perm[(size_t)s * C + r];
+            if (row < 0) continue;
+            for (int k = rp[row], j = 0; k < rp[row + 1]; k++, j++) {
+                scol[(size_t)sp[s] + (size_t)j * C + r] = cl[k];
+                sval[(size_t)sp[s] + (size_t)j * C + r] = vl[k];
+            }
+        }
+    PCK(cudaSetDevice(h->device));
+    PCK(cudaMalloc(&h->slicePtr, sizeof(int) * sp.size()));
+    PCK(cudaMalloc(&h->perm, sizeof(int) * perm.size()));
+    PCK(cudaMalloc(&h->scol, sizeof(int) * std::max<size_t>(scol.size(), 1)));
+    PCK(cudaMalloc(&h->sval, sizeof(double) * std::max<size_t>(sval.size(), 1)));
+    PCK(cudaMemcpy(h->slicePtr, sp.data(), sizeof(int) * sp.size(), cudaMemcpyHostToDevice));
+    PCK(cudaMemcpy(h->perm, perm.data(), sizeof(int) * perm.size(), cudaMemcpyHostToDevice));
+    PCK(cudaMemcpy(h->scol, scol.data(), sizeof(int) * scol.size(), cudaMemcpyHostToDevice));
+    PCK(cudaMemcpy(h->sval, sval.data(), sizeof(double) * sval.size(), cudaMemcpyHostToDevice));
+    h->nSlices = nSlices;
+    h->sellEntries = sp[nSlices];
+    return MMADMM_OK;
+}
 
 // One triangular solve.  tri_mode 1: runs of consecutive levels that each fit a few passes of the cluster's 2048 threads go
 // out as ONE k_tri_cluster launch (natural-order ILU(0) on a structured 2D mesh: thousands of levels of a few hundred rows);
@@ -371,6 +459,7 @@ int mmadmm_pcg_create(int n, const int *rowptr, const int *col, const double *va
     *out = h;
     h->n = n; h->nnz = rowptr[n]; h->precond = precond; h->device = device;
     const int nnz = h->nnz;
+    h->rowptr_h.assign(rowptr, rowptr + n + 1); h->col_h.assign(col, col + nnz); h->val_h.assign(val, val + nnz);
     // pattern checks: sorted columns, diagonal present
     std::vector<int> diagPos(n, -1);
     for (int i = 0; i < n; i++) {
@@ -465,7 +554,7 @@ int mmadmm_pcg_create(int n, const int *rowptr, const int *col, const double *va
     PCK(up((void **)&h->r, nullptr, vb)); PCK(up((void **)&h->z, nullptr, vb)); PCK(up((void **)&h->p, nullptr, vb));
     PCK(up((void **)&h->q, nullptr, vb)); PCK(up((void **)&h->x, nullptr, vb)); PCK(up((void **)&h->b, nullptr, vb));
     PCK(up((void **)&h->tmp, nullptr, vb));
-    h->nblk = std::max(cdiv(n, TPB), spmv_parts(h));
+    h->nblk = std::max(std::max(cdiv(n, TPB), spmv_parts(h)), cdiv((size_t)((n + 31) / 32) * 32, TPB));
     PCK(up((void **)&h->part0, nullptr, sizeof(double) * (size_t)h->nblk));
     PCK(up((void **)&h->part1, nullptr, sizeof(double) * (size_t)h->nblk));
     PCK(up((void **)&h->scal, nullptr, sizeof(double) * S_COUNT));
@@ -477,6 +566,13 @@ int mmadmm_pcg_create(int n, const int *rowptr, const int *col, const double *va
 int mmadmm_pcg_set_option(mmadmm_pcg *h, const char *name, int value) {
     if (!h || !name) return MMADMM_EINVAL;
     if (!std::strcmp(name, "tri_mode")) { h->triMode = value ? 1 : 0; return MMADMM_OK; }
+    if (!std::strcmp(name, "spmv_format")) {   // 0: CSR (sub-warp per row), 1: SELL-32-4096
+        if (value != 0 && value != 1) return MMADMM_EINVAL;
+        if (value == 1) { int rc = build_sell(h); if (rc) return rc; }
+        h->spmvFormat = value;
+        return MMADMM_OK;
+    }
+    if (!std::strcmp(name, "sell_padding_permille")) return h->nnz ? (int)((h->sellEntries - h->nnz) * 1000 / h->nnz) : 0;   // query
     h->err = std::string("unknown option ") + name;
     return MMADMM_EINVAL;
 }
@@ -727,6 +823,7 @@ void mmadmm_pcg_destroy(mmadmm_pcg *h) {
     cudaFree(h->r); cudaFree(h->z); cudaFree(h->p); cudaFree(h->q); cudaFree(h->x); cudaFree(h->b); cudaFree(h->tmp);
     cudaFree(h->part0); cudaFree(h->part1); cudaFree(h->scal);
     for (int k = 0; k < 4; k++) cudaFree(h->bi[k]);
+    cudaFree(h->slicePtr); cudaFree(h->scol); cudaFree(h->sval); cudaFree(h->perm);
     if (h->scal_h) cudaFreeHost(h->scal_h);
     if (h->stream) cudaStreamDestroy(h->stream);
     delete h;
