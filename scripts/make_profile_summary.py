@@ -33,8 +33,11 @@ def raw(rep):
     for d in rows[2:]:
         m = {"kernel": d[h.index("Kernel Name")]}
         for i, n in enumerate(h):
-            if n in KEYS or ("issue_stalled" in n and "per_issue_active" in n):
-                m[n] = (d[i], u[i])
+            short = n.split(".", 2)[-1] if n.startswith(("FBSP.", "breakdown:")) else n   # section-prefixed names of the raw page
+            for cand in (n, short):
+                if cand in KEYS or ("issue_stalled" in cand and "per_issue_active" in cand):
+                    m[cand] = (d[i], u[i])
+                    break
         res.append(m)
     return res
 
@@ -50,7 +53,11 @@ def launches(path):
     return sorted(((k, n, t / n / 1e3, 100 * t / tot) for k, (n, t) in agg.items()), key=lambda x: -x[3]), tot
 
 
-md = [f"# Round 1, capture {pre[-1].upper()} (`profiles/{pre}_*`)\n",
+def load_line(f):
+    return json.loads([ln for ln in open(f).read().split("\n") if ln.startswith("{")][-1])
+
+
+md = [f"# Round {int(pre[1:3])}, capture {pre[-1].upper()} (`profiles/{pre}_*`)\n",
       "Produced by `scripts/gpu_profile.sh` on one B200 (bench lines first, each ncu pass only after its command had exited 0 "
       "without ncu) and `scripts/make_profile_summary.py`.\n"]
 for wl in ("c2", "c3", "c4", "ref"):
@@ -58,7 +65,7 @@ for wl in ("c2", "c3", "c4", "ref"):
     if not os.path.exists(f) or not open(f).read().strip():
         continue
     shutil.copy(f, os.path.join(out, f"{pre}_bench_{wl}.json"))
-    d = json.loads(open(f).read().strip().split("\n")[-1])
+    d = load_line(f)
     if wl == "ref":
         md.append(f"* reference arm (`--impl reference`): {d['value'] / 1e6:.2f} M element-prox/s, {d['cpu_baseline']['sample']}\n")
         continue
@@ -86,17 +93,17 @@ for wl in ("c2", "c4"):
     avg = {k: a for k, n, a, s in rows}
     pick = lambda pat: next((a for k, a in avg.items() if pat in k), 0.0)
     D = "3" if wl == "c4" else "2"
-    prox = pick("k_prox_vw") if wl == "c4" else pick("k_prox_p")
+    prox = (pick("k_prox_q") or pick("k_prox_vw")) if wl == "c4" else pick("k_prox_p")
     # (k_xfirst<D,1> = predictor + first x-solve, k_xupdate<D,0,0,1,1> = the x-update after the sweep on the dual sums; the
     # pre-"usum" names are kept so that older captures still summarise)
     step = (prox + pick(f"k_xupdate<{D}, 0, 0, 1, 1>") + pick(f"k_xfirst<{D}, 1>") + pick(f"k_xupdate<{D}, 0, 0, 1>(") +
             pick(f"k_xupdate<{D}, 1, 0, 0>(") + pick("k_predict_extrap") + pick("k_finalize"))
     if step > 0:
-        bj = json.loads(open(os.path.join(src, f"bench_{wl}.json")).read().strip().split("\n")[-1])
+        bj = load_line(os.path.join(src, f"bench_{wl}.json"))
         ph = bj["phase_ms_per_step"]
         md.append(f"Steady-state step from this list: prox {prox:.0f} of {step:.0f} µs = {100 * prox / step:.1f} %; phase timers of the bench line: "
                   f"{100 * ph['prox'] / (ph['prox'] + ph['xupdate'] + ph['predict'] + ph['residual']):.1f} %.\n")
-for name in ("prof_c2", "prof_c4", "prof_xup"):
+for name in ("prof_c2", "prof_c4", "prof_xup", "prof_tri"):
     rep = os.path.join(src, name + ".ncu-rep")
     if not os.path.exists(rep):
         continue
@@ -115,5 +122,27 @@ for name in ("prof_c2", "prof_c4", "prof_xup"):
                   f"* FP64 pipe {g('sm__inst_executed_pipe_fp64.avg.pct_of_peak_sustained_active')} %, issue slots {g('smsp__issue_active.avg.pct_of_peak_sustained_active')} %, "
                   f"L1 data pipe {g('l1tex__data_pipe_lsu_wavefronts.avg.pct_of_peak_sustained_elapsed')} %, L2 hit {g('lts__t_sector_hit_rate.pct')} %\n"
                   f"* stalls per issue: {', '.join(f'{n} {v:.2f}' for v, n in stalls)}\n")
+# SASS evidence that the library is Blackwell-native code: bulk-copy (TMA) engine, mbarriers, cp.async, cluster barriers, FP64 FMAs;
+# and what must NOT be there (tensor-core MMAs: nothing here is a contraction)
+so = os.path.join("mm-admm_b200", "libmmadmm_b200.so")
+if os.path.exists(so):
+    sass = subprocess.run(["cuobjdump", "-sass", so], capture_output=True, text=True).stdout
+    import re
+    pats = ["UBLKCP.S.G", "UBLKCP.G.S", "UTMALDG", "SYNCS", "LDGSTS", "UCGABAR_ARV", "UCGABAR_WAIT", "DFMA", "DMUL", "DADD", "MUFU.RSQ64H", "SHFL",
+            "UTCHMMA", "UTCQMMA", "HMMA", "IMMA", "DMMA", "MEMBAR.SC.SYS", "ST.E.STRONG.SYS", "LD.E.STRONG.SYS"]
+    counts = {k: len(re.findall(r"\b" + re.escape(k), sass)) for k in pats}
+    arch = sorted(set(re.findall(r"arch = (sm_\w+)", sass)))
+    json.dump({"library": so, "arch": arch, "instruction_counts": counts}, open(os.path.join(out, f"{pre}_sass_counts.json"), "w"), indent=1)
+    md.append(f"### SASS of `{so}` (`cuobjdump -sass`, `{pre}_sass_counts.json`): arch {arch}\n")
+    md.append("| mnemonic | count | what it is |\n|---|---|---|\n" + "".join(
+        f"| `{k}` | {counts[k]} | {w} |\n" for k, w in [
+            ("UBLKCP.S.G", "cp.async.bulk global -> shared (TMA bulk copy engine): inverse-Hessian tiles in"),
+            ("UBLKCP.G.S", "cp.async.bulk shared -> global: inverse-Hessian tiles out"),
+            ("UTMALDG", "tensor-map TMA loads (none: one contiguous bulk copy per tile needs no tensor map)"),
+            ("SYNCS", "mbarrier operations (transaction barriers of the bulk copies)"),
+            ("LDGSTS", "cp.async per-thread gathers into shared memory (next tile's vertices, connectivity)"),
+            ("UCGABAR_ARV", "thread-block-cluster barrier arrive (k_tri_cluster)"), ("UCGABAR_WAIT", "cluster barrier wait"),
+            ("DFMA", "FP64 fused multiply-add"), ("SHFL", "warp shuffles (3D prox exchange, reductions)"),
+            ("UTCHMMA", "tcgen05 MMA (none: no contraction on this path)"), ("HMMA", "mma.sync (none)"), ("DMMA", "FP64 mma (none)")]))
 open(os.path.join(out, f"{pre}_summary.md"), "w").write("\n".join(md))
 print("wrote", os.path.join(out, f"{pre}_summary.md"))
