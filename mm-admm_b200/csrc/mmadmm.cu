@@ -1123,6 +1123,13 @@ __global__ void __launch_bounds__(TPB_V, MINB) k_xupdate(int P, size_t Es, const
         const int k0 = incPtr[p], k1 = incPtr[p + 1];
         const int sh = sharedSlot ? sharedSlot[p] : -1;
         const bool rec = UREC && sh < 0;
+        // UREC: the primal share sum_s |x_new - z_s|^2 is formed in the SAME pass as zsum, shifted by the vertex's previous
+        // position xo (known before the pass; |z_s - xo| and |x_new - xo| are step-sized, so nothing large cancels):
+        //   sum_s |d - e_s|^2 = val |d|^2 - 2 d . S1 + S2,  d = x_new - xo, e_s = z_s - xo, S1 = sum e_s, S2 = sum |e_s|^2.
+        // The second pass over the slots (half of the kernel's L1 requests) disappears; x itself is unchanged bit for bit.
+        double xo[D], S1[D], S2 = 0.0;
+#pragma unroll
+        for (int l = 0; l < D; l++) { xo[l] = UREC ? x[(size_t)D * p + l] : 0.0; S1[l] = 0.0; }
         if (UREC && sh >= 0) {   // shared with another rank: slot-by-slot form, plain loop (few vertices)
             for (int k = k0; k < k1; k++) {
                 const int slot = __ldg(incIdx + k);
@@ -1165,8 +1172,12 @@ __global__ void __launch_bounds__(TPB_V, MINB) k_xupdate(int P, size_t Es, const
                     if (slot[j] >= 0) {
 #pragma unroll
                         for (int l = 0; l < D; l++) {
-                            if (UREC) s[l] += zv[j][l];   // zsum
-                            else { s[l] += w * (w * (zv[j][l] - uv[j][l])); us[l] += uv[j][l]; }
+                            if (UREC) {
+                                s[l] += zv[j][l];   // zsum
+                                const double el = zv[j][l] - xo[l];
+                                S1[l] += el;
+                                S2 += el * el;
+                            } else { s[l] += w * (w * (zv[j][l] - uv[j][l])); us[l] += uv[j][l]; }
                         }
                     }
             }
@@ -1175,7 +1186,7 @@ __global__ void __launch_bounds__(TPB_V, MINB) k_xupdate(int P, size_t Es, const
 #pragma unroll
             for (int l = 0; l < D; l++) {
                 if (rec) {
-                    const double un = (usum[(size_t)D * p + l] + (double)(k1 - k0) * x[(size_t)D * p + l]) - s[l];
+                    const double un = (usum[(size_t)D * p + l] + (double)(k1 - k0) * xo[l]) - s[l];
                     usum[(size_t)D * p + l] = un;
                     s[l] = w * (w * (s[l] - un));
                 } else {
@@ -1194,7 +1205,15 @@ __global__ void __launch_bounds__(TPB_V, MINB) k_xupdate(int P, size_t Es, const
             xn[l] = ((m * xBar[(size_t)D * p + l]) + dtsq * s[l]) / td;
             if (sh < 0) x[(size_t)D * p + l] = xn[l];
         }
-        if (PRIMAL && sh < 0) {   // second pass over the (L1-resident) slots: differences, not expanded squares
+        if (PRIMAL && rec) {
+            double acc = S2;
+#pragma unroll
+            for (int l = 0; l < D; l++) {
+                const double dl = xn[l] - xo[l];
+                acc += dl * ((double)(k1 - k0) * dl - 2.0 * S1[l]);
+            }
+            prim = acc > 0.0 ? acc : 0.0;
+        } else if (PRIMAL && sh < 0) {   // second pass over the (L1-resident) slots: differences, not expanded squares
             for (int k = k0; k < k1; k++) {
                 int slot = __ldg(incIdx + k);
                 size_t e = (size_t)(slot >> 2);
