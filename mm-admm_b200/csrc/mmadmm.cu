@@ -1584,7 +1584,7 @@ __global__ void k_block_grad_dbg(ElemArgs<D> a, int e0, int ne, const double *zs
 struct mmadmm_ctx {
     int D = 0, n = 0, P = 0, E = 0, device = 0;
     size_t Es = 0;               // element-plane stride
-    int proxVariant = 0;
+    int proxVariant = 0, xupVariant = 0;
     // ---- distributed (element-block partition, one process per GPU) ----
     bool dist = false;
     int rank = 0, nranks = 1, Pglobal = 0, Eglobal = 0;
@@ -2756,10 +2756,20 @@ int xupdate_shared(mmadmm_ctx *ctx, const double *zsrc, bool push, unsigned long
 template <int D, bool ZSRC, bool UZERO, bool PRIMAL, bool UREC>
 int xupdate_bulk(mmadmm_ctx *ctx, const double *zsrc, bool skipShared) {
     const double dtsq = ctx->dt * ctx->dt;
-    // chunk size / occupancy of the recurrence form, measured on C2 and C4: 2D 2 slots per chunk at full occupancy
-    // (32 registers), 3D 8 slots per chunk (80 registers); the differences are a few per cent of the kernel
-    auto kern = !UREC ? k_xupdate<D, ZSRC, UZERO, PRIMAL, UREC>
-                      : (D == 2 ? k_xupdate<D, ZSRC, UZERO, PRIMAL, UREC, 2, 8> : k_xupdate<D, ZSRC, UZERO, PRIMAL, UREC, 8, 1>);
+    auto kern = k_xupdate<D, ZSRC, UZERO, PRIMAL, UREC>;
+    if constexpr (UREC) {   // slots per chunk / resident CTAs of the recurrence form ("xup_variant", A/B runs; 0 = tuned default)
+        switch (ctx->xupVariant) {
+            case 1: kern = k_xupdate<D, ZSRC, UZERO, PRIMAL, UREC, 4, 4>; break;
+            case 2: kern = k_xupdate<D, ZSRC, UZERO, PRIMAL, UREC, 2, 6>; break;
+            case 3: kern = k_xupdate<D, ZSRC, UZERO, PRIMAL, UREC, 8, 2>; break;
+            case 4: kern = k_xupdate<D, ZSRC, UZERO, PRIMAL, UREC, 4, 2>; break;
+            case 5: kern = k_xupdate<D, ZSRC, UZERO, PRIMAL, UREC, 2, 8>; break;
+            case 6: kern = k_xupdate<D, ZSRC, UZERO, PRIMAL, UREC, 8, 1>; break;
+            // measured with the single-pass form (scripts/gpu_r2_q.sh): 2D 2 slots per chunk at 6 CTAs per SM (40 registers, no
+            // spills) 0.143 ms against 0.147 (2,8) / 0.145 (4,4) / 0.166 (8,2); 3D 4 slots at 4 CTAs 0.256 against 0.280 (8,1) / 0.295 (2,6)
+            default: kern = (D == 2) ? k_xupdate<D, ZSRC, UZERO, PRIMAL, UREC, 2, 6> : k_xupdate<D, ZSRC, UZERO, PRIMAL, UREC, 4, 4>; break;
+        }
+    }
     kern<<<ctx->nblkV, TPB_V, 0, ctx->stream>>>(
         ctx->P, ctx->Es, ctx->incPtr, ctx->incIdx, ctx->z, ctx->u, zsrc, ctx->xBar, ctx->tdiag, ctx->m, dtsq, ctx->w, ctx->x,
         ctx->partPrimal, ctx->dist ? ctx->sharedSlot : nullptr, ctx->sPart, ctx->vorder, ctx->usum, HaloPush(), skipShared ? 1 : 0);
@@ -3612,6 +3622,7 @@ int mmadmm_set_option(mmadmm_ctx *ctx, const char *name, int value) {
         return MMADMM_OK;
     }
     if (!strcmp(name, "prox_variant")) { ctx->proxVariant = value; return MMADMM_OK; }
+    if (!strcmp(name, "xup_variant")) { ctx->xupVariant = value; return MMADMM_OK; }
     if (!strcmp(name, "usum_period")) {
         if (value < 0) return MMADMM_EINVAL;
         ctx->usumPeriod = value; ctx->usumAge = 0;
