@@ -521,6 +521,11 @@ class MeshIntegrator:
     def set_option(self, name, value):
         self._check(self.L.mmadmm_set_option(self.h, name.encode(), int(value)))
 
+    def set_dt(self, dt):
+        """Change the step size (the reference's driver assigns MeshIntegrator::dt between steps)."""
+        self._check(self.L.mmadmm_set_dt(self.h, float(dt)))
+        self.dt = float(dt)
+
     def p2p_active(self):
         """True when a distributed context exchanges halo sums / scalars by NVLink peer stores (CUDA IPC) instead of NCCL."""
         return self.L.mmadmm_set_option(self.h, b"p2p_active", 0) == 0

@@ -1093,6 +1093,29 @@ __global__ void __launch_bounds__(1024) k_finalize(int n0, const double *p0, int
 // ------------------------------------------------------------------------------------------------
 // vertex kernels
 // ------------------------------------------------------------------------------------------------
+// x of the first x-solve of a step at one vertex component (see k_xfirst): one definition for k_xfirst and for the speculative
+// form inside k_xupdate, so that both round identically
+__device__ __forceinline__ double xfirst_value(double m, double dtsq, double w, double val, double xb, double zs, double us, double td) {
+    // explicit roundings (no contraction, like the oracle's -ffp-contract=off): identical bits in both kernels
+    const double sv = w * (w * __dsub_rn(__dmul_rn(val, zs), us));
+    return __dadd_rn(__dmul_rn(m, xb), __dmul_rn(dtsq, sv)) / td;
+}
+// What a k_xupdate launch needs to ALSO be the last kernel of a single-GPU step:
+//  * next: the next outer step's predictor + first x-solve (k_xfirst<EXTRAP>) computed speculatively from this update's
+//    result (x_new, usum+ and xPrev are all at hand in the thread): xBarNext = 2 x_new - xPrev, xNext = first solve.  If the
+//    host then ends the step (the usual case: one ADMM iteration per step), the next step starts by swapping buffers
+//    instead of launching k_xfirst (0.04 ms and 227 MB on C2 against 100 MB more here);
+//  * fin: the fixed-order final reduction of the residual partials (k_finalize) by the last CTA to finish.
+struct StepTail {
+    const double *xPrev = nullptr;
+    double *xNext = nullptr, *xBarNext = nullptr;
+    int nProx = 0;                       // fin: number of prox partials; 0 = no fused reduction
+    const double *partIh = nullptr, *partDual = nullptr;
+    double *out = nullptr;               // 3 scalars (mapped host memory)
+    const unsigned *statusIn = nullptr;
+    unsigned *statusOut = nullptr, *ticket = nullptr;
+};
+
 // K3b+K4(+K5): x = (m*xBar + dt^2 * sum_{inc, ascending element} w*(w*(z-u))) / tdiag   (src/MeshIntegrator.cpp:137-138,159-160)
 //   ZSRC : z == D*zsrc, so every incident slot of vertex p holds zsrc[p] (first solve of a step; z planes not read)
 //   UZERO: u == 0 (before the first step; u planes not read)
@@ -1107,9 +1130,10 @@ __global__ void __launch_bounds__(TPB_V, MINB) k_xupdate(int P, size_t Es, const
                                                    const double *u, const double *zsrc, const double *xBar,
                                                    const double *tdiag, double m, double dtsq, double w, double *x,
                                                    double *partPrimal, const int *sharedSlot, double *sPart, const int *vorder,
-                                                   double *usum, const HaloPush hp, const int skipShared) {
+                                                   double *usum, const HaloPush hp, const int skipShared, const StepTail tail) {
     static_assert(!UREC || (PRIMAL && !ZSRC && !UZERO), "the recurrence belongs to the update that follows a prox sweep");
     __shared__ double red[32];
+    __shared__ int lastCta;
     const int tix = blockIdx.x * TPB_V + threadIdx.x;
     double prim = 0.0;
     // skipShared: the vertices shared with other ranks were handled by an earlier launch over the shared list (their partial
@@ -1127,9 +1151,9 @@ __global__ void __launch_bounds__(TPB_V, MINB) k_xupdate(int P, size_t Es, const
         // position xo (known before the pass; |z_s - xo| and |x_new - xo| are step-sized, so nothing large cancels):
         //   sum_s |d - e_s|^2 = val |d|^2 - 2 d . S1 + S2,  d = x_new - xo, e_s = z_s - xo, S1 = sum e_s, S2 = sum |e_s|^2.
         // The second pass over the slots (half of the kernel's L1 requests) disappears; x itself is unchanged bit for bit.
-        double xo[D], S1[D], S2 = 0.0;
+        double xo[D], S1[D], S2 = 0.0, usn[D];
 #pragma unroll
-        for (int l = 0; l < D; l++) { xo[l] = UREC ? x[(size_t)D * p + l] : 0.0; S1[l] = 0.0; }
+        for (int l = 0; l < D; l++) { xo[l] = UREC ? x[(size_t)D * p + l] : 0.0; S1[l] = 0.0; usn[l] = 0.0; }
         if (UREC && sh >= 0) {   // shared with another rank: slot-by-slot form, plain loop (few vertices)
             for (int k = k0; k < k1; k++) {
                 const int slot = __ldg(incIdx + k);
@@ -1188,6 +1212,7 @@ __global__ void __launch_bounds__(TPB_V, MINB) k_xupdate(int P, size_t Es, const
                 if (rec) {
                     const double un = (usum[(size_t)D * p + l] + (double)(k1 - k0) * xo[l]) - s[l];
                     usum[(size_t)D * p + l] = un;
+                    usn[l] = un;
                     s[l] = w * (w * (s[l] - un));
                 } else {
                     usum[(size_t)D * p + l] = us[l];
@@ -1213,7 +1238,18 @@ __global__ void __launch_bounds__(TPB_V, MINB) k_xupdate(int P, size_t Es, const
                 acc += dl * ((double)(k1 - k0) * dl - 2.0 * S1[l]);
             }
             prim = acc > 0.0 ? acc : 0.0;
-        } else if (PRIMAL && sh < 0) {   // second pass over the (L1-resident) slots: differences, not expanded squares
+        }
+        if (UREC && rec && tail.xNext) {   // the next step's predictor and first x-solve, speculatively (see StepTail)
+            const double val = (double)(k1 - k0);
+#pragma unroll
+            for (int l = 0; l < D; l++) {
+                const size_t i = (size_t)D * p + l;
+                const double xb = 2 * xn[l] - tail.xPrev[i];
+                tail.xBarNext[i] = xb;
+                tail.xNext[i] = xfirst_value(m, dtsq, w, val, xb, xb, usn[l], td);
+            }
+        }
+        if (PRIMAL && !rec && sh < 0) {   // second pass over the (L1-resident) slots: differences, not expanded squares
             for (int k = k0; k < k1; k++) {
                 int slot = __ldg(incIdx + k);
                 size_t e = (size_t)(slot >> 2);
@@ -1238,6 +1274,28 @@ __global__ void __launch_bounds__(TPB_V, MINB) k_xupdate(int P, size_t Es, const
         if (threadIdx.x == 0) partPrimal[blockIdx.x] = r;
     }
     if (hp.ptr) halo_push_publish(hp);
+    if (UREC && tail.nProx > 0) {   // the CTA that finishes last reduces the step's three scalars in k_finalize's fixed order
+        if (threadIdx.x == 0) {
+            __threadfence();
+            const unsigned t = atomicAdd(tail.ticket, 1u);
+            lastCta = (t == gridDim.x - 1);
+            if (lastCta) *tail.ticket = 0;   // ready for the next launch (stream order)
+        }
+        __syncthreads();
+        if (!lastCta) return;
+        __threadfence();
+        const double *ps[3] = {tail.partIh, partPrimal, tail.partDual};
+        const int ns[3] = {tail.nProx, (int)gridDim.x, tail.nProx};
+#pragma unroll
+        for (int q = 0; q < 3; q++) {
+            double sq = 0.0;
+            for (int i = threadIdx.x; i < ns[q]; i += TPB_V) sq += __ldcg(ps[q] + i);
+            const double r = block_sum(sq, red);
+            if (threadIdx.x == 0) tail.out[q] = r;
+            __syncthreads();
+        }
+        if (threadIdx.x == 0) *tail.statusOut = *tail.statusIn;
+    }
 }
 
 // Distributed x-update, shared vertices: x from the exchanged total, and their share of ||D x - z||^2 over the LOCAL slots
@@ -1358,8 +1416,7 @@ __global__ void __launch_bounds__(TPB_V) k_xfirst(size_t N, const int *incPtr, c
     }
     if (sharedSlot && sharedSlot[p] >= 0) return;
     const double val = (double)(incPtr[p + 1] - incPtr[p]);
-    const double sv = w * (w * (val * zs - usum[i]));
-    x[i] = ((m * xb) + dtsq * sv) / tdiag[p];
+    x[i] = xfirst_value(m, dtsq, w, val, xb, zs, usum[i], tdiag[p]);
 }
 
 // K7 for the vertices shared with other ranks only (so that their partial sums can be formed and pushed before the bulk pass)
@@ -1621,6 +1678,16 @@ struct mmadmm_ctx {
     int *F[4] = {nullptr, nullptr, nullptr, nullptr};
     uint8_t *mask = nullptr, *fixedBits = nullptr, *nonIntBits = nullptr;
     double *x = nullptr, *xPrev = nullptr, *xBar = nullptr, *Vc = nullptr, *tdiag = nullptr;
+    // single-GPU step tail (StepTail): the next step's xBar and first x-solve written by the last k_xupdate<UREC> of a step;
+    // specValid: they belong to the state x / xPrev / usum / dt / rho / tau as it is now (anything that touches those clears it)
+    double *xSpec = nullptr, *xBarSpec = nullptr;
+    bool specValid = false;
+    unsigned *finTicket = nullptr;
+    // option "step_tail": bit 0 speculative first solve, bit 1 final reduction in k_xupdate.  Measured (scripts/gpu_r2_r.sh, C2
+    // ms/step): 0: 0.770, 1: 0.759, 2: 0.776, 3: 0.771 -- the ticket + fences of the fused reduction cost the 4,100 CTAs of
+    // k_xupdate more (+0.019 ms) than the k_finalize launch they replace (0.011 ms), so only bit 0 is on by default
+    int tailMode = 1;
+    long long specUsed = 0;
     double *z = nullptr, *u = nullptr, *B = nullptr, *gs = nullptr;
     int *incPtr = nullptr, *incIdx = nullptr, *vorder = nullptr, *valence_d = nullptr;
     double *grid = nullptr, *ax = nullptr, *ay = nullptr, *az = nullptr;
@@ -2366,6 +2433,10 @@ int create_impl(mmadmm_ctx *ctx, const double *Vp, const double *Vc, const int *
     CK(cudaMalloc(&ctx->x, sizeof(double) * NV));
     CK(cudaMalloc(&ctx->xPrev, sizeof(double) * NV));
     CK(cudaMalloc(&ctx->xBar, sizeof(double) * NV));
+    CK(cudaMalloc(&ctx->xSpec, sizeof(double) * NV));
+    CK(cudaMalloc(&ctx->xBarSpec, sizeof(double) * NV));
+    CK(cudaMalloc(&ctx->finTicket, sizeof(unsigned)));
+    CK(cudaMemsetAsync(ctx->finTicket, 0, sizeof(unsigned), st));
     CK(cudaMalloc(&ctx->tdiag, sizeof(double) * (size_t)P));
     CK(cudaMemcpyAsync(ctx->x, Vp, sizeof(double) * NV, cudaMemcpyHostToDevice, st));
     CK(cudaMemcpyAsync(ctx->xPrev, ctx->x, sizeof(double) * NV, cudaMemcpyDeviceToDevice, st));
@@ -2749,12 +2820,12 @@ int xupdate_shared(mmadmm_ctx *ctx, const double *zsrc, bool push, unsigned long
     // primal partials of this launch are all zero (shared vertices leave theirs to xupdate_finish): scratch region
     k_xupdate<D, ZSRC, UZERO, PRIMAL, UREC><<<ctx->nblkSh, TPB_V, 0, ctx->stream>>>(
         ctx->nShared, ctx->Es, ctx->incPtr, ctx->incIdx, ctx->z, ctx->u, zsrc, ctx->xBar, ctx->tdiag, ctx->m, dtsq, ctx->w, ctx->x,
-        ctx->partPrimal + ctx->nblkV + ctx->nblkSh, ctx->sharedSlot, ctx->sPart, ctx->sharedIdx, ctx->usum, hp, 0);
+        ctx->partPrimal + ctx->nblkV + ctx->nblkSh, ctx->sharedSlot, ctx->sPart, ctx->sharedIdx, ctx->usum, hp, 0, StepTail());
     ctx->launches++;
     return MMADMM_OK;
 }
 template <int D, bool ZSRC, bool UZERO, bool PRIMAL, bool UREC>
-int xupdate_bulk(mmadmm_ctx *ctx, const double *zsrc, bool skipShared) {
+int xupdate_bulk(mmadmm_ctx *ctx, const double *zsrc, bool skipShared, const StepTail &tail = StepTail()) {
     const double dtsq = ctx->dt * ctx->dt;
     auto kern = k_xupdate<D, ZSRC, UZERO, PRIMAL, UREC>;
     if constexpr (UREC) {   // slots per chunk / resident CTAs of the recurrence form ("xup_variant", A/B runs; 0 = tuned default)
@@ -2765,6 +2836,8 @@ int xupdate_bulk(mmadmm_ctx *ctx, const double *zsrc, bool skipShared) {
             case 4: kern = k_xupdate<D, ZSRC, UZERO, PRIMAL, UREC, 4, 2>; break;
             case 5: kern = k_xupdate<D, ZSRC, UZERO, PRIMAL, UREC, 2, 8>; break;
             case 6: kern = k_xupdate<D, ZSRC, UZERO, PRIMAL, UREC, 8, 1>; break;
+            case 7: kern = k_xupdate<D, ZSRC, UZERO, PRIMAL, UREC, 2, 5>; break;
+            case 8: kern = k_xupdate<D, ZSRC, UZERO, PRIMAL, UREC, 4, 5>; break;
             // measured with the single-pass form (scripts/gpu_r2_q.sh): 2D 2 slots per chunk at 6 CTAs per SM (40 registers, no
             // spills) 0.143 ms against 0.147 (2,8) / 0.145 (4,4) / 0.166 (8,2); 3D 4 slots at 4 CTAs 0.256 against 0.280 (8,1) / 0.295 (2,6)
             default: kern = (D == 2) ? k_xupdate<D, ZSRC, UZERO, PRIMAL, UREC, 2, 6> : k_xupdate<D, ZSRC, UZERO, PRIMAL, UREC, 4, 4>; break;
@@ -2772,7 +2845,7 @@ int xupdate_bulk(mmadmm_ctx *ctx, const double *zsrc, bool skipShared) {
     }
     kern<<<ctx->nblkV, TPB_V, 0, ctx->stream>>>(
         ctx->P, ctx->Es, ctx->incPtr, ctx->incIdx, ctx->z, ctx->u, zsrc, ctx->xBar, ctx->tdiag, ctx->m, dtsq, ctx->w, ctx->x,
-        ctx->partPrimal, ctx->dist ? ctx->sharedSlot : nullptr, ctx->sPart, ctx->vorder, ctx->usum, HaloPush(), skipShared ? 1 : 0);
+        ctx->partPrimal, ctx->dist ? ctx->sharedSlot : nullptr, ctx->sPart, ctx->vorder, ctx->usum, HaloPush(), skipShared ? 1 : 0, tail);
     ctx->launches++;
     return MMADMM_OK;
 }
@@ -2822,9 +2895,20 @@ template <int D> int step_impl(mmadmm_ctx *ctx, int nIters, double tol, double *
     cudaStream_t st = ctx->stream;
     const int P = ctx->P;
     const size_t NV = (size_t)P * D;
+    const bool fast = ctx->usumPeriod > 0;   // x-updates on the per-vertex dual sums (k_xfirst, k_xupdate<UREC>)
+    // Single GPU: the previous step's last k_xupdate already wrote this step's xBar and first x-solve (StepTail).  Taking them
+    // over is a rotation of buffers: xPrev <- x, x <- xSpec, xBar <- xBarSpec -- exactly what k_xfirst<EXTRAP> would store.
+    const bool tailOk = fast && !ctx->dist && !(ctx->projMask & 2);
+    const bool specUse = ctx->specValid && tailOk && !ctx->gradUse && ctx->stepsTaken > 2;
+    ctx->specValid = false;
+    if (specUse) {
+        double *t = ctx->xPrev;
+        ctx->xPrev = ctx->x; ctx->x = ctx->xSpec; ctx->xSpec = t;
+        std::swap(ctx->xBar, ctx->xBarSpec);
+        ctx->specUsed++;
+    }
     ElemArgs<D> a = ctx->elemArgs<D>(tol / 100);   // BFGS tolerance tol/100, 50 iterations (src/Mesh.cpp:968)
     const int gE = ctx->nblkE, gV = ctx->nblkV;
-    const bool fast = ctx->usumPeriod > 0;   // x-updates on the per-vertex dual sums (k_xfirst, k_xupdate<UREC>)
     const bool ovl = ctx->dist && ctx->nShared > 0 && ctx->p2p;   // exchange overlapped with the bulk vertex passes
     bool extrapFused = false;
 
@@ -2861,7 +2945,7 @@ template <int D> int step_impl(mmadmm_ctx *ctx, int nIters, double tol, double *
     ctx->phaseBegin(2);
     {
         auto xfirst = [&]() {   // all vertices that are not shared with another rank; no element state is read
-            if (!fast) return;
+            if (!fast || specUse) return;
             const int *ss = ctx->dist ? ctx->sharedSlot : nullptr;
             if (extrapFused)
                 k_xfirst<D, true><<<cdiv(NV, TPB_V), TPB_V, 0, st>>>(NV, ctx->incPtr, ctx->usum, nullptr, ctx->xBar, ctx->xPrev, ctx->tdiag,
@@ -2879,6 +2963,7 @@ template <int D> int step_impl(mmadmm_ctx *ctx, int nIters, double tol, double *
 
     double Ihstart = 0, primal = 0, dual = 0;
     int i;
+    bool specWritten = false;
     for (i = 0; i < nIters; i++) {
         a.zsrc = (i == 0) ? zsrc : nullptr;
         a.uZero = (i == 0 && uZero) ? 1 : 0;
@@ -2895,18 +2980,36 @@ template <int D> int step_impl(mmadmm_ctx *ctx, int nIters, double tol, double *
         ctx->hessComputed = true;
         ctx->stepTaken = true;
         ctx->phaseBegin(2);
+        bool fusedFin = false;
         {
             const bool rec = fast && ctx->usumAge + 1 < ctx->usumPeriod;
             ctx->usumAge = rec ? ctx->usumAge + 1 : 0;
-            int rcx = rec ? launch_xupdate_t<D, false, false, true, true>(ctx, nullptr) : launch_xupdate_t<D, false, false, true>(ctx, nullptr);
+            int rcx = MMADMM_OK;
+            specWritten = false;
+            if (rec && tailOk && ctx->tailMode) {   // the step's last kernel (see StepTail)
+                StepTail tl;
+                if (ctx->tailMode & 1) { tl.xPrev = ctx->xPrev; tl.xNext = ctx->xSpec; tl.xBarNext = ctx->xBarSpec; specWritten = true; }
+                if (ctx->tailMode & 2) {
+                    tl.nProx = ctx->nProxPart; tl.partIh = ctx->partIh; tl.partDual = ctx->partDual; tl.out = ctx->scal_hd;
+                    tl.statusIn = ctx->status_d; tl.statusOut = ctx->status_hd; tl.ticket = ctx->finTicket;
+                    fusedFin = true;
+                }
+                rcx = xupdate_bulk<D, false, false, true, true>(ctx, nullptr, false, tl);
+            } else {
+                rcx = rec ? launch_xupdate_t<D, false, false, true, true>(ctx, nullptr) : launch_xupdate_t<D, false, false, true>(ctx, nullptr);
+            }
             if (rcx) return rcx;
         }
         ctx->phaseEnd();
         ctx->phaseBegin(3);
         const int nbp = ctx->nProxPart;
-        // synchronises; sums over ranks on a distributed context
-        int rc = finalize_scalars(ctx, nbp, ctx->partIh, gV + ((ctx->dist && ctx->nShared > 0) ? ctx->nblkSh : 0), ctx->partPrimal, nbp,
+        int rc = MMADMM_OK;
+        if (fusedFin) {   // the scalars and the status word are in mapped host memory when the stream has drained
+            CK(cudaStreamSynchronize(st));
+        } else {          // synchronises; sums over ranks on a distributed context
+            rc = finalize_scalars(ctx, nbp, ctx->partIh, gV + ((ctx->dist && ctx->nShared > 0) ? ctx->nblkSh : 0), ctx->partPrimal, nbp,
                                   ctx->partDual, 0);
+        }
         ctx->phaseEnd();
         if (rc) return rc;
         ctx->admmIters++;
@@ -2925,6 +3028,7 @@ template <int D> int step_impl(mmadmm_ctx *ctx, int nIters, double tol, double *
     }
     CK(cudaGetLastError());
     ctx->stepsTaken++;
+    ctx->specValid = specWritten;
     if (ctx->wb.mode) {   // updateAfterStep: Vp <- x
         int rcw = wb_issue(ctx);
         if (rcw) return rcw;
@@ -3259,6 +3363,7 @@ int mmadmm_set_dt(mmadmm_ctx *ctx, double dt) {
     if (!ctx || !(dt >= 0)) return MMADMM_EINVAL;
     CK(cudaSetDevice(ctx->device));
     ctx->dt = dt;
+    ctx->specValid = false;
     k_tdiag<<<cdiv(ctx->P, 256), 256, 0, ctx->stream>>>(ctx->P, ctx->incPtr, ctx->valence_d, ctx->m, dt * dt, ctx->w, ctx->tdiag);
     ctx->launches++;
     CK(cudaStreamSynchronize(ctx->stream));
@@ -3275,6 +3380,7 @@ int mmadmm_step(mmadmm_ctx *ctx, int nIters, double tol, double *Ih, int *itersT
 int mmadmm_euler_step(mmadmm_ctx *ctx, double *Ih) {
     if (!ctx) return MMADMM_EINVAL;
     CK(cudaSetDevice(ctx->device));
+    ctx->specValid = false;
     return (ctx->D == 2) ? euler_impl<2>(ctx, Ih) : euler_impl<3>(ctx, Ih);
 }
 
@@ -3282,6 +3388,7 @@ int mmadmm_backward_euler_step(mmadmm_ctx *ctx, double dt, double tol, double *I
     if (!ctx || !(tol > 0.0)) return MMADMM_EINVAL;
     CK(cudaSetDevice(ctx->device));
     if (!(dt > 0.0)) dt = ctx->dt;
+    ctx->specValid = false;
     return (ctx->D == 2) ? beuler_impl<2>(ctx, dt, tol, Ih, newtonIters, linIters) : beuler_impl<3>(ctx, dt, tol, Ih, newtonIters, linIters);
 }
 
@@ -3410,6 +3517,7 @@ int mmadmm_restore(mmadmm_ctx *ctx) {
     if (!ctx) return MMADMM_EINVAL;
     mmadmm_ctx::Ckpt &c = ctx->ck;
     if (!c.valid) { ctx->err = "mmadmm_restore: no checkpoint has been taken"; return MMADMM_EINVAL; }
+    ctx->specValid = false;
     CK(cudaSetDevice(ctx->device));
     int rc = wb_fence(ctx);
     if (rc) return rc;
@@ -3607,6 +3715,13 @@ int mmadmm_get_timing(mmadmm_ctx *ctx, double *ms5, long long *counts5, int rese
 
 int mmadmm_set_option(mmadmm_ctx *ctx, const char *name, int value) {
     if (!ctx || !name) return MMADMM_EINVAL;
+    if (!strcmp(name, "spec_used")) return (int)std::min<long long>(ctx->specUsed, 1 << 30);   // query: steps started from the tail
+    ctx->specValid = false;
+    if (!strcmp(name, "step_tail")) {   // single-GPU step tail (StepTail): bit 0 speculative first solve, bit 1 fused final reduction
+        if (value < 0 || value > 3) return MMADMM_EINVAL;
+        ctx->tailMode = value;
+        return MMADMM_OK;
+    }
     if (!strcmp(name, "timing")) {
         ctx->timingOn = value != 0;
         if (ctx->timingOn) {   // event pool up front: creating events is not something to do between two steps
@@ -3679,6 +3794,7 @@ void mmadmm_destroy(mmadmm_ctx *ctx) {
     cudaFree(ctx->ck.B); cudaFree(ctx->ck.hist);
     for (int v = 0; v < 4; v++) cudaFree(ctx->F[v]);
     cudaFree(ctx->mask); cudaFree(ctx->fixedBits); cudaFree(ctx->nonIntBits);
+    cudaFree(ctx->xSpec); cudaFree(ctx->xBarSpec); cudaFree(ctx->finTicket);
     cudaFree(ctx->x); cudaFree(ctx->xPrev); cudaFree(ctx->xBar); cudaFree(ctx->Vc); cudaFree(ctx->tdiag);
     cudaFree(ctx->z); cudaFree(ctx->u); cudaFree(ctx->usum); cudaFree(ctx->B); cudaFree(ctx->gs);
     cudaFree(ctx->incPtr); cudaFree(ctx->incIdx); cudaFree(ctx->vorder); cudaFree(ctx->valence_d);

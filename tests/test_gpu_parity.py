@@ -339,6 +339,39 @@ def test_checkpoint_restore_continues_bit_identically(D, nx, kind):
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("D,nx,kind", [(2, 96, 3), (3, 12, 3)])
+def test_step_tail_modes_are_bit_identical(D, nx, kind):
+    """Option "step_tail" (single GPU): the last k_xupdate of a step also writes the NEXT step's predictor and first x-solve
+    (bit 0; the next step then starts by rotating buffers instead of launching k_xfirst) and reduces the step's scalars in its
+    last CTA (bit 1).  Both are re-arrangements of the same arithmetic: positions, element state and BFGS histograms are
+    bit-identical in all four modes, also across a dt change and an energy query between steps; the scalars agree to
+    rounding (another summation tree)."""
+    Vp, F, mask = mm.generate_uniform_rect_mesh(D, nx, nx, nx if D == 3 else 0)
+    mon = mm.TestMonitor(D, kind).evaluate_at_vertices(Vp)
+    res = {}
+    for mode in (0, 1, 2, 3):
+        mesh = mm.Mesh(Vp.copy(), F.copy(), mask, mon, rho=50.0, tau=0.5)
+        s = mm.MeshIntegrator(0.025, mesh)
+        s.set_option("step_tail", mode)
+        ih = []
+        for k in range(9):
+            if k == 6:
+                s.set_dt(0.02)        # invalidates what the previous step wrote ahead
+            ih.append((s.step(10, 1e-3), s.last["primal"], s.last["dual"], s.last["iters"]))
+            if k == 4:
+                s.getEnergy()
+        used = s.L.mmadmm_set_option(s.h, b"spec_used", 0)
+        assert (used >= 4) if (mode & 1) else (used == 0), (mode, used)
+        res[mode] = (np.array(ih), mesh.Vp.copy(), s.state(0), s.state(1), s.state(2), s.stats()["bfgs_hist"].copy())
+        s.close()
+    for mode in (1, 2, 3):
+        for a, b in zip(res[mode][1:], res[0][1:]):
+            assert np.array_equal(a, b), mode
+        assert np.array_equal(res[mode][0][:, 3], res[0][0][:, 3])
+        assert np.allclose(res[mode][0], res[0][0], rtol=1e-12, atol=0)
+
+
+@pytest.mark.gpu
 @pytest.mark.parametrize("D,nx,kind", [(2, 48, 3), (3, 6, 3)])
 def test_deferred_writeback_equals_strict(D, nx, kind):
     """Mesh::updateAfterStep (Vp <- x after every step, src/Mesh.cpp:1030-1035) as mmadmm_set_writeback: strict = landed when step()
@@ -381,7 +414,7 @@ def test_deferred_writeback_equals_strict(D, nx, kind):
 def test_boundary_sliding_matches_oracle(D, nx, kind, disc, mask_bits):
     """Option "boundary_projection": Mesh::projectOntoBoundary (src/Mesh.cpp:118-241) at the two call sites of the ADMM path the
     reference has commented out (:975-984 prox, :1020-1026 updateAfterStep).  NEW behaviour -- no reference result exists with it
-    on, so parity is GPU vs the CPU oracle only: 1e-9 on energies, equal iteration counts, and the FREE nodes end ON the boundary
+    on, so parity is GPU vs the CPU oracle only: 1e-9 on energies (1e-7 on the disc, see below), equal iteration counts, and the FREE nodes end ON the boundary
     when the updateAfterStep site is active.  Node positions are held to 1e-7: with FREE rim nodes the per-element solves run up
     to a dozen BFGS iterations behind a finite-difference Hessian (cf. test_3d_free_boundary_comp_mesh_and_graduse) and the
     projection adds branchy geometry on top; measured on the B200: 1e-15 on the box, 8.7e-9 on the disc after four steps."""
@@ -400,7 +433,9 @@ def test_boundary_sliding_matches_oracle(D, nx, kind, disc, mask_bits):
     for s in range(6):
         ih = solver.step(10, 1e-3); ro = orc.step(10, 1e-3)
         assert ro["status"] == 0 and solver.last["iters"] == ro["iters"], (s, solver.last, ro)
-        assert abs(ih - ro["Ih"]) <= TOL_E2E * abs(ro["Ih"])
+        # energies: 1e-9 on the boxes; on the disc they follow the positions (8.7e-9 there -> 6.1e-9 on the energy, measured),
+        # and which side of 1e-9 they land on changes with the rounding of unrelated kernels
+        assert abs(ih - ro["Ih"]) <= (TOL_X if disc else TOL_E2E) * abs(ro["Ih"]), (s, ih, ro["Ih"])
         assert rel(mesh.Vp, orc.x()) < TOL_X, s
     assert rel(solver.state(0), orc.z()) < 1e-6       # element copies of the FREE vertices: 3.5e-7 measured on the 3D cube
     free = mask == mm.BOUNDARY_FREE
