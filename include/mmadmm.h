@@ -92,6 +92,20 @@ int mmadmm_update_monitor(mmadmm_ctx *ctx, const double *monVertex);
 /* Replaces MeshIntegrator<D>::getEnergy -> Mesh::computeEnergy (src/Mesh.cpp:496-530). */
 int mmadmm_energy(mmadmm_ctx *ctx, double *I);
 
+/* NO COUNTERPART IN THE REFERENCE: added for callers that cannot call cudaMalloc
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  The same energy as mmadmm_energy (same
+ * kernels, same fixed-order reduction, bit-identical result), but the per-block partial sums go into a file-scope
+ * `static __device__` array of MMADMM_NOALLOC_MAX_BLOCKS doubles (1 MiB; every GPU that loads the library holds it until
+ * exit) and the call makes no cudaMalloc / cudaFree / allocating library call.
+ *   x_dev : node positions to evaluate at, DEVICE pointer, P x D row-major (as mmadmm_get_x_device writes them); NULL = the
+ *           context's current positions.  I : host pointer, receives the energy.
+ * Limits: single-GPU contexts only; at most MMADMM_NOALLOC_MAX_BLOCKS * 128 = 16,777,216 elements (larger meshes ->
+ * MMADMM_EINVAL with a message in mmadmm_last_error).  All calls on one GPU share the one array, which keeps the last
+ * call's partial sums (nothing in it has to start at zero: a call overwrites what it reads): calls that overlap on the GPU
+ * (two contexts / two host threads on the same device) race -- serialise them. */
+#define MMADMM_NOALLOC_MAX_BLOCKS 131072
+int mmadmm_energy_noalloc(mmadmm_ctx *ctx, const double *x_dev, double *I);
+
 /* Replaces Mesh::updateAfterStep / copyX (src/Mesh.cpp:996-1004,1016-1036): current node positions, P x D.
  * On a distributed context this is a collective call that assembles the GLOBAL vector on every rank. */
 int mmadmm_get_x(mmadmm_ctx *ctx, double *x);

@@ -28,7 +28,7 @@ ERRORS = {1: "EINVAL", 2: "ECUDA", 3: "EINVERTED", 4: "ESINGULAR", 5: "ENCCL", 6
 
 # every symbol include/mmadmm.h declares (checked by tests/test_abi.py)
 ABI_SYMBOLS = [
-    "mmadmm_create", "mmadmm_set_dt", "mmadmm_step", "mmadmm_energy", "mmadmm_get_x", "mmadmm_get_x_device", "mmadmm_get_x_colmajor", "mmadmm_host_register", "mmadmm_host_unregister", "mmadmm_get_F",
+    "mmadmm_create", "mmadmm_set_dt", "mmadmm_step", "mmadmm_energy", "mmadmm_energy_noalloc", "mmadmm_get_x", "mmadmm_get_x_device", "mmadmm_get_x_colmajor", "mmadmm_host_register", "mmadmm_host_unregister", "mmadmm_get_F",
     "mmadmm_euler_step", "mmadmm_backward_euler_step", "mmadmm_backward_euler_jacobian", "mmadmm_grid_dims", "mmadmm_get_state", "mmadmm_eval_monitor", "mmadmm_block_grad", "mmadmm_block_grad_at", "mmadmm_get_stats",
     "mmadmm_get_timing", "mmadmm_set_option", "mmadmm_stream", "mmadmm_destroy", "mmadmm_last_error",
     "mmadmm_version", "mmadmm_plan_create", "mmadmm_plan_sizes", "mmadmm_plan_get", "mmadmm_plan_destroy",
@@ -80,6 +80,7 @@ def lib():
                                     C.c_double, C.c_int, C.c_int, C.POINTER(vp)]
         L.mmadmm_step.argtypes = [vp, C.c_int, C.c_double, _c_dp, _c_ip, _c_dp, _c_dp]
         L.mmadmm_energy.argtypes = [vp, _c_dp]
+        L.mmadmm_energy_noalloc.argtypes = [vp, vp, _c_dp]
         L.mmadmm_set_dt.argtypes = [vp, C.c_double]
         L.mmadmm_euler_step.argtypes = [vp, _c_dp]
         L.mmadmm_backward_euler_step.argtypes = [vp, C.c_double, C.c_double, _c_dp, _c_ip, _c_ip]
@@ -469,6 +470,15 @@ class MeshIntegrator:
             self.fence()
         v = C.c_double()
         self._check(self.L.mmadmm_energy(self.h, C.byref(v)))
+        return v.value
+
+    def getEnergyNoAlloc(self, x_dev=None):
+        """mmadmm_energy_noalloc: the same energy through the static device scratch (no allocation in the call);
+        x_dev = device address (int) of P x D row-major node positions, None = the context's current positions."""
+        if self._sync_vp == "deferred":
+            self.fence()
+        v = C.c_double()
+        self._check(self.L.mmadmm_energy_noalloc(self.h, C.c_void_p(x_dev) if x_dev else None, C.byref(v)))
         return v.value
 
     def done(self):

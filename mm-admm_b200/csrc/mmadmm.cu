@@ -21,6 +21,7 @@
 #include <vector>
 
 #include <dlfcn.h>
+#include <pthread.h>
 #include <time.h>
 
 #include "../../include/mmadmm.h"
@@ -3417,6 +3418,67 @@ int mmadmm_energy(mmadmm_ctx *ctx, double *I) {
     if (!ctx || !I) return MMADMM_EINVAL;
     CK(cudaSetDevice(ctx->device));
     return (ctx->D == 2) ? energy_impl<2>(ctx, I) : energy_impl<3>(ctx, I);
+}
+
+// ------------------------------------------------------------------------------------------------
+// Allocation-free energy evaluation (no counterpart in the reference; see include/mmadmm.h).
+// k_energy's per-block partial sums go into ONE file-scope device array instead of a cudaMalloc'ed buffer.  Every GPU that loads
+// the library holds the array (1 MiB + 256 B) until exit; every call on a device shares it, so calls that overlap on the GPU race.
+// Nothing in it has to start at zero: a call overwrites partials [0, nblk) and reads back exactly those.
+// ------------------------------------------------------------------------------------------------
+static __device__ __align__(256) double g_energy_scratch[MMADMM_NOALLOC_MAX_BLOCKS + 32];
+
+// In host code `g_energy_scratch` is only a host-side stand-in for the symbol: the device address comes from
+// cudaGetSymbolAddress, once per device, with that device current.
+static double *energy_scratch_ptr(int device, cudaError_t *err) {
+    static double *ptrs[64] = {};
+    static pthread_mutex_t mu = PTHREAD_MUTEX_INITIALIZER;
+    *err = cudaSuccess;
+    if (device < 0 || device >= 64) { *err = cudaErrorInvalidDevice; return nullptr; }
+    pthread_mutex_lock(&mu);
+    double *p = ptrs[device];
+    if (!p) {
+        int cur = -1;
+        *err = cudaGetDevice(&cur);
+        if (*err == cudaSuccess && cur != device) *err = cudaSetDevice(device);
+        if (*err == cudaSuccess) *err = cudaGetSymbolAddress((void **)&p, g_energy_scratch);
+        if (*err == cudaSuccess) ptrs[device] = p; else p = nullptr;
+    }
+    pthread_mutex_unlock(&mu);
+    return p;
+}
+
+int mmadmm_energy_noalloc(mmadmm_ctx *ctx, const double *x_dev, double *I) {
+    if (!ctx || !I) return MMADMM_EINVAL;
+    if (ctx->dist) { ctx->err = "mmadmm_energy_noalloc: single-GPU contexts only"; return MMADMM_EINVAL; }
+    if (ctx->nblkE > MMADMM_NOALLOC_MAX_BLOCKS) {
+        char b[256];
+        snprintf(b, sizeof(b), "mmadmm_energy_noalloc: %d elements need %d partial sums, the static scratch holds %d (at most %lld elements)",
+                 ctx->E, ctx->nblkE, MMADMM_NOALLOC_MAX_BLOCKS, (long long)MMADMM_NOALLOC_MAX_BLOCKS * TPB);
+        ctx->err = b;
+        return MMADMM_EINVAL;
+    }
+    CK(cudaSetDevice(ctx->device));
+    cudaError_t se;
+    double *scratch = energy_scratch_ptr(ctx->device, &se);
+    CK(se);
+    cudaStream_t st = ctx->stream;
+    if (ctx->D == 2) {
+        ElemArgs<2> a = ctx->elemArgs<2>(0.0);
+        if (x_dev) a.x = x_dev;
+        k_energy<2><<<ctx->nblkE, TPB, 0, st>>>(a, scratch);
+    } else {
+        ElemArgs<3> a = ctx->elemArgs<3>(0.0);
+        if (x_dev) a.x = x_dev;
+        k_energy<3><<<ctx->nblkE, TPB, 0, st>>>(a, scratch);
+    }
+    // same fixed-order final reduction as mmadmm_energy; the scalar and the status word land in the context's mapped host words
+    k_finalize<<<1, 1024, 0, st>>>(ctx->nblkE, scratch, 0, nullptr, 0, nullptr, ctx->scal_hd + 3, ctx->status_d, ctx->status_hd);
+    ctx->launches += 2;
+    CK(cudaGetLastError());
+    CK(cudaStreamSynchronize(st));
+    *I = ctx->scal_h[3];
+    return check_status(ctx);
 }
 
 int mmadmm_get_x(mmadmm_ctx *ctx, double *x) {
