@@ -501,6 +501,8 @@ def method2_line(args):
     mon = mm.TestMonitor(2, 4).evaluate_at_vertices(Vp)
     mesh = mm.Mesh(Vp.copy(), F.copy(), mask, mon, rho=50.0, tau=0.5, integration_mode=2)
     solver = mm.MeshIntegrator(0.025, mesh, sync_vp=False)
+    for kv in args.opt:                                  # e.g. m2_row_block=1 (row per thread), 2 (default: one vertex), 4
+        solver.set_option(kv.split("=")[0], int(kv.split("=")[1]))
     warm = []
     for _ in range(max(1, min(args.warmup, 2))):
         t0 = time.perf_counter()
@@ -535,7 +537,7 @@ def method2_line(args):
             "warmup": len(warm), "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
             "data": "synthetic",
             "config": {"workload": f"Method 2 (backward Euler) on SquareGrid 2D nx=ny={nx} ({F.shape[0]:,} triangles), MEx4, dt=0.025 tau=0.5, tol 1e-3",
-                       "unknowns": n, "jacobian_nnz": nnz, "newton_iters": newton, "bicgstab_iters": lin},
+                       "unknowns": n, "jacobian_nnz": nnz, "newton_iters": newton, "bicgstab_iters": lin, "options": args.opt},
             "wall_ms_per_step": wall / K * 1e3, "gpu_launches": launches,
             "e2e": {"value": K / wall, "unit": "outer steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 64 * max(lin, 1) // K,
                     "note": "wall clock through MeshIntegrator.backwardsEulerStep; as in the reference this path does not write Vp back per step"},

@@ -258,18 +258,31 @@ int mmadmm_pcg_spmv(mmadmm_pcg *h, const double *x, double *y);
 int mmadmm_pcg_precond(mmadmm_pcg *h, const double *r, double *z);
 /* ILU(0) factor values in A's CSR pattern (unit lower below the diagonal, U on and above it). */
 int mmadmm_pcg_get_ilu(mmadmm_pcg *h, double *lu);
+/* New values on the SAME pattern, from a DEVICE array in the handle's CSR order: replaces LASolver's numeric re-factorisation
+ * (jac->factor after set_entry, lib/LASolver/ILU_class.cpp:300-444, as Mesh::buildEulerJac runs it at every Jacobian rebuild,
+ * src/Mesh.cpp:1111-1261).  Pattern, level schedules and buffers are kept; the Jacobi diagonal and (precond = 1) the ILU(0)
+ * factor are recomputed on the device, the factor level by level in LASolver's IKJ order with separately rounded multiply and
+ * subtract: bit-identical to a factor computed on the host.  MMADMM_ESINGULAR on a zero pivot. */
+int mmadmm_pcg_refactor_device(mmadmm_pcg *h, const double *val_dev);
 /* "spmv_format": 0 (default) = CSR with a sub-warp per row; 1 = SELL-C-sigma (C = 32 rows per slice = one warp, sigma = 4096-row
  * sorting window, column-major slices: every value / index load is one coalesced line; a thread owns a row and accumulates in
  * ascending column order like LASolver's matmult, accel_class.cpp:521-549), built from the CSR arrays on first use.  Both serve
  * every solver entry point.  "sell_padding_permille" is a query: padding entries per 1000 stored entries.
  * "tri_mode": 1 (default) = in the ILU(0) triangular solves every run of consecutive levels of at most 8192 rows is ONE launch
  * of a thread-block cluster that walks the levels with cluster barriers (wider levels keep a launch each); 0 = one launch
- * per level.  Results are bit-identical. */
+ * per level.  Results are bit-identical.
+ * "row_block": BS = 1 (default), 2, 3, 4 or 6 (the last group may be short): the triangular solves schedule GROUPS of BS consecutive rows, one
+ * thread solving its group's rows in natural order with the operands of its own group in registers, so only dependencies
+ * between groups make levels: on a Jacobian with D x D vertex blocks BS = D halves (2D) / thirds (3D) the level count (the
+ * Method 2 context sets BS = D; option "m2_row_block").  Same FMA chains in the same order: bit-identical to BS = 1. */
 int mmadmm_pcg_set_option(mmadmm_pcg *h, const char *name, int value);
-/* info4 = {threads per row of the SpMV kernel, lower levels, upper levels, kernels launched so far}. */
+/* info4 = {threads per row of the SpMV kernel, lower levels, upper levels (of groups when row_block > 1), kernels launched so far}. */
 int mmadmm_pcg_info(mmadmm_pcg *h, int *info4);
 /* Average device time (ms, CUDA events) of one SpMV + dot launch over `reps` launches. */
 int mmadmm_pcg_time_spmv(mmadmm_pcg *h, int reps, double *ms);
+/* Average device time (ms, CUDA events) of one preconditioner application z = M^{-1} r (Jacobi scaling, or the two ILU(0)
+ * triangular solves in the current "tri_mode" / "row_block") over `reps` applications. */
+int mmadmm_pcg_time_precond(mmadmm_pcg *h, int reps, double *ms);
 const char *mmadmm_pcg_last_error(mmadmm_pcg *h);
 /* Measured FP64 FMA peak of the device in TFLOP/s (DFMA microbenchmark, 8 independent chains per thread). */
 int mmadmm_measure_fp64_peak(int device, double *tflops);

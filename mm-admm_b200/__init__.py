@@ -35,7 +35,7 @@ ABI_SYMBOLS = [
     "mmadmm_comm_unique_id", "mmadmm_create_dist", "mmadmm_local_sizes", "mmadmm_get_x_local",
     "mmadmm_pcg_create", "mmadmm_pcg_solve", "mmadmm_pcg_solve_device", "mmadmm_pcg_bicgstab", "mmadmm_pcg_bicgstab_device", "mmadmm_pcg_spmv", "mmadmm_pcg_precond",
     "mmadmm_update_monitor", "mmadmm_set_writeback", "mmadmm_writeback_fence", "mmadmm_checkpoint", "mmadmm_restore",
-    "mmadmm_pcg_get_ilu", "mmadmm_pcg_set_option", "mmadmm_pcg_info", "mmadmm_pcg_time_spmv", "mmadmm_pcg_last_error", "mmadmm_pcg_destroy", "mmadmm_measure_fp64_peak",
+    "mmadmm_pcg_get_ilu", "mmadmm_pcg_refactor_device", "mmadmm_pcg_set_option", "mmadmm_pcg_info", "mmadmm_pcg_time_spmv", "mmadmm_pcg_time_precond", "mmadmm_pcg_last_error", "mmadmm_pcg_destroy", "mmadmm_measure_fp64_peak",
 ]
 
 
@@ -129,8 +129,10 @@ def lib():
         L.mmadmm_pcg_spmv.argtypes = [vp, _c_dp, _c_dp]
         L.mmadmm_pcg_precond.argtypes = [vp, _c_dp, _c_dp]
         L.mmadmm_pcg_get_ilu.argtypes = [vp, _c_dp]
+        L.mmadmm_pcg_refactor_device.argtypes = [vp, vp]
         L.mmadmm_pcg_info.argtypes = [vp, _c_ip]
         L.mmadmm_pcg_time_spmv.argtypes = [vp, C.c_int, _c_dp]
+        L.mmadmm_pcg_time_precond.argtypes = [vp, C.c_int, _c_dp]
         L.mmadmm_pcg_last_error.restype = C.c_char_p
         L.mmadmm_pcg_last_error.argtypes = [vp]
         L.mmadmm_measure_fp64_peak.argtypes = [C.c_int, _c_dp]
@@ -283,10 +285,20 @@ class PCG:
         self._check(self.L.mmadmm_pcg_get_ilu(self.h, _dp(lu)))
         return lu
 
+    def refactor_device(self, val_dev):
+        """mmadmm_pcg_refactor_device: new values (device address, CSR order) on the same pattern; Jacobi diagonal and ILU(0)
+        factor recomputed on the device (LASolver's numeric `factor`)."""
+        self._check(self.L.mmadmm_pcg_refactor_device(self.h, C.c_void_p(int(val_dev))))
+
     def info(self):
         a = np.zeros(4, dtype=np.int32)
         self._check(self.L.mmadmm_pcg_info(self.h, _ip(a)))
         return dict(lanes=int(a[0]), lower_levels=int(a[1]), upper_levels=int(a[2]), launches=int(a[3]))
+
+    def time_precond(self, reps=5):
+        ms = C.c_double()
+        self._check(self.L.mmadmm_pcg_time_precond(self.h, int(reps), C.byref(ms)))
+        return ms.value
 
     def time_spmv(self, reps=20):
         ms = C.c_double()

@@ -1731,6 +1731,7 @@ struct mmadmm_ctx {
         mmadmm_pcg *solver = nullptr;
         long long newtonIters = 0, linIters = 0, jacBuilds = 0;
         int triMode = 1;   // mmadmm_pcg "tri_mode" of the Method 2 solver (option "m2_tri_mode")
+        int rowBlock = -1; // mmadmm_pcg "row_block" of the Method 2 solver (option "m2_row_block"); -1 = D (one vertex per thread)
     } m2;
 
     // checkpoint of the whole integrator state (mmadmm_checkpoint / mmadmm_restore)
@@ -3144,10 +3145,18 @@ template <int D> int m2_build_jac(mmadmm_ctx *ctx, double dt) {
     a.x = m.vp0;
     k_m2_jac<D><<<cdiv(ctx->P, 128), 128, 0, st>>>(a, ctx->mask, ctx->incPtr, ctx->incIdx, m.adjPtr_d, m.adjIdx_d, dt / ctx->tau, m.val_d);
     ctx->launches++;
+    if (m.solver) {
+        // a rebuild: same pattern, level schedules and buffers; numeric ILU(0) re-factorisation on the device (jac->factor)
+        CK(cudaStreamSynchronize(st));
+        CK(cudaGetLastError());
+        int rcr = mmadmm_pcg_refactor_device(m.solver, m.val_d);
+        if (rcr) { ctx->err = std::string("Method 2 Jacobian: ") + mmadmm_pcg_last_error(m.solver); return rcr; }
+        m.jacValid = true; m.jacDt = dt; m.jacBuilds++;
+        return MMADMM_OK;
+    }
     CK(cudaMemcpyAsync(m.val_h.data(), m.val_d, sizeof(double) * (size_t)m.nnz, cudaMemcpyDeviceToHost, st));
     CK(cudaStreamSynchronize(st));
     CK(cudaGetLastError());
-    if (m.solver) { mmadmm_pcg_destroy(m.solver); m.solver = nullptr; }
     int rc = mmadmm_pcg_create(m.N, m.rowptr_h.data(), m.col_h.data(), m.val_h.data(), 1, ctx->device, &m.solver);
     if (rc) {
         ctx->err = std::string("Method 2 Jacobian: ") + (m.solver ? mmadmm_pcg_last_error(m.solver) : "solver allocation failed");
@@ -3155,6 +3164,8 @@ template <int D> int m2_build_jac(mmadmm_ctx *ctx, double dt) {
         return rc;
     }
     mmadmm_pcg_set_option(m.solver, "tri_mode", m.triMode);
+    rc = mmadmm_pcg_set_option(m.solver, "row_block", m.rowBlock < 0 ? D : m.rowBlock);
+    if (rc) { ctx->err = std::string("Method 2 row_block: ") + mmadmm_pcg_last_error(m.solver); return rc; }
     m.jacValid = true; m.jacDt = dt; m.jacBuilds++;
     return MMADMM_OK;
 }
@@ -3410,7 +3421,7 @@ int mmadmm_backward_euler_jacobian(mmadmm_ctx *ctx, int *sizes2, int *rowptr, in
     if (sizes2) { sizes2[0] = m.N; sizes2[1] = m.nnz; }
     if (rowptr) std::memcpy(rowptr, m.rowptr_h.data(), sizeof(int) * ((size_t)m.N + 1));
     if (col) std::memcpy(col, m.col_h.data(), sizeof(int) * (size_t)m.nnz);
-    if (val) std::memcpy(val, m.val_h.data(), sizeof(double) * (size_t)m.nnz);
+    if (val) CK(cudaMemcpy(val, m.val_d, sizeof(double) * (size_t)m.nnz, cudaMemcpyDeviceToHost));   // val_h is only the first build's copy
     return MMADMM_OK;
 }
 
@@ -3796,6 +3807,14 @@ int mmadmm_set_option(mmadmm_ctx *ctx, const char *name, int value) {
     if (!strcmp(name, "m2_tri_mode")) {   // Method 2 triangular solves: 1 = one cluster launch per solve, 0 = one launch per level
         ctx->m2.triMode = value ? 1 : 0;
         if (ctx->m2.solver) mmadmm_pcg_set_option(ctx->m2.solver, "tri_mode", ctx->m2.triMode);
+        return MMADMM_OK;
+    }
+    if (!strcmp(name, "m2_row_block")) {  // rows per thread of the Method 2 triangular solves: 1, D (default, -1), 2 D
+        ctx->m2.rowBlock = value;
+        if (ctx->m2.solver) {
+            int rc = mmadmm_pcg_set_option(ctx->m2.solver, "row_block", value < 0 ? ctx->D : value);
+            if (rc) { ctx->err = std::string("m2_row_block: ") + mmadmm_pcg_last_error(ctx->m2.solver); return rc; }
+        }
         return MMADMM_OK;
     }
     if (!strcmp(name, "prox_variant")) { ctx->proxVariant = value; return MMADMM_OK; }

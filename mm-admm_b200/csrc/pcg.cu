@@ -192,6 +192,158 @@ k_tri_cluster(int l0, int l1, const int *__restrict__ lvlOff, const int *__restr
     }
 }
 
+// ILU(0) numeric factor on A's own pattern, one L-level per launch (rows of a level need only rows of earlier levels): IKJ order
+// exactly as LASolver's level-0 factor (ILU_class.cpp:300-444) and the numpy restatement run it on the host -- for k < i in row i
+// ascending: l_ik = a_ik / u_kk, then a_ij -= l_ik u_kj for the j > k of pattern(i), found by merging the two sorted rows.  The
+// multiply and the subtract are rounded separately (__dmul_rn / __dsub_rn: host compilers do not contract them), so the factor
+// is bit-identical to the host one.  flag: 1 = zero pivot.
+__global__ void __launch_bounds__(TPB) k_ilu_level(int lo, int hi, const int *__restrict__ rows, const int *__restrict__ rowptr,
+                                                    const int *__restrict__ col, const int *__restrict__ diagPos, double *lu, int *flag) {
+    const int t = lo + blockIdx.x * TPB + threadIdx.x;
+    if (t >= hi) return;
+    const int i = rows[t];
+    const int dp = diagPos[i], re = rowptr[i + 1];
+    for (int k = rowptr[i]; k < dp; k++) {
+        const int c = col[k];
+        const int dc = diagPos[c];
+        const double piv = lu[dc];
+        if (piv == 0.0) { *flag = 1; return; }
+        const double lik = lu[k] / piv;
+        lu[k] = lik;
+        int p = k + 1;
+        const int ce = rowptr[c + 1];
+        for (int kk = dc + 1; kk < ce && p < re; kk++) {
+            const int cj = col[kk];
+            while (p < re && col[p] < cj) p++;
+            if (p < re && col[p] == cj) { lu[p] = __dsub_rn(lu[p], __dmul_rn(lik, lu[kk])); p++; }
+        }
+    }
+    if (lu[dp] == 0.0) *flag = 1;
+}
+__global__ void k_inv_diag(int n, const int *__restrict__ diagPos, const double *__restrict__ val, double *invDiag) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) invDiag[i] = 1.0 / val[diagPos[i]];   // Eigen's DiagonalPreconditioner stores 1/diag
+}
+
+// ---- block rows (option "row_block" = BS) ----
+// A GROUP is BS consecutive rows [base, base + BS) solved by ONE thread in natural order (ascending for L, descending for U): the
+// dependencies inside a group are honoured by the sequence, so only dependencies on OTHER groups define levels.  On the Method 2
+// Jacobian (D x D blocks per vertex pair) BS = D halves (2D) / thirds (3D) the number of levels, BS = 2D shortens the wavefront
+// once more.  Every row is still the same FMA chain in ascending k; an operand of the thread's own group comes from a register
+// instead of memory: bit-identical to the row-per-thread kernels (tests/test_zz_gpu_method2.py).
+template <int BS> __device__ __forceinline__ double pick_own(const double (&own)[BS], int g) {
+    double v = own[0];
+#pragma unroll
+    for (int q = 1; q < BS; q++) v = (g == q) ? own[q] : v;
+    return v;
+}
+template <bool LOWER, int BS>
+__device__ __forceinline__ void tri_group_plain(int n, int base, const int *__restrict__ rowptr, const int *__restrict__ diagPos,
+                                                const int *__restrict__ col, const double *__restrict__ lu,
+                                                const double *__restrict__ rhs, double *out) {
+    double own[BS];
+#pragma unroll
+    for (int j = 0; j < BS; j++) own[j] = 0.0;
+#pragma unroll
+    for (int jj = 0; jj < BS; jj++) {
+        const int j = LOWER ? jj : BS - 1 - jj;
+        const int i = base + j;
+        if (i >= n) continue;   // the last group may be short
+        const int dp = diagPos[i];
+        const int kb = LOWER ? rowptr[i] : dp + 1, ke = LOWER ? dp : rowptr[i + 1];
+        double s = rhs[i];
+        for (int k = kb; k < ke; k++) {
+            const int c = col[k], g = c - base;
+            const double v = (g >= 0 && g < BS) ? pick_own<BS>(own, g) : __ldcg(out + c);
+            s -= lu[k] * v;
+        }
+        own[j] = LOWER ? s : s / lu[dp];
+        out[i] = own[j];
+    }
+}
+// one level of groups, full-width launch
+template <bool LOWER, int BS>
+__global__ void __launch_bounds__(TPB) k_tri_level_blk(int n, int lo, int hi, const int *__restrict__ groups, const int *__restrict__ rowptr,
+                                                        const int *__restrict__ col, const int *__restrict__ diagPos,
+                                                        const double *__restrict__ lu, const double *__restrict__ rhs, double *out) {
+    const int t = lo + blockIdx.x * TPB + threadIdx.x;
+    if (t >= hi) return;
+    tri_group_plain<LOWER, BS>(n, groups[t], rowptr, diagPos, col, lu, rhs, out);
+}
+// k_tri_cluster on groups: the first CACHE (column, factor) pairs of every row of the thread's group are fetched inside the split
+// cluster barrier; after the wait ALL their operands that live in other groups are requested at once (one L2 round trip per
+// level, not one per row), then the BS chains run in sequence.
+template <bool LOWER, int BS, int CACHE>
+__global__ void __cluster_dims__(TC_CLUSTER, 1, 1) __launch_bounds__(TC_THREADS)
+k_tri_cluster_blk(int n, int l0, int l1, const int *__restrict__ lvlOff, const int *__restrict__ groups, const int2 *__restrict__ kbe,
+                  const int *__restrict__ rowptr, const int *__restrict__ diagPos, const int *__restrict__ col,
+                  const double *__restrict__ lu, const double *__restrict__ rhs, double *out) {
+    const int tid = blockIdx.x * TC_THREADS + threadIdx.x;
+    constexpr int NTHR = TC_THREADS * TC_CLUSTER;
+    int lo = lvlOff[l0], hi = lvlOff[l0 + 1];
+    int base = 0, kb[BS], ke[BS], c[BS][CACHE];
+    double s[BS], dv[BS], a[BS][CACHE];
+#pragma unroll
+    for (int j = 0; j < BS; j++) { kb[j] = ke[j] = 0; s[j] = 0.0; dv[j] = 1.0; }
+    auto fetch = [&](int t) {
+        base = groups[t];
+#pragma unroll
+        for (int j = 0; j < BS; j++) {
+            const int2 e = kbe[(size_t)t * BS + j];   // rows past n (short last group): empty extent
+            kb[j] = e.x; ke[j] = e.y;
+            if (base + j < n) {
+                s[j] = rhs[base + j];
+                if (!LOWER) dv[j] = lu[e.x - 1];   // U rows start right after the diagonal
+            }
+#pragma unroll
+            for (int q = 0; q < CACHE; q++)
+                if (e.x + q < e.y) { c[j][q] = col[e.x + q]; a[j][q] = lu[e.x + q]; }
+        }
+    };
+    if (lo + tid < hi) fetch(lo + tid);
+    for (int l = l0; l < l1; l++) {
+        if (lo + tid < hi) {
+            double o[BS][CACHE], own[BS];
+#pragma unroll
+            for (int j = 0; j < BS; j++) {
+                own[j] = 0.0;
+#pragma unroll
+                for (int q = 0; q < CACHE; q++) {
+                    const int g = c[j][q] - base;
+                    o[j][q] = (kb[j] + q < ke[j] && !(g >= 0 && g < BS)) ? __ldcg(out + c[j][q]) : 0.0;
+                }
+            }
+#pragma unroll
+            for (int jj = 0; jj < BS; jj++) {
+                const int j = LOWER ? jj : BS - 1 - jj;
+                double sj = s[j];
+#pragma unroll
+                for (int q = 0; q < CACHE; q++)
+                    if (kb[j] + q < ke[j]) {
+                        const int g = c[j][q] - base;
+                        const double v = (g >= 0 && g < BS) ? pick_own<BS>(own, g) : o[j][q];
+                        sj -= a[j][q] * v;
+                    }
+                for (int k = kb[j] + CACHE; k < ke[j]; k++) {
+                    const int cc = col[k], g = cc - base;
+                    const double v = (g >= 0 && g < BS) ? pick_own<BS>(own, g) : __ldcg(out + cc);
+                    sj -= lu[k] * v;
+                }
+                own[j] = LOWER ? sj : sj / dv[j];
+                if (base + j < n) out[base + j] = own[j];
+            }
+        }
+        for (int t = lo + tid + NTHR; t < hi; t += NTHR)   // levels wider than the cluster: further passes, no register cache
+            tri_group_plain<LOWER, BS>(n, groups[t], rowptr, diagPos, col, lu, rhs, out);
+        cluster_arrive_release();
+        if (l + 1 < l1) {
+            lo = hi; hi = lvlOff[l + 2];
+            if (lo + tid < hi) fetch(lo + tid);
+        }
+        cluster_wait_acquire();
+    }
+}
+
 // scal layout (device doubles): 0 rz, 1 pAp, 2 alpha, 3 beta, 4 rr, 5 rzNew, 6 bb
 enum { S_RZ = 0, S_PAP = 1, S_ALPHA = 2, S_BETA = 3, S_RR = 4, S_RZNEW = 5, S_BB = 6, S_COUNT = 8 };
 
@@ -317,6 +469,14 @@ struct mmadmm_pcg {
     int *lvlL_d = nullptr, *lvlU_d = nullptr;     // level offsets on the device (k_tri_cluster)
     int2 *kbeL = nullptr, *kbeU = nullptr;        // off-diagonal extent [kb, ke) of the rows in level order (k_tri_cluster)
     int triMode = 1;                              // 1: one cluster launch per triangular solve; 0: one launch per level
+    int *flag_d = nullptr;                        // zero-pivot flag of the device ILU(0) factor
+    int rowBlock = 1;                             // "row_block": rows per group of the triangular solves (1 = row per thread)
+    int *grpL = nullptr, *grpU = nullptr;         // base rows of the groups in level order
+    int *lvlGL_d = nullptr, *lvlGU_d = nullptr;   // group-level offsets (device)
+    int2 *kbeGL = nullptr, *kbeGU = nullptr;      // [group in level order][row of the group]: off-diagonal extent
+    std::vector<int> lvlGL, lvlGU;                // group-level offsets (host)
+    std::vector<int> diagPos_h;
+    bool valHostStale = false;                    // val_h older than the device values (after mmadmm_pcg_refactor_device)
     int spmvFormat = 0;                           // 0: CSR, sub-warp per row; 1: SELL-32-4096 (built on first use)
     int nSlices = 0;
     long long sellEntries = 0;
@@ -369,6 +529,11 @@ int spmv_parts(const mmadmm_pcg *h) {
 // CSR -> SELL-32-4096 on the host (once), uploaded next to the CSR arrays
 int build_sell(mmadmm_pcg *h) {
     if (h->slicePtr) return MMADMM_OK;
+    if (h->valHostStale) {
+        PCK(cudaSetDevice(h->device));
+        PCK(cudaMemcpy(h->val_h.data(), h->val, sizeof(double) * (size_t)h->nnz, cudaMemcpyDeviceToHost));
+        h->valHostStale = false;
+    }
     const int n = h->n, C = 32, SIGMA = 4096;
     const std::vector<int> &rp = h->rowptr_h, &cl = h->col_h;
     const std::vector<double> &vl = h->val_h;
@@ -410,6 +575,96 @@ int build_sell(mmadmm_pcg *h) {
     return MMADMM_OK;
 }
 
+// lu <- ILU(0) of the values in h->val (device), by the L-level schedule; h->flag_d is the zero-pivot flag
+int ilu_factor_device(mmadmm_pcg *h) {
+    PCK(cudaMemcpyAsync(h->lu, h->val, sizeof(double) * (size_t)h->nnz, cudaMemcpyDeviceToDevice, h->stream));
+    PCK(cudaMemsetAsync(h->flag_d, 0, sizeof(int), h->stream));
+    const int nlev = (int)h->lvlL.size() - 1;
+    for (int l = 0; l < nlev; l++) {   // (level 0 rows have no entries left of the diagonal: only their pivot is checked)
+        const int lo = h->lvlL[l], hi = h->lvlL[l + 1];
+        k_ilu_level<<<cdiv(hi - lo, TPB), TPB, 0, h->stream>>>(lo, hi, h->rowsL, h->rowptr, h->col, h->diagPos, h->lu, h->flag_d);
+        h->launches++;
+    }
+    int flag = 0;
+    PCK(cudaMemcpyAsync(&flag, h->flag_d, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+    PCK(cudaStreamSynchronize(h->stream));
+    PCK(cudaGetLastError());
+    if (flag) { h->err = "zero pivot in ILU(0)"; return MMADMM_ESINGULAR; }
+    return MMADMM_OK;
+}
+
+void free_groups(mmadmm_pcg *h) {
+    void *ptrs[6] = {h->grpL, h->grpU, h->lvlGL_d, h->lvlGU_d, h->kbeGL, h->kbeGU};
+    for (void *q : ptrs) {
+        const cudaError_t e = cudaFree(q);
+        if (e != cudaSuccess) h->err = std::string("free_groups: cudaFree: ") + cudaGetErrorString(e);
+    }
+    h->grpL = h->grpU = h->lvlGL_d = h->lvlGU_d = nullptr;
+    h->kbeGL = h->kbeGU = nullptr;
+    h->lvlGL.clear(); h->lvlGU.clear();
+}
+// Level schedule of the groups [g*bs, (g+1)*bs): level(g) = 1 + max level of the OTHER groups its rows depend on.
+int build_groups(mmadmm_pcg *h, int bs) {
+    free_groups(h);
+    h->rowBlock = 1;
+    if (bs == 1) return MMADMM_OK;
+    const int n = h->n;
+    if (h->precond != 1 || (bs != 2 && bs != 3 && bs != 4 && bs != 6)) {
+        h->err = "row_block: 1, 2, 3, 4 or 6 rows per group, on an ILU(0) handle";
+        return MMADMM_EINVAL;
+    }
+    const int ng = (n + bs - 1) / bs;   // the last group may be short
+    const std::vector<int> &rp = h->rowptr_h, &cl = h->col_h, &dg = h->diagPos_h;
+    std::vector<int> lev(ng, 0);
+    auto bucket = [&](int nlev, std::vector<int> &grp, std::vector<int> &off) {
+        off.assign(nlev + 1, 0);
+        for (int g = 0; g < ng; g++) off[lev[g] + 1]++;
+        for (int l = 0; l < nlev; l++) off[l + 1] += off[l];
+        grp.resize(ng);
+        std::vector<int> cur(off.begin(), off.end() - 1);
+        for (int g = 0; g < ng; g++) grp[cur[lev[g]]++] = g * bs;
+    };
+    auto upload = [&](const std::vector<int> &grp, const std::vector<int> &off, bool lower, int **grp_d, int **off_d, int2 **kbe_d) -> cudaError_t {
+        std::vector<int2> e((size_t)ng * bs);
+        for (int t = 0; t < ng; t++)
+            for (int j = 0; j < bs; j++) {
+                const int i = grp[t] + j;
+                e[(size_t)t * bs + j] = i >= n ? make_int2(0, 0) : lower ? make_int2(rp[i], dg[i]) : make_int2(dg[i] + 1, rp[i + 1]);
+            }
+        cudaError_t er;
+        if ((er = cudaMalloc(grp_d, sizeof(int) * (size_t)ng)) != cudaSuccess) return er;
+        if ((er = cudaMalloc(off_d, sizeof(int) * off.size())) != cudaSuccess) return er;
+        if ((er = cudaMalloc(kbe_d, sizeof(int2) * e.size())) != cudaSuccess) return er;
+        if ((er = cudaMemcpy(*grp_d, grp.data(), sizeof(int) * (size_t)ng, cudaMemcpyHostToDevice)) != cudaSuccess) return er;
+        if ((er = cudaMemcpy(*off_d, off.data(), sizeof(int) * off.size(), cudaMemcpyHostToDevice)) != cudaSuccess) return er;
+        return cudaMemcpy(*kbe_d, e.data(), sizeof(int2) * e.size(), cudaMemcpyHostToDevice);
+    };
+    PCK(cudaSetDevice(h->device));
+    std::vector<int> grp;
+    int nl = 0;
+    for (int g = 0; g < ng; g++) {
+        int l = 0;
+        for (int i = g * bs; i < std::min(n, (g + 1) * bs); i++)
+            for (int k = rp[i]; k < dg[i]; k++)
+                if (cl[k] < g * bs) l = std::max(l, lev[cl[k] / bs] + 1);
+        lev[g] = l; nl = std::max(nl, l + 1);
+    }
+    bucket(nl, grp, h->lvlGL);
+    PCK(upload(grp, h->lvlGL, true, &h->grpL, &h->lvlGL_d, &h->kbeGL));
+    int nu = 0;
+    for (int g = ng - 1; g >= 0; g--) {
+        int l = 0;
+        for (int i = g * bs; i < std::min(n, (g + 1) * bs); i++)
+            for (int k = dg[i] + 1; k < rp[i + 1]; k++)
+                if (cl[k] >= (g + 1) * bs) l = std::max(l, lev[cl[k] / bs] + 1);
+        lev[g] = l; nu = std::max(nu, l + 1);
+    }
+    bucket(nu, grp, h->lvlGU);
+    PCK(upload(grp, h->lvlGU, false, &h->grpU, &h->lvlGU_d, &h->kbeGU));
+    h->rowBlock = bs;
+    return MMADMM_OK;
+}
+
 // One triangular solve.  tri_mode 1: runs of consecutive levels that each fit a few passes of the cluster's 2048 threads go
 // out as ONE k_tri_cluster launch (natural-order ILU(0) on a structured 2D mesh: thousands of levels of a few hundred rows);
 // wider levels (e.g. all cell-centre rows of the upper factor, plane-sized levels in 3D) keep one full-width launch each.
@@ -439,8 +694,44 @@ void tri_solve(mmadmm_pcg *h, const std::vector<int> &lvl, const int *lvl_d, con
     }
 }
 
+// Same on groups of BS rows ("row_block").
+template <bool LOWER, int BS, int CACHE>
+void tri_solve_blk(mmadmm_pcg *h, const std::vector<int> &lvl, const int *lvl_d, const int *groups, const int2 *kbe, const double *rhs,
+                   double *out) {
+    const int nlev = (int)lvl.size() - 1;
+    const int wide = 4 * TC_THREADS * TC_CLUSTER;
+    int l = 0;
+    while (l < nlev) {
+        int e = l;
+        if (h->triMode == 1)
+            while (e < nlev && lvl[e + 1] - lvl[e] <= wide) e++;
+        if (e - l >= 4) {
+            k_tri_cluster_blk<LOWER, BS, CACHE><<<TC_CLUSTER, TC_THREADS, 0, h->stream>>>(h->n, l, e, lvl_d, groups, kbe, h->rowptr, h->diagPos,
+                                                                                          h->col, h->lu, rhs, out);
+            h->launches++;
+            l = e;
+        } else {
+            const int lo = lvl[l], hi = lvl[l + 1];
+            k_tri_level_blk<LOWER, BS><<<cdiv(hi - lo, TPB), TPB, 0, h->stream>>>(h->n, lo, hi, groups, h->rowptr, h->col, h->diagPos, h->lu, rhs, out);
+            h->launches++;
+            l++;
+        }
+    }
+}
+template <int BS, int CACHE> void apply_ilu_blk(mmadmm_pcg *h, const double *r, double *z) {
+    tri_solve_blk<true, BS, CACHE>(h, h->lvlGL, h->lvlGL_d, h->grpL, h->kbeGL, r, h->tmp);
+    tri_solve_blk<false, BS, CACHE>(h, h->lvlGU, h->lvlGU_d, h->grpU, h->kbeGU, h->tmp, z);
+}
+
 // z = (LU)^{-1} r by level-scheduled forward and backward substitution
 void apply_ilu(mmadmm_pcg *h, const double *r, double *z) {
+    switch (h->rowBlock) {
+        case 2: apply_ilu_blk<2, 14>(h, r, z); return;
+        case 3: apply_ilu_blk<3, 10>(h, r, z); return;
+        case 4: apply_ilu_blk<4, 8>(h, r, z); return;
+        case 6: apply_ilu_blk<6, 5>(h, r, z); return;
+        default: break;
+    }
     tri_solve<true>(h, h->lvlL, h->lvlL_d, h->rowsL, h->kbeL, r, h->tmp);
     tri_solve<false>(h, h->lvlU, h->lvlU_d, h->rowsU, h->kbeU, h->tmp, z);
 }
@@ -485,31 +776,12 @@ int mmadmm_pcg_create(int n, const int *rowptr, const int *col, const double *va
     PCK(up((void **)&h->col, col, sizeof(int) * (size_t)nnz));
     PCK(up((void **)&h->val, val, sizeof(double) * (size_t)nnz));
     PCK(up((void **)&h->diagPos, diagPos.data(), sizeof(int) * (size_t)n));
+    h->diagPos_h = diagPos;
     std::vector<double> invDiag(n);
     for (int i = 0; i < n; i++) invDiag[i] = 1.0 / val[diagPos[i]];   // Eigen's DiagonalPreconditioner stores 1/diag
     PCK(up((void **)&h->invDiag, invDiag.data(), sizeof(double) * (size_t)n));
-    std::vector<double> lu;
     std::vector<int> rowsL, rowsU;
     if (precond == 1) {
-        // ILU(0), IKJ order on A's own pattern: for k < i in row i: a_ik /= a_kk; a_ij -= a_ik a_kj for j > k in pattern(i)
-        lu.assign(val, val + nnz);
-        std::vector<int> pos(n, -1);
-        for (int i = 0; i < n; i++) {
-            for (int k = rowptr[i]; k < rowptr[i + 1]; k++) pos[col[k]] = k;
-            for (int k = rowptr[i]; k < diagPos[i]; k++) {
-                const int c = col[k];
-                const double piv = lu[diagPos[c]];
-                if (piv == 0.0) { h->err = "zero pivot in ILU(0)"; return MMADMM_ESINGULAR; }
-                const double lik = lu[k] / piv;
-                lu[k] = lik;
-                for (int kk = diagPos[c] + 1; kk < rowptr[c + 1]; kk++) {
-                    const int pj = pos[col[kk]];
-                    if (pj >= 0) lu[pj] -= lik * lu[kk];
-                }
-            }
-            if (lu[diagPos[i]] == 0.0) { h->err = "zero pivot in ILU(0)"; return MMADMM_ESINGULAR; }
-            for (int k = rowptr[i]; k < rowptr[i + 1]; k++) pos[col[k]] = -1;
-        }
         // level schedule: level(i) = 1 + max level of the rows it depends on
         std::vector<int> lev(n, 0);
         int nl = 0;
@@ -534,7 +806,8 @@ int mmadmm_pcg_create(int n, const int *rowptr, const int *col, const double *va
             lev[i] = l; nu = std::max(nu, l + 1);
         }
         bucket(nu, rowsU, h->lvlU);
-        PCK(up((void **)&h->lu, lu.data(), sizeof(double) * (size_t)nnz));
+        PCK(up((void **)&h->lu, nullptr, sizeof(double) * (size_t)nnz));
+        PCK(up((void **)&h->flag_d, nullptr, sizeof(int)));
         PCK(up((void **)&h->rowsL, rowsL.data(), sizeof(int) * (size_t)n));
         PCK(up((void **)&h->rowsU, rowsU.data(), sizeof(int) * (size_t)n));
         {
@@ -549,6 +822,8 @@ int mmadmm_pcg_create(int n, const int *rowptr, const int *col, const double *va
         }
         PCK(up((void **)&h->lvlL_d, h->lvlL.data(), sizeof(int) * h->lvlL.size()));
         PCK(up((void **)&h->lvlU_d, h->lvlU.data(), sizeof(int) * h->lvlU.size()));
+        PCK(cudaStreamSynchronize(h->stream));   // rowsL / rowsU are locals
+        { int rcf = ilu_factor_device(h); if (rcf) return rcf; }   // the numeric factor runs on the device, level by level
     }
     const size_t vb = sizeof(double) * (size_t)n;
     PCK(up((void **)&h->r, nullptr, vb)); PCK(up((void **)&h->z, nullptr, vb)); PCK(up((void **)&h->p, nullptr, vb));
@@ -566,9 +841,18 @@ int mmadmm_pcg_create(int n, const int *rowptr, const int *col, const double *va
 int mmadmm_pcg_set_option(mmadmm_pcg *h, const char *name, int value) {
     if (!h || !name) return MMADMM_EINVAL;
     if (!std::strcmp(name, "tri_mode")) { h->triMode = value ? 1 : 0; return MMADMM_OK; }
+    if (!std::strcmp(name, "row_block")) {
+        PCK(cudaSetDevice(h->device));
+        PCK(cudaStreamSynchronize(h->stream));
+        { cudaError_t e0 = cudaGetLastError(); if (e0 != cudaSuccess) { h->err = std::string("row_block: error pending on entry: ") + cudaGetErrorString(e0); return MMADMM_ECUDA; } }
+        int rc = build_groups(h, value);
+        if (rc) return rc;
+        { cudaError_t e1 = cudaGetLastError(); if (e1 != cudaSuccess) { h->err = std::string("row_block: error left by build_groups: ") + cudaGetErrorString(e1) + " / " + h->err; return MMADMM_ECUDA; } }
+        return MMADMM_OK;
+    }
     if (!std::strcmp(name, "spmv_format")) {   // 0: CSR (sub-warp per row), 1: SELL-32-4096
         if (value != 0 && value != 1) return MMADMM_EINVAL;
-        if (value == 1) { int rc = build_sell(h); if (rc) return rc; }
+        if (value == 1) { int rc = build_sell(h); if (rc) return rc; PCK(cudaGetLastError()); }
         h->spmvFormat = value;
         return MMADMM_OK;
     }
@@ -580,8 +864,9 @@ int mmadmm_pcg_set_option(mmadmm_pcg *h, const char *name, int value) {
 int mmadmm_pcg_info(mmadmm_pcg *h, int *info4) {
     if (!h || !info4) return MMADMM_EINVAL;
     info4[0] = h->lanes;
-    info4[1] = (int)h->lvlL.size() > 0 ? (int)h->lvlL.size() - 1 : 0;
-    info4[2] = (int)h->lvlU.size() > 0 ? (int)h->lvlU.size() - 1 : 0;
+    const std::vector<int> &lL = h->rowBlock > 1 ? h->lvlGL : h->lvlL, &lU = h->rowBlock > 1 ? h->lvlGU : h->lvlU;
+    info4[1] = (int)lL.size() > 0 ? (int)lL.size() - 1 : 0;
+    info4[2] = (int)lU.size() > 0 ? (int)lU.size() - 1 : 0;
     info4[3] = (int)std::min<long long>(h->launches, 2147483647LL);
     return MMADMM_OK;
 }
@@ -617,6 +902,27 @@ int mmadmm_pcg_get_ilu(mmadmm_pcg *h, double *lu) {
 
 // Device-resident solve: b_dev -> x_dev (both n doubles on h's device), zero initial guess like Eigen's solve().
 // Stops when ||r||_2 <= tol ||b||_2 (Eigen::ConjugateGradient's criterion) or after maxit iterations.
+int mmadmm_pcg_refactor_device(mmadmm_pcg *h, const double *val_dev) {
+    if (!h || !val_dev) return MMADMM_EINVAL;
+    PCK(cudaSetDevice(h->device));
+    PCK(cudaMemcpyAsync(h->val, val_dev, sizeof(double) * (size_t)h->nnz, cudaMemcpyDeviceToDevice, h->stream));
+    k_inv_diag<<<cdiv(h->n, TPB), TPB, 0, h->stream>>>(h->n, h->diagPos, h->val, h->invDiag);
+    h->launches++;
+    if (h->slicePtr) {   // the SELL copy holds values too: rebuild it from the new ones (host-side build, rare)
+        PCK(cudaMemcpyAsync(h->val_h.data(), h->val, sizeof(double) * (size_t)h->nnz, cudaMemcpyDeviceToHost, h->stream));
+        PCK(cudaStreamSynchronize(h->stream));
+        cudaFree(h->slicePtr); cudaFree(h->scol); cudaFree(h->sval); cudaFree(h->perm);
+        h->slicePtr = h->scol = h->perm = nullptr; h->sval = nullptr;
+        int rc = build_sell(h);
+        if (rc) return rc;
+    } else {
+        h->valHostStale = true;
+    }
+    if (h->precond == 1) return ilu_factor_device(h);
+    PCK(cudaStreamSynchronize(h->stream));
+    return MMADMM_OK;
+}
+
 int mmadmm_pcg_solve_device(mmadmm_pcg *h, const double *b_dev, double *x_dev, double tol, int maxit, int *iters, double *relres) {
     if (!h || !b_dev || !x_dev) return MMADMM_EINVAL;
     PCK(cudaSetDevice(h->device));
@@ -783,6 +1089,29 @@ int mmadmm_pcg_time_spmv(mmadmm_pcg *h, int reps, double *ms) {
 
 // Measured FP64 FMA throughput of the device (TFLOP/s, 2 flops per DFMA): the denominator of the prox kernel's FP64-pipe
 // figure (MEASURED_PEAKS.json has no FP64 entry; SURVEY.md 8d asks for a DFMA microbenchmark on the box).
+int mmadmm_pcg_time_precond(mmadmm_pcg *h, int reps, double *ms) {
+    if (!h || !ms || reps <= 0) return MMADMM_EINVAL;
+    PCK(cudaSetDevice(h->device));
+    cudaEvent_t e0, e1;
+    PCK(cudaEventCreate(&e0)); PCK(cudaEventCreate(&e1));
+    PCK(cudaMemsetAsync(h->r, 0, sizeof(double) * (size_t)h->n, h->stream));
+    auto apply = [&]() {
+        if (h->precond == 1) apply_ilu(h, h->r, h->z);
+        else { k_jacobi<<<cdiv(h->n, TPB), TPB, 0, h->stream>>>(h->n, h->r, h->invDiag, h->z); h->launches++; }
+    };
+    apply();
+    PCK(cudaEventRecord(e0, h->stream));
+    for (int k = 0; k < reps; k++) apply();
+    PCK(cudaEventRecord(e1, h->stream));
+    PCK(cudaStreamSynchronize(h->stream));
+    PCK(cudaGetLastError());
+    float t = 0.f;
+    PCK(cudaEventElapsedTime(&t, e0, e1));
+    cudaEventDestroy(e0); cudaEventDestroy(e1);
+    *ms = (double)t / reps;
+    return MMADMM_OK;
+}
+
 int mmadmm_measure_fp64_peak(int device, double *tflops) {
     if (!tflops) return MMADMM_EINVAL;
     int ndev = 0;
@@ -820,6 +1149,8 @@ void mmadmm_pcg_destroy(mmadmm_pcg *h) {
     cudaSetDevice(h->device);
     cudaFree(h->rowptr); cudaFree(h->col); cudaFree(h->diagPos); cudaFree(h->val); cudaFree(h->lu); cudaFree(h->invDiag);
     cudaFree(h->rowsL); cudaFree(h->rowsU); cudaFree(h->lvlL_d); cudaFree(h->lvlU_d); cudaFree(h->kbeL); cudaFree(h->kbeU);
+    free_groups(h);
+    cudaFree(h->flag_d);
     cudaFree(h->r); cudaFree(h->z); cudaFree(h->p); cudaFree(h->q); cudaFree(h->x); cudaFree(h->b); cudaFree(h->tmp);
     cudaFree(h->part0); cudaFree(h->part1); cudaFree(h->scal);
     for (int k = 0; k < 4; k++) cudaFree(h->bi[k]);

@@ -81,6 +81,55 @@ def test_pcg_on_coupled_spd_matrix(D, nx, precond):
     s.close()
 
 
+@pytest.mark.parametrize("D,nx", [(2, 16), (3, 5)])
+def test_device_ilu0_factor_and_refactor_are_bit_identical_to_the_host_factor(D, nx):
+    """The ILU(0) factor is computed on the device level by level (k_ilu_level) in LASolver's IKJ order with separately rounded
+    multiply and subtract: the same bits as the numpy restatement (pcg_oracle.ilu0, itself within 1e-14 of the reference's
+    factor).  mmadmm_pcg_refactor_device = LASolver's numeric `factor` on an unchanged pattern: new values from a device array,
+    everything that holds values (Jacobi diagonal, factor, SELL copy) follows."""
+    import torch
+    Vp, F, _ = mesh(D, nx)
+    A = PO.laplacian_like_matrix(F, Vp.shape[0], D, 0.5, 0.5, 50.0)
+    A.sort_indices()
+    n = A.shape[0]
+    rng = np.random.default_rng(7)
+    s = mm.PCG(A.indptr, A.indices, A.data, "ilu0")
+    lu, diag = PO.ilu0(A)
+    assert np.array_equal(s.ilu(), lu)
+    A2 = A.copy()
+    A2.data = A.data * (1.0 + 0.05 * rng.standard_normal(A.nnz))      # no longer symmetric: ILU(0) does not care
+    A2.data[diag] = np.abs(A.data[diag]) * 1.2
+    v = torch.from_numpy(A2.data.copy()).to("cuda:0")
+    torch.cuda.synchronize()
+    s.refactor_device(v.data_ptr())
+    lu2, _ = PO.ilu0(A2)
+    assert np.array_equal(s.ilu(), lu2)
+    fresh = mm.PCG(A2.indptr, A2.indices, A2.data, "ilu0")
+    r = rng.standard_normal(n)
+    assert np.array_equal(s.precond(r), fresh.precond(r))
+    assert np.array_equal(s.spmv(r), fresh.spmv(r))
+    xa, ita, _ = s.bicgstab(r, 1e-8, 2000); xb, itb, _ = fresh.bicgstab(r, 1e-8, 2000)
+    assert ita == itb > 0 and np.array_equal(xa, xb)
+    zf = fresh.precond(r)
+    for bs in (2, 3, 4, 6):                                            # block rows keep serving the refreshed factor
+        s.set_option("row_block", bs)
+        assert np.array_equal(s.precond(-r), -zf)                      # (a different right-hand side first: the result buffer
+        assert np.array_equal(s.precond(r), zf)                        # must be rewritten, not left over from the last call)
+    s.set_option("row_block", 1)
+    s.set_option("spmv_format", 1)                                     # the SELL copy is rebuilt from refreshed values
+    assert rel(s.spmv(r), A2 @ r) < 1e-13
+    v.copy_(torch.from_numpy(A.data))
+    torch.cuda.synchronize()
+    s.refactor_device(v.data_ptr())
+    assert rel(s.spmv(r), A @ r) < 1e-13 and np.array_equal(s.ilu(), lu)
+    bad = A.data.copy(); bad[diag[0]] = 0.0
+    v.copy_(torch.from_numpy(bad)); torch.cuda.synchronize()
+    with pytest.raises(mm.MMADMMError) as ei:
+        s.refactor_device(v.data_ptr())
+    assert "ESINGULAR" in str(ei.value) or "zero pivot" in str(ei.value)
+    s.close(); fresh.close()
+
+
 def test_pcg_rejects_bad_input_and_reports_breakdown():
     indptr = np.array([0, 1, 2], dtype=np.int32); idx = np.array([1, 0], dtype=np.int32); val = np.array([1.0, 1.0])
     with pytest.raises(mm.MMADMMError):
