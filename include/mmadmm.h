@@ -268,9 +268,15 @@ int mmadmm_pcg_refactor_device(mmadmm_pcg *h, const double *val_dev);
  * sorting window, column-major slices: every value / index load is one coalesced line; a thread owns a row and accumulates in
  * ascending column order like LASolver's matmult, accel_class.cpp:521-549), built from the CSR arrays on first use.  Both serve
  * every solver entry point.  "sell_padding_permille" is a query: padding entries per 1000 stored entries.
- * "tri_mode": 1 (default) = in the ILU(0) triangular solves every run of consecutive levels of at most 8192 rows is ONE launch
- * of a thread-block cluster that walks the levels with cluster barriers (wider levels keep a launch each); 0 = one launch
- * per level.  Results are bit-identical.
+ * "tri_mode": how the ILU(0) triangular solves (LASolver's scaler_ILU::solve, ILU_class.cpp:447-527) run.  0 = one launch per
+ * level.  1 (default of a bare handle) = every run of consecutive levels of at most 8192 rows is ONE launch of a thread-block
+ * cluster that walks the levels with cluster barriers (wider levels keep a launch each).  2 (what the Method 2 context uses;
+ * option "m2_tri_mode") = DATAFLOW: one persistent launch per solve, no barrier at all -- the result vector is pre-filled with
+ * a sentinel, a row's 8-byte result is its own ready flag, consumers poll their operands through L2, warps claim 32-group
+ * chunks in level order from an atomic counter; the factor is read from a chunk-major copy (coalesced), in BS x BS block
+ * form when the pattern is made of dense blocks and row_block = BS ("tri_blocks" = 0 forces the generic form).
+ * "tri_layout": 1 = the cluster kernels of tri_mode 1 read a level-major (ELL) copy of the factor instead of CSR.
+ * All modes and layouts run every row's FMA chain in ascending column order: results are bit-identical.
  * "row_block": BS = 1 (default), 2, 3, 4 or 6 (the last group may be short): the triangular solves schedule GROUPS of BS consecutive rows, one
  * thread solving its group's rows in natural order with the operands of its own group in registers, so only dependencies
  * between groups make levels: on a Jacobian with D x D vertex blocks BS = D halves (2D) / thirds (3D) the level count (the

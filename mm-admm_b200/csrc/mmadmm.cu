@@ -1730,8 +1730,9 @@ struct mmadmm_ctx {
         double *val_d = nullptr, *vp0 = nullptr, *xn = nullptr, *rhs = nullptr, *dx = nullptr, *part = nullptr;
         mmadmm_pcg *solver = nullptr;
         long long newtonIters = 0, linIters = 0, jacBuilds = 0;
-        int triMode = 1;   // mmadmm_pcg "tri_mode" of the Method 2 solver (option "m2_tri_mode")
+        int triMode = 2;   // mmadmm_pcg "tri_mode" of the Method 2 solver (option "m2_tri_mode"): 2 = dataflow solve
         int rowBlock = -1; // mmadmm_pcg "row_block" of the Method 2 solver (option "m2_row_block"); -1 = D (one vertex per thread)
+        int triLayout = 1; // mmadmm_pcg "tri_layout" of the Method 2 solver (option "m2_tri_layout"): 1 = level-ELL copy of the factor
     } m2;
 
     // checkpoint of the whole integrator state (mmadmm_checkpoint / mmadmm_restore)
@@ -3163,9 +3164,8 @@ template <int D> int m2_build_jac(mmadmm_ctx *ctx, double dt) {
         if (m.solver) { mmadmm_pcg_destroy(m.solver); m.solver = nullptr; }
         return rc;
     }
-    mmadmm_pcg_set_option(m.solver, "tri_mode", m.triMode);
-    rc = mmadmm_pcg_set_option(m.solver, "row_block", m.rowBlock < 0 ? D : m.rowBlock);
-    if (rc) { ctx->err = std::string("Method 2 row_block: ") + mmadmm_pcg_last_error(m.solver); return rc; }
+    rc = mmadmm_pcg_set_option(m.solver, "tri_schedule", (m.rowBlock < 0 ? D : m.rowBlock) | (m.triLayout << 8) | ((m.triMode + 1) << 12));
+    if (rc) { ctx->err = std::string("Method 2 tri_schedule: ") + mmadmm_pcg_last_error(m.solver); return rc; }
     m.jacValid = true; m.jacDt = dt; m.jacBuilds++;
     return MMADMM_OK;
 }
@@ -3804,16 +3804,21 @@ int mmadmm_set_option(mmadmm_ctx *ctx, const char *name, int value) {
         return MMADMM_OK;
     }
     if (!strcmp(name, "stats")) { ctx->statsOn = value != 0; return MMADMM_OK; }
-    if (!strcmp(name, "m2_tri_mode")) {   // Method 2 triangular solves: 1 = one cluster launch per solve, 0 = one launch per level
-        ctx->m2.triMode = value ? 1 : 0;
-        if (ctx->m2.solver) mmadmm_pcg_set_option(ctx->m2.solver, "tri_mode", ctx->m2.triMode);
+    if (!strcmp(name, "m2_tri_mode")) {   // Method 2 triangular solves: 2 = dataflow (one persistent launch), 1 = cluster launches, 0 = one launch per level
+        if (value < 0 || value > 2) return MMADMM_EINVAL;
+        ctx->m2.triMode = value;
+        if (ctx->m2.solver) {
+            int rc = mmadmm_pcg_set_option(ctx->m2.solver, "tri_mode", ctx->m2.triMode);
+            if (rc) { ctx->err = std::string("m2_tri_mode: ") + mmadmm_pcg_last_error(ctx->m2.solver); return rc; }
+        }
         return MMADMM_OK;
     }
-    if (!strcmp(name, "m2_row_block")) {  // rows per thread of the Method 2 triangular solves: 1, D (default, -1), 2 D
-        ctx->m2.rowBlock = value;
+    if (!strcmp(name, "m2_row_block") || !strcmp(name, "m2_tri_layout")) {
+        // rows per thread of the Method 2 triangular solves: 1, D (default, -1), 2 D; level-ELL copy of the factor: 1 (default) / 0
+        if (name[3] == 'r') ctx->m2.rowBlock = value; else ctx->m2.triLayout = value ? 1 : 0;
         if (ctx->m2.solver) {
-            int rc = mmadmm_pcg_set_option(ctx->m2.solver, "row_block", value < 0 ? ctx->D : value);
-            if (rc) { ctx->err = std::string("m2_row_block: ") + mmadmm_pcg_last_error(ctx->m2.solver); return rc; }
+            int rc = mmadmm_pcg_set_option(ctx->m2.solver, "tri_schedule", (ctx->m2.rowBlock < 0 ? ctx->D : ctx->m2.rowBlock) | (ctx->m2.triLayout << 8) | ((ctx->m2.triMode + 1) << 12));
+            if (rc) { ctx->err = std::string(name) + ": " + mmadmm_pcg_last_error(ctx->m2.solver); return rc; }
         }
         return MMADMM_OK;
     }

@@ -25,6 +25,7 @@
 #include <algorithm>
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -344,6 +345,438 @@ k_tri_cluster_blk(int n, int l0, int l1, const int *__restrict__ lvlOff, const i
     }
 }
 
+// ---- level-ELL copy of the factor ("tri_layout" = 1) ----
+// The cluster kernels above read every row where CSR put it: along a wavefront the rows of one level lie ~1 MB apart (one DRAM
+// page and one TLB entry per row, 4- and 8-byte loads that share no sector between the threads of a warp) and the extent of a row
+// must arrive before its entries can be requested.  Here every level that fits one pass of the cluster (<= 2048 groups) owns a
+// CONTIGUOUS block: plane (j, q) = entry q of row j of the groups, in the level's group order, so thread t reads element t of each
+// plane -- coalesced, one page, no dependent load.  U blocks carry the diagonal as plane 0.  meta[l] = {first group, last group + 1,
+// block offset or -1 (level not in this layout), planes per row}.  Pads: column -1.  The arithmetic is untouched (same chains,
+// ascending entries): bit-identical to the CSR kernels.
+__global__ void k_lell_fill(size_t slots, const int *__restrict__ src, const double *__restrict__ lu, double *val) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < slots) { const int k = src[i]; val[i] = k >= 0 ? lu[k] : 1.0; }
+}
+template <bool LOWER, int BS, int CACHE>
+__global__ void __cluster_dims__(TC_CLUSTER, 1, 1) __launch_bounds__(TC_THREADS)
+k_tri_cluster_lell(int n, int l0, int l1, const int4 *__restrict__ meta, const int *__restrict__ groups, const int *__restrict__ colT,
+                   const double *__restrict__ valT, const double *__restrict__ rhs, double *out
+#ifdef MMADMM_TRI_PROF
+                   , int pmode   // timing experiments only (results are wrong for pmode != 0): 1 no `out` gathers, 2 no factor loads, 3 barrier only, 4 no fences
+#endif
+) {
+#ifndef MMADMM_TRI_PROF
+    constexpr int pmode = 0;
+#endif
+    const int tid = blockIdx.x * TC_THREADS + threadIdx.x;
+    constexpr int P0 = LOWER ? 0 : 1;
+    int4 cur = meta[l0];
+    int4 nxt = (l0 + 1 < l1) ? meta[l0 + 1] : cur;
+    int base = 0, baseN = 0, c[BS][CACHE];
+    double s[BS], dv[BS], a[BS][CACHE];
+#pragma unroll
+    for (int j = 0; j < BS; j++) { s[j] = 0.0; dv[j] = 1.0; }
+    // registers <- this thread's group of level mt: right-hand sides, diagonals, the first CACHE planes of every row
+    auto fetch = [&](const int4 &mt, int b) {
+        const int w = mt.y - mt.x, MP = mt.w + P0;
+        const size_t o0 = (size_t)mt.z + tid;
+#pragma unroll
+        for (int j = 0; j < BS; j++) {
+            s[j] = (b + j < n) ? rhs[b + j] : 0.0;
+            if (!LOWER) dv[j] = valT[o0 + (size_t)(j * MP) * w];
+#pragma unroll
+            for (int q = 0; q < CACHE; q++) {
+                c[j][q] = -1;
+                if (q < mt.w && pmode < 2) {
+                    const size_t o = o0 + (size_t)(j * MP + P0 + q) * w;
+                    c[j][q] = colT[o];
+                    a[j][q] = valT[o];
+                }
+            }
+        }
+    };
+    if (tid < cur.y - cur.x) { base = groups[cur.x + tid]; fetch(cur, base); }
+    if (l0 + 1 < l1 && tid < nxt.y - nxt.x) baseN = groups[nxt.x + tid];
+    for (int l = l0; l < l1; l++) {
+        const int w = cur.y - cur.x, MP = cur.w + P0;
+        if (tid < w) {
+            double o[BS][CACHE], own[BS];
+#pragma unroll
+            for (int j = 0; j < BS; j++) {
+                own[j] = 0.0;
+#pragma unroll
+                for (int q = 0; q < CACHE; q++) {
+                    const int cc = c[j][q], g = cc - base;
+                    o[j][q] = (cc >= 0 && !(g >= 0 && g < BS) && pmode != 1) ? __ldcg(out + cc) : 0.0;
+                }
+            }
+#pragma unroll
+            for (int jj = 0; jj < BS; jj++) {
+                const int j = LOWER ? jj : BS - 1 - jj;
+                double sj = s[j];
+#pragma unroll
+                for (int q = 0; q < CACHE; q++) {
+                    const int cc = c[j][q], g = cc - base;
+                    if (cc >= 0) {
+                        const double v = (g >= 0 && g < BS) ? pick_own<BS>(own, g) : o[j][q];
+                        sj -= a[j][q] * v;
+                    }
+                }
+                for (int q = CACHE; q < cur.w; q++) {   // rows longer than the register cache: the remaining planes, still coalesced
+                    const size_t off = (size_t)cur.z + tid + (size_t)(j * MP + P0 + q) * w;
+                    const int cc = colT[off], g = cc - base;
+                    if (cc >= 0) {
+                        const double v = (g >= 0 && g < BS) ? pick_own<BS>(own, g) : __ldcg(out + cc);
+                        sj -= valT[off] * v;
+                    }
+                }
+                own[j] = LOWER ? sj : sj / dv[j];
+                if (base + j < n && pmode != 3) out[base + j] = own[j];
+            }
+        }
+        if (pmode == 4) asm volatile("barrier.cluster.arrive.relaxed.aligned;" ::: "memory"); else cluster_arrive_release();
+        if (l + 1 < l1) {
+            cur = nxt; base = baseN;
+            if (tid < cur.y - cur.x && pmode != 3) fetch(cur, base);
+            if (l + 2 < l1) {
+                nxt = meta[l + 2];
+                if (tid < nxt.y - nxt.x) baseN = groups[nxt.x + tid];
+            }
+        }
+        if (pmode == 4) asm volatile("barrier.cluster.wait.aligned;" ::: "memory"); else cluster_wait_acquire();
+    }
+}
+
+// ---- dataflow ("sync-free") triangular solve: "tri_mode" = 2 ----
+// No barrier between levels at all.  The result vector is pre-filled with a sentinel bit pattern; a row's 8-byte result IS its
+// ready flag: a consumer polls its operands with gpu-scope relaxed loads until none is the sentinel, then runs the same FMA chain
+// in ascending k and publishes its own result with one relaxed store (no fence: there is no separate flag to order against).
+// Work is cut into CHUNKS of 32 groups in level order, every level padded to a whole chunk, so the 32 lanes of a warp never
+// depend on each other (a lane spinning on a lane of its own warp would wait forever at the reconvergence point).  Warps of a
+// persistent grid CLAIM chunks in order from an atomic counter: a chunk only depends on chunks claimed earlier by warps that
+// are running, so the wavefront cannot deadlock whatever the residency of the grid.  Factor entries come from a chunk-ELL copy
+// (plane (j, q) of a chunk = 32 contiguous entries: coalesced, loaded before the operands are polled), U chunks carry the
+// diagonal as plane 0.  A level costs one store-to-visible plus one L2 round trip instead of a cluster barrier with its
+// release/acquire fences (measured: 1.8-2.5 us of a 3.4-5.3 us level), and all SMs stream the factor.
+// Polling is bounded (trap after ~1 s): a protocol bug is a CUDA error, never a hung GPU.
+constexpr unsigned long long TRI_SENTINEL = 0xFFF8DEADBEEF0001ull;   // a NaN payload no computation produces
+__device__ __forceinline__ double ld_relaxed_gpu(const double *p) {
+    double v;
+    asm volatile("ld.relaxed.gpu.global.f64 %0, [%1];" : "=d"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_relaxed_gpu(double *p, double v) { asm volatile("st.relaxed.gpu.global.f64 [%0], %1;" ::"l"(p), "d"(v) : "memory"); }
+__global__ void k_tri_sf_prepare(int n, double *out, unsigned *counter) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) out[i] = __longlong_as_double((long long)TRI_SENTINEL);
+    if (i == 0) *counter = 0u;
+}
+// one operand, polled on its own (rows longer than the register cache)
+__device__ __forceinline__ double tri_sf_wait(const double *p) {
+    for (int spins = 0;; spins++) {
+        const double v = ld_relaxed_gpu(p);
+        if ((unsigned long long)__double_as_longlong(v) != TRI_SENTINEL) return v;
+        if (spins > 4) __nanosleep(64);
+        if (spins > (1 << 24)) __trap();
+    }
+}
+#ifdef MMADMM_TRI_PROF
+// timing experiments: per chunk {claimed, factor planes in registers, proxy operand seen, all operands seen, results stored} (ns)
+__device__ unsigned long long g_sf_prof[5 * 65536];
+__device__ __forceinline__ unsigned long long gtimer() { unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); return t; }
+#define SF_STAMP(k) do { if (lane == 0 && chunk >= profLo && chunk < profLo + 65536) g_sf_prof[5 * (chunk - profLo) + (k)] = gtimer(); } while (0)
+#else
+#define SF_STAMP(k) do { } while (0)
+#endif
+template <bool LOWER, int BS, int CACHE>
+__global__ void __launch_bounds__(TC_THREADS) k_tri_syncfree(int n, int nChunks, const longlong2 *__restrict__ meta, const int *__restrict__ items,
+                                                            const int *__restrict__ colT, const double *__restrict__ valT,
+                                                            const double *__restrict__ rhs, double *out, unsigned *counter
+#ifdef MMADMM_TRI_PROF
+                                                            , int profLo
+#endif
+) {
+    static_assert(BS * CACHE <= 32, "operand mask is one word");
+    const int lane = threadIdx.x & 31;
+    constexpr int P0 = LOWER ? 0 : 1;
+    int chunk = 0;
+    if (lane == 0) chunk = (int)atomicAdd(counter, 1u);
+    chunk = __shfl_sync(0xffffffffu, chunk, 0);
+    while (chunk < nChunks) {
+        int next = 0;
+        if (lane == 0) next = (int)atomicAdd(counter, 1u);   // claimed now, needed after this chunk: the round trip is hidden
+        SF_STAMP(0);
+        const longlong2 mt = meta[chunk];
+        const int m = (int)mt.y, MP = m + P0;
+        const int base = items[(size_t)chunk * 32 + lane];   // -1: padding lane (its planes hold column -1)
+        const size_t o0 = (size_t)mt.x + lane;
+        int c[BS][CACHE];
+        double a[BS][CACHE], s[BS], dv[BS], o[BS][CACHE], own[BS];
+        unsigned need = 0u;
+#pragma unroll
+        for (int j = 0; j < BS; j++) {
+            own[j] = 0.0;
+            s[j] = (base >= 0 && base + j < n) ? rhs[base + j] : 0.0;
+            dv[j] = LOWER ? 1.0 : valT[o0 + (size_t)(j * MP) * 32];
+#pragma unroll
+            for (int q = 0; q < CACHE; q++) {
+                c[j][q] = -1;
+                if (q < m) {
+                    const size_t off = o0 + (size_t)(j * MP + P0 + q) * 32;
+                    c[j][q] = colT[off];
+                    a[j][q] = valT[off];
+                }
+                const int g = c[j][q] - base;
+                o[j][q] = 0.0;
+                if (c[j][q] >= 0 && !(g >= 0 && g < BS)) need |= 1u << (j * CACHE + q);
+            }
+        }
+        // Operands of other groups.  Warps run far ahead of the wavefront (that is what hides the DRAM latency of the factor), and
+        // a thousand waiting warps polling 28 operands x 32 lanes saturate L2 (measured: a level then costs 2-4 us).  So while a
+        // warp waits, ONE lane polls ONE operand for all of it -- the first lane that needs anything, the operand expected last
+        // (nearest row: highest column of an L row, lowest of a U row).  The lanes of a chunk belong to one level and their
+        // operands to the levels just before it, so when the proxy has arrived the rest is there or about to be: every lane then
+        // requests all its operands at once and re-requests only those that still read as the sentinel.  Correctness never
+        // rests on the proxy: every operand is checked by the lane that uses it.
+        {
+#ifdef MMADMM_TRI_PROF
+            { double acc = s[0]; for (int j = 0; j < BS; j++) for (int q = 0; q < CACHE; q++) if (c[j][q] >= 0) acc += a[j][q];
+              if (acc == 1.2345e-300) out[0] = acc; }   // the stamp below waits for the factor planes
+            SF_STAMP(1);
+#endif
+            const unsigned waiting = __ballot_sync(0xffffffffu, need != 0u);
+            if (waiting) {
+                if (lane == __ffs(waiting) - 1) {
+                    const int b = LOWER ? 31 - __clz(need) : __ffs(need) - 1;
+                    const double *p = out;
+#pragma unroll
+                    for (int j = 0; j < BS; j++)
+#pragma unroll
+                        for (int q = 0; q < CACHE; q++)
+                            if (b == j * CACHE + q) p = out + c[j][q];
+                    for (int spins = 0;; spins++) {
+                        const double v = ld_relaxed_gpu(p);
+                        if ((unsigned long long)__double_as_longlong(v) != TRI_SENTINEL) break;
+                        if (spins > (1 << 24)) __trap();   // no sleep: one load per round trip per warp is no load on L2, and a sleep
+                                                           // (granularity ~1 us) would sit on the critical path of every level
+                    }
+                }
+                __syncwarp();
+            }
+        }
+        SF_STAMP(2);
+        // The wavefront is now a few levels away.  Every lane waits for ITS operand expected last with one load per round trip
+        // (a sweep over all 28 operands per poll costs a microsecond of LSU and L2 time per warp and made a level 3-5 us), then
+        // requests everything it still needs in one batch, then waits for the few stragglers one at a time.
+        for (bool swept = false; need;) {
+            const int b = LOWER ? 31 - __clz(need) : __ffs(need) - 1;
+            const double *p = out;
+#pragma unroll
+            for (int j = 0; j < BS; j++)
+#pragma unroll
+                for (int q = 0; q < CACHE; q++)
+                    if (b == j * CACHE + q) p = out + c[j][q];
+            double v;
+            for (int spins = 0;; spins++) {
+                v = ld_relaxed_gpu(p);
+                if ((unsigned long long)__double_as_longlong(v) != TRI_SENTINEL) break;
+                if (spins > (1 << 24)) __trap();
+            }
+#pragma unroll
+            for (int j = 0; j < BS; j++)
+#pragma unroll
+                for (int q = 0; q < CACHE; q++)
+                    if (b == j * CACHE + q) o[j][q] = v;
+            need &= ~(1u << b);
+            if (!swept) {
+                swept = true;
+#pragma unroll
+                for (int j = 0; j < BS; j++)
+#pragma unroll
+                    for (int q = 0; q < CACHE; q++)
+                        if (need & (1u << (j * CACHE + q))) {
+                            const double vv = ld_relaxed_gpu(out + c[j][q]);
+                            if ((unsigned long long)__double_as_longlong(vv) != TRI_SENTINEL) { o[j][q] = vv; need &= ~(1u << (j * CACHE + q)); }
+                        }
+            }
+        }
+        __syncwarp();
+        SF_STAMP(3);
+#pragma unroll
+        for (int jj = 0; jj < BS; jj++) {
+            const int j = LOWER ? jj : BS - 1 - jj;
+            double sj = s[j];
+#pragma unroll
+            for (int q = 0; q < CACHE; q++) {
+                const int cc = c[j][q], g = cc - base;
+                if (cc >= 0) {
+                    const double v = (g >= 0 && g < BS) ? pick_own<BS>(own, g) : o[j][q];
+                    sj -= a[j][q] * v;
+                }
+            }
+            for (int q = CACHE; q < m; q++) {
+                const size_t off = o0 + (size_t)(j * MP + P0 + q) * 32;
+                const int cc = colT[off], g = cc - base;
+                if (cc >= 0) {
+                    const double v = (g >= 0 && g < BS) ? pick_own<BS>(own, g) : tri_sf_wait(out + cc);
+                    sj -= valT[off] * v;
+                }
+            }
+            own[j] = LOWER ? sj : sj / dv[j];
+            if (base >= 0 && base + j < n) st_relaxed_gpu(out + base + j, own[j]);
+        }
+        SF_STAMP(4);
+        chunk = __shfl_sync(0xffffffffu, next, 0);
+    }
+}
+
+// ---- dataflow solve on BS x BS blocks ----
+// On a matrix made of dense BS x BS blocks (the Method 2 Jacobian: one block per pair of adjacent vertices) the BS rows of a group
+// read the SAME operands: the generic kernel above requests each of them once per row, 8 bytes at a time, and what a hop of the
+// wavefront costs is exactly that -- scattered strong loads, 32 sectors per warp instruction (measured: a level = 2.6 us with
+// 14 operand loads per lane, 4.3 us with 28).  Here a lane holds its group's neighbour BLOCKS: one operand request per
+// neighbour group (a 16-byte load for BS = 2), shared by the BS rows.  Operands that were computed long ago (the cell-centre
+// rows of the upper factor) are picked up when the chunk is claimed, off the critical path.  Row arithmetic in CSR order:
+// L row = neighbour blocks ascending, then the group's own columns; U row = own columns, then neighbour blocks: same bits.
+template <int BS> __device__ __forceinline__ bool ld_group(const double *p, double (&v)[BS]) {
+    if (BS == 2) {
+        asm volatile("ld.relaxed.gpu.global.v2.f64 {%0, %1}, [%2];" : "=d"(v[0]), "=d"(v[1]) : "l"(p) : "memory");
+    } else {
+#pragma unroll
+        for (int k = 0; k < BS; k++) v[k] = ld_relaxed_gpu(p + k);
+    }
+    bool ok = true;
+#pragma unroll
+    for (int k = 0; k < BS; k++) ok = ok && ((unsigned long long)__double_as_longlong(v[k]) != TRI_SENTINEL);
+    return ok;
+}
+template <bool LOWER, int BS, int NBC>
+__global__ void __launch_bounds__(TC_THREADS) k_tri_sf_block(int n, int nChunks, const longlong2 *__restrict__ meta, const int *__restrict__ items,
+                                                            const int *__restrict__ nbrT, const double *__restrict__ valT,
+                                                            const double *__restrict__ rhs, double *out, unsigned *counter
+#ifdef MMADMM_TRI_PROF
+                                                            , int profLo
+#endif
+) {
+    const int lane = threadIdx.x & 31;
+    constexpr int BB = BS * BS;
+    int chunk = 0;
+    if (lane == 0) chunk = (int)atomicAdd(counter, 1u);
+    chunk = __shfl_sync(0xffffffffu, chunk, 0);
+    while (chunk < nChunks) {
+        int next = 0;
+        if (lane == 0) next = (int)atomicAdd(counter, 1u);
+        SF_STAMP(0);
+        const longlong2 mt = meta[chunk];                    // x: first value slot, y: first index slot << 8 | neighbour planes
+        const int m = (int)(mt.y & 255);
+        const size_t oV = (size_t)mt.x + lane, oI = (size_t)(mt.y >> 8) + lane;
+        const int base = items[(size_t)chunk * 32 + lane];   // first row of the lane's group; -1: padding lane
+        double d[BB], a[NBC][BB], o[NBC][BS], s[BS], own[BS];
+        int nb[NBC];
+        unsigned need = 0u;
+#pragma unroll
+        for (int k = 0; k < BB; k++) d[k] = valT[oV + (size_t)k * 32];
+#pragma unroll
+        for (int r = 0; r < BS; r++) { s[r] = base >= 0 ? rhs[base + r] : 0.0; own[r] = 0.0; }
+#pragma unroll
+        for (int q = 0; q < NBC; q++) {
+            nb[q] = q < m ? nbrT[oI + (size_t)q * 32] : -1;
+            if (nb[q] >= 0) {
+                need |= 1u << q;
+#pragma unroll
+                for (int k = 0; k < BB; k++) a[q][k] = valT[oV + (size_t)(BB * (1 + q) + k) * 32];
+            }
+        }
+        // operands that have been there for a long time: one batch now, while nobody waits for this chunk
+#pragma unroll
+        for (int q = 0; q < NBC; q++)
+            if (need & (1u << q)) {
+                double v[BS];
+                if (ld_group<BS>(out + nb[q], v)) {
+#pragma unroll
+                    for (int k = 0; k < BS; k++) o[q][k] = v[k];
+                    need &= ~(1u << q);
+                }
+            }
+        // a far-ahead warp waits through ONE lane polling ONE neighbour (see k_tri_syncfree)
+        SF_STAMP(1);
+        {
+            const unsigned waiting = __ballot_sync(0xffffffffu, need != 0u);
+            if (waiting) {
+                if (lane == __ffs(waiting) - 1) {
+                    const int b = LOWER ? 31 - __clz(need) : __ffs(need) - 1;
+                    const double *p = out;
+#pragma unroll
+                    for (int q = 0; q < NBC; q++)
+                        if (b == q) p = out + nb[q];
+                    for (int spins = 0;; spins++) {
+                        if ((unsigned long long)__double_as_longlong(ld_relaxed_gpu(p)) != TRI_SENTINEL) break;
+                        if (spins > (1 << 24)) __trap();
+                    }
+                }
+                __syncwarp();
+            }
+        }
+        // then every lane waits for its own neighbours, nearest (expected last) first, one request per round trip (requesting all
+        // missing ones together measured slower: 13.7 vs 12.5 ms per application on the C2-size Jacobian)
+        SF_STAMP(2);
+        for (int spins = 0; need; spins++) {
+            const int b = LOWER ? 31 - __clz(need) : __ffs(need) - 1;
+#pragma unroll
+            for (int q = 0; q < NBC; q++)
+                if (b == q) {
+                    double v[BS];
+                    if (ld_group<BS>(out + nb[q], v)) {
+#pragma unroll
+                        for (int k = 0; k < BS; k++) o[q][k] = v[k];
+                        need &= ~(1u << q);
+                    }
+                }
+            if (spins > (1 << 24)) __trap();
+        }
+        __syncwarp();
+        SF_STAMP(3);
+#pragma unroll
+        for (int rr = 0; rr < BS; rr++) {
+            const int r = LOWER ? rr : BS - 1 - rr;
+            double sj = s[r];
+            if (!LOWER) {
+#pragma unroll
+                for (int cidx = 0; cidx < BS; cidx++)
+                    if (cidx > r) sj -= d[r * BS + cidx] * own[cidx];
+            }
+#pragma unroll
+            for (int q = 0; q < NBC; q++)
+                if (nb[q] >= 0) {
+#pragma unroll
+                    for (int cidx = 0; cidx < BS; cidx++) sj -= a[q][r * BS + cidx] * o[q][cidx];
+                }
+            for (int q = NBC; q < m; q++) {   // more neighbours than the register cache holds
+                const int nq = nbrT[oI + (size_t)q * 32];
+                if (nq >= 0) {
+#pragma unroll
+                    for (int cidx = 0; cidx < BS; cidx++) sj -= valT[oV + (size_t)(BB * (1 + q) + r * BS + cidx) * 32] * tri_sf_wait(out + nq + cidx);
+                }
+            }
+            if (LOWER) {
+#pragma unroll
+                for (int cidx = 0; cidx < BS; cidx++)
+                    if (cidx < r) sj -= d[r * BS + cidx] * own[cidx];
+            }
+            own[r] = LOWER ? sj : sj / d[r * BS + r];
+        }
+        if (base >= 0) {
+            if (BS == 2) asm volatile("st.relaxed.gpu.global.v2.f64 [%0], {%1, %2};" ::"l"(out + base), "d"(own[0]), "d"(own[1]) : "memory");
+            else {
+#pragma unroll
+                for (int r = 0; r < BS; r++) st_relaxed_gpu(out + base + r, own[r]);
+            }
+        }
+        SF_STAMP(4);
+        chunk = __shfl_sync(0xffffffffu, next, 0);
+    }
+}
+
 // scal layout (device doubles): 0 rz, 1 pAp, 2 alpha, 3 beta, 4 rr, 5 rzNew, 6 bb
 enum { S_RZ = 0, S_PAP = 1, S_ALPHA = 2, S_BETA = 3, S_RR = 4, S_RZNEW = 5, S_BB = 6, S_COUNT = 8 };
 
@@ -475,6 +908,19 @@ struct mmadmm_pcg {
     int *lvlGL_d = nullptr, *lvlGU_d = nullptr;   // group-level offsets (device)
     int2 *kbeGL = nullptr, *kbeGU = nullptr;      // [group in level order][row of the group]: off-diagonal extent
     std::vector<int> lvlGL, lvlGU;                // group-level offsets (host)
+    int triLayout = 0;                            // "tri_layout": 1 = level-ELL copy of the factor for the cluster kernels
+    struct Chell {                                // chunk-ELL copy of the factor for the dataflow solve ("tri_mode" 2)
+        longlong2 *meta_d = nullptr; int *items = nullptr, *col = nullptr, *src = nullptr; double *val = nullptr;
+        size_t slots = 0; int nChunks = 0;
+        bool blocked = false;                     // BS x BS block form (k_tri_sf_block): col = neighbour planes, val = block planes
+    } chellL, chellU;
+    unsigned *sfCounter = nullptr;
+    int sfGrid = 0;                               // CTAs of the dataflow kernel (SM count x resident CTAs per SM)
+    int sfBlocks = 1;                             // "tri_blocks": use the BS x BS block form of the dataflow solve where the pattern allows
+    struct Lell {
+        int4 *meta_d = nullptr; int *col = nullptr, *src = nullptr; double *val = nullptr; size_t slots = 0;
+        std::vector<int4> meta;
+    } lellL, lellU;
     std::vector<int> diagPos_h;
     bool valHostStale = false;                    // val_h older than the device values (after mmadmm_pcg_refactor_device)
     int spmvFormat = 0;                           // 0: CSR, sub-warp per row; 1: SELL-32-4096 (built on first use)
@@ -570,11 +1016,13 @@ int build_sell(mmadmm_pcg *h) {
     PCK(cudaMemcpy(h->perm, perm.data(), sizeof(int) * perm.size(), cudaMemcpyHostToDevice));
     PCK(cudaMemcpy(h->scol, scol.data(), sizeof(int) * scol.size(), cudaMemcpyHostToDevice));
     PCK(cudaMemcpy(h->sval, sval.data(), sizeof(double) * sval.size(), cudaMemcpyHostToDevice));
+    PCK(cudaDeviceSynchronize());   // as in build_groups: the uploads above must have landed before h->stream reads them
     h->nSlices = nSlices;
     h->sellEntries = sp[nSlices];
     return MMADMM_OK;
 }
 
+int lell_refresh(mmadmm_pcg *h);
 // lu <- ILU(0) of the values in h->val (device), by the L-level schedule; h->flag_d is the zero-pivot flag
 int ilu_factor_device(mmadmm_pcg *h) {
     PCK(cudaMemcpyAsync(h->lu, h->val, sizeof(double) * (size_t)h->nnz, cudaMemcpyDeviceToDevice, h->stream));
@@ -590,7 +1038,7 @@ int ilu_factor_device(mmadmm_pcg *h) {
     PCK(cudaStreamSynchronize(h->stream));
     PCK(cudaGetLastError());
     if (flag) { h->err = "zero pivot in ILU(0)"; return MMADMM_ESINGULAR; }
-    return MMADMM_OK;
+    return lell_refresh(h);
 }
 
 void free_groups(mmadmm_pcg *h) {
@@ -602,14 +1050,37 @@ void free_groups(mmadmm_pcg *h) {
     h->grpL = h->grpU = h->lvlGL_d = h->lvlGU_d = nullptr;
     h->kbeGL = h->kbeGU = nullptr;
     h->lvlGL.clear(); h->lvlGU.clear();
+    for (mmadmm_pcg::Chell *L : {&h->chellL, &h->chellU}) {
+        cudaFree(L->meta_d); cudaFree(L->items); cudaFree(L->col); cudaFree(L->src); cudaFree(L->val);
+        L->meta_d = nullptr; L->items = L->col = L->src = nullptr; L->val = nullptr; L->slots = 0; L->nChunks = 0; L->blocked = false;
+    }
+    for (mmadmm_pcg::Lell *L : {&h->lellL, &h->lellU}) {
+        cudaFree(L->meta_d); cudaFree(L->col); cudaFree(L->src); cudaFree(L->val);
+        L->meta_d = nullptr; L->col = L->src = nullptr; L->val = nullptr; L->slots = 0; L->meta.clear();
+    }
+}
+// factor values -> the level-ELL copies (after every numeric factorisation)
+int lell_refresh(mmadmm_pcg *h) {
+    for (mmadmm_pcg::Lell *L : {&h->lellL, &h->lellU})
+        if (L->slots) {
+            k_lell_fill<<<cdiv(L->slots, TPB), TPB, 0, h->stream>>>(L->slots, L->src, h->lu, L->val);
+            h->launches++;
+        }
+    for (mmadmm_pcg::Chell *L : {&h->chellL, &h->chellU})
+        if (L->slots) {
+            k_lell_fill<<<cdiv(L->slots, TPB), TPB, 0, h->stream>>>(L->slots, L->src, h->lu, L->val);
+            h->launches++;
+        }
+    PCK(cudaGetLastError());
+    return MMADMM_OK;
 }
 // Level schedule of the groups [g*bs, (g+1)*bs): level(g) = 1 + max level of the OTHER groups its rows depend on.
 int build_groups(mmadmm_pcg *h, int bs) {
     free_groups(h);
     h->rowBlock = 1;
-    if (bs == 1) return MMADMM_OK;
+    if (bs == 1 && !h->triLayout && h->triMode != 2) return MMADMM_OK;
     const int n = h->n;
-    if (h->precond != 1 || (bs != 2 && bs != 3 && bs != 4 && bs != 6)) {
+    if (h->precond != 1 || (bs != 1 && bs != 2 && bs != 3 && bs != 4 && bs != 6)) {
         h->err = "row_block: 1, 2, 3, 4 or 6 rows per group, on an ILU(0) handle";
         return MMADMM_EINVAL;
     }
@@ -639,7 +1110,185 @@ int build_groups(mmadmm_pcg *h, int bs) {
         if ((er = cudaMemcpy(*off_d, off.data(), sizeof(int) * off.size(), cudaMemcpyHostToDevice)) != cudaSuccess) return er;
         return cudaMemcpy(*kbe_d, e.data(), sizeof(int2) * e.size(), cudaMemcpyHostToDevice);
     };
+    // level-ELL block of every level of at most one cluster pass (see k_tri_cluster_lell)
+    auto lell = [&](const std::vector<int> &grp, const std::vector<int> &off, bool lower, mmadmm_pcg::Lell &L) -> cudaError_t {
+        const int nlev = (int)off.size() - 1, P0 = lower ? 0 : 1, maxw = TC_THREADS * TC_CLUSTER;
+        auto len = [&](int i) { return lower ? dg[i] - rp[i] : rp[i + 1] - dg[i] - 1; };
+        L.meta.assign(nlev, make_int4(0, 0, -1, 0));
+        size_t slots = 0;
+        for (int l = 0; l < nlev; l++) {
+            const int lo = off[l], hi = off[l + 1], w = hi - lo;
+            L.meta[l] = make_int4(lo, hi, -1, 0);
+            if (w > maxw) continue;
+            int m = 0;
+            for (int t = lo; t < hi; t++)
+                for (int j = 0; j < bs; j++)
+                    if (grp[t] + j < n) m = std::max(m, len(grp[t] + j));
+            const size_t need = (size_t)bs * (m + P0) * w;
+            if (slots + need >= (size_t)1 << 31) continue;   // offsets are ints: the rest stays in CSR
+            L.meta[l].z = (int)slots; L.meta[l].w = m;
+            slots += need;
+        }
+        std::vector<int> colv(slots, -1), srcv(slots, -1);
+        for (int l = 0; l < nlev; l++) {
+            const int4 mt = L.meta[l];
+            if (mt.z < 0) continue;
+            const int w = mt.y - mt.x, MP = mt.w + P0;
+            for (int t = mt.x; t < mt.y; t++)
+                for (int j = 0; j < bs; j++) {
+                    const int i = grp[t] + j;
+                    if (i >= n) continue;
+                    const size_t o0 = (size_t)mt.z + (t - mt.x);
+                    if (!lower) { colv[o0 + (size_t)(j * MP) * w] = -2; srcv[o0 + (size_t)(j * MP) * w] = dg[i]; }
+                    const int kb = lower ? rp[i] : dg[i] + 1;
+                    for (int q = 0; q < len(i); q++) {
+                        const size_t o = o0 + (size_t)(j * MP + P0 + q) * w;
+                        colv[o] = cl[kb + q]; srcv[o] = kb + q;
+                    }
+                }
+        }
+        L.slots = slots;
+        cudaError_t er;
+        if ((er = cudaMalloc(&L.meta_d, sizeof(int4) * std::max<size_t>(L.meta.size(), 1))) != cudaSuccess) return er;
+        if ((er = cudaMemcpy(L.meta_d, L.meta.data(), sizeof(int4) * L.meta.size(), cudaMemcpyHostToDevice)) != cudaSuccess) return er;
+        if (!slots) return cudaSuccess;
+        if ((er = cudaMalloc(&L.col, sizeof(int) * slots)) != cudaSuccess) return er;
+        if ((er = cudaMalloc(&L.src, sizeof(int) * slots)) != cudaSuccess) return er;
+        if ((er = cudaMalloc(&L.val, sizeof(double) * slots)) != cudaSuccess) return er;
+        if ((er = cudaMemcpy(L.col, colv.data(), sizeof(int) * slots, cudaMemcpyHostToDevice)) != cudaSuccess) return er;
+        return cudaMemcpy(L.src, srcv.data(), sizeof(int) * slots, cudaMemcpyHostToDevice);
+    };
+    // chunk-ELL copy for the dataflow solve: chunks of 32 groups in level order, every level padded to whole chunks
+    auto chell = [&](const std::vector<int> &grp, const std::vector<int> &off, bool lower, mmadmm_pcg::Chell &L) -> cudaError_t {
+        const int nlev = (int)off.size() - 1, P0 = lower ? 0 : 1;
+        auto len = [&](int i) { return lower ? dg[i] - rp[i] : rp[i + 1] - dg[i] - 1; };
+        std::vector<int> items;
+        items.reserve((size_t)ng + 32 * (size_t)nlev);
+        for (int l = 0; l < nlev; l++) {
+            for (int t = off[l]; t < off[l + 1]; t++) items.push_back(grp[t]);
+            while (items.size() % 32) items.push_back(-1);
+        }
+        const int nChunks = (int)(items.size() / 32);
+        std::vector<longlong2> meta(nChunks);
+        size_t slots = 0;
+        for (int c = 0; c < nChunks; c++) {
+            int m = 0;
+            for (int r = 0; r < 32; r++) {
+                const int b = items[(size_t)c * 32 + r];
+                if (b < 0) continue;
+                for (int j = 0; j < bs; j++)
+                    if (b + j < n) m = std::max(m, len(b + j));
+            }
+            meta[c] = make_longlong2((long long)slots, m);
+            slots += (size_t)bs * (m + P0) * 32;
+        }
+        std::vector<int> colv(slots, -1), srcv(slots, -1);
+        for (int c = 0; c < nChunks; c++) {
+            const int MP = (int)meta[c].y + P0;
+            for (int r = 0; r < 32; r++) {
+                const int b = items[(size_t)c * 32 + r];
+                if (b < 0) continue;
+                const size_t o0 = (size_t)meta[c].x + r;
+                for (int j = 0; j < bs; j++) {
+                    const int i = b + j;
+                    if (i >= n) continue;
+                    if (!lower) { colv[o0 + (size_t)(j * MP) * 32] = -2; srcv[o0 + (size_t)(j * MP) * 32] = dg[i]; }
+                    const int kb = lower ? rp[i] : dg[i] + 1;
+                    for (int q = 0; q < len(i); q++) {
+                        const size_t o = o0 + (size_t)(j * MP + P0 + q) * 32;
+                        colv[o] = cl[kb + q]; srcv[o] = kb + q;
+                    }
+                }
+            }
+        }
+        L.slots = slots; L.nChunks = nChunks;
+        cudaError_t er;
+        if ((er = cudaMalloc(&L.meta_d, sizeof(longlong2) * std::max<size_t>(meta.size(), 1))) != cudaSuccess) return er;
+        if ((er = cudaMalloc(&L.items, sizeof(int) * std::max<size_t>(items.size(), 1))) != cudaSuccess) return er;
+        if ((er = cudaMalloc(&L.col, sizeof(int) * std::max<size_t>(slots, 1))) != cudaSuccess) return er;
+        if ((er = cudaMalloc(&L.src, sizeof(int) * std::max<size_t>(slots, 1))) != cudaSuccess) return er;
+        if ((er = cudaMalloc(&L.val, sizeof(double) * std::max<size_t>(slots, 1))) != cudaSuccess) return er;
+        if ((er = cudaMemcpy(L.meta_d, meta.data(), sizeof(longlong2) * meta.size(), cudaMemcpyHostToDevice)) != cudaSuccess) return er;
+        if ((er = cudaMemcpy(L.items, items.data(), sizeof(int) * items.size(), cudaMemcpyHostToDevice)) != cudaSuccess) return er;
+        if ((er = cudaMemcpy(L.col, colv.data(), sizeof(int) * slots, cudaMemcpyHostToDevice)) != cudaSuccess) return er;
+        return cudaMemcpy(L.src, srcv.data(), sizeof(int) * slots, cudaMemcpyHostToDevice);
+    };
+    // Block form of the chunk-ELL copy (k_tri_sf_block): possible when every group is bs full rows whose columns are the same
+    // aligned runs of bs (dense bs x bs blocks, the group's own block among them).
+    auto blockable = [&]() -> bool {
+        if ((bs != 2 && bs != 3) || n % bs) return false;
+        for (int g = 0; g < ng; g++) {
+            const int i0 = g * bs, len0 = rp[i0 + 1] - rp[i0];
+            if (len0 % bs) return false;
+            bool own = false;
+            for (int k = rp[i0]; k < rp[i0 + 1]; k += bs) {
+                if (cl[k] % bs) return false;
+                for (int c = 1; c < bs; c++)
+                    if (cl[k + c] != cl[k] + c) return false;
+                own = own || cl[k] == i0;
+            }
+            if (!own) return false;
+            for (int r = 1; r < bs; r++) {
+                if (rp[i0 + r + 1] - rp[i0 + r] != len0) return false;
+                for (int k = 0; k < len0; k++)
+                    if (cl[rp[i0 + r] + k] != cl[rp[i0] + k]) return false;
+            }
+        }
+        return true;
+    };
+    auto chell_block = [&](const std::vector<int> &grp, const std::vector<int> &off, bool lower, mmadmm_pcg::Chell &L) -> cudaError_t {
+        const int nlev = (int)off.size() - 1, BB = bs * bs;
+        std::vector<int> items;
+        items.reserve((size_t)ng + 32 * (size_t)nlev);
+        for (int l = 0; l < nlev; l++) {
+            for (int t = off[l]; t < off[l + 1]; t++) items.push_back(grp[t]);
+            while (items.size() % 32) items.push_back(-1);
+        }
+        const int nChunks = (int)(items.size() / 32);
+        // position of the group's own block in its row, number of neighbour blocks on this side
+        auto ownPos = [&](int b) { int p = 0; while (cl[rp[b] + p * bs] != b) p++; return p; };
+        auto nNbr = [&](int b) { const int p = ownPos(b); return lower ? p : (rp[b + 1] - rp[b]) / bs - p - 1; };
+        std::vector<longlong2> meta(nChunks);
+        size_t slotsV = 0, slotsI = 0;
+        for (int c = 0; c < nChunks; c++) {
+            int m = 0;
+            for (int r = 0; r < 32; r++) { const int b = items[(size_t)c * 32 + r]; if (b >= 0) m = std::max(m, nNbr(b)); }
+            if (m > 255) return cudaErrorInvalidValue;
+            meta[c] = make_longlong2((long long)slotsV, (long long)((slotsI << 8) | (size_t)m));
+            slotsV += (size_t)BB * (1 + m) * 32;
+            slotsI += (size_t)m * 32;
+        }
+        std::vector<int> nbrv(std::max<size_t>(slotsI, 1), -1), srcv(slotsV, -1);
+        for (int c = 0; c < nChunks; c++) {
+            for (int r = 0; r < 32; r++) {
+                const int b = items[(size_t)c * 32 + r];
+                if (b < 0) continue;
+                const size_t oV = (size_t)meta[c].x + r, oI = (size_t)(meta[c].y >> 8) + r;
+                const int p = ownPos(b), cnt = nNbr(b), first = lower ? 0 : p + 1;
+                for (int rr = 0; rr < bs; rr++)
+                    for (int cc = 0; cc < bs; cc++) srcv[oV + (size_t)(rr * bs + cc) * 32] = rp[b + rr] + p * bs + cc;
+                for (int q = 0; q < cnt; q++) {
+                    nbrv[oI + (size_t)q * 32] = cl[rp[b] + (first + q) * bs];
+                    for (int rr = 0; rr < bs; rr++)
+                        for (int cc = 0; cc < bs; cc++) srcv[oV + (size_t)(BB * (1 + q) + rr * bs + cc) * 32] = rp[b + rr] + (first + q) * bs + cc;
+                }
+            }
+        }
+        L.slots = slotsV; L.nChunks = nChunks; L.blocked = true;
+        cudaError_t er;
+        if ((er = cudaMalloc(&L.meta_d, sizeof(longlong2) * std::max<size_t>(meta.size(), 1))) != cudaSuccess) return er;
+        if ((er = cudaMalloc(&L.items, sizeof(int) * std::max<size_t>(items.size(), 1))) != cudaSuccess) return er;
+        if ((er = cudaMalloc(&L.col, sizeof(int) * nbrv.size())) != cudaSuccess) return er;
+        if ((er = cudaMalloc(&L.src, sizeof(int) * std::max<size_t>(slotsV, 1))) != cudaSuccess) return er;
+        if ((er = cudaMalloc(&L.val, sizeof(double) * std::max<size_t>(slotsV, 1))) != cudaSuccess) return er;
+        if ((er = cudaMemcpy(L.meta_d, meta.data(), sizeof(longlong2) * meta.size(), cudaMemcpyHostToDevice)) != cudaSuccess) return er;
+        if ((er = cudaMemcpy(L.items, items.data(), sizeof(int) * items.size(), cudaMemcpyHostToDevice)) != cudaSuccess) return er;
+        if ((er = cudaMemcpy(L.col, nbrv.data(), sizeof(int) * nbrv.size(), cudaMemcpyHostToDevice)) != cudaSuccess) return er;
+        return cudaMemcpy(L.src, srcv.data(), sizeof(int) * slotsV, cudaMemcpyHostToDevice);
+    };
+    const bool useBlocks = h->triMode == 2 && h->sfBlocks && blockable();
     PCK(cudaSetDevice(h->device));
+    if (!h->sfCounter) PCK(cudaMalloc(&h->sfCounter, sizeof(unsigned)));
     std::vector<int> grp;
     int nl = 0;
     for (int g = 0; g < ng; g++) {
@@ -651,6 +1300,8 @@ int build_groups(mmadmm_pcg *h, int bs) {
     }
     bucket(nl, grp, h->lvlGL);
     PCK(upload(grp, h->lvlGL, true, &h->grpL, &h->lvlGL_d, &h->kbeGL));
+    if (h->triLayout && h->triMode != 2) PCK(lell(grp, h->lvlGL, true, h->lellL));
+    if (h->triMode == 2) PCK(useBlocks ? chell_block(grp, h->lvlGL, true, h->chellL) : chell(grp, h->lvlGL, true, h->chellL));
     int nu = 0;
     for (int g = ng - 1; g >= 0; g--) {
         int l = 0;
@@ -661,8 +1312,13 @@ int build_groups(mmadmm_pcg *h, int bs) {
     }
     bucket(nu, grp, h->lvlGU);
     PCK(upload(grp, h->lvlGU, false, &h->grpU, &h->lvlGU_d, &h->kbeGU));
+    if (h->triLayout && h->triMode != 2) PCK(lell(grp, h->lvlGU, false, h->lellU));
+    if (h->triMode == 2) PCK(useBlocks ? chell_block(grp, h->lvlGU, false, h->chellU) : chell(grp, h->lvlGU, false, h->chellU));
     h->rowBlock = bs;
-    return MMADMM_OK;
+    // cudaMemcpy from pageable memory may return before the DMA has landed, and h->stream does not synchronise with the legacy
+    // stream: without this the fill kernel below could read a half-uploaded index array (seen as a rare, per-process-stable mismatch)
+    PCK(cudaDeviceSynchronize());
+    return lell_refresh(h);
 }
 
 // One triangular solve.  tri_mode 1: runs of consecutive levels that each fit a few passes of the cluster's 2048 threads go
@@ -700,12 +1356,59 @@ void tri_solve_blk(mmadmm_pcg *h, const std::vector<int> &lvl, const int *lvl_d,
                    double *out) {
     const int nlev = (int)lvl.size() - 1;
     const int wide = 4 * TC_THREADS * TC_CLUSTER;
+    const mmadmm_pcg::Chell &C = LOWER ? h->chellL : h->chellU;
+    if (h->triMode == 2 && C.nChunks > 0) {   // the whole solve: sentinel fill + one persistent launch
+        k_tri_sf_prepare<<<cdiv(h->n, TPB), TPB, 0, h->stream>>>(h->n, out, h->sfCounter);
+        static const int gridEnv = getenv("MMADMM_SF_GRID") ? atoi(getenv("MMADMM_SF_GRID")) : 0;   // experiments
+        const int grid = gridEnv > 0 ? gridEnv : std::min(2 * h->sfGrid, cdiv(C.nChunks, TC_THREADS / 32));   // chunks are claimed dynamically: CTAs that are not resident at once are harmless
+        if (C.blocked) {
+#ifdef MMADMM_TRI_PROF
+            static const int profLoB = getenv("MMADMM_SF_PROF_LO") ? atoi(getenv("MMADMM_SF_PROF_LO")) : 0;
+            static const int profU = getenv("MMADMM_SF_PROF_UPPER") ? 1 : 0;
+            const int pl = (LOWER != (profU == 1)) ? profLoB : (1 << 30);
+            if (BS == 2) k_tri_sf_block<LOWER, 2, 8><<<grid, TC_THREADS, 0, h->stream>>>(h->n, C.nChunks, C.meta_d, C.items, C.col, C.val, rhs, out, h->sfCounter, pl);
+            else k_tri_sf_block<LOWER, 3, 5><<<grid, TC_THREADS, 0, h->stream>>>(h->n, C.nChunks, C.meta_d, C.items, C.col, C.val, rhs, out, h->sfCounter, pl);
+#else
+            if (BS == 2) k_tri_sf_block<LOWER, 2, 8><<<grid, TC_THREADS, 0, h->stream>>>(h->n, C.nChunks, C.meta_d, C.items, C.col, C.val, rhs, out, h->sfCounter);
+            else k_tri_sf_block<LOWER, 3, 5><<<grid, TC_THREADS, 0, h->stream>>>(h->n, C.nChunks, C.meta_d, C.items, C.col, C.val, rhs, out, h->sfCounter);
+#endif
+            h->launches += 2;
+            return;
+        }
+#ifdef MMADMM_TRI_PROF
+        static const int profLo = getenv("MMADMM_SF_PROF_LO") ? atoi(getenv("MMADMM_SF_PROF_LO")) : 0;
+        k_tri_syncfree<LOWER, BS, (BS * CACHE <= 32 ? CACHE : 32 / BS)><<<grid, TC_THREADS, 0, h->stream>>>(h->n, C.nChunks, C.meta_d, C.items, C.col, C.val, rhs, out,
+                                                                                                        h->sfCounter, LOWER ? profLo : (1 << 30));
+#else
+        k_tri_syncfree<LOWER, BS, (BS * CACHE <= 32 ? CACHE : 32 / BS)><<<grid, TC_THREADS, 0, h->stream>>>(h->n, C.nChunks, C.meta_d, C.items, C.col, C.val, rhs, out,
+                                                                                                        h->sfCounter);
+#endif
+        h->launches += 2;
+        return;
+    }
+    const mmadmm_pcg::Lell &L = LOWER ? h->lellL : h->lellU;
+    const bool useLell = h->triMode == 1 && h->triLayout == 1 && (int)L.meta.size() == nlev;
     int l = 0;
     while (l < nlev) {
         int e = l;
+        if (useLell) {
+            while (e < nlev && L.meta[e].z >= 0) e++;
+            if (e - l >= 4) {
+#ifdef MMADMM_TRI_PROF
+                static const int pmode = getenv("MMADMM_TRI_PROF_MODE") ? atoi(getenv("MMADMM_TRI_PROF_MODE")) : 0;
+                k_tri_cluster_lell<LOWER, BS, CACHE><<<TC_CLUSTER, TC_THREADS, 0, h->stream>>>(h->n, l, e, L.meta_d, groups, L.col, L.val, rhs, out, pmode);
+#else
+                k_tri_cluster_lell<LOWER, BS, CACHE><<<TC_CLUSTER, TC_THREADS, 0, h->stream>>>(h->n, l, e, L.meta_d, groups, L.col, L.val, rhs, out);
+#endif
+                h->launches++;
+                l = e;
+                continue;
+            }
+            e = l;
+        }
         if (h->triMode == 1)
             while (e < nlev && lvl[e + 1] - lvl[e] <= wide) e++;
-        if (e - l >= 4) {
+        if (e - l >= 4 && !useLell) {
             k_tri_cluster_blk<LOWER, BS, CACHE><<<TC_CLUSTER, TC_THREADS, 0, h->stream>>>(h->n, l, e, lvl_d, groups, kbe, h->rowptr, h->diagPos,
                                                                                           h->col, h->lu, rhs, out);
             h->launches++;
@@ -725,7 +1428,8 @@ template <int BS, int CACHE> void apply_ilu_blk(mmadmm_pcg *h, const double *r, 
 
 // z = (LU)^{-1} r by level-scheduled forward and backward substitution
 void apply_ilu(mmadmm_pcg *h, const double *r, double *z) {
-    switch (h->rowBlock) {
+    switch (h->grpL ? h->rowBlock : 0) {
+        case 1: apply_ilu_blk<1, 14>(h, r, z); return;
         case 2: apply_ilu_blk<2, 14>(h, r, z); return;
         case 3: apply_ilu_blk<3, 10>(h, r, z); return;
         case 4: apply_ilu_blk<4, 8>(h, r, z); return;
@@ -840,7 +1544,66 @@ int mmadmm_pcg_create(int n, const int *rowptr, const int *col, const double *va
 
 int mmadmm_pcg_set_option(mmadmm_pcg *h, const char *name, int value) {
     if (!h || !name) return MMADMM_EINVAL;
-    if (!std::strcmp(name, "tri_mode")) { h->triMode = value ? 1 : 0; return MMADMM_OK; }
+    if (!std::strcmp(name, "tri_mode")) {
+        if (value < 0 || value > 2) return MMADMM_EINVAL;
+        const bool rebuild = (value == 2) != (h->triMode == 2) && h->precond == 1;
+        h->triMode = value;
+        if (rebuild) {   // the dataflow solve has its own copy of the factor (chunk-ELL)
+            PCK(cudaSetDevice(h->device));
+            PCK(cudaStreamSynchronize(h->stream));
+            if (!h->sfGrid) {
+                cudaDeviceProp pr;
+                PCK(cudaGetDeviceProperties(&pr, h->device));
+                h->sfGrid = pr.multiProcessorCount;   // 1 CTA of 256 threads per SM (register-bound)
+            }
+            int rc = build_groups(h, h->rowBlock);
+            if (rc) return rc;
+            PCK(cudaStreamSynchronize(h->stream));
+            PCK(cudaGetLastError());
+        }
+        return MMADMM_OK;
+    }
+    if (!std::strcmp(name, "tri_blocks")) {   // 1 (default): block form of the dataflow solve where the pattern is made of BS x BS blocks
+        h->sfBlocks = value ? 1 : 0;
+        if (h->triMode == 2 && h->precond == 1) {
+            PCK(cudaSetDevice(h->device));
+            PCK(cudaStreamSynchronize(h->stream));
+            int rc = build_groups(h, h->rowBlock);
+            if (rc) return rc;
+            PCK(cudaStreamSynchronize(h->stream));
+            PCK(cudaGetLastError());
+        }
+        return MMADMM_OK;
+    }
+    if (!std::strcmp(name, "tri_schedule")) {   // row_block | tri_layout << 8 in one build
+        if (h->precond != 1) { h->err = "tri_schedule needs an ILU(0) handle"; return MMADMM_EINVAL; }
+        PCK(cudaSetDevice(h->device));
+        PCK(cudaStreamSynchronize(h->stream));
+        h->triLayout = (value >> 8) & 1;
+        if ((value >> 12) & 3) h->triMode = ((value >> 12) & 3) - 1;   // bits 12-13: tri_mode + 1 (0 = keep)
+        if (h->triMode == 2 && !h->sfGrid) {
+            cudaDeviceProp pr;
+            PCK(cudaGetDeviceProperties(&pr, h->device));
+            h->sfGrid = pr.multiProcessorCount;
+        }
+        int rc = build_groups(h, value & 0xff);
+        if (rc) return rc;
+        PCK(cudaStreamSynchronize(h->stream));
+        PCK(cudaGetLastError());
+        return MMADMM_OK;
+    }
+    if (!std::strcmp(name, "tri_layout")) {
+        if (value != 0 && value != 1) return MMADMM_EINVAL;
+        if (h->precond != 1) { h->err = "tri_layout needs an ILU(0) handle"; return MMADMM_EINVAL; }
+        PCK(cudaSetDevice(h->device));
+        PCK(cudaStreamSynchronize(h->stream));
+        h->triLayout = value;
+        int rc = build_groups(h, h->rowBlock);
+        if (rc) return rc;
+        PCK(cudaStreamSynchronize(h->stream));
+        PCK(cudaGetLastError());
+        return MMADMM_OK;
+    }
     if (!std::strcmp(name, "row_block")) {
         PCK(cudaSetDevice(h->device));
         PCK(cudaStreamSynchronize(h->stream));
@@ -1112,6 +1875,12 @@ int mmadmm_pcg_time_precond(mmadmm_pcg *h, int reps, double *ms) {
     return MMADMM_OK;
 }
 
+#ifdef MMADMM_TRI_PROF
+// timing experiments: per-chunk time stamps of the last LOWER dataflow solve + the chunk's first item's level is the caller's business
+int mmadmm_pcg_debug_sf_prof(unsigned long long *out5x65536) {
+    return cudaMemcpyFromSymbol(out5x65536, g_sf_prof, sizeof(unsigned long long) * 5 * 65536) == cudaSuccess ? 0 : 2;
+}
+#endif
 int mmadmm_measure_fp64_peak(int device, double *tflops) {
     if (!tflops) return MMADMM_EINVAL;
     int ndev = 0;
@@ -1150,7 +1919,7 @@ void mmadmm_pcg_destroy(mmadmm_pcg *h) {
     cudaFree(h->rowptr); cudaFree(h->col); cudaFree(h->diagPos); cudaFree(h->val); cudaFree(h->lu); cudaFree(h->invDiag);
     cudaFree(h->rowsL); cudaFree(h->rowsU); cudaFree(h->lvlL_d); cudaFree(h->lvlU_d); cudaFree(h->kbeL); cudaFree(h->kbeU);
     free_groups(h);
-    cudaFree(h->flag_d);
+    cudaFree(h->flag_d); cudaFree(h->sfCounter);
     cudaFree(h->r); cudaFree(h->z); cudaFree(h->p); cudaFree(h->q); cudaFree(h->x); cudaFree(h->b); cudaFree(h->tmp);
     cudaFree(h->part0); cudaFree(h->part1); cudaFree(h->scal);
     for (int k = 0; k < 4; k++) cudaFree(h->bi[k]);

@@ -1,0 +1,19 @@
+#!/bin/bash
+# Round 2, GPU call AI (1 GPU): block dataflow solve, all missing neighbours per poll; Method 2 default = dataflow
+O=gpurun_out/r02_ai; mkdir -p $O
+timeout 900 python -m pytest tests/test_zz_gpu_method2.py tests/test_gpu_pcg.py -m gpu -q -s > $O/pytest_m2.log 2>&1; echo "pytest rc=$?"; grep -n "^E  \|passed\|failed" $O/pytest_m2.log | head -5
+timeout 600 python scripts/m2_parts.py 1024 > $O/m2_parts_nx1024.json 2> $O/m2_parts.err; echo "parts rc=$?"; python -c "
+import json; d=json.load(open('$O/m2_parts_nx1024.json')); print({k:v for k,v in d.items() if 'row_block' in k})"; tail -3 $O/m2_parts.err
+for cfg in "m2_tri_mode=2" "m2_tri_mode=1"; do
+  tag=$(echo $cfg | tr ' =' '__'); opts=""; for o in $cfg; do opts="$opts --opt $o"; done
+  timeout 900 python bench.py --method 2 --steps 5 --warmup 1 --no-cpu-baseline $opts > $O/bench_$tag.json 2> $O/bench_$tag.err; echo "$tag rc=$?"
+done
+python - <<'PY'
+import json,glob
+for f in sorted(glob.glob('gpurun_out/r02_ai/bench_m2*.json')):
+    try:
+        d=json.loads([l for l in open(f).read().split('\n') if l.startswith('{')][0])
+        print(f.split('/')[-1], '%.2f ms/step' % d['ms_per_step'], 'first step %.0f ms' % d['warmup_steps'][0]['ms'], d['config']['newton_iters'], d['config']['bicgstab_iters'], d['gpu_launches'], d['energy_last'])
+    except Exception as e:
+        print(f, 'ERR', e)
+PY

@@ -40,8 +40,15 @@ for mode in (0, 1):
     out[f"bicgstab_ms_tri{mode}"] = best(lambda: pcg.bicgstab(r * 1e-3, 1e-6, 10000), 3)
     out[f"bicgstab_iters_tri{mode}"] = pcg.bicgstab(r * 1e-3, 1e-6, 10000)[1]
 pcg.set_option("tri_mode", 1)
-for bs in (1, 2):             # block rows: groups of bs consecutive rows per thread (device-timed preconditioner application)
+for lay in (0, 1):            # 1: level-ELL copy of the factor for the cluster kernels
+    pcg.set_option("tri_layout", lay)
+    for bs in (1, 2):         # block rows: groups of bs consecutive rows per thread (device-timed preconditioner application)
+        pcg.set_option("row_block", bs)
+        i2 = pcg.info()
+        out[f"layout_{lay}_row_block_{bs}"] = {"levels": [i2["lower_levels"], i2["upper_levels"]], "precond_ms_device": round(pcg.time_precond(5), 3)}
+pcg.set_option("tri_mode", 2)     # dataflow solve: no barrier between levels
+for bs in (1, 2):
     pcg.set_option("row_block", bs)
     i2 = pcg.info()
-    out[f"row_block_{bs}"] = {"levels": [i2["lower_levels"], i2["upper_levels"]], "precond_ms_device": round(pcg.time_precond(5), 3)}
+    out[f"dataflow_row_block_{bs}"] = {"levels": [i2["lower_levels"], i2["upper_levels"]], "precond_ms_device": round(pcg.time_precond(5), 3)}
 print(json.dumps(out))

@@ -115,13 +115,20 @@ def test_device_ilu0_factor_and_refactor_are_bit_identical_to_the_host_factor(D,
         s.set_option("row_block", bs)
         assert np.array_equal(s.precond(-r), -zf)                      # (a different right-hand side first: the result buffer
         assert np.array_equal(s.precond(r), zf)                        # must be rewritten, not left over from the last call)
-    s.set_option("row_block", 1)
+    s.set_option("tri_layout", 1)                                      # ... and so does the level-ELL copy of the factor
+    for bs in (1, 2, 3):
+        s.set_option("row_block", bs)
+        assert np.array_equal(s.precond(-r), -zf)
+        assert np.array_equal(s.precond(r), zf)
+    z0 = mm.PCG(A.indptr, A.indices, A.data, "ilu0")
+    zA = z0.precond(r); z0.close()
     s.set_option("spmv_format", 1)                                     # the SELL copy is rebuilt from refreshed values
     assert rel(s.spmv(r), A2 @ r) < 1e-13
     v.copy_(torch.from_numpy(A.data))
     torch.cuda.synchronize()
     s.refactor_device(v.data_ptr())
     assert rel(s.spmv(r), A @ r) < 1e-13 and np.array_equal(s.ilu(), lu)
+    assert np.array_equal(s.precond(r), zA)                            # level-ELL copy refreshed by the re-factorisation
     bad = A.data.copy(); bad[diag[0]] = 0.0
     v.copy_(torch.from_numpy(bad)); torch.cuda.synchronize()
     with pytest.raises(mm.MMADMMError) as ei:

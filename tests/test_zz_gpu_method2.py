@@ -122,15 +122,22 @@ def test_block_row_triangular_solves_are_bit_identical(D, nx):
     pcg = mm.PCG(rowptr, col, val, precond="ilu0")
     rng = np.random.default_rng(12)
     r = rng.standard_normal(n)
-    out = {}
+    out, bad = {}, []
     for bs in (1, D, 2 * D, 4):          # 4 does not divide n in 3D / on odd vertex counts: the last group is short
-        for mode in (0, 1):
-            pcg.set_option("tri_mode", mode)
+        for mode in (0, 1, 2, 3, 4):     # 2 = cluster launches on the level-ELL copy of the factor ("tri_layout" 1); 3 = dataflow solve
+            pcg.set_option("tri_blocks", 0 if mode == 4 else 1)   # (block form where bs = D fits the pattern); 4 = dataflow, generic form
+            pcg.set_option("tri_mode", 2 if mode >= 3 else min(mode, 1))
+            pcg.set_option("tri_layout", 1 if mode == 2 else 0)
             pcg.set_option("row_block", bs)
             info = pcg.info()
+            for rep in range(3):                                     # the result buffer is rewritten; repeated: the dataflow solve
+                zm = pcg.precond(-r)                                 # must not depend on timing
+                if (1, 1) in out and not np.array_equal(zm, -out[1, 1][0]):
+                    bad.append((bs, mode, rep, "precond(-r)", int((zm != -out[1, 1][0]).sum())))
             z = pcg.precond(r)
             x, it, relres = pcg.bicgstab(r * 1e-3, 1e-6, 10000)
             out[bs, mode] = (z, x, it, info["lower_levels"], info["upper_levels"])
+    assert not bad, bad
     z1, x1, it1, nl1, nu1 = out[1, 1]
     for (bs, mode), (z, x, it, nl, nu) in out.items():
         assert np.array_equal(z, z1), (bs, mode)
