@@ -541,11 +541,12 @@ def method2_line(args):
             "wall_ms_per_step": wall / K * 1e3, "gpu_launches": launches,
             "e2e": {"value": K / wall, "unit": "outer steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 64 * max(lin, 1) // K,
                     "note": "wall clock through MeshIntegrator.backwardsEulerStep; as in the reference this path does not write Vp back per step"},
-            "roofline": {"kernel": "ILU(0)+BiCGSTAB iteration (k_tri_cluster x4, k_spmv_dot x2, vector kernels)", "bound": "hbm", "achieved": achieved,
+            "roofline": {"kernel": "ILU(0)+BiCGSTAB iteration (4 triangular solves -- k_tri_sf_block, the dataflow solve, by default --, k_spmv_dot x2, vector kernels)", "bound": "hbm", "achieved": achieved,
                          "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
                          "algorithmic_bytes_per_launch": bytes_iter,
-                         "note": "latency-bound by construction: natural-order ILU(0) on a structured mesh has thousands of levels of a few "
-                                 "hundred rows (DESIGN.md 3.5); the fraction is reported, not claimed"},
+                         "note": "a dependency chain, not a stream: natural-order ILU(0) on a structured mesh has thousands of levels of a few "
+                                 "hundred rows and what bounds a solve is the latency of one hop of the wavefront (DESIGN.md 3.5); the fraction "
+                                 "is reported, not claimed"},
             "clocks": clocks, "warmup_steps": warm, "energy_last": ih}
     solver.close()
     if not args.no_cpu_baseline:

@@ -1876,6 +1876,12 @@ int mmadmm_pcg_time_precond(mmadmm_pcg *h, int reps, double *ms) {
 }
 
 #ifdef MMADMM_TRI_PROF
+// timing experiments: group-level offsets of the lower (which = 0) / upper (1) schedule; returns the number of entries
+int mmadmm_pcg_debug_levels(mmadmm_pcg *h, int which, int *out, int cap) {
+    const std::vector<int> &v = which ? h->lvlGU : h->lvlGL;
+    for (int i = 0; i < (int)v.size() && i < cap; i++) out[i] = v[i];
+    return (int)v.size();
+}
 // timing experiments: per-chunk time stamps of the last LOWER dataflow solve + the chunk's first item's level is the caller's business
 int mmadmm_pcg_debug_sf_prof(unsigned long long *out5x65536) {
     return cudaMemcpyFromSymbol(out5x65536, g_sf_prof, sizeof(unsigned long long) * 5 * 65536) == cudaSuccess ? 0 : 2;

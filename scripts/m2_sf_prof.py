@@ -1,5 +1,6 @@
 """Per-chunk time stamps of the dataflow triangular solve (profiling build, -DMMADMM_TRI_PROF): where a level's time goes.
-usage: python scripts/m2_sf_prof.py [nx] [row_block]"""
+Stamps per chunk: 0 claimed, 1 factor planes + early operands requested, 2 proxy operand seen, 3 all operands of all lanes seen,
+4 results stored.  usage: [MMADMM_SF_PROF_UPPER=1] python scripts/m2_sf_prof.py [nx] [row_block]"""
 import ctypes as C, importlib, json, os, sys
 import numpy as np
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
@@ -8,6 +9,7 @@ mm = importlib.import_module("mm-admm_b200")
 mm.LIB_PATH = os.path.join(ROOT, "build", "prof", "libmmadmm_b200_prof.so")
 nx = int(sys.argv[1]) if len(sys.argv) > 1 else 1024
 bs = int(sys.argv[2]) if len(sys.argv) > 2 else 2
+upper = 1 if os.environ.get("MMADMM_SF_PROF_UPPER") else 0
 Vp, F, mask = mm.generate_uniform_rect_mesh(2, nx, nx, 0)
 mon = mm.TestMonitor(2, 4).evaluate_at_vertices(Vp)
 mesh = mm.Mesh(Vp.copy(), F.copy(), mask, mon, rho=50.0, tau=0.5, integration_mode=2)
@@ -17,31 +19,35 @@ pcg = mm.PCG(rowptr, col, val, precond="ilu0")
 pcg.set_option("tri_mode", 2); pcg.set_option("row_block", bs)
 r = np.random.default_rng(1).standard_normal(len(rowptr) - 1)
 pcg.precond(r); pcg.precond(r)
-buf = np.zeros(5 * 65536, dtype=np.uint64)
 L = mm.lib()
+lv = np.zeros(1 << 16, dtype=np.int32)
+L.mmadmm_pcg_debug_levels.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int]
+nlv = L.mmadmm_pcg_debug_levels(pcg.h, upper, lv.ctypes.data_as(C.c_void_p), len(lv))
+off = lv[:nlv].astype(np.int64)
+widths = np.diff(off)
+starts = np.concatenate([[0], np.cumsum((widths + 31) // 32)])        # first chunk of every level
+buf = np.zeros(5 * 65536, dtype=np.uint64)
 assert L.mmadmm_pcg_debug_sf_prof(buf.ctypes.data_as(C.c_void_p)) == 0
 t = buf.reshape(65536, 5).astype(np.int64)
-# L solve on the (nx+1)^2 lattice, vertices numbered row by row: level l holds the groups with i + j = l (bs = 2: one vertex per group)
-per = 2 // bs if bs <= 2 else 1
-widths = [min(l // per + 1, nx + 1, 2 * nx + 1 - l // per) for l in range((2 * nx + 1) * per)]
-starts = np.concatenate([[0], np.cumsum([(w + 31) // 32 for w in widths])])
-t0 = t[:, 0].min()
-rows = []
-for l in range(600 * per, 606 * per):
-    a, b = starts[l], starts[l + 1]
-    if b > 65536: break
-    seg = t[a:b]
-    prev = t[starts[l - 1]:starts[l], 4].max()
-    rows.append({"level": l, "chunks": int(b - a), "claim_to_loaded_us": round(float((seg[:, 1] - seg[:, 0]).mean()) / 1e3, 2),
-                 "loaded_to_proxy_us": round(float((seg[:, 2] - seg[:, 1]).mean()) / 1e3, 2),
-                 "proxy_to_all_us": round(float((seg[:, 3] - seg[:, 2]).mean()) / 1e3, 2),
-                 "all_to_stored_us": round(float((seg[:, 4] - seg[:, 3]).mean()) / 1e3, 2),
-                 "prev_level_last_store_to_proxy_seen_us": round(float((seg[:, 2] - prev).mean()) / 1e3, 2),
-                 "level_done_after_prev_us": round(float(seg[:, 4].max() - prev) / 1e3, 2),
-                 "claimed_before_prev_done_us": round(float((prev - seg[:, 0]).mean()) / 1e3, 2)})
-for rw in rows: print(json.dumps(rw))
-w = t[starts[300 * per]:starts[900 * per]]
-print("chunks in levels 300..900: mean us  claim->loaded %.2f  loaded->proxy %.1f  proxy->all operands %.2f  operands->stored %.2f" % tuple(
+nl = int(np.searchsorted(starts, 65536, side="right")) - 1               # levels fully inside the stamped window
+done = np.array([t[starts[l]:starts[l + 1], 4].max() for l in range(nl)])
+first = np.array([t[starts[l]:starts[l + 1], 4].min() for l in range(nl)])
+print(json.dumps({"solve": "upper" if upper else "lower", "levels": int(nlv - 1), "levels_stamped": nl, "chunks": int(starts[-1]),
+                  "width_mean": float(widths[:nl].mean()), "width_max": int(widths[:nl].max())}))
+lo, hi = min(100, nl // 4), nl - 2
+hop = np.diff(done[lo:hi])
+print("level l done - level l-1 done (us): mean %.3f  median %.3f  p10 %.3f  p90 %.3f" % (hop.mean() / 1e3, np.median(hop) / 1e3,
+      np.percentile(hop, 10) / 1e3, np.percentile(hop, 90) / 1e3))
+spread = (done - first)[lo:hi]
+print("spread of a level's chunk completions (us): mean %.3f  p90 %.3f" % (spread.mean() / 1e3, np.percentile(spread, 90) / 1e3))
+w = t[starts[lo]:starts[hi]]
+print("per chunk, mean us: claim->requested %.2f  requested->proxy %.1f  proxy->all operands %.2f  operands->stored %.2f" % tuple(
     float((w[:, k + 1] - w[:, k]).mean()) / 1e3 for k in range(4)))
-lv = [t[starts[l]:starts[l + 1], 4].max() for l in range(200 * per, 900 * per) if starts[l + 1] <= 65536]
-print("mean us per level over levels 200..900:", round(float(np.diff(lv).mean()) / 1e3, 3))
+# when a chunk of level l has its operands relative to the completion of level l-1 (negative: before the previous level was complete)
+rel3 = np.concatenate([t[starts[l]:starts[l + 1], 3] - done[l - 1] for l in range(lo, hi)])
+rel2 = np.concatenate([t[starts[l]:starts[l + 1], 2] - done[l - 1] for l in range(lo, hi)])
+print("all operands seen - previous level done (us): mean %.3f  p10 %.3f  p90 %.3f" % (rel3.mean() / 1e3, np.percentile(rel3, 10) / 1e3, np.percentile(rel3, 90) / 1e3))
+print("proxy seen - previous level done (us): mean %.3f  p10 %.3f  p90 %.3f" % (rel2.mean() / 1e3, np.percentile(rel2, 10) / 1e3, np.percentile(rel2, 90) / 1e3))
+for l in range(lo + 200, lo + 204):
+    seg = t[starts[l]:starts[l + 1]]
+    print("level", l, "width", int(widths[l]), "chunk stored times rel. to previous level done (us):", np.round((seg[:, 4] - done[l - 1]) / 1e3, 2).tolist())
