@@ -653,11 +653,14 @@ template <int BS> __device__ __forceinline__ bool ld_group(const double *p, doub
 template <bool LOWER, int BS, int NBC>
 __global__ void __launch_bounds__(TC_THREADS) k_tri_sf_block(int n, int nChunks, const longlong2 *__restrict__ meta, const int *__restrict__ items,
                                                             const int *__restrict__ nbrT, const double *__restrict__ valT,
-                                                            const double *__restrict__ rhs, double *out, unsigned *counter
+                                                            const double *__restrict__ rhs, double *out, unsigned *counter, int proxy
 #ifdef MMADMM_TRI_PROF
-                                                            , int profLo
+                                                            , int profLo, int pmode   // pmode (timing only, results wrong): 1 no proxy phase, 2 no FP chain, 4 no early batch
 #endif
 ) {
+#ifndef MMADMM_TRI_PROF
+    constexpr int pmode = 0;
+#endif
     const int lane = threadIdx.x & 31;
     constexpr int BB = BS * BS;
     int chunk = 0;
@@ -690,7 +693,7 @@ __global__ void __launch_bounds__(TC_THREADS) k_tri_sf_block(int n, int nChunks,
         // operands that have been there for a long time: one batch now, while nobody waits for this chunk
 #pragma unroll
         for (int q = 0; q < NBC; q++)
-            if (need & (1u << q)) {
+            if ((need & (1u << q)) && !(pmode & 4)) {
                 double v[BS];
                 if (ld_group<BS>(out + nb[q], v)) {
 #pragma unroll
@@ -698,10 +701,12 @@ __global__ void __launch_bounds__(TC_THREADS) k_tri_sf_block(int n, int nChunks,
                     need &= ~(1u << q);
                 }
             }
-        // a far-ahead warp waits through ONE lane polling ONE neighbour (see k_tri_syncfree)
+        // optional ("tri_proxy" 1): a far-ahead warp waits through ONE lane polling ONE neighbour (see k_tri_syncfree).  Off by
+        // default here: with one 16-byte request per lane per round trip the polls of all waiting warps together stay far
+        // below what L2 serves, and the extra detection step cost 0.9 us per level (12.7 vs 16.5 ms per application).
         SF_STAMP(1);
         {
-            const unsigned waiting = __ballot_sync(0xffffffffu, need != 0u);
+            const unsigned waiting = (!proxy || (pmode & 1)) ? 0u : __ballot_sync(0xffffffffu, need != 0u);
             if (waiting) {
                 if (lane == __ffs(waiting) - 1) {
                     const int b = LOWER ? 31 - __clz(need) : __ffs(need) - 1;
@@ -747,7 +752,7 @@ __global__ void __launch_bounds__(TC_THREADS) k_tri_sf_block(int n, int nChunks,
             }
 #pragma unroll
             for (int q = 0; q < NBC; q++)
-                if (nb[q] >= 0) {
+                if (nb[q] >= 0 && !(pmode & 2)) {
 #pragma unroll
                     for (int cidx = 0; cidx < BS; cidx++) sj -= a[q][r * BS + cidx] * o[q][cidx];
                 }
@@ -763,7 +768,7 @@ __global__ void __launch_bounds__(TC_THREADS) k_tri_sf_block(int n, int nChunks,
                 for (int cidx = 0; cidx < BS; cidx++)
                     if (cidx < r) sj -= d[r * BS + cidx] * own[cidx];
             }
-            own[r] = LOWER ? sj : sj / d[r * BS + r];
+            own[r] = (LOWER || (pmode & 2)) ? sj : sj / d[r * BS + r];
         }
         if (base >= 0) {
             if (BS == 2) asm volatile("st.relaxed.gpu.global.v2.f64 [%0], {%1, %2};" ::"l"(out + base), "d"(own[0]), "d"(own[1]) : "memory");
@@ -915,7 +920,9 @@ struct mmadmm_pcg {
         bool blocked = false;                     // BS x BS block form (k_tri_sf_block): col = neighbour planes, val = block planes
     } chellL, chellU;
     unsigned *sfCounter = nullptr;
+    int sfGridX2 = 2;                             // dataflow grid = sfGrid * sfGridX2 / 2 CTAs ("tri_sf_ctas_per_sm_x2")
     int sfGrid = 0;                               // CTAs of the dataflow kernel (SM count x resident CTAs per SM)
+    int sfProxy = 0;                              // "tri_proxy": block dataflow kernel waits through one proxy lane per warp first
     int sfBlocks = 1;                             // "tri_blocks": use the BS x BS block form of the dataflow solve where the pattern allows
     struct Lell {
         int4 *meta_d = nullptr; int *col = nullptr, *src = nullptr; double *val = nullptr; size_t slots = 0;
@@ -1360,17 +1367,18 @@ void tri_solve_blk(mmadmm_pcg *h, const std::vector<int> &lvl, const int *lvl_d,
     if (h->triMode == 2 && C.nChunks > 0) {   // the whole solve: sentinel fill + one persistent launch
         k_tri_sf_prepare<<<cdiv(h->n, TPB), TPB, 0, h->stream>>>(h->n, out, h->sfCounter);
         static const int gridEnv = getenv("MMADMM_SF_GRID") ? atoi(getenv("MMADMM_SF_GRID")) : 0;   // experiments
-        const int grid = gridEnv > 0 ? gridEnv : std::min(2 * h->sfGrid, cdiv(C.nChunks, TC_THREADS / 32));   // chunks are claimed dynamically: CTAs that are not resident at once are harmless
+        const int grid = gridEnv > 0 ? gridEnv : std::min(std::max(1, h->sfGrid * h->sfGridX2 / 2), cdiv(C.nChunks, TC_THREADS / 32));   // chunks are claimed dynamically: CTAs that are not resident at once are harmless
         if (C.blocked) {
 #ifdef MMADMM_TRI_PROF
             static const int profLoB = getenv("MMADMM_SF_PROF_LO") ? atoi(getenv("MMADMM_SF_PROF_LO")) : 0;
             static const int profU = getenv("MMADMM_SF_PROF_UPPER") ? 1 : 0;
             const int pl = (LOWER != (profU == 1)) ? profLoB : (1 << 30);
-            if (BS == 2) k_tri_sf_block<LOWER, 2, 8><<<grid, TC_THREADS, 0, h->stream>>>(h->n, C.nChunks, C.meta_d, C.items, C.col, C.val, rhs, out, h->sfCounter, pl);
-            else k_tri_sf_block<LOWER, 3, 5><<<grid, TC_THREADS, 0, h->stream>>>(h->n, C.nChunks, C.meta_d, C.items, C.col, C.val, rhs, out, h->sfCounter, pl);
+            static const int pmodeB = getenv("MMADMM_TRI_PROF_MODE") ? atoi(getenv("MMADMM_TRI_PROF_MODE")) : 0;
+            if (BS == 2) k_tri_sf_block<LOWER, 2, 8><<<grid, TC_THREADS, 0, h->stream>>>(h->n, C.nChunks, C.meta_d, C.items, C.col, C.val, rhs, out, h->sfCounter, h->sfProxy, pl, pmodeB);
+            else k_tri_sf_block<LOWER, 3, 5><<<grid, TC_THREADS, 0, h->stream>>>(h->n, C.nChunks, C.meta_d, C.items, C.col, C.val, rhs, out, h->sfCounter, h->sfProxy, pl, pmodeB);
 #else
-            if (BS == 2) k_tri_sf_block<LOWER, 2, 8><<<grid, TC_THREADS, 0, h->stream>>>(h->n, C.nChunks, C.meta_d, C.items, C.col, C.val, rhs, out, h->sfCounter);
-            else k_tri_sf_block<LOWER, 3, 5><<<grid, TC_THREADS, 0, h->stream>>>(h->n, C.nChunks, C.meta_d, C.items, C.col, C.val, rhs, out, h->sfCounter);
+            if (BS == 2) k_tri_sf_block<LOWER, 2, 8><<<grid, TC_THREADS, 0, h->stream>>>(h->n, C.nChunks, C.meta_d, C.items, C.col, C.val, rhs, out, h->sfCounter, h->sfProxy);
+            else k_tri_sf_block<LOWER, 3, 5><<<grid, TC_THREADS, 0, h->stream>>>(h->n, C.nChunks, C.meta_d, C.items, C.col, C.val, rhs, out, h->sfCounter, h->sfProxy);
 #endif
             h->launches += 2;
             return;
@@ -1563,6 +1571,8 @@ int mmadmm_pcg_set_option(mmadmm_pcg *h, const char *name, int value) {
         }
         return MMADMM_OK;
     }
+    if (!std::strcmp(name, "tri_proxy")) { h->sfProxy = value ? 1 : 0; return MMADMM_OK; }
+    if (!std::strcmp(name, "tri_sf_ctas_per_sm_x2")) { if (value < 1 || value > 8) return MMADMM_EINVAL; h->sfGridX2 = value; return MMADMM_OK; }
     if (!std::strcmp(name, "tri_blocks")) {   // 1 (default): block form of the dataflow solve where the pattern is made of BS x BS blocks
         h->sfBlocks = value ? 1 : 0;
         if (h->triMode == 2 && h->precond == 1) {

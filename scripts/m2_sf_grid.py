@@ -4,6 +4,7 @@ import numpy as np
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 mm = importlib.import_module("mm-admm_b200")
+if os.environ.get("MMADMM_USE_PROF_LIB"): mm.LIB_PATH = os.path.join(ROOT, "build", "prof", "libmmadmm_b200_prof.so")
 nx = int(sys.argv[1]) if len(sys.argv) > 1 else 1024
 Vp, F, mask = mm.generate_uniform_rect_mesh(2, nx, nx, 0)
 mon = mm.TestMonitor(2, 4).evaluate_at_vertices(Vp)
@@ -12,4 +13,4 @@ solver = mm.MeshIntegrator(0.025, mesh)
 rowptr, col, val = solver.backward_euler_jacobian()
 pcg = mm.PCG(rowptr, col, val, precond="ilu0")
 pcg.set_option("tri_mode", 2); pcg.set_option("row_block", 2)
-print(json.dumps({"grid": os.environ.get("MMADMM_SF_GRID"), "precond_ms_device": round(pcg.time_precond(5), 3)}))
+print(json.dumps({"grid": os.environ.get("MMADMM_SF_GRID"), "pmode": os.environ.get("MMADMM_TRI_PROF_MODE"), "precond_ms_device": round(pcg.time_precond(5), 3)}))
