@@ -483,6 +483,7 @@ __device__ __forceinline__ double tri_sf_wait(const double *p) {
 #ifdef MMADMM_TRI_PROF
 // timing experiments: per chunk {claimed, factor planes in registers, proxy operand seen, all operands seen, results stored} (ns)
 __device__ unsigned long long g_sf_prof[5 * 65536];
+__device__ int g_sf_spins[65536];   // lane 0: polls issued in the per-lane wait of the chunk
 __device__ __forceinline__ unsigned long long gtimer() { unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); return t; }
 #define SF_STAMP(k) do { if (lane == 0 && chunk >= profLo && chunk < profLo + 65536) g_sf_prof[5 * (chunk - profLo) + (k)] = gtimer(); } while (0)
 #else
@@ -638,13 +639,15 @@ __global__ void __launch_bounds__(TC_THREADS) k_tri_syncfree(int n, int nChunks,
 // neighbour group (a 16-byte load for BS = 2), shared by the BS rows.  Operands that were computed long ago (the cell-centre
 // rows of the upper factor) are picked up when the chunk is claimed, off the critical path.  Row arithmetic in CSR order:
 // L row = neighbour blocks ascending, then the group's own columns; U row = own columns, then neighbour blocks: same bits.
-template <int BS> __device__ __forceinline__ bool ld_group(const double *p, double (&v)[BS]) {
+template <int BS> __device__ __forceinline__ void ld_group_raw(const double *p, double (&v)[BS]) {
     if (BS == 2) {
         asm volatile("ld.relaxed.gpu.global.v2.f64 {%0, %1}, [%2];" : "=d"(v[0]), "=d"(v[1]) : "l"(p) : "memory");
     } else {
 #pragma unroll
         for (int k = 0; k < BS; k++) v[k] = ld_relaxed_gpu(p + k);
     }
+}
+template <int BS> __device__ __forceinline__ bool group_ready(const double (&v)[BS]) {
     bool ok = true;
 #pragma unroll
     for (int k = 0; k < BS; k++) ok = ok && ((unsigned long long)__double_as_longlong(v[k]) != TRI_SENTINEL);
@@ -691,16 +694,20 @@ __global__ void __launch_bounds__(TC_THREADS) k_tri_sf_block(int n, int nChunks,
             }
         }
         // operands that have been there for a long time: one batch now, while nobody waits for this chunk
+        // (all requests are issued before any result is looked at: one round trip for the batch, not one per neighbour)
+        {
+            double v[NBC][BS];
 #pragma unroll
-        for (int q = 0; q < NBC; q++)
-            if ((need & (1u << q)) && !(pmode & 4)) {
-                double v[BS];
-                if (ld_group<BS>(out + nb[q], v)) {
+            for (int q = 0; q < NBC; q++)
+                if ((need & (1u << q)) && !(pmode & 4)) ld_group_raw<BS>(out + nb[q], v[q]);
 #pragma unroll
-                    for (int k = 0; k < BS; k++) o[q][k] = v[k];
+            for (int q = 0; q < NBC; q++)
+                if ((need & (1u << q)) && !(pmode & 4) && group_ready<BS>(v[q])) {
+#pragma unroll
+                    for (int k = 0; k < BS; k++) o[q][k] = v[q][k];
                     need &= ~(1u << q);
                 }
-            }
+        }
         // optional ("tri_proxy" 1): a far-ahead warp waits through ONE lane polling ONE neighbour (see k_tri_syncfree).  Off by
         // default here: with one 16-byte request per lane per round trip the polls of all waiting warps together stay far
         // below what L2 serves, and the extra detection step cost 0.9 us per level (12.7 vs 16.5 ms per application).
@@ -722,22 +729,26 @@ __global__ void __launch_bounds__(TC_THREADS) k_tri_sf_block(int n, int nChunks,
                 __syncwarp();
             }
         }
-        // then every lane waits for its own neighbours, nearest (expected last) first, one request per round trip (requesting all
-        // missing ones together measured slower: 13.7 vs 12.5 ms per application on the C2-size Jacobian)
+        // then every lane waits for its own neighbours: per round trip ALL still-missing ones are requested before any result is
+        // looked at (a request followed by its own test, neighbour after neighbour, serialises the round trips -- and so do
+        // lanes that wait for different neighbour slots: measured 0.51 us per poll instead of the 0.19 us of one relaxed load)
         SF_STAMP(2);
         for (int spins = 0; need; spins++) {
-            const int b = LOWER ? 31 - __clz(need) : __ffs(need) - 1;
+            double v[NBC][BS];
 #pragma unroll
             for (int q = 0; q < NBC; q++)
-                if (b == q) {
-                    double v[BS];
-                    if (ld_group<BS>(out + nb[q], v)) {
+                if (need & (1u << q)) ld_group_raw<BS>(out + nb[q], v[q]);
 #pragma unroll
-                        for (int k = 0; k < BS; k++) o[q][k] = v[k];
-                        need &= ~(1u << q);
-                    }
+            for (int q = 0; q < NBC; q++)
+                if ((need & (1u << q)) && group_ready<BS>(v[q])) {
+#pragma unroll
+                    for (int k = 0; k < BS; k++) o[q][k] = v[q][k];
+                    need &= ~(1u << q);
                 }
             if (spins > (1 << 24)) __trap();
+#ifdef MMADMM_TRI_PROF
+            if (lane == 0 && chunk >= profLo && chunk < profLo + 65536) g_sf_spins[chunk - profLo] = spins + 1;
+#endif
         }
         __syncwarp();
         SF_STAMP(3);
@@ -1893,6 +1904,7 @@ int mmadmm_pcg_debug_levels(mmadmm_pcg *h, int which, int *out, int cap) {
     return (int)v.size();
 }
 // timing experiments: per-chunk time stamps of the last LOWER dataflow solve + the chunk's first item's level is the caller's business
+int mmadmm_pcg_debug_sf_spins(int *out65536) { return cudaMemcpyFromSymbol(out65536, g_sf_spins, sizeof(int) * 65536) == cudaSuccess ? 0 : 2; }
 int mmadmm_pcg_debug_sf_prof(unsigned long long *out5x65536) {
     return cudaMemcpyFromSymbol(out5x65536, g_sf_prof, sizeof(unsigned long long) * 5 * 65536) == cudaSuccess ? 0 : 2;
 }

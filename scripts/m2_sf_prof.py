@@ -48,6 +48,13 @@ rel3 = np.concatenate([t[starts[l]:starts[l + 1], 3] - done[l - 1] for l in rang
 rel2 = np.concatenate([t[starts[l]:starts[l + 1], 2] - done[l - 1] for l in range(lo, hi)])
 print("all operands seen - previous level done (us): mean %.3f  p10 %.3f  p90 %.3f" % (rel3.mean() / 1e3, np.percentile(rel3, 10) / 1e3, np.percentile(rel3, 90) / 1e3))
 print("proxy seen - previous level done (us): mean %.3f  p10 %.3f  p90 %.3f" % (rel2.mean() / 1e3, np.percentile(rel2, 10) / 1e3, np.percentile(rel2, 90) / 1e3))
+sp = np.zeros(65536, dtype=np.int32)
+if L.mmadmm_pcg_debug_sf_spins(sp.ctypes.data_as(C.c_void_p)) == 0:
+    ws = sp[starts[lo]:starts[hi]]
+    dur = (w[:, 3] - w[:, 2]) / 1e3
+    ok = ws > 0
+    print("per-lane wait of lane 0: polls per chunk mean %.1f  median %.0f;  us per poll %.3f  (chunks with polls: %d of %d)" % (
+        ws[ok].mean(), np.median(ws[ok]), float(dur[ok].sum() / ws[ok].sum()), int(ok.sum()), len(ws)))
 for l in range(lo + 200, lo + 204):
     seg = t[starts[l]:starts[l + 1]]
     print("level", l, "width", int(widths[l]), "chunk stored times rel. to previous level done (us):", np.round((seg[:, 4] - done[l - 1]) / 1e3, 2).tolist())
