@@ -27,6 +27,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <ctime>
 #include <string>
 #include <vector>
 
@@ -36,6 +37,17 @@ namespace {
 
 constexpr int TPB = 256;
 inline int cdiv(size_t a, size_t b) { return (int)((a + b - 1) / b); }
+// MMADMM_DEBUG_SETUP=1: host-side phase times of the set-up paths on stderr
+struct SetupTimer {
+    bool on; timespec t0; const char *what;
+    explicit SetupTimer(const char *w) : on(getenv("MMADMM_DEBUG_SETUP") != nullptr), what(w) { if (on) clock_gettime(CLOCK_MONOTONIC, &t0); }
+    void lap(const char *phase) {
+        if (!on) return;
+        timespec t1; clock_gettime(CLOCK_MONOTONIC, &t1);
+        fprintf(stderr, "[mmadmm setup] %s: %s %.1f ms\n", what, phase, (t1.tv_sec - t0.tv_sec) * 1e3 + (t1.tv_nsec - t0.tv_nsec) * 1e-6);
+        t0 = t1;
+    }
+};
 
 __device__ __forceinline__ double warp_sum_d(double v) {
 #pragma unroll
@@ -1304,7 +1316,9 @@ int build_groups(mmadmm_pcg *h, int bs) {
         if ((er = cudaMemcpy(L.col, nbrv.data(), sizeof(int) * nbrv.size(), cudaMemcpyHostToDevice)) != cudaSuccess) return er;
         return cudaMemcpy(L.src, srcv.data(), sizeof(int) * slotsV, cudaMemcpyHostToDevice);
     };
+    SetupTimer tg("build_groups");
     const bool useBlocks = h->triMode == 2 && h->sfBlocks && blockable();
+    tg.lap("block-structure check");
     PCK(cudaSetDevice(h->device));
     if (!h->sfCounter) PCK(cudaMalloc(&h->sfCounter, sizeof(unsigned)));
     std::vector<int> grp;
@@ -1316,10 +1330,12 @@ int build_groups(mmadmm_pcg *h, int bs) {
                 if (cl[k] < g * bs) l = std::max(l, lev[cl[k] / bs] + 1);
         lev[g] = l; nl = std::max(nl, l + 1);
     }
+    tg.lap("lower group levels");
     bucket(nl, grp, h->lvlGL);
     PCK(upload(grp, h->lvlGL, true, &h->grpL, &h->lvlGL_d, &h->kbeGL));
     if (h->triLayout && h->triMode != 2) PCK(lell(grp, h->lvlGL, true, h->lellL));
     if (h->triMode == 2) PCK(useBlocks ? chell_block(grp, h->lvlGL, true, h->chellL) : chell(grp, h->lvlGL, true, h->chellL));
+    tg.lap("lower schedule + factor copy layout + uploads");
     int nu = 0;
     for (int g = ng - 1; g >= 0; g--) {
         int l = 0;
@@ -1328,10 +1344,12 @@ int build_groups(mmadmm_pcg *h, int bs) {
                 if (cl[k] >= (g + 1) * bs) l = std::max(l, lev[cl[k] / bs] + 1);
         lev[g] = l; nu = std::max(nu, l + 1);
     }
+    tg.lap("upper group levels");
     bucket(nu, grp, h->lvlGU);
     PCK(upload(grp, h->lvlGU, false, &h->grpU, &h->lvlGU_d, &h->kbeGU));
     if (h->triLayout && h->triMode != 2) PCK(lell(grp, h->lvlGU, false, h->lellU));
     if (h->triMode == 2) PCK(useBlocks ? chell_block(grp, h->lvlGU, false, h->chellU) : chell(grp, h->lvlGU, false, h->chellU));
+    tg.lap("upper schedule + factor copy layout + uploads");
     h->rowBlock = bs;
     // cudaMemcpy from pageable memory may return before the DMA has landed, and h->stream does not synchronise with the legacy
     // stream: without this the fill kernel below could read a half-uploaded index array (seen as a rare, per-process-stable mismatch)
@@ -1471,6 +1489,7 @@ int mmadmm_pcg_create(int n, const int *rowptr, const int *col, const double *va
     if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) return MMADMM_ENODEVICE;
     mmadmm_pcg *h = new mmadmm_pcg();
     *out = h;
+    SetupTimer tm("pcg_create");
     h->n = n; h->nnz = rowptr[n]; h->precond = precond; h->device = device;
     const int nnz = h->nnz;
     h->rowptr_h.assign(rowptr, rowptr + n + 1); h->col_h.assign(col, col + nnz); h->val_h.assign(val, val + nnz);
@@ -1486,6 +1505,7 @@ int mmadmm_pcg_create(int n, const int *rowptr, const int *col, const double *va
         }
         if (diagPos[i] < 0) { h->err = "every row needs a stored diagonal entry"; return MMADMM_EINVAL; }
     }
+    tm.lap("host copies + pattern check");
     const double avg = (double)nnz / n;
     h->lanes = avg <= 3 ? 1 : avg <= 6 ? 2 : avg <= 12 ? 4 : avg <= 24 ? 8 : avg <= 48 ? 16 : 32;
     PCK(cudaSetDevice(device));
@@ -1505,6 +1525,7 @@ int mmadmm_pcg_create(int n, const int *rowptr, const int *col, const double *va
     PCK(up((void **)&h->invDiag, invDiag.data(), sizeof(double) * (size_t)n));
     std::vector<int> rowsL, rowsU;
     if (precond == 1) {
+        tm.lap("uploads queued");
         // level schedule: level(i) = 1 + max level of the rows it depends on
         std::vector<int> lev(n, 0);
         int nl = 0;
@@ -1545,8 +1566,10 @@ int mmadmm_pcg_create(int n, const int *rowptr, const int *col, const double *va
         }
         PCK(up((void **)&h->lvlL_d, h->lvlL.data(), sizeof(int) * h->lvlL.size()));
         PCK(up((void **)&h->lvlU_d, h->lvlU.data(), sizeof(int) * h->lvlU.size()));
+        tm.lap("level schedules + uploads");
         PCK(cudaStreamSynchronize(h->stream));   // rowsL / rowsU are locals
         { int rcf = ilu_factor_device(h); if (rcf) return rcf; }   // the numeric factor runs on the device, level by level
+        tm.lap("device ILU(0) factor");
     }
     const size_t vb = sizeof(double) * (size_t)n;
     PCK(up((void **)&h->r, nullptr, vb)); PCK(up((void **)&h->z, nullptr, vb)); PCK(up((void **)&h->p, nullptr, vb));
