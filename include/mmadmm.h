@@ -282,6 +282,11 @@ int mmadmm_pcg_refactor_device(mmadmm_pcg *h, const double *val_dev);
  * between groups make levels: on a Jacobian with D x D vertex blocks BS = D halves (2D) / thirds (3D) the level count (the
  * Method 2 context sets BS = D; option "m2_row_block").  Same FMA chains in the same order: bit-identical to BS = 1. */
 int mmadmm_pcg_set_option(mmadmm_pcg *h, const char *name, int value);
+/* Host-only (no device): the level schedule that "row_block" = bs gives the triangular solves of an ILU(0) factor on this pattern
+ * (LASolver solves row by row, ILU_class.cpp:447-527; the levels are this library's parallel order of the same arithmetic).
+ * levL / levU (may be NULL): level of every group [g bs, (g+1) bs) of the lower / upper solve, ceil(n / bs) entries each;
+ * info3 = {lower levels, upper levels, 1 if the pattern is made of dense bs x bs blocks (block form of the dataflow solve)}. */
+int mmadmm_pcg_plan_levels(int n, const int *rowptr, const int *col, int bs, int *levL, int *levU, int *info3);
 /* info4 = {threads per row of the SpMV kernel, lower levels, upper levels (of groups when row_block > 1), kernels launched so far}. */
 int mmadmm_pcg_info(mmadmm_pcg *h, int *info4);
 /* Average device time (ms, CUDA events) of one SpMV + dot launch over `reps` launches. */

@@ -35,8 +35,21 @@ ABI_SYMBOLS = [
     "mmadmm_comm_unique_id", "mmadmm_create_dist", "mmadmm_local_sizes", "mmadmm_get_x_local",
     "mmadmm_pcg_create", "mmadmm_pcg_solve", "mmadmm_pcg_solve_device", "mmadmm_pcg_bicgstab", "mmadmm_pcg_bicgstab_device", "mmadmm_pcg_spmv", "mmadmm_pcg_precond",
     "mmadmm_update_monitor", "mmadmm_set_writeback", "mmadmm_writeback_fence", "mmadmm_checkpoint", "mmadmm_restore",
-    "mmadmm_pcg_get_ilu", "mmadmm_pcg_refactor_device", "mmadmm_pcg_set_option", "mmadmm_pcg_info", "mmadmm_pcg_time_spmv", "mmadmm_pcg_time_precond", "mmadmm_pcg_last_error", "mmadmm_pcg_destroy", "mmadmm_measure_fp64_peak",
+    "mmadmm_pcg_get_ilu", "mmadmm_pcg_plan_levels", "mmadmm_pcg_refactor_device", "mmadmm_pcg_set_option", "mmadmm_pcg_info", "mmadmm_pcg_time_spmv", "mmadmm_pcg_time_precond", "mmadmm_pcg_last_error", "mmadmm_pcg_destroy", "mmadmm_measure_fp64_peak",
 ]
+
+
+def pcg_plan_levels(rowptr, col, bs):
+    """mmadmm_pcg_plan_levels (host only, no GPU needed): (levL, levU, info) of the group schedule that row_block = bs gives
+    the ILU(0) triangular solves on this CSR pattern; info = dict(lower_levels, upper_levels, blockable)."""
+    rowptr = np.ascontiguousarray(rowptr, dtype=np.int32); col = np.ascontiguousarray(col, dtype=np.int32)
+    n = len(rowptr) - 1
+    ng = (n + bs - 1) // bs
+    levL = np.zeros(ng, dtype=np.int32); levU = np.zeros(ng, dtype=np.int32); info = np.zeros(3, dtype=np.int32)
+    rc = lib().mmadmm_pcg_plan_levels(n, _ip(rowptr), _ip(col), int(bs), _ip(levL), _ip(levU), _ip(info))
+    if rc:
+        raise MMADMMError(f"mmadmm_pcg_plan_levels error {ERRORS.get(rc, rc)}")
+    return levL, levU, dict(lower_levels=int(info[0]), upper_levels=int(info[1]), blockable=bool(info[2]))
 
 
 class MMADMMError(RuntimeError):
@@ -129,6 +142,7 @@ def lib():
         L.mmadmm_pcg_spmv.argtypes = [vp, _c_dp, _c_dp]
         L.mmadmm_pcg_precond.argtypes = [vp, _c_dp, _c_dp]
         L.mmadmm_pcg_get_ilu.argtypes = [vp, _c_dp]
+        L.mmadmm_pcg_plan_levels.argtypes = [C.c_int, _c_ip, _c_ip, C.c_int, _c_ip, _c_ip, _c_ip]
         L.mmadmm_pcg_refactor_device.argtypes = [vp, vp]
         L.mmadmm_pcg_info.argtypes = [vp, _c_ip]
         L.mmadmm_pcg_time_spmv.argtypes = [vp, C.c_int, _c_dp]

@@ -1071,6 +1071,58 @@ int ilu_factor_device(mmadmm_pcg *h) {
     return lell_refresh(h);
 }
 
+// ---- host-side planning of the group schedules (no device needed: mmadmm_pcg_plan_levels, tests/test_pcg_plan.py) ----
+// Level of every group [g*bs, min(n, (g+1)*bs)) of the lower (upper) solve: 1 + the highest level among the OTHER groups that hold
+// a column left (right) of the group in one of its rows; rows of a group are solved in sequence by one thread.  Returns the
+// number of levels.
+int plan_group_levels(int n, int bs, bool lower, const int *rp, const int *cl, const int *dg, std::vector<int> &lev) {
+    const int ng = (n + bs - 1) / bs;
+    lev.assign(ng, 0);
+    int nlev = 0;
+    if (lower) {
+        for (int g = 0; g < ng; g++) {
+            int l = 0;
+            for (int i = g * bs; i < std::min(n, (g + 1) * bs); i++)
+                for (int k = rp[i]; k < dg[i]; k++)
+                    if (cl[k] < g * bs) l = std::max(l, lev[cl[k] / bs] + 1);
+            lev[g] = l; nlev = std::max(nlev, l + 1);
+        }
+    } else {
+        for (int g = ng - 1; g >= 0; g--) {
+            int l = 0;
+            for (int i = g * bs; i < std::min(n, (g + 1) * bs); i++)
+                for (int k = dg[i] + 1; k < rp[i + 1]; k++)
+                    if (cl[k] >= (g + 1) * bs) l = std::max(l, lev[cl[k] / bs] + 1);
+            lev[g] = l; nlev = std::max(nlev, l + 1);
+        }
+    }
+    return nlev;
+}
+// Block form of the dataflow solve (k_tri_sf_block) is possible when every group is bs full rows whose columns are the same
+// aligned runs of bs (dense bs x bs blocks, the group's own block among them).
+bool plan_blockable(int n, int bs, const int *rp, const int *cl) {
+    if ((bs != 2 && bs != 3) || n % bs) return false;
+    const int ng = n / bs;
+    for (int g = 0; g < ng; g++) {
+        const int i0 = g * bs, len0 = rp[i0 + 1] - rp[i0];
+        if (len0 % bs) return false;
+        bool own = false;
+        for (int k = rp[i0]; k < rp[i0 + 1]; k += bs) {
+            if (cl[k] % bs) return false;
+            for (int c = 1; c < bs; c++)
+                if (cl[k + c] != cl[k] + c) return false;
+            own = own || cl[k] == i0;
+        }
+        if (!own) return false;
+        for (int r = 1; r < bs; r++) {
+            if (rp[i0 + r + 1] - rp[i0 + r] != len0) return false;
+            for (int k = 0; k < len0; k++)
+                if (cl[rp[i0 + r] + k] != cl[rp[i0] + k]) return false;
+        }
+    }
+    return true;
+}
+
 void free_groups(mmadmm_pcg *h) {
     void *ptrs[6] = {h->grpL, h->grpU, h->lvlGL_d, h->lvlGU_d, h->kbeGL, h->kbeGU};
     for (void *q : ptrs) {
@@ -1243,29 +1295,6 @@ int build_groups(mmadmm_pcg *h, int bs) {
         if ((er = cudaMemcpy(L.col, colv.data(), sizeof(int) * slots, cudaMemcpyHostToDevice)) != cudaSuccess) return er;
         return cudaMemcpy(L.src, srcv.data(), sizeof(int) * slots, cudaMemcpyHostToDevice);
     };
-    // Block form of the chunk-ELL copy (k_tri_sf_block): possible when every group is bs full rows whose columns are the same
-    // aligned runs of bs (dense bs x bs blocks, the group's own block among them).
-    auto blockable = [&]() -> bool {
-        if ((bs != 2 && bs != 3) || n % bs) return false;
-        for (int g = 0; g < ng; g++) {
-            const int i0 = g * bs, len0 = rp[i0 + 1] - rp[i0];
-            if (len0 % bs) return false;
-            bool own = false;
-            for (int k = rp[i0]; k < rp[i0 + 1]; k += bs) {
-                if (cl[k] % bs) return false;
-                for (int c = 1; c < bs; c++)
-                    if (cl[k + c] != cl[k] + c) return false;
-                own = own || cl[k] == i0;
-            }
-            if (!own) return false;
-            for (int r = 1; r < bs; r++) {
-                if (rp[i0 + r + 1] - rp[i0 + r] != len0) return false;
-                for (int k = 0; k < len0; k++)
-                    if (cl[rp[i0 + r] + k] != cl[rp[i0] + k]) return false;
-            }
-        }
-        return true;
-    };
     auto chell_block = [&](const std::vector<int> &grp, const std::vector<int> &off, bool lower, mmadmm_pcg::Chell &L) -> cudaError_t {
         const int nlev = (int)off.size() - 1, BB = bs * bs;
         std::vector<int> items;
@@ -1317,33 +1346,19 @@ int build_groups(mmadmm_pcg *h, int bs) {
         return cudaMemcpy(L.src, srcv.data(), sizeof(int) * slotsV, cudaMemcpyHostToDevice);
     };
     SetupTimer tg("build_groups");
-    const bool useBlocks = h->triMode == 2 && h->sfBlocks && blockable();
+    const bool useBlocks = h->triMode == 2 && h->sfBlocks && plan_blockable(n, bs, rp.data(), cl.data());
     tg.lap("block-structure check");
     PCK(cudaSetDevice(h->device));
     if (!h->sfCounter) PCK(cudaMalloc(&h->sfCounter, sizeof(unsigned)));
     std::vector<int> grp;
-    int nl = 0;
-    for (int g = 0; g < ng; g++) {
-        int l = 0;
-        for (int i = g * bs; i < std::min(n, (g + 1) * bs); i++)
-            for (int k = rp[i]; k < dg[i]; k++)
-                if (cl[k] < g * bs) l = std::max(l, lev[cl[k] / bs] + 1);
-        lev[g] = l; nl = std::max(nl, l + 1);
-    }
+    const int nl = plan_group_levels(n, bs, true, rp.data(), cl.data(), dg.data(), lev);
     tg.lap("lower group levels");
     bucket(nl, grp, h->lvlGL);
     PCK(upload(grp, h->lvlGL, true, &h->grpL, &h->lvlGL_d, &h->kbeGL));
     if (h->triLayout && h->triMode != 2) PCK(lell(grp, h->lvlGL, true, h->lellL));
     if (h->triMode == 2) PCK(useBlocks ? chell_block(grp, h->lvlGL, true, h->chellL) : chell(grp, h->lvlGL, true, h->chellL));
     tg.lap("lower schedule + factor copy layout + uploads");
-    int nu = 0;
-    for (int g = ng - 1; g >= 0; g--) {
-        int l = 0;
-        for (int i = g * bs; i < std::min(n, (g + 1) * bs); i++)
-            for (int k = dg[i] + 1; k < rp[i + 1]; k++)
-                if (cl[k] >= (g + 1) * bs) l = std::max(l, lev[cl[k] / bs] + 1);
-        lev[g] = l; nu = std::max(nu, l + 1);
-    }
+    const int nu = plan_group_levels(n, bs, false, rp.data(), cl.data(), dg.data(), lev);
     tg.lap("upper group levels");
     bucket(nu, grp, h->lvlGU);
     PCK(upload(grp, h->lvlGU, false, &h->grpU, &h->lvlGU_d, &h->kbeGU));
@@ -1480,6 +1495,25 @@ void apply_ilu(mmadmm_pcg *h, const double *r, double *z) {
 }  // namespace
 
 extern "C" {
+
+int mmadmm_pcg_plan_levels(int n, const int *rowptr, const int *col, int bs, int *levL, int *levU, int *info3) {
+    if (n <= 0 || !rowptr || !col || (bs != 1 && bs != 2 && bs != 3 && bs != 4 && bs != 6)) return MMADMM_EINVAL;
+    std::vector<int> dg(n, -1);
+    for (int i = 0; i < n; i++) {
+        for (int k = rowptr[i]; k < rowptr[i + 1]; k++) {
+            if (col[k] < 0 || col[k] >= n || (k > rowptr[i] && col[k] <= col[k - 1])) return MMADMM_EINVAL;
+            if (col[k] == i) dg[i] = k;
+        }
+        if (dg[i] < 0) return MMADMM_EINVAL;
+    }
+    std::vector<int> lev;
+    const int nl = plan_group_levels(n, bs, true, rowptr, col, dg.data(), lev);
+    if (levL) std::copy(lev.begin(), lev.end(), levL);
+    const int nu = plan_group_levels(n, bs, false, rowptr, col, dg.data(), lev);
+    if (levU) std::copy(lev.begin(), lev.end(), levU);
+    if (info3) { info3[0] = nl; info3[1] = nu; info3[2] = plan_blockable(n, bs, rowptr, col) ? 1 : 0; }
+    return MMADMM_OK;
+}
 
 int mmadmm_pcg_create(int n, const int *rowptr, const int *col, const double *val, int precond, int device, mmadmm_pcg **out) {
     if (!out) return MMADMM_EINVAL;
