@@ -276,6 +276,11 @@ int mmadmm_pcg_refactor_device(mmadmm_pcg *h, const double *val_dev);
  * chunks in level order from an atomic counter; the factor is read from a chunk-major copy (coalesced), in BS x BS block
  * form when the pattern is made of dense blocks and row_block = BS ("tri_blocks" = 0 forces the generic form).
  * "tri_layout": 1 = the cluster kernels of tri_mode 1 read a level-major (ELL) copy of the factor instead of CSR.
+ * "tri_schedule" = row_block | tri_layout << 8 | (tri_mode + 1) << 12 sets the three at once (one rebuild of the schedules;
+ * bits 12-13 zero = keep tri_mode).  "tri_proxy" 1: the block dataflow kernel lets a waiting warp poll through one lane first
+ * (default 0).  "tri_sf_ctas_per_sm_x2" (1..8, default 2): CTAs of the dataflow kernels = SMs x value / 2.
+ * The copies cost memory: chunk-major factor copy = (values 8 B + source index 4 B) per stored entry + padding, once per
+ * triangular factor (C2-size Method 2 Jacobian, 58.7 M entries: about 1.3 GB next to the 0.7 GB of CSR values and indices).
  * All modes and layouts run every row's FMA chain in ascending column order: results are bit-identical.
  * "row_block": BS = 1 (default), 2, 3, 4 or 6 (the last group may be short): the triangular solves schedule GROUPS of BS consecutive rows, one
  * thread solving its group's rows in natural order with the operands of its own group in registers, so only dependencies
