@@ -1007,6 +1007,8 @@ int build_sell(mmadmm_pcg *h) {
     if (h->slicePtr) return MMADMM_OK;
     if (h->valHostStale) {
         PCK(cudaSetDevice(h->device));
+        PCK(cudaStreamSynchronize(h->stream));
+        h->val_h.resize((size_t)h->nnz);
         PCK(cudaMemcpy(h->val_h.data(), h->val, sizeof(double) * (size_t)h->nnz, cudaMemcpyDeviceToHost));
         h->valHostStale = false;
     }
@@ -1265,7 +1267,8 @@ int build_groups(mmadmm_pcg *h, int bs) {
             slots += (size_t)bs * (m + P0) * 32;
         }
         std::vector<int> colv(slots, -1), srcv(slots, -1);
-        for (int c = 0; c < nChunks; c++) {
+#pragma omp parallel for schedule(static)
+        for (int c = 0; c < nChunks; c++) {   // chunks own disjoint slots
             const int MP = (int)meta[c].y + P0;
             for (int r = 0; r < 32; r++) {
                 const int b = items[(size_t)c * 32 + r];
@@ -1318,7 +1321,8 @@ int build_groups(mmadmm_pcg *h, int bs) {
             slotsI += (size_t)m * 32;
         }
         std::vector<int> nbrv(std::max<size_t>(slotsI, 1), -1), srcv(slotsV, -1);
-        for (int c = 0; c < nChunks; c++) {
+#pragma omp parallel for schedule(static)
+        for (int c = 0; c < nChunks; c++) {   // chunks own disjoint slots
             for (int r = 0; r < 32; r++) {
                 const int b = items[(size_t)c * 32 + r];
                 if (b < 0) continue;
@@ -1526,7 +1530,8 @@ int mmadmm_pcg_create(int n, const int *rowptr, const int *col, const double *va
     SetupTimer tm("pcg_create");
     h->n = n; h->nnz = rowptr[n]; h->precond = precond; h->device = device;
     const int nnz = h->nnz;
-    h->rowptr_h.assign(rowptr, rowptr + n + 1); h->col_h.assign(col, col + nnz); h->val_h.assign(val, val + nnz);
+    h->rowptr_h.assign(rowptr, rowptr + n + 1); h->col_h.assign(col, col + nnz);
+    h->valHostStale = true;   // the host copy of the values (SELL build only) is fetched from the device when needed
     // pattern checks: sorted columns, diagonal present
     std::vector<int> diagPos(n, -1);
     for (int i = 0; i < n; i++) {
@@ -1750,7 +1755,7 @@ int mmadmm_pcg_refactor_device(mmadmm_pcg *h, const double *val_dev) {
     k_inv_diag<<<cdiv(h->n, TPB), TPB, 0, h->stream>>>(h->n, h->diagPos, h->val, h->invDiag);
     h->launches++;
     if (h->slicePtr) {   // the SELL copy holds values too: rebuild it from the new ones (host-side build, rare)
-        PCK(cudaMemcpyAsync(h->val_h.data(), h->val, sizeof(double) * (size_t)h->nnz, cudaMemcpyDeviceToHost, h->stream));
+        h->valHostStale = true;   // build_sell fetches the new values
         PCK(cudaStreamSynchronize(h->stream));
         cudaFree(h->slicePtr); cudaFree(h->scol); cudaFree(h->sval); cudaFree(h->perm);
         h->slicePtr = h->scol = h->perm = nullptr; h->sval = nullptr;
