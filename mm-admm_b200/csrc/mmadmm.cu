@@ -581,7 +581,9 @@ __global__ void __launch_bounds__(TPB_, MINB) k_prox(ElemArgs<D> a) {
 // forms only its own vertex's block of the gradient (block_grad_own_iso).
 // (Round 1's k_prox_vw gave a CTA of four vertex WARPS one 32-element tile and paid four CTA barriers per BFGS iteration:
 // 3.81 ms on C4; this form: see DESIGN.md 3.2.)
-template <bool COMP, bool ISO, int WPB, int MINB>
+// KEEP: the thread's own rows of B (3 x 12) stay in registers from pass 1 to pass 3 (and across BFGS iterations): 108 instead
+// of 180 shared-memory accesses per thread and iteration, at 72 more registers (A/B variants, "prox_variant" 3-5).
+template <bool COMP, bool ISO, int WPB, int MINB, bool KEEP = false>
 __global__ void __launch_bounds__(WPB * 32, MINB) k_prox_q(const __grid_constant__ ElemArgs<3> a) {
     constexpr int D = 3, n = 12, NN = 144, NV = 4, DD = 9;
     constexpr unsigned FULL = 0xffffffffu;
@@ -725,16 +727,23 @@ __global__ void __launch_bounds__(WPB * 32, MINB) k_prox_q(const __grid_constant
         mbar_wait(barB, (unsigned)(it & 1));
         bool done = !active;
         int iters = 0;
+        double Br[KEEP ? D : 1][KEEP ? n : 1];
         for (int iter = 0; iter < 50; iter++) {
             double pk[D], yk[D], By[D], yB[D], G1[D];
             {   // pass 1: pk = -B Gk (own rows), full step
                 double Gall[n];
                 all_of(Gk, Gall);
+                if (KEEP && iter == 0) {
+#pragma unroll
+                    for (int rl = 0; rl < D; rl++)
+#pragma unroll
+                        for (int c = 0; c < n; c++) Br[KEEP ? rl : 0][KEEP ? c : 0] = BROW(rl, c);
+                }
 #pragma unroll
                 for (int rl = 0; rl < D; rl++) {
-                    double sacc = BROW(rl, 0) * Gall[0];
+                    double sacc = (KEEP ? Br[KEEP ? rl : 0][0] : BROW(rl, 0)) * Gall[0];
 #pragma unroll
-                    for (int c = 1; c < n; c++) sacc += BROW(rl, c) * Gall[c];
+                    for (int c = 1; c < n; c++) sacc += (KEEP ? Br[KEEP ? rl : 0][KEEP ? c : 0] : BROW(rl, c)) * Gall[c];
                     pk[rl] = -sacc;
                 }
             }
@@ -756,9 +765,9 @@ __global__ void __launch_bounds__(WPB * 32, MINB) k_prox_q(const __grid_constant
                 all_of(yk, Yall);
 #pragma unroll
                 for (int rl = 0; rl < D; rl++) {
-                    double sacc = BROW(rl, 0) * Yall[0];
+                    double sacc = (KEEP ? Br[KEEP ? rl : 0][0] : BROW(rl, 0)) * Yall[0];
 #pragma unroll
-                    for (int c = 1; c < n; c++) sacc += BROW(rl, c) * Yall[c];
+                    for (int c = 1; c < n; c++) sacc += (KEEP ? Br[KEEP ? rl : 0][KEEP ? c : 0] : BROW(rl, c)) * Yall[c];
                     By[rl] = sacc;
                 }
 #pragma unroll
@@ -787,7 +796,12 @@ __global__ void __launch_bounds__(WPB * 32, MINB) k_prox_q(const __grid_constant
 #pragma unroll
                         for (int c = 0; c < n; c++) {
                             double *bp = const_cast<double *>(&BROW(rl, c));
-                            *bp += (a1 * Pall[c] - a2 * Pall[c]) - a3 * YBall[c];
+                            if (KEEP) {
+                                Br[KEEP ? rl : 0][KEEP ? c : 0] += (a1 * Pall[c] - a2 * Pall[c]) - a3 * YBall[c];
+                                *bp = Br[KEEP ? rl : 0][KEEP ? c : 0];
+                            } else {
+                                *bp += (a1 * Pall[c] - a2 * Pall[c]) - a3 * YBall[c];
+                            }
                         }
                     }
                     iters = iter + 1;
@@ -2779,12 +2793,12 @@ template <> int launch_prox<2>(mmadmm_ctx *ctx, const ElemArgs<2> &a) {
         default: return launch_prox_p<2, 2, 6, PF_PREFETCH_GRID>(ctx, a, 0);
     }
 }
-template <int WPB, int MINB> int launch_prox_q(mmadmm_ctx *ctx, const ElemArgs<3> &a, int slot) {
+template <int WPB, int MINB, bool KEEP = false> int launch_prox_q(mmadmm_ctx *ctx, const ElemArgs<3> &a, int slot) {
     const bool iso = a.mg.iso != nullptr;
     const size_t warpBytes = ((size_t)(144 * SUB3 + (ctx->compMesh ? 4 : 3) * 3 * 32) * 8 + 2 * 32 * 4 + 16 + 127) / 128 * 128;
     const size_t smem = warpBytes * WPB;
-    auto kern = ctx->compMesh ? (iso ? k_prox_q<true, true, WPB, MINB> : k_prox_q<true, false, WPB, MINB>)
-                              : (iso ? k_prox_q<false, true, WPB, MINB> : k_prox_q<false, false, WPB, MINB>);
+    auto kern = ctx->compMesh ? (iso ? k_prox_q<true, true, WPB, MINB, KEEP> : k_prox_q<true, false, WPB, MINB, KEEP>)
+                              : (iso ? k_prox_q<false, true, WPB, MINB, KEEP> : k_prox_q<false, false, WPB, MINB, KEEP>);
     if (!ctx->smemAttrSet[slot + (iso ? 8 : 0)]) {
         CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         ctx->smemAttrSet[slot + (iso ? 8 : 0)] = true;
@@ -2799,6 +2813,9 @@ template <> int launch_prox<3>(mmadmm_ctx *ctx, const ElemArgs<3> &a) {
     switch (ctx->proxVariant) {
         case 1: return launch_prox_q<2, 6>(ctx, a, 1);         // 2-warp CTAs
         case 2: return launch_prox_q<4, 4>(ctx, a, 2);         // 16 warps per SM at 128 registers
+        case 3: return launch_prox_q<4, 2, true>(ctx, a, 3);   // own B rows in registers, 8 warps per SM (255 registers)
+        case 4: return launch_prox_q<2, 5, true>(ctx, a, 4);   // own B rows in registers, 10 warps per SM (204 registers)
+        case 5: return launch_prox_q<4, 3, true>(ctx, a, 5);   // own B rows in registers, 12 warps per SM (168 registers)
         default: return launch_prox_q<4, 3>(ctx, a, 0);        // 12 warps per SM
     }
 }
