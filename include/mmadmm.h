@@ -279,6 +279,8 @@ int mmadmm_pcg_refactor_device(mmadmm_pcg *h, const double *val_dev);
  * "tri_schedule" = row_block | tri_layout << 8 | (tri_mode + 1) << 12 sets the three at once (one rebuild of the schedules;
  * bits 12-13 zero = keep tri_mode).  "tri_proxy" 1: the block dataflow kernel lets a waiting warp poll through one lane first
  * (default 0).  "tri_sf_ctas_per_sm_x2" (1..8, default 2): CTAs of the dataflow kernels = SMs x value / 2.
+ * "ilu_thread_kernel" 1: the ILU(0) factor kernel with a thread per row even where the warp-per-row form fits (rows of at
+ * most 64 entries); same bits (tests).
  * The copies cost memory: chunk-major factor copy = (values 8 B + source index 4 B) per stored entry + padding, once per
  * triangular factor (C2-size Method 2 Jacobian, 58.7 M entries: about 1.3 GB next to the 0.7 GB of CSR values and indices).
  * All modes and layouts run every row's FMA chain in ascending column order: results are bit-identical.

@@ -233,6 +233,44 @@ __global__ void __launch_bounds__(TPB) k_ilu_level(int lo, int hi, const int *__
     }
     if (lu[dp] == 0.0) *flag = 1;
 }
+// The same factorisation with a WARP per row (rows of at most 64 stored entries): the row lives in registers, two entries per
+// lane; for every L entry k in turn the pivot row's U part is read coalesced and matched against the row by shuffles, so a row
+// costs two dependent round trips per L entry instead of two per (L entry, U entry) pair.  Every stored entry still receives its
+// updates in ascending k with separately rounded multiply and subtract: same bits as k_ilu_level and as the host factor.
+__global__ void __launch_bounds__(TPB) k_ilu_level_warp(int lo, int hi, const int *__restrict__ rows, const int *__restrict__ rowptr,
+                                                         const int *__restrict__ col, const int *__restrict__ diagPos, double *lu, int *flag) {
+    const int lane = threadIdx.x & 31;
+    const int t = lo + (blockIdx.x * TPB + threadIdx.x) / 32;
+    if (t >= hi) return;
+    const int i = rows[t], r0 = rowptr[i], len = rowptr[i + 1] - r0, dpl = diagPos[i] - r0;
+    int c0 = lane < len ? col[r0 + lane] : 0x7fffffff, c1 = lane + 32 < len ? col[r0 + lane + 32] : 0x7fffffff;
+    double v0 = lane < len ? lu[r0 + lane] : 0.0, v1 = lane + 32 < len ? lu[r0 + lane + 32] : 0.0;
+    for (int k = 0; k < dpl; k++) {
+        const int ck = __shfl_sync(0xffffffffu, k < 32 ? c0 : c1, k & 31);
+        const double vk = __shfl_sync(0xffffffffu, k < 32 ? v0 : v1, k & 31);
+        const int dc = diagPos[ck], ce = rowptr[ck + 1];
+        const double piv = lu[dc];
+        if (piv == 0.0) { if (lane == 0) *flag = 1; return; }
+        const double lik = vk / piv;
+        if (lane == (k & 31)) { if (k < 32) v0 = lik; else v1 = lik; }
+        for (int base = dc + 1; base < ce; base += 32) {
+            const int kk = base + lane;
+            const int cu = kk < ce ? col[kk] : -1;
+            const double vu = kk < ce ? lu[kk] : 0.0;
+            const int cnt = min(32, ce - base);
+            for (int j = 0; j < cnt; j++) {
+                const int cj = __shfl_sync(0xffffffffu, cu, j);
+                const double vj = __shfl_sync(0xffffffffu, vu, j);
+                if (c0 == cj) v0 = __dsub_rn(v0, __dmul_rn(lik, vj));
+                if (c1 == cj) v1 = __dsub_rn(v1, __dmul_rn(lik, vj));
+            }
+        }
+    }
+    if (lane < len) lu[r0 + lane] = v0;
+    if (lane + 32 < len) lu[r0 + lane + 32] = v1;
+    const double dv = __shfl_sync(0xffffffffu, dpl < 32 ? v0 : v1, dpl & 31);
+    if (dv == 0.0 && lane == 0) *flag = 1;
+}
 __global__ void k_inv_diag(int n, const int *__restrict__ diagPos, const double *__restrict__ val, double *invDiag) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n) invDiag[i] = 1.0 / val[diagPos[i]];   // Eigen's DiagonalPreconditioner stores 1/diag
@@ -805,6 +843,30 @@ __global__ void __launch_bounds__(TC_THREADS) k_tri_sf_block(int n, int nChunks,
     }
 }
 
+// Index planes of the block form of the chunk-major factor copy, built on the device (the host only lays out chunks): for the
+// group of (chunk, lane) the neighbour planes (first column of every neighbour block on this side) and, per value slot, the
+// position of its entry in the CSR factor (what k_lell_fill gathers from).  Pads keep the -1 of the memset.
+__global__ void k_chell_block_fill(int nChunks, int bs, int lower, const longlong2 *__restrict__ meta, const int *__restrict__ items,
+                                   const int *__restrict__ rp, const int *__restrict__ cl, int *nbr, int *src) {
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= nChunks * 32) return;
+    const int c = t >> 5, r = t & 31, b = items[t];
+    if (b < 0) return;
+    const longlong2 mt = meta[c];
+    const size_t oV = (size_t)mt.x + r, oI = (size_t)(mt.y >> 8) + r;
+    const int BB = bs * bs, r0 = rp[b], nblk = (rp[b + 1] - r0) / bs;
+    int p = 0;
+    while (cl[r0 + p * bs] != b) p++;
+    const int cnt = lower ? p : nblk - p - 1, first = lower ? 0 : p + 1;
+    for (int rr = 0; rr < bs; rr++)
+        for (int cc = 0; cc < bs; cc++) src[oV + (size_t)(rr * bs + cc) * 32] = rp[b + rr] + p * bs + cc;
+    for (int q = 0; q < cnt; q++) {
+        nbr[oI + (size_t)q * 32] = cl[r0 + (first + q) * bs];
+        for (int rr = 0; rr < bs; rr++)
+            for (int cc = 0; cc < bs; cc++) src[oV + (size_t)(BB * (1 + q) + rr * bs + cc) * 32] = rp[b + rr] + (first + q) * bs + cc;
+    }
+}
+
 // scal layout (device doubles): 0 rz, 1 pAp, 2 alpha, 3 beta, 4 rr, 5 rzNew, 6 bb
 enum { S_RZ = 0, S_PAP = 1, S_ALPHA = 2, S_BETA = 3, S_RR = 4, S_RZNEW = 5, S_BB = 6, S_COUNT = 8 };
 
@@ -952,6 +1014,10 @@ struct mmadmm_pcg {
         std::vector<int4> meta;
     } lellL, lellU;
     std::vector<int> diagPos_h;
+    int iluThreadKernel = 0;                      // "ilu_thread_kernel" 1: thread-per-row factor kernel even where the warp form fits (tests)
+    int maxRowLen = 0;                            // longest row (stored entries): <= 64 -> warp-per-row ILU(0) factor kernel
+    std::vector<int> rowsL_h;                     // rows in lower-level order (host), for the deferred part of the row schedule
+    bool rowSchedule = false;                     // ensure_row_schedule has run
     bool valHostStale = false;                    // val_h older than the device values (after mmadmm_pcg_refactor_device)
     int spmvFormat = 0;                           // 0: CSR, sub-warp per row; 1: SELL-32-4096 (built on first use)
     int nSlices = 0;
@@ -1062,7 +1128,8 @@ int ilu_factor_device(mmadmm_pcg *h) {
     const int nlev = (int)h->lvlL.size() - 1;
     for (int l = 0; l < nlev; l++) {   // (level 0 rows have no entries left of the diagonal: only their pivot is checked)
         const int lo = h->lvlL[l], hi = h->lvlL[l + 1];
-        k_ilu_level<<<cdiv(hi - lo, TPB), TPB, 0, h->stream>>>(lo, hi, h->rowsL, h->rowptr, h->col, h->diagPos, h->lu, h->flag_d);
+        if (h->maxRowLen <= 64 && !h->iluThreadKernel) k_ilu_level_warp<<<cdiv((size_t)(hi - lo) * 32, TPB), TPB, 0, h->stream>>>(lo, hi, h->rowsL, h->rowptr, h->col, h->diagPos, h->lu, h->flag_d);
+        else k_ilu_level<<<cdiv(hi - lo, TPB), TPB, 0, h->stream>>>(lo, hi, h->rowsL, h->rowptr, h->col, h->diagPos, h->lu, h->flag_d);
         h->launches++;
     }
     int flag = 0;
@@ -1071,6 +1138,46 @@ int ilu_factor_device(mmadmm_pcg *h) {
     PCK(cudaGetLastError());
     if (flag) { h->err = "zero pivot in ILU(0)"; return MMADMM_ESINGULAR; }
     return lell_refresh(h);
+}
+
+// The part of the row-per-thread schedule that only tri_mode 0 / 1 with row_block 1 read (mmadmm_pcg_create builds just what
+// the factorisation needs): upper levels and rows in upper-level order, row extents in level order, level offsets on the device.
+int ensure_row_schedule(mmadmm_pcg *h) {
+    if (h->rowSchedule || h->precond != 1) return MMADMM_OK;
+    const int n = h->n;
+    const std::vector<int> &rp = h->rowptr_h, &cl = h->col_h, &dg = h->diagPos_h, &rowsL = h->rowsL_h;
+    PCK(cudaSetDevice(h->device));
+    std::vector<int> lev(n, 0), rowsU(n);
+    int nu = 0;
+    for (int i = n - 1; i >= 0; i--) {
+        int l = 0;
+        for (int k = dg[i] + 1; k < rp[i + 1]; k++) l = std::max(l, lev[cl[k]] + 1);
+        lev[i] = l; nu = std::max(nu, l + 1);
+    }
+    h->lvlU.assign(nu + 1, 0);
+    for (int i = 0; i < n; i++) h->lvlU[lev[i] + 1]++;
+    for (int l = 0; l < nu; l++) h->lvlU[l + 1] += h->lvlU[l];
+    {
+        std::vector<int> cur(h->lvlU.begin(), h->lvlU.end() - 1);
+        for (int i = 0; i < n; i++) rowsU[cur[lev[i]]++] = i;
+    }
+    std::vector<int2> eL(n), eU(n);
+    for (int t = 0; t < n; t++) {
+        eL[t] = make_int2(rp[rowsL[t]], dg[rowsL[t]]);
+        eU[t] = make_int2(dg[rowsU[t]] + 1, rp[rowsU[t] + 1]);
+    }
+    auto up = [&](void **dst, const void *src, size_t bytes) -> cudaError_t {
+        cudaError_t e = cudaMalloc(dst, std::max<size_t>(bytes, 8));
+        return e != cudaSuccess ? e : cudaMemcpy(*dst, src, bytes, cudaMemcpyHostToDevice);
+    };
+    PCK(up((void **)&h->rowsU, rowsU.data(), sizeof(int) * (size_t)n));
+    PCK(up((void **)&h->kbeL, eL.data(), sizeof(int2) * (size_t)n));
+    PCK(up((void **)&h->kbeU, eU.data(), sizeof(int2) * (size_t)n));
+    PCK(up((void **)&h->lvlL_d, h->lvlL.data(), sizeof(int) * h->lvlL.size()));
+    PCK(up((void **)&h->lvlU_d, h->lvlU.data(), sizeof(int) * h->lvlU.size()));
+    PCK(cudaDeviceSynchronize());   // pageable uploads must have landed before h->stream (non-blocking) reads them
+    h->rowSchedule = true;
+    return MMADMM_OK;
 }
 
 // ---- host-side planning of the group schedules (no device needed: mmadmm_pcg_plan_levels, tests/test_pcg_plan.py) ----
@@ -1320,34 +1427,23 @@ int build_groups(mmadmm_pcg *h, int bs) {
             slotsV += (size_t)BB * (1 + m) * 32;
             slotsI += (size_t)m * 32;
         }
-        std::vector<int> nbrv(std::max<size_t>(slotsI, 1), -1), srcv(slotsV, -1);
-#pragma omp parallel for schedule(static)
-        for (int c = 0; c < nChunks; c++) {   // chunks own disjoint slots
-            for (int r = 0; r < 32; r++) {
-                const int b = items[(size_t)c * 32 + r];
-                if (b < 0) continue;
-                const size_t oV = (size_t)meta[c].x + r, oI = (size_t)(meta[c].y >> 8) + r;
-                const int p = ownPos(b), cnt = nNbr(b), first = lower ? 0 : p + 1;
-                for (int rr = 0; rr < bs; rr++)
-                    for (int cc = 0; cc < bs; cc++) srcv[oV + (size_t)(rr * bs + cc) * 32] = rp[b + rr] + p * bs + cc;
-                for (int q = 0; q < cnt; q++) {
-                    nbrv[oI + (size_t)q * 32] = cl[rp[b] + (first + q) * bs];
-                    for (int rr = 0; rr < bs; rr++)
-                        for (int cc = 0; cc < bs; cc++) srcv[oV + (size_t)(BB * (1 + q) + rr * bs + cc) * 32] = rp[b + rr] + (first + q) * bs + cc;
-                }
-            }
-        }
         L.slots = slotsV; L.nChunks = nChunks; L.blocked = true;
+        const size_t nI = std::max<size_t>(slotsI, 1), nV = std::max<size_t>(slotsV, 1);
         cudaError_t er;
         if ((er = cudaMalloc(&L.meta_d, sizeof(longlong2) * std::max<size_t>(meta.size(), 1))) != cudaSuccess) return er;
         if ((er = cudaMalloc(&L.items, sizeof(int) * std::max<size_t>(items.size(), 1))) != cudaSuccess) return er;
-        if ((er = cudaMalloc(&L.col, sizeof(int) * nbrv.size())) != cudaSuccess) return er;
-        if ((er = cudaMalloc(&L.src, sizeof(int) * std::max<size_t>(slotsV, 1))) != cudaSuccess) return er;
-        if ((er = cudaMalloc(&L.val, sizeof(double) * std::max<size_t>(slotsV, 1))) != cudaSuccess) return er;
+        if ((er = cudaMalloc(&L.col, sizeof(int) * nI)) != cudaSuccess) return er;
+        if ((er = cudaMalloc(&L.src, sizeof(int) * nV)) != cudaSuccess) return er;
+        if ((er = cudaMalloc(&L.val, sizeof(double) * nV)) != cudaSuccess) return er;
         if ((er = cudaMemcpy(L.meta_d, meta.data(), sizeof(longlong2) * meta.size(), cudaMemcpyHostToDevice)) != cudaSuccess) return er;
         if ((er = cudaMemcpy(L.items, items.data(), sizeof(int) * items.size(), cudaMemcpyHostToDevice)) != cudaSuccess) return er;
-        if ((er = cudaMemcpy(L.col, nbrv.data(), sizeof(int) * nbrv.size(), cudaMemcpyHostToDevice)) != cudaSuccess) return er;
-        return cudaMemcpy(L.src, srcv.data(), sizeof(int) * slotsV, cudaMemcpyHostToDevice);
+        if ((er = cudaDeviceSynchronize()) != cudaSuccess) return er;   // pageable uploads landed before h->stream reads them
+        // the index planes (0.2 GB per factor at C2 size) are written by the device, not filled on the host and uploaded
+        if ((er = cudaMemsetAsync(L.col, 0xFF, sizeof(int) * nI, h->stream)) != cudaSuccess) return er;
+        if ((er = cudaMemsetAsync(L.src, 0xFF, sizeof(int) * nV, h->stream)) != cudaSuccess) return er;
+        k_chell_block_fill<<<cdiv((size_t)nChunks * 32, TPB), TPB, 0, h->stream>>>(nChunks, bs, lower ? 1 : 0, L.meta_d, L.items, h->rowptr, h->col, L.col, L.src);
+        h->launches++;
+        return cudaGetLastError();
     };
     SetupTimer tg("build_groups");
     const bool useBlocks = h->triMode == 2 && h->sfBlocks && plan_blockable(n, bs, rp.data(), cl.data());
@@ -1483,17 +1579,19 @@ template <int BS, int CACHE> void apply_ilu_blk(mmadmm_pcg *h, const double *r, 
 }
 
 // z = (LU)^{-1} r by level-scheduled forward and backward substitution
-void apply_ilu(mmadmm_pcg *h, const double *r, double *z) {
+int apply_ilu(mmadmm_pcg *h, const double *r, double *z) {
     switch (h->grpL ? h->rowBlock : 0) {
-        case 1: apply_ilu_blk<1, 14>(h, r, z); return;
-        case 2: apply_ilu_blk<2, 14>(h, r, z); return;
-        case 3: apply_ilu_blk<3, 10>(h, r, z); return;
-        case 4: apply_ilu_blk<4, 8>(h, r, z); return;
-        case 6: apply_ilu_blk<6, 5>(h, r, z); return;
+        case 1: apply_ilu_blk<1, 14>(h, r, z); return MMADMM_OK;
+        case 2: apply_ilu_blk<2, 14>(h, r, z); return MMADMM_OK;
+        case 3: apply_ilu_blk<3, 10>(h, r, z); return MMADMM_OK;
+        case 4: apply_ilu_blk<4, 8>(h, r, z); return MMADMM_OK;
+        case 6: apply_ilu_blk<6, 5>(h, r, z); return MMADMM_OK;
         default: break;
     }
+    { int rc = ensure_row_schedule(h); if (rc) return rc; }
     tri_solve<true>(h, h->lvlL, h->lvlL_d, h->rowsL, h->kbeL, r, h->tmp);
     tri_solve<false>(h, h->lvlU, h->lvlU_d, h->rowsU, h->kbeU, h->tmp, z);
+    return MMADMM_OK;
 }
 
 }  // namespace
@@ -1543,6 +1641,7 @@ int mmadmm_pcg_create(int n, const int *rowptr, const int *col, const double *va
             if (col[k] == i) diagPos[i] = k;
         }
         if (diagPos[i] < 0) { h->err = "every row needs a stored diagonal entry"; return MMADMM_EINVAL; }
+        h->maxRowLen = std::max(h->maxRowLen, rowptr[i + 1] - rowptr[i]);
     }
     tm.lap("host copies + pattern check");
     const double avg = (double)nnz / n;
@@ -1582,31 +1681,14 @@ int mmadmm_pcg_create(int n, const int *rowptr, const int *col, const double *va
             for (int i = 0; i < n; i++) rows[cur[lev[i]]++] = i;
         };
         bucket(nl, rowsL, h->lvlL);
-        int nu = 0;
-        for (int i = n - 1; i >= 0; i--) {
-            int l = 0;
-            for (int k = diagPos[i] + 1; k < rowptr[i + 1]; k++) l = std::max(l, lev[col[k]] + 1);
-            lev[i] = l; nu = std::max(nu, l + 1);
-        }
-        bucket(nu, rowsU, h->lvlU);
         PCK(up((void **)&h->lu, nullptr, sizeof(double) * (size_t)nnz));
         PCK(up((void **)&h->flag_d, nullptr, sizeof(int)));
         PCK(up((void **)&h->rowsL, rowsL.data(), sizeof(int) * (size_t)n));
-        PCK(up((void **)&h->rowsU, rowsU.data(), sizeof(int) * (size_t)n));
-        {
-            std::vector<int2> eL(n), eU(n);
-            for (int t = 0; t < n; t++) {
-                eL[t] = make_int2(rowptr[rowsL[t]], diagPos[rowsL[t]]);
-                eU[t] = make_int2(diagPos[rowsU[t]] + 1, rowptr[rowsU[t] + 1]);
-            }
-            PCK(up((void **)&h->kbeL, eL.data(), sizeof(int2) * (size_t)n));
-            PCK(up((void **)&h->kbeU, eU.data(), sizeof(int2) * (size_t)n));
-            PCK(cudaStreamSynchronize(h->stream));   // eL / eU go out of scope
-        }
-        PCK(up((void **)&h->lvlL_d, h->lvlL.data(), sizeof(int) * h->lvlL.size()));
-        PCK(up((void **)&h->lvlU_d, h->lvlU.data(), sizeof(int) * h->lvlU.size()));
+        // the rest of the row-per-thread schedule (upper levels, row extents in level order, level offsets on the device) is only
+        // read by tri_mode 0 / 1 with row_block 1: built on first use (ensure_row_schedule)
         tm.lap("level schedules + uploads");
-        PCK(cudaStreamSynchronize(h->stream));   // rowsL / rowsU are locals
+        PCK(cudaStreamSynchronize(h->stream));   // rowsL is a local
+        h->rowsL_h.swap(rowsL);
         { int rcf = ilu_factor_device(h); if (rcf) return rcf; }   // the numeric factor runs on the device, level by level
         tm.lap("device ILU(0) factor");
     }
@@ -1644,6 +1726,7 @@ int mmadmm_pcg_set_option(mmadmm_pcg *h, const char *name, int value) {
         }
         return MMADMM_OK;
     }
+    if (!std::strcmp(name, "ilu_thread_kernel")) { h->iluThreadKernel = value ? 1 : 0; return MMADMM_OK; }
     if (!std::strcmp(name, "tri_proxy")) { h->sfProxy = value ? 1 : 0; return MMADMM_OK; }
     if (!std::strcmp(name, "tri_sf_ctas_per_sm_x2")) { if (value < 1 || value > 8) return MMADMM_EINVAL; h->sfGridX2 = value; return MMADMM_OK; }
     if (!std::strcmp(name, "tri_blocks")) {   // 1 (default): block form of the dataflow solve where the pattern is made of BS x BS blocks
@@ -1710,7 +1793,8 @@ int mmadmm_pcg_set_option(mmadmm_pcg *h, const char *name, int value) {
 int mmadmm_pcg_info(mmadmm_pcg *h, int *info4) {
     if (!h || !info4) return MMADMM_EINVAL;
     info4[0] = h->lanes;
-    const std::vector<int> &lL = h->rowBlock > 1 ? h->lvlGL : h->lvlL, &lU = h->rowBlock > 1 ? h->lvlGU : h->lvlU;
+    if (!h->grpL) { int rc = ensure_row_schedule(h); if (rc) return rc; }   // the upper row levels are built on first use
+    const std::vector<int> &lL = h->grpL ? h->lvlGL : h->lvlL, &lU = h->grpL ? h->lvlGU : h->lvlU;
     info4[1] = (int)lL.size() > 0 ? (int)lL.size() - 1 : 0;
     info4[2] = (int)lU.size() > 0 ? (int)lU.size() - 1 : 0;
     info4[3] = (int)std::min<long long>(h->launches, 2147483647LL);
@@ -1732,7 +1816,7 @@ int mmadmm_pcg_precond(mmadmm_pcg *h, const double *r, double *z) {
     if (!h || !r || !z) return MMADMM_EINVAL;
     PCK(cudaSetDevice(h->device));
     PCK(cudaMemcpyAsync(h->r, r, sizeof(double) * (size_t)h->n, cudaMemcpyHostToDevice, h->stream));
-    if (h->precond == 1) apply_ilu(h, h->r, h->z);
+    if (h->precond == 1) { int rca = apply_ilu(h, h->r, h->z); if (rca) return rca; }
     else { k_jacobi<<<cdiv(h->n, TPB), TPB, 0, h->stream>>>(h->n, h->r, h->invDiag, h->z); h->launches++; }
     PCK(cudaMemcpyAsync(z, h->z, sizeof(double) * (size_t)h->n, cudaMemcpyDeviceToHost, h->stream));
     PCK(cudaStreamSynchronize(h->stream));
@@ -1778,7 +1862,7 @@ int mmadmm_pcg_solve_device(mmadmm_pcg *h, const double *b_dev, double *x_dev, d
     PCK(cudaMemsetAsync(x_dev, 0, vb, st));
     PCK(cudaMemcpyAsync(h->r, b_dev, vb, cudaMemcpyDeviceToDevice, st));   // r = b - A*0
     // z = M^{-1} r ; rz, rr(=bb)
-    if (h->precond == 1) apply_ilu(h, h->r, h->z);
+    if (h->precond == 1) { int rca = apply_ilu(h, h->r, h->z); if (rca) return rca; }
     else k_jacobi<<<g, TPB, 0, st>>>(n, h->r, h->invDiag, h->z);
     k_dot2<<<g, TPB, 0, st>>>(n, h->r, h->z, h->r, h->part0, h->part1);
     k_scalars<<<1, 1024, 0, st>>>(g, h->part0, h->part1, h->scal, 2);
@@ -1797,7 +1881,7 @@ int mmadmm_pcg_solve_device(mmadmm_pcg *h, const double *b_dev, double *x_dev, d
         k_scalars<<<1, 1024, 0, st>>>(spmv_parts(h), h->part0, nullptr, h->scal, 0);   // alpha = rz / pAp
         if (h->precond == 1) {
             k_cg_update<false><<<g, TPB, 0, st>>>(n, h->scal, h->p, h->q, h->invDiag, x_dev, h->r, h->z, h->part0, h->part1);
-            apply_ilu(h, h->r, h->z);
+            { int rca = apply_ilu(h, h->r, h->z); if (rca) return rca; }
             k_dot2<<<g, TPB, 0, st>>>(n, h->r, h->z, h->r, h->part0, h->part1);
             h->launches++;
         } else {
@@ -1866,13 +1950,13 @@ int mmadmm_pcg_bicgstab_device(mmadmm_pcg *h, const double *b_dev, double *x_dev
         beta *= (alpha / (omega + tiny));
         rholst = rho;
         k_bi_p<<<g, TPB, 0, st>>>(n, beta, omega, res, avbar, pvec);
-        apply_ilu(h, pvec, vbar);
+        { int rca = apply_ilu(h, pvec, vbar); if (rca) return rca; }
         launch_spmv(h, vbar, avbar, nullptr);
         double r0av, dummy2;
         PCK(dots(res0, avbar, avbar, &r0av, &dummy2));
         alpha = rho / r0av;
         k_bi_s<<<g, TPB, 0, st>>>(n, alpha, res, avbar, svec);
-        apply_ilu(h, svec, zvec);
+        { int rca = apply_ilu(h, svec, zvec); if (rca) return rca; }
         launch_spmv(h, zvec, tvec, nullptr);
         double ts, tt;
         PCK(dots(tvec, svec, tvec, &ts, &tt));
@@ -1941,13 +2025,15 @@ int mmadmm_pcg_time_precond(mmadmm_pcg *h, int reps, double *ms) {
     cudaEvent_t e0, e1;
     PCK(cudaEventCreate(&e0)); PCK(cudaEventCreate(&e1));
     PCK(cudaMemsetAsync(h->r, 0, sizeof(double) * (size_t)h->n, h->stream));
-    auto apply = [&]() {
-        if (h->precond == 1) apply_ilu(h, h->r, h->z);
-        else { k_jacobi<<<cdiv(h->n, TPB), TPB, 0, h->stream>>>(h->n, h->r, h->invDiag, h->z); h->launches++; }
+    auto apply = [&]() -> int {
+        if (h->precond == 1) return apply_ilu(h, h->r, h->z);
+        k_jacobi<<<cdiv(h->n, TPB), TPB, 0, h->stream>>>(h->n, h->r, h->invDiag, h->z);
+        h->launches++;
+        return MMADMM_OK;
     };
-    apply();
+    { int rca = apply(); if (rca) return rca; }
     PCK(cudaEventRecord(e0, h->stream));
-    for (int k = 0; k < reps; k++) apply();
+    for (int k = 0; k < reps; k++) { int rca = apply(); if (rca) return rca; }
     PCK(cudaEventRecord(e1, h->stream));
     PCK(cudaStreamSynchronize(h->stream));
     PCK(cudaGetLastError());

@@ -104,6 +104,10 @@ def test_device_ilu0_factor_and_refactor_are_bit_identical_to_the_host_factor(D,
     s.refactor_device(v.data_ptr())
     lu2, _ = PO.ilu0(A2)
     assert np.array_equal(s.ilu(), lu2)
+    s.set_option("ilu_thread_kernel", 1)                                # the thread-per-row factor kernel (rows longer than 64 entries
+    s.refactor_device(v.data_ptr())                                    # take it by themselves): same bits as the warp-per-row one
+    assert np.array_equal(s.ilu(), lu2)
+    s.set_option("ilu_thread_kernel", 0)
     fresh = mm.PCG(A2.indptr, A2.indices, A2.data, "ilu0")
     r = rng.standard_normal(n)
     assert np.array_equal(s.precond(r), fresh.precond(r))
