@@ -124,6 +124,14 @@ def test_device_ilu0_factor_and_refactor_are_bit_identical_to_the_host_factor(D,
         s.set_option("row_block", bs)
         assert np.array_equal(s.precond(-r), -zf)
         assert np.array_equal(s.precond(r), zf)
+    s.set_option("tri_mode", 2)                                        # ... and the chunk-major copies of the dataflow solve
+    for bs, blocks in ((1, 1), (2, 1), (D, 1), (D, 0), (4, 1)):        # (generic form and, where bs = D fits the pattern, block form)
+        s.set_option("tri_blocks", blocks)
+        s.set_option("row_block", bs)
+        assert np.array_equal(s.precond(-r), -zf)
+        assert np.array_equal(s.precond(r), zf)
+    s.set_option("tri_blocks", 1)
+    s.set_option("row_block", D)                                       # stays on for the re-factorisation below
     z0 = mm.PCG(A.indptr, A.indices, A.data, "ilu0")
     zA = z0.precond(r); z0.close()
     s.set_option("spmv_format", 1)                                     # the SELL copy is rebuilt from refreshed values
