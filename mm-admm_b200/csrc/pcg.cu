@@ -704,7 +704,7 @@ template <int BS> __device__ __forceinline__ bool group_ready(const double (&v)[
     return ok;
 }
 template <bool LOWER, int BS, int NBC>
-__global__ void __launch_bounds__(TC_THREADS) k_tri_sf_block(int n, int nChunks, const longlong2 *__restrict__ meta, const int *__restrict__ items,
+__global__ void __launch_bounds__(TC_THREADS, 1) k_tri_sf_block(int n, int nChunks, const longlong2 *__restrict__ meta, const int *__restrict__ items,
                                                             const int *__restrict__ nbrT, const double *__restrict__ valT,
                                                             const double *__restrict__ rhs, double *out, unsigned *counter, int proxy
 #ifdef MMADMM_TRI_PROF
@@ -745,18 +745,13 @@ __global__ void __launch_bounds__(TC_THREADS) k_tri_sf_block(int n, int nChunks,
         }
         // operands that have been there for a long time: one batch now, while nobody waits for this chunk
         // (all requests are issued before any result is looked at: one round trip for the batch, not one per neighbour)
-        {
-            double v[NBC][BS];
+        {   // (straight into the operand registers: a group that is not complete yet is simply requested again)
 #pragma unroll
             for (int q = 0; q < NBC; q++)
-                if ((need & (1u << q)) && !(pmode & 4)) ld_group_raw<BS>(out + nb[q], v[q]);
+                if ((need & (1u << q)) && !(pmode & 4)) ld_group_raw<BS>(out + nb[q], o[q]);
 #pragma unroll
             for (int q = 0; q < NBC; q++)
-                if ((need & (1u << q)) && !(pmode & 4) && group_ready<BS>(v[q])) {
-#pragma unroll
-                    for (int k = 0; k < BS; k++) o[q][k] = v[q][k];
-                    need &= ~(1u << q);
-                }
+                if ((need & (1u << q)) && !(pmode & 4) && group_ready<BS>(o[q])) need &= ~(1u << q);
         }
         // optional ("tri_proxy" 1): a far-ahead warp waits through ONE lane polling ONE neighbour (see k_tri_syncfree).  Off by
         // default here: with one 16-byte request per lane per round trip the polls of all waiting warps together stay far
@@ -784,17 +779,12 @@ __global__ void __launch_bounds__(TC_THREADS) k_tri_sf_block(int n, int nChunks,
         // lanes that wait for different neighbour slots: measured 0.51 us per poll instead of the 0.19 us of one relaxed load)
         SF_STAMP(2);
         for (int spins = 0; need; spins++) {
-            double v[NBC][BS];
 #pragma unroll
             for (int q = 0; q < NBC; q++)
-                if (need & (1u << q)) ld_group_raw<BS>(out + nb[q], v[q]);
+                if (need & (1u << q)) ld_group_raw<BS>(out + nb[q], o[q]);
 #pragma unroll
             for (int q = 0; q < NBC; q++)
-                if ((need & (1u << q)) && group_ready<BS>(v[q])) {
-#pragma unroll
-                    for (int k = 0; k < BS; k++) o[q][k] = v[q][k];
-                    need &= ~(1u << q);
-                }
+                if ((need & (1u << q)) && group_ready<BS>(o[q])) need &= ~(1u << q);
             if (spins > (1 << 24)) __trap();
 #ifdef MMADMM_TRI_PROF
             if (lane == 0 && chunk >= profLo && chunk < profLo + 65536) g_sf_spins[chunk - profLo] = spins + 1;
@@ -1519,10 +1509,10 @@ void tri_solve_blk(mmadmm_pcg *h, const std::vector<int> &lvl, const int *lvl_d,
             const int pl = (LOWER != (profU == 1)) ? profLoB : (1 << 30);
             static const int pmodeB = getenv("MMADMM_TRI_PROF_MODE") ? atoi(getenv("MMADMM_TRI_PROF_MODE")) : 0;
             if (BS == 2) k_tri_sf_block<LOWER, 2, 8><<<grid, TC_THREADS, 0, h->stream>>>(h->n, C.nChunks, C.meta_d, C.items, C.col, C.val, rhs, out, h->sfCounter, h->sfProxy, pl, pmodeB);
-            else k_tri_sf_block<LOWER, 3, 5><<<grid, TC_THREADS, 0, h->stream>>>(h->n, C.nChunks, C.meta_d, C.items, C.col, C.val, rhs, out, h->sfCounter, h->sfProxy, pl, pmodeB);
+            else k_tri_sf_block<LOWER, 3, 8><<<grid, TC_THREADS, 0, h->stream>>>(h->n, C.nChunks, C.meta_d, C.items, C.col, C.val, rhs, out, h->sfCounter, h->sfProxy, pl, pmodeB);
 #else
             if (BS == 2) k_tri_sf_block<LOWER, 2, 8><<<grid, TC_THREADS, 0, h->stream>>>(h->n, C.nChunks, C.meta_d, C.items, C.col, C.val, rhs, out, h->sfCounter, h->sfProxy);
-            else k_tri_sf_block<LOWER, 3, 5><<<grid, TC_THREADS, 0, h->stream>>>(h->n, C.nChunks, C.meta_d, C.items, C.col, C.val, rhs, out, h->sfCounter, h->sfProxy);
+            else k_tri_sf_block<LOWER, 3, 8><<<grid, TC_THREADS, 0, h->stream>>>(h->n, C.nChunks, C.meta_d, C.items, C.col, C.val, rhs, out, h->sfCounter, h->sfProxy);
 #endif
             h->launches += 2;
             return;
