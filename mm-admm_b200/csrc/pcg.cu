@@ -1500,8 +1500,7 @@ void tri_solve_blk(mmadmm_pcg *h, const std::vector<int> &lvl, const int *lvl_d,
     const mmadmm_pcg::Chell &C = LOWER ? h->chellL : h->chellU;
     if (h->triMode == 2 && C.nChunks > 0) {   // the whole solve: sentinel fill + one persistent launch
         k_tri_sf_prepare<<<cdiv(h->n, TPB), TPB, 0, h->stream>>>(h->n, out, h->sfCounter);
-        static const int gridEnv = getenv("MMADMM_SF_GRID") ? atoi(getenv("MMADMM_SF_GRID")) : 0;   // experiments
-        const int grid = gridEnv > 0 ? gridEnv : std::min(std::max(1, h->sfGrid * h->sfGridX2 / 2), cdiv(C.nChunks, TC_THREADS / 32));   // chunks are claimed dynamically: CTAs that are not resident at once are harmless
+        const int grid = std::min(std::max(1, h->sfGrid * h->sfGridX2 / 2), cdiv(C.nChunks, TC_THREADS / 32));   // chunks are claimed dynamically: CTAs that are not resident at once are harmless
         if (C.blocked) {
 #ifdef MMADMM_TRI_PROF
             static const int profLoB = getenv("MMADMM_SF_PROF_LO") ? atoi(getenv("MMADMM_SF_PROF_LO")) : 0;

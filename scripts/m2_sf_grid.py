@@ -1,4 +1,5 @@
-"""Dataflow triangular solve: device time of a preconditioner application for the grid size in MMADMM_SF_GRID (experiments)."""
+"""Dataflow triangular solve: device time of a preconditioner application per grid size (option tri_sf_ctas_per_sm_x2: CTAs = SMs x value / 2).
+(profiles/r02_al_dataflow_grid_sweep.jsonl was taken with an environment override of the CTA count, 8 ... 296, that the library no longer has.)"""
 import importlib, json, os, sys
 import numpy as np
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
@@ -13,4 +14,6 @@ solver = mm.MeshIntegrator(0.025, mesh)
 rowptr, col, val = solver.backward_euler_jacobian()
 pcg = mm.PCG(rowptr, col, val, precond="ilu0")
 pcg.set_option("tri_mode", 2); pcg.set_option("row_block", 2)
-print(json.dumps({"grid": os.environ.get("MMADMM_SF_GRID"), "pmode": os.environ.get("MMADMM_TRI_PROF_MODE"), "precond_ms_device": round(pcg.time_precond(5), 3)}))
+for x2 in (1, 2, 4):
+    pcg.set_option("tri_sf_ctas_per_sm_x2", x2)
+    print(json.dumps({"ctas_per_sm": x2 / 2, "pmode": os.environ.get("MMADMM_TRI_PROF_MODE"), "precond_ms_device": round(pcg.time_precond(5), 3)}))
