@@ -542,7 +542,7 @@ __device__ __forceinline__ unsigned long long gtimer() { unsigned long long t; a
 template <bool LOWER, int BS, int CACHE>
 __global__ void __launch_bounds__(TC_THREADS) k_tri_syncfree(int n, int nChunks, const longlong2 *__restrict__ meta, const int *__restrict__ items,
                                                             const int *__restrict__ colT, const double *__restrict__ valT,
-                                                            const double *__restrict__ rhs, double *out, unsigned *counter
+                                                            const double *__restrict__ rhs, double *out, unsigned *counter, int proxy
 #ifdef MMADMM_TRI_PROF
                                                             , int profLo
 #endif
@@ -582,19 +582,13 @@ __global__ void __launch_bounds__(TC_THREADS) k_tri_syncfree(int n, int nChunks,
                 if (c[j][q] >= 0 && !(g >= 0 && g < BS)) need |= 1u << (j * CACHE + q);
             }
         }
-        // Operands of other groups.  Warps run far ahead of the wavefront (that is what hides the DRAM latency of the factor), and
-        // a thousand waiting warps polling 28 operands x 32 lanes saturate L2 (measured: a level then costs 2-4 us).  So while a
-        // warp waits, ONE lane polls ONE operand for all of it -- the first lane that needs anything, the operand expected last
-        // (nearest row: highest column of an L row, lowest of a U row).  The lanes of a chunk belong to one level and their
-        // operands to the levels just before it, so when the proxy has arrived the rest is there or about to be: every lane then
-        // requests all its operands at once and re-requests only those that still read as the sentinel.  Correctness never
-        // rests on the proxy: every operand is checked by the lane that uses it.
-        {
-#ifdef MMADMM_TRI_PROF
-            { double acc = s[0]; for (int j = 0; j < BS; j++) for (int q = 0; q < CACHE; q++) if (c[j][q] >= 0) acc += a[j][q];
-              if (acc == 1.2345e-300) out[0] = acc; }   // the stamp below waits for the factor planes
-            SF_STAMP(1);
-#endif
+        // Operands of other groups: per round trip every lane requests ALL it still misses and only then looks at the results
+        // (requests tested one by one, or lanes of a warp waiting in different branches, serialise the round trips); what
+        // arrived stays in its register, the rest is requested again.  "tri_proxy" 1 puts a cheaper first stage in front for
+        // warps that run far ahead of the wavefront: ONE lane polls ONE operand (the nearest row: highest column of an L row,
+        // lowest of a U row) until it has arrived.
+        SF_STAMP(1);
+        if (proxy) {
             const unsigned waiting = __ballot_sync(0xffffffffu, need != 0u);
             if (waiting) {
                 if (lane == __ffs(waiting) - 1) {
@@ -606,50 +600,26 @@ __global__ void __launch_bounds__(TC_THREADS) k_tri_syncfree(int n, int nChunks,
                         for (int q = 0; q < CACHE; q++)
                             if (b == j * CACHE + q) p = out + c[j][q];
                     for (int spins = 0;; spins++) {
-                        const double v = ld_relaxed_gpu(p);
-                        if ((unsigned long long)__double_as_longlong(v) != TRI_SENTINEL) break;
-                        if (spins > (1 << 24)) __trap();   // no sleep: one load per round trip per warp is no load on L2, and a sleep
-                                                           // (granularity ~1 us) would sit on the critical path of every level
+                        if ((unsigned long long)__double_as_longlong(ld_relaxed_gpu(p)) != TRI_SENTINEL) break;
+                        if (spins > (1 << 24)) __trap();
                     }
                 }
                 __syncwarp();
             }
         }
         SF_STAMP(2);
-        // The wavefront is now a few levels away.  Every lane waits for ITS operand expected last with one load per round trip
-        // (a sweep over all 28 operands per poll costs a microsecond of LSU and L2 time per warp and made a level 3-5 us), then
-        // requests everything it still needs in one batch, then waits for the few stragglers one at a time.
-        for (bool swept = false; need;) {
-            const int b = LOWER ? 31 - __clz(need) : __ffs(need) - 1;
-            const double *p = out;
+        for (int spins = 0; need; spins++) {
 #pragma unroll
             for (int j = 0; j < BS; j++)
 #pragma unroll
                 for (int q = 0; q < CACHE; q++)
-                    if (b == j * CACHE + q) p = out + c[j][q];
-            double v;
-            for (int spins = 0;; spins++) {
-                v = ld_relaxed_gpu(p);
-                if ((unsigned long long)__double_as_longlong(v) != TRI_SENTINEL) break;
-                if (spins > (1 << 24)) __trap();
-            }
+                    if (need & (1u << (j * CACHE + q))) o[j][q] = ld_relaxed_gpu(out + c[j][q]);
 #pragma unroll
             for (int j = 0; j < BS; j++)
 #pragma unroll
                 for (int q = 0; q < CACHE; q++)
-                    if (b == j * CACHE + q) o[j][q] = v;
-            need &= ~(1u << b);
-            if (!swept) {
-                swept = true;
-#pragma unroll
-                for (int j = 0; j < BS; j++)
-#pragma unroll
-                    for (int q = 0; q < CACHE; q++)
-                        if (need & (1u << (j * CACHE + q))) {
-                            const double vv = ld_relaxed_gpu(out + c[j][q]);
-                            if ((unsigned long long)__double_as_longlong(vv) != TRI_SENTINEL) { o[j][q] = vv; need &= ~(1u << (j * CACHE + q)); }
-                        }
-            }
+                    if ((need & (1u << (j * CACHE + q))) && (unsigned long long)__double_as_longlong(o[j][q]) != TRI_SENTINEL) need &= ~(1u << (j * CACHE + q));
+            if (spins > (1 << 24)) __trap();
         }
         __syncwarp();
         SF_STAMP(3);
@@ -1519,10 +1489,10 @@ void tri_solve_blk(mmadmm_pcg *h, const std::vector<int> &lvl, const int *lvl_d,
 #ifdef MMADMM_TRI_PROF
         static const int profLo = getenv("MMADMM_SF_PROF_LO") ? atoi(getenv("MMADMM_SF_PROF_LO")) : 0;
         k_tri_syncfree<LOWER, BS, (BS * CACHE <= 32 ? CACHE : 32 / BS)><<<grid, TC_THREADS, 0, h->stream>>>(h->n, C.nChunks, C.meta_d, C.items, C.col, C.val, rhs, out,
-                                                                                                        h->sfCounter, LOWER ? profLo : (1 << 30));
+                                                                                                        h->sfCounter, h->sfProxy, LOWER ? profLo : (1 << 30));
 #else
         k_tri_syncfree<LOWER, BS, (BS * CACHE <= 32 ? CACHE : 32 / BS)><<<grid, TC_THREADS, 0, h->stream>>>(h->n, C.nChunks, C.meta_d, C.items, C.col, C.val, rhs, out,
-                                                                                                        h->sfCounter);
+                                                                                                        h->sfCounter, h->sfProxy);
 #endif
         h->launches += 2;
         return;
