@@ -277,8 +277,7 @@ int mmadmm_pcg_refactor_device(mmadmm_pcg *h, const double *val_dev);
  * form when the pattern is made of dense blocks and row_block = BS ("tri_blocks" = 0 forces the generic form).
  * "tri_layout": 1 = the cluster kernels of tri_mode 1 read a level-major (ELL) copy of the factor instead of CSR.
  * "tri_schedule" = row_block | tri_layout << 8 | (tri_mode + 1) << 12 sets the three at once (one rebuild of the schedules;
- * bits 12-13 zero = keep tri_mode).  "tri_proxy" 1: the block dataflow kernel lets a waiting warp poll through one lane first
- * (default 0).  "tri_sf_ctas_per_sm_x2" (1..8, default 2): CTAs of the dataflow kernels = SMs x value / 2.
+ * bits 12-13 zero = keep tri_mode).  "tri_proxy" 1: the dataflow kernels let a waiting warp poll through one lane first (default 0).  "tri_sf_ctas_per_sm_x2" (1..8, default 2): CTAs of the dataflow kernels = SMs x value / 2.
  * "ilu_thread_kernel" 1: the ILU(0) factor kernel with a thread per row even where the warp-per-row form fits (rows of at
  * most 64 entries); same bits (tests).
  * The copies cost memory: chunk-major factor copy = (values 8 B + source index 4 B) per stored entry + padding, once per
