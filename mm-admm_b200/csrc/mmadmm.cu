@@ -3118,19 +3118,26 @@ int m2_init(mmadmm_ctx *ctx) {
                 for (int j = 0; j < V; j++) nb[cur[Fh[(size_t)e * V + i]]++] = Fh[(size_t)e * V + j];
     }
     std::vector<int> adjPtr(P + 1, 0), adjIdx;
-    adjIdx.reserve(nb.size() / 2 + P);
-    for (int p = 0; p < P; p++) {
+#pragma omp parallel for schedule(static)
+    for (int p = 0; p < P; p++) {   // sorted, de-duplicated in place; the count goes to adjPtr[p + 1]
         auto b = nb.begin() + ptr[p], e2 = nb.begin() + ptr[p + 1];
         std::sort(b, e2);
-        auto u = std::unique(b, e2);
-        if (b == u) adjIdx.push_back(p);   // a vertex no element uses still needs its diagonal
-        else adjIdx.insert(adjIdx.end(), b, u);
-        adjPtr[p + 1] = (int)adjIdx.size();
+        const int cnt = (int)(std::unique(b, e2) - b);
+        adjPtr[p + 1] = cnt ? cnt : 1;   // a vertex no element uses still needs its diagonal
+    }
+    for (int p = 0; p < P; p++) adjPtr[p + 1] += adjPtr[p];
+    adjIdx.resize((size_t)adjPtr[P]);
+#pragma omp parallel for schedule(static)
+    for (int p = 0; p < P; p++) {
+        const int cnt = adjPtr[p + 1] - adjPtr[p];
+        if (ptr[p + 1] == ptr[p]) adjIdx[adjPtr[p]] = p;
+        else std::copy(nb.begin() + ptr[p], nb.begin() + ptr[p] + cnt, adjIdx.begin() + adjPtr[p]);
     }
     const size_t nnz = (size_t)D * D * adjIdx.size();
     if (nnz > (size_t)std::numeric_limits<int>::max()) { ctx->err = "Method 2: Jacobian has more than 2^31 entries"; return MMADMM_EINVAL; }
     m.N = P * D; m.nnz = (int)nnz;
     m.rowptr_h.resize((size_t)m.N + 1); m.col_h.resize(nnz); m.val_h.resize(nnz);
+#pragma omp parallel for schedule(static)
     for (int p = 0; p < P; p++) {
         const int a0 = adjPtr[p], deg = adjPtr[p + 1] - a0;
         for (int q = 0; q < D; q++) {
